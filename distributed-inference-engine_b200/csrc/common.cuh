@@ -1,0 +1,127 @@
+// Shared host/device helpers for libdie.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/die.h"
+
+namespace die {
+
+// ---- error plumbing ---------------------------------------------------------------------
+char* err_buf();                       // thread-local, 512 bytes
+void count_launch(unsigned n = 1);     // gpu_launches accounting for bench.py
+
+#define DIE_FAIL(code, ...)                                   \
+    do {                                                      \
+        snprintf(::die::err_buf(), 512, __VA_ARGS__);         \
+        return (code);                                        \
+    } while (0)
+
+#define DIE_CUDA(expr)                                                                   \
+    do {                                                                                 \
+        cudaError_t e__ = (expr);                                                        \
+        if (e__ != cudaSuccess)                                                          \
+            DIE_FAIL(DIE_ERR_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #expr,          \
+                     cudaGetErrorString(e__));                                           \
+    } while (0)
+
+#define DIE_LAUNCH_CHECK()                                                               \
+    do {                                                                                 \
+        ::die::count_launch();                                                           \
+        cudaError_t e__ = cudaGetLastError();                                            \
+        if (e__ != cudaSuccess)                                                          \
+            DIE_FAIL(DIE_ERR_CUDA, "%s:%d kernel launch -> %s", __FILE__, __LINE__,      \
+                     cudaGetErrorString(e__));                                           \
+    } while (0)
+
+#define DIE_TRY(expr)                        \
+    do {                                     \
+        die_status_t s__ = (expr);           \
+        if (s__ != DIE_OK) return s__;       \
+    } while (0)
+
+inline int num_sms() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// ---- device helpers ---------------------------------------------------------------------
+struct __align__(16) u128 {
+    unsigned long long lo, hi;
+};
+
+#ifdef __CUDACC__
+__device__ __forceinline__ u128 ld128(const void* p) {
+    u128 r;
+    asm volatile("ld.global.v2.u64 {%0, %1}, [%2];" : "=l"(r.lo), "=l"(r.hi) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ void st128(void* p, u128 v) {
+    asm volatile("st.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(v.lo), "l"(v.hi) : "memory");
+}
+// 128-bit compare-and-swap (ATOMG.E.CAS.128 on sm_100a).
+__device__ __forceinline__ u128 cas128(void* addr, u128 cmp, u128 val) {
+    u128 old;
+    asm volatile(
+        "{\n\t.reg .b128 c, v, o;\n\t"
+        "mov.b128 c, {%3, %4};\n\t"
+        "mov.b128 v, {%5, %6};\n\t"
+        "atom.global.cas.b128 o, [%2], c, v;\n\t"
+        "mov.b128 {%0, %1}, o;\n\t}"
+        : "=l"(old.lo), "=l"(old.hi)
+        : "l"(addr), "l"(cmp.lo), "l"(cmp.hi), "l"(val.lo), "l"(val.hi)
+        : "memory");
+    return old;
+}
+// streaming 128-bit accesses that do not allocate in L1 (read-once / write-once payload)
+__device__ __forceinline__ int4 ldg_stream(const int4* p) {
+    int4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void stg_stream(int4* p, const int4& v) {
+    asm volatile("st.global.L1::no_allocate.v4.s32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
+                 "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31u; }
+
+// block-wide exclusive scan of one unsigned per thread (1024 threads); returns the block total
+__device__ __forceinline__ unsigned block_scan_1024(unsigned cnt, unsigned& excl, unsigned* s_warp) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned w = s_warp[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned v = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += v;
+        }
+        s_warp[lane] = w;  // inclusive over warps
+    }
+    __syncthreads();
+    excl = (warp ? s_warp[warp - 1] : 0u) + (incl - cnt);
+    return s_warp[31];
+}
+#endif
+
+}  // namespace die

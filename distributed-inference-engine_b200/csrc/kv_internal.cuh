@@ -1,0 +1,174 @@
+// K2/K3: GPU-resident KV store with the reference's LRU + TTL semantics (src/kvstore.py:26-236).
+//
+// HBM layout
+//   slots : capacity x 64 B (power-of-two capacity >= 2*max_size), open addressing, linear probing.
+//           sector 0 = {fingerprint (128-bit MD5 of the key), created_at f64, ttl f64}   (read-mostly)
+//           sector 1 = {lru stamp u64, value u64, last_accessed f64, access_count u32}  (hot, mutable)
+//           fingerprint (0,0) = EMPTY, (~0,~0) = TOMBSTONE.
+//   log   : ring of uint32 slot indices indexed by LRU stamp.  Every touch (get hit, insert) of
+//           batch op i gets stamp t+i and writes log[t+i] = slot.  The reference's OrderedDict
+//           (_access_order, kvstore.py:71-78) is the subsequence of log records that are still
+//           current (slot.stamp == position); its head (next victim, kvstore.py:89-91) is the first
+//           current record at or after `head`.  Stale records are skipped lazily.
+//   rows  : optional free-list of result-row handles (pipeline mode): an insert pops a row for its
+//           value, every delete/eviction pushes it back.
+//
+// Batch semantics ("as if applied in request order")
+//   get   : order-independent once stamps are op indices (atomicMax) -> fully parallel.
+//   set   : parallel fast path when provably identical to the sequential result, i.e. no key of
+//           the batch that already lives in the table sits inside the window of log records the
+//           batch's evictions can reach, and that window does not run out of pre-batch entries.
+//           Otherwise an exact sequential kernel replays the ops one by one (kvstore.py:104-134),
+//           including the reference's StopIteration when nothing stamped is left to evict.
+#pragma once
+#include <math.h>
+
+#include "common.cuh"
+
+namespace die {
+
+struct __align__(64) Slot {
+    unsigned long long fp_lo, fp_hi;
+    double created_at;
+    double ttl;                // NaN = None
+    unsigned long long stamp;  // 0 = not in the LRU order (batch_set insert not yet stamped)
+    unsigned long long value;
+    double last_accessed;
+    unsigned int access_count;
+    unsigned int pad;
+};
+static_assert(sizeof(Slot) == 64, "slot must be one 64-byte record");
+
+struct KvState {
+    // persistent counters
+    unsigned long long size, hits, misses, evictions, head, n_tomb, n_empty_claimed, free_top;
+    unsigned long long status, slow_batches, n_dropped_last;
+    // per set-batch scratch (reset by the last kernel of each batch)
+    unsigned long long n_pre, n_absent, min_prev, n_new, conflict, n_dropped;
+};
+
+struct KvView {
+    Slot* slots;
+    uint32_t* log;
+    KvState* st;
+    uint32_t* free_rows;       // nullptr unless the table manages result rows
+    unsigned long long mask;   // capacity - 1
+    unsigned long long rmask;  // ring_cap - 1
+    unsigned long long max_size;
+    double default_ttl;
+};
+
+#ifdef __CUDACC__
+constexpr unsigned long long FP_TOMB_WORD = ~0ull;
+__device__ __forceinline__ bool fp_eq(u128 a, u128 b) { return a.lo == b.lo && a.hi == b.hi; }
+__device__ __forceinline__ bool fp_empty(u128 a) { return a.lo == 0ull && a.hi == 0ull; }
+__device__ __forceinline__ bool fp_tomb(u128 a) { return a.lo == FP_TOMB_WORD && a.hi == FP_TOMB_WORD; }
+__device__ __forceinline__ u128 fp_of(uint4 d) {
+    return u128{(unsigned long long)d.x | ((unsigned long long)d.y << 32),
+                (unsigned long long)d.z | ((unsigned long long)d.w << 32)};
+}
+
+__device__ __forceinline__ u128 ld_fp(const Slot* s) {
+    u128 r;  // .cg: slots are mutated by other SMs inside the same kernel, never trust L1
+    asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(r.lo), "=l"(r.hi) : "l"(s) : "memory");
+    return r;
+}
+__device__ __forceinline__ unsigned long long ld_u64_cg(const unsigned long long* p) {
+    unsigned long long r;
+    asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(r) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ void ld_created_ttl(const Slot* s, double& created, double& ttl) {
+    asm volatile("ld.global.cg.v2.f64 {%0, %1}, [%2];"
+                 : "=d"(created), "=d"(ttl)
+                 : "l"(&s->created_at)
+                 : "memory");
+}
+
+// Linear probe for `key`; returns slot index or -1 (stops at the first EMPTY slot).
+__device__ __forceinline__ long long kv_find(const KvView& kv, u128 key) {
+    unsigned long long s = key.lo & kv.mask;
+    for (unsigned long long n = 0; n <= kv.mask; ++n) {
+        const u128 fp = ld_fp(&kv.slots[s]);
+        if (fp_eq(fp, key)) return (long long)s;
+        if (fp_empty(fp)) return -1;
+        s = (s + 1) & kv.mask;
+    }
+    return -1;
+}
+
+__device__ __forceinline__ bool ttl_expired(double now, double created, double ttl) {
+    return !isnan(ttl) && (now - created) > ttl;  // strict '>' (kvstore.py:204)
+}
+
+__device__ __forceinline__ void warp_add(unsigned long long* ctr, bool pred) {
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m && lane_id() == 0) atomicAdd(ctr, (unsigned long long)__popc(m));
+}
+__device__ __forceinline__ void warp_sub(unsigned long long* ctr, bool pred) {
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m && lane_id() == 0) atomicAdd(ctr, (unsigned long long)(-(long long)__popc(m)));
+}
+
+// result-row handles (pipeline mode).  A kernel either pushes or pops, never both, except the
+// single-threaded sequential replay.
+__device__ __forceinline__ void release_row(const KvView& kv, unsigned long long value) {
+    if (kv.free_rows) kv.free_rows[atomicAdd(&kv.st->free_top, 1ull)] = (uint32_t)value;
+}
+__device__ __forceinline__ unsigned long long acquire_row(const KvView& kv) {
+    return kv.free_rows[atomicAdd(&kv.st->free_top, (unsigned long long)(-1ll)) - 1ull];
+}
+#endif  // __CUDACC__
+
+}  // namespace die
+
+struct die_kv {
+    int device;
+    uint64_t max_size, capacity, ring_cap;
+    double default_ttl;
+    die::Slot* slots;
+    uint32_t* log;
+    die::KvState* st;
+    uint32_t* free_rows;  // pipeline mode only
+    uint64_t n_rows;
+    uint64_t tail;        // next LRU stamp to hand out (host-tracked: every batch op consumes one)
+    uint64_t head_lb;     // host lower bound of the device-side head
+    uint64_t claims_ub;   // upper bound of EMPTY slots consumed since the last rebuild
+    uint64_t live_at_rebuild;
+    uint64_t max_chunk;   // largest batch one launch sequence may take
+    int32_t* op_slot;     // scratch [op_cap]
+    uint64_t op_cap;
+    uint64_t dropped_prefix;  // dropped values written by earlier chunks of the last set batch
+};
+
+namespace die {
+
+inline KvView view_of(const die_kv* kv) {
+    KvView v;
+    v.slots = kv->slots;
+    v.log = kv->log;
+    v.st = kv->st;
+    v.free_rows = kv->free_rows;
+    v.mask = kv->capacity - 1;
+    v.rmask = kv->ring_cap - 1;
+    v.max_size = kv->max_size;
+    v.default_ttl = kv->default_ttl;
+    return v;
+}
+
+// n_rows > 0: the table hands out result-row handles in [0, n_rows) as values (pipeline mode).
+die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_rows, die_kv** out);
+
+// Batched KVCache.get; stamps are kv->tail + i.  Advances kv->tail by B.
+die_status_t kv_get_batch_impl(die_kv* kv, const uint32_t* digests, int32_t B, double now, uint8_t* hit_out,
+                               uint64_t* value_out, int32_t* slot_out, cudaStream_t s);
+
+// Batched KVCache.set.  skip (optional, [M]): ops with skip[i] == 1 are not applied (their stamp
+// is still reserved).  known_absent != 0: the caller guarantees that no active key lives in the
+// table (true for the misses of the get batch just before) and n_active_dev holds their count.
+die_status_t kv_set_batch_impl(die_kv* kv, const uint32_t* digests, const uint64_t* values, const double* ttl,
+                               int32_t M, double now, int32_t deferred, const uint8_t* skip, int known_absent,
+                               const uint32_t* n_active_dev, int32_t* slot_out, uint64_t* dropped_out,
+                               cudaStream_t s);
+
+}  // namespace die

@@ -1,0 +1,914 @@
+// K2/K3 kernels + host entry points of the KV store (src/kvstore.py:26-236).
+// Layout and batch semantics are documented at the top of kv_internal.cuh.
+#include <algorithm>
+#include <vector>
+
+#include "kv_internal.cuh"
+
+namespace die {
+
+constexpr int KV_THREADS = 256;
+
+// ------------------------------------------------------------------------------------------------
+// get / contains  (kvstore.py:136-164, 221-228)
+// ------------------------------------------------------------------------------------------------
+template <bool CONTAINS>
+__global__ void __launch_bounds__(KV_THREADS)
+kv_get_kernel(KvView kv, const uint4* __restrict__ digests, int B, double now, unsigned long long t,
+              uint8_t* __restrict__ code_out, unsigned long long* __restrict__ value_out,
+              int32_t* __restrict__ slot_out) {
+    const int i = blockIdx.x * KV_THREADS + threadIdx.x;
+    const bool active = i < B;
+    int code = 0;
+    unsigned long long value = 0;
+    long long s = -1;
+    if (active) {
+        const u128 key = fp_of(digests[i]);
+        s = kv_find(kv, key);
+        if (s >= 0) {
+            Slot* sl = &kv.slots[s];
+            double created, ttl;
+            ld_created_ttl(sl, created, ttl);
+            if (ttl_expired(now, created, ttl)) {
+                // delete(key) (kvstore.py:153-156); exactly one of several duplicate ops wins
+                const u128 old = cas128(sl, key, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+                if (fp_eq(old, key)) {
+                    value = ld_u64_cg(&sl->value);
+                    sl->stamp = 0ull;
+                    release_row(kv, value);
+                    code = 2;
+                }
+                s = -1;
+            } else {
+                code = 1;
+                value = ld_u64_cg(&sl->value);
+                if (!CONTAINS) {
+                    const unsigned long long stamp = t + (unsigned long long)i;
+                    atomicMax(&sl->stamp, stamp);  // move_to_end: the last toucher wins
+                    kv.log[stamp & kv.rmask] = (uint32_t)s;
+                    atomicAdd(&sl->access_count, 1u);
+                    sl->last_accessed = now;
+                }
+            }
+        }
+        code_out[i] = (uint8_t)code;
+        if (value_out) value_out[i] = value;
+        if (slot_out) slot_out[i] = code == 1 ? (int32_t)s : -1;
+    }
+    if (!CONTAINS) {
+        warp_add(&kv.st->hits, active && code == 1);
+        warp_add(&kv.st->misses, active && code != 1);
+    }
+    const bool deleted = active && code == 2;
+    warp_sub(&kv.st->size, deleted);
+    warp_add(&kv.st->n_tomb, deleted);
+}
+
+// delete (kvstore.py:178-187)
+__global__ void __launch_bounds__(KV_THREADS)
+kv_delete_kernel(KvView kv, const uint4* __restrict__ digests, int B, uint8_t* __restrict__ deleted_out,
+                 unsigned long long* __restrict__ value_out) {
+    const int i = blockIdx.x * KV_THREADS + threadIdx.x;
+    const bool active = i < B;
+    bool deleted = false;
+    if (active) {
+        const u128 key = fp_of(digests[i]);
+        const long long s = kv_find(kv, key);
+        unsigned long long value = 0;
+        if (s >= 0) {
+            Slot* sl = &kv.slots[s];
+            const u128 old = cas128(sl, key, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+            if (fp_eq(old, key)) {
+                value = ld_u64_cg(&sl->value);
+                sl->stamp = 0ull;
+                release_row(kv, value);
+                deleted = true;
+            }
+        }
+        deleted_out[i] = deleted ? 1 : 0;
+        if (value_out) value_out[i] = value;
+    }
+    warp_sub(&kv.st->size, deleted);
+    warp_add(&kv.st->n_tomb, deleted);
+}
+
+// __len__ purge (kvstore.py:230-236): every expired entry is deleted.
+__global__ void __launch_bounds__(KV_THREADS)
+kv_purge_kernel(KvView kv, double now, unsigned long long* __restrict__ purged_out,
+                unsigned long long purged_cap, unsigned long long* __restrict__ n_purged) {
+    const unsigned long long cap = kv.mask + 1;
+    for (unsigned long long s = blockIdx.x * (unsigned long long)KV_THREADS + threadIdx.x; s < cap;
+         s += (unsigned long long)gridDim.x * KV_THREADS) {
+        Slot* sl = &kv.slots[s];
+        const u128 fp = ld_fp(sl);
+        if (fp_empty(fp) || fp_tomb(fp)) continue;
+        if (ttl_expired(now, sl->created_at, sl->ttl)) {
+            const unsigned long long value = sl->value;
+            st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+            sl->stamp = 0ull;
+            release_row(kv, value);
+            atomicAdd(&kv.st->size, (unsigned long long)(-1ll));
+            atomicAdd(&kv.st->n_tomb, 1ull);
+            const unsigned long long k = atomicAdd(n_purged, 1ull);
+            if (purged_out && k < purged_cap) purged_out[k] = value;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// set, phase A: read-only precheck.  Finds the batch keys that already live in the table.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(KV_THREADS)
+kv_set_precheck_kernel(KvView kv, const uint4* __restrict__ digests, int M, const uint8_t* __restrict__ skip,
+                       int32_t* __restrict__ op_slot) {
+    const int i = blockIdx.x * KV_THREADS + threadIdx.x;
+    const bool active = i < M && !(skip && skip[i] == 1);
+    bool pre = false;
+    if (active) {
+        const long long s = kv_find(kv, fp_of(digests[i]));
+        op_slot[i] = (int32_t)s;
+        if (s >= 0) {
+            pre = true;
+            const unsigned long long p = ld_u64_cg(&kv.slots[s].stamp);
+            if (p > 0) atomicMin(&kv.st->min_prev, p);
+        }
+    }
+    warp_add(&kv.st->n_pre, active && pre);
+    warp_add(&kv.st->n_absent, active && !pre);
+}
+
+// ------------------------------------------------------------------------------------------------
+// LRU window walk, one CTA of 1024 threads.  Visits log records from `head` in stamp order and
+// selects the first E current ones (the E least-recently-used entries).  apply=true evicts them.
+// Returns (to all threads) one past the E-th current record, or ~0 when fewer than E exist
+// before `limit`.
+// ------------------------------------------------------------------------------------------------
+constexpr int WIN_THREADS = 1024;
+constexpr int WIN_ITEMS = 4;
+
+__device__ __forceinline__ bool record_current(const KvView& kv, unsigned long long p, uint32_t& slot) {
+    slot = kv.log[p & kv.rmask];
+    return (unsigned long long)slot <= kv.mask && ld_u64_cg(&kv.slots[slot].stamp) == p;
+}
+
+__device__ __forceinline__ void evict_slot(const KvView& kv, uint32_t s, unsigned long long* dropped_out) {
+    Slot* sl = &kv.slots[s];
+    const unsigned long long value = sl->value;
+    if (dropped_out) dropped_out[atomicAdd(&kv.st->n_dropped, 1ull)] = value;
+    release_row(kv, value);
+    st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+    sl->stamp = 0ull;
+}
+
+__device__ unsigned long long lru_window_select(const KvView& kv, unsigned long long head,
+                                                unsigned long long limit, unsigned long long E, bool apply,
+                                                unsigned long long* dropped_out,
+                                                unsigned long long* first_current /*optional*/) {
+    __shared__ unsigned int s_warp[32];
+    __shared__ unsigned long long s_hnew;
+    __shared__ unsigned long long s_first;
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        s_hnew = ~0ull;
+        s_first = ~0ull;
+    }
+    __syncthreads();
+    unsigned long long found = 0, pos = head;
+    while (found < E && pos < limit) {
+        bool valid[WIN_ITEMS];
+        uint32_t slot[WIN_ITEMS];
+        unsigned cnt = 0;
+#pragma unroll
+        for (int k = 0; k < WIN_ITEMS; ++k) {
+            const unsigned long long p = pos + (unsigned long long)tid * WIN_ITEMS + k;
+            valid[k] = p < limit && record_current(kv, p, slot[k]);
+            cnt += valid[k];
+        }
+        unsigned excl;
+        const unsigned total = block_scan_1024(cnt, excl, s_warp);
+        unsigned long long rank = found + excl;
+#pragma unroll
+        for (int k = 0; k < WIN_ITEMS; ++k) {
+            if (!valid[k]) continue;
+            const unsigned long long p = pos + (unsigned long long)tid * WIN_ITEMS + k;
+            if (rank == 0) s_first = p;
+            if (rank < E) {
+                if (apply) evict_slot(kv, slot[k], dropped_out);
+                if (rank == E - 1) s_hnew = p + 1;
+            }
+            ++rank;
+        }
+        found += total;
+        pos += (unsigned long long)WIN_THREADS * WIN_ITEMS;
+        __syncthreads();
+    }
+    __syncthreads();
+    if (first_current) *first_current = s_first;
+    return s_hnew;
+}
+
+// set, phase B: can the batch's evictions reach a key of this batch, or run out of victims?
+__global__ void __launch_bounds__(WIN_THREADS)
+kv_set_window_kernel(KvView kv, unsigned long long t, const uint32_t* __restrict__ n_active_dev, int deferred) {
+    KvState* st = kv.st;
+    __shared__ unsigned long long s_first;
+    if (deferred == 2) {  // set(..., batch=True) on its own: entries stay outside the LRU order
+        if (threadIdx.x == 0) st->conflict = 1;
+        return;
+    }
+    const unsigned long long size = st->size;
+    const unsigned long long n_absent = n_active_dev ? (unsigned long long)*n_active_dev : st->n_absent;
+    const unsigned long long n_pre = n_active_dev ? 0ull : st->n_pre;
+    const unsigned long long min_prev = st->min_prev;
+    const unsigned long long head = st->head;
+    const unsigned long long e_ub = size + n_absent > kv.max_size ? size + n_absent - kv.max_size : 0ull;
+    if (e_ub == 0) return;  // conflict stays 0
+    const unsigned long long h_ub = lru_window_select(kv, head, t, e_ub, false, nullptr, &s_first);
+    if (threadIdx.x == 0) {
+        if (h_ub == ~0ull)
+            st->conflict = 1;  // fewer stamped pre-batch entries than evictions that may be needed
+        else if (n_pre > 0 && min_prev < h_ub)
+            st->conflict = 1;  // an entry this batch re-sets is within reach of its evictions
+        if (s_first != ~0ull && s_first > head) st->head = s_first;  // drop leading stale records
+    }
+}
+
+// set, phase C: parallel find-or-claim + stamp.  No-op when the batch goes to the sequential path.
+// have_precheck == 0: every active key is known to be absent (no precheck was run).
+__global__ void __launch_bounds__(KV_THREADS)
+kv_set_claim_kernel(KvView kv, const uint4* __restrict__ digests, int M, double now, unsigned long long t,
+                    int own_values, const uint8_t* __restrict__ skip, int have_precheck,
+                    int32_t* __restrict__ op_slot,
+                    int32_t* __restrict__ slot_out, unsigned long long* __restrict__ dropped_out) {
+    if (kv.st->conflict) return;
+    const int i = blockIdx.x * KV_THREADS + threadIdx.x;
+    const bool active = i < M && !(skip && skip[i] == 1);
+    bool claimed = false, from_empty = false;
+    if (active) {
+        const u128 key = fp_of(digests[i]);
+        long long s = have_precheck ? op_slot[i] : -1;
+        const bool pre = s >= 0;
+        if (!pre) {
+            // insert: claim the first free slot of the probe chain with a 128-bit CAS on the fingerprint
+            for (;;) {
+                unsigned long long cur = key.lo & kv.mask;
+                long long first_free = -1;
+                bool first_free_empty = false, found = false;
+                for (unsigned long long n = 0; n <= kv.mask; ++n) {
+                    const u128 fp = ld_fp(&kv.slots[cur]);
+                    if (fp_eq(fp, key)) {  // a duplicate op of this batch already inserted it
+                        s = (long long)cur;
+                        found = true;
+                        break;
+                    }
+                    if (fp_tomb(fp) && first_free < 0) first_free = (long long)cur;
+                    if (fp_empty(fp)) {
+                        if (first_free < 0) {
+                            first_free = (long long)cur;
+                            first_free_empty = true;
+                        }
+                        break;
+                    }
+                    cur = (cur + 1) & kv.mask;
+                }
+                if (found) break;
+                if (first_free < 0) continue;  // cannot happen: the host keeps >= capacity/4 EMPTY slots
+                const u128 expect = first_free_empty ? u128{0ull, 0ull} : u128{FP_TOMB_WORD, FP_TOMB_WORD};
+                const u128 old = cas128(&kv.slots[first_free], expect, key);
+                if (fp_eq(old, expect)) {
+                    s = first_free;
+                    claimed = true;
+                    from_empty = first_free_empty;
+                    break;
+                }
+                if (fp_eq(old, key)) {
+                    s = first_free;
+                    break;
+                }
+                // somebody else's key took the slot: walk the chain again
+            }
+        }
+        Slot* sl = &kv.slots[s];
+        const unsigned long long stamp = t + (unsigned long long)i;
+        const unsigned long long old_stamp = atomicMax(&sl->stamp, stamp);
+        const bool first_touch = pre && old_stamp < t;  // set of an existing key = delete + insert
+        if (first_touch && dropped_out && !own_values)
+            dropped_out[atomicAdd(&kv.st->n_dropped, 1ull)] = ld_u64_cg(&sl->value);
+        if (claimed || first_touch) {
+            sl->created_at = now;
+            sl->last_accessed = now;
+            sl->access_count = 0u;
+            if (own_values) {  // the table owns the value: a result-row handle, or the slot index
+                if (claimed) sl->value = kv.free_rows ? acquire_row(kv) : (unsigned long long)s;
+                sl->ttl = kv.default_ttl;
+            }
+        }
+        kv.log[stamp & kv.rmask] = (uint32_t)s;
+        op_slot[i] = (int32_t)s;
+        if (slot_out) slot_out[i] = (int32_t)s;
+    } else if (i < M && slot_out) {
+        slot_out[i] = -1;
+    }
+    warp_add(&kv.st->n_new, active && claimed);
+    warp_add(&kv.st->size, active && claimed);
+    warp_add(&kv.st->n_empty_claimed, active && claimed && from_empty);
+    warp_sub(&kv.st->n_tomb, active && claimed && !from_empty);
+}
+
+// set, phase C2: the last op that touched a slot (largest stamp) owns its value / ttl.
+__global__ void __launch_bounds__(KV_THREADS)
+kv_set_finalize_kernel(KvView kv, int M, unsigned long long t, const unsigned long long* __restrict__ values,
+                       const double* __restrict__ ttl, const uint8_t* __restrict__ skip,
+                       const int32_t* __restrict__ op_slot) {
+    if (kv.st->conflict) return;
+    const int i = blockIdx.x * KV_THREADS + threadIdx.x;
+    if (i >= M || (skip && skip[i] == 1)) return;
+    const int32_t s = op_slot[i];
+    Slot* sl = &kv.slots[s];
+    if (ld_u64_cg(&sl->stamp) != t + (unsigned long long)i) return;
+    if (values) sl->value = values[i];
+    const double x = ttl ? ttl[i] : NAN;
+    sl->ttl = isnan(x) ? kv.default_ttl : x;
+}
+
+// Exact sequential replay of a set batch (kvstore.py:104-134, 170-176), one thread.
+__device__ void kv_set_sequential(const KvView& kv, const uint4* digests, const unsigned long long* values,
+                                  const double* ttl, int M, double now, unsigned long long t, int deferred,
+                                  const uint8_t* skip, int32_t* slot_out, unsigned long long* dropped_out) {
+    KvState* st = kv.st;
+    unsigned long long size = st->size, head = st->head, evictions = st->evictions;
+    long long n_tomb = (long long)st->n_tomb;
+    unsigned long long n_empty_claimed = st->n_empty_claimed;
+    const bool own_values = values == nullptr;
+    bool aborted = false;
+    int i = 0;
+    for (; i < M; ++i) {
+        if (skip && skip[i] == 1) {
+            if (slot_out) slot_out[i] = -1;
+            continue;
+        }
+        const u128 key = fp_of(digests[i]);
+        long long s = kv_find(kv, key);
+        if (s >= 0) {  // if key in self.cache: self.delete(key)
+            Slot* sl = &kv.slots[s];
+            const unsigned long long v = sl->value;
+            if (dropped_out && !own_values) dropped_out[st->n_dropped++] = v;
+            release_row(kv, v);
+            st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+            sl->stamp = 0ull;
+            --size;
+            ++n_tomb;
+        }
+        if (size >= kv.max_size) {  // _evict_if_needed
+            ++evictions;            // counted before the pop (kvstore.py:87)
+            const unsigned long long bound = deferred ? t : t + (unsigned long long)i;
+            long long victim = -1;
+            while (head < bound) {
+                const unsigned long long p = head++;
+                uint32_t r;
+                if (record_current(kv, p, r)) {
+                    victim = (long long)r;
+                    break;
+                }
+            }
+            if (victim < 0) {  // next(iter(OrderedDict())) -> StopIteration
+                st->status = DIE_ERR_STOP_ITERATION;
+                aborted = true;
+                break;
+            }
+            Slot* v = &kv.slots[victim];
+            const unsigned long long vv = v->value;
+            if (dropped_out) dropped_out[st->n_dropped++] = vv;
+            release_row(kv, vv);
+            st128(v, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+            v->stamp = 0ull;
+            --size;
+            ++n_tomb;
+        }
+        unsigned long long cur = key.lo & kv.mask;
+        for (;;) {
+            const u128 fp = ld_fp(&kv.slots[cur]);
+            if (fp_empty(fp)) {
+                ++n_empty_claimed;
+                break;
+            }
+            if (fp_tomb(fp)) {
+                --n_tomb;
+                break;
+            }
+            cur = (cur + 1) & kv.mask;
+        }
+        Slot* sl = &kv.slots[cur];
+        const double x = ttl ? ttl[i] : NAN;
+        sl->created_at = now;
+        sl->ttl = isnan(x) ? kv.default_ttl : x;
+        sl->value = values ? values[i] : (kv.free_rows ? acquire_row(kv) : cur);
+        sl->last_accessed = now;
+        sl->access_count = 0u;
+        if (deferred) {
+            sl->stamp = 0ull;
+        } else {
+            const unsigned long long stamp = t + (unsigned long long)i;
+            sl->stamp = stamp;
+            kv.log[stamp & kv.rmask] = (uint32_t)cur;
+        }
+        st128(sl, key);
+        ++size;
+        if (slot_out) slot_out[i] = (int32_t)cur;
+    }
+    if (aborted && slot_out)
+        for (int j = i; j < M; ++j) slot_out[j] = -1;
+    if (deferred == 1 && !aborted) {  // for key in items: self._update_access(key)
+        for (int j = 0; j < M; ++j) {
+            if (skip && skip[j] == 1) continue;
+            const long long s = kv_find(kv, fp_of(digests[j]));
+            if (s < 0) continue;
+            const unsigned long long stamp = t + (unsigned long long)j;
+            kv.slots[s].stamp = stamp;
+            kv.log[stamp & kv.rmask] = (uint32_t)s;
+        }
+    }
+    st->size = size;
+    st->head = head;
+    st->evictions = evictions;
+    st->n_tomb = (unsigned long long)n_tomb;
+    st->n_empty_claimed = n_empty_claimed;
+    st->slow_batches += 1;
+}
+
+// set, phase D: evict the E least-recently-used entries, or run the sequential replay.
+__global__ void __launch_bounds__(WIN_THREADS)
+kv_set_evict_kernel(KvView kv, const uint4* __restrict__ digests, const unsigned long long* __restrict__ values,
+                    const double* __restrict__ ttl, int M, double now, unsigned long long t, int deferred,
+                    const uint8_t* __restrict__ skip, int32_t* __restrict__ slot_out,
+                    unsigned long long* __restrict__ dropped_out) {
+    KvState* st = kv.st;
+    const unsigned long long conflict = st->conflict, size = st->size, head = st->head;
+    __syncthreads();
+    if (conflict) {
+        if (threadIdx.x == 0)
+            kv_set_sequential(kv, digests, values, ttl, M, now, t, deferred, skip, slot_out, dropped_out);
+    } else {
+        const unsigned long long E = size > kv.max_size ? size - kv.max_size : 0ull;
+        if (E > 0) {
+            const unsigned long long hnew = lru_window_select(kv, head, t, E, true, dropped_out, nullptr);
+            if (threadIdx.x == 0) {
+                st->size = size - E;
+                st->evictions += E;
+                st->n_tomb += E;
+                if (hnew != ~0ull) st->head = hnew;
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {  // hand the scratch back clean for the next batch
+        st->n_dropped_last = st->n_dropped;
+        st->n_pre = st->n_absent = st->n_new = st->conflict = st->n_dropped = 0ull;
+        st->min_prev = ~0ull;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// maintenance: re-append the current LRU records at the tail of a fresh ring (order kept)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(WIN_THREADS)
+kv_compact_kernel(KvView kv, uint32_t* __restrict__ new_log, unsigned long long tail,
+                  unsigned long long* __restrict__ n_kept) {
+    __shared__ unsigned int s_warp[32];
+    const int tid = threadIdx.x;
+    unsigned long long kept = 0;
+    const unsigned long long head = kv.st->head;
+    __syncthreads();
+    for (unsigned long long pos = head; pos < tail; pos += (unsigned long long)WIN_THREADS * WIN_ITEMS) {
+        bool valid[WIN_ITEMS];
+        uint32_t slot[WIN_ITEMS];
+        unsigned cnt = 0;
+#pragma unroll
+        for (int k = 0; k < WIN_ITEMS; ++k) {
+            const unsigned long long p = pos + (unsigned long long)tid * WIN_ITEMS + k;
+            valid[k] = p < tail && record_current(kv, p, slot[k]);
+            cnt += valid[k];
+        }
+        unsigned excl;
+        const unsigned total = block_scan_1024(cnt, excl, s_warp);
+        unsigned long long rank = kept + excl;
+        __syncthreads();  // every validity check of this tile is done before any stamp moves
+#pragma unroll
+        for (int k = 0; k < WIN_ITEMS; ++k) {
+            if (!valid[k]) continue;
+            const unsigned long long np = tail + rank;  // beyond every old position: no aliasing
+            new_log[np & kv.rmask] = slot[k];
+            kv.slots[slot[k]].stamp = np;
+            ++rank;
+        }
+        kept += total;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        *n_kept = kept;
+        kv.st->head = tail;
+    }
+}
+
+// maintenance: rebuild the table without tombstones
+__global__ void __launch_bounds__(KV_THREADS)
+kv_rehash_kernel(KvView kv, const Slot* __restrict__ old_slots, unsigned long long old_cap) {
+    for (unsigned long long o = blockIdx.x * (unsigned long long)KV_THREADS + threadIdx.x; o < old_cap;
+         o += (unsigned long long)gridDim.x * KV_THREADS) {
+        const Slot* src = &old_slots[o];
+        const u128 key{src->fp_lo, src->fp_hi};
+        if (fp_empty(key) || fp_tomb(key)) continue;
+        unsigned long long cur = key.lo & kv.mask;
+        for (;;) {
+            const u128 old = cas128(&kv.slots[cur], u128{0ull, 0ull}, key);
+            if (fp_empty(old)) break;
+            cur = (cur + 1) & kv.mask;
+        }
+        Slot* dst = &kv.slots[cur];
+        const unsigned long long stamp = src->stamp;
+        dst->created_at = src->created_at;
+        dst->ttl = src->ttl;
+        dst->stamp = stamp;
+        dst->value = src->value;
+        dst->last_accessed = src->last_accessed;
+        dst->access_count = src->access_count;
+        if (stamp) kv.log[stamp & kv.rmask] = (uint32_t)cur;
+    }
+}
+
+__global__ void kv_state_init_kernel(KvView kv, unsigned long long head, unsigned long long n_rows) {
+    KvState* st = kv.st;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        st->hits = st->misses = st->evictions = 0ull;
+        st->size = 0ull;
+        st->head = head;
+        st->n_tomb = st->n_empty_claimed = 0ull;
+        st->free_top = n_rows;
+        st->n_pre = st->n_absent = st->n_new = st->conflict = st->n_dropped = 0ull;
+        st->min_prev = ~0ull;
+    }
+    for (unsigned long long r = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; r < n_rows;
+         r += (unsigned long long)gridDim.x * blockDim.x)
+        kv.free_rows[r] = (uint32_t)(n_rows - 1 - r);  // row 0 is popped first
+}
+
+static uint64_t next_pow2(uint64_t x) {
+    uint64_t p = 1;
+    while (p < x) p <<= 1;
+    return p;
+}
+
+die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_rows, die_kv** out) {
+    if (max_size > (1ull << 30)) DIE_FAIL(DIE_ERR_TOO_LARGE, "die_kv_create: max_size > 2^30");
+    die_kv* kv = new die_kv();
+    memset(kv, 0, sizeof(*kv));
+    DIE_CUDA(cudaGetDevice(&kv->device));
+    kv->max_size = max_size;
+    kv->default_ttl = default_ttl;
+    kv->capacity = next_pow2(std::max<uint64_t>(2 * max_size, 4096));
+    kv->ring_cap = next_pow2(std::max<uint64_t>(4 * max_size, 1ull << 20));
+    kv->max_chunk = std::min<uint64_t>(kv->capacity / 8, std::min<uint64_t>(kv->ring_cap / 4, 1ull << 22));
+    kv->tail = 1;
+    kv->head_lb = 1;
+    kv->n_rows = n_rows;
+    DIE_CUDA(cudaMalloc(&kv->slots, kv->capacity * sizeof(Slot)));
+    DIE_CUDA(cudaMalloc(&kv->log, kv->ring_cap * sizeof(uint32_t)));
+    DIE_CUDA(cudaMalloc(&kv->st, sizeof(KvState)));
+    if (n_rows) DIE_CUDA(cudaMalloc(&kv->free_rows, n_rows * sizeof(uint32_t)));
+    DIE_CUDA(cudaMemset(kv->slots, 0, kv->capacity * sizeof(Slot)));
+    DIE_CUDA(cudaMemset(kv->log, 0xff, kv->ring_cap * sizeof(uint32_t)));
+    DIE_CUDA(cudaMemset(kv->st, 0, sizeof(KvState)));
+    kv_state_init_kernel<<<n_rows ? 256 : 1, 256>>>(view_of(kv), 1ull, n_rows);
+    DIE_LAUNCH_CHECK();
+    DIE_CUDA(cudaDeviceSynchronize());
+    *out = kv;
+    return DIE_OK;
+}
+
+static die_status_t ensure_scratch(die_kv* kv, uint64_t n) {
+    if (n <= kv->op_cap) return DIE_OK;
+    const uint64_t cap = next_pow2(std::max<uint64_t>(n, 1024));
+    if (kv->op_slot) DIE_CUDA(cudaFree(kv->op_slot));
+    kv->op_slot = nullptr;
+    kv->op_cap = 0;
+    DIE_CUDA(cudaMalloc(&kv->op_slot, cap * sizeof(int32_t)));
+    kv->op_cap = cap;
+    return DIE_OK;
+}
+
+static die_status_t kv_maintain(die_kv* kv, int force, cudaStream_t s) {
+    KvState h;
+    DIE_CUDA(cudaMemcpyAsync(&h, kv->st, sizeof(KvState), cudaMemcpyDeviceToHost, s));
+    DIE_CUDA(cudaStreamSynchronize(s));
+    kv->head_lb = h.head;
+    const uint64_t span = kv->tail - h.head;
+    if (force || span > kv->ring_cap / 2) {
+        uint32_t* new_log = nullptr;
+        unsigned long long* n_kept = nullptr;
+        DIE_CUDA(cudaMalloc(&new_log, kv->ring_cap * sizeof(uint32_t)));
+        DIE_CUDA(cudaMalloc(&n_kept, sizeof(unsigned long long)));
+        DIE_CUDA(cudaMemsetAsync(new_log, 0xff, kv->ring_cap * sizeof(uint32_t), s));
+        kv_compact_kernel<<<1, WIN_THREADS, 0, s>>>(view_of(kv), new_log, kv->tail, n_kept);
+        DIE_LAUNCH_CHECK();
+        unsigned long long kept = 0;
+        DIE_CUDA(cudaMemcpyAsync(&kept, n_kept, sizeof(kept), cudaMemcpyDeviceToHost, s));
+        DIE_CUDA(cudaStreamSynchronize(s));
+        cudaFree(kv->log);
+        cudaFree(n_kept);
+        kv->log = new_log;
+        kv->head_lb = kv->tail;
+        kv->tail += kept;
+    }
+    const uint64_t empties = kv->capacity - h.size - h.n_tomb;
+    if (force || empties < kv->capacity / 4 + kv->max_chunk) {
+        Slot* fresh = nullptr;
+        DIE_CUDA(cudaMalloc(&fresh, kv->capacity * sizeof(Slot)));
+        DIE_CUDA(cudaMemsetAsync(fresh, 0, kv->capacity * sizeof(Slot), s));
+        Slot* old = kv->slots;
+        kv->slots = fresh;
+        kv_rehash_kernel<<<num_sms() * 8, KV_THREADS, 0, s>>>(view_of(kv), old, kv->capacity);
+        DIE_LAUNCH_CHECK();
+        h.n_tomb = 0;
+        h.n_empty_claimed = h.size;
+        DIE_CUDA(cudaMemcpyAsync(&kv->st->n_tomb, &h.n_tomb, sizeof(h.n_tomb), cudaMemcpyHostToDevice, s));
+        DIE_CUDA(cudaMemcpyAsync(&kv->st->n_empty_claimed, &h.n_empty_claimed, sizeof(h.n_empty_claimed),
+                                 cudaMemcpyHostToDevice, s));
+        DIE_CUDA(cudaStreamSynchronize(s));
+        cudaFree(old);
+        kv->live_at_rebuild = h.size;
+    } else {
+        kv->live_at_rebuild = h.size + h.n_tomb;  // tighten the conservative bound with the real count
+    }
+    kv->claims_ub = 0;
+    return DIE_OK;
+}
+
+// Called before a batch of n ops: keeps the ring and the EMPTY-slot reserve safe using host bounds only.
+static die_status_t reserve_for_batch(die_kv* kv, uint64_t n, bool inserts, cudaStream_t s) {
+    bool need = (kv->tail + n - kv->head_lb) > kv->ring_cap - 16;
+    if (inserts && kv->live_at_rebuild + kv->claims_ub + n + kv->capacity / 4 > kv->capacity) need = true;
+    if (need) DIE_TRY(kv_maintain(kv, 0, s));
+    if ((kv->tail + n - kv->head_lb) > kv->ring_cap - 16) DIE_TRY(kv_maintain(kv, 1, s));
+    if (inserts) kv->claims_ub += n;
+    return DIE_OK;
+}
+
+die_status_t kv_get_batch_impl(die_kv* kv, const uint32_t* digests, int32_t B, double now, uint8_t* hit_out,
+                               uint64_t* value_out, int32_t* slot_out, cudaStream_t s) {
+    for (int64_t done = 0; done < B;) {
+        const int n = (int)std::min<int64_t>(B - done, (int64_t)kv->max_chunk);
+        DIE_TRY(reserve_for_batch(kv, n, false, s));
+        kv_get_kernel<false><<<ceil_div(n, KV_THREADS), KV_THREADS, 0, s>>>(
+            view_of(kv), reinterpret_cast<const uint4*>(digests) + done, n, now, kv->tail, hit_out + done,
+            reinterpret_cast<unsigned long long*>(value_out ? value_out + done : nullptr),
+            slot_out ? slot_out + done : nullptr);
+        DIE_LAUNCH_CHECK();
+        kv->tail += n;
+        done += n;
+    }
+    return DIE_OK;
+}
+
+die_status_t kv_set_batch_impl(die_kv* kv, const uint32_t* digests, const uint64_t* values, const double* ttl,
+                               int32_t M, double now, int32_t deferred, const uint8_t* skip, int known_absent,
+                               const uint32_t* n_active_dev, int32_t* slot_out, uint64_t* dropped_out,
+                               cudaStream_t s) {
+    if (known_absent && ((int64_t)M > (int64_t)kv->max_chunk || !n_active_dev))
+        DIE_FAIL(DIE_ERR_TOO_LARGE, "kv_set_batch: known_absent batches must fit one chunk (%d > %llu)", M,
+                 (unsigned long long)kv->max_chunk);
+    if (deferred && (int64_t)M > (int64_t)kv->max_chunk)
+        DIE_FAIL(DIE_ERR_TOO_LARGE, "kv_set_batch: a batch_set of %d items exceeds this table's limit of %llu", M,
+                 (unsigned long long)kv->max_chunk);
+    uint64_t dropped_base = 0;
+    kv->dropped_prefix = 0;
+    for (int64_t done = 0; done < M;) {
+        const int n = (int)std::min<int64_t>(M - done, (int64_t)kv->max_chunk);
+        DIE_TRY(ensure_scratch(kv, n));
+        DIE_TRY(reserve_for_batch(kv, n, true, s));
+        const KvView v = view_of(kv);
+        const uint4* dg = reinterpret_cast<const uint4*>(digests) + done;
+        const unsigned long long* vals =
+            reinterpret_cast<const unsigned long long*>(values ? values + done : nullptr);
+        const double* tt = ttl ? ttl + done : nullptr;
+        const uint8_t* sk = skip ? skip + done : nullptr;
+        int32_t* so = slot_out ? slot_out + done : nullptr;
+        unsigned long long* dr =
+            reinterpret_cast<unsigned long long*>(dropped_out ? dropped_out + dropped_base : nullptr);
+        const int grid = ceil_div(n, KV_THREADS);
+        const int own_values = values ? 0 : 1;
+        if (!known_absent) {
+            kv_set_precheck_kernel<<<grid, KV_THREADS, 0, s>>>(v, dg, n, sk, kv->op_slot);
+            DIE_LAUNCH_CHECK();
+        }
+        kv_set_window_kernel<<<1, WIN_THREADS, 0, s>>>(v, kv->tail, known_absent ? n_active_dev : nullptr, deferred);
+        DIE_LAUNCH_CHECK();
+        kv_set_claim_kernel<<<grid, KV_THREADS, 0, s>>>(v, dg, n, now, kv->tail, own_values, sk,
+                                                        known_absent ? 0 : 1, kv->op_slot, so, dr);
+        DIE_LAUNCH_CHECK();
+        if (values || ttl) {
+            kv_set_finalize_kernel<<<grid, KV_THREADS, 0, s>>>(v, n, kv->tail, vals, tt, sk, kv->op_slot);
+            DIE_LAUNCH_CHECK();
+        }
+        kv_set_evict_kernel<<<1, WIN_THREADS, 0, s>>>(v, dg, vals, tt, n, now, kv->tail, deferred, sk, so, dr);
+        DIE_LAUNCH_CHECK();
+        kv->tail += n;
+        done += n;
+        if (done < M) {
+            // chunked batches are rare (tiny tables / huge batches): keep the dropped list contiguous
+            // and stop where the reference would have raised
+            KvState h;
+            DIE_CUDA(cudaMemcpyAsync(&h, kv->st, sizeof(KvState), cudaMemcpyDeviceToHost, s));
+            DIE_CUDA(cudaStreamSynchronize(s));
+            dropped_base += h.n_dropped_last;
+            kv->dropped_prefix = dropped_base;
+            if (h.status) {
+                if (slot_out) DIE_CUDA(cudaMemsetAsync(slot_out + done, 0xff, (size_t)(M - done) * sizeof(int32_t), s));
+                break;
+            }
+        }
+    }
+    return DIE_OK;
+}
+
+}  // namespace die
+
+// ================================================================================================
+// C-ABI
+// ================================================================================================
+using namespace die;
+
+extern "C" die_status_t die_kv_create(uint64_t max_size, int32_t policy, double default_ttl, die_kv_t** out) {
+    if (!out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_create: null out");
+    if (policy != DIE_KV_POLICY_LRU)
+        DIE_FAIL(DIE_ERR_UNSUPPORTED, "die_kv_create: only eviction_policy='lru' is built (policy=%d)", policy);
+    return kv_create_impl(max_size, default_ttl, 0, out);
+}
+
+extern "C" die_status_t die_kv_destroy(die_kv_t* kv) {
+    if (!kv) return DIE_OK;
+    cudaFree(kv->slots);
+    cudaFree(kv->log);
+    cudaFree(kv->st);
+    cudaFree(kv->op_slot);
+    cudaFree(kv->free_rows);
+    delete kv;
+    return DIE_OK;
+}
+
+extern "C" die_status_t die_kv_maintain_sync(die_kv_t* kv, int32_t force, die_stream_t stream) {
+    if (!kv) DIE_FAIL(DIE_ERR_INVALID, "die_kv_maintain_sync: null kv");
+    return kv_maintain(kv, force, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" die_status_t die_kv_get_batch(die_kv_t* kv, const uint32_t* digests, int32_t B, double now,
+                                         uint8_t* hit_out, uint64_t* value_out, int32_t* slot_out,
+                                         die_stream_t stream) {
+    if (!kv || B < 0) DIE_FAIL(DIE_ERR_INVALID, "die_kv_get_batch: bad arguments");
+    if (B == 0) return DIE_OK;
+    if (!digests || !hit_out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_get_batch: null digests/hit_out");
+    return kv_get_batch_impl(kv, digests, B, now, hit_out, value_out, slot_out, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" die_status_t die_kv_contains_batch(die_kv_t* kv, const uint32_t* digests, int32_t B, double now,
+                                              uint8_t* out, uint64_t* value_out, die_stream_t stream) {
+    if (!kv || B < 0) DIE_FAIL(DIE_ERR_INVALID, "die_kv_contains_batch: bad arguments");
+    if (B == 0) return DIE_OK;
+    if (!digests || !out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_contains_batch: null digests/out");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    kv_get_kernel<true><<<ceil_div(B, KV_THREADS), KV_THREADS, 0, s>>>(
+        view_of(kv), reinterpret_cast<const uint4*>(digests), B, now, 0ull, out,
+        reinterpret_cast<unsigned long long*>(value_out), nullptr);
+    DIE_LAUNCH_CHECK();
+    return DIE_OK;
+}
+
+extern "C" die_status_t die_kv_delete_batch(die_kv_t* kv, const uint32_t* digests, int32_t B,
+                                            uint8_t* deleted_out, uint64_t* value_out, die_stream_t stream) {
+    if (!kv || B < 0) DIE_FAIL(DIE_ERR_INVALID, "die_kv_delete_batch: bad arguments");
+    if (B == 0) return DIE_OK;
+    if (!digests || !deleted_out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_delete_batch: null digests/deleted_out");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    kv_delete_kernel<<<ceil_div(B, KV_THREADS), KV_THREADS, 0, s>>>(
+        view_of(kv), reinterpret_cast<const uint4*>(digests), B, deleted_out,
+        reinterpret_cast<unsigned long long*>(value_out));
+    DIE_LAUNCH_CHECK();
+    return DIE_OK;
+}
+
+extern "C" die_status_t die_kv_set_batch(die_kv_t* kv, const uint32_t* digests, const uint64_t* values,
+                                         const double* ttl, int32_t M, double now, int32_t deferred_stamp,
+                                         int32_t* slot_out, uint64_t* dropped_out, die_stream_t stream) {
+    if (!kv || M < 0) DIE_FAIL(DIE_ERR_INVALID, "die_kv_set_batch: bad arguments");
+    if (M == 0) return DIE_OK;
+    if (!digests) DIE_FAIL(DIE_ERR_INVALID, "die_kv_set_batch: null digests");
+    return kv_set_batch_impl(kv, digests, values, ttl, M, now, deferred_stamp, nullptr, 0, nullptr, slot_out,
+                             dropped_out, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" die_status_t die_kv_len_sync(die_kv_t* kv, double now, uint64_t* purged_out, uint64_t purged_cap,
+                                        uint64_t* n_purged, uint64_t* len_out, die_stream_t stream) {
+    if (!kv || !len_out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_len_sync: bad arguments");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    unsigned long long* d_n = nullptr;
+    DIE_CUDA(cudaMalloc(&d_n, sizeof(unsigned long long)));
+    DIE_CUDA(cudaMemsetAsync(d_n, 0, sizeof(unsigned long long), s));
+    kv_purge_kernel<<<num_sms() * 8, KV_THREADS, 0, s>>>(view_of(kv), now,
+                                                         reinterpret_cast<unsigned long long*>(purged_out),
+                                                         purged_cap, d_n);
+    DIE_LAUNCH_CHECK();
+    unsigned long long n = 0, size = 0;
+    DIE_CUDA(cudaMemcpyAsync(&n, d_n, sizeof(n), cudaMemcpyDeviceToHost, s));
+    DIE_CUDA(cudaMemcpyAsync(&size, &kv->st->size, sizeof(size), cudaMemcpyDeviceToHost, s));
+    DIE_CUDA(cudaStreamSynchronize(s));
+    cudaFree(d_n);
+    if (n_purged) *n_purged = n;
+    *len_out = size;
+    return DIE_OK;
+}
+
+extern "C" die_status_t die_kv_clear(die_kv_t* kv, die_stream_t stream) {
+    if (!kv) DIE_FAIL(DIE_ERR_INVALID, "die_kv_clear: null kv");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    DIE_CUDA(cudaMemsetAsync(kv->slots, 0, kv->capacity * sizeof(Slot), s));
+    kv_state_init_kernel<<<kv->n_rows ? 256 : 1, 256, 0, s>>>(view_of(kv), kv->tail, kv->n_rows);
+    DIE_LAUNCH_CHECK();
+    kv->head_lb = kv->tail;
+    kv->claims_ub = 0;
+    kv->live_at_rebuild = 0;
+    return DIE_OK;
+}
+
+extern "C" die_status_t die_kv_stats_sync(die_kv_t* kv, uint64_t out[8], die_stream_t stream) {
+    if (!kv || !out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_stats_sync: bad arguments");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    KvState h;
+    DIE_CUDA(cudaMemcpyAsync(&h, kv->st, sizeof(KvState), cudaMemcpyDeviceToHost, s));
+    DIE_CUDA(cudaStreamSynchronize(s));
+    kv->head_lb = h.head;
+    out[0] = h.hits;
+    out[1] = h.misses;
+    out[2] = h.evictions;
+    out[3] = h.size;
+    out[4] = kv->max_size;
+    out[5] = kv->capacity;
+    out[6] = h.n_tomb;
+    out[7] = kv->tail - h.head;
+    return DIE_OK;
+}
+
+extern "C" die_status_t die_kv_sync_status(die_kv_t* kv, int32_t* status, uint64_t* n_dropped,
+                                           uint32_t* slow_path_batches, die_stream_t stream) {
+    if (!kv) DIE_FAIL(DIE_ERR_INVALID, "die_kv_sync_status: null kv");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    KvState h;
+    DIE_CUDA(cudaMemcpyAsync(&h, kv->st, sizeof(KvState), cudaMemcpyDeviceToHost, s));
+    DIE_CUDA(cudaStreamSynchronize(s));
+    kv->head_lb = h.head;
+    if (status) *status = (int32_t)h.status;
+    if (n_dropped) *n_dropped = kv->dropped_prefix + h.n_dropped_last;
+    if (slow_path_batches) *slow_path_batches = (uint32_t)h.slow_batches;
+    if (h.status) {
+        const unsigned long long zero = 0;
+        DIE_CUDA(cudaMemcpyAsync(&kv->st->status, &zero, sizeof(zero), cudaMemcpyHostToDevice, s));
+        DIE_CUDA(cudaStreamSynchronize(s));
+    }
+    return DIE_OK;
+}
+
+extern "C" die_status_t die_kv_dump_sync(die_kv_t* kv, uint64_t cap, uint32_t* digests, uint64_t* values,
+                                         double* created_at, double* last_accessed, uint32_t* access_count,
+                                         double* ttl, uint8_t* stamped, uint64_t* n_out, die_stream_t stream) {
+    if (!kv || !n_out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_dump_sync: bad arguments");
+    if (kv->capacity > (1ull << 24)) DIE_FAIL(DIE_ERR_TOO_LARGE, "die_kv_dump_sync: parity dump is for small tables");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    std::vector<Slot> host(kv->capacity);
+    DIE_CUDA(cudaMemcpyAsync(host.data(), kv->slots, kv->capacity * sizeof(Slot), cudaMemcpyDeviceToHost, s));
+    DIE_CUDA(cudaStreamSynchronize(s));
+    std::vector<const Slot*> live;
+    for (const Slot& sl : host) {
+        const bool empty = sl.fp_lo == 0 && sl.fp_hi == 0;
+        const bool tomb = sl.fp_lo == ~0ull && sl.fp_hi == ~0ull;
+        if (!empty && !tomb) live.push_back(&sl);
+    }
+    std::stable_sort(live.begin(), live.end(), [](const Slot* a, const Slot* b) {
+        const unsigned long long sa = a->stamp ? a->stamp : ~0ull, sb = b->stamp ? b->stamp : ~0ull;
+        return sa < sb;
+    });
+    *n_out = live.size();
+    for (uint64_t k = 0; k < live.size() && k < cap; ++k) {
+        const Slot* sl = live[k];
+        if (digests) {
+            digests[4 * k + 0] = (uint32_t)sl->fp_lo;
+            digests[4 * k + 1] = (uint32_t)(sl->fp_lo >> 32);
+            digests[4 * k + 2] = (uint32_t)sl->fp_hi;
+            digests[4 * k + 3] = (uint32_t)(sl->fp_hi >> 32);
+        }
+        if (values) values[k] = sl->value;
+        if (created_at) created_at[k] = sl->created_at;
+        if (last_accessed) last_accessed[k] = sl->last_accessed;
+        if (access_count) access_count[k] = sl->access_count;
+        if (ttl) ttl[k] = sl->ttl;
+        if (stamped) stamped[k] = sl->stamp ? 1 : 0;
+    }
+    return DIE_OK;
+}

@@ -1,0 +1,111 @@
+"""Tensor-level wrappers over the C-ABI (one Python function per entry point of include/die.h).
+
+torch is used for device memory and streams only; every byte of work is done by libdie's kernels.
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _cabi
+from ._cabi import check, ptr, require_cuda, stream_ptr
+
+
+class KeyBatch:
+    """CSR of UTF-8 key bytes on the device (`key.encode()` of model_registry.py:159)."""
+
+    def __init__(self, key_bytes: torch.Tensor, key_off: torch.Tensor):
+        self.key_bytes, self.key_off = key_bytes, key_off
+
+    def __len__(self) -> int:
+        return self.key_off.numel() - 1
+
+    @staticmethod
+    def encode_host(keys: Sequence[str]):
+        """-> (uint8[total], int64[B+1]) numpy arrays."""
+        enc = [k.encode() for k in keys]
+        off = np.zeros(len(enc) + 1, dtype=np.int64)
+        if enc:
+            np.cumsum([len(e) for e in enc], out=off[1:])
+        data = np.frombuffer(b"".join(enc), dtype=np.uint8) if off[-1] else np.zeros(0, dtype=np.uint8)
+        return data, off
+
+    @classmethod
+    def from_strings(cls, keys: Sequence[str], device="cuda") -> "KeyBatch":
+        require_cuda()
+        data, off = cls.encode_host(keys)
+        kb = torch.from_numpy(data.copy()).to(device) if data.size else torch.zeros(16, dtype=torch.uint8, device=device)
+        return cls(kb, torch.from_numpy(off).to(device))
+
+
+def route_md5(keys: KeyBatch, n_shards: int, routable: Optional[torch.Tensor] = None,
+              healthy_idx: Optional[torch.Tensor] = None, failover: bool = True, want_digests: bool = True,
+              want_counts: bool = False):
+    """-> (shard int32[B], digests uint32[B,4] | None, dest_counts int32[n_shards] | None)."""
+    lib = require_cuda()
+    B = len(keys)
+    dev = keys.key_off.device
+    shard = torch.empty(B, dtype=torch.int32, device=dev)
+    digests = torch.empty((B, 4), dtype=torch.int32, device=dev) if want_digests else None
+    counts = torch.empty(max(n_shards, 1), dtype=torch.int32, device=dev) if want_counts else None
+    n_healthy = 0 if healthy_idx is None else healthy_idx.numel()
+    check(lib.die_route_md5(ptr(keys.key_bytes), ptr(keys.key_off), B, n_shards, ptr(routable), ptr(healthy_idx),
+                            n_healthy, 1 if failover else 0, ptr(shard), ptr(digests), ptr(counts), stream_ptr()))
+    return shard, digests, (counts[:n_shards] if counts is not None else None)
+
+
+def pack_ragged(values: torch.Tensor, off: torch.Tensor, Lpad: int, src_index: Optional[torch.Tensor] = None,
+                n_rows: Optional[int] = None):
+    """values: 1-D tensor of payload elements, off: int64[n_req+1] -> (packed [R, Lpad], lengths int32[R])."""
+    lib = require_cuda()
+    R = (off.numel() - 1) if src_index is None else src_index.numel()
+    if n_rows is not None:
+        R = n_rows
+    out = torch.empty((R, Lpad), dtype=values.dtype, device=values.device)
+    lengths = torch.empty(R, dtype=torch.int32, device=values.device)
+    check(lib.die_pack_ragged(ptr(values), ptr(off), ptr(src_index), R, values.element_size(), Lpad, ptr(out),
+                              ptr(lengths), stream_ptr()))
+    return out, lengths
+
+
+def unpack_ragged(packed: torch.Tensor, off_out: torch.Tensor, out_values: torch.Tensor,
+                  dst_index: Optional[torch.Tensor] = None):
+    lib = require_cuda()
+    R, Lpad = packed.shape
+    check(lib.die_unpack_ragged(ptr(packed), ptr(off_out), ptr(dst_index), R, packed.element_size(), Lpad,
+                                ptr(out_values), stream_ptr()))
+    return out_values
+
+
+def echo_fwd(x: torch.Tensor) -> torch.Tensor:
+    lib = require_cuda()
+    x = x.contiguous()
+    y = torch.empty_like(x)
+    check(lib.die_echo_fwd(ptr(x), ptr(y), x.numel() * x.element_size(), stream_ptr()))
+    return y
+
+
+def linear_fwd(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], precision: int = _cabi.LINEAR_FP32):
+    lib = require_cuda()
+    assert x.dtype == torch.float32 and w.dtype == torch.float32 and x.is_contiguous() and w.is_contiguous()
+    B, K = x.shape
+    N = w.shape[0]
+    y = torch.empty((B, N), dtype=torch.float32, device=x.device)
+    check(lib.die_linear_fwd_f32(ptr(x), ptr(w), ptr(b), ptr(y), B, K, N, precision, stream_ptr()))
+    return y
+
+
+def mlp_fwd_bf16(x, w1, b1, w2, b2):
+    lib = require_cuda()
+    B, D = x.shape
+    H = w1.shape[0]
+    hidden = torch.empty((B, H), dtype=torch.bfloat16, device=x.device)
+    y = torch.empty((B, D), dtype=torch.bfloat16, device=x.device)
+    check(lib.die_mlp_fwd_bf16(ptr(x), ptr(w1), ptr(b1), ptr(w2), ptr(b2), ptr(hidden), ptr(y), B, D, H, stream_ptr()))
+    return y
+
+
+NAN = math.nan

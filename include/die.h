@@ -1,0 +1,219 @@
+/*
+ * die.h -- C-ABI of libdie.so: the B200 (sm_100a) implementation of the reference's one
+ * data-parallel hot path, route -> probe -> pack -> infer -> unpack.
+ *
+ * The reference (a pure-Python prototype) has no FFI; the interface each entry point
+ * replaces is a Python method, cited as file:line relative to the reference checkout.
+ * INTEGRATION.md shows the ctypes stub a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - every function returns a die_status_t (0 = DIE_OK) and never throws or aborts;
+ *     die_last_error() gives the message of the calling thread's last failure;
+ *   - unless a parameter is marked [host], pointers are DEVICE pointers owned by the caller
+ *     (e.g. torch tensors' data_ptr()); only die_kv_t / die_pipeline_t handles own memory;
+ *   - all device work is enqueued on the cudaStream_t passed as `stream` (a void* here so the
+ *     header needs no CUDA include); functions whose name ends in _sync or that return
+ *     values through [host] pointers synchronise that stream;
+ *   - one host thread per handle; handles are bound to the device current at creation.
+ */
+#ifndef DIE_H_
+#define DIE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DIE_ABI_VERSION 1
+
+typedef int32_t die_status_t;
+enum {
+    DIE_OK = 0,
+    DIE_ERR_INVALID = 1,        /* bad argument */
+    DIE_ERR_CUDA = 2,           /* a CUDA runtime call failed */
+    DIE_ERR_NOMEM = 3,
+    DIE_ERR_STOP_ITERATION = 4, /* the reference would have raised StopIteration (kvstore.py:89) */
+    DIE_ERR_TOO_LARGE = 5,
+    DIE_ERR_UNSUPPORTED = 6
+};
+
+typedef void* die_stream_t; /* cudaStream_t */
+
+int32_t die_abi_version(void);
+const char* die_last_error(void);
+/* Makes `device` current for this thread inside the library's CUDA runtime instance. */
+die_status_t die_set_device(int32_t device);
+/* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
+uint64_t die_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * K1  route: shard = int(md5(key).hexdigest(), 16) % n_shards, then the health gate + failover.
+ * Replaces ModelRegistry.get_shard_for_key (src/model_registry.py:149-161),
+ * Router.route_request (src/router.py:140-184) and Router._find_alternative_shard
+ * (src/router.py:186-221) for a whole batch of keys.
+ *
+ *   key_bytes/key_off : CSR of the UTF-8 key bytes; key i = key_bytes[key_off[i] .. key_off[i+1])
+ *   routable[s]       : 1 if shard position s may be returned directly, i.e. its worker is
+ *                       registered and (healthy or !prefer_healthy); NULL = all routable
+ *   healthy_idx[h]    : shard positions whose worker is HEALTHY, in shard-list order
+ *                       (router.py:197-201); used when the primary is not routable
+ *   failover          : Router.failover_enabled
+ *   shard_out[i]      : shard LIST POSITION (not shard_id), or -1 where the reference returns None
+ *   digest_out        : optional [B,4] uint32, the MD5 state words A,B,C,D (digest bytes, LE words)
+ *   dest_counts       : optional [n_shards] int32, number of requests routed to each position
+ * ------------------------------------------------------------------------------------------ */
+die_status_t die_route_md5(const uint8_t* key_bytes, const int64_t* key_off, int32_t B,
+                           int32_t n_shards, const uint8_t* routable,
+                           const int32_t* healthy_idx, int32_t n_healthy, int32_t failover,
+                           int32_t* shard_out, uint32_t* digest_out, int32_t* dest_counts,
+                           die_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K2/K3  KV store: GPU-resident open-addressing table keyed by the 128-bit MD5 of the key,
+ * with the reference's LRU + TTL semantics applied "as if" the batch ran in request order.
+ * Replaces KVCache (src/kvstore.py:26-236, eviction_policy="lru").
+ *   default_ttl : NaN = None.   ttl arrays: NaN = "ttl=None" (use default_ttl); NULL = all None.
+ *   now         : the value time.time() would return for every op of this batch.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct die_kv die_kv_t;
+
+#define DIE_KV_POLICY_LRU 0
+
+/* KVCache.__init__ (kvstore.py:38-61). policy other than LRU -> DIE_ERR_UNSUPPORTED. */
+die_status_t die_kv_create(uint64_t max_size, int32_t policy, double default_ttl, die_kv_t** out);
+die_status_t die_kv_destroy(die_kv_t* kv);
+
+/* KVCache.get / batch_get (kvstore.py:136-168) for B keys in request order.
+ *   hit_out[i]   : 1 hit; 0 miss (absent); 2 miss because expired -- this op deleted the entry
+ *                  and value_out[i] holds the dropped value
+ *   value_out[i] : stored value on hit
+ *   slot_out     : optional, table slot index of a hit (-1 otherwise)                        */
+die_status_t die_kv_get_batch(die_kv_t* kv, const uint32_t* digests, int32_t B, double now,
+                              uint8_t* hit_out, uint64_t* value_out, int32_t* slot_out,
+                              die_stream_t stream);
+
+/* KVCache.set applied to M (key, value, ttl) triples in request order (kvstore.py:104-134);
+ * deferred_stamp == 1 gives KVCache.batch_set (kvstore.py:170-176; keys must be distinct);
+ * deferred_stamp == 2 gives set(..., batch=True) on its own: inserted but never put in the LRU order.
+ *   values NULL        : the table picks the value itself (slot index, or a result-row handle
+ *                        when it belongs to a die_pipeline_t)
+ *   slot_out           : optional [M], slot holding op i's key after the batch
+ *   dropped_out        : optional [2*M] values of entries evicted or overwritten by this batch;
+ *   the count and the StopIteration condition are read back with die_kv_sync_status().        */
+die_status_t die_kv_set_batch(die_kv_t* kv, const uint32_t* digests, const uint64_t* values,
+                              const double* ttl, int32_t M, double now, int32_t deferred_stamp,
+                              int32_t* slot_out, uint64_t* dropped_out, die_stream_t stream);
+
+/* KVCache.delete (kvstore.py:178-187): deleted_out[i] = 1 if the key was present (value_out[i] = its value). */
+die_status_t die_kv_delete_batch(die_kv_t* kv, const uint32_t* digests, int32_t B,
+                                 uint8_t* deleted_out, uint64_t* value_out, die_stream_t stream);
+/* KVCache.__contains__ (kvstore.py:221-228): 1 present; 0 absent; 2 expired (deleted, value_out set). */
+die_status_t die_kv_contains_batch(die_kv_t* kv, const uint32_t* digests, int32_t B, double now,
+                                   uint8_t* out, uint64_t* value_out, die_stream_t stream);
+/* KVCache.__len__ (kvstore.py:230-236): purge every expired entry, then count.  purged_out (optional,
+ * device, capacity purged_cap) receives the dropped values. Synchronises. */
+die_status_t die_kv_len_sync(die_kv_t* kv, double now, uint64_t* purged_out, uint64_t purged_cap,
+                             uint64_t* n_purged /*[host]*/, uint64_t* len_out /*[host]*/, die_stream_t stream);
+/* KVCache.clear (kvstore.py:189-198). */
+die_status_t die_kv_clear(die_kv_t* kv, die_stream_t stream);
+/* KVCache.get_stats (kvstore.py:206-219): out = {hits, misses, evictions, size (unpurged), max_size,
+ * capacity, tombstones, lru_log_span}. Synchronises. */
+die_status_t die_kv_stats_sync(die_kv_t* kv, uint64_t out[8] /*[host]*/, die_stream_t stream);
+/* Synchronises, returns and clears the sticky batch status: DIE_OK or DIE_ERR_STOP_ITERATION
+ * (in *status), and how many values the last set batch wrote to dropped_out. */
+die_status_t die_kv_sync_status(die_kv_t* kv, int32_t* status /*[host]*/, uint64_t* n_dropped /*[host]*/,
+                                uint32_t* slow_path_batches /*[host], optional*/, die_stream_t stream);
+/* Parity dump: the live entries in LRU order (head = next victim), unstamped entries last in slot
+ * order; arrays are [host] with room for `cap` entries.  Mirrors list(_access_order) + self.cache. */
+die_status_t die_kv_dump_sync(die_kv_t* kv, uint64_t cap, uint32_t* digests /*[cap,4]*/, uint64_t* values,
+                              double* created_at, double* last_accessed, uint32_t* access_count,
+                              double* ttl, uint8_t* stamped, uint64_t* n_out, die_stream_t stream);
+/* Housekeeping that has no counterpart in the reference: renumber the LRU log and/or rebuild the
+ * table when tombstones pile up.  Called automatically by the batch entry points when their
+ * conservative host-side bounds require it; force != 0 does both now.  Synchronises. */
+die_status_t die_kv_maintain_sync(die_kv_t* kv, int32_t force, die_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K4/K5  pack / unpack.  Replace Batcher._process_batch's gather
+ * `inputs_list = [req.inputs for req in requests_to_process]` (src/batcher.py:211) and scatter
+ * `for req, result in zip(...): req.future.set_result(result)` (src/batcher.py:225-227).
+ *   values/off : ragged CSR of request payloads, off in ELEMENTS (elem_bytes each)
+ *   src_index  : optional [R]; packed row r holds request src_index[r] (NULL: request r)
+ *   out        : [R, Lpad] row-major, rows zero-padded; lengths_out[r] = element count of row r
+ * Rows longer than Lpad are truncated to Lpad (lengths_out still holds the full length).
+ * ------------------------------------------------------------------------------------------ */
+die_status_t die_pack_ragged(const void* values, const int64_t* off, const int32_t* src_index,
+                             int32_t R, int32_t elem_bytes, int32_t Lpad, void* out,
+                             int32_t* lengths_out, die_stream_t stream);
+/* Row r of packed [R, Lpad] -> request q = dst_index ? dst_index[r] : r, written to
+ * out_values[off_out[q] .. off_out[q+1]). */
+die_status_t die_unpack_ragged(const void* packed, const int64_t* off_out, const int32_t* dst_index,
+                               int32_t R, int32_t elem_bytes, int32_t Lpad, void* out_values,
+                               die_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K6-K8  mock-model forward.  The reference's model is an echo (src/mock_models/fake_model.py:52);
+ * the linear layer and the MLP are the configs BASELINE.json names and have no reference arithmetic.
+ * ------------------------------------------------------------------------------------------ */
+die_status_t die_echo_fwd(const void* in, void* out, uint64_t bytes, die_stream_t stream);
+#define DIE_LINEAR_FP32 0 /* CUDA-core FMA, fp32 accumulate */
+#define DIE_LINEAR_TF32 1 /* tcgen05 kind::tf32, fp32 accumulate in TMEM */
+/* Y[B,N] = X[B,K] @ W[N,K]^T + b[N], fp32 storage. */
+die_status_t die_linear_fwd_f32(const float* X, const float* W, const float* b, float* Y,
+                                int32_t B, int32_t K, int32_t N, int32_t precision, die_stream_t stream);
+/* Y[B,D] = bf16( bf16(relu(X[B,D] @ W1[H,D]^T + b1)) @ W2[D,H]^T + b2 ); X,W1,W2,Y bf16, b1,b2 fp32,
+ * hidden [B,H] bf16 scratch supplied by the caller. */
+die_status_t die_mlp_fwd_bf16(const void* X, const void* W1, const float* b1, const void* W2,
+                              const float* b2, void* hidden, void* Y, int32_t B, int32_t D, int32_t H,
+                              die_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Composed pipeline for one owner shard (SURVEY.md call-stack (E); the coordinator the
+ * reference's README.md:56-60 describes but never wrote).  One call = one flushed batch:
+ * route -> get -> pack misses -> model -> unpack -> set misses, results in request order.
+ * Fixed-width payloads (dim_in elements in, dim_out elements out, fp32).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct die_pipeline die_pipeline_t;
+#define DIE_MODEL_ECHO 0
+#define DIE_MODEL_LINEAR_FP32 1
+#define DIE_MODEL_LINEAR_TF32 2
+
+typedef struct {
+    uint64_t kv_max_size;
+    double default_ttl;     /* NaN = None */
+    int32_t max_batch;      /* largest B a call may pass */
+    int32_t dim_in;         /* elements per request payload */
+    int32_t dim_out;        /* elements per result (== dim_in for echo) */
+    int32_t model;          /* DIE_MODEL_* */
+    int32_t max_key_bytes;  /* upper bound of key bytes per batch (host-buffer entry point) */
+    int32_t reserved;
+    const float* weight;    /* [host] [dim_out, dim_in] (linear) or NULL */
+    const float* bias;      /* [host] [dim_out] or NULL */
+} die_pipeline_config_t;
+
+die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, die_pipeline_t** out);
+die_status_t die_pipeline_destroy(die_pipeline_t* p);
+die_kv_t* die_pipeline_kv(die_pipeline_t* p);
+/* Inputs already resident in HBM.  payload [B, dim_in] fp32; out [B, dim_out] fp32;
+ * hit_out [B] uint8 (1 = served from the cache); digest_out optional [B,4]. */
+die_status_t die_pipeline_run_device(die_pipeline_t* p, const uint8_t* key_bytes, const int64_t* key_off,
+                                     int32_t B, const float* payload, double now, float* out,
+                                     uint8_t* hit_out, uint32_t* digest_out, die_stream_t stream);
+/* The owner-side half of the path for requests whose digests are already known (after the
+ * all-to-all dispatch): get -> pack -> model -> unpack -> set. */
+die_status_t die_pipeline_run_owner_device(die_pipeline_t* p, const uint32_t* digests, int32_t B,
+                                           const float* payload, double now, float* out, uint8_t* hit_out,
+                                           die_stream_t stream);
+/* Same through HOST buffers (pinned recommended): copies keys + payload in, results + hit flags
+ * out, and synchronises.  This is the call the reference-facing Python plugin makes. */
+die_status_t die_pipeline_run_host(die_pipeline_t* p, const uint8_t* key_bytes /*[host]*/,
+                                   const int64_t* key_off /*[host]*/, int32_t B,
+                                   const float* payload /*[host]*/, double now, float* out /*[host]*/,
+                                   uint8_t* hit_out /*[host]*/, die_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DIE_H_ */
