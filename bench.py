@@ -1,0 +1,378 @@
+#!/usr/bin/env python
+"""Headline benchmark: requests/sec of the batched route -> probe -> pack -> infer -> unpack path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (BASELINE.json configs[1], "C2"): flushed batches of 4096 requests, key "user-%010d" with ids
+uniform in [0, 1e7), payload 128 fp32, mock linear model 128->128, one owner KV cache of 2^20 entries
+per GPU (LRU, default_ttl 300 s), so about 10 % of the requests hit the cache and every batch evicts.
+One step = one flushed batch through the whole path.  Every step has its own freshly drawn inputs
+(resident in HBM before the timed region; K steps x 2.2 MB, larger than L2 for K >= 60).
+
+Prints ONE JSON line (see the contract in the task description): `value` is device-resident
+throughput, `e2e` goes through the C-ABI with host buffers, `roofline` describes the dominant kernel
+timed with CUDA events on its own stream, `cpu_baseline` is the CPU oracle port timed on this host.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "distributed-inference-engine_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+B, D = 4096, 128
+KV_MAX, ID_SPACE, TTL = 1 << 20, 10 ** 7, 300.0
+KEY_LEN = 15
+METRIC = "requests/sec, batched route->probe->pack->infer->unpack"
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# synthetic inputs
+# ----------------------------------------------------------------------------------------------------------------
+def key_bytes_of(ids: np.ndarray) -> np.ndarray:
+    """b"user-%010d" for every id -> uint8 [n, 15] without a Python loop."""
+    digits = (ids[:, None] // (10 ** np.arange(9, -1, -1, dtype=np.int64))[None, :]) % 10 + 48
+    out = np.empty((ids.size, KEY_LEN), dtype=np.uint8)
+    out[:, :5] = np.frombuffer(b"user-", dtype=np.uint8)
+    out[:, 5:] = digits.astype(np.uint8)
+    return out
+
+
+def make_batches(rng, n_batches, id_space=ID_SPACE, payload=True):
+    ids = rng.integers(0, id_space, (n_batches, B), dtype=np.int64)
+    keys = key_bytes_of(ids.reshape(-1)).reshape(n_batches, B * KEY_LEN)
+    off = np.arange(B + 1, dtype=np.int64) * KEY_LEN
+    x = rng.standard_normal((n_batches, B, D), dtype=np.float32) if payload else None
+    return ids, keys, off, x
+
+
+def model_weights():
+    rng = np.random.default_rng(12345)
+    w = (rng.standard_normal((D, D)) / np.sqrt(D)).astype(np.float32)
+    b = rng.standard_normal(D).astype(np.float32)
+    return w, b
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# CPU baseline (oracle port of the reference's pure-Python path) -- the one place bench.py may run oracle/
+# ----------------------------------------------------------------------------------------------------------------
+def cpu_worker(seed, n_timed, scale=8):
+    """Prefill a scaled-down cache (1/scale of the entries and of the id space: same ~10 % hit rate),
+    then time n_timed flushed batches through the composed reference port.  Returns (requests, seconds)."""
+    from oracle.pipeline import BaselinePipeline
+    w, b = model_weights()
+    w64 = w.astype(np.float64)
+
+    def model(rows):
+        if not rows:
+            return []
+        y = (np.stack(rows) @ w.T + b).astype(np.float32)
+        return [y[i] for i in range(len(rows))]
+
+    kv_max, space = KV_MAX // scale, ID_SPACE // scale
+    pipe = BaselinePipeline(1, kv_max, TTL, model, max_batch_size=B)
+    rng = np.random.default_rng(1000 + seed)
+    n_fill = int(kv_max * 1.15 / B) + 1
+    now = 1000.0
+    for _ in range(n_fill):
+        ids = rng.integers(0, space, B)
+        keys = ["user-%010d" % i for i in ids]
+        x = rng.standard_normal((B, D), dtype=np.float32)
+        now += 0.01
+        pipe.process(keys, list(x), now)
+    batches = []
+    for _ in range(n_timed):
+        ids = rng.integers(0, space, B)
+        batches.append((["user-%010d" % i for i in ids], list(rng.standard_normal((B, D), dtype=np.float32))))
+    t0 = time.perf_counter()
+    for keys, rows in batches:
+        now += 0.01
+        pipe.process(keys, rows, now)
+    dt = time.perf_counter() - t0
+    del w64
+    return n_timed * B, dt
+
+
+def cpu_baseline_single(n_timed=24):
+    n, dt = cpu_worker(0, n_timed)
+    return {"value": n / dt, "unit": "requests/s", "cores": 1, "kind": "port",
+            "sample": f"{n_timed} batches x {B} requests after prefill; cache 2^17 entries and id space 1.25e6 "
+                      f"(both 1/8 of the GPU run, same ~10% hit rate); oracle/pipeline.py BaselinePipeline "
+                      f"(hashlib.md5 + dict/OrderedDict + asyncio batcher + numpy fp32 linear), sleeps removed"}
+
+
+def run_reference(args):
+    """`--impl reference`: the reference's pure-Python path (oracle port; the Python reference itself cannot
+    travel to the GPU box) on all usable host cores, as independent one-shard replicas."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    cores = max(1, min(os.cpu_count() or 1, 32))
+    n_timed = max(4, min(args.steps, 24))
+    t0 = time.perf_counter()
+    with mp.get_context("fork").Pool(cores) as pool:
+        res = pool.starmap(cpu_worker, [(s, n_timed) for s in range(cores)])
+    total = sum(r[0] for r in res)
+    slowest = max(r[1] for r in res)
+    value = total / slowest
+    line = {"metric": METRIC, "value": value, "unit": "requests/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * slowest / n_timed, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
+            "config": workload_config(args.gpus),
+            "cpu_baseline": {"value": value, "unit": "requests/s", "cores": cores, "kind": "port",
+                             "sample": f"{cores} replica processes x {n_timed} batches x {B} requests after prefill, "
+                                       f"cache and id space scaled 1/8; wall {time.perf_counter() - t0:.1f}s"},
+            "e2e": {"value": value, "unit": "requests/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def workload_config(n_gpus):
+    return {"workload": "C2: 4096-request flushed batches, key 'user-%010d' (ids uniform in [0,1e7)), 128-dim fp32 "
+                        "payload, mock linear 128->128, LRU+TTL cache of 2^20 entries per GPU (~10% hits, evicting)",
+            "batch": B, "dim": D, "kv_max_size": KV_MAX, "id_space": ID_SPACE, "default_ttl": TTL,
+            "parallelism": f"hash-shard x{n_gpus}", "l2_policy": "every step reads fresh inputs; K steps x 2.2 MB"}
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# clocks
+# ----------------------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.samples, self.reasons, self.stop_flag, self.max_mhz = [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:  # noqa: BLE001
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:  # noqa: BLE001
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if mask & bit:
+                        self.reasons.add(k)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.002)
+
+    def result(self):
+        self.stop_flag = True
+        self.join(timeout=1.0)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from die import _cabi, ops
+    from die.pipeline import DispatchPipeline
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = _cabi.require_cuda()
+    K, W = args.steps, max(args.warmup, 3)
+    rng = np.random.default_rng(7 + rank)
+    w, b = model_weights()
+
+    if world > 1:
+        from die.exchange import ShardedDispatcher
+        runner = ShardedDispatcher(world, rank, KV_MAX, B, D, w, b, TTL)
+    else:
+        runner = None
+    pipe = DispatchPipeline(KV_MAX, B * (2 if world > 1 else 1), D, D, "linear", w, b, TTL, max_key_bytes=2 * B * KEY_LEN) \
+        if runner is None else runner.pipe
+
+    off_d = torch.from_numpy(np.arange(B + 1, dtype=np.int64) * KEY_LEN).cuda()
+
+    def to_device(keys, x):
+        return torch.from_numpy(keys).cuda(), torch.from_numpy(x).cuda()
+
+    def step_device(kb, xb, now, out, hit):
+        if runner is None:
+            pipe.run_device(ops.KeyBatch(kb, off_d), xb, now, out, hit)
+        else:
+            runner.step(ops.KeyBatch(kb, off_d), xb, now, out, hit)
+
+    # ---- prefill the cache to capacity (untimed) -------------------------------------------------------------
+    now = 1000.0
+    out_ring = [torch.empty((B, D), dtype=torch.float32, device="cuda") for _ in range(64)]
+    hit_ring = [torch.empty(B, dtype=torch.uint8, device="cuda") for _ in range(64)]
+    n_fill = int(KV_MAX * 1.15 / B) + 1
+    for c in range(0, n_fill, 32):
+        _, keys, _, x = make_batches(rng, min(32, n_fill - c))
+        kd, xd = to_device(keys, x)
+        for i in range(kd.shape[0]):
+            now += 0.01
+            step_device(kd[i], xd[i], now, out_ring[i % 64], hit_ring[i % 64])
+    torch.cuda.synchronize()
+
+    # ---- timed: inputs resident in HBM ------------------------------------------------------------------------
+    _, keys, _, x = make_batches(rng, W + K)
+    kd, xd = to_device(keys, x)
+    for i in range(W):
+        now += 0.01
+        step_device(kd[i], xd[i], now, out_ring[i % 64], hit_ring[i % 64])
+    torch.cuda.synchronize()
+    stats0 = pipe.kv.stats()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = lib.die_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(W, W + K):
+        now += 0.01
+        step_device(kd[i], xd[i], now, out_ring[i % 64], hit_ring[i % 64])
+    ev1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = lib.die_launch_count() - launches0
+    clocks = sampler.result()
+    stats1 = pipe.kv.stats()
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+    value = world * K * B / (ms / 1e3)
+    hit_rate = (stats1["hits"] - stats0["hits"]) / max(1, (stats1["hits"] - stats0["hits"]) + (stats1["misses"] - stats0["misses"]))
+
+    # ---- e2e: host buffers through the C-ABI (H2D + kernels + D2H inside the timed region) ---------------------
+    e2e = None
+    if world == 1:
+        _, keys, off, x = make_batches(rng, K)
+        hk = torch.from_numpy(np.concatenate([keys, np.zeros((K, 16), np.uint8)], axis=1)).pin_memory()
+        ho = torch.from_numpy(off).pin_memory()
+        hx = torch.from_numpy(x).pin_memory()
+        hout = torch.empty((8, B, D), dtype=torch.float32).pin_memory()
+        hhit = torch.empty((8, B), dtype=torch.uint8).pin_memory()
+        for i in range(min(3, K)):
+            now += 0.01
+            pipe.run_host(hk[i], ho, hx[i], now, hout[i % 8], hhit[i % 8])
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(K):
+            now += 0.01
+            pipe.run_host(hk[i], ho, hx[i], now, hout[i % 8], hhit[i % 8])
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        e2e = {"value": K * B / dt, "unit": "requests/s",
+               "h2d_bytes_per_step": B * KEY_LEN + (B + 1) * 8 + B * D * 4, "d2h_bytes_per_step": B * D * 4 + B,
+               "ms_per_step": 1e3 * dt / K, "api": "die_pipeline_run_host (C-ABI, pinned host buffers)"}
+
+    # ---- per-stage device time (CUDA events on the launching stream) and roofline -------------------------------
+    stages, roofline = {}, None
+    if world == 1:
+        n_prof = min(K, 50)
+        _, keys, _, x = make_batches(rng, n_prof)
+        kd2, xd2 = to_device(keys, x)
+        s0 = pipe.kv.stats()
+        _cabi.check(lib.die_profile_begin())
+        for i in range(n_prof):
+            now += 0.01
+            step_device(kd2[i], xd2[i], now, out_ring[i % 64], hit_ring[i % 64])
+        import ctypes
+        ms_arr, cnt_arr, n_st = (ctypes.c_double * 32)(), (ctypes.c_uint64 * 32)(), ctypes.c_int32()
+        _cabi.check(lib.die_profile_end(32, ms_arr, cnt_arr, ctypes.byref(n_st)))
+        s1 = pipe.kv.stats()
+        hits = (s1["hits"] - s0["hits"]) / n_prof
+        miss = (s1["misses"] - s0["misses"]) / n_prof
+        evic = (s1["evictions"] - s0["evictions"]) / n_prof
+        row = D * 4
+        alg = {  # algorithmic bytes per launch (SURVEY.md section 8(d) per-request figures x requests per launch)
+            "route_md5": B * (KEY_LEN + 8 + 4 + 16),
+            "kv_get": hits * 121 + miss * 89,
+            "miss_scan": B * 5,
+            "pack_hits": B * 2 * row + B * 13,
+            "model": miss * (2 * row + 16),
+            "kv_set_window": evic * 12,
+            "kv_set_claim": miss * 160,
+            "kv_set_evict": evic * (128 + 12),
+            "unpack_store": miss * 3 * row + B * 9,
+        }
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:  # noqa: BLE001
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        peak_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+        total_ms = sum(ms_arr[i] for i in range(n_st.value))
+        for i in range(n_st.value):
+            if cnt_arr[i] == 0:
+                continue
+            name = lib.die_profile_stage_name(i).decode()
+            per = ms_arr[i] / cnt_arr[i]
+            gbs = alg.get(name, 0) / (per * 1e-3) / 1e9 if per > 0 else 0.0
+            stages[name] = {"us_per_launch": round(per * 1e3, 3), "launches_per_step": cnt_arr[i] / n_prof,
+                            "share": round(ms_arr[i] / total_ms, 4), "alg_bytes_per_launch": round(alg.get(name, 0)),
+                            "gbs": round(gbs, 1), "frac_of_hbm_peak": round(gbs / peak, 4)}
+        dom = max(stages, key=lambda n: stages[n]["share"])
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": stages[dom]["gbs"], "peak": peak, "unit": "GB/s",
+                    "frac": stages[dom]["frac_of_hbm_peak"], "traffic": None, "peak_source": peak_src,
+                    "us_per_launch": stages[dom]["us_per_launch"], "alg_bytes_per_launch": stages[dom]["alg_bytes_per_launch"],
+                    "note": "4 MiB of payload per 4096-request batch is below one launch's latency floor; see DESIGN.md"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline_single()
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": "requests/s", "n_gpus": world, "steps": K, "warmup": W,
+                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": dict(workload_config(world), hit_rate=round(hit_rate, 4)),
+                "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e, "roofline": roofline, "stages": stages,
+                "cpu_baseline": cpu}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

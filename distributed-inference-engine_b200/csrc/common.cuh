@@ -10,6 +10,13 @@
 namespace die {
 
 // ---- error plumbing ---------------------------------------------------------------------
+enum Stage {
+    ST_ROUTE = 0, ST_KV_GET, ST_KV_CONTAINS, ST_KV_DELETE, ST_KV_PURGE, ST_KV_PRECHECK, ST_KV_WINDOW, ST_KV_CLAIM,
+    ST_KV_FINALIZE, ST_KV_EVICT, ST_KV_MAINT, ST_MISS_SCAN, ST_PACK_HITS, ST_MODEL, ST_UNPACK_STORE, ST_PACK,
+    ST_UNPACK, ST_COUNT
+};
+void prof_before(int stage, cudaStream_t s);
+void prof_after(int stage, cudaStream_t s);
 char* err_buf();                       // thread-local, 512 bytes
 void count_launch(unsigned n = 1);     // gpu_launches accounting for bench.py
 
@@ -34,6 +41,15 @@ void count_launch(unsigned n = 1);     // gpu_launches accounting for bench.py
         if (e__ != cudaSuccess)                                                          \
             DIE_FAIL(DIE_ERR_CUDA, "%s:%d kernel launch -> %s", __FILE__, __LINE__,      \
                      cudaGetErrorString(e__));                                           \
+    } while (0)
+
+// Launch a kernel, optionally bracketed by CUDA events on its own stream (die_profile_begin/end).
+#define DIE_LAUNCH(stage, stream, ...)             \
+    do {                                           \
+        ::die::prof_before((stage), (stream));     \
+        __VA_ARGS__;                               \
+        ::die::prof_after((stage), (stream));      \
+        DIE_LAUNCH_CHECK();                        \
     } while (0)
 
 #define DIE_TRY(expr)                        \

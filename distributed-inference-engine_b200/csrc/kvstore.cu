@@ -578,8 +578,7 @@ die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_ro
     DIE_CUDA(cudaMemset(kv->slots, 0, kv->capacity * sizeof(Slot)));
     DIE_CUDA(cudaMemset(kv->log, 0xff, kv->ring_cap * sizeof(uint32_t)));
     DIE_CUDA(cudaMemset(kv->st, 0, sizeof(KvState)));
-    kv_state_init_kernel<<<n_rows ? 256 : 1, 256>>>(view_of(kv), 1ull, n_rows);
-    DIE_LAUNCH_CHECK();
+    DIE_LAUNCH(ST_KV_MAINT, (cudaStream_t)0, kv_state_init_kernel<<<n_rows ? 256 : 1, 256>>>(view_of(kv), 1ull, n_rows));
     DIE_CUDA(cudaDeviceSynchronize());
     *out = kv;
     return DIE_OK;
@@ -608,8 +607,7 @@ static die_status_t kv_maintain(die_kv* kv, int force, cudaStream_t s) {
         DIE_CUDA(cudaMalloc(&new_log, kv->ring_cap * sizeof(uint32_t)));
         DIE_CUDA(cudaMalloc(&n_kept, sizeof(unsigned long long)));
         DIE_CUDA(cudaMemsetAsync(new_log, 0xff, kv->ring_cap * sizeof(uint32_t), s));
-        kv_compact_kernel<<<1, WIN_THREADS, 0, s>>>(view_of(kv), new_log, kv->tail, n_kept);
-        DIE_LAUNCH_CHECK();
+        DIE_LAUNCH(ST_KV_MAINT, s, kv_compact_kernel<<<1, WIN_THREADS, 0, s>>>(view_of(kv), new_log, kv->tail, n_kept));
         unsigned long long kept = 0;
         DIE_CUDA(cudaMemcpyAsync(&kept, n_kept, sizeof(kept), cudaMemcpyDeviceToHost, s));
         DIE_CUDA(cudaStreamSynchronize(s));
@@ -626,8 +624,7 @@ static die_status_t kv_maintain(die_kv* kv, int force, cudaStream_t s) {
         DIE_CUDA(cudaMemsetAsync(fresh, 0, kv->capacity * sizeof(Slot), s));
         Slot* old = kv->slots;
         kv->slots = fresh;
-        kv_rehash_kernel<<<num_sms() * 8, KV_THREADS, 0, s>>>(view_of(kv), old, kv->capacity);
-        DIE_LAUNCH_CHECK();
+        DIE_LAUNCH(ST_KV_MAINT, s, kv_rehash_kernel<<<num_sms() * 8, KV_THREADS, 0, s>>>(view_of(kv), old, kv->capacity));
         h.n_tomb = 0;
         h.n_empty_claimed = h.size;
         DIE_CUDA(cudaMemcpyAsync(&kv->st->n_tomb, &h.n_tomb, sizeof(h.n_tomb), cudaMemcpyHostToDevice, s));
@@ -658,11 +655,10 @@ die_status_t kv_get_batch_impl(die_kv* kv, const uint32_t* digests, int32_t B, d
     for (int64_t done = 0; done < B;) {
         const int n = (int)std::min<int64_t>(B - done, (int64_t)kv->max_chunk);
         DIE_TRY(reserve_for_batch(kv, n, false, s));
-        kv_get_kernel<false><<<ceil_div(n, KV_THREADS), KV_THREADS, 0, s>>>(
+        DIE_LAUNCH(ST_KV_GET, s, kv_get_kernel<false><<<ceil_div(n, KV_THREADS), KV_THREADS, 0, s>>>(
             view_of(kv), reinterpret_cast<const uint4*>(digests) + done, n, now, kv->tail, hit_out + done,
             reinterpret_cast<unsigned long long*>(value_out ? value_out + done : nullptr),
-            slot_out ? slot_out + done : nullptr);
-        DIE_LAUNCH_CHECK();
+            slot_out ? slot_out + done : nullptr));
         kv->tail += n;
         done += n;
     }
@@ -697,20 +693,15 @@ die_status_t kv_set_batch_impl(die_kv* kv, const uint32_t* digests, const uint64
         const int grid = ceil_div(n, KV_THREADS);
         const int own_values = values ? 0 : 1;
         if (!known_absent) {
-            kv_set_precheck_kernel<<<grid, KV_THREADS, 0, s>>>(v, dg, n, sk, kv->op_slot);
-            DIE_LAUNCH_CHECK();
+            DIE_LAUNCH(ST_KV_PRECHECK, s, kv_set_precheck_kernel<<<grid, KV_THREADS, 0, s>>>(v, dg, n, sk, kv->op_slot));
         }
-        kv_set_window_kernel<<<1, WIN_THREADS, 0, s>>>(v, kv->tail, known_absent ? n_active_dev : nullptr, deferred);
-        DIE_LAUNCH_CHECK();
-        kv_set_claim_kernel<<<grid, KV_THREADS, 0, s>>>(v, dg, n, now, kv->tail, own_values, sk,
-                                                        known_absent ? 0 : 1, kv->op_slot, so, dr);
-        DIE_LAUNCH_CHECK();
+        DIE_LAUNCH(ST_KV_WINDOW, s, kv_set_window_kernel<<<1, WIN_THREADS, 0, s>>>(v, kv->tail, known_absent ? n_active_dev : nullptr, deferred));
+        DIE_LAUNCH(ST_KV_CLAIM, s, kv_set_claim_kernel<<<grid, KV_THREADS, 0, s>>>(v, dg, n, now, kv->tail, own_values, sk,
+                                                        known_absent ? 0 : 1, kv->op_slot, so, dr));
         if (values || ttl) {
-            kv_set_finalize_kernel<<<grid, KV_THREADS, 0, s>>>(v, n, kv->tail, vals, tt, sk, kv->op_slot);
-            DIE_LAUNCH_CHECK();
+            DIE_LAUNCH(ST_KV_FINALIZE, s, kv_set_finalize_kernel<<<grid, KV_THREADS, 0, s>>>(v, n, kv->tail, vals, tt, sk, kv->op_slot));
         }
-        kv_set_evict_kernel<<<1, WIN_THREADS, 0, s>>>(v, dg, vals, tt, n, now, kv->tail, deferred, sk, so, dr);
-        DIE_LAUNCH_CHECK();
+        DIE_LAUNCH(ST_KV_EVICT, s, kv_set_evict_kernel<<<1, WIN_THREADS, 0, s>>>(v, dg, vals, tt, n, now, kv->tail, deferred, sk, so, dr));
         kv->tail += n;
         done += n;
         if (done < M) {
@@ -775,10 +766,9 @@ extern "C" die_status_t die_kv_contains_batch(die_kv_t* kv, const uint32_t* dige
     if (B == 0) return DIE_OK;
     if (!digests || !out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_contains_batch: null digests/out");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    kv_get_kernel<true><<<ceil_div(B, KV_THREADS), KV_THREADS, 0, s>>>(
+    DIE_LAUNCH(ST_KV_CONTAINS, s, kv_get_kernel<true><<<ceil_div(B, KV_THREADS), KV_THREADS, 0, s>>>(
         view_of(kv), reinterpret_cast<const uint4*>(digests), B, now, 0ull, out,
-        reinterpret_cast<unsigned long long*>(value_out), nullptr);
-    DIE_LAUNCH_CHECK();
+        reinterpret_cast<unsigned long long*>(value_out), nullptr));
     return DIE_OK;
 }
 
@@ -788,10 +778,9 @@ extern "C" die_status_t die_kv_delete_batch(die_kv_t* kv, const uint32_t* digest
     if (B == 0) return DIE_OK;
     if (!digests || !deleted_out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_delete_batch: null digests/deleted_out");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    kv_delete_kernel<<<ceil_div(B, KV_THREADS), KV_THREADS, 0, s>>>(
+    DIE_LAUNCH(ST_KV_DELETE, s, kv_delete_kernel<<<ceil_div(B, KV_THREADS), KV_THREADS, 0, s>>>(
         view_of(kv), reinterpret_cast<const uint4*>(digests), B, deleted_out,
-        reinterpret_cast<unsigned long long*>(value_out));
-    DIE_LAUNCH_CHECK();
+        reinterpret_cast<unsigned long long*>(value_out)));
     return DIE_OK;
 }
 
@@ -812,10 +801,9 @@ extern "C" die_status_t die_kv_len_sync(die_kv_t* kv, double now, uint64_t* purg
     unsigned long long* d_n = nullptr;
     DIE_CUDA(cudaMalloc(&d_n, sizeof(unsigned long long)));
     DIE_CUDA(cudaMemsetAsync(d_n, 0, sizeof(unsigned long long), s));
-    kv_purge_kernel<<<num_sms() * 8, KV_THREADS, 0, s>>>(view_of(kv), now,
+    DIE_LAUNCH(ST_KV_PURGE, s, kv_purge_kernel<<<num_sms() * 8, KV_THREADS, 0, s>>>(view_of(kv), now,
                                                          reinterpret_cast<unsigned long long*>(purged_out),
-                                                         purged_cap, d_n);
-    DIE_LAUNCH_CHECK();
+                                                         purged_cap, d_n));
     unsigned long long n = 0, size = 0;
     DIE_CUDA(cudaMemcpyAsync(&n, d_n, sizeof(n), cudaMemcpyDeviceToHost, s));
     DIE_CUDA(cudaMemcpyAsync(&size, &kv->st->size, sizeof(size), cudaMemcpyDeviceToHost, s));
@@ -830,8 +818,7 @@ extern "C" die_status_t die_kv_clear(die_kv_t* kv, die_stream_t stream) {
     if (!kv) DIE_FAIL(DIE_ERR_INVALID, "die_kv_clear: null kv");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     DIE_CUDA(cudaMemsetAsync(kv->slots, 0, kv->capacity * sizeof(Slot), s));
-    kv_state_init_kernel<<<kv->n_rows ? 256 : 1, 256, 0, s>>>(view_of(kv), kv->tail, kv->n_rows);
-    DIE_LAUNCH_CHECK();
+    DIE_LAUNCH(ST_KV_MAINT, s, kv_state_init_kernel<<<kv->n_rows ? 256 : 1, 256, 0, s>>>(view_of(kv), kv->tail, kv->n_rows));
     kv->head_lb = kv->tail;
     kv->claims_ub = 0;
     kv->live_at_rebuild = 0;

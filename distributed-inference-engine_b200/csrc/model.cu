@@ -76,16 +76,17 @@ die_status_t echo_launch(const void* in, void* out, uint64_t bytes, cudaStream_t
     const uint64_t nvec = vec ? bytes / 16 : 0;
     if (nvec) {
         const long long blocks = (long long)((nvec + 255) / 256);
-        echo_vec_kernel<<<(int)std::min<long long>(blocks, (long long)num_sms() * 16), 256, 0, s>>>(
-            static_cast<const int4*>(in), static_cast<int4*>(out), (long long)nvec);
-        DIE_LAUNCH_CHECK();
+        const int grid = (int)std::min<long long>(blocks, (long long)num_sms() * 16);
+        DIE_LAUNCH(ST_MODEL, s, echo_vec_kernel<<<grid, 256, 0, s>>>(static_cast<const int4*>(in),
+                                                                     static_cast<int4*>(out), (long long)nvec));
     }
     const uint64_t tail = bytes - nvec * 16;
     if (tail) {
         const long long blocks = (long long)((tail + 255) / 256);
-        echo_byte_kernel<<<(int)std::min<long long>(blocks, (long long)num_sms() * 16), 256, 0, s>>>(
-            static_cast<const uint8_t*>(in) + nvec * 16, static_cast<uint8_t*>(out) + nvec * 16, (long long)tail);
-        DIE_LAUNCH_CHECK();
+        const int grid = (int)std::min<long long>(blocks, (long long)num_sms() * 16);
+        DIE_LAUNCH(ST_MODEL, s, echo_byte_kernel<<<grid, 256, 0, s>>>(static_cast<const uint8_t*>(in) + nvec * 16,
+                                                                      static_cast<uint8_t*>(out) + nvec * 16,
+                                                                      (long long)tail));
     }
     return DIE_OK;
 }
@@ -94,8 +95,7 @@ die_status_t linear_f32_launch(const float* X, const float* W, const float* b, f
                                const uint32_t* n_rows_dev, cudaStream_t s) {
     if (B == 0 || N == 0) return DIE_OK;
     dim3 grid(ceil_div(B, LIN_BM), ceil_div(N, LIN_BN));
-    linear_f32_kernel<<<grid, 256, 0, s>>>(X, W, b, Y, B, K, N, n_rows_dev);
-    DIE_LAUNCH_CHECK();
+    DIE_LAUNCH(ST_MODEL, s, linear_f32_kernel<<<grid, 256, 0, s>>>(X, W, b, Y, B, K, N, n_rows_dev));
     return DIE_OK;
 }
 

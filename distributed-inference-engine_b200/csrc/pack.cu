@@ -138,15 +138,14 @@ extern "C" die_status_t die_pack_ragged(const void* values, const int64_t* off, 
     const bool vec = row_bytes % 16 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
     if (vec) {
         const int vpr = (int)(row_bytes / 16);
-        pack_vec_kernel<<<grid_for((long long)R * vpr), PACK_THREADS, 0, s>>>(
+        DIE_LAUNCH(ST_PACK, s, pack_vec_kernel<<<grid_for((long long)R * vpr), PACK_THREADS, 0, s>>>(
             static_cast<const uint8_t*>(values), off, src_index, R, elem_bytes, vpr, static_cast<int4*>(out),
-            lengths_out);
+            lengths_out));
     } else {
-        pack_elem_kernel<<<grid_for((long long)R * Lpad), PACK_THREADS, 0, s>>>(
+        DIE_LAUNCH(ST_PACK, s, pack_elem_kernel<<<grid_for((long long)R * Lpad), PACK_THREADS, 0, s>>>(
             static_cast<const uint8_t*>(values), off, src_index, R, elem_bytes, Lpad, static_cast<uint8_t*>(out),
-            lengths_out);
+            lengths_out));
     }
-    DIE_LAUNCH_CHECK();
     return DIE_OK;
 }
 
@@ -163,14 +162,13 @@ extern "C" die_status_t die_unpack_ragged(const void* packed, const int64_t* off
                      (elem_bytes == 1 || elem_bytes == 2 || (elem_bytes & 3) == 0);
     if (vec) {
         const int vpr1 = (int)(row_bytes / 16) + 1;
-        unpack_vec_kernel<<<grid_for((long long)R * vpr1), PACK_THREADS, 0, s>>>(
+        DIE_LAUNCH(ST_UNPACK, s, unpack_vec_kernel<<<grid_for((long long)R * vpr1), PACK_THREADS, 0, s>>>(
             static_cast<const uint8_t*>(packed), off_out, dst_index, R, elem_bytes, (int)row_bytes, vpr1,
-            static_cast<uint8_t*>(out_values));
+            static_cast<uint8_t*>(out_values)));
     } else {
-        unpack_elem_kernel<<<grid_for((long long)R * Lpad), PACK_THREADS, 0, s>>>(
+        DIE_LAUNCH(ST_UNPACK, s, unpack_elem_kernel<<<grid_for((long long)R * Lpad), PACK_THREADS, 0, s>>>(
             static_cast<const uint8_t*>(packed), off_out, dst_index, R, elem_bytes, Lpad,
-            static_cast<uint8_t*>(out_values));
+            static_cast<uint8_t*>(out_values)));
     }
-    DIE_LAUNCH_CHECK();
     return DIE_OK;
 }

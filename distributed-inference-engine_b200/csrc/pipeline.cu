@@ -128,18 +128,15 @@ static die_status_t run_owner(die_pipeline* p, const uint32_t* digests, int B, c
     const int vin = c.dim_in / 4, vout = c.dim_out / 4;
     uint8_t* code = hit_out ? hit_out : p->code;
     DIE_TRY(kv_get_batch_impl(p->kv, digests, B, now, code, p->value, nullptr, s));
-    miss_scan_kernel<<<1, 1024, 0, s>>>(code, B, p->miss_rank, p->n_miss);
-    DIE_LAUNCH_CHECK();
-    pack_hits_kernel<<<grid_256((long long)B * std::max(vin, vout)), 256, 0, s>>>(
+    DIE_LAUNCH(ST_MISS_SCAN, s, miss_scan_kernel<<<1, 1024, 0, s>>>(code, B, p->miss_rank, p->n_miss));
+    DIE_LAUNCH(ST_PACK_HITS, s, pack_hits_kernel<<<grid_256((long long)B * std::max(vin, vout)), 256, 0, s>>>(
         reinterpret_cast<const int4*>(payload), code, p->miss_rank,
         reinterpret_cast<const unsigned long long*>(p->value), reinterpret_cast<const int4*>(p->arena), B, vin, vout,
-        reinterpret_cast<int4*>(p->packed_in), reinterpret_cast<int4*>(out));
-    DIE_LAUNCH_CHECK();
+        reinterpret_cast<int4*>(p->packed_in), reinterpret_cast<int4*>(out)));
     if (c.model == DIE_MODEL_ECHO) {
-        echo_rows_kernel<<<grid_256((long long)B * vin), 256, 0, s>>>(reinterpret_cast<const int4*>(p->packed_in),
+        DIE_LAUNCH(ST_MODEL, s, echo_rows_kernel<<<grid_256((long long)B * vin), 256, 0, s>>>(reinterpret_cast<const int4*>(p->packed_in),
                                                                        reinterpret_cast<int4*>(p->packed_out), vin,
-                                                                       p->n_miss);
-        DIE_LAUNCH_CHECK();
+                                                                       p->n_miss));
     } else if (c.model == DIE_MODEL_LINEAR_FP32) {
         DIE_TRY(linear_f32_launch(p->packed_in, p->W, p->bias, p->packed_out, B, c.dim_in, c.dim_out, p->n_miss, s));
     } else {
@@ -147,10 +144,9 @@ static die_status_t run_owner(die_pipeline* p, const uint32_t* digests, int B, c
     }
     const unsigned long long t_set = p->kv->tail;
     DIE_TRY(kv_set_batch_impl(p->kv, digests, nullptr, nullptr, B, now, 0, code, 1, p->n_miss, p->set_slot, nullptr, s));
-    unpack_store_kernel<<<grid_256((long long)B * vout), 256, 0, s>>>(
+    DIE_LAUNCH(ST_UNPACK_STORE, s, unpack_store_kernel<<<grid_256((long long)B * vout), 256, 0, s>>>(
         view_of(p->kv), reinterpret_cast<const int4*>(p->packed_out), code, p->miss_rank, p->set_slot, t_set, B, vout,
-        reinterpret_cast<int4*>(out), reinterpret_cast<int4*>(p->arena));
-    DIE_LAUNCH_CHECK();
+        reinterpret_cast<int4*>(out), reinterpret_cast<int4*>(p->arena)));
     return DIE_OK;
 }
 

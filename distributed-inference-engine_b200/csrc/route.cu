@@ -110,9 +110,8 @@ extern "C" die_status_t die_route_md5(const uint8_t* key_bytes, const int64_t* k
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (dest_counts && n_shards > 0) DIE_CUDA(cudaMemsetAsync(dest_counts, 0, sizeof(int32_t) * n_shards, s));
     if (B == 0) return DIE_OK;
-    route_md5_kernel<<<ceil_div(B, ROUTE_THREADS), ROUTE_THREADS, 0, s>>>(
+    DIE_LAUNCH(ST_ROUTE, s, route_md5_kernel<<<ceil_div(B, ROUTE_THREADS), ROUTE_THREADS, 0, s>>>(
         key_bytes, key_off, B, n_shards, routable, healthy_idx, n_healthy, failover, shard_out,
-        reinterpret_cast<uint4*>(digest_out), dest_counts);
-    DIE_LAUNCH_CHECK();
+        reinterpret_cast<uint4*>(digest_out), dest_counts));
     return DIE_OK;
 }

@@ -39,6 +39,9 @@ SIGNATURES = {
     "die_last_error": (c_char_p, []),
     "die_set_device": (c_int32, [c_int32]),
     "die_launch_count": (c_uint64, []),
+    "die_profile_begin": (c_int32, []),
+    "die_profile_end": (c_int32, [c_int32, POINTER(c_double), POINTER(c_uint64), POINTER(c_int32)]),
+    "die_profile_stage_name": (c_char_p, [c_int32]),
     "die_route_md5": (c_int32, [P, P, c_int32, c_int32, P, P, c_int32, c_int32, P, P, P, P]),
     "die_kv_create": (c_int32, [c_uint64, c_int32, c_double, POINTER(c_void_p)]),
     "die_kv_destroy": (c_int32, [P]),

@@ -48,6 +48,16 @@ die_status_t die_set_device(int32_t device);
 /* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
 uint64_t die_launch_count(void);
 
+/* Diagnostics with no counterpart in the reference: while a profile is open every kernel this
+ * library launches is bracketed by CUDA events on the kernel's own stream; die_profile_end()
+ * synchronises the device and returns, per stage, the summed device time (ms) and launch count.
+ * Used by bench.py for the roofline of the dominant kernel; adds event overhead, so never left
+ * on during a throughput measurement. */
+die_status_t die_profile_begin(void);
+die_status_t die_profile_end(int32_t cap, double* ms_out /*[host]*/, uint64_t* count_out /*[host]*/,
+                             int32_t* n_stages /*[host]*/);
+const char* die_profile_stage_name(int32_t stage);
+
 /* ------------------------------------------------------------------------------------------
  * K1  route: shard = int(md5(key).hexdigest(), 16) % n_shards, then the health gate + failover.
  * Replaces ModelRegistry.get_shard_for_key (src/model_registry.py:149-161),

@@ -1,0 +1,235 @@
+"""GPU parity: K2/K3 KV store through the C-ABI.  Every check is bit-exact: results per op, hit/miss,
+LRU order, counters, entry metadata -- against traces recorded from the reference's KVCache and
+against the CPU oracle on seeded random batches."""
+import hashlib
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+from oracle import ref_port as rp
+
+pytestmark = pytest.mark.gpu
+
+
+def md5_words(keys):
+    raw = b"".join(hashlib.md5(k.encode()).digest() for k in keys)
+    return torch.from_numpy(np.frombuffer(raw, dtype=np.int32).reshape(-1, 4).copy()).cuda()
+
+
+# ------------------------------------------------------------------ reference traces on the drop-in class
+def replay_on_drop_in(t):
+    from die.kvstore import KVCache
+    clock = [1000.0]
+    kv = KVCache(t["max_size"], "lru", t["default_ttl"], clock=lambda: clock[0])
+    res = []
+    for op in t["ops"]:
+        name = op[0]
+        try:
+            if name == "advance":
+                clock[0] += op[1]
+                r = None
+            elif name == "set":
+                r = kv.set(op[1], op[2], ttl=op[3])
+            elif name == "get":
+                r = kv.get(op[1], "DFLT")
+            elif name == "batch_get":
+                r = kv.batch_get(op[1])
+            elif name == "batch_set":
+                r = kv.batch_set(dict((k, v) for k, v in op[1]), ttl=op[2])
+            elif name == "delete":
+                r = kv.delete(op[1])
+            elif name == "contains":
+                r = op[1] in kv
+            elif name == "len":
+                r = len(kv)
+            elif name == "clear":
+                r = kv.clear()
+            elif name == "stats":
+                r = kv.get_stats()
+        except StopIteration:
+            r = "!StopIteration"
+        res.append(r)
+    return kv, res
+
+
+@pytest.mark.parametrize("name", sorted(load_golden("kv_traces.json").keys()))
+def test_reference_trace_on_drop_in_kvcache(name):
+    t = load_golden("kv_traces.json")[name]
+    kv, res = replay_on_drop_in(t)
+    assert res == t["results"]
+    assert kv.get_stats() == t["final"]["stats"]
+    assert list(kv._access_order) == t["final"]["lru"]
+    got = {k: [e.value, e.created_at, e.last_accessed, e.access_count, e.ttl] for k, e in kv.cache.items()}
+    assert got == t["final"]["entries"]
+    assert kv.hits == t["final"]["stats"]["hits"] and kv.evictions == t["final"]["stats"]["evictions"]
+    assert kv.max_size == t["max_size"] and kv.eviction_policy == "lru"
+
+
+def test_unsupported_policies_raise():
+    from die.kvstore import KVCache
+    for pol in ("lfu", "FIFO"):
+        with pytest.raises(NotImplementedError):
+            KVCache(4, pol)
+
+
+# ------------------------------------------------------------------ batched device API vs the oracle
+class PortMirror:
+    """Applies the same batches to the CPU oracle, sequentially in request order."""
+
+    def __init__(self, max_size, default_ttl):
+        self.now = 0.0
+        self.kv = rp.PortKVCache(max_size, default_ttl, clock=lambda: self.now)
+
+    def get_batch(self, keys, now):
+        self.now = now
+        out = []
+        for k in keys:
+            v = self.kv.get(k, None)
+            out.append(v)
+        return out
+
+    def set_batch(self, keys, values, ttls, now):
+        self.now = now
+        for k, v, t in zip(keys, values, ttls):
+            self.kv.set(k, v, ttl=t)
+
+
+def compare_state(dkv, port, digest_of):
+    st = dkv.stats()
+    ps = port.kv.stats()
+    assert (st["hits"], st["misses"], st["evictions"], st["size"]) == (ps["hits"], ps["misses"], ps["evictions"], ps["size"])
+    d = dkv.dump()
+    order = [bytes(x) for x in d["digests"].numpy().view(np.uint8).reshape(-1, 16)]
+    stamped = d["stamped"].numpy().astype(bool)
+    want = [digest_of(k) for k in port.kv.lru_order()]
+    assert [o for o, s in zip(order, stamped) if s] == want
+    vals = dict(zip(order, d["values"].tolist()))
+    created = dict(zip(order, d["created_at"].tolist()))
+    cnt = dict(zip(order, d["access_count"].tolist()))
+    ttl = dict(zip(order, d["ttl"].tolist()))
+    for k, e in port.kv.cache.items():
+        dg = digest_of(k)
+        assert vals[dg] == e.value and created[dg] == e.created_at and cnt[dg] == e.access_count
+        assert (e.ttl is None and math.isnan(ttl[dg])) or ttl[dg] == e.ttl
+
+
+@pytest.mark.parametrize("cfg", [
+    # max_size, default_ttl, key space, batches, max batch, ttl choices
+    (64, None, 200, 60, 48, [None]),
+    (500, 20.0, 900, 40, 700, [None, None, 5.0, 0.0]),
+    (4000, None, 6000, 25, 3000, [None, 30.0]),
+    (37, 3.0, 60, 80, 90, [None, 1.0, 8.0]),       # batches larger than the cache: sequential path
+    (3, None, 10, 60, 7, [None]),
+    (1, None, 4, 40, 5, [None, 1.0]),
+])
+def test_random_batches_match_oracle(cfg):
+    from die.kvstore import DeviceKV
+    max_size, dttl, space, n_batches, max_b, ttl_choices = cfg
+    rng = np.random.default_rng(max_size * 7 + space)
+    dkv = DeviceKV(max_size, dttl)
+    port = PortMirror(max_size, dttl)
+    cache_digest = {}
+
+    def digest_of(k):
+        if k not in cache_digest:
+            cache_digest[k] = hashlib.md5(k.encode()).digest()
+        return cache_digest[k]
+
+    now, next_val = 100.0, 1
+    for b in range(n_batches):
+        now += float(rng.choice([0.0, 0.5, 2.0, 6.0]))
+        B = int(rng.integers(1, max_b + 1))
+        keys = ["k%d" % i for i in rng.integers(0, space, B)]
+        dig = md5_words(keys)
+        if rng.random() < 0.5:
+            hit, value = dkv.get_batch(dig, now)
+            want = port.get_batch(keys, now)
+            assert [int(h == 1) for h in hit.tolist()] == [int(v is not None) for v in want], b
+            got_vals = [v if h == 1 else None for h, v in zip(hit.tolist(), value.tolist())]
+            assert got_vals == want, b
+        else:
+            values = list(range(next_val, next_val + B))
+            next_val += B
+            ttls = [ttl_choices[i] for i in rng.integers(0, len(ttl_choices), B)]
+            tt = torch.tensor([math.nan if t is None else t for t in ttls], dtype=torch.float64, device="cuda")
+            dkv.set_batch(dig, torch.tensor(values, dtype=torch.int64, device="cuda"), now, tt)
+            port.set_batch(keys, values, ttls, now)
+            status, _, _ = dkv.sync_status()
+            assert status == 0
+        if b % 7 == 3:
+            dkv.maintain(force=True)  # LRU-log renumbering + table rebuild must not change anything
+        compare_state(dkv, port, digest_of)
+
+
+def test_fast_path_is_taken_when_cache_is_large_and_slow_path_when_forced():
+    from die.kvstore import DeviceKV
+    dkv = DeviceKV(1000, None)
+    keys = ["a%d" % i for i in range(3000)]
+    for i in range(0, 3000, 500):
+        dkv.set_batch(md5_words(keys[i:i + 500]), torch.arange(i, i + 500, dtype=torch.int64, device="cuda"), 1.0)
+    status, _, slow = dkv.sync_status()
+    assert status == 0 and slow == 0          # evictions served by the parallel path
+    st = dkv.stats()
+    assert st["size"] == 1000 and st["evictions"] == 2000
+    # re-set the LRU head inside an evicting batch: Appendix A.2 #1 order dependence -> exact replay
+    dkv.set_batch(md5_words(["new-key", keys[2000]]), torch.tensor([7, 8], dtype=torch.int64, device="cuda"), 2.0)
+    status, _, slow = dkv.sync_status()
+    assert status == 0 and slow == 1
+    assert dkv.stats()["evictions"] == 2002   # head evicted, then re-inserted as new -> a second eviction
+
+
+def test_pipeline_style_fill_at_scale_matches_oracle():
+    """get -> set(misses) rounds on a 200k-entry table, 32768 ops per batch."""
+    from die.kvstore import DeviceKV
+    max_size, B, rounds, space = 200_000, 32768, 14, 400_000
+    rng = np.random.default_rng(11)
+    dkv = DeviceKV(max_size, 50.0)
+    port = PortMirror(max_size, 50.0)
+    now = 10.0
+    for r in range(rounds):
+        now += 4.0
+        ids = rng.integers(0, space, B)
+        keys = ["user-%010d" % i for i in ids]
+        dig = md5_words(keys)
+        hit, value = dkv.get_batch(dig, now)
+        want = port.get_batch(keys, now)
+        hl = hit.cpu().numpy()
+        assert np.array_equal(hl == 1, np.array([v is not None for v in want])), r
+        miss = np.nonzero(hl != 1)[0]
+        mkeys = [keys[i] for i in miss]
+        vals = [int(ids[i]) + 1 for i in miss]
+        dkv.set_batch(dig[torch.from_numpy(miss).cuda()], torch.tensor(vals, dtype=torch.int64, device="cuda"), now)
+        port.set_batch(mkeys, vals, [None] * len(vals), now)
+    status, _, slow = dkv.sync_status()
+    st, ps = dkv.stats(), port.kv.stats()
+    assert status == 0 and slow == 0
+    assert (st["hits"], st["misses"], st["evictions"], st["size"]) == (ps["hits"], ps["misses"], ps["evictions"], ps["size"])
+    d = dkv.dump()
+    order = [bytes(x) for x in d["digests"].numpy().view(np.uint8).reshape(-1, 16)]
+    assert order == [hashlib.md5(k.encode()).digest() for k in port.kv.lru_order()]
+
+
+def test_contains_delete_len_clear_batched():
+    from die.kvstore import DeviceKV
+    dkv = DeviceKV(100, None)
+    keys = ["c%d" % i for i in range(50)]
+    tt = torch.tensor([1.0 if i % 2 else math.nan for i in range(50)], dtype=torch.float64, device="cuda")
+    dkv.set_batch(md5_words(keys), torch.arange(50, dtype=torch.int64, device="cuda"), 0.0, tt)
+    out, _ = dkv.contains_batch(md5_words(keys + ["zz"]), 0.5)
+    assert out.tolist() == [1] * 50 + [0]
+    out, val = dkv.contains_batch(md5_words(keys[:10]), 5.0)       # odd keys expired: deleted, no counters touched
+    assert out.tolist() == [2 if i % 2 else 1 for i in range(10)]
+    assert [v for o, v in zip(out.tolist(), val.tolist()) if o == 2] == [1, 3, 5, 7, 9]
+    st = dkv.stats()
+    assert (st["hits"], st["misses"], st["size"]) == (0, 0, 45)
+    deleted, val = dkv.delete_batch(md5_words(["c0", "c0", "c1", "nope"]))
+    assert sorted(deleted.tolist()[:2]) == [0, 1] and deleted.tolist()[2:] == [0, 0]
+    n, purged = dkv.len_sync(5.0)
+    assert n == 24 and sorted(purged) == list(range(11, 50, 2))
+    dkv.clear()
+    assert dkv.stats()["size"] == 0 and dkv.len_sync(0.0)[0] == 0
+    hit, _ = dkv.get_batch(md5_words(keys[:4]), 0.0)
+    assert hit.tolist() == [0, 0, 0, 0]

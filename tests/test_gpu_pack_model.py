@@ -1,0 +1,111 @@
+"""GPU parity: K4/K5 ragged pack / unpack (bit-exact layout) and K6/K8 mock-model forwards."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import models
+
+pytestmark = pytest.mark.gpu
+
+NP_OF = {1: np.uint8, 2: np.int16, 4: np.float32, 8: np.int64}
+
+
+def ragged(rng, n_req, max_len, elem_bytes, min_len=0):
+    lens = rng.integers(min_len, max_len + 1, n_req)
+    off = np.zeros(n_req + 1, dtype=np.int64)
+    np.cumsum(lens, out=off[1:])
+    total = int(off[-1])
+    if elem_bytes == 4:
+        vals = rng.standard_normal(total + 8).astype(np.float32)
+    else:
+        vals = rng.integers(0, 120, total + 8).astype(NP_OF[elem_bytes])
+    return vals, off, lens
+
+
+def pack_ref(vals, off, Lpad, src_index=None):
+    idx = range(len(off) - 1) if src_index is None else src_index
+    out = np.zeros((len(idx), Lpad), dtype=vals.dtype)
+    for r, q in enumerate(idx):
+        n = min(int(off[q + 1] - off[q]), Lpad)
+        out[r, :n] = vals[off[q]:off[q] + n]
+    return out
+
+
+@pytest.mark.parametrize("elem_bytes,n_req,Lpad,min_len", [(4, 256, 2048, 16), (4, 1000, 64, 0), (4, 4096, 128, 128),
+                                                           (1, 300, 48, 0), (2, 300, 40, 0), (8, 200, 10, 0),
+                                                           (4, 77, 13, 0), (1, 50, 7, 0)])
+def test_pack_layout_and_unpack_roundtrip(elem_bytes, n_req, Lpad, min_len):
+    from die import ops
+    rng = np.random.default_rng(n_req + Lpad)
+    vals, off, lens = ragged(rng, n_req, Lpad, elem_bytes, min_len)
+    v_d, off_d = torch.from_numpy(vals).cuda(), torch.from_numpy(off).cuda()
+    packed, lengths = ops.pack_ragged(v_d, off_d, Lpad)
+    assert np.array_equal(packed.cpu().numpy(), pack_ref(vals, off, Lpad))      # row i = request i, zero padded
+    assert lengths.cpu().tolist() == lens.tolist()
+    # gather form: row r = request src_index[r] (the misses of a batch, in arrival order)
+    sel = np.sort(rng.choice(n_req, size=max(n_req // 3, 1), replace=False)).astype(np.int32)
+    packed_sel, lengths_sel = ops.pack_ragged(v_d, off_d, Lpad, torch.from_numpy(sel).cuda())
+    assert np.array_equal(packed_sel.cpu().numpy(), pack_ref(vals, off, Lpad, sel))
+    assert lengths_sel.cpu().tolist() == lens[sel].tolist()
+    # unpack is the exact inverse on the payload bytes; bytes outside the slices stay untouched
+    sentinel = 77 if elem_bytes != 4 else -5.0
+    flat = torch.full((len(vals),), sentinel, dtype=v_d.dtype, device="cuda")
+    ops.unpack_ragged(packed, off_d, flat)
+    got = flat.cpu().numpy()
+    assert np.array_equal(got[:off[-1]], vals[:off[-1]]) and np.all(got[off[-1]:] == sentinel)
+    # scatter form: packed row r -> request dst_index[r]
+    flat2 = torch.full((len(vals),), sentinel, dtype=v_d.dtype, device="cuda")
+    ops.unpack_ragged(packed_sel, off_d, flat2, torch.from_numpy(sel).cuda())
+    want = np.full(len(vals), sentinel, dtype=vals.dtype)
+    for q in sel:
+        want[off[q]:off[q + 1]] = vals[off[q]:off[q + 1]]
+    assert np.array_equal(flat2.cpu().numpy(), want)
+
+
+def test_pack_truncates_rows_longer_than_lpad_and_handles_empty():
+    from die import ops
+    vals = np.arange(100, dtype=np.float32)
+    off = np.array([0, 0, 30, 30, 100], dtype=np.int64)
+    packed, lengths = ops.pack_ragged(torch.from_numpy(vals).cuda(), torch.from_numpy(off).cuda(), 32)
+    assert lengths.cpu().tolist() == [0, 30, 0, 70]
+    assert np.array_equal(packed.cpu().numpy(), pack_ref(vals, off, 32))
+    empty, _ = ops.pack_ragged(torch.zeros(4, device="cuda"), torch.zeros(1, dtype=torch.int64, device="cuda"), 8)
+    assert empty.shape == (0, 8)
+
+
+def test_pack_unpack_full_size_roundtrip_property():
+    """configs[2] shape: 64 flushes x 256 requests of 16..2048 fp32 -> pack -> unpack == identity."""
+    from die import ops
+    rng = np.random.default_rng(2)
+    vals, off, lens = ragged(rng, 256 * 64, 2048, 4, 16)
+    v_d, off_d = torch.from_numpy(vals).cuda(), torch.from_numpy(off).cuda()
+    packed, lengths = ops.pack_ragged(v_d, off_d, 2048)
+    flat = torch.zeros_like(v_d)
+    ops.unpack_ragged(packed, off_d, flat)
+    assert torch.equal(flat[:off[-1]], v_d[:off[-1]])
+    assert int(lengths.sum()) == int(off[-1])
+    # checksum of the padded batch == checksum of the ragged payload (padding is all zero)
+    assert int(packed.view(torch.int32).to(torch.int64).sum()) == int(v_d[:off[-1]].view(torch.int32).to(torch.int64).sum())
+
+
+def test_echo_is_bit_exact():
+    from die import ops
+    for n in (1, 5, 4096 * 128, 1000003):
+        x = torch.randn(n, device="cuda")
+        assert torch.equal(ops.echo_fwd(x), x)
+    xb = torch.randint(0, 255, (1001,), dtype=torch.uint8, device="cuda")
+    assert torch.equal(ops.echo_fwd(xb[1:]), xb[1:])  # unaligned bytes
+
+
+@pytest.mark.parametrize("B,K,N", [(4096, 128, 128), (1, 128, 128), (63, 100, 72), (1000, 2048, 256)])
+def test_linear_fp32_within_tolerance_of_f64_oracle(B, K, N):
+    """Tolerance (oracle/models.py): |d| <= 1e-5 * sum_k |x_k w_k| + 1e-6 for the fp32 FMA path."""
+    from die import ops
+    rng = np.random.default_rng(B + K)
+    x = rng.standard_normal((B, K)).astype(np.float32)
+    w = (rng.standard_normal((N, K)) / np.sqrt(K)).astype(np.float32)
+    b = rng.standard_normal(N).astype(np.float32)
+    y = ops.linear_fwd(torch.from_numpy(x).cuda(), torch.from_numpy(w).cuda(), torch.from_numpy(b).cuda()).cpu().numpy()
+    want = models.linear_f64(x, w, b)
+    tol = 1e-5 * models.linear_abs_bound(x, w) + 1e-6
+    assert np.all(np.abs(y.astype(np.float64) - want) <= tol)
