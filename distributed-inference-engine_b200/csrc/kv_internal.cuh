@@ -157,7 +157,9 @@ inline KvView view_of(const die_kv* kv) {
 }
 
 // n_rows > 0: the table hands out result-row handles in [0, n_rows) as values (pipeline mode).
-die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_rows, die_kv** out);
+// min_batch: the table is sized so that one launch sequence can take a batch of this many ops.
+die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_rows, uint64_t min_batch,
+                            die_kv** out);
 
 // Batched KVCache.get; stamps are kv->tail + i.  Advances kv->tail by B.
 die_status_t kv_get_batch_impl(die_kv* kv, const uint32_t* digests, int32_t B, double now, uint8_t* hit_out,

@@ -558,15 +558,16 @@ static uint64_t next_pow2(uint64_t x) {
     return p;
 }
 
-die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_rows, die_kv** out) {
+die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_rows, uint64_t min_batch,
+                            die_kv** out) {
     if (max_size > (1ull << 30)) DIE_FAIL(DIE_ERR_TOO_LARGE, "die_kv_create: max_size > 2^30");
     die_kv* kv = new die_kv();
     memset(kv, 0, sizeof(*kv));
     DIE_CUDA(cudaGetDevice(&kv->device));
     kv->max_size = max_size;
     kv->default_ttl = default_ttl;
-    kv->capacity = next_pow2(std::max<uint64_t>(2 * max_size, 4096));
-    kv->ring_cap = next_pow2(std::max<uint64_t>(4 * max_size, 1ull << 20));
+    kv->capacity = next_pow2(std::max<uint64_t>(std::max<uint64_t>(2 * max_size, 8 * min_batch), 4096));
+    kv->ring_cap = next_pow2(std::max<uint64_t>(std::max<uint64_t>(4 * max_size, 8 * min_batch), 1ull << 20));
     kv->max_chunk = std::min<uint64_t>(kv->capacity / 8, std::min<uint64_t>(kv->ring_cap / 4, 1ull << 22));
     kv->tail = 1;
     kv->head_lb = 1;
@@ -732,7 +733,7 @@ extern "C" die_status_t die_kv_create(uint64_t max_size, int32_t policy, double 
     if (!out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_create: null out");
     if (policy != DIE_KV_POLICY_LRU)
         DIE_FAIL(DIE_ERR_UNSUPPORTED, "die_kv_create: only eviction_policy='lru' is built (policy=%d)", policy);
-    return kv_create_impl(max_size, default_ttl, 0, out);
+    return kv_create_impl(max_size, default_ttl, 0, 0, out);
 }
 
 extern "C" die_status_t die_kv_destroy(die_kv_t* kv) {

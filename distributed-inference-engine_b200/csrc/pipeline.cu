@@ -171,7 +171,7 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
     p->cfg.bias = nullptr;
     const uint64_t B = (uint64_t)cfg->max_batch;
     p->n_rows = cfg->kv_max_size + B + 64;
-    DIE_TRY(kv_create_impl(cfg->kv_max_size, cfg->default_ttl, p->n_rows, &p->kv));
+    DIE_TRY(kv_create_impl(cfg->kv_max_size, cfg->default_ttl, p->n_rows, B, &p->kv));
     if ((uint64_t)cfg->max_batch > p->kv->max_chunk)
         DIE_FAIL(DIE_ERR_TOO_LARGE, "die_pipeline_create: max_batch %d exceeds the table's batch limit %llu",
                  cfg->max_batch, (unsigned long long)p->kv->max_chunk);
