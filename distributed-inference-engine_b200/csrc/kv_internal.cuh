@@ -118,6 +118,72 @@ __device__ __forceinline__ void release_row(const KvView& kv, unsigned long long
 __device__ __forceinline__ unsigned long long acquire_row(const KvView& kv) {
     return kv.free_rows[atomicAdd(&kv.st->free_top, (unsigned long long)(-1ll)) - 1ull];
 }
+// One KVCache.get (kvstore.py:136-164) / __contains__ (:221-228) probe.  Returns the code
+// (1 hit, 0 absent, 2 expired-and-deleted-by-this-op); `deleted` tells the caller to account for it.
+template <bool CONTAINS>
+__device__ __forceinline__ int kv_get_one(const KvView& kv, u128 key, double now, unsigned long long stamp,
+                                          unsigned long long& value, long long& slot) {
+    value = 0;
+    slot = kv_find(kv, key);
+    if (slot < 0) return 0;
+    Slot* sl = &kv.slots[slot];
+    double created, ttl;
+    ld_created_ttl(sl, created, ttl);
+    if (ttl_expired(now, created, ttl)) {
+        // delete(key) (kvstore.py:153-156); exactly one of several duplicate ops wins
+        const u128 old = cas128(sl, key, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+        slot = -1;
+        if (!fp_eq(old, key)) return 0;
+        value = ld_u64_cg(&sl->value);
+        sl->stamp = 0ull;
+        release_row(kv, value);
+        return 2;
+    }
+    value = ld_u64_cg(&sl->value);
+    if (!CONTAINS) {
+        atomicMax(&sl->stamp, stamp);  // move_to_end: the last toucher of the batch wins
+        kv.log[stamp & kv.rmask] = (uint32_t)slot;
+        atomicAdd(&sl->access_count, 1u);
+        sl->last_accessed = now;
+    }
+    return 1;
+}
+
+// Insert of a key that is known not to live in the table before this batch: claim the first free
+// slot of the probe chain with a 128-bit CAS on the fingerprint.  Duplicate ops of the same batch
+// converge on one slot (claimed == true for exactly one of them).
+__device__ __forceinline__ long long kv_claim_absent(const KvView& kv, u128 key, bool& claimed, bool& from_empty) {
+    claimed = false;
+    from_empty = false;
+    for (;;) {
+        unsigned long long cur = key.lo & kv.mask;
+        long long first_free = -1;
+        bool first_free_empty = false;
+        for (unsigned long long n = 0; n <= kv.mask; ++n) {
+            const u128 fp = ld_fp(&kv.slots[cur]);
+            if (fp_eq(fp, key)) return (long long)cur;  // a duplicate op of this batch already inserted it
+            if (fp_tomb(fp) && first_free < 0) first_free = (long long)cur;
+            if (fp_empty(fp)) {
+                if (first_free < 0) {
+                    first_free = (long long)cur;
+                    first_free_empty = true;
+                }
+                break;
+            }
+            cur = (cur + 1) & kv.mask;
+        }
+        if (first_free < 0) continue;  // cannot happen: the host keeps >= capacity/4 EMPTY slots
+        const u128 expect = first_free_empty ? u128{0ull, 0ull} : u128{FP_TOMB_WORD, FP_TOMB_WORD};
+        const u128 old = cas128(&kv.slots[first_free], expect, key);
+        if (fp_eq(old, expect)) {
+            claimed = true;
+            from_empty = first_free_empty;
+            return first_free;
+        }
+        if (fp_eq(old, key)) return first_free;
+        // somebody else's key took the slot: walk the chain again
+    }
+}
 #endif  // __CUDACC__
 
 }  // namespace die
@@ -127,6 +193,7 @@ struct die_kv {
     uint64_t max_size, capacity, ring_cap;
     double default_ttl;
     die::Slot* slots;
+    die::Slot* slots_spare;  // second table buffer, allocated at the first rebuild and reused
     uint32_t* log;
     die::KvState* st;
     uint32_t* free_rows;  // pipeline mode only
@@ -160,6 +227,10 @@ inline KvView view_of(const die_kv* kv) {
 // min_batch: the table is sized so that one launch sequence can take a batch of this many ops.
 die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_rows, uint64_t min_batch,
                             die_kv** out);
+
+// Host-side guard run before a batch of n ops: keeps the LRU ring and the EMPTY-slot reserve safe
+// using conservative host bounds (synchronises only when a bound is about to be crossed).
+die_status_t kv_reserve(die_kv* kv, uint64_t n, bool inserts, cudaStream_t s);
 
 // Batched KVCache.get; stamps are kv->tail + i.  Advances kv->tail by B.
 die_status_t kv_get_batch_impl(die_kv* kv, const uint32_t* digests, int32_t B, double now, uint8_t* hit_out,

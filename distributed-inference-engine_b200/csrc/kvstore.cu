@@ -20,37 +20,10 @@ kv_get_kernel(KvView kv, const uint4* __restrict__ digests, int B, double now, u
     const int i = blockIdx.x * KV_THREADS + threadIdx.x;
     const bool active = i < B;
     int code = 0;
-    unsigned long long value = 0;
-    long long s = -1;
     if (active) {
-        const u128 key = fp_of(digests[i]);
-        s = kv_find(kv, key);
-        if (s >= 0) {
-            Slot* sl = &kv.slots[s];
-            double created, ttl;
-            ld_created_ttl(sl, created, ttl);
-            if (ttl_expired(now, created, ttl)) {
-                // delete(key) (kvstore.py:153-156); exactly one of several duplicate ops wins
-                const u128 old = cas128(sl, key, u128{FP_TOMB_WORD, FP_TOMB_WORD});
-                if (fp_eq(old, key)) {
-                    value = ld_u64_cg(&sl->value);
-                    sl->stamp = 0ull;
-                    release_row(kv, value);
-                    code = 2;
-                }
-                s = -1;
-            } else {
-                code = 1;
-                value = ld_u64_cg(&sl->value);
-                if (!CONTAINS) {
-                    const unsigned long long stamp = t + (unsigned long long)i;
-                    atomicMax(&sl->stamp, stamp);  // move_to_end: the last toucher wins
-                    kv.log[stamp & kv.rmask] = (uint32_t)s;
-                    atomicAdd(&sl->access_count, 1u);
-                    sl->last_accessed = now;
-                }
-            }
-        }
+        unsigned long long value;
+        long long s;
+        code = kv_get_one<CONTAINS>(kv, fp_of(digests[i]), now, t + (unsigned long long)i, value, s);
         code_out[i] = (uint8_t)code;
         if (value_out) value_out[i] = value;
         if (slot_out) slot_out[i] = code == 1 ? (int32_t)s : -1;
@@ -248,46 +221,7 @@ kv_set_claim_kernel(KvView kv, const uint4* __restrict__ digests, int M, double 
         const u128 key = fp_of(digests[i]);
         long long s = have_precheck ? op_slot[i] : -1;
         const bool pre = s >= 0;
-        if (!pre) {
-            // insert: claim the first free slot of the probe chain with a 128-bit CAS on the fingerprint
-            for (;;) {
-                unsigned long long cur = key.lo & kv.mask;
-                long long first_free = -1;
-                bool first_free_empty = false, found = false;
-                for (unsigned long long n = 0; n <= kv.mask; ++n) {
-                    const u128 fp = ld_fp(&kv.slots[cur]);
-                    if (fp_eq(fp, key)) {  // a duplicate op of this batch already inserted it
-                        s = (long long)cur;
-                        found = true;
-                        break;
-                    }
-                    if (fp_tomb(fp) && first_free < 0) first_free = (long long)cur;
-                    if (fp_empty(fp)) {
-                        if (first_free < 0) {
-                            first_free = (long long)cur;
-                            first_free_empty = true;
-                        }
-                        break;
-                    }
-                    cur = (cur + 1) & kv.mask;
-                }
-                if (found) break;
-                if (first_free < 0) continue;  // cannot happen: the host keeps >= capacity/4 EMPTY slots
-                const u128 expect = first_free_empty ? u128{0ull, 0ull} : u128{FP_TOMB_WORD, FP_TOMB_WORD};
-                const u128 old = cas128(&kv.slots[first_free], expect, key);
-                if (fp_eq(old, expect)) {
-                    s = first_free;
-                    claimed = true;
-                    from_empty = first_free_empty;
-                    break;
-                }
-                if (fp_eq(old, key)) {
-                    s = first_free;
-                    break;
-                }
-                // somebody else's key took the slot: walk the chain again
-            }
-        }
+        if (!pre) s = kv_claim_absent(kv, key, claimed, from_empty);
         Slot* sl = &kv.slots[s];
         const unsigned long long stamp = t + (unsigned long long)i;
         const unsigned long long old_stamp = atomicMax(&sl->stamp, stamp);
@@ -566,9 +500,9 @@ die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_ro
     DIE_CUDA(cudaGetDevice(&kv->device));
     kv->max_size = max_size;
     kv->default_ttl = default_ttl;
-    kv->capacity = next_pow2(std::max<uint64_t>(std::max<uint64_t>(2 * max_size, 8 * min_batch), 4096));
+    kv->capacity = next_pow2(std::max<uint64_t>(std::max<uint64_t>(4 * max_size, 16 * min_batch), 4096));
     kv->ring_cap = next_pow2(std::max<uint64_t>(std::max<uint64_t>(4 * max_size, 8 * min_batch), 1ull << 20));
-    kv->max_chunk = std::min<uint64_t>(kv->capacity / 8, std::min<uint64_t>(kv->ring_cap / 4, 1ull << 22));
+    kv->max_chunk = std::min<uint64_t>(kv->capacity / 16, std::min<uint64_t>(kv->ring_cap / 4, 1ull << 22));
     kv->tail = 1;
     kv->head_lb = 1;
     kv->n_rows = n_rows;
@@ -618,10 +552,10 @@ static die_status_t kv_maintain(die_kv* kv, int force, cudaStream_t s) {
         kv->head_lb = kv->tail;
         kv->tail += kept;
     }
-    const uint64_t empties = kv->capacity - h.size - h.n_tomb;
-    if (force || empties < kv->capacity / 4 + kv->max_chunk) {
-        Slot* fresh = nullptr;
-        DIE_CUDA(cudaMalloc(&fresh, kv->capacity * sizeof(Slot)));
+    // probe chains stay short while used slots (live + tombstones) stay under 3/8 of the capacity
+    if (force || h.size + h.n_tomb + kv->max_chunk > kv->capacity / 8 * 3) {
+        Slot* fresh = kv->slots_spare;
+        if (!fresh) DIE_CUDA(cudaMalloc(&fresh, kv->capacity * sizeof(Slot)));
         DIE_CUDA(cudaMemsetAsync(fresh, 0, kv->capacity * sizeof(Slot), s));
         Slot* old = kv->slots;
         kv->slots = fresh;
@@ -632,7 +566,7 @@ static die_status_t kv_maintain(die_kv* kv, int force, cudaStream_t s) {
         DIE_CUDA(cudaMemcpyAsync(&kv->st->n_empty_claimed, &h.n_empty_claimed, sizeof(h.n_empty_claimed),
                                  cudaMemcpyHostToDevice, s));
         DIE_CUDA(cudaStreamSynchronize(s));
-        cudaFree(old);
+        kv->slots_spare = old;  // kept for the next rebuild: no cudaMalloc/cudaFree on the serving path
         kv->live_at_rebuild = h.size;
     } else {
         kv->live_at_rebuild = h.size + h.n_tomb;  // tighten the conservative bound with the real count
@@ -642,9 +576,9 @@ static die_status_t kv_maintain(die_kv* kv, int force, cudaStream_t s) {
 }
 
 // Called before a batch of n ops: keeps the ring and the EMPTY-slot reserve safe using host bounds only.
-static die_status_t reserve_for_batch(die_kv* kv, uint64_t n, bool inserts, cudaStream_t s) {
+die_status_t kv_reserve(die_kv* kv, uint64_t n, bool inserts, cudaStream_t s) {
     bool need = (kv->tail + n - kv->head_lb) > kv->ring_cap - 16;
-    if (inserts && kv->live_at_rebuild + kv->claims_ub + n + kv->capacity / 4 > kv->capacity) need = true;
+    if (inserts && kv->live_at_rebuild + kv->claims_ub + n > kv->capacity / 8 * 3) need = true;
     if (need) DIE_TRY(kv_maintain(kv, 0, s));
     if ((kv->tail + n - kv->head_lb) > kv->ring_cap - 16) DIE_TRY(kv_maintain(kv, 1, s));
     if (inserts) kv->claims_ub += n;
@@ -655,7 +589,7 @@ die_status_t kv_get_batch_impl(die_kv* kv, const uint32_t* digests, int32_t B, d
                                uint64_t* value_out, int32_t* slot_out, cudaStream_t s) {
     for (int64_t done = 0; done < B;) {
         const int n = (int)std::min<int64_t>(B - done, (int64_t)kv->max_chunk);
-        DIE_TRY(reserve_for_batch(kv, n, false, s));
+        DIE_TRY(kv_reserve(kv, n, false, s));
         DIE_LAUNCH(ST_KV_GET, s, kv_get_kernel<false><<<ceil_div(n, KV_THREADS), KV_THREADS, 0, s>>>(
             view_of(kv), reinterpret_cast<const uint4*>(digests) + done, n, now, kv->tail, hit_out + done,
             reinterpret_cast<unsigned long long*>(value_out ? value_out + done : nullptr),
@@ -681,7 +615,7 @@ die_status_t kv_set_batch_impl(die_kv* kv, const uint32_t* digests, const uint64
     for (int64_t done = 0; done < M;) {
         const int n = (int)std::min<int64_t>(M - done, (int64_t)kv->max_chunk);
         DIE_TRY(ensure_scratch(kv, n));
-        DIE_TRY(reserve_for_batch(kv, n, true, s));
+        DIE_TRY(kv_reserve(kv, n, true, s));
         const KvView v = view_of(kv);
         const uint4* dg = reinterpret_cast<const uint4*>(digests) + done;
         const unsigned long long* vals =
@@ -739,6 +673,7 @@ extern "C" die_status_t die_kv_create(uint64_t max_size, int32_t policy, double 
 extern "C" die_status_t die_kv_destroy(die_kv_t* kv) {
     if (!kv) return DIE_OK;
     cudaFree(kv->slots);
+    cudaFree(kv->slots_spare);
     cudaFree(kv->log);
     cudaFree(kv->st);
     cudaFree(kv->op_slot);

@@ -1,36 +1,48 @@
 // Composed hot path for one owner shard: route -> get -> pack misses -> model -> unpack -> set.
 // This is SURVEY.md call-stack (E) -- the coordinator the reference's README.md:56-60 describes
-// but never wrote -- built from the same kernels the stand-alone C-ABI entry points launch.
+// but never wrote.  Cached values are result rows in `arena`; the table hands out row handles.
 //
-// Per flushed batch of B fixed-width requests (all device-side, no host sync):
-//   1 route_md5_kernel        keys -> 128-bit digests                       (model_registry.py:159)
-//   2 kv_get_kernel           hit / miss / expired, LRU stamps, row handles (kvstore.py:136-164)
-//   3 miss_scan_kernel        rank of every miss in request order           (batcher.py:211 order)
-//   4 pack_hits_kernel        misses: payload -> packed[rank];  hits: result row -> out
-//   5 model forward           packed -> packed_out (echo / linear)          (fake_model.py:52)
-//   6 kv set (3 kernels)      misses inserted in request order, LRU evictions (kvstore.py:104-134)
-//   7 unpack_store_kernel     packed_out[rank] -> out[q] and -> the cached result row of the
-//                             op that owns the slot (last duplicate wins)   (batcher.py:225-227)
-// Cached values are result rows in `arena`; the table hands out row handles (kv_internal.cuh).
+// Fast sequence (max_batch <= kv_max_size, so a batch can never need more victims than the table
+// holds and the sequential replay of kvstore.cu is unreachable) -- 4 launches per flushed batch:
+//   1 pipe_get_kernel         MD5 of the keys (model_registry.py:159) + KVCache.get per request
+//                             (kvstore.py:136-164); the last CTA to finish then ranks the misses in
+//                             request order (batcher.py:211) and walks the LRU log for the victim
+//                             candidates of this batch's inserts (kvstore.py:82-93)
+//   2 pipe_claim_pack_kernel  misses: insert key (kvstore.py:104-134) | PACK payload -> packed[rank];
+//                             hits: cached result row -> out
+//   3 model forward           packed -> packed_out (echo / linear)            (fake_model.py:52)
+//   4 pipe_unpack_evict_kernel UNPACK packed_out[rank] -> out[q] (batcher.py:225-227) and -> the
+//                             cached row of the op that owns the slot | evict the LRU victims
+// General sequence (tiny caches): the stand-alone kernels of kvstore.cu, 9 launches.
 #include "kv_internal.cuh"
 #include "model_internal.cuh"
+#include "route_device.cuh"
+
+struct PipeCtrl {
+    unsigned int n_miss, ticket_get, ticket_claim, any_dup;
+    unsigned long long e_ub, e_final;
+};
 
 struct die_pipeline {
     die_pipeline_config_t cfg;
     die_kv* kv;
+    bool fast;
     uint64_t n_rows;
-    float* arena;     // [n_rows, dim_out]
-    float* W;         // [dim_out, dim_in]
-    float* bias;      // [dim_out]
-    uint32_t* digests;  // [B,4]
-    int32_t* shard;     // [B]
-    uint8_t* code;      // [B]
-    uint64_t* value;    // [B]
-    int32_t* miss_rank; // [B]
-    uint32_t* n_miss;   // [1]
-    int32_t* set_slot;  // [B]
-    float* packed_in;   // [B, dim_in]
-    float* packed_out;  // [B, dim_out]
+    float* arena;        // [n_rows, dim_out]
+    float* W;            // [dim_out, dim_in]
+    float* bias;         // [dim_out]
+    uint32_t* digests;   // [B,4]
+    int32_t* shard;      // [B]
+    uint8_t* code;       // [B]
+    uint64_t* value;     // [B] result-row handle of a hit
+    int32_t* miss_rank;  // [B]
+    int32_t* set_slot;   // [B]
+    int32_t* set_row;    // [B]
+    uint32_t* cand_slot; // [B] victim candidates, LRU order
+    uint64_t* cand_pos;  // [B] their log positions
+    PipeCtrl* ctrl;
+    float* packed_in;    // [B, dim_in]
+    float* packed_out;   // [B, dim_out]
     // staging for the host-buffer entry point
     uint8_t* d_key_bytes;
     int64_t* d_key_off;
@@ -41,7 +53,274 @@ struct die_pipeline {
 
 namespace die {
 
-// rank[q] = number of misses before q (request order) for misses, -1 for hits; *n_miss = total.
+constexpr int PT = 256;  // threads per CTA of the pipeline kernels (== ROUTE_THREADS)
+static_assert(PT == ROUTE_THREADS, "the fused get kernel stages keys with the route kernel's CTA shape");
+
+// block-wide exclusive scan for PT threads
+__device__ __forceinline__ unsigned block_scan_pt(unsigned cnt, unsigned& excl, unsigned* s_warp) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned w = lane < PT / 32 ? s_warp[lane] : 0u;
+#pragma unroll
+        for (int o = 1; o < PT / 32; o <<= 1) {
+            const unsigned v = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += v;
+        }
+        if (lane < PT / 32) s_warp[lane] = w;
+    }
+    __syncthreads();
+    excl = (warp ? s_warp[warp - 1] : 0u) + (incl - cnt);
+    return s_warp[PT / 32 - 1];
+}
+
+__device__ __forceinline__ unsigned ld_u8_cg(const uint8_t* p) {
+    unsigned r;
+    asm volatile("ld.global.cg.u8 %0, [%1];" : "=r"(r) : "l"(p) : "memory");
+    return r;
+}
+
+struct PipeBufs {
+    uint8_t* code;
+    unsigned long long* value;
+    int32_t* miss_rank;
+    int32_t* set_slot;
+    int32_t* set_row;
+    uint32_t* cand_slot;
+    unsigned long long* cand_pos;
+    PipeCtrl* ctrl;
+};
+
+// Tail of the get kernel, run by the last CTA: miss ranks + victim candidates for this batch.
+__device__ void pipe_scan_and_window(const KvView& kv, const PipeBufs& pb, int B, unsigned long long t_set) {
+    __shared__ unsigned s_warp[PT / 32];
+    __shared__ unsigned long long s_first;
+    const int tid = threadIdx.x;
+    constexpr int ITEMS = 8;
+    unsigned base = 0;
+    for (int pos = 0; pos < B; pos += PT * ITEMS) {
+        const int q0 = pos + tid * ITEMS;
+        bool miss[ITEMS];
+        unsigned cnt = 0;
+#pragma unroll
+        for (int k = 0; k < ITEMS; ++k) {
+            miss[k] = q0 + k < B && ld_u8_cg(pb.code + q0 + k) != 1u;
+            cnt += miss[k];
+        }
+        unsigned excl;
+        const unsigned total = block_scan_pt(cnt, excl, s_warp);
+        unsigned r = base + excl;
+#pragma unroll
+        for (int k = 0; k < ITEMS; ++k)
+            if (q0 + k < B) pb.miss_rank[q0 + k] = miss[k] ? (int32_t)r++ : -1;
+        base += total;
+        __syncthreads();
+    }
+    KvState* st = kv.st;
+    const unsigned long long size = ld_u64_cg(&st->size), head = ld_u64_cg(&st->head);
+    const unsigned long long e_ub = size + base > kv.max_size ? size + base - kv.max_size : 0ull;
+    if (tid == 0) {
+        s_first = ~0ull;
+        pb.ctrl->n_miss = base;
+        pb.ctrl->e_ub = e_ub;
+        pb.ctrl->e_final = 0ull;
+        pb.ctrl->ticket_get = 0u;
+        pb.ctrl->ticket_claim = 0u;
+        pb.ctrl->any_dup = 0u;
+    }
+    __syncthreads();
+    // the first e_ub current log records from the head are the LRU victims, oldest first (kvstore.py:89-91)
+    constexpr int WI = 4;
+    unsigned long long found = 0;
+    for (unsigned long long pos = head; found < e_ub && pos < t_set; pos += (unsigned long long)PT * WI) {
+        bool valid[WI];
+        uint32_t slot[WI];
+        unsigned cnt = 0;
+#pragma unroll
+        for (int k = 0; k < WI; ++k) {
+            const unsigned long long p = pos + (unsigned long long)tid * WI + k;
+            slot[k] = 0;
+            valid[k] = false;
+            if (p < t_set) {
+                slot[k] = kv.log[p & kv.rmask];
+                valid[k] = (unsigned long long)slot[k] <= kv.mask && ld_u64_cg(&kv.slots[slot[k]].stamp) == p;
+            }
+            cnt += valid[k];
+        }
+        unsigned excl;
+        const unsigned total = block_scan_pt(cnt, excl, s_warp);
+        unsigned long long rank = found + excl;
+#pragma unroll
+        for (int k = 0; k < WI; ++k) {
+            if (!valid[k]) continue;
+            const unsigned long long p = pos + (unsigned long long)tid * WI + k;
+            if (rank == 0) s_first = p;
+            if (rank < e_ub) {
+                pb.cand_slot[rank] = slot[k];
+                pb.cand_pos[rank] = p;
+            }
+            ++rank;
+        }
+        found += total;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        if (found < e_ub) st->status = DIE_ERR_INVALID;  // unreachable when max_batch <= max_size
+        if (s_first != ~0ull && s_first > head) st->head = s_first;  // drop leading stale records
+    }
+}
+
+template <bool FROM_KEYS>
+__global__ void __launch_bounds__(PT)
+pipe_get_kernel(KvView kv, PipeBufs pb, const uint8_t* __restrict__ key_bytes, const int64_t* __restrict__ key_off,
+                uint4* __restrict__ digests, int B, double now, unsigned long long t_get, unsigned long long t_set) {
+    __shared__ __align__(16) uint8_t stage[FROM_KEYS ? ROUTE_STAGE_BYTES + 32 : 16];
+    __shared__ bool s_last;
+    const int i = blockIdx.x * PT + threadIdx.x;
+    const bool active = i < B;
+    u128 key{0ull, 0ull};
+    if (FROM_KEYS) {
+        const Md5State st = cta_hash_keys(key_bytes, key_off, B, stage);
+        if (active) {
+            const uint4 d = make_uint4(st.a, st.b, st.c, st.d);
+            digests[i] = d;
+            key = fp_of(d);
+        }
+    } else if (active) {
+        key = fp_of(digests[i]);
+    }
+    int code = 0;
+    if (active) {
+        unsigned long long value;
+        long long s;
+        code = kv_get_one<false>(kv, key, now, t_get + (unsigned long long)i, value, s);
+        pb.code[i] = (uint8_t)code;
+        pb.value[i] = value;
+    }
+    warp_add(&kv.st->hits, active && code == 1);
+    warp_add(&kv.st->misses, active && code != 1);
+    const bool deleted = active && code == 2;
+    warp_sub(&kv.st->size, deleted);
+    warp_add(&kv.st->n_tomb, deleted);
+    // the last CTA to get here has every CTA's results in L2 and runs the batch-wide tail
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&pb.ctrl->ticket_get, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    pipe_scan_and_window(kv, pb, B, t_set);
+}
+
+// CTAs [0, g_claim): KVCache.set of every miss (all known absent).  CTAs [g_claim, ...): PACK + hit copy.
+__global__ void __launch_bounds__(PT)
+pipe_claim_pack_kernel(KvView kv, PipeBufs pb, const uint4* __restrict__ digests, int B, double now,
+                       unsigned long long t_set, int g_claim, const int4* __restrict__ payload,
+                       const int4* __restrict__ arena, int vin, int vout, int4* __restrict__ packed_in,
+                       int4* __restrict__ out) {
+    if ((int)blockIdx.x < g_claim) {
+        __shared__ bool s_last;
+        const int i = blockIdx.x * PT + threadIdx.x;
+        const bool active = i < B && pb.code[i] != 1;
+        bool claimed = false, from_empty = false;
+        if (active) {
+            const u128 key = fp_of(digests[i]);
+            const long long s = kv_claim_absent(kv, key, claimed, from_empty);
+            Slot* sl = &kv.slots[s];
+            const unsigned long long stamp = t_set + (unsigned long long)i;
+            atomicMax(&sl->stamp, stamp);
+            int32_t row = -1;
+            if (claimed) {
+                row = (int32_t)acquire_row(kv);
+                sl->value = (unsigned long long)row;
+                sl->created_at = now;
+                sl->ttl = kv.default_ttl;
+                sl->last_accessed = now;
+                sl->access_count = 0u;
+            } else {
+                pb.ctrl->any_dup = 1u;  // same key twice in the batch: the later op owns the cached row
+            }
+            kv.log[stamp & kv.rmask] = (uint32_t)s;
+            pb.set_slot[i] = (int32_t)s;
+            pb.set_row[i] = row;
+        }
+        warp_add(&kv.st->size, active && claimed);
+        warp_add(&kv.st->n_empty_claimed, active && claimed && from_empty);
+        warp_sub(&kv.st->n_tomb, active && claimed && !from_empty);
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) s_last = atomicAdd(&pb.ctrl->ticket_claim, 1u) == (unsigned)g_claim - 1;
+        __syncthreads();
+        if (s_last && threadIdx.x == 0) {
+            __threadfence();
+            const unsigned long long size = ld_u64_cg(&kv.st->size);
+            pb.ctrl->e_final = size > kv.max_size ? size - kv.max_size : 0ull;  // _evict_if_needed count
+        }
+        return;
+    }
+    const int vmax = vin > vout ? vin : vout;
+    const long long total = (long long)B * vmax;
+    const long long stride = (long long)(gridDim.x - g_claim) * PT;
+    for (long long v = (long long)(blockIdx.x - g_claim) * PT + threadIdx.x; v < total; v += stride) {
+        const long long q = v / vmax;
+        const int c = (int)(v - q * vmax);
+        if (pb.code[q] == 1) {
+            if (c < vout) stg_stream(out + q * vout + c, ldg_stream(arena + (long long)pb.value[q] * vout + c));
+        } else if (c < vin) {
+            stg_stream(packed_in + (long long)pb.miss_rank[q] * vin + c, ldg_stream(payload + q * vin + c));
+        }
+    }
+}
+
+// CTAs [0, g_evict): evict the e_final least-recently-used entries.  Rest: UNPACK + store the cached rows.
+__global__ void __launch_bounds__(PT)
+pipe_unpack_evict_kernel(KvView kv, PipeBufs pb, const int4* __restrict__ packed_out, unsigned long long t_set, int B,
+                         int g_evict, int vout, int4* __restrict__ out, int4* __restrict__ arena) {
+    if ((int)blockIdx.x < g_evict) {
+        const unsigned long long e = pb.ctrl->e_final;
+        const unsigned long long g = (unsigned long long)blockIdx.x * PT + threadIdx.x;
+        if (g < e) {
+            Slot* sl = &kv.slots[pb.cand_slot[g]];
+            release_row(kv, sl->value);
+            st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+            sl->stamp = 0ull;
+        }
+        if (g == 0 && e > 0) {  // nobody else reads these counters in this kernel
+            KvState* st = kv.st;
+            st->size -= e;
+            st->evictions += e;
+            st->n_tomb += e;
+            st->head = pb.cand_pos[e - 1] + 1;
+        }
+        return;
+    }
+    const bool any_dup = pb.ctrl->any_dup != 0u;
+    const long long total = (long long)B * vout;
+    const long long stride = (long long)(gridDim.x - g_evict) * PT;
+    for (long long v = (long long)(blockIdx.x - g_evict) * PT + threadIdx.x; v < total; v += stride) {
+        const long long q = v / vout;
+        const int c = (int)(v - q * vout);
+        if (pb.code[q] == 1) continue;
+        const int4 y = ldg_stream(packed_out + (long long)pb.miss_rank[q] * vout + c);
+        stg_stream(out + v, y);
+        if (c == 0) pb.code[q] = 0;  // callers see 1 = served from the cache, 0 = computed (2 -> 0)
+        long long row = pb.set_row[q];
+        if (any_dup) {
+            const Slot* sl = &kv.slots[pb.set_slot[q]];
+            row = sl->stamp == t_set + (unsigned long long)q ? (long long)sl->value : -1;
+        }
+        if (row >= 0) stg_stream(arena + row * vout + c, y);
+    }
+}
+
+// ---- general sequence (tiny caches), built from the stand-alone kernels ------------------------------
 __global__ void __launch_bounds__(1024)
 miss_scan_kernel(const uint8_t* __restrict__ code, int B, int32_t* __restrict__ rank, uint32_t* __restrict__ n_miss) {
     __shared__ unsigned s_warp[32];
@@ -67,8 +346,6 @@ miss_scan_kernel(const uint8_t* __restrict__ code, int B, int32_t* __restrict__ 
     if (threadIdx.x == 0) *n_miss = base;
 }
 
-// misses: packed_in[rank[q]] = payload[q]   (PACK, batcher.py:211)
-// hits  : out[q] = arena[value[q]]          (the cached result)
 __global__ void __launch_bounds__(256)
 pack_hits_kernel(const int4* __restrict__ payload, const uint8_t* __restrict__ code,
                  const int32_t* __restrict__ rank, const unsigned long long* __restrict__ value,
@@ -94,8 +371,6 @@ echo_rows_kernel(const int4* __restrict__ in, int4* __restrict__ out, int vrow, 
         stg_stream(out + v, ldg_stream(in + v));
 }
 
-// UNPACK (batcher.py:225-227): result row of miss q goes to out[q]; the op that owns the table
-// slot after the batch (stamp == t_set + q, i.e. the last duplicate) also stores it in its row.
 __global__ void __launch_bounds__(256)
 unpack_store_kernel(KvView kv, const int4* __restrict__ packed_out, uint8_t* __restrict__ code,
                     const int32_t* __restrict__ rank, const int32_t* __restrict__ set_slot, unsigned long long t_set,
@@ -107,7 +382,7 @@ unpack_store_kernel(KvView kv, const int4* __restrict__ packed_out, uint8_t* __r
         if (code[q] == 1) continue;
         const int4 y = ldg_stream(packed_out + (long long)rank[q] * vout + c);
         stg_stream(out + v, y);
-        if (c == 0) code[q] = 0;  // callers see 1 = served from the cache, 0 = computed
+        if (c == 0) code[q] = 0;  // callers see 1 = served from the cache, 0 = computed (2 -> 0)
         const int32_t s = set_slot[q];
         if (s >= 0) {
             const Slot* sl = &kv.slots[s];
@@ -122,28 +397,80 @@ static int grid_256(long long items) {
     return (int)(blocks < 1 ? 1 : (blocks < cap ? blocks : cap));
 }
 
-static die_status_t run_owner(die_pipeline* p, const uint32_t* digests, int B, const float* payload, double now,
-                              float* out, uint8_t* hit_out, cudaStream_t s) {
+static die_status_t run_model(die_pipeline* p, int B, cudaStream_t s) {
+    const die_pipeline_config_t& c = p->cfg;
+    const uint32_t* n_miss = &p->ctrl->n_miss;
+    if (c.model == DIE_MODEL_ECHO) {
+        const int vin = c.dim_in / 4;
+        DIE_LAUNCH(ST_MODEL, s, echo_rows_kernel<<<grid_256((long long)B * vin), 256, 0, s>>>(
+            reinterpret_cast<const int4*>(p->packed_in), reinterpret_cast<int4*>(p->packed_out), vin, n_miss));
+        return DIE_OK;
+    }
+    if (c.model == DIE_MODEL_LINEAR_FP32)
+        return linear_f32_launch(p->packed_in, p->W, p->bias, p->packed_out, B, c.dim_in, c.dim_out, n_miss, s);
+    return linear_tf32_launch(p->packed_in, p->W, p->bias, p->packed_out, B, c.dim_in, c.dim_out, n_miss, s);
+}
+
+static PipeBufs bufs_of(die_pipeline* p, uint8_t* code) {
+    PipeBufs pb;
+    pb.code = code;
+    pb.value = reinterpret_cast<unsigned long long*>(p->value);
+    pb.miss_rank = p->miss_rank;
+    pb.set_slot = p->set_slot;
+    pb.set_row = p->set_row;
+    pb.cand_slot = p->cand_slot;
+    pb.cand_pos = reinterpret_cast<unsigned long long*>(p->cand_pos);
+    pb.ctrl = p->ctrl;
+    return pb;
+}
+
+// key_off != nullptr: hash the keys in the get kernel (digests are written to `digests`);
+// otherwise `digests` are inputs.
+static die_status_t run_fast(die_pipeline* p, const uint8_t* key_bytes, const int64_t* key_off, uint32_t* digests,
+                             int B, const float* payload, double now, float* out, uint8_t* hit_out, cudaStream_t s) {
+    const die_pipeline_config_t& c = p->cfg;
+    die_kv* kv = p->kv;
+    const int vin = c.dim_in / 4, vout = c.dim_out / 4;
+    uint8_t* code = hit_out ? hit_out : p->code;
+    DIE_TRY(kv_reserve(kv, (uint64_t)B, false, s));
+    DIE_TRY(kv_reserve(kv, (uint64_t)B, true, s));
+    const unsigned long long t_get = kv->tail, t_set = kv->tail + (unsigned long long)B;
+    kv->tail += 2ull * (unsigned long long)B;
+    const KvView v = view_of(kv);
+    const PipeBufs pb = bufs_of(p, code);
+    const int g = ceil_div(B, PT);
+    uint4* dg = reinterpret_cast<uint4*>(digests);
+    if (key_off)
+        DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<true><<<g, PT, 0, s>>>(v, pb, key_bytes, key_off, dg, B, now, t_get, t_set));
+    else
+        DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<false><<<g, PT, 0, s>>>(v, pb, nullptr, nullptr, dg, B, now, t_get, t_set));
+    const int g_pack = grid_256((long long)B * std::max(vin, vout));
+    DIE_LAUNCH(ST_KV_CLAIM, s, pipe_claim_pack_kernel<<<g + g_pack, PT, 0, s>>>(
+        v, pb, dg, B, now, t_set, g, reinterpret_cast<const int4*>(payload), reinterpret_cast<const int4*>(p->arena),
+        vin, vout, reinterpret_cast<int4*>(p->packed_in), reinterpret_cast<int4*>(out)));
+    DIE_TRY(run_model(p, B, s));
+    const int g_unpack = grid_256((long long)B * vout);
+    DIE_LAUNCH(ST_UNPACK_STORE, s, pipe_unpack_evict_kernel<<<g + g_unpack, PT, 0, s>>>(
+        v, pb, reinterpret_cast<const int4*>(p->packed_out), t_set, B, g, vout, reinterpret_cast<int4*>(out),
+        reinterpret_cast<int4*>(p->arena)));
+    return DIE_OK;
+}
+
+static die_status_t run_general(die_pipeline* p, const uint32_t* digests, int B, const float* payload, double now,
+                                float* out, uint8_t* hit_out, cudaStream_t s) {
     const die_pipeline_config_t& c = p->cfg;
     const int vin = c.dim_in / 4, vout = c.dim_out / 4;
     uint8_t* code = hit_out ? hit_out : p->code;
+    uint32_t* n_miss = &p->ctrl->n_miss;
     DIE_TRY(kv_get_batch_impl(p->kv, digests, B, now, code, p->value, nullptr, s));
-    DIE_LAUNCH(ST_MISS_SCAN, s, miss_scan_kernel<<<1, 1024, 0, s>>>(code, B, p->miss_rank, p->n_miss));
+    DIE_LAUNCH(ST_MISS_SCAN, s, miss_scan_kernel<<<1, 1024, 0, s>>>(code, B, p->miss_rank, n_miss));
     DIE_LAUNCH(ST_PACK_HITS, s, pack_hits_kernel<<<grid_256((long long)B * std::max(vin, vout)), 256, 0, s>>>(
         reinterpret_cast<const int4*>(payload), code, p->miss_rank,
         reinterpret_cast<const unsigned long long*>(p->value), reinterpret_cast<const int4*>(p->arena), B, vin, vout,
         reinterpret_cast<int4*>(p->packed_in), reinterpret_cast<int4*>(out)));
-    if (c.model == DIE_MODEL_ECHO) {
-        DIE_LAUNCH(ST_MODEL, s, echo_rows_kernel<<<grid_256((long long)B * vin), 256, 0, s>>>(reinterpret_cast<const int4*>(p->packed_in),
-                                                                       reinterpret_cast<int4*>(p->packed_out), vin,
-                                                                       p->n_miss));
-    } else if (c.model == DIE_MODEL_LINEAR_FP32) {
-        DIE_TRY(linear_f32_launch(p->packed_in, p->W, p->bias, p->packed_out, B, c.dim_in, c.dim_out, p->n_miss, s));
-    } else {
-        DIE_TRY(linear_tf32_launch(p->packed_in, p->W, p->bias, p->packed_out, B, c.dim_in, c.dim_out, p->n_miss, s));
-    }
+    DIE_TRY(run_model(p, B, s));
     const unsigned long long t_set = p->kv->tail;
-    DIE_TRY(kv_set_batch_impl(p->kv, digests, nullptr, nullptr, B, now, 0, code, 1, p->n_miss, p->set_slot, nullptr, s));
+    DIE_TRY(kv_set_batch_impl(p->kv, digests, nullptr, nullptr, B, now, 0, code, 1, n_miss, p->set_slot, nullptr, s));
     DIE_LAUNCH(ST_UNPACK_STORE, s, unpack_store_kernel<<<grid_256((long long)B * vout), 256, 0, s>>>(
         view_of(p->kv), reinterpret_cast<const int4*>(p->packed_out), code, p->miss_rank, p->set_slot, t_set, B, vout,
         reinterpret_cast<int4*>(out), reinterpret_cast<int4*>(p->arena)));
@@ -160,16 +487,17 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
         DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_create: max_batch > 0 and dims multiple of 4 fp32 required");
     if (cfg->model == DIE_MODEL_ECHO && cfg->dim_in != cfg->dim_out)
         DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_create: echo needs dim_in == dim_out");
-    if (cfg->model != DIE_MODEL_ECHO && (!cfg->weight || !cfg->bias))
-        DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_create: linear model needs weight and bias");
     if (cfg->model < DIE_MODEL_ECHO || cfg->model > DIE_MODEL_LINEAR_TF32)
         DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_create: unknown model %d", cfg->model);
+    if (cfg->model != DIE_MODEL_ECHO && (!cfg->weight || !cfg->bias))
+        DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_create: linear model needs weight and bias");
     die_pipeline* p = new die_pipeline();
     memset(p, 0, sizeof(*p));
     p->cfg = *cfg;
     p->cfg.weight = nullptr;
     p->cfg.bias = nullptr;
     const uint64_t B = (uint64_t)cfg->max_batch;
+    p->fast = B <= cfg->kv_max_size;
     p->n_rows = cfg->kv_max_size + B + 64;
     DIE_TRY(kv_create_impl(cfg->kv_max_size, cfg->default_ttl, p->n_rows, B, &p->kv));
     if ((uint64_t)cfg->max_batch > p->kv->max_chunk)
@@ -188,8 +516,12 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
     DIE_CUDA(cudaMalloc(&p->code, B));
     DIE_CUDA(cudaMalloc(&p->value, B * sizeof(uint64_t)));
     DIE_CUDA(cudaMalloc(&p->miss_rank, B * sizeof(int32_t)));
-    DIE_CUDA(cudaMalloc(&p->n_miss, sizeof(uint32_t)));
     DIE_CUDA(cudaMalloc(&p->set_slot, B * sizeof(int32_t)));
+    DIE_CUDA(cudaMalloc(&p->set_row, B * sizeof(int32_t)));
+    DIE_CUDA(cudaMalloc(&p->cand_slot, B * sizeof(uint32_t)));
+    DIE_CUDA(cudaMalloc(&p->cand_pos, B * sizeof(uint64_t)));
+    DIE_CUDA(cudaMalloc(&p->ctrl, sizeof(PipeCtrl)));
+    DIE_CUDA(cudaMemset(p->ctrl, 0, sizeof(PipeCtrl)));
     DIE_CUDA(cudaMalloc(&p->packed_in, B * cfg->dim_in * sizeof(float)));
     DIE_CUDA(cudaMalloc(&p->packed_out, B * cfg->dim_out * sizeof(float)));
     const size_t key_bytes = cfg->max_key_bytes > 0 ? (size_t)cfg->max_key_bytes : B * 64;
@@ -206,9 +538,9 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
 extern "C" die_status_t die_pipeline_destroy(die_pipeline_t* p) {
     if (!p) return DIE_OK;
     die_kv_destroy(p->kv);
-    void* bufs[] = {p->arena, p->W, p->bias, p->digests, p->shard, p->code, p->value, p->miss_rank, p->n_miss,
-                    p->set_slot, p->packed_in, p->packed_out, p->d_key_bytes, p->d_key_off, p->d_payload, p->d_out,
-                    p->d_hit};
+    void* bufs[] = {p->arena, p->W, p->bias, p->digests, p->shard, p->code, p->value, p->miss_rank, p->set_slot,
+                    p->set_row, p->cand_slot, p->cand_pos, p->ctrl, p->packed_in, p->packed_out, p->d_key_bytes,
+                    p->d_key_off, p->d_payload, p->d_out, p->d_hit};
     for (void* b : bufs) cudaFree(b);
     delete p;
     return DIE_OK;
@@ -222,7 +554,9 @@ extern "C" die_status_t die_pipeline_run_owner_device(die_pipeline_t* p, const u
     if (!p || B < 0 || B > p->cfg.max_batch) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_owner_device: bad B");
     if (B == 0) return DIE_OK;
     if (!digests || !payload || !out) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_owner_device: null buffer");
-    return run_owner(p, digests, B, payload, now, out, hit_out, static_cast<cudaStream_t>(stream));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (p->fast) return run_fast(p, nullptr, nullptr, const_cast<uint32_t*>(digests), B, payload, now, out, hit_out, s);
+    return run_general(p, digests, B, payload, now, out, hit_out, s);
 }
 
 extern "C" die_status_t die_pipeline_run_device(die_pipeline_t* p, const uint8_t* key_bytes, const int64_t* key_off,
@@ -231,9 +565,11 @@ extern "C" die_status_t die_pipeline_run_device(die_pipeline_t* p, const uint8_t
     if (!p || B < 0 || B > p->cfg.max_batch) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_device: bad B");
     if (B == 0) return DIE_OK;
     if (!key_off || !payload || !out) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_device: null buffer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
     uint32_t* dg = digest_out ? digest_out : p->digests;
+    if (p->fast) return run_fast(p, key_bytes, key_off, dg, B, payload, now, out, hit_out, s);
     DIE_TRY(die_route_md5(key_bytes, key_off, B, 1, nullptr, nullptr, 0, 0, p->shard, dg, nullptr, stream));
-    return run_owner(p, dg, B, payload, now, out, hit_out, static_cast<cudaStream_t>(stream));
+    return run_general(p, dg, B, payload, now, out, hit_out, s);
 }
 
 extern "C" die_status_t die_pipeline_run_host(die_pipeline_t* p, const uint8_t* key_bytes, const int64_t* key_off,

@@ -6,32 +6,9 @@
 // keys; the CTA's contiguous byte span is staged into shared memory with coalesced 128-bit loads
 // (warp-cooperative), then every lane hashes its own key out of shared memory.  Spans that do not
 // fit (very long keys) are read straight from global memory by the owning lane.
-#include "common.cuh"
-#include "md5.cuh"
+#include "route_device.cuh"
 
 namespace die {
-
-constexpr int ROUTE_THREADS = 256;
-constexpr int ROUTE_STAGE_BYTES = 24 * 1024;
-constexpr int ROUTE_SMEM_SHARDS = 1024;
-
-struct SmemKeySrc {
-    const uint8_t* base;  // shared-memory address of the key's first byte (any alignment)
-    __device__ __forceinline__ uint32_t byte(uint32_t p) const { return base[p]; }
-    __device__ __forceinline__ uint32_t word(uint32_t p) const {
-        const uintptr_t a = reinterpret_cast<uintptr_t>(base + p);
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~uintptr_t(3));
-        return __funnelshift_r(w[0], w[1], (uint32_t)(a & 3) * 8);
-    }
-};
-
-struct GlobalKeySrc {
-    const uint8_t* base;
-    __device__ __forceinline__ uint32_t byte(uint32_t p) const { return __ldg(base + p); }
-    __device__ __forceinline__ uint32_t word(uint32_t p) const {
-        return byte(p) | (byte(p + 1) << 8) | (byte(p + 2) << 16) | (byte(p + 3) << 24);
-    }
-};
 
 __global__ void __launch_bounds__(ROUTE_THREADS)
 route_md5_kernel(const uint8_t* __restrict__ key_bytes, const int64_t* __restrict__ key_off, int B,
@@ -43,36 +20,13 @@ route_md5_kernel(const uint8_t* __restrict__ key_bytes, const int64_t* __restric
     __shared__ int s_counts[ROUTE_SMEM_SHARDS];
 
     const int tid = threadIdx.x;
-    const int k0 = blockIdx.x * ROUTE_THREADS;
-    const int k1 = min(B, k0 + ROUTE_THREADS);
     const bool count_smem = dest_counts != nullptr && n_shards <= ROUTE_SMEM_SHARDS;
     if (count_smem)
         for (int s = tid; s < n_shards; s += ROUTE_THREADS) s_counts[s] = 0;
-
-    const int64_t b0 = key_off[k0], b1 = key_off[k1];
-    const uintptr_t g0 = reinterpret_cast<uintptr_t>(key_bytes) + (uintptr_t)b0;
-    const uintptr_t ga = g0 & ~uintptr_t(15);
-    const uint32_t lead = (uint32_t)(g0 - ga);
-    const int64_t span = (int64_t)lead + (b1 - b0);
-    const bool staged = span <= ROUTE_STAGE_BYTES;
-    if (staged && b1 > b0) {
-        const int nvec = (int)((span + 15) >> 4);
-        const int4* src = reinterpret_cast<const int4*>(ga);
-        int4* dst = reinterpret_cast<int4*>(stage);
-        for (int v = tid; v < nvec; v += ROUTE_THREADS) dst[v] = ldg_stream(src + v);
-    }
-    __syncthreads();
-
-    const int i = k0 + tid;
+    const Md5State st = cta_hash_keys(key_bytes, key_off, B, stage);
+    const int i = blockIdx.x * ROUTE_THREADS + tid;
     int shard = -1;
     if (i < B) {
-        const int64_t off = key_off[i];
-        const uint32_t len = (uint32_t)(key_off[i + 1] - off);
-        Md5State st;
-        if (staged)
-            st = md5_key(SmemKeySrc{stage + lead + (uint32_t)(off - b0)}, len);
-        else
-            st = md5_key(GlobalKeySrc{key_bytes + off}, len);
         if (digest_out) digest_out[i] = make_uint4(st.a, st.b, st.c, st.d);
         if (n_shards > 0) {
             const uint32_t p = md5_mod(st, (uint32_t)n_shards);
