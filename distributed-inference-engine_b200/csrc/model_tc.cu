@@ -1,12 +1,138 @@
-// K6/K7 on the 5th-generation tensor cores (tcgen05 + TMEM).  Placeholder launchers until the
-// kernels land: they fail loudly instead of falling back to another path.
+// K6 on the 5th-generation tensor cores: Y[B,N] = X[B,K] @ W[N,K]^T + b with TF32 inputs and fp32
+// accumulation in TMEM (tcgen05.mma.kind::tf32).  BASELINE.json configs[1] "mock linear model"; no
+// reference arithmetic exists (fake_model.py:52 is an echo), oracle/models.py defines the result.
+//
+// One CTA = one 128-row tile of X against the whole W (N <= 256 columns, K <= a few hundred):
+//   - all 8 warps copy the X tile and W into shared memory with coalesced 128-bit loads, storing
+//     them in the canonical K-major SWIZZLE_128B layout (blocks of [rows x 32 tf32]);
+//   - one thread issues K/8 tcgen05.mma (M=128, N, K=8) and commits them to an mbarrier;
+//   - warps 0-3 read the fp32 accumulators with tcgen05.ld (32 lanes x 32 columns), add the bias
+//     and stage the tile in shared memory; all warps then write whole rows with 512-byte coalesced
+//     stores.  The layer is HBM-bound (32 flop/B), so the tensor pipe only has to stay out of the way.
 #include "model_internal.cuh"
+#include "tc_common.cuh"
 
 namespace die {
 
-die_status_t linear_tf32_launch(const float*, const float*, const float*, float*, int, int, int,
-                                const uint32_t*, cudaStream_t) {
-    DIE_FAIL(DIE_ERR_UNSUPPORTED, "linear tf32 (tcgen05) kernel is not built yet");
+constexpr int TC_M = 128;
+constexpr int TC_THREADS = 256;
+
+__device__ __forceinline__ uint32_t pow2_cols(uint32_t n) {
+    uint32_t c = 32;
+    while (c < n) c <<= 1;
+    return c;
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, const float* __restrict__ bias,
+                   float* __restrict__ Y, int B, int K, int N, const uint32_t* __restrict__ n_rows_dev) {
+    extern __shared__ uint8_t smem_raw[];
+    // SWIZZLE_128B atoms must start on 1024-byte boundaries of the shared window
+    uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base;
+    if (n_rows_dev) B = min(B, (int)*n_rows_dev);
+    const int m0 = blockIdx.x * TC_M;
+    if (m0 >= B) return;  // uniform for the CTA
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int KB = K / 32;            // 128-byte (32 x tf32) blocks along K
+    const int chunks_per_row = K / 4; // 16-byte chunks per operand row
+    uint8_t* a_base = smem;                         // KB blocks of [128 rows x 128 B]
+    uint8_t* b_base = smem + (size_t)KB * TC_M * 128;  // KB blocks of [N rows x 128 B]
+    const uint32_t ncols = pow2_cols((uint32_t)N);
+
+    if (warp == 0) tc::tmem_alloc(&tmem_base, ncols);
+    if (tid == 32) tc::mbar_init(&bar, 1);
+
+    for (int idx = tid; idx < TC_M * chunks_per_row; idx += TC_THREADS) {
+        const int r = idx / chunks_per_row, ck = idx - r * chunks_per_row;
+        int4 v = make_int4(0, 0, 0, 0);
+        if (m0 + r < B) v = ldg_stream(reinterpret_cast<const int4*>(X + (size_t)(m0 + r) * K) + ck);
+        *reinterpret_cast<int4*>(a_base + (size_t)(ck >> 3) * (TC_M * 128) + tc::sw128_offset(r, ck & 7)) = v;
+    }
+    for (int idx = tid; idx < N * chunks_per_row; idx += TC_THREADS) {
+        const int r = idx / chunks_per_row, ck = idx - r * chunks_per_row;
+        const int4 v = __ldg(reinterpret_cast<const int4*>(W + (size_t)r * K) + ck);
+        *reinterpret_cast<int4*>(b_base + (size_t)(ck >> 3) * ((size_t)N * 128) + tc::sw128_offset(r, ck & 7)) = v;
+    }
+    tc::fence_proxy_async_smem();
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    const uint32_t taddr = tmem_base;
+
+    if (tid == 0) {
+        const uint32_t idesc = tc::instr_desc(tc::FMT_TF32, TC_M, (uint32_t)N);
+        const uint32_t a_s = tc::smem_u32(a_base), b_s = tc::smem_u32(b_base);
+        for (int kb = 0; kb < KB; ++kb) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {  // 4 x (K = 8 tf32 = 32 bytes) per 128-byte block
+                const uint64_t ad = tc::smem_desc_k_major_sw128(a_s + kb * (TC_M * 128) + j * 32);
+                const uint64_t bd = tc::smem_desc_k_major_sw128(b_s + kb * (N * 128) + j * 32);
+                tc::mma_tf32(taddr, ad, bd, idesc, (kb | j) != 0);
+            }
+        }
+        tc::mma_commit(&bar);
+    }
+    tc::mbar_wait(&bar, 0);
+    tc::fence_after_thread_sync();
+
+    // epilogue: TMEM -> registers (+bias) -> shared (row pitch N+4 floats) -> coalesced rows
+    float* stage = reinterpret_cast<float*>(smem);
+    const int pitch = N + 4;
+    if (warp < 4) {
+        const int row = warp * 32 + lane;
+        for (int c0 = 0; c0 < N; c0 += 32) {
+            uint32_t v[32];
+            tc::tmem_ld_32x32(taddr + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                if (c0 + j < N) {
+                    float4 o;
+                    o.x = __uint_as_float(v[j + 0]) + (bias ? bias[c0 + j + 0] : 0.f);
+                    o.y = __uint_as_float(v[j + 1]) + (bias ? bias[c0 + j + 1] : 0.f);
+                    o.z = __uint_as_float(v[j + 2]) + (bias ? bias[c0 + j + 2] : 0.f);
+                    o.w = __uint_as_float(v[j + 3]) + (bias ? bias[c0 + j + 3] : 0.f);
+                    *reinterpret_cast<float4*>(stage + (size_t)row * pitch + c0 + j) = o;
+                }
+            }
+        }
+    }
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    const int rows = min(TC_M, B - m0);
+    const int vec_per_row = N / 4;
+    for (int r = warp; r < rows; r += TC_THREADS / 32) {
+        for (int c = lane; c < vec_per_row; c += 32) {
+            const int4 o = *reinterpret_cast<const int4*>(stage + (size_t)r * pitch + c * 4);
+            stg_stream(reinterpret_cast<int4*>(Y + (size_t)(m0 + r) * N) + c, o);
+        }
+    }
+    if (warp == 0) {
+        tc::fence_after_thread_sync();
+        tc::tmem_dealloc(taddr, ncols);
+    }
+}
+
+die_status_t linear_tf32_launch(const float* X, const float* W, const float* b, float* Y, int B, int K, int N,
+                                const uint32_t* n_rows_dev, cudaStream_t s) {
+    if (B == 0) return DIE_OK;
+    if (K % 32 != 0 || N % 16 != 0 || N < 16 || N > 256)
+        DIE_FAIL(DIE_ERR_UNSUPPORTED, "linear tf32: needs K %% 32 == 0 and N in [16,256] multiple of 16 (K=%d N=%d)", K, N);
+    if ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(Y)) & 15)
+        DIE_FAIL(DIE_ERR_UNSUPPORTED, "linear tf32: X, W and Y must be 16-byte aligned");
+    const size_t operands = (size_t)(TC_M + N) * K * sizeof(float);
+    const size_t staging = (size_t)TC_M * (N + 4) * sizeof(float);
+    const size_t smem = std::max(operands, staging) + 1024;  // + slack for the 1024-byte alignment
+    if (smem > 200 * 1024)
+        DIE_FAIL(DIE_ERR_UNSUPPORTED, "linear tf32: (128+N)*K*4 = %zu bytes of operands exceed shared memory", smem);
+    static size_t configured = 0;
+    if (smem > configured) {
+        DIE_CUDA(cudaFuncSetAttribute(linear_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    DIE_LAUNCH(ST_MODEL, s, linear_tf32_kernel<<<ceil_div(B, TC_M), TC_THREADS, smem, s>>>(X, W, b, Y, B, K, N, n_rows_dev));
+    return DIE_OK;
 }
 
 die_status_t mlp_bf16_launch(const void*, const void*, const float*, const void*, const float*, void*, void*, int,

@@ -103,7 +103,7 @@ __device__ void pipe_scan_and_window(const KvView& kv, const PipeBufs& pb, int B
     __shared__ unsigned s_warp[PT / 32];
     __shared__ unsigned long long s_first;
     const int tid = threadIdx.x;
-    constexpr int ITEMS = 8;
+    constexpr int ITEMS = 16;  // 4096 requests per pass of the CTA
     unsigned base = 0;
     for (int pos = 0; pos < B; pos += PT * ITEMS) {
         const int q0 = pos + tid * ITEMS;
@@ -137,7 +137,7 @@ __device__ void pipe_scan_and_window(const KvView& kv, const PipeBufs& pb, int B
     }
     __syncthreads();
     // the first e_ub current log records from the head are the LRU victims, oldest first (kvstore.py:89-91)
-    constexpr int WI = 4;
+    constexpr int WI = 16;  // 4096 independent log/slot reads in flight per pass
     unsigned long long found = 0;
     for (unsigned long long pos = head; found < e_ub && pos < t_set; pos += (unsigned long long)PT * WI) {
         bool valid[WI];

@@ -109,3 +109,30 @@ def test_linear_fp32_within_tolerance_of_f64_oracle(B, K, N):
     want = models.linear_f64(x, w, b)
     tol = 1e-5 * models.linear_abs_bound(x, w) + 1e-6
     assert np.all(np.abs(y.astype(np.float64) - want) <= tol)
+
+
+@pytest.mark.parametrize("B,K,N", [(4096, 128, 128), (1, 128, 128), (129, 32, 16), (1000, 64, 256), (3670, 128, 128), (300, 256, 64)])
+def test_linear_tf32_tensor_core_within_tolerance(B, K, N):
+    """tcgen05 kind::tf32 path.  Tolerance (oracle/models.py): |d| <= 2**-10 * sum_k |x_k w_k| + 1e-6."""
+    from die import _cabi, ops
+    rng = np.random.default_rng(B * 3 + K)
+    x = rng.standard_normal((B, K)).astype(np.float32)
+    w = (rng.standard_normal((N, K)) / np.sqrt(K)).astype(np.float32)
+    b = rng.standard_normal(N).astype(np.float32)
+    xd, wd, bd = torch.from_numpy(x).cuda(), torch.from_numpy(w).cuda(), torch.from_numpy(b).cuda()
+    y = ops.linear_fwd(xd, wd, bd, _cabi.LINEAR_TF32).cpu().numpy()
+    want = models.linear_f64(x, w, b)
+    tol = 2.0 ** -10 * models.linear_abs_bound(x, w) + 1e-6
+    err = np.abs(y.astype(np.float64) - want)
+    assert np.all(err <= tol), (float(err.max()), float(tol.min()))
+    # and it is not the fp32 kernel in disguise: tf32 truncation must be visible somewhere
+    y32 = ops.linear_fwd(xd, wd, bd, _cabi.LINEAR_FP32).cpu().numpy()
+    assert B * N < 2000 or not np.array_equal(y, y32)
+
+
+def test_linear_tf32_rejects_unsupported_shapes():
+    from die import _cabi, ops
+    x = torch.zeros((8, 100), device="cuda")
+    w = torch.zeros((72, 100), device="cuda")
+    with pytest.raises(_cabi.DieError):
+        ops.linear_fwd(x, w, None, _cabi.LINEAR_TF32)
