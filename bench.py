@@ -31,6 +31,7 @@ B, D = 4096, 128
 KV_MAX, ID_SPACE, TTL = 1 << 20, 10 ** 7, 300.0
 KEY_LEN = 15
 METRIC = "requests/sec, batched route->probe->pack->infer->unpack"
+MODEL = os.environ.get("DIE_BENCH_MODEL", "linear_tf32")  # tcgen05 kind::tf32 GEMM, fp32 accumulate
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -222,7 +223,7 @@ def main():
         runner = ShardedDispatcher(world, rank, KV_MAX, B, D, w, b, TTL)
     else:
         runner = None
-    pipe = DispatchPipeline(KV_MAX, B * (2 if world > 1 else 1), D, D, "linear", w, b, TTL, max_key_bytes=2 * B * KEY_LEN) \
+    pipe = DispatchPipeline(KV_MAX, B * (2 if world > 1 else 1), D, D, MODEL, w, b, TTL, max_key_bytes=2 * B * KEY_LEN) \
         if runner is None else runner.pipe
 
     off_d = torch.from_numpy(np.arange(B + 1, dtype=np.int64) * KEY_LEN).cuda()
@@ -365,8 +366,9 @@ def main():
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "requests/s", "n_gpus": world, "steps": K, "warmup": W,
-                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-                "data": "synthetic", "config": dict(workload_config(world), hit_rate=round(hit_rate, 4)),
+                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "tf32" if MODEL == "linear_tf32" else "f32",
+                "data": "synthetic", "config": dict(workload_config(world), hit_rate=round(hit_rate, 4), model=MODEL),
                 "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e, "roofline": roofline, "stages": stages,
                 "cpu_baseline": cpu}
         print(json.dumps(line))

@@ -21,6 +21,7 @@
 struct PipeCtrl {
     unsigned int n_miss, ticket_get, ticket_claim, any_dup;
     unsigned long long e_ub, e_final;
+    unsigned long long ts[8];  // %globaltimer marks of the last get kernel (ns): diagnostics only
 };
 
 struct die_pipeline {
@@ -81,6 +82,12 @@ __device__ __forceinline__ unsigned block_scan_pt(unsigned cnt, unsigned& excl, 
     return s_warp[PT / 32 - 1];
 }
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 __device__ __forceinline__ unsigned ld_u8_cg(const uint8_t* p) {
     unsigned r;
     asm volatile("ld.global.cg.u8 %0, [%1];" : "=r"(r) : "l"(p) : "memory");
@@ -124,6 +131,7 @@ __device__ void pipe_scan_and_window(const KvView& kv, const PipeBufs& pb, int B
         __syncthreads();
     }
     KvState* st = kv.st;
+    if (tid == 0) pb.ctrl->ts[3] = globaltimer_ns();  // scan done
     const unsigned long long size = ld_u64_cg(&st->size), head = ld_u64_cg(&st->head);
     const unsigned long long e_ub = size + base > kv.max_size ? size + base - kv.max_size : 0ull;
     if (tid == 0) {
@@ -172,6 +180,8 @@ __device__ void pipe_scan_and_window(const KvView& kv, const PipeBufs& pb, int B
         __syncthreads();
     }
     if (tid == 0) {
+        pb.ctrl->ts[4] = globaltimer_ns();  // window done
+        pb.ctrl->ts[5] = found;
         if (found < e_ub) st->status = DIE_ERR_INVALID;  // unreachable when max_batch <= max_size
         if (s_first != ~0ull && s_first > head) st->head = s_first;  // drop leading stale records
     }
@@ -185,6 +195,7 @@ pipe_get_kernel(KvView kv, PipeBufs pb, const uint8_t* __restrict__ key_bytes, c
     __shared__ bool s_last;
     const int i = blockIdx.x * PT + threadIdx.x;
     const bool active = i < B;
+    if (i == 0) pb.ctrl->ts[0] = globaltimer_ns();  // kernel start (CTA 0)
     u128 key{0ull, 0ull};
     if (FROM_KEYS) {
         const Md5State st = cta_hash_keys(key_bytes, key_off, B, stage);
@@ -197,6 +208,7 @@ pipe_get_kernel(KvView kv, PipeBufs pb, const uint8_t* __restrict__ key_bytes, c
         key = fp_of(digests[i]);
     }
     int code = 0;
+    if (i == 0) pb.ctrl->ts[1] = globaltimer_ns();  // keys hashed (CTA 0)
     if (active) {
         unsigned long long value;
         long long s;
@@ -216,6 +228,7 @@ pipe_get_kernel(KvView kv, PipeBufs pb, const uint8_t* __restrict__ key_bytes, c
     __syncthreads();
     if (!s_last) return;
     __threadfence();
+    if (threadIdx.x == 0) pb.ctrl->ts[2] = globaltimer_ns();  // all CTAs probed, tail starts
     pipe_scan_and_window(kv, pb, B, t_set);
 }
 
@@ -547,6 +560,15 @@ extern "C" die_status_t die_pipeline_destroy(die_pipeline_t* p) {
 }
 
 extern "C" die_kv_t* die_pipeline_kv(die_pipeline_t* p) { return p ? p->kv : nullptr; }
+
+extern "C" die_status_t die_pipeline_debug_marks_sync(die_pipeline_t* p, uint64_t out[8]) {
+    if (!p || !out) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_debug_marks_sync: null argument");
+    DIE_CUDA(cudaDeviceSynchronize());
+    PipeCtrl h;
+    DIE_CUDA(cudaMemcpy(&h, p->ctrl, sizeof(h), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 8; ++i) out[i] = h.ts[i];
+    return DIE_OK;
+}
 
 extern "C" die_status_t die_pipeline_run_owner_device(die_pipeline_t* p, const uint32_t* digests, int32_t B,
                                                       const float* payload, double now, float* out,

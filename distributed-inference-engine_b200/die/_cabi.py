@@ -63,6 +63,7 @@ SIGNATURES = {
     "die_pipeline_create": (c_int32, [POINTER(PipelineConfig), POINTER(c_void_p)]),
     "die_pipeline_destroy": (c_int32, [P]),
     "die_pipeline_kv": (c_void_p, [P]),
+    "die_pipeline_debug_marks_sync": (c_int32, [P, POINTER(c_uint64)]),
     "die_pipeline_run_device": (c_int32, [P, P, P, c_int32, P, c_double, P, P, P, P]),
     "die_pipeline_run_owner_device": (c_int32, [P, P, c_int32, P, c_double, P, P, P]),
     "die_pipeline_run_host": (c_int32, [P, P, P, c_int32, P, c_double, P, P, P]),

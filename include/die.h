@@ -206,6 +206,9 @@ typedef struct {
 die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, die_pipeline_t** out);
 die_status_t die_pipeline_destroy(die_pipeline_t* p);
 die_kv_t* die_pipeline_kv(die_pipeline_t* p);
+/* Diagnostics (no reference counterpart): %globaltimer marks (ns) written by the last fused get kernel:
+ * [0] start, [1] keys hashed, [2] all probes done, [3] misses ranked, [4] victim window done, [5] victims found. */
+die_status_t die_pipeline_debug_marks_sync(die_pipeline_t* p, uint64_t out[8] /*[host]*/);
 /* Inputs already resident in HBM.  payload [B, dim_in] fp32; out [B, dim_out] fp32;
  * hit_out [B] uint8 (1 = served from the cache); digest_out optional [B,4]. */
 die_status_t die_pipeline_run_device(die_pipeline_t* p, const uint8_t* key_bytes, const int64_t* key_off,

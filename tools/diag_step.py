@@ -10,7 +10,7 @@ from die.pipeline import DispatchPipeline
 B, D = bench.B, bench.D
 w, b = bench.model_weights()
 kvmax = int(sys.argv[1]) if len(sys.argv) > 1 else bench.KV_MAX
-pipe = DispatchPipeline(kvmax, B, D, D, "linear", w, b, 300.0)
+pipe = DispatchPipeline(kvmax, B, D, D, bench.MODEL, w, b, 300.0)
 rng = np.random.default_rng(0)
 off_d = torch.from_numpy(np.arange(B + 1, dtype=np.int64) * 15).cuda()
 out = torch.empty((B, D), device="cuda"); hit = torch.empty(B, dtype=torch.uint8, device="cuda")
@@ -51,4 +51,14 @@ for i in range(N * 9):
     a.add_(1.0)
 t1 = time.perf_counter(); torch.cuda.synchronize(); t2 = time.perf_counter()
 print(f"torch add_: enqueue {1e6*(t1-t0)/(N*9):.1f} us, total {1e6*(t2-t0)/(N*9):.1f} us per launch")
+import ctypes
+marks = (ctypes.c_uint64 * 8)()
+_, keys3, _, x3 = bench.make_batches(rng, 6)
+kd3, xd3 = torch.from_numpy(keys3).cuda(), torch.from_numpy(x3).cuda()
+for rep in range(6):
+    now += 0.01; pipe.run_device(ops.KeyBatch(kd3[rep], off_d), xd3[rep], now, out, hit)
+    lib.die_pipeline_debug_marks_sync(pipe._h, marks)
+    m = list(marks)
+    print("get kernel marks (us): hash %.1f probe %.1f scan %.1f window %.1f (victims %d)" % tuple(
+        [(m[i + 1] - m[i]) / 1e3 for i in range(4)] + [m[5]]))
 print(pipe.kv.stats())
