@@ -835,3 +835,75 @@ extern "C" die_status_t die_kv_dump_sync(die_kv_t* kv, uint64_t cap, uint32_t* d
     }
     return DIE_OK;
 }
+
+// ================================================================================================
+// die_kv_set_batch_noalloc: the same batched set, for hosts that must not touch the CUDA allocator
+// ================================================================================================
+// A serving loop that has reserved all of its device memory up front, code running inside a
+// latency-critical section where cudaMalloc's implicit device-wide synchronisation is not acceptable,
+// or an embedding runtime that simply forbids allocation after start-up cannot use die_kv_set_batch:
+// that entry point grows its per-op scratch with cudaMalloc and may rebuild the table.  This variant
+// takes its per-op scratch (one int32 slot index per op) from a fixed array that lives in the
+// library's device image, so every GPU that loads libdie.so carries 256 KiB for it until the
+// process exits.  Inputs and outputs are still the caller's buffers.
+namespace die {
+constexpr int32_t KV_NOALLOC_MAX_OPS = 65536;  // DIE_KV_NOALLOC_MAX_OPS in include/die.h
+static __device__ __align__(256) int32_t g_noalloc_op_slot[KV_NOALLOC_MAX_OPS];
+constexpr int KV_NOALLOC_MAX_DEVICES = 64;
+// Device address of g_noalloc_op_slot on each device.  The symbol's name is only a host-side stand-in,
+// never a device pointer: the address comes from cudaGetSymbolAddress, once per device.
+static int32_t* g_noalloc_scratch[KV_NOALLOC_MAX_DEVICES] = {nullptr};
+}  // namespace die
+
+extern "C" die_status_t die_kv_set_batch_noalloc(die_kv_t* kv, const uint32_t* digests, const uint64_t* values,
+                                                 const double* ttl, int32_t M, double now, int32_t deferred_stamp,
+                                                 int32_t* slot_out, uint64_t* dropped_out, die_stream_t stream) {
+    if (!kv || M < 0) DIE_FAIL(DIE_ERR_INVALID, "die_kv_set_batch_noalloc: bad arguments");
+    if (M == 0) return DIE_OK;
+    if (!digests) DIE_FAIL(DIE_ERR_INVALID, "die_kv_set_batch_noalloc: null digests");
+    if (M > KV_NOALLOC_MAX_OPS)
+        DIE_FAIL(DIE_ERR_TOO_LARGE, "die_kv_set_batch_noalloc: %d ops exceed the fixed scratch of %d ops; split the batch",
+                 M, KV_NOALLOC_MAX_OPS);
+    if ((uint64_t)M > kv->max_chunk)
+        DIE_FAIL(DIE_ERR_TOO_LARGE, "die_kv_set_batch_noalloc: %d ops exceed this table's per-launch limit of %llu", M,
+                 (unsigned long long)kv->max_chunk);
+    int dev = -1;
+    DIE_CUDA(cudaGetDevice(&dev));
+    if (dev != kv->device || dev < 0 || dev >= KV_NOALLOC_MAX_DEVICES)
+        DIE_FAIL(DIE_ERR_INVALID, "die_kv_set_batch_noalloc: table lives on device %d, current device is %d", kv->device, dev);
+    if (!g_noalloc_scratch[dev]) {  // one-time set-up for this device (do it before any stream capture)
+        void* p = nullptr;
+        DIE_CUDA(cudaGetSymbolAddress(&p, g_noalloc_op_slot));
+        g_noalloc_scratch[dev] = static_cast<int32_t*>(p);
+    }
+    int32_t* scratch = g_noalloc_scratch[dev];
+    // Housekeeping (LRU-ring compaction, table rebuild) allocates, so it is never started from here: when the
+    // conservative host-side bounds say it is due, the caller is told to run it where allocation is allowed.
+    const uint64_t n = (uint64_t)M;
+    if ((kv->tail + n - kv->head_lb) > kv->ring_cap - 16 ||
+        kv->live_at_rebuild + kv->claims_ub + n > kv->capacity / 8 * 3)
+        DIE_FAIL(DIE_ERR_NOMEM,
+                 "die_kv_set_batch_noalloc: table housekeeping is due and would allocate; call die_kv_maintain_sync "
+                 "(or any die_kv_*_sync) at a point where allocation is allowed, then retry");
+    kv->claims_ub += n;
+    kv->dropped_prefix = 0;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const KvView v = view_of(kv);
+    const uint4* dg = reinterpret_cast<const uint4*>(digests);
+    const unsigned long long* vals = reinterpret_cast<const unsigned long long*>(values);
+    unsigned long long* dr = reinterpret_cast<unsigned long long*>(dropped_out);
+    const int grid = ceil_div(M, KV_THREADS);
+    // Nothing in the scratch has to start at zero: the precheck writes op_slot[i] for every op before any
+    // later kernel of this call reads it.  What the previous call left there is simply overwritten.
+    DIE_LAUNCH(ST_KV_PRECHECK, s, kv_set_precheck_kernel<<<grid, KV_THREADS, 0, s>>>(v, dg, M, nullptr, scratch));
+    DIE_LAUNCH(ST_KV_WINDOW, s, kv_set_window_kernel<<<1, WIN_THREADS, 0, s>>>(v, kv->tail, nullptr, deferred_stamp));
+    DIE_LAUNCH(ST_KV_CLAIM, s, kv_set_claim_kernel<<<grid, KV_THREADS, 0, s>>>(v, dg, M, now, kv->tail, values ? 0 : 1,
+                                                                              nullptr, 1, scratch, slot_out, dr));
+    if (values || ttl)
+        DIE_LAUNCH(ST_KV_FINALIZE, s, kv_set_finalize_kernel<<<grid, KV_THREADS, 0, s>>>(v, M, kv->tail, vals, ttl,
+                                                                                         nullptr, scratch));
+    DIE_LAUNCH(ST_KV_EVICT, s, kv_set_evict_kernel<<<1, WIN_THREADS, 0, s>>>(v, dg, vals, ttl, M, now, kv->tail,
+                                                                             deferred_stamp, nullptr, slot_out, dr));
+    kv->tail += n;
+    return DIE_OK;
+}

@@ -47,6 +47,7 @@ SIGNATURES = {
     "die_kv_destroy": (c_int32, [P]),
     "die_kv_get_batch": (c_int32, [P, P, c_int32, c_double, P, P, P, P]),
     "die_kv_set_batch": (c_int32, [P, P, P, P, c_int32, c_double, c_int32, P, P, P]),
+    "die_kv_set_batch_noalloc": (c_int32, [P, P, P, P, c_int32, c_double, c_int32, P, P, P]),
     "die_kv_delete_batch": (c_int32, [P, P, c_int32, P, P, P]),
     "die_kv_contains_batch": (c_int32, [P, P, c_int32, c_double, P, P, P]),
     "die_kv_len_sync": (c_int32, [P, c_double, P, c_uint64, POINTER(c_uint64), POINTER(c_uint64), P]),

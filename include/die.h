@@ -116,6 +116,26 @@ die_status_t die_kv_set_batch(die_kv_t* kv, const uint32_t* digests, const uint6
                               const double* ttl, int32_t M, double now, int32_t deferred_stamp,
                               int32_t* slot_out, uint64_t* dropped_out, die_stream_t stream);
 
+/* No counterpart in the reference.  die_kv_set_batch for callers that are not allowed to allocate device
+ * memory once they are up: a serving loop that reserved all HBM at start, a latency-critical section that
+ * cannot take cudaMalloc's device-wide synchronisation, a runtime that forbids allocation after
+ * initialisation.  Same arguments and same results as die_kv_set_batch, but
+ *   - the per-op scratch (one int32 per op) is a fixed 256 KiB array inside the library's device image
+ *     (every GPU that loads libdie.so holds it until the process exits), so M must be
+ *     <= DIE_KV_NOALLOC_MAX_OPS and <= the table's per-launch limit, else DIE_ERR_TOO_LARGE;
+ *   - it never calls cudaMalloc/cudaFree and never starts table housekeeping (which allocates): when the
+ *     host-side bounds say housekeeping is due it returns DIE_ERR_NOMEM and the caller runs
+ *     die_kv_maintain_sync where allocation is allowed, then retries;
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress); make
+ *     that first call before starting any stream capture on that device;
+ *   - all calls share the one array and it keeps the previous call's contents (nothing in it needs
+ *     clearing: each call overwrites what it reads).  Two calls whose kernels overlap on the GPU
+ *     (different streams, different tables) race on it: serialise them. */
+#define DIE_KV_NOALLOC_MAX_OPS 65536
+die_status_t die_kv_set_batch_noalloc(die_kv_t* kv, const uint32_t* digests, const uint64_t* values,
+                                      const double* ttl, int32_t M, double now, int32_t deferred_stamp,
+                                      int32_t* slot_out, uint64_t* dropped_out, die_stream_t stream);
+
 /* KVCache.delete (kvstore.py:178-187): deleted_out[i] = 1 if the key was present (value_out[i] = its value). */
 die_status_t die_kv_delete_batch(die_kv_t* kv, const uint32_t* digests, int32_t B,
                                  uint8_t* deleted_out, uint64_t* value_out, die_stream_t stream);
