@@ -1,0 +1,89 @@
+// Stable bucket-by-destination of a routed batch: the "group requests by owner shard" step that sits
+// between Router.route_request (src/router.py:140) and the per-worker hand-off in SURVEY.md call-stack (E).
+// The reference has no such code (its coordinator was never written); order inside a bucket is request
+// order, which is what fixes the owner-side "request order" the LRU parity is defined against.
+//
+// One CTA of 1024 threads walks the batch in tiles of 4096 requests; for every destination it ranks the
+// tile's requests with a block scan, so positions are deterministic (no atomics).  Requests routed to
+// None (-1) form a last bucket.  Sized for dispatch fan-outs (n_shards <= 64), not for general sorting.
+#include "common.cuh"
+
+namespace die {
+
+constexpr int BK_THREADS = 1024;
+constexpr int BK_ITEMS = 4;
+constexpr int BK_MAX_SHARDS = 64;
+
+__global__ void __launch_bounds__(BK_THREADS)
+bucket_by_shard_kernel(const int32_t* __restrict__ shard, int B, int n_shards, int64_t* __restrict__ offsets,
+                       int32_t* __restrict__ perm, int32_t* __restrict__ pos) {
+    __shared__ unsigned s_warp[32];
+    __shared__ unsigned s_total[BK_MAX_SHARDS + 1];
+    __shared__ unsigned s_base[BK_MAX_SHARDS + 2];
+    const int tid = threadIdx.x;
+    const int nb = n_shards + 1;  // last bucket: unroutable
+    // pass 1: bucket sizes
+    for (int d = tid; d < nb; d += BK_THREADS) s_total[d] = 0;
+    __syncthreads();
+    for (int i = tid; i < B; i += BK_THREADS) {
+        const int s = shard[i];
+        atomicAdd(&s_total[s < 0 || s >= n_shards ? n_shards : s], 1u);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        unsigned acc = 0;
+        for (int d = 0; d < nb; ++d) {
+            s_base[d] = acc;
+            offsets[d] = acc;
+            acc += s_total[d];
+        }
+        s_base[nb] = acc;
+        offsets[nb] = acc;
+    }
+    __syncthreads();
+    // pass 2: stable ranks, tile by tile
+    for (int t0 = 0; t0 < B; t0 += BK_THREADS * BK_ITEMS) {
+        int my[BK_ITEMS];
+#pragma unroll
+        for (int k = 0; k < BK_ITEMS; ++k) {
+            const int i = t0 + tid * BK_ITEMS + k;
+            int s = i < B ? shard[i] : -2;
+            if (s != -2 && (s < 0 || s >= n_shards)) s = n_shards;
+            my[k] = s;
+        }
+        for (int d = 0; d < nb; ++d) {
+            unsigned cnt = 0;
+#pragma unroll
+            for (int k = 0; k < BK_ITEMS; ++k) cnt += my[k] == d;
+            unsigned excl;
+            const unsigned total = block_scan_1024(cnt, excl, s_warp);
+            unsigned r = s_base[d] + excl;
+#pragma unroll
+            for (int k = 0; k < BK_ITEMS; ++k) {
+                if (my[k] == d) {
+                    const int i = t0 + tid * BK_ITEMS + k;
+                    perm[r] = i;
+                    pos[i] = (int32_t)r;
+                    ++r;
+                }
+            }
+            __syncthreads();
+            if (tid == 0) s_base[d] += total;
+            __syncthreads();
+        }
+    }
+}
+
+}  // namespace die
+
+extern "C" die_status_t die_bucket_by_shard(const int32_t* shard, int32_t B, int32_t n_shards, int64_t* offsets_out,
+                                            int32_t* perm_out, int32_t* pos_out, die_stream_t stream) {
+    using namespace die;
+    if (B < 0 || n_shards < 0 || n_shards > BK_MAX_SHARDS)
+        DIE_FAIL(DIE_ERR_INVALID, "die_bucket_by_shard: n_shards must be in [0, %d]", BK_MAX_SHARDS);
+    if (!offsets_out || (B > 0 && (!shard || !perm_out || !pos_out)))
+        DIE_FAIL(DIE_ERR_INVALID, "die_bucket_by_shard: null buffer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    DIE_LAUNCH(ST_BUCKET, s, bucket_by_shard_kernel<<<1, BK_THREADS, 0, s>>>(shard, B, n_shards, offsets_out, perm_out, pos_out));
+    return DIE_OK;
+}

@@ -1,0 +1,127 @@
+"""Hash-sharded dispatch across ranks: shard list position s <-> rank s <-> GPU s.
+
+Replaces the hop the reference makes over TCP + JSON, one request per connection
+(src/worker.py:84-133), with two all-to-alls over NVLink per flushed batch:
+
+  every rank ingests its own batch   -> route (K1, n_shards = world) -> stable bucket by owner
+  dispatch  all-to-all               -> digests + payload rows travel to their owner rank
+  owner     get -> pack -> model -> unpack -> set on its own KV shard (die_pipeline_run_owner_device);
+            it sees the sources in rank order, request order kept inside each source
+            (the order oracle/pipeline.py::process_exchange applies)
+  return    all-to-all               -> results and hit flags travel back, scattered to request order
+
+The collective calls go through torch.distributed (NCCL on GPUs); everything else is a libdie kernel.
+The per-stage work is injected (`stages`) so that the exchange bookkeeping itself -- split sizes, ordering,
+the two all-to-alls -- can be exercised with the gloo backend on CPU tensors by the test-suite.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+
+class GpuStages:
+    """The production stages: libdie kernels on the current CUDA device."""
+
+    def __init__(self, world: int, kv_max_size: int, max_batch: int, dim: int, weight, bias, default_ttl,
+                 model: str = "linear_tf32", dim_out: Optional[int] = None):
+        from . import ops
+        from .pipeline import DispatchPipeline
+        self.ops = ops
+        self.world = world
+        self.dim, self.dim_out = dim, dim if dim_out is None else dim_out
+        # an owner can receive more than one rank's batch worth of requests when the hash is unlucky
+        self.pipe = DispatchPipeline(kv_max_size, 2 * max_batch, dim, self.dim_out, model, weight, bias, default_ttl)
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self._row_off = {}
+
+    def row_offsets(self, n: int, width: int) -> torch.Tensor:
+        key = (n, width)
+        if key not in self._row_off:
+            self._row_off[key] = torch.arange(n + 1, dtype=torch.int64, device=self.device) * width
+        return self._row_off[key]
+
+    def route(self, keys):
+        shard, digests, _ = self.ops.route_md5(keys, self.world)
+        return shard, digests
+
+    def bucket(self, shard):
+        return self.ops.bucket_by_shard(shard, self.world)
+
+    def gather_rows(self, rows: torch.Tensor, perm: torch.Tensor) -> torch.Tensor:
+        """rows[perm] with the pack kernel (fixed-width rows are a CSR with constant stride)."""
+        flat = rows.reshape(-1)
+        width = rows.shape[1]
+        out, _ = self.ops.pack_ragged(flat, self.row_offsets(rows.shape[0], width), width, perm)
+        return out
+
+    def scatter_rows(self, rows: torch.Tensor, perm: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+        """out[perm[j]] = rows[j] with the unpack kernel."""
+        self.ops.unpack_ragged(rows, self.row_offsets(out.shape[0], out.shape[1]), out.reshape(-1), perm)
+        return out
+
+    def owner(self, digests: torch.Tensor, payload: torch.Tensor, now: float):
+        n = digests.shape[0]
+        cap = self.pipe.max_batch
+        if n <= cap:
+            return self.pipe.run_owner_device(digests, payload, now)
+        outs, hits = [], []
+        for a in range(0, n, cap):  # rare: split, still in arrival order
+            o, h = self.pipe.run_owner_device(digests[a:a + cap].contiguous(), payload[a:a + cap].contiguous(), now)
+            outs.append(o)
+            hits.append(h)
+        return torch.cat(outs), torch.cat(hits)
+
+    def empty(self, shape, dtype):
+        return torch.empty(shape, dtype=dtype, device=self.device)
+
+
+class ShardedDispatcher:
+    def __init__(self, world: int, rank: int, kv_max_size: int = 0, max_batch: int = 0, dim: int = 0, weight=None,
+                 bias=None, default_ttl=None, stages=None, group=None, model: str = "linear_tf32"):
+        self.world, self.rank, self.group = world, rank, group
+        self.stages = stages if stages is not None else GpuStages(world, kv_max_size, max_batch, dim, weight, bias,
+                                                                  default_ttl, model)
+        self.pipe = getattr(self.stages, "pipe", None)
+        self.last_recv = 0
+
+    def step(self, keys, payload: torch.Tensor, now: float, out: Optional[torch.Tensor] = None,
+             hit: Optional[torch.Tensor] = None):
+        """One flushed batch ingested on this rank.  Returns (out [B, dim_out], hit uint8 [B], shard int32 [B])."""
+        st, W = self.stages, self.world
+        B = payload.shape[0]
+        shard, digests = st.route(keys)
+        offsets, perm, _pos = st.bucket(shard)
+        send_dig = st.gather_rows(digests, perm)
+        send_pay = st.gather_rows(payload, perm)
+        # split sizes: one small exchange + the step's only host read-back
+        counts = (offsets[1:W + 1] - offsets[:W]).to(torch.int64)
+        recv_counts = torch.empty_like(counts)
+        dist.all_to_all_single(recv_counts, counts, group=self.group)
+        in_split = counts.tolist()
+        out_split = recv_counts.tolist()
+        n_send, n_recv = sum(in_split), sum(out_split)
+        self.last_recv = n_recv
+        recv_dig = st.empty((n_recv, digests.shape[1]), digests.dtype)
+        recv_pay = st.empty((n_recv, payload.shape[1]), payload.dtype)
+        dist.all_to_all_single(recv_dig, send_dig[:n_send], out_split, in_split, group=self.group)
+        dist.all_to_all_single(recv_pay, send_pay[:n_send], out_split, in_split, group=self.group)
+        res, res_hit = st.owner(recv_dig, recv_pay, now) if n_recv else (
+            st.empty((0, getattr(st, "dim_out", payload.shape[1])), payload.dtype), st.empty((0,), torch.uint8))
+        back = st.empty((B, res.shape[1]), res.dtype)
+        back_hit = st.empty((B, 1), torch.uint8)
+        dist.all_to_all_single(back[:n_send], res, in_split, out_split, group=self.group)
+        dist.all_to_all_single(back_hit[:n_send], res_hit.reshape(-1, 1), in_split, out_split, group=self.group)
+        if n_send < B:  # requests the router returned None for: no result
+            back[n_send:].zero_()
+            back_hit[n_send:].zero_()
+        out = st.empty((B, res.shape[1]), res.dtype) if out is None else out
+        hit2 = st.empty((B, 1), torch.uint8)
+        st.scatter_rows(back, perm, out)
+        st.scatter_rows(back_hit, perm, hit2)
+        if hit is not None:
+            hit.copy_(hit2.reshape(-1))
+            return out, hit, shard
+        return out, hit2.reshape(-1), shard

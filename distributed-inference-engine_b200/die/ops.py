@@ -57,6 +57,17 @@ def route_md5(keys: KeyBatch, n_shards: int, routable: Optional[torch.Tensor] = 
     return shard, digests, (counts[:n_shards] if counts is not None else None)
 
 
+def bucket_by_shard(shard: torch.Tensor, n_shards: int):
+    """-> (offsets int64[n_shards+2], perm int32[B], pos int32[B]); stable, unroutable (-1) requests last."""
+    lib = require_cuda()
+    B = shard.numel()
+    offsets = torch.empty(n_shards + 2, dtype=torch.int64, device=shard.device)
+    perm = torch.empty(B, dtype=torch.int32, device=shard.device)
+    pos = torch.empty(B, dtype=torch.int32, device=shard.device)
+    check(lib.die_bucket_by_shard(ptr(shard), B, n_shards, ptr(offsets), ptr(perm), ptr(pos), stream_ptr()))
+    return offsets, perm, pos
+
+
 def pack_ragged(values: torch.Tensor, off: torch.Tensor, Lpad: int, src_index: Optional[torch.Tensor] = None,
                 n_rows: Optional[int] = None):
     """values: 1-D tensor of payload elements, off: int64[n_req+1] -> (packed [R, Lpad], lengths int32[R])."""

@@ -80,6 +80,15 @@ die_status_t die_route_md5(const uint8_t* key_bytes, const int64_t* key_off, int
                            int32_t* shard_out, uint32_t* digest_out, int32_t* dest_counts,
                            die_stream_t stream);
 
+/* Stable grouping of a routed batch by destination shard: the hand-off between Router.route_request
+ * (src/router.py:140) and the owner workers in the composed path (the reference's coordinator, README.md:56-60,
+ * was never written).  Requests keep request order inside their bucket; shard -1 (None) forms a last bucket.
+ *   offsets_out [n_shards+2] : bucket starts (int64), offsets_out[n_shards+1] == B
+ *   perm_out    [B]          : request index placed at send position j
+ *   pos_out     [B]          : send position of request i (inverse of perm)                                  */
+die_status_t die_bucket_by_shard(const int32_t* shard, int32_t B, int32_t n_shards, int64_t* offsets_out,
+                                 int32_t* perm_out, int32_t* pos_out, die_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------
  * K2/K3  KV store: GPU-resident open-addressing table keyed by the 128-bit MD5 of the key,
  * with the reference's LRU + TTL semantics applied "as if" the batch ran in request order.

@@ -1,0 +1,76 @@
+"""GPU: stable bucket-by-shard kernel, and (when the box has >= 2 GPUs) the NCCL sharded dispatch vs the oracle."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("B,n", [(4096, 8), (1, 1), (10000, 3), (257, 64), (5000, 2)])
+def test_bucket_by_shard_is_a_stable_partition(B, n):
+    from die import ops
+    rng = np.random.default_rng(B + n)
+    shard = rng.integers(-1, n, B).astype(np.int32)
+    offsets, perm, pos = ops.bucket_by_shard(torch.from_numpy(shard).cuda(), n)
+    key = np.where(shard < 0, n, shard)
+    want_perm = np.argsort(key, kind="stable")
+    assert np.array_equal(perm.cpu().numpy(), want_perm)
+    assert np.array_equal(pos.cpu().numpy()[want_perm], np.arange(B))
+    counts = np.bincount(key, minlength=n + 1)
+    assert offsets.cpu().tolist() == [0] + np.cumsum(counts).tolist()
+
+
+def _worker(rank, world, port, ret):
+    sys.path[:0] = [ROOT, os.path.join(ROOT, "distributed-inference-engine_b200")]
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from die import ops
+        from die.exchange import ShardedDispatcher
+        from oracle import models
+        from oracle.pipeline import OraclePipeline
+        B, D, steps, max_size, ttl = 1024, 128, 8, 3000, 7.0
+        rng = np.random.default_rng(5)
+        w = (rng.standard_normal((D, D)) / np.sqrt(D)).astype(np.float32)
+        b = rng.standard_normal(D).astype(np.float32)
+        disp = ShardedDispatcher(world, rank, max_size, B, D, w, b, ttl, model="linear")
+
+        def fn(rows):
+            y = models.linear_f64(np.stack(rows), w, b) if rows else []
+            return [y[i] for i in range(len(rows))]
+
+        ref = OraclePipeline(world, max_size, ttl, fn)
+        now = 3.0
+        for _ in range(steps):
+            now += float(rng.choice([0.5, 2.0, 4.0]))
+            per_rank = []
+            for _r in range(world):
+                keys = ["user-%010d" % i for i in rng.integers(0, 5000, B)]
+                per_rank.append((keys, rng.standard_normal((B, D)).astype(np.float32)))
+            keys, pay = per_rank[rank]
+            out, hit, shard = disp.step(ops.KeyBatch.from_strings(keys), torch.from_numpy(pay).cuda(), now)
+            want = ref.process_exchange([(k, [r for r in p]) for k, p in per_rank], now)[rank]
+            assert shard.tolist() == want["shard"] and hit.tolist() == want["hit"]
+            assert np.all(np.abs(out.cpu().numpy() - np.stack(want["out"])) <= 1e-5 * np.abs(np.stack(want["out"])) + 2e-4)
+        st, mine = disp.pipe.kv.stats(), ref.state()[rank]
+        assert (st["hits"], st["misses"], st["evictions"], st["size"]) == (mine["hits"], mine["misses"], mine["evictions"], mine["size"])
+        ret[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (run with gpurun --gpus 2)")
+def test_two_gpu_sharded_dispatch_matches_oracle():
+    import torch.multiprocessing as mp
+    world = 2
+    port = 29600 + (os.getpid() % 2000)
+    with mp.Manager() as m:
+        ret = m.dict()
+        mp.spawn(_worker, args=(world, port, ret), nprocs=world, join=True)
+        assert dict(ret) == {0: "ok", 1: "ok"}
