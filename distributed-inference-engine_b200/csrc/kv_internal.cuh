@@ -120,26 +120,53 @@ __device__ __forceinline__ unsigned long long acquire_row(const KvView& kv) {
 }
 // One KVCache.get (kvstore.py:136-164) / __contains__ (:221-228) probe.  Returns the code
 // (1 hit, 0 absent, 2 expired-and-deleted-by-this-op); `deleted` tells the caller to account for it.
+// Both 32-byte sectors of a slot, fetched with three independent 16-byte loads so that a hit costs one
+// DRAM round trip instead of three dependent ones.
+struct SlotLine {
+    u128 fp;
+    double created, ttl;
+    unsigned long long stamp, value;
+};
+__device__ __forceinline__ SlotLine ld_slot_line(const Slot* s) {
+    SlotLine l;
+    asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(l.fp.lo), "=l"(l.fp.hi) : "l"(s));
+    asm volatile("ld.global.cg.v2.f64 {%0, %1}, [%2];" : "=d"(l.created), "=d"(l.ttl) : "l"(&s->created_at));
+    asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(l.stamp), "=l"(l.value) : "l"(&s->stamp));
+    return l;
+}
+
+// One KVCache.get (kvstore.py:136-164) / __contains__ (:221-228) probe.  Returns the code
+// (1 hit, 0 absent, 2 expired-and-deleted-by-this-op).
 template <bool CONTAINS>
 __device__ __forceinline__ int kv_get_one(const KvView& kv, u128 key, double now, unsigned long long stamp,
                                           unsigned long long& value, long long& slot) {
     value = 0;
-    slot = kv_find(kv, key);
-    if (slot < 0) return 0;
-    Slot* sl = &kv.slots[slot];
-    double created, ttl;
-    ld_created_ttl(sl, created, ttl);
-    if (ttl_expired(now, created, ttl)) {
+    slot = -1;
+    unsigned long long cur = key.lo & kv.mask;
+    SlotLine l;
+    bool found = false;
+    for (unsigned long long n = 0; n <= kv.mask; ++n) {
+        l = ld_slot_line(&kv.slots[cur]);
+        if (fp_eq(l.fp, key)) {
+            found = true;
+            break;
+        }
+        if (fp_empty(l.fp)) break;
+        cur = (cur + 1) & kv.mask;
+    }
+    if (!found) return 0;
+    Slot* sl = &kv.slots[cur];
+    if (ttl_expired(now, l.created, l.ttl)) {
         // delete(key) (kvstore.py:153-156); exactly one of several duplicate ops wins
         const u128 old = cas128(sl, key, u128{FP_TOMB_WORD, FP_TOMB_WORD});
-        slot = -1;
         if (!fp_eq(old, key)) return 0;
-        value = ld_u64_cg(&sl->value);
+        value = l.value;
         sl->stamp = 0ull;
         release_row(kv, value);
         return 2;
     }
-    value = ld_u64_cg(&sl->value);
+    slot = (long long)cur;
+    value = l.value;
     if (!CONTAINS) {
         atomicMax(&sl->stamp, stamp);  // move_to_end: the last toucher of the batch wins
         kv.log[stamp & kv.rmask] = (uint32_t)slot;

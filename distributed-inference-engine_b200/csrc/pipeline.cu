@@ -116,11 +116,17 @@ __device__ void pipe_scan_and_window(const KvView& kv, const PipeBufs& pb, int B
         const int q0 = pos + tid * ITEMS;
         bool miss[ITEMS];
         unsigned cnt = 0;
+        if (q0 + ITEMS <= B && (reinterpret_cast<uintptr_t>(pb.code + q0) & 15) == 0) {
+            const uint4 c4 = __ldcg(reinterpret_cast<const uint4*>(pb.code + q0));  // 16 hit codes at once
+            const unsigned w[4] = {c4.x, c4.y, c4.z, c4.w};
 #pragma unroll
-        for (int k = 0; k < ITEMS; ++k) {
-            miss[k] = q0 + k < B && ld_u8_cg(pb.code + q0 + k) != 1u;
-            cnt += miss[k];
+            for (int k = 0; k < ITEMS; ++k) miss[k] = ((w[k >> 2] >> (8 * (k & 3))) & 0xffu) != 1u;
+        } else {
+#pragma unroll
+            for (int k = 0; k < ITEMS; ++k) miss[k] = q0 + k < B && ld_u8_cg(pb.code + q0 + k) != 1u;
         }
+#pragma unroll
+        for (int k = 0; k < ITEMS; ++k) cnt += miss[k];
         unsigned excl;
         const unsigned total = block_scan_pt(cnt, excl, s_warp);
         unsigned r = base + excl;
@@ -148,18 +154,21 @@ __device__ void pipe_scan_and_window(const KvView& kv, const PipeBufs& pb, int B
     constexpr int WI = 16;  // 4096 independent log/slot reads in flight per pass
     unsigned long long found = 0;
     for (unsigned long long pos = head; found < e_ub && pos < t_set; pos += (unsigned long long)PT * WI) {
+        // three separate unrolled passes so the 16 log reads, then the 16 dependent stamp reads, are all in
+        // flight together (an in-order warp would otherwise serialise 16 dependent pairs)
         bool valid[WI];
         uint32_t slot[WI];
+        unsigned long long stamp[WI];
         unsigned cnt = 0;
+        const unsigned long long p0 = pos + (unsigned long long)tid * WI;
+#pragma unroll
+        for (int k = 0; k < WI; ++k) slot[k] = p0 + k < t_set ? __ldcg(&kv.log[(p0 + k) & kv.rmask]) : 0xffffffffu;
+#pragma unroll
+        for (int k = 0; k < WI; ++k)
+            stamp[k] = (unsigned long long)slot[k] <= kv.mask ? __ldcg(&kv.slots[slot[k]].stamp) : 0ull;
 #pragma unroll
         for (int k = 0; k < WI; ++k) {
-            const unsigned long long p = pos + (unsigned long long)tid * WI + k;
-            slot[k] = 0;
-            valid[k] = false;
-            if (p < t_set) {
-                slot[k] = kv.log[p & kv.rmask];
-                valid[k] = (unsigned long long)slot[k] <= kv.mask && ld_u64_cg(&kv.slots[slot[k]].stamp) == p;
-            }
+            valid[k] = p0 + k < t_set && stamp[k] == p0 + k;
             cnt += valid[k];
         }
         unsigned excl;
