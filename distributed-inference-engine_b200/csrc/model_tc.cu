@@ -23,38 +23,50 @@ __device__ __forceinline__ uint32_t pow2_cols(uint32_t n) {
     return c;
 }
 
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src, uint32_t src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(tc::smem_u32(smem_dst)), "l"(gmem_src),
+                 "r"(src_bytes)
+                 : "memory");
+}
+
+// grid = (row tiles, column splits): CTA (x, y) computes rows [128x, 128x+128) x columns [y*Nc, (y+1)*Nc).
 __global__ void __launch_bounds__(TC_THREADS, 1)
 linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, const float* __restrict__ bias,
-                   float* __restrict__ Y, int B, int K, int N, const uint32_t* __restrict__ n_rows_dev) {
+                   float* __restrict__ Y, int B, int K, int N, int Nc, const uint32_t* __restrict__ n_rows_dev) {
     extern __shared__ uint8_t smem_raw[];
     // SWIZZLE_128B atoms must start on 1024-byte boundaries of the shared window
     uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
     __shared__ __align__(8) uint64_t bar;
     __shared__ uint32_t tmem_base;
     if (n_rows_dev) B = min(B, (int)*n_rows_dev);
-    const int m0 = blockIdx.x * TC_M;
+    const int m0 = blockIdx.x * TC_M, n0 = blockIdx.y * Nc;
     if (m0 >= B) return;  // uniform for the CTA
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int KB = K / 32;            // 128-byte (32 x tf32) blocks along K
-    const int chunks_per_row = K / 4; // 16-byte chunks per operand row
-    uint8_t* a_base = smem;                         // KB blocks of [128 rows x 128 B]
-    uint8_t* b_base = smem + (size_t)KB * TC_M * 128;  // KB blocks of [N rows x 128 B]
-    const uint32_t ncols = pow2_cols((uint32_t)N);
+    const int KB = K / 32;             // 128-byte (32 x tf32) blocks along K
+    const int chunks_per_row = K / 4;  // 16-byte chunks per operand row
+    uint8_t* a_base = smem;                               // KB blocks of [128 rows x 128 B]
+    uint8_t* b_base = smem + (size_t)KB * TC_M * 128;     // KB blocks of [Nc rows x 128 B]
+    const uint32_t ncols = pow2_cols((uint32_t)Nc);
 
     if (warp == 0) tc::tmem_alloc(&tmem_base, ncols);
     if (tid == 32) tc::mbar_init(&bar, 1);
 
-    for (int idx = tid; idx < TC_M * chunks_per_row; idx += TC_THREADS) {
-        const int r = idx / chunks_per_row, ck = idx - r * chunks_per_row;
-        int4 v = make_int4(0, 0, 0, 0);
-        if (m0 + r < B) v = ldg_stream(reinterpret_cast<const int4*>(X + (size_t)(m0 + r) * K) + ck);
-        *reinterpret_cast<int4*>(a_base + (size_t)(ck >> 3) * (TC_M * 128) + tc::sw128_offset(r, ck & 7)) = v;
+    // operands -> shared memory with cp.async (LDGSTS): a warp owns a row, lanes own its 16-byte chunks, so
+    // every request is one contiguous 512-byte row segment and nothing is staged in registers
+    for (int r = warp; r < TC_M; r += TC_THREADS / 32) {
+        const bool live = m0 + r < B;
+        const float* src = X + (size_t)(live ? m0 + r : 0) * K;
+        for (int ck = lane; ck < chunks_per_row; ck += 32)
+            cp_async16(a_base + (size_t)(ck >> 3) * (TC_M * 128) + tc::sw128_offset(r, ck & 7), src + ck * 4,
+                       live ? 16u : 0u);  // src-size 0 zero-fills rows past the end of the batch
     }
-    for (int idx = tid; idx < N * chunks_per_row; idx += TC_THREADS) {
-        const int r = idx / chunks_per_row, ck = idx - r * chunks_per_row;
-        const int4 v = __ldg(reinterpret_cast<const int4*>(W + (size_t)r * K) + ck);
-        *reinterpret_cast<int4*>(b_base + (size_t)(ck >> 3) * ((size_t)N * 128) + tc::sw128_offset(r, ck & 7)) = v;
+    for (int r = warp; r < Nc; r += TC_THREADS / 32) {
+        const float* src = W + (size_t)(n0 + r) * K;
+        for (int ck = lane; ck < chunks_per_row; ck += 32)
+            cp_async16(b_base + (size_t)(ck >> 3) * ((size_t)Nc * 128) + tc::sw128_offset(r, ck & 7), src + ck * 4, 16u);
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     tc::fence_proxy_async_smem();
     tc::fence_before_thread_sync();
     __syncthreads();
@@ -62,13 +74,13 @@ linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, con
     const uint32_t taddr = tmem_base;
 
     if (tid == 0) {
-        const uint32_t idesc = tc::instr_desc(tc::FMT_TF32, TC_M, (uint32_t)N);
+        const uint32_t idesc = tc::instr_desc(tc::FMT_TF32, TC_M, (uint32_t)Nc);
         const uint32_t a_s = tc::smem_u32(a_base), b_s = tc::smem_u32(b_base);
         for (int kb = 0; kb < KB; ++kb) {
 #pragma unroll
             for (int j = 0; j < 4; ++j) {  // 4 x (K = 8 tf32 = 32 bytes) per 128-byte block
                 const uint64_t ad = tc::smem_desc_k_major_sw128(a_s + kb * (TC_M * 128) + j * 32);
-                const uint64_t bd = tc::smem_desc_k_major_sw128(b_s + kb * (N * 128) + j * 32);
+                const uint64_t bd = tc::smem_desc_k_major_sw128(b_s + kb * (Nc * 128) + j * 32);
                 tc::mma_tf32(taddr, ad, bd, idesc, (kb | j) != 0);
             }
         }
@@ -77,22 +89,22 @@ linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, con
     tc::mbar_wait(&bar, 0);
     tc::fence_after_thread_sync();
 
-    // epilogue: TMEM -> registers (+bias) -> shared (row pitch N+4 floats) -> coalesced rows
+    // epilogue: TMEM -> registers (+bias) -> shared (row pitch Nc+4 floats) -> coalesced row segments
     float* stage = reinterpret_cast<float*>(smem);
-    const int pitch = N + 4;
+    const int pitch = Nc + 4;
     if (warp < 4) {
         const int row = warp * 32 + lane;
-        for (int c0 = 0; c0 < N; c0 += 32) {
+        for (int c0 = 0; c0 < Nc; c0 += 32) {
             uint32_t v[32];
             tc::tmem_ld_32x32(taddr + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
-                if (c0 + j < N) {
+                if (c0 + j < Nc) {
                     float4 o;
-                    o.x = __uint_as_float(v[j + 0]) + (bias ? bias[c0 + j + 0] : 0.f);
-                    o.y = __uint_as_float(v[j + 1]) + (bias ? bias[c0 + j + 1] : 0.f);
-                    o.z = __uint_as_float(v[j + 2]) + (bias ? bias[c0 + j + 2] : 0.f);
-                    o.w = __uint_as_float(v[j + 3]) + (bias ? bias[c0 + j + 3] : 0.f);
+                    o.x = __uint_as_float(v[j + 0]) + (bias ? bias[n0 + c0 + j + 0] : 0.f);
+                    o.y = __uint_as_float(v[j + 1]) + (bias ? bias[n0 + c0 + j + 1] : 0.f);
+                    o.z = __uint_as_float(v[j + 2]) + (bias ? bias[n0 + c0 + j + 2] : 0.f);
+                    o.w = __uint_as_float(v[j + 3]) + (bias ? bias[n0 + c0 + j + 3] : 0.f);
                     *reinterpret_cast<float4*>(stage + (size_t)row * pitch + c0 + j) = o;
                 }
             }
@@ -101,12 +113,11 @@ linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, con
     tc::fence_before_thread_sync();
     __syncthreads();
     const int rows = min(TC_M, B - m0);
-    const int vec_per_row = N / 4;
-    for (int r = warp; r < rows; r += TC_THREADS / 32) {
-        for (int c = lane; c < vec_per_row; c += 32) {
-            const int4 o = *reinterpret_cast<const int4*>(stage + (size_t)r * pitch + c * 4);
-            stg_stream(reinterpret_cast<int4*>(Y + (size_t)(m0 + r) * N) + c, o);
-        }
+    const int vec_per_row = Nc / 4;
+    for (int e = tid; e < rows * vec_per_row; e += TC_THREADS) {
+        const int r = e / vec_per_row, c = e - r * vec_per_row;
+        const int4 o = *reinterpret_cast<const int4*>(stage + (size_t)r * pitch + c * 4);
+        stg_stream(reinterpret_cast<int4*>(Y + (size_t)(m0 + r) * N + n0) + c, o);
     }
     if (warp == 0) {
         tc::fence_after_thread_sync();
@@ -121,8 +132,16 @@ die_status_t linear_tf32_launch(const float* X, const float* W, const float* b, 
         DIE_FAIL(DIE_ERR_UNSUPPORTED, "linear tf32: needs K %% 32 == 0 and N in [16,256] multiple of 16 (K=%d N=%d)", K, N);
     if ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(Y)) & 15)
         DIE_FAIL(DIE_ERR_UNSUPPORTED, "linear tf32: X, W and Y must be 16-byte aligned");
-    const size_t operands = (size_t)(TC_M + N) * K * sizeof(float);
-    const size_t staging = (size_t)TC_M * (N + 4) * sizeof(float);
+    // split the columns over CTAs until the grid covers the SMs (the layer is bandwidth/latency bound:
+    // more CTAs = more loads in flight; X tiles are re-read from L2, not from HBM)
+    const int tiles = ceil_div(B, TC_M);
+    int n_split = 1;
+    while (tiles * n_split * 2 <= num_sms() && (N / (n_split * 2)) >= 32 && (N / (n_split * 2)) % 16 == 0 &&
+           N % (n_split * 2) == 0)
+        n_split *= 2;
+    const int Nc = N / n_split;
+    const size_t operands = (size_t)(TC_M + Nc) * K * sizeof(float);
+    const size_t staging = (size_t)TC_M * (Nc + 4) * sizeof(float);
     const size_t smem = std::max(operands, staging) + 1024;  // + slack for the 1024-byte alignment
     if (smem > 200 * 1024)
         DIE_FAIL(DIE_ERR_UNSUPPORTED, "linear tf32: (128+N)*K*4 = %zu bytes of operands exceed shared memory", smem);
@@ -131,7 +150,8 @@ die_status_t linear_tf32_launch(const float* X, const float* W, const float* b, 
         DIE_CUDA(cudaFuncSetAttribute(linear_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    DIE_LAUNCH(ST_MODEL, s, linear_tf32_kernel<<<ceil_div(B, TC_M), TC_THREADS, smem, s>>>(X, W, b, Y, B, K, N, n_rows_dev));
+    dim3 grid(tiles, n_split);
+    DIE_LAUNCH(ST_MODEL, s, linear_tf32_kernel<<<grid, TC_THREADS, smem, s>>>(X, W, b, Y, B, K, N, Nc, n_rows_dev));
     return DIE_OK;
 }
 
