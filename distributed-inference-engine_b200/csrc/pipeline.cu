@@ -44,12 +44,17 @@ struct die_pipeline {
     PipeCtrl* ctrl;
     float* packed_in;    // [B, dim_in]
     float* packed_out;   // [B, dim_out]
-    // staging for the host-buffer entry point
-    uint8_t* d_key_bytes;
-    int64_t* d_key_off;
-    float* d_payload;
-    float* d_out;
-    uint8_t* d_hit;
+    // staging for the host-buffer entry points (NBUF sets: copy-in, compute and copy-out of consecutive
+    // batches overlap in die_pipeline_run_host_many)
+    static constexpr int NBUF = 3;
+    uint8_t* d_key_bytes;   // NBUF x (max_key_bytes + 16)
+    int64_t* d_key_off;     // NBUF x (B + 1)
+    float* d_payload;       // NBUF x B x dim_in
+    float* d_out;           // NBUF x B x dim_out
+    uint8_t* d_hit;         // NBUF x B
+    size_t key_stage_stride;
+    cudaStream_t s_in, s_out;
+    cudaEvent_t ev_in[NBUF], ev_done[NBUF], ev_out[NBUF];
 };
 
 namespace die {
@@ -548,11 +553,20 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
     DIE_CUDA(cudaMalloc(&p->packed_out, B * cfg->dim_out * sizeof(float)));
     const size_t key_bytes = cfg->max_key_bytes > 0 ? (size_t)cfg->max_key_bytes : B * 64;
     p->cfg.max_key_bytes = (int32_t)key_bytes;
-    DIE_CUDA(cudaMalloc(&p->d_key_bytes, key_bytes + 16));
-    DIE_CUDA(cudaMalloc(&p->d_key_off, (B + 1) * sizeof(int64_t)));
-    DIE_CUDA(cudaMalloc(&p->d_payload, B * cfg->dim_in * sizeof(float)));
-    DIE_CUDA(cudaMalloc(&p->d_out, B * cfg->dim_out * sizeof(float)));
-    DIE_CUDA(cudaMalloc(&p->d_hit, B));
+    constexpr int NB = die_pipeline::NBUF;
+    p->key_stage_stride = (key_bytes + 16 + 255) / 256 * 256;
+    DIE_CUDA(cudaMalloc(&p->d_key_bytes, NB * p->key_stage_stride));
+    DIE_CUDA(cudaMalloc(&p->d_key_off, NB * (B + 1) * sizeof(int64_t)));
+    DIE_CUDA(cudaMalloc(&p->d_payload, NB * B * cfg->dim_in * sizeof(float)));
+    DIE_CUDA(cudaMalloc(&p->d_out, NB * B * cfg->dim_out * sizeof(float)));
+    DIE_CUDA(cudaMalloc(&p->d_hit, NB * B));
+    DIE_CUDA(cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking));
+    DIE_CUDA(cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking));
+    for (int i = 0; i < NB; ++i) {
+        DIE_CUDA(cudaEventCreateWithFlags(&p->ev_in[i], cudaEventDisableTiming));
+        DIE_CUDA(cudaEventCreateWithFlags(&p->ev_done[i], cudaEventDisableTiming));
+        DIE_CUDA(cudaEventCreateWithFlags(&p->ev_out[i], cudaEventDisableTiming));
+    }
     *out = p;
     return DIE_OK;
 }
@@ -564,6 +578,13 @@ extern "C" die_status_t die_pipeline_destroy(die_pipeline_t* p) {
                     p->set_row, p->cand_slot, p->cand_pos, p->ctrl, p->packed_in, p->packed_out, p->d_key_bytes,
                     p->d_key_off, p->d_payload, p->d_out, p->d_hit};
     for (void* b : bufs) cudaFree(b);
+    if (p->s_in) cudaStreamDestroy(p->s_in);
+    if (p->s_out) cudaStreamDestroy(p->s_out);
+    for (int i = 0; i < die_pipeline::NBUF; ++i) {
+        if (p->ev_in[i]) cudaEventDestroy(p->ev_in[i]);
+        if (p->ev_done[i]) cudaEventDestroy(p->ev_done[i]);
+        if (p->ev_out[i]) cudaEventDestroy(p->ev_out[i]);
+    }
     delete p;
     return DIE_OK;
 }
@@ -622,6 +643,74 @@ extern "C" die_status_t die_pipeline_run_host(die_pipeline_t* p, const uint8_t* 
                                     stream));
     DIE_CUDA(cudaMemcpyAsync(out, p->d_out, (size_t)B * c.dim_out * sizeof(float), cudaMemcpyDeviceToHost, s));
     if (hit_out) DIE_CUDA(cudaMemcpyAsync(hit_out, p->d_hit, (size_t)B, cudaMemcpyDeviceToHost, s));
+    DIE_CUDA(cudaStreamSynchronize(s));
+    return DIE_OK;
+}
+
+// A queue of flushed batches submitted in one call: batch j reads key_bytes + j*key_bytes_stride,
+// key_off + j*key_off_stride (0 = every batch has the same offsets), payload + j*B*dim_in and writes
+// out + (j % out_ring)*B*dim_out, hit_out + (j % out_ring)*B.  Batches are applied strictly in order.
+extern "C" die_status_t die_pipeline_run_device_many(die_pipeline_t* p, int32_t n_batches, const uint8_t* key_bytes,
+                                                     int64_t key_bytes_stride, const int64_t* key_off,
+                                                     int64_t key_off_stride, int32_t B, const float* payload,
+                                                     double now0, double now_step, float* out, uint8_t* hit_out,
+                                                     int32_t out_ring, die_stream_t stream) {
+    if (!p || n_batches < 0 || out_ring < 1) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_device_many: bad arguments");
+    const size_t in_row = (size_t)B * p->cfg.dim_in, out_row = (size_t)B * p->cfg.dim_out;
+    for (int32_t j = 0; j < n_batches; ++j) {
+        const int r = j % out_ring;
+        DIE_TRY(die_pipeline_run_device(p, key_bytes + (size_t)j * key_bytes_stride, key_off + (size_t)j * key_off_stride,
+                                        B, payload + (size_t)j * in_row, now0 + j * now_step, out + (size_t)r * out_row,
+                                        hit_out ? hit_out + (size_t)r * B : nullptr, nullptr, stream));
+    }
+    return DIE_OK;
+}
+
+// The same queue through HOST buffers (pinned): copy-in of batch j+1, the kernels of batch j and the copy-out of
+// batch j-1 run on three streams over NBUF staging sets.  out [n, B, dim_out] and hit_out [n, B] are all written.
+// Synchronises before returning.
+extern "C" die_status_t die_pipeline_run_host_many(die_pipeline_t* p, int32_t n_batches, const uint8_t* key_bytes,
+                                                   int64_t key_bytes_stride, const int64_t* key_off,
+                                                   int64_t key_off_stride, int32_t B, const float* payload,
+                                                   double now0, double now_step, float* out, uint8_t* hit_out,
+                                                   die_stream_t stream) {
+    if (!p || n_batches < 0 || B <= 0 || B > p->cfg.max_batch)
+        DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_host_many: bad arguments");
+    if (!key_off || !payload || !out) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_host_many: null buffer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const die_pipeline_config_t& c = p->cfg;
+    constexpr int NB = die_pipeline::NBUF;
+    const size_t in_row = (size_t)B * c.dim_in, out_row = (size_t)B * c.dim_out;
+    for (int32_t j = 0; j < n_batches; ++j) {
+        const int b = j % NB;
+        const int64_t* ko = key_off + (size_t)j * key_off_stride;
+        const int64_t nbytes = ko[B] - ko[0];
+        if (ko[0] != 0 || nbytes < 0 || nbytes > c.max_key_bytes)
+            DIE_FAIL(DIE_ERR_TOO_LARGE, "die_pipeline_run_host_many: batch %d has %lld key bytes (limit %d)", j,
+                     (long long)nbytes, c.max_key_bytes);
+        uint8_t* dk = p->d_key_bytes + (size_t)b * p->key_stage_stride;
+        int64_t* dko = p->d_key_off + (size_t)b * (B + 1);
+        float* dp = p->d_payload + (size_t)b * ((size_t)c.max_batch * c.dim_in);
+        float* dout = p->d_out + (size_t)b * ((size_t)c.max_batch * c.dim_out);
+        uint8_t* dh = p->d_hit + (size_t)b * c.max_batch;
+        // staging set b is free once batch j-NB has been computed (inputs) and copied out (outputs)
+        if (j >= NB) {
+            DIE_CUDA(cudaStreamWaitEvent(p->s_in, p->ev_done[b], 0));
+            DIE_CUDA(cudaStreamWaitEvent(s, p->ev_out[b], 0));
+        }
+        if (nbytes) DIE_CUDA(cudaMemcpyAsync(dk, key_bytes + (size_t)j * key_bytes_stride, (size_t)nbytes, cudaMemcpyHostToDevice, p->s_in));
+        DIE_CUDA(cudaMemcpyAsync(dko, ko, (size_t)(B + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, p->s_in));
+        DIE_CUDA(cudaMemcpyAsync(dp, payload + (size_t)j * in_row, in_row * sizeof(float), cudaMemcpyHostToDevice, p->s_in));
+        DIE_CUDA(cudaEventRecord(p->ev_in[b], p->s_in));
+        DIE_CUDA(cudaStreamWaitEvent(s, p->ev_in[b], 0));
+        DIE_TRY(die_pipeline_run_device(p, dk, dko, B, dp, now0 + j * now_step, dout, dh, nullptr, stream));
+        DIE_CUDA(cudaEventRecord(p->ev_done[b], s));
+        DIE_CUDA(cudaStreamWaitEvent(p->s_out, p->ev_done[b], 0));
+        DIE_CUDA(cudaMemcpyAsync(out + (size_t)j * out_row, dout, out_row * sizeof(float), cudaMemcpyDeviceToHost, p->s_out));
+        if (hit_out) DIE_CUDA(cudaMemcpyAsync(hit_out + (size_t)j * B, dh, (size_t)B, cudaMemcpyDeviceToHost, p->s_out));
+        DIE_CUDA(cudaEventRecord(p->ev_out[b], p->s_out));
+    }
+    DIE_CUDA(cudaStreamSynchronize(p->s_out));
     DIE_CUDA(cudaStreamSynchronize(s));
     return DIE_OK;
 }

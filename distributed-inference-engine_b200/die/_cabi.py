@@ -69,6 +69,9 @@ SIGNATURES = {
     "die_pipeline_run_device": (c_int32, [P, P, P, c_int32, P, c_double, P, P, P, P]),
     "die_pipeline_run_owner_device": (c_int32, [P, P, c_int32, P, c_double, P, P, P]),
     "die_pipeline_run_host": (c_int32, [P, P, P, c_int32, P, c_double, P, P, P]),
+    "die_pipeline_run_device_many": (c_int32, [P, c_int32, P, c_int64, P, c_int64, c_int32, P, c_double, c_double, P, P,
+                                               c_int32, P]),
+    "die_pipeline_run_host_many": (c_int32, [P, c_int32, P, c_int64, P, c_int64, c_int32, P, c_double, c_double, P, P, P]),
 }
 
 _lib = None

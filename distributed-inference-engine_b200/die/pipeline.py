@@ -69,6 +69,25 @@ class DispatchPipeline:
         check(self._lib.die_pipeline_run_host(self._h, ptr(key_bytes), ptr(key_off), B, ptr(payload), now, ptr(out),
                                               ptr(hit), stream_ptr()))
 
+    def run_device_many(self, key_bytes: torch.Tensor, key_off: torch.Tensor, payload: torch.Tensor, now0: float,
+                        now_step: float, out: torch.Tensor, hit: torch.Tensor) -> None:
+        """A queue of flushed batches resident in HBM: key_bytes [n, stride] uint8, key_off [B+1] (shared) or
+        [n, B+1], payload [n, B, dim_in]; out [ring, B, dim_out], hit [ring, B] are reused round-robin."""
+        n, B = payload.shape[0], payload.shape[1]
+        shared = key_off.dim() == 1
+        check(self._lib.die_pipeline_run_device_many(self._h, n, ptr(key_bytes), key_bytes.stride(0), ptr(key_off),
+                                                     0 if shared else key_off.stride(0), B, ptr(payload), now0, now_step,
+                                                     ptr(out), ptr(hit), out.shape[0], stream_ptr()))
+
+    def run_host_many(self, key_bytes: torch.Tensor, key_off: torch.Tensor, payload: torch.Tensor, now0: float,
+                      now_step: float, out: torch.Tensor, hit: torch.Tensor) -> None:
+        """The same queue through pinned host buffers; out [n, B, dim_out], hit [n, B] (pinned).  Synchronous."""
+        n, B = payload.shape[0], payload.shape[1]
+        shared = key_off.dim() == 1
+        check(self._lib.die_pipeline_run_host_many(self._h, n, ptr(key_bytes), key_bytes.stride(0), ptr(key_off),
+                                                   0 if shared else key_off.stride(0), B, ptr(payload), now0, now_step,
+                                                   ptr(out), ptr(hit), stream_ptr()))
+
     def process(self, keys: Sequence[str], payloads: np.ndarray, now: float):
         """Convenience for tests: python strings + numpy rows -> numpy results."""
         kb, off = ops.KeyBatch.encode_host(keys)

@@ -255,6 +255,21 @@ die_status_t die_pipeline_run_host(die_pipeline_t* p, const uint8_t* key_bytes /
                                    const float* payload /*[host]*/, double now, float* out /*[host]*/,
                                    uint8_t* hit_out /*[host]*/, die_stream_t stream);
 
+/* A queue of n flushed batches in one call (each batch is still one pass of the path, applied strictly in
+ * order): batch j reads key_bytes + j*key_bytes_stride, key_off + j*key_off_stride (0 = shared offsets),
+ * payload + j*B*dim_in; device form writes out + (j % out_ring)*B*dim_out and hit_out + (j % out_ring)*B. */
+die_status_t die_pipeline_run_device_many(die_pipeline_t* p, int32_t n_batches, const uint8_t* key_bytes,
+                                          int64_t key_bytes_stride, const int64_t* key_off, int64_t key_off_stride,
+                                          int32_t B, const float* payload, double now0, double now_step, float* out,
+                                          uint8_t* hit_out, int32_t out_ring, die_stream_t stream);
+/* Host-buffer form ([host] pinned pointers; out [n,B,dim_out], hit_out [n,B]): copy-in, kernels and copy-out of
+ * consecutive batches overlap on three streams.  Synchronises before returning. */
+die_status_t die_pipeline_run_host_many(die_pipeline_t* p, int32_t n_batches, const uint8_t* key_bytes /*[host]*/,
+                                        int64_t key_bytes_stride, const int64_t* key_off /*[host]*/,
+                                        int64_t key_off_stride, int32_t B, const float* payload /*[host]*/,
+                                        double now0, double now_step, float* out /*[host]*/,
+                                        uint8_t* hit_out /*[host]*/, die_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -126,3 +126,34 @@ def test_device_resident_entry_point_equals_host_entry_point():
         out_h, hit_h = a.process(keys, x, 1.0 + step)
         out_d, hit_d = b.run_device(ops.KeyBatch.from_strings(keys), torch.from_numpy(x).cuda(), 1.0 + step)
         assert np.array_equal(out_h, out_d.cpu().numpy()) and np.array_equal(hit_h, hit_d.cpu().numpy())
+
+
+def test_queue_entry_points_equal_per_batch_calls():
+    """die_pipeline_run_device_many / run_host_many = the same batches one call at a time."""
+    from die import ops
+    from die.pipeline import DispatchPipeline
+    rng = np.random.default_rng(21)
+    n, B, D = 7, 512, 32
+    ids = rng.integers(0, 3000, (n, B))
+    keys = [["q%08d" % i for i in row] for row in ids]
+    x = rng.standard_normal((n, B, D)).astype(np.float32)
+    kb = np.stack([np.frombuffer("".join(k).encode(), dtype=np.uint8) for k in keys])
+    off = np.arange(B + 1, dtype=np.int64) * 9
+    a = DispatchPipeline(1500, B, D, model="echo", default_ttl=3.0)
+    b = DispatchPipeline(1500, B, D, model="echo", default_ttl=3.0)
+    c = DispatchPipeline(1500, B, D, model="echo", default_ttl=3.0)
+    want_out, want_hit = [], []
+    for j in range(n):
+        o, h = a.process(keys[j], x[j], 5.0 + j * 1.5)
+        want_out.append(o)
+        want_hit.append(h)
+    out = torch.empty((n, B, D), device="cuda")
+    hit = torch.empty((n, B), dtype=torch.uint8, device="cuda")
+    b.run_device_many(torch.from_numpy(kb).cuda(), torch.from_numpy(off).cuda(), torch.from_numpy(x).cuda(), 5.0, 1.5, out, hit)
+    assert np.array_equal(out.cpu().numpy(), np.stack(want_out)) and np.array_equal(hit.cpu().numpy(), np.stack(want_hit))
+    hout = torch.empty((n, B, D)).pin_memory()
+    hhit = torch.empty((n, B), dtype=torch.uint8).pin_memory()
+    kbp = torch.from_numpy(np.concatenate([kb, np.zeros((n, 16), np.uint8)], axis=1)).pin_memory()
+    c.run_host_many(kbp, torch.from_numpy(off).pin_memory(), torch.from_numpy(x).pin_memory(), 5.0, 1.5, hout, hhit)
+    assert np.array_equal(hout.numpy(), np.stack(want_out)) and np.array_equal(hhit.numpy(), np.stack(want_hit))
+    assert a.kv.stats() == b.kv.stats() == c.kv.stats()
