@@ -2,7 +2,7 @@
 #pragma once
 #include <algorithm>
 
-#include "common.cuh"
+#include "kv_internal.cuh"
 
 namespace die {
 
@@ -12,6 +12,25 @@ die_status_t linear_f32_launch(const float* X, const float* W, const float* b, f
                                const uint32_t* n_rows_dev, cudaStream_t s);
 die_status_t linear_tf32_launch(const float* X, const float* W, const float* b, float* Y, int B, int K, int N,
                                 const uint32_t* n_rows_dev, cudaStream_t s);
+// Fused pipeline epilogue of the TF32 linear kernel (see model_tc.cu): scatter results to request order and to
+// the cached rows, and evict the batch's LRU victims in the same launch.
+struct TcScatter {
+    KvView kv;
+    const int32_t* miss_req;   // rank -> request index
+    const int32_t* set_row;    // request -> cached-row handle (-1: ask the slot)
+    const int32_t* set_slot;   // request -> table slot
+    const uint32_t* cand_slot; // LRU victims, oldest first
+    const unsigned long long* cand_pos;
+    const unsigned long long* e_final;
+    const unsigned int* any_dup;
+    unsigned long long t_set;
+    float* out;                // [B, N]
+    float* arena;              // [n_rows, N]
+    uint8_t* code;             // [B]
+    int tiles;
+};
+die_status_t linear_tf32_scatter_launch(const float* X, const float* W, const float* b, int B, int K, int N,
+                                        const uint32_t* n_rows_dev, const TcScatter& sc, cudaStream_t s);
 die_status_t mlp_bf16_launch(const void* X, const void* W1, const float* b1, const void* W2, const float* b2,
                              void* hidden, void* Y, int B, int D, int H, cudaStream_t s);
 

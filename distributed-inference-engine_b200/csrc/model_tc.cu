@@ -9,6 +9,7 @@
 //   - warps 0-3 read the fp32 accumulators with tcgen05.ld (32 lanes x 32 columns), add the bias
 //     and stage the tile in shared memory; all warps then write whole rows with 512-byte coalesced
 //     stores.  The layer is HBM-bound (32 flop/B), so the tensor pipe only has to stay out of the way.
+#include "kv_internal.cuh"
 #include "model_internal.cuh"
 #include "tc_common.cuh"
 
@@ -30,9 +31,33 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src,
 }
 
 // grid = (row tiles, column splits): CTA (x, y) computes rows [128x, 128x+128) x columns [y*Nc, (y+1)*Nc).
+// SCATTER (pipeline): row `rank` of X is the rank-th miss of the batch; its result goes straight to
+// out[request] and to the cached row of the op that owns the table slot (UNPACK, batcher.py:225-227, fused
+// into the GEMM epilogue), and CTAs with blockIdx.x >= tiles evict the batch's LRU victims.
+template <bool SCATTER>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, const float* __restrict__ bias,
-                   float* __restrict__ Y, int B, int K, int N, int Nc, const uint32_t* __restrict__ n_rows_dev) {
+                   float* __restrict__ Y, int B, int K, int N, int Nc, const uint32_t* __restrict__ n_rows_dev,
+                   TcScatter sc) {
+    if (SCATTER && (int)blockIdx.x >= sc.tiles) {  // eviction CTAs (kvstore.py:82-93), 256 victims each
+        const unsigned long long e = *sc.e_final;
+        const unsigned long long g =
+            ((unsigned long long)(blockIdx.x - sc.tiles) * gridDim.y + blockIdx.y) * TC_THREADS + threadIdx.x;
+        if (g < e) {
+            Slot* sl = &sc.kv.slots[sc.cand_slot[g]];
+            release_row(sc.kv, sl->value);
+            st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+            sl->stamp = 0ull;
+        }
+        if (g == 0 && e > 0) {  // nobody else reads these counters in this kernel
+            KvState* st = sc.kv.st;
+            st->size -= e;
+            st->evictions += e;
+            st->n_tomb += e;
+            st->head = sc.cand_pos[e - 1] + 1;
+        }
+        return;
+    }
     extern __shared__ uint8_t smem_raw[];
     // SWIZZLE_128B atoms must start on 1024-byte boundaries of the shared window
     uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -114,10 +139,23 @@ linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, con
     __syncthreads();
     const int rows = min(TC_M, B - m0);
     const int vec_per_row = Nc / 4;
+    const bool any_dup = SCATTER ? (*sc.any_dup != 0u) : false;
     for (int e = tid; e < rows * vec_per_row; e += TC_THREADS) {
         const int r = e / vec_per_row, c = e - r * vec_per_row;
         const int4 o = *reinterpret_cast<const int4*>(stage + (size_t)r * pitch + c * 4);
-        stg_stream(reinterpret_cast<int4*>(Y + (size_t)(m0 + r) * N + n0) + c, o);
+        if (!SCATTER) {
+            stg_stream(reinterpret_cast<int4*>(Y + (size_t)(m0 + r) * N + n0) + c, o);
+        } else {
+            const int q = sc.miss_req[m0 + r];
+            stg_stream(reinterpret_cast<int4*>(sc.out + (size_t)q * N + n0) + c, o);
+            if (c == 0 && blockIdx.y == 0) sc.code[q] = 0;  // callers see 1 = served from the cache, 0 = computed
+            long long row = sc.set_row[q];
+            if (any_dup) {  // same key twice in the batch: only the last op's result is cached
+                const Slot* sl = &sc.kv.slots[sc.set_slot[q]];
+                row = sl->stamp == sc.t_set + (unsigned long long)q ? (long long)sl->value : -1;
+            }
+            if (row >= 0) stg_stream(reinterpret_cast<int4*>(sc.arena + (size_t)row * N + n0) + c, o);
+        }
     }
     if (warp == 0) {
         tc::fence_after_thread_sync();
@@ -125,8 +163,8 @@ linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, con
     }
 }
 
-die_status_t linear_tf32_launch(const float* X, const float* W, const float* b, float* Y, int B, int K, int N,
-                                const uint32_t* n_rows_dev, cudaStream_t s) {
+static die_status_t tf32_launch(const float* X, const float* W, const float* b, float* Y, int B, int K, int N,
+                                const uint32_t* n_rows_dev, const TcScatter* scatter, cudaStream_t s) {
     if (B == 0) return DIE_OK;
     if (K % 32 != 0 || N % 16 != 0 || N < 16 || N > 256)
         DIE_FAIL(DIE_ERR_UNSUPPORTED, "linear tf32: needs K %% 32 == 0 and N in [16,256] multiple of 16 (K=%d N=%d)", K, N);
@@ -145,14 +183,36 @@ die_status_t linear_tf32_launch(const float* X, const float* W, const float* b, 
     const size_t smem = std::max(operands, staging) + 1024;  // + slack for the 1024-byte alignment
     if (smem > 200 * 1024)
         DIE_FAIL(DIE_ERR_UNSUPPORTED, "linear tf32: (128+N)*K*4 = %zu bytes of operands exceed shared memory", smem);
-    static size_t configured = 0;
-    if (smem > configured) {
-        DIE_CUDA(cudaFuncSetAttribute(linear_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+    static size_t configured[2] = {0, 0};
+    const int which = scatter ? 1 : 0;
+    if (smem > configured[which]) {
+        if (scatter)
+            DIE_CUDA(cudaFuncSetAttribute(linear_tf32_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        else
+            DIE_CUDA(cudaFuncSetAttribute(linear_tf32_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[which] = smem;
     }
-    dim3 grid(tiles, n_split);
-    DIE_LAUNCH(ST_MODEL, s, linear_tf32_kernel<<<grid, TC_THREADS, smem, s>>>(X, W, b, Y, B, K, N, Nc, n_rows_dev));
+    if (scatter) {
+        TcScatter sc = *scatter;
+        sc.tiles = tiles;
+        const int evict_ctas = ceil_div(B, TC_THREADS);
+        dim3 grid(tiles + ceil_div(evict_ctas, n_split), n_split);
+        DIE_LAUNCH(ST_MODEL, s, linear_tf32_kernel<true><<<grid, TC_THREADS, smem, s>>>(X, W, b, Y, B, K, N, Nc, n_rows_dev, sc));
+    } else {
+        dim3 grid(tiles, n_split);
+        DIE_LAUNCH(ST_MODEL, s, linear_tf32_kernel<false><<<grid, TC_THREADS, smem, s>>>(X, W, b, Y, B, K, N, Nc, n_rows_dev, TcScatter{}));
+    }
     return DIE_OK;
+}
+
+die_status_t linear_tf32_launch(const float* X, const float* W, const float* b, float* Y, int B, int K, int N,
+                                const uint32_t* n_rows_dev, cudaStream_t s) {
+    return tf32_launch(X, W, b, Y, B, K, N, n_rows_dev, nullptr, s);
+}
+
+die_status_t linear_tf32_scatter_launch(const float* X, const float* W, const float* b, int B, int K, int N,
+                                        const uint32_t* n_rows_dev, const TcScatter& sc, cudaStream_t s) {
+    return tf32_launch(X, W, b, sc.out, B, K, N, n_rows_dev, &sc, s);
 }
 
 die_status_t mlp_bf16_launch(const void*, const void*, const float*, const void*, const float*, void*, void*, int,

@@ -37,6 +37,7 @@ struct die_pipeline {
     uint8_t* code;       // [B]
     uint64_t* value;     // [B] result-row handle of a hit
     int32_t* miss_rank;  // [B]
+    int32_t* miss_req;   // [B] inverse of miss_rank
     int32_t* set_slot;   // [B]
     int32_t* set_row;    // [B]
     uint32_t* cand_slot; // [B] victim candidates, LRU order
@@ -103,6 +104,7 @@ struct PipeBufs {
     uint8_t* code;
     unsigned long long* value;
     int32_t* miss_rank;
+    int32_t* miss_req;
     int32_t* set_slot;
     int32_t* set_row;
     uint32_t* cand_slot;
@@ -110,10 +112,9 @@ struct PipeBufs {
     PipeCtrl* ctrl;
 };
 
-// Tail of the get kernel, run by the last CTA: miss ranks + victim candidates for this batch.
-__device__ void pipe_scan_and_window(const KvView& kv, const PipeBufs& pb, int B, unsigned long long t_set) {
+// Tail of the get kernel, run by the last CTA: rank the misses of the batch in request order.
+__device__ void pipe_scan_tail(const KvView& kv, const PipeBufs& pb, int B) {
     __shared__ unsigned s_warp[PT / 32];
-    __shared__ unsigned long long s_first;
     const int tid = threadIdx.x;
     constexpr int ITEMS = 16;  // 4096 requests per pass of the CTA
     unsigned base = 0;
@@ -136,26 +137,41 @@ __device__ void pipe_scan_and_window(const KvView& kv, const PipeBufs& pb, int B
         const unsigned total = block_scan_pt(cnt, excl, s_warp);
         unsigned r = base + excl;
 #pragma unroll
-        for (int k = 0; k < ITEMS; ++k)
-            if (q0 + k < B) pb.miss_rank[q0 + k] = miss[k] ? (int32_t)r++ : -1;
+        for (int k = 0; k < ITEMS; ++k) {
+            if (q0 + k >= B) continue;
+            pb.miss_rank[q0 + k] = miss[k] ? (int32_t)r : -1;
+            if (miss[k]) pb.miss_req[r++] = q0 + k;  // rank -> request, for the fused GEMM epilogue
+        }
         base += total;
         __syncthreads();
     }
     KvState* st = kv.st;
-    if (tid == 0) pb.ctrl->ts[3] = globaltimer_ns();  // scan done
-    const unsigned long long size = ld_u64_cg(&st->size), head = ld_u64_cg(&st->head);
-    const unsigned long long e_ub = size + base > kv.max_size ? size + base - kv.max_size : 0ull;
     if (tid == 0) {
-        s_first = ~0ull;
+        const unsigned long long size = ld_u64_cg(&st->size);
+        pb.ctrl->ts[3] = globaltimer_ns();  // scan done
         pb.ctrl->n_miss = base;
-        pb.ctrl->e_ub = e_ub;
+        // upper bound of the evictions this batch's inserts can need (duplicate keys insert only once)
+        pb.ctrl->e_ub = size + base > kv.max_size ? size + base - kv.max_size : 0ull;
         pb.ctrl->e_final = 0ull;
         pb.ctrl->ticket_get = 0u;
         pb.ctrl->ticket_claim = 0u;
         pb.ctrl->any_dup = 0u;
+        st->hits += (unsigned long long)B - base;  // the batch's counters, added once (kvstore.py:150,163)
+        st->misses += base;
     }
+}
+
+// One CTA (run next to the claim / pack CTAs of the second kernel): the first e_ub current log records from
+// the head are the LRU victims, oldest first (kvstore.py:89-91).  Only pre-batch entries and this batch's
+// hits are eligible (positions < t_set); entries being inserted concurrently carry stamps >= t_set.
+__device__ void pipe_window_cta(const KvView& kv, const PipeBufs& pb, unsigned long long t_set) {
+    __shared__ unsigned s_warp[PT / 32];
+    __shared__ unsigned long long s_first;
+    const int tid = threadIdx.x;
+    KvState* st = kv.st;
+    const unsigned long long head = ld_u64_cg(&st->head), e_ub = pb.ctrl->e_ub;
+    if (tid == 0) s_first = ~0ull;
     __syncthreads();
-    // the first e_ub current log records from the head are the LRU victims, oldest first (kvstore.py:89-91)
     constexpr int WI = 16;  // 4096 independent log/slot reads in flight per pass
     unsigned long long found = 0;
     for (unsigned long long pos = head; found < e_ub && pos < t_set; pos += (unsigned long long)PT * WI) {
@@ -230,11 +246,11 @@ pipe_get_kernel(KvView kv, PipeBufs pb, const uint8_t* __restrict__ key_bytes, c
         pb.code[i] = (uint8_t)code;
         pb.value[i] = value;
     }
-    warp_add(&kv.st->hits, active && code == 1);
-    warp_add(&kv.st->misses, active && code != 1);
-    const bool deleted = active && code == 2;
-    warp_sub(&kv.st->size, deleted);
-    warp_add(&kv.st->n_tomb, deleted);
+    const bool deleted = active && code == 2;  // rare: only expired entries
+    if (__any_sync(0xffffffffu, deleted)) {
+        warp_sub(&kv.st->size, deleted);
+        warp_add(&kv.st->n_tomb, deleted);
+    }
     // the last CTA to get here has every CTA's results in L2 and runs the batch-wide tail
     __threadfence();
     __syncthreads();
@@ -243,10 +259,11 @@ pipe_get_kernel(KvView kv, PipeBufs pb, const uint8_t* __restrict__ key_bytes, c
     if (!s_last) return;
     __threadfence();
     if (threadIdx.x == 0) pb.ctrl->ts[2] = globaltimer_ns();  // all CTAs probed, tail starts
-    pipe_scan_and_window(kv, pb, B, t_set);
+    pipe_scan_tail(kv, pb, B);
 }
 
-// CTAs [0, g_claim): KVCache.set of every miss (all known absent).  CTAs [g_claim, ...): PACK + hit copy.
+// CTAs [0, g_claim): KVCache.set of every miss (all known absent).  Last CTA: LRU victim window.
+// CTAs in between: PACK + hit copy.
 __global__ void __launch_bounds__(PT)
 pipe_claim_pack_kernel(KvView kv, PipeBufs pb, const uint4* __restrict__ digests, int B, double now,
                        unsigned long long t_set, int g_claim, const int4* __restrict__ payload,
@@ -292,9 +309,13 @@ pipe_claim_pack_kernel(KvView kv, PipeBufs pb, const uint4* __restrict__ digests
         }
         return;
     }
+    if (blockIdx.x == gridDim.x - 1) {
+        pipe_window_cta(kv, pb, t_set);
+        return;
+    }
     const int vmax = vin > vout ? vin : vout;
     const long long total = (long long)B * vmax;
-    const long long stride = (long long)(gridDim.x - g_claim) * PT;
+    const long long stride = (long long)(gridDim.x - 1 - g_claim) * PT;
     for (long long v = (long long)(blockIdx.x - g_claim) * PT + threadIdx.x; v < total; v += stride) {
         const long long q = v / vmax;
         const int c = (int)(v - q * vmax);
@@ -443,6 +464,7 @@ static PipeBufs bufs_of(die_pipeline* p, uint8_t* code) {
     pb.code = code;
     pb.value = reinterpret_cast<unsigned long long*>(p->value);
     pb.miss_rank = p->miss_rank;
+    pb.miss_req = p->miss_req;
     pb.set_slot = p->set_slot;
     pb.set_row = p->set_row;
     pb.cand_slot = p->cand_slot;
@@ -472,13 +494,36 @@ static die_status_t run_fast(die_pipeline* p, const uint8_t* key_bytes, const in
     else
         DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<false><<<g, PT, 0, s>>>(v, pb, nullptr, nullptr, dg, B, now, t_get, t_set));
     const int g_pack = grid_256((long long)B * std::max(vin, vout));
-    DIE_LAUNCH(ST_KV_CLAIM, s, pipe_claim_pack_kernel<<<g + g_pack, PT, 0, s>>>(
+    DIE_LAUNCH(ST_KV_CLAIM, s, pipe_claim_pack_kernel<<<g + g_pack + 1, PT, 0, s>>>(
         v, pb, dg, B, now, t_set, g, reinterpret_cast<const int4*>(payload), reinterpret_cast<const int4*>(p->arena),
         vin, vout, reinterpret_cast<int4*>(p->packed_in), reinterpret_cast<int4*>(out)));
-    DIE_TRY(run_model(p, B, s));
+    if (c.model == DIE_MODEL_LINEAR_TF32) {
+        // third and last launch: tensor-core GEMM whose epilogue is the UNPACK, plus the eviction CTAs
+        TcScatter sc;
+        sc.kv = v;
+        sc.miss_req = p->miss_req;
+        sc.set_row = p->set_row;
+        sc.set_slot = p->set_slot;
+        sc.cand_slot = p->cand_slot;
+        sc.cand_pos = reinterpret_cast<const unsigned long long*>(p->cand_pos);
+        sc.e_final = &p->ctrl->e_final;
+        sc.any_dup = &p->ctrl->any_dup;
+        sc.t_set = t_set;
+        sc.out = out;
+        sc.arena = p->arena;
+        sc.code = code;
+        sc.tiles = 0;
+        return linear_tf32_scatter_launch(p->packed_in, p->W, p->bias, B, c.dim_in, c.dim_out, &p->ctrl->n_miss, sc, s);
+    }
+    // echo is the identity (fake_model.py:52): the unpack kernel reads the packed batch directly
+    const float* result = p->packed_in;
+    if (c.model != DIE_MODEL_ECHO) {
+        DIE_TRY(run_model(p, B, s));
+        result = p->packed_out;
+    }
     const int g_unpack = grid_256((long long)B * vout);
     DIE_LAUNCH(ST_UNPACK_STORE, s, pipe_unpack_evict_kernel<<<g + g_unpack, PT, 0, s>>>(
-        v, pb, reinterpret_cast<const int4*>(p->packed_out), t_set, B, g, vout, reinterpret_cast<int4*>(out),
+        v, pb, reinterpret_cast<const int4*>(result), t_set, B, g, vout, reinterpret_cast<int4*>(out),
         reinterpret_cast<int4*>(p->arena)));
     return DIE_OK;
 }
@@ -543,6 +588,7 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
     DIE_CUDA(cudaMalloc(&p->code, B));
     DIE_CUDA(cudaMalloc(&p->value, B * sizeof(uint64_t)));
     DIE_CUDA(cudaMalloc(&p->miss_rank, B * sizeof(int32_t)));
+    DIE_CUDA(cudaMalloc(&p->miss_req, B * sizeof(int32_t)));
     DIE_CUDA(cudaMalloc(&p->set_slot, B * sizeof(int32_t)));
     DIE_CUDA(cudaMalloc(&p->set_row, B * sizeof(int32_t)));
     DIE_CUDA(cudaMalloc(&p->cand_slot, B * sizeof(uint32_t)));
@@ -574,8 +620,8 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
 extern "C" die_status_t die_pipeline_destroy(die_pipeline_t* p) {
     if (!p) return DIE_OK;
     die_kv_destroy(p->kv);
-    void* bufs[] = {p->arena, p->W, p->bias, p->digests, p->shard, p->code, p->value, p->miss_rank, p->set_slot,
-                    p->set_row, p->cand_slot, p->cand_pos, p->ctrl, p->packed_in, p->packed_out, p->d_key_bytes,
+    void* bufs[] = {p->arena, p->W, p->bias, p->digests, p->shard, p->code, p->value, p->miss_rank, p->miss_req,
+                    p->set_slot, p->set_row, p->cand_slot, p->cand_pos, p->ctrl, p->packed_in, p->packed_out, p->d_key_bytes,
                     p->d_key_off, p->d_payload, p->d_out, p->d_hit};
     for (void* b : bufs) cudaFree(b);
     if (p->s_in) cudaStreamDestroy(p->s_in);
