@@ -2,7 +2,7 @@
 #pragma once
 #include <algorithm>
 
-#include "kv_internal.cuh"
+#include "pipeline_device.cuh"
 
 namespace die {
 
@@ -19,9 +19,7 @@ struct TcScatter {
     const int32_t* miss_req;   // rank -> request index
     const int32_t* set_row;    // request -> cached-row handle (-1: ask the slot)
     const int32_t* set_slot;   // request -> table slot
-    const uint32_t* cand_slot; // LRU victims, oldest first
-    const unsigned long long* cand_pos;
-    const unsigned long long* e_final;
+    PipeBufs pb;               // victim window + control block of the batch
     const unsigned int* any_dup;
     unsigned long long t_set;
     float* out;                // [B, N]

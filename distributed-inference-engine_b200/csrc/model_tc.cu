@@ -9,7 +9,6 @@
 //   - warps 0-3 read the fp32 accumulators with tcgen05.ld (32 lanes x 32 columns), add the bias
 //     and stage the tile in shared memory; all warps then write whole rows with 512-byte coalesced
 //     stores.  The layer is HBM-bound (32 flop/B), so the tensor pipe only has to stay out of the way.
-#include "kv_internal.cuh"
 #include "model_internal.cuh"
 #include "tc_common.cuh"
 
@@ -39,23 +38,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, const float* __restrict__ bias,
                    float* __restrict__ Y, int B, int K, int N, int Nc, const uint32_t* __restrict__ n_rows_dev,
                    TcScatter sc) {
-    if (SCATTER && (int)blockIdx.x >= sc.tiles) {  // eviction CTAs (kvstore.py:82-93), 256 victims each
-        const unsigned long long e = *sc.e_final;
-        const unsigned long long g =
-            ((unsigned long long)(blockIdx.x - sc.tiles) * gridDim.y + blockIdx.y) * TC_THREADS + threadIdx.x;
-        if (g < e) {
-            Slot* sl = &sc.kv.slots[sc.cand_slot[g]];
-            release_row(sc.kv, sl->value);
-            st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});
-            sl->stamp = 0ull;
-        }
-        if (g == 0 && e > 0) {  // nobody else reads these counters in this kernel
-            KvState* st = sc.kv.st;
-            st->size -= e;
-            st->evictions += e;
-            st->n_tomb += e;
-            st->head = sc.cand_pos[e - 1] + 1;
-        }
+    if (SCATTER && (int)blockIdx.x >= sc.tiles) {  // eviction CTAs (kvstore.py:82-93), 256 window records each
+        pipe_evict_cta(sc.kv, sc.pb, (int)((blockIdx.x - sc.tiles) * gridDim.y + blockIdx.y), sc.t_set);
         return;
     }
     extern __shared__ uint8_t smem_raw[];
@@ -195,7 +179,7 @@ static die_status_t tf32_launch(const float* X, const float* W, const float* b, 
     if (scatter) {
         TcScatter sc = *scatter;
         sc.tiles = tiles;
-        const int evict_ctas = ceil_div(B, TC_THREADS);
+        const int evict_ctas = sc.pb.n_chunks * (WCHUNK / PT);
         dim3 grid(tiles + ceil_div(evict_ctas, n_split), n_split);
         DIE_LAUNCH(ST_MODEL, s, linear_tf32_kernel<true><<<grid, TC_THREADS, smem, s>>>(X, W, b, Y, B, K, N, Nc, n_rows_dev, sc));
     } else {

@@ -14,15 +14,9 @@
 //   4 pipe_unpack_evict_kernel UNPACK packed_out[rank] -> out[q] (batcher.py:225-227) and -> the
 //                             cached row of the op that owns the slot | evict the LRU victims
 // General sequence (tiny caches): the stand-alone kernels of kvstore.cu, 9 launches.
-#include "kv_internal.cuh"
 #include "model_internal.cuh"
+#include "pipeline_device.cuh"
 #include "route_device.cuh"
-
-struct PipeCtrl {
-    unsigned int n_miss, ticket_get, ticket_claim, any_dup;
-    unsigned long long e_ub, e_final;
-    unsigned long long ts[8];  // %globaltimer marks of the last get kernel (ns): diagnostics only
-};
 
 struct die_pipeline {
     die_pipeline_config_t cfg;
@@ -40,8 +34,9 @@ struct die_pipeline {
     int32_t* miss_req;   // [B] inverse of miss_rank
     int32_t* set_slot;   // [B]
     int32_t* set_row;    // [B]
-    uint32_t* cand_slot; // [B] victim candidates, LRU order
-    uint64_t* cand_pos;  // [B] their log positions
+    uint32_t* wmask;     // victim window: validity bitmap, 1024 log records per chunk
+    uint32_t* wcount;    // current records per chunk
+    int n_chunks;
     PipeCtrl* ctrl;
     float* packed_in;    // [B, dim_in]
     float* packed_out;   // [B, dim_out]
@@ -60,7 +55,6 @@ struct die_pipeline {
 
 namespace die {
 
-constexpr int PT = 256;  // threads per CTA of the pipeline kernels (== ROUTE_THREADS)
 static_assert(PT == ROUTE_THREADS, "the fused get kernel stages keys with the route kernel's CTA shape");
 
 // block-wide exclusive scan for PT threads
@@ -99,18 +93,6 @@ __device__ __forceinline__ unsigned ld_u8_cg(const uint8_t* p) {
     asm volatile("ld.global.cg.u8 %0, [%1];" : "=r"(r) : "l"(p) : "memory");
     return r;
 }
-
-struct PipeBufs {
-    uint8_t* code;
-    unsigned long long* value;
-    int32_t* miss_rank;
-    int32_t* miss_req;
-    int32_t* set_slot;
-    int32_t* set_row;
-    uint32_t* cand_slot;
-    unsigned long long* cand_pos;
-    PipeCtrl* ctrl;
-};
 
 // Tail of the get kernel, run by the last CTA: rank the misses of the batch in request order.
 __device__ void pipe_scan_tail(const KvView& kv, const PipeBufs& pb, int B) {
@@ -156,65 +138,44 @@ __device__ void pipe_scan_tail(const KvView& kv, const PipeBufs& pb, int B) {
         pb.ctrl->ticket_get = 0u;
         pb.ctrl->ticket_claim = 0u;
         pb.ctrl->any_dup = 0u;
-        st->hits += (unsigned long long)B - base;  // the batch's counters, added once (kvstore.py:150,163)
-        st->misses += base;
+        atomicAdd(&st->hits, (unsigned long long)B - base);  // the batch's counters, added once (kvstore.py:150,163)
+        atomicAdd(&st->misses, (unsigned long long)base);
     }
+    for (int c = tid; c < pb.n_chunks; c += PT) pb.wcount[c] = 0u;
 }
 
-// One CTA (run next to the claim / pack CTAs of the second kernel): the first e_ub current log records from
-// the head are the LRU victims, oldest first (kvstore.py:89-91).  Only pre-batch entries and this batch's
-// hits are eligible (positions < t_set); entries being inserted concurrently carry stamps >= t_set.
-__device__ void pipe_window_cta(const KvView& kv, const PipeBufs& pb, unsigned long long t_set) {
-    __shared__ unsigned s_warp[PT / 32];
-    __shared__ unsigned long long s_first;
-    const int tid = threadIdx.x;
-    KvState* st = kv.st;
-    const unsigned long long head = ld_u64_cg(&st->head), e_ub = pb.ctrl->e_ub;
-    if (tid == 0) s_first = ~0ull;
-    __syncthreads();
-    constexpr int WI = 16;  // 4096 independent log/slot reads in flight per pass
-    unsigned long long found = 0;
-    for (unsigned long long pos = head; found < e_ub && pos < t_set; pos += (unsigned long long)PT * WI) {
-        // three separate unrolled passes so the 16 log reads, then the 16 dependent stamp reads, are all in
-        // flight together (an in-order warp would otherwise serialise 16 dependent pairs)
-        bool valid[WI];
-        uint32_t slot[WI];
-        unsigned long long stamp[WI];
-        unsigned cnt = 0;
-        const unsigned long long p0 = pos + (unsigned long long)tid * WI;
+// Victim window, stage 1 (CTAs next to the claim / pack CTAs of the second kernel): chunk c of 1024 log
+// records starting at the LRU head gets a bitmap of its records that are still current (= entries that are
+// in the reference's _access_order, kvstore.py:71-78) and their count.  Chunks are independent; the order
+// (oldest first, kvstore.py:89-91) is restored in stage 2 from the per-chunk counts.  Only pre-batch entries
+// and this batch's hits are eligible (positions < t_set); concurrent inserts carry stamps >= t_set.
+__device__ void pipe_window_chunk(const KvView& kv, const PipeBufs& pb, int chunk, unsigned long long t_set) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned long long head = ld_u64_cg(&kv.st->head);
+    if (chunk == 0 && tid == 0) pb.ctrl->whead = head;
+    constexpr int PER = WCHUNK / PT;  // records per thread, strided so that a warp covers 32 consecutive records
+    uint32_t slot[PER];
+    unsigned long long stamp[PER];
+    const unsigned long long base = head + (unsigned long long)chunk * WCHUNK;
 #pragma unroll
-        for (int k = 0; k < WI; ++k) slot[k] = p0 + k < t_set ? __ldcg(&kv.log[(p0 + k) & kv.rmask]) : 0xffffffffu;
-#pragma unroll
-        for (int k = 0; k < WI; ++k)
-            stamp[k] = (unsigned long long)slot[k] <= kv.mask ? __ldcg(&kv.slots[slot[k]].stamp) : 0ull;
-#pragma unroll
-        for (int k = 0; k < WI; ++k) {
-            valid[k] = p0 + k < t_set && stamp[k] == p0 + k;
-            cnt += valid[k];
-        }
-        unsigned excl;
-        const unsigned total = block_scan_pt(cnt, excl, s_warp);
-        unsigned long long rank = found + excl;
-#pragma unroll
-        for (int k = 0; k < WI; ++k) {
-            if (!valid[k]) continue;
-            const unsigned long long p = pos + (unsigned long long)tid * WI + k;
-            if (rank == 0) s_first = p;
-            if (rank < e_ub) {
-                pb.cand_slot[rank] = slot[k];
-                pb.cand_pos[rank] = p;
-            }
-            ++rank;
-        }
-        found += total;
-        __syncthreads();
+    for (int k = 0; k < PER; ++k) {
+        const unsigned long long p = base + (unsigned long long)(k * PT + tid);
+        slot[k] = p < t_set ? __ldcg(&kv.log[p & kv.rmask]) : 0xffffffffu;
     }
-    if (tid == 0) {
-        pb.ctrl->ts[4] = globaltimer_ns();  // window done
-        pb.ctrl->ts[5] = found;
-        if (found < e_ub) st->status = DIE_ERR_INVALID;  // unreachable when max_batch <= max_size
-        if (s_first != ~0ull && s_first > head) st->head = s_first;  // drop leading stale records
+#pragma unroll
+    for (int k = 0; k < PER; ++k)
+        stamp[k] = (unsigned long long)slot[k] <= kv.mask ? __ldcg(&kv.slots[slot[k]].stamp) : 0ull;
+    unsigned cnt = 0;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+        const unsigned long long p = base + (unsigned long long)(k * PT + tid);
+        const unsigned m = __ballot_sync(0xffffffffu, p < t_set && stamp[k] == p);
+        if (lane == 0) {
+            pb.wmask[chunk * 32 + k * (PT / 32) + warp] = m;  // word w covers records [32w, 32w+32) of the chunk
+            cnt += __popc(m);
+        }
     }
+    if (lane == 0 && cnt) atomicAdd(&pb.wcount[chunk], cnt);
 }
 
 template <bool FROM_KEYS>
@@ -262,7 +223,7 @@ pipe_get_kernel(KvView kv, PipeBufs pb, const uint8_t* __restrict__ key_bytes, c
     pipe_scan_tail(kv, pb, B);
 }
 
-// CTAs [0, g_claim): KVCache.set of every miss (all known absent).  Last CTA: LRU victim window.
+// CTAs [0, g_claim): KVCache.set of every miss (all known absent).  Last n_chunks CTAs: LRU victim window.
 // CTAs in between: PACK + hit copy.
 __global__ void __launch_bounds__(PT)
 pipe_claim_pack_kernel(KvView kv, PipeBufs pb, const uint4* __restrict__ digests, int B, double now,
@@ -309,13 +270,14 @@ pipe_claim_pack_kernel(KvView kv, PipeBufs pb, const uint4* __restrict__ digests
         }
         return;
     }
-    if (blockIdx.x == gridDim.x - 1) {
-        pipe_window_cta(kv, pb, t_set);
+    const int first_window = (int)gridDim.x - pb.n_chunks;
+    if ((int)blockIdx.x >= first_window) {
+        pipe_window_chunk(kv, pb, (int)blockIdx.x - first_window, t_set);
         return;
     }
     const int vmax = vin > vout ? vin : vout;
     const long long total = (long long)B * vmax;
-    const long long stride = (long long)(gridDim.x - 1 - g_claim) * PT;
+    const long long stride = (long long)(first_window - g_claim) * PT;
     for (long long v = (long long)(blockIdx.x - g_claim) * PT + threadIdx.x; v < total; v += stride) {
         const long long q = v / vmax;
         const int c = (int)(v - q * vmax);
@@ -332,21 +294,7 @@ __global__ void __launch_bounds__(PT)
 pipe_unpack_evict_kernel(KvView kv, PipeBufs pb, const int4* __restrict__ packed_out, unsigned long long t_set, int B,
                          int g_evict, int vout, int4* __restrict__ out, int4* __restrict__ arena) {
     if ((int)blockIdx.x < g_evict) {
-        const unsigned long long e = pb.ctrl->e_final;
-        const unsigned long long g = (unsigned long long)blockIdx.x * PT + threadIdx.x;
-        if (g < e) {
-            Slot* sl = &kv.slots[pb.cand_slot[g]];
-            release_row(kv, sl->value);
-            st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});
-            sl->stamp = 0ull;
-        }
-        if (g == 0 && e > 0) {  // nobody else reads these counters in this kernel
-            KvState* st = kv.st;
-            st->size -= e;
-            st->evictions += e;
-            st->n_tomb += e;
-            st->head = pb.cand_pos[e - 1] + 1;
-        }
+        pipe_evict_cta(kv, pb, (int)blockIdx.x, t_set);
         return;
     }
     const bool any_dup = pb.ctrl->any_dup != 0u;
@@ -467,8 +415,9 @@ static PipeBufs bufs_of(die_pipeline* p, uint8_t* code) {
     pb.miss_req = p->miss_req;
     pb.set_slot = p->set_slot;
     pb.set_row = p->set_row;
-    pb.cand_slot = p->cand_slot;
-    pb.cand_pos = reinterpret_cast<unsigned long long*>(p->cand_pos);
+    pb.wmask = p->wmask;
+    pb.wcount = p->wcount;
+    pb.n_chunks = p->n_chunks;
     pb.ctrl = p->ctrl;
     return pb;
 }
@@ -494,7 +443,7 @@ static die_status_t run_fast(die_pipeline* p, const uint8_t* key_bytes, const in
     else
         DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<false><<<g, PT, 0, s>>>(v, pb, nullptr, nullptr, dg, B, now, t_get, t_set));
     const int g_pack = grid_256((long long)B * std::max(vin, vout));
-    DIE_LAUNCH(ST_KV_CLAIM, s, pipe_claim_pack_kernel<<<g + g_pack + 1, PT, 0, s>>>(
+    DIE_LAUNCH(ST_KV_CLAIM, s, pipe_claim_pack_kernel<<<g + g_pack + p->n_chunks, PT, 0, s>>>(
         v, pb, dg, B, now, t_set, g, reinterpret_cast<const int4*>(payload), reinterpret_cast<const int4*>(p->arena),
         vin, vout, reinterpret_cast<int4*>(p->packed_in), reinterpret_cast<int4*>(out)));
     if (c.model == DIE_MODEL_LINEAR_TF32) {
@@ -504,9 +453,7 @@ static die_status_t run_fast(die_pipeline* p, const uint8_t* key_bytes, const in
         sc.miss_req = p->miss_req;
         sc.set_row = p->set_row;
         sc.set_slot = p->set_slot;
-        sc.cand_slot = p->cand_slot;
-        sc.cand_pos = reinterpret_cast<const unsigned long long*>(p->cand_pos);
-        sc.e_final = &p->ctrl->e_final;
+        sc.pb = pb;
         sc.any_dup = &p->ctrl->any_dup;
         sc.t_set = t_set;
         sc.out = out;
@@ -522,8 +469,9 @@ static die_status_t run_fast(die_pipeline* p, const uint8_t* key_bytes, const in
         result = p->packed_out;
     }
     const int g_unpack = grid_256((long long)B * vout);
-    DIE_LAUNCH(ST_UNPACK_STORE, s, pipe_unpack_evict_kernel<<<g + g_unpack, PT, 0, s>>>(
-        v, pb, reinterpret_cast<const int4*>(result), t_set, B, g, vout, reinterpret_cast<int4*>(out),
+    const int g_evict = p->n_chunks * (WCHUNK / PT);
+    DIE_LAUNCH(ST_UNPACK_STORE, s, pipe_unpack_evict_kernel<<<g_evict + g_unpack, PT, 0, s>>>(
+        v, pb, reinterpret_cast<const int4*>(result), t_set, B, g_evict, vout, reinterpret_cast<int4*>(out),
         reinterpret_cast<int4*>(p->arena)));
     return DIE_OK;
 }
@@ -591,8 +539,9 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
     DIE_CUDA(cudaMalloc(&p->miss_req, B * sizeof(int32_t)));
     DIE_CUDA(cudaMalloc(&p->set_slot, B * sizeof(int32_t)));
     DIE_CUDA(cudaMalloc(&p->set_row, B * sizeof(int32_t)));
-    DIE_CUDA(cudaMalloc(&p->cand_slot, B * sizeof(uint32_t)));
-    DIE_CUDA(cudaMalloc(&p->cand_pos, B * sizeof(uint64_t)));
+    p->n_chunks = (int)((4 * B + WCHUNK - 1) / WCHUNK);  // window = 4 log records per request of the largest batch
+    DIE_CUDA(cudaMalloc(&p->wmask, (size_t)p->n_chunks * 32 * sizeof(uint32_t)));
+    DIE_CUDA(cudaMalloc(&p->wcount, (size_t)p->n_chunks * sizeof(uint32_t)));
     DIE_CUDA(cudaMalloc(&p->ctrl, sizeof(PipeCtrl)));
     DIE_CUDA(cudaMemset(p->ctrl, 0, sizeof(PipeCtrl)));
     DIE_CUDA(cudaMalloc(&p->packed_in, B * cfg->dim_in * sizeof(float)));
@@ -621,7 +570,7 @@ extern "C" die_status_t die_pipeline_destroy(die_pipeline_t* p) {
     if (!p) return DIE_OK;
     die_kv_destroy(p->kv);
     void* bufs[] = {p->arena, p->W, p->bias, p->digests, p->shard, p->code, p->value, p->miss_rank, p->miss_req,
-                    p->set_slot, p->set_row, p->cand_slot, p->cand_pos, p->ctrl, p->packed_in, p->packed_out, p->d_key_bytes,
+                    p->set_slot, p->set_row, p->wmask, p->wcount, p->ctrl, p->packed_in, p->packed_out, p->d_key_bytes,
                     p->d_key_off, p->d_payload, p->d_out, p->d_hit};
     for (void* b : bufs) cudaFree(b);
     if (p->s_in) cudaStreamDestroy(p->s_in);
