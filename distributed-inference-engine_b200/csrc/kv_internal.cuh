@@ -45,6 +45,9 @@ struct KvState {
     unsigned long long status, slow_batches, n_dropped_last;
     // per set-batch scratch (reset by the last kernel of each batch)
     unsigned long long n_pre, n_absent, min_prev, n_new, conflict, n_dropped;
+    // hit / miss counters of the batched get, spread over 16 x 64-byte lines so that thousands of CTAs do not
+    // serialise on one L2 atomic unit; readers add them to hits / misses
+    unsigned long long hit_part[16][8], miss_part[16][8];
 };
 
 struct KvView {
@@ -108,6 +111,17 @@ __device__ __forceinline__ void warp_add(unsigned long long* ctr, bool pred) {
 __device__ __forceinline__ void warp_sub(unsigned long long* ctr, bool pred) {
     const unsigned m = __ballot_sync(0xffffffffu, pred);
     if (m && lane_id() == 0) atomicAdd(ctr, (unsigned long long)(-(long long)__popc(m)));
+}
+
+// One atomic per CTA instead of one per warp: counters shared by a whole launch live in one L2 sector, and
+// same-address atomics from every warp of a large batch would serialise there.  All threads must call.
+__device__ __forceinline__ void block_add(unsigned long long* ctr, bool pred) {
+    const int n = __syncthreads_count(pred);
+    if (threadIdx.x == 0 && n) atomicAdd(ctr, (unsigned long long)n);
+}
+__device__ __forceinline__ void block_sub(unsigned long long* ctr, bool pred) {
+    const int n = __syncthreads_count(pred);
+    if (threadIdx.x == 0 && n) atomicAdd(ctr, (unsigned long long)(-(long long)n));
 }
 
 // result-row handles (pipeline mode).  A kernel either pushes or pops, never both, except the

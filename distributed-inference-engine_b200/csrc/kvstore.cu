@@ -29,12 +29,12 @@ kv_get_kernel(KvView kv, const uint4* __restrict__ digests, int B, double now, u
         if (slot_out) slot_out[i] = code == 1 ? (int32_t)s : -1;
     }
     if (!CONTAINS) {
-        warp_add(&kv.st->hits, active && code == 1);
-        warp_add(&kv.st->misses, active && code != 1);
+        block_add(&kv.st->hit_part[blockIdx.x & 15][0], active && code == 1);
+        block_add(&kv.st->miss_part[blockIdx.x & 15][0], active && code != 1);
     }
     const bool deleted = active && code == 2;
-    warp_sub(&kv.st->size, deleted);
-    warp_add(&kv.st->n_tomb, deleted);
+    block_sub(&kv.st->size, deleted);
+    block_add(&kv.st->n_tomb, deleted);
 }
 
 // delete (kvstore.py:178-187)
@@ -61,8 +61,8 @@ kv_delete_kernel(KvView kv, const uint4* __restrict__ digests, int B, uint8_t* _
         deleted_out[i] = deleted ? 1 : 0;
         if (value_out) value_out[i] = value;
     }
-    warp_sub(&kv.st->size, deleted);
-    warp_add(&kv.st->n_tomb, deleted);
+    block_sub(&kv.st->size, deleted);
+    block_add(&kv.st->n_tomb, deleted);
 }
 
 // __len__ purge (kvstore.py:230-236): every expired entry is deleted.
@@ -106,8 +106,8 @@ kv_set_precheck_kernel(KvView kv, const uint4* __restrict__ digests, int M, cons
             if (p > 0) atomicMin(&kv.st->min_prev, p);
         }
     }
-    warp_add(&kv.st->n_pre, active && pre);
-    warp_add(&kv.st->n_absent, active && !pre);
+    block_add(&kv.st->n_pre, active && pre);
+    block_add(&kv.st->n_absent, active && !pre);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -243,10 +243,10 @@ kv_set_claim_kernel(KvView kv, const uint4* __restrict__ digests, int M, double 
     } else if (i < M && slot_out) {
         slot_out[i] = -1;
     }
-    warp_add(&kv.st->n_new, active && claimed);
-    warp_add(&kv.st->size, active && claimed);
-    warp_add(&kv.st->n_empty_claimed, active && claimed && from_empty);
-    warp_sub(&kv.st->n_tomb, active && claimed && !from_empty);
+    block_add(&kv.st->n_new, active && claimed);
+    block_add(&kv.st->size, active && claimed);
+    block_add(&kv.st->n_empty_claimed, active && claimed && from_empty);
+    block_sub(&kv.st->n_tomb, active && claimed && !from_empty);
 }
 
 // set, phase C2: the last op that touched a slot (largest stamp) owns its value / ttl.
@@ -474,6 +474,7 @@ __global__ void kv_state_init_kernel(KvView kv, unsigned long long head, unsigne
     KvState* st = kv.st;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         st->hits = st->misses = st->evictions = 0ull;
+        for (int i = 0; i < 16; ++i) st->hit_part[i][0] = st->miss_part[i][0] = 0ull;
         st->size = 0ull;
         st->head = head;
         st->n_tomb = st->n_empty_claimed = 0ull;
@@ -770,6 +771,10 @@ extern "C" die_status_t die_kv_stats_sync(die_kv_t* kv, uint64_t out[8], die_str
     kv->head_lb = h.head;
     out[0] = h.hits;
     out[1] = h.misses;
+    for (int i = 0; i < 16; ++i) {
+        out[0] += h.hit_part[i][0];
+        out[1] += h.miss_part[i][0];
+    }
     out[2] = h.evictions;
     out[3] = h.size;
     out[4] = kv->max_size;

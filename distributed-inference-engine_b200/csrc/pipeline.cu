@@ -256,9 +256,9 @@ pipe_claim_pack_kernel(KvView kv, PipeBufs pb, const uint4* __restrict__ digests
             pb.set_slot[i] = (int32_t)s;
             pb.set_row[i] = row;
         }
-        warp_add(&kv.st->size, active && claimed);
-        warp_add(&kv.st->n_empty_claimed, active && claimed && from_empty);
-        warp_sub(&kv.st->n_tomb, active && claimed && !from_empty);
+        block_add(&kv.st->size, active && claimed);
+        block_add(&kv.st->n_empty_claimed, active && claimed && from_empty);
+        block_sub(&kv.st->n_tomb, active && claimed && !from_empty);
         __threadfence();
         __syncthreads();
         if (threadIdx.x == 0) s_last = atomicAdd(&pb.ctrl->ticket_claim, 1u) == (unsigned)g_claim - 1;
