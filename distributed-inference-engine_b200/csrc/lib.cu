@@ -93,3 +93,47 @@ extern "C" die_status_t die_profile_end(int32_t cap, double* ms_out, uint64_t* c
 extern "C" const char* die_profile_stage_name(int32_t stage) {
     return stage >= 0 && stage < ST_COUNT ? kStageNames[stage] : "";
 }
+
+// ---- calibration kernel: random-sector read ceiling ---------------------------------------------------------
+// The table kernels are bound by random 32/64-byte accesses, not by streaming bandwidth.  This kernel issues
+// `per_thread` independent random reads of `bytes_each` (16, 32 or 64) per thread over a large buffer and
+// nothing else, to give bench.py the denominator "what the memory system delivers for random sectors".
+namespace die {
+__global__ void __launch_bounds__(256)
+random_read_kernel(const uint4* __restrict__ buf, unsigned long long n_vec16, int per_thread, int vec_per_access,
+                   unsigned long long seed, unsigned long long* __restrict__ sink) {
+    unsigned long long x = (blockIdx.x * 256ull + threadIdx.x) * 0x9E3779B97F4A7C15ull + seed;
+    uint4 acc = make_uint4(0, 0, 0, 0);
+    for (int it = 0; it < per_thread; it += 8) {
+        uint4 v[8];
+        unsigned long long idx[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            x ^= x >> 12; x ^= x << 25; x ^= x >> 27;   // xorshift64*
+            idx[k] = ((x * 0x2545F4914F6CDD1Dull) % (n_vec16 / vec_per_access)) * vec_per_access;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            v[k] = __ldcg(buf + idx[k]);
+            for (int j = 1; j < vec_per_access; ++j) {
+                const uint4 w = __ldcg(buf + idx[k] + j);
+                v[k].x ^= w.x; v[k].y ^= w.y; v[k].z ^= w.z; v[k].w ^= w.w;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { acc.x ^= v[k].x; acc.y ^= v[k].y; acc.z ^= v[k].z; acc.w ^= v[k].w; }
+    }
+    if ((acc.x ^ acc.y ^ acc.z ^ acc.w) == 0x12345678u) *sink = acc.x;  // keep the loads alive
+}
+}  // namespace die
+
+extern "C" die_status_t die_debug_random_read(const void* buf, uint64_t bytes, int32_t n_threads, int32_t per_thread,
+                                              int32_t bytes_each, uint64_t seed, uint64_t* sink, die_stream_t stream) {
+    if (!buf || bytes < 4096 || n_threads <= 0 || per_thread <= 0 || (bytes_each != 16 && bytes_each != 32 && bytes_each != 64))
+        DIE_FAIL(DIE_ERR_INVALID, "die_debug_random_read: bad arguments");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    DIE_LAUNCH(ST_BUCKET, s, random_read_kernel<<<(n_threads + 255) / 256, 256, 0, s>>>(
+        static_cast<const uint4*>(buf), bytes / 16, (per_thread + 7) / 8 * 8, bytes_each / 16, seed,
+        reinterpret_cast<unsigned long long*>(sink)));
+    return DIE_OK;
+}

@@ -1,11 +1,11 @@
 // K4/K5: ragged pack / unpack.  Replace the Batcher's gather and scatter one-liners
 // (src/batcher.py:211 and :225-227) for device-resident CSR payloads.
 //
-// Work unit = one 16-byte vector of the PADDED side (always 16-byte aligned).  The ragged side
+// One warp per row, lanes stream 16-byte vectors.  The padded side is always 16-byte aligned; the ragged side
 // is read/written at its natural alignment: reads use two aligned 128-bit loads + a funnel shift
-// (pack_device.cuh), so DRAM traffic stays at the algorithmic bytes; stores to ragged rows are
-// full 128-bit where the vector lies inside the row and element-wise at the two ragged ends.
-// Grid = a multiple of the SM count, grid-stride over vectors.
+// (pack_device.cuh), so DRAM traffic stays at the algorithmic bytes; stores to ragged rows are full 128-bit
+// where the vector lies inside the row and element-wise at the two ragged ends.
+// Grid = up to 16 CTAs per SM, grid-stride over rows.
 #include "common.cuh"
 #include "pack_device.cuh"
 
@@ -13,30 +13,33 @@ namespace die {
 
 constexpr int PACK_THREADS = 256;
 
-// out[r, :] = values[off[q] : off[q+1]] zero-padded, q = src_index ? src_index[r] : r
+// out[r, :] = values[off[q] : off[q+1]] zero-padded, q = src_index ? src_index[r] : r.
+// One warp per row (grid-stride over rows): the row's offsets are read once, lanes stream its 16-byte vectors,
+// first the live part (shifted loads from the ragged source), then the zero padding (stores only).
 __global__ void __launch_bounds__(PACK_THREADS)
 pack_vec_kernel(const uint8_t* __restrict__ values, const int64_t* __restrict__ off,
                 const int32_t* __restrict__ src_index, long long R, int elem_bytes, int vpr /*vectors per row*/,
                 int4* __restrict__ out, int32_t* __restrict__ lengths_out) {
-    const long long total = R * vpr;
+    const int lane = threadIdx.x & 31;
+    const long long warps = (long long)gridDim.x * (PACK_THREADS / 32);
     const int row_bytes = vpr * 16;
-    for (long long v = blockIdx.x * (long long)PACK_THREADS + threadIdx.x; v < total;
-         v += (long long)gridDim.x * PACK_THREADS) {
-        const long long r = v / vpr;
-        const int c = (int)(v - r * vpr);
+    for (long long r = (long long)blockIdx.x * (PACK_THREADS / 32) + (threadIdx.x >> 5); r < R; r += warps) {
         const long long q = src_index ? src_index[r] : r;
         const long long o0 = off[q], o1 = off[q + 1];
         const long long len_bytes_full = (o1 - o0) * elem_bytes;
         const int len_bytes = (int)(len_bytes_full < row_bytes ? len_bytes_full : row_bytes);
-        if (c == 0 && lengths_out) lengths_out[r] = (int32_t)(o1 - o0);
-        const int keep = len_bytes - c * 16;  // bytes of this vector that carry payload
-        int4 val = make_int4(0, 0, 0, 0);
-        if (keep > 0) {
-            const uint8_t* src = values + o0 * elem_bytes + (long long)c * 16;
-            val = load16_shifted(src, 0, keep < 16 ? keep : 16);
+        if (lane == 0 && lengths_out) lengths_out[r] = (int32_t)(o1 - o0);
+        const uint8_t* src = values + o0 * elem_bytes;
+        int4* dst = out + r * vpr;
+        const int live = (len_bytes + 15) >> 4;  // vectors that carry payload
+        for (int c = lane; c < live; c += 32) {
+            const int keep = len_bytes - c * 16;
+            int4 val = load16_shifted(src + (long long)c * 16, 0, keep < 16 ? keep : 16);
             if (keep < 16) val = mask_tail16(val, keep);
+            stg_stream(dst + c, val);
         }
-        stg_stream(out + v, val);
+        const int4 zero = make_int4(0, 0, 0, 0);
+        for (int c = live + lane; c < vpr; c += 32) stg_stream(dst + c, zero);
     }
 }
 
@@ -59,17 +62,16 @@ pack_elem_kernel(const uint8_t* __restrict__ values, const int64_t* __restrict__
 }
 
 // out_values[off_out[q] : off_out[q+1]] = packed[r, :len], q = dst_index ? dst_index[r] : r.
-// Work unit = one 16-byte ALIGNED vector of the ragged destination; vpr1 = vectors per row + 1
-// because a row of Lpad*elem_bytes bytes at an arbitrary offset can straddle one extra vector.
+// One warp per row; the work unit of a lane is one 16-byte ALIGNED vector of the ragged destination, so
+// stores are full 128-bit except at the two ragged ends of the row (element-wise there: neighbouring rows
+// share those vectors).  Only the live part of the padded row is read.
 __global__ void __launch_bounds__(PACK_THREADS)
 unpack_vec_kernel(const uint8_t* __restrict__ packed, const int64_t* __restrict__ off_out,
                   const int32_t* __restrict__ dst_index, long long R, int elem_bytes, int row_bytes, int vpr1,
                   uint8_t* __restrict__ out_values) {
-    const long long total = R * vpr1;
-    for (long long v = blockIdx.x * (long long)PACK_THREADS + threadIdx.x; v < total;
-         v += (long long)gridDim.x * PACK_THREADS) {
-        const long long r = v / vpr1;
-        const int c = (int)(v - r * vpr1);
+    const int lane = threadIdx.x & 31;
+    const long long warps = (long long)gridDim.x * (PACK_THREADS / 32);
+    for (long long r = (long long)blockIdx.x * (PACK_THREADS / 32) + (threadIdx.x >> 5); r < R; r += warps) {
         const long long q = dst_index ? dst_index[r] : r;
         const long long o0 = off_out[q];
         long long len_bytes = (off_out[q + 1] - o0) * elem_bytes;
@@ -77,24 +79,27 @@ unpack_vec_kernel(const uint8_t* __restrict__ packed, const int64_t* __restrict_
         if (len_bytes <= 0) continue;
         const uintptr_t d0 = reinterpret_cast<uintptr_t>(out_values) + (uintptr_t)(o0 * elem_bytes);
         const uintptr_t d1 = d0 + (uintptr_t)len_bytes;
-        const uintptr_t va = (d0 & ~uintptr_t(15)) + (uintptr_t)c * 16;  // this thread's aligned vector
-        if (va >= d1) continue;
-        const int first = va < d0 ? (int)(d0 - va) : 0;             // first byte of the vector inside the row
-        const int last = va + 16 > d1 ? (int)(d1 - va) : 16;        // one past the last byte inside the row
-        // source byte for destination byte va+k is packed_row + (va + k - d0)
-        const uint8_t* src = packed + r * (long long)row_bytes + ((long long)va - (long long)d0);
-        const int4 val = load16_shifted(src, first, last);
-        if (first == 0 && last == 16) {
-            stg_stream(reinterpret_cast<int4*>(va), val);
-        } else {
-            const unsigned w[4] = {(unsigned)val.x, (unsigned)val.y, (unsigned)val.z, (unsigned)val.w};
-            uint8_t* dst = reinterpret_cast<uint8_t*>(va);
-            if ((elem_bytes & 3) == 0) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    if (4 * j >= first && 4 * j + 4 <= last) reinterpret_cast<unsigned*>(dst)[j] = w[j];
+        const uintptr_t a0 = d0 & ~uintptr_t(15);
+        const int nvec = (int)((d1 - a0 + 15) >> 4);  // aligned destination vectors the row touches
+        const uint8_t* row = packed + r * (long long)row_bytes;
+        for (int c = lane; c < nvec; c += 32) {
+            const uintptr_t va = a0 + (uintptr_t)c * 16;
+            const int first = va < d0 ? (int)(d0 - va) : 0;       // first byte of the vector inside the row
+            const int last = va + 16 > d1 ? (int)(d1 - va) : 16;  // one past the last byte inside the row
+            // source byte for destination byte va+k is row + (va + k - d0)
+            const int4 val = load16_shifted(row + ((long long)va - (long long)d0), first, last);
+            if (first == 0 && last == 16) {
+                stg_stream(reinterpret_cast<int4*>(va), val);
             } else {
-                for (int k = first; k < last; ++k) dst[k] = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
+                const unsigned w[4] = {(unsigned)val.x, (unsigned)val.y, (unsigned)val.z, (unsigned)val.w};
+                uint8_t* dst = reinterpret_cast<uint8_t*>(va);
+                if ((elem_bytes & 3) == 0) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (4 * j >= first && 4 * j + 4 <= last) reinterpret_cast<unsigned*>(dst)[j] = w[j];
+                } else {
+                    for (int k = first; k < last; ++k) dst[k] = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
+                }
             }
         }
     }
@@ -138,7 +143,7 @@ extern "C" die_status_t die_pack_ragged(const void* values, const int64_t* off, 
     const bool vec = row_bytes % 16 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
     if (vec) {
         const int vpr = (int)(row_bytes / 16);
-        DIE_LAUNCH(ST_PACK, s, pack_vec_kernel<<<grid_for((long long)R * vpr), PACK_THREADS, 0, s>>>(
+        DIE_LAUNCH(ST_PACK, s, pack_vec_kernel<<<grid_for((long long)R * 32), PACK_THREADS, 0, s>>>(
             static_cast<const uint8_t*>(values), off, src_index, R, elem_bytes, vpr, static_cast<int4*>(out),
             lengths_out));
     } else {
@@ -162,7 +167,7 @@ extern "C" die_status_t die_unpack_ragged(const void* packed, const int64_t* off
                      (elem_bytes == 1 || elem_bytes == 2 || (elem_bytes & 3) == 0);
     if (vec) {
         const int vpr1 = (int)(row_bytes / 16) + 1;
-        DIE_LAUNCH(ST_UNPACK, s, unpack_vec_kernel<<<grid_for((long long)R * vpr1), PACK_THREADS, 0, s>>>(
+        DIE_LAUNCH(ST_UNPACK, s, unpack_vec_kernel<<<grid_for((long long)R * 32), PACK_THREADS, 0, s>>>(
             static_cast<const uint8_t*>(packed), off_out, dst_index, R, elem_bytes, (int)row_bytes, vpr1,
             static_cast<uint8_t*>(out_values)));
     } else {

@@ -42,6 +42,7 @@ SIGNATURES = {
     "die_profile_begin": (c_int32, []),
     "die_profile_end": (c_int32, [c_int32, POINTER(c_double), POINTER(c_uint64), POINTER(c_int32)]),
     "die_profile_stage_name": (c_char_p, [c_int32]),
+    "die_debug_random_read": (c_int32, [P, c_uint64, c_int32, c_int32, c_int32, c_uint64, P, P]),
     "die_route_md5": (c_int32, [P, P, c_int32, c_int32, P, P, c_int32, c_int32, P, P, P, P]),
     "die_bucket_by_shard": (c_int32, [P, c_int32, c_int32, P, P, P, P]),
     "die_kv_create": (c_int32, [c_uint64, c_int32, c_double, POINTER(c_void_p)]),

@@ -58,6 +58,12 @@ die_status_t die_profile_end(int32_t cap, double* ms_out /*[host]*/, uint64_t* c
                              int32_t* n_stages /*[host]*/);
 const char* die_profile_stage_name(int32_t stage);
 
+/* Calibration (no reference counterpart): n_threads threads each issue per_thread independent random reads of
+ * bytes_each (16/32/64) bytes over buf[0..bytes).  bench.py times it to obtain the random-sector ceiling the
+ * table kernels are held against, next to the streaming-copy peak. */
+die_status_t die_debug_random_read(const void* buf, uint64_t bytes, int32_t n_threads, int32_t per_thread,
+                                   int32_t bytes_each, uint64_t seed, uint64_t* sink, die_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------
  * K1  route: shard = int(md5(key).hexdigest(), 16) % n_shards, then the health gate + failover.
  * Replaces ModelRegistry.get_shard_for_key (src/model_registry.py:149-161),

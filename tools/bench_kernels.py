@@ -63,6 +63,20 @@ def run(kv_entries=10_000_000, quick=False):
     K.append(entry("echo_vec_kernel", s, 2 * n * 4, n * 4, "bytes", peak, "256 MB copy"))
     del xs
 
+    # ---- random-sector ceiling over a 4 GB buffer (calibration kernel) -----------------------------------------
+    lib = _cabi.require_cuda()
+    big = torch.empty(1 << 30, dtype=torch.float32, device="cuda")  # 4 GB
+    sink = torch.zeros(1, dtype=torch.int64, device="cuda")
+    out["random_read_ceiling"] = {}
+    for each in (32, 64):
+        n_thr, per = 1 << 20, 16
+        s = timed(lambda i: _cabi.check(lib.die_debug_random_read(big.data_ptr(), big.numel() * 4, n_thr, per, each, 1234 + i,
+                                                                  sink.data_ptr(), _cabi.stream_ptr())), 5)
+        acc = n_thr * per
+        out["random_read_ceiling"][f"{each}B"] = {"accesses_per_s": round(acc / s, 1), "gbs": round(acc * each / s / 1e9, 1),
+                                                  "frac_of_hbm_peak": round(acc * each / s / 1e9 / peak, 4)}
+    del big
+
     # ---- route: 1M keys of 15 bytes ------------------------------------------------------------------------------
     nk = 1 << 20
     sets = []
