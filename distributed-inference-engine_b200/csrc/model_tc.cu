@@ -199,9 +199,4 @@ die_status_t linear_tf32_scatter_launch(const float* X, const float* W, const fl
     return tf32_launch(X, W, b, sc.out, B, K, N, n_rows_dev, &sc, s);
 }
 
-die_status_t mlp_bf16_launch(const void*, const void*, const float*, const void*, const float*, void*, void*, int,
-                             int, int, cudaStream_t) {
-    DIE_FAIL(DIE_ERR_UNSUPPORTED, "bf16 MLP (tcgen05) kernel is not built yet");
-}
-
 }  // namespace die

@@ -136,3 +136,24 @@ def test_linear_tf32_rejects_unsupported_shapes():
     w = torch.zeros((72, 100), device="cuda")
     with pytest.raises(_cabi.DieError):
         ops.linear_fwd(x, w, None, _cabi.LINEAR_TF32)
+
+
+@pytest.mark.parametrize("B,D,H", [(256, 512, 512), (100, 256, 1024), (1024, 4096, 4096)])
+def test_mlp_bf16_tensor_core_within_tolerance(B, D, H):
+    """configs[4] MLP on tcgen05 (TMA + TMEM).  Tolerance (oracle/models.py): per row
+    |d| <= 2**-7 * |y| + 1e-2 * max_j |y_j|  (bf16 output rounding + fp32 accumulation order)."""
+    from die import ops
+    rng = np.random.default_rng(B + D)
+    x = models.to_bf16(rng.standard_normal((B, D)).astype(np.float32))
+    w1 = models.to_bf16((rng.standard_normal((H, D)) / np.sqrt(D)).astype(np.float32))
+    w2 = models.to_bf16((rng.standard_normal((D, H)) / np.sqrt(H)).astype(np.float32))
+    b1 = rng.standard_normal(H).astype(np.float32)
+    b2 = rng.standard_normal(D).astype(np.float32)
+    dev = lambda a: torch.from_numpy(a).cuda()  # noqa: E731
+    y = ops.mlp_fwd_bf16(dev(x).bfloat16(), dev(w1).bfloat16(), dev(b1), dev(w2).bfloat16(), dev(b2))
+    y = y.float().cpu().numpy().astype(np.float64)
+    want = models.mlp_bf16(x, w1, b1, w2, b2)
+    tol = 2.0 ** -7 * np.abs(want) + 1e-2 * np.abs(want).max(axis=1, keepdims=True)
+    err = np.abs(y - want)
+    assert np.all(err <= tol), (float(err.max()), float((err / tol).max()))
+    assert float(np.abs(y).mean()) > 0.1  # not all zeros
