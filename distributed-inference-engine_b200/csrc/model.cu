@@ -12,8 +12,16 @@ namespace die {
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 echo_vec_kernel(const int4* __restrict__ in, int4* __restrict__ out, long long nvec) {
-    for (long long v = blockIdx.x * 256ll + threadIdx.x; v < nvec; v += (long long)gridDim.x * 256)
-        stg_stream(out + v, ldg_stream(in + v));
+    const long long stride = (long long)gridDim.x * 256;
+    for (long long v = blockIdx.x * 256ll + threadIdx.x; v < nvec; v += 4 * stride) {
+        int4 val[4];  // four loads in flight per thread before the first store
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (v + j * stride < nvec) val[j] = ldg_stream(in + v + j * stride);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (v + j * stride < nvec) stg_stream(out + v + j * stride, val[j]);
+    }
 }
 __global__ void __launch_bounds__(256)
 echo_byte_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, long long n) {

@@ -32,20 +32,26 @@ pack_vec_kernel(const uint8_t* __restrict__ values, const int64_t* __restrict__ 
         const uint8_t* src = values + o0 * elem_bytes;
         int4* dst = out + r * vpr;
         const int live = (len_bytes + 15) >> 4;  // vectors that carry payload
-        const uintptr_t sa = reinterpret_cast<uintptr_t>(src);
-        const unsigned m = (unsigned)(sa & 15);
-        const int4* base = reinterpret_cast<const int4*>(sa - m);
-        const int n_al = (int)((m + len_bytes + 15) >> 4);  // aligned source chunks that hold payload
-        for (int c0 = 0; c0 < live; c0 += 32) {             // warp-uniform trip count
-            int4 val = warp_load16_shifted(base, m, c0, n_al);
-            const int c = c0 + lane;
-            if (c < live) {
+        // four vectors per lane per trip: all loads are issued before the first store, so a warp keeps
+        // 8 x 512 bytes in flight instead of stalling on each load/store pair
+        for (int c0 = lane; c0 < live; c0 += 128) {
+            int4 val[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int c = c0 + 32 * j;
                 const int keep = len_bytes - c * 16;
-                if (keep < 16) val = mask_tail16(val, keep);
-                stg_stream(dst + c, val);
+                val[j] = make_int4(0, 0, 0, 0);
+                if (c < live) {
+                    val[j] = load16_shifted(src + (long long)c * 16, 0, keep < 16 ? keep : 16);
+                    if (keep < 16) val[j] = mask_tail16(val[j], keep);
+                }
             }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (c0 + 32 * j < live) stg_stream(dst + c0 + 32 * j, val[j]);
         }
         const int4 zero = make_int4(0, 0, 0, 0);
+#pragma unroll 4
         for (int c = live + lane; c < vpr; c += 32) stg_stream(dst + c, zero);
     }
 }
@@ -89,34 +95,28 @@ unpack_vec_kernel(const uint8_t* __restrict__ packed, const int64_t* __restrict_
         const uintptr_t a0 = d0 & ~uintptr_t(15);
         const int nvec = (int)((d1 - a0 + 15) >> 4);  // aligned destination vectors the row touches
         const uint8_t* row = packed + r * (long long)row_bytes;
-        // destination vector c holds source bytes [16c - lead, 16c - lead + 16) of the (16-byte aligned) row,
-        // lead = d0 & 15: a byte stream that starts (16 - lead) % 16 bytes into the aligned chunk below it
-        const unsigned lead = (unsigned)(d0 & 15);
-        const unsigned m = (16u - lead) & 15u;
-        const int4* base = reinterpret_cast<const int4*>(row) - (lead ? 1 : 0);
-        const int n_al_src = (int)((len_bytes + 15) >> 4) + (lead ? 1 : 0);  // chunk 0 is the (unread) one below the row
-        for (int c0 = 0; c0 < nvec; c0 += 32) {  // warp-uniform trip count
-            const int c = c0 + lane;
-            int4 val;
-            {   // like warp_load16_shifted, but chunk index 0 lies before the row when lead != 0 and is never loaded
-                int4 lo = make_int4(0, 0, 0, 0);
-                if (c < n_al_src && !(lead && c == 0)) lo = ldg_stream(base + c);
-                if (m == 0) {
-                    val = lo;
-                } else {
-                    int4 hi;
-                    hi.x = __shfl_down_sync(0xffffffffu, lo.x, 1);
-                    hi.y = __shfl_down_sync(0xffffffffu, lo.y, 1);
-                    hi.z = __shfl_down_sync(0xffffffffu, lo.z, 1);
-                    hi.w = __shfl_down_sync(0xffffffffu, lo.w, 1);
-                    if (lane == 31) hi = c + 1 < n_al_src ? ldg_stream(base + c + 1) : make_int4(0, 0, 0, 0);
-                    val = funnel16(lo, hi, m);
-                }
+        for (int c0 = lane; c0 < nvec; c0 += 128) {
+          int4 vals[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {  // issue the loads of four vectors before any store
+            const int c = c0 + 32 * j;
+            vals[j] = make_int4(0, 0, 0, 0);
+            if (c < nvec) {
+                const uintptr_t va = a0 + (uintptr_t)c * 16;
+                const int first = va < d0 ? (int)(d0 - va) : 0;
+                const int last = va + 16 > d1 ? (int)(d1 - va) : 16;
+                vals[j] = load16_shifted(row + ((long long)va - (long long)d0), first, last);
             }
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int c = c0 + 32 * j;
             if (c >= nvec) continue;
             const uintptr_t va = a0 + (uintptr_t)c * 16;
             const int first = va < d0 ? (int)(d0 - va) : 0;       // first byte of the vector inside the row
             const int last = va + 16 > d1 ? (int)(d1 - va) : 16;  // one past the last byte inside the row
+            // source byte for destination byte va+k is row + (va + k - d0)
+            const int4 val = vals[j];
             if (first == 0 && last == 16) {
                 stg_stream(reinterpret_cast<int4*>(va), val);
             } else {
@@ -130,6 +130,7 @@ unpack_vec_kernel(const uint8_t* __restrict__ packed, const int64_t* __restrict_
                     for (int k = first; k < last; ++k) dst[k] = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
                 }
             }
+          }
         }
     }
 }

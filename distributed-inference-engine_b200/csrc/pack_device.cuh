@@ -41,52 +41,6 @@ __device__ __forceinline__ int4 load16_shifted(const uint8_t* src, int first, in
     return make_int4((int)o[0], (int)o[1], (int)o[2], (int)o[3]);
 }
 
-// bytes [m, m+16) of the 32-byte pair (lo, hi), m in 1..15
-__device__ __forceinline__ int4 funnel16(const int4& lo, const int4& hi, unsigned m) {
-    const unsigned w[8] = {(unsigned)lo.x, (unsigned)lo.y, (unsigned)lo.z, (unsigned)lo.w,
-                           (unsigned)hi.x, (unsigned)hi.y, (unsigned)hi.z, (unsigned)hi.w};
-    const unsigned sb = (m & 3) * 8;
-    unsigned o[4];
-    switch (m >> 2) {
-        case 0:
-#pragma unroll
-            for (int j = 0; j < 4; ++j) o[j] = __funnelshift_r(w[j], w[j + 1], sb);
-            break;
-        case 1:
-#pragma unroll
-            for (int j = 0; j < 4; ++j) o[j] = __funnelshift_r(w[j + 1], w[j + 2], sb);
-            break;
-        case 2:
-#pragma unroll
-            for (int j = 0; j < 4; ++j) o[j] = __funnelshift_r(w[j + 2], w[j + 3], sb);
-            break;
-        default:
-#pragma unroll
-            for (int j = 0; j < 4; ++j) o[j] = __funnelshift_r(w[j + 3], w[j + 4], sb);
-            break;
-    }
-    return make_int4((int)o[0], (int)o[1], (int)o[2], (int)o[3]);
-}
-
-// Warp-cooperative shifted read.  `base` is the 16-byte aligned address at or below the first byte of a
-// byte stream that starts `m` bytes (0..15) into it; `n_al` aligned chunks cover the stream.  Lane l returns the
-// 16 stream bytes [16c, 16c+16) for c = c0 + l: every lane loads aligned chunk c once and takes chunk c+1 from
-// its neighbour by shuffle (lane 31 loads it), so each byte crosses L2->SM once.  All 32 lanes must call.
-__device__ __forceinline__ int4 warp_load16_shifted(const int4* base, unsigned m, int c0, int n_al) {
-    const int lane = threadIdx.x & 31;
-    const int c = c0 + lane;
-    int4 lo = make_int4(0, 0, 0, 0);
-    if (c < n_al) lo = ldg_stream(base + c);
-    if (m == 0) return lo;
-    int4 hi;
-    hi.x = __shfl_down_sync(0xffffffffu, lo.x, 1);
-    hi.y = __shfl_down_sync(0xffffffffu, lo.y, 1);
-    hi.z = __shfl_down_sync(0xffffffffu, lo.z, 1);
-    hi.w = __shfl_down_sync(0xffffffffu, lo.w, 1);
-    if (lane == 31) hi = c + 1 < n_al ? ldg_stream(base + c + 1) : make_int4(0, 0, 0, 0);
-    return funnel16(lo, hi, m);
-}
-
 // Zero the bytes of v at positions >= keep (0..16).
 __device__ __forceinline__ int4 mask_tail16(int4 v, int keep) {
     unsigned w[4] = {(unsigned)v.x, (unsigned)v.y, (unsigned)v.z, (unsigned)v.w};
