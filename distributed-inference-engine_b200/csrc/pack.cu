@@ -1,7 +1,8 @@
 // K4/K5: ragged pack / unpack.  Replace the Batcher's gather and scatter one-liners
 // (src/batcher.py:211 and :225-227) for device-resident CSR payloads.
 //
-// One warp per row, lanes stream 16-byte vectors.  The padded side is always 16-byte aligned; the ragged side
+// pack: one thread per 16-byte vector of the padded batch (grid-stride); unpack: one warp per row, lanes
+// stream the row's vectors.  The padded side is always 16-byte aligned; the ragged side
 // is read/written at its natural alignment: reads use two aligned 128-bit loads + a funnel shift
 // (pack_device.cuh), so DRAM traffic stays at the algorithmic bytes; stores to ragged rows are full 128-bit
 // where the vector lies inside the row and element-wise at the two ragged ends.
@@ -13,46 +14,30 @@ namespace die {
 
 constexpr int PACK_THREADS = 256;
 
-// out[r, :] = values[off[q] : off[q+1]] zero-padded, q = src_index ? src_index[r] : r.
-// One warp per row (grid-stride over rows): the row's offsets are read once, lanes stream its 16-byte vectors,
-// first the live part (shifted loads from the ragged source), then the zero padding (stores only).
+// out[r, :] = values[off[q] : off[q+1]] zero-padded, q = src_index ? src_index[r] : r
 __global__ void __launch_bounds__(PACK_THREADS)
 pack_vec_kernel(const uint8_t* __restrict__ values, const int64_t* __restrict__ off,
                 const int32_t* __restrict__ src_index, long long R, int elem_bytes, int vpr /*vectors per row*/,
                 int4* __restrict__ out, int32_t* __restrict__ lengths_out) {
-    const int lane = threadIdx.x & 31;
-    const long long warps = (long long)gridDim.x * (PACK_THREADS / 32);
+    const long long total = R * vpr;
     const int row_bytes = vpr * 16;
-    for (long long r = (long long)blockIdx.x * (PACK_THREADS / 32) + (threadIdx.x >> 5); r < R; r += warps) {
+    for (long long v = blockIdx.x * (long long)PACK_THREADS + threadIdx.x; v < total;
+         v += (long long)gridDim.x * PACK_THREADS) {
+        const long long r = v / vpr;
+        const int c = (int)(v - r * vpr);
         const long long q = src_index ? src_index[r] : r;
         const long long o0 = off[q], o1 = off[q + 1];
         const long long len_bytes_full = (o1 - o0) * elem_bytes;
         const int len_bytes = (int)(len_bytes_full < row_bytes ? len_bytes_full : row_bytes);
-        if (lane == 0 && lengths_out) lengths_out[r] = (int32_t)(o1 - o0);
-        const uint8_t* src = values + o0 * elem_bytes;
-        int4* dst = out + r * vpr;
-        const int live = (len_bytes + 15) >> 4;  // vectors that carry payload
-        // four vectors per lane per trip: all loads are issued before the first store, so a warp keeps
-        // 8 x 512 bytes in flight instead of stalling on each load/store pair
-        for (int c0 = lane; c0 < live; c0 += 128) {
-            int4 val[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int c = c0 + 32 * j;
-                const int keep = len_bytes - c * 16;
-                val[j] = make_int4(0, 0, 0, 0);
-                if (c < live) {
-                    val[j] = load16_shifted(src + (long long)c * 16, 0, keep < 16 ? keep : 16);
-                    if (keep < 16) val[j] = mask_tail16(val[j], keep);
-                }
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-                if (c0 + 32 * j < live) stg_stream(dst + c0 + 32 * j, val[j]);
+        if (c == 0 && lengths_out) lengths_out[r] = (int32_t)(o1 - o0);
+        const int keep = len_bytes - c * 16;  // bytes of this vector that carry payload
+        int4 val = make_int4(0, 0, 0, 0);
+        if (keep > 0) {
+            const uint8_t* src = values + o0 * elem_bytes + (long long)c * 16;
+            val = load16_shifted(src, 0, keep < 16 ? keep : 16);
+            if (keep < 16) val = mask_tail16(val, keep);
         }
-        const int4 zero = make_int4(0, 0, 0, 0);
-#pragma unroll 4
-        for (int c = live + lane; c < vpr; c += 32) stg_stream(dst + c, zero);
+        stg_stream(out + v, val);
     }
 }
 
@@ -173,7 +158,7 @@ extern "C" die_status_t die_pack_ragged(const void* values, const int64_t* off, 
     const bool vec = row_bytes % 16 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
     if (vec) {
         const int vpr = (int)(row_bytes / 16);
-        DIE_LAUNCH(ST_PACK, s, pack_vec_kernel<<<grid_for((long long)R * 32), PACK_THREADS, 0, s>>>(
+        DIE_LAUNCH(ST_PACK, s, pack_vec_kernel<<<grid_for((long long)R * vpr), PACK_THREADS, 0, s>>>(
             static_cast<const uint8_t*>(values), off, src_index, R, elem_bytes, vpr, static_cast<int4*>(out),
             lengths_out));
     } else {
