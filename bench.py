@@ -219,8 +219,9 @@ def main():
     w, b = model_weights()
 
     if world > 1:
-        from die.exchange import ShardedDispatcher
-        runner = ShardedDispatcher(world, rank, KV_MAX, B, D, w, b, TTL)
+        from die.exchange import PeerDispatcher, ShardedDispatcher
+        cls = ShardedDispatcher if os.environ.get("DIE_BENCH_EXCHANGE", "peer") == "nccl" else PeerDispatcher
+        runner = cls(world, rank, KV_MAX, B, D, w, b, TTL, model=MODEL)
     else:
         runner = None
     pipe = DispatchPipeline(KV_MAX, B * (2 if world > 1 else 1), D, D, MODEL, w, b, TTL, max_key_bytes=2 * B * KEY_LEN) \

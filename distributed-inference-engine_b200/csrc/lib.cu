@@ -17,7 +17,7 @@ void count_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxe
 static const char* const kStageNames[ST_COUNT] = {
     "route_md5",   "kv_get",      "kv_contains", "kv_delete",  "kv_purge", "kv_set_precheck",
     "kv_set_window", "kv_set_claim", "kv_set_finalize", "kv_set_evict", "kv_maintenance", "miss_scan",
-    "pack_hits",   "model",       "unpack_store", "pack_ragged", "unpack_ragged", "bucket_by_shard"};
+    "pack_hits",   "model",       "unpack_store", "pack_ragged", "unpack_ragged", "bucket_by_shard", "exchange"};
 
 struct ProfRec {
     int stage;

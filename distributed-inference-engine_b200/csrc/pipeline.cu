@@ -181,9 +181,11 @@ __device__ void pipe_window_chunk(const KvView& kv, const PipeBufs& pb, int chun
 template <bool FROM_KEYS>
 __global__ void __launch_bounds__(PT)
 pipe_get_kernel(KvView kv, PipeBufs pb, const uint8_t* __restrict__ key_bytes, const int64_t* __restrict__ key_off,
-                uint4* __restrict__ digests, int B, double now, unsigned long long t_get, unsigned long long t_set) {
+                uint4* __restrict__ digests, int B, const uint32_t* __restrict__ n_req_dev, double now,
+                unsigned long long t_get, unsigned long long t_set) {
     __shared__ __align__(16) uint8_t stage[FROM_KEYS ? ROUTE_STAGE_BYTES + 32 : 16];
     __shared__ bool s_last;
+    if (n_req_dev) B = min(B, (int)*n_req_dev);  // batch size known only on the device (after an exchange)
     const int i = blockIdx.x * PT + threadIdx.x;
     const bool active = i < B;
     if (i == 0) pb.ctrl->ts[0] = globaltimer_ns();  // kernel start (CTA 0)
@@ -226,10 +228,11 @@ pipe_get_kernel(KvView kv, PipeBufs pb, const uint8_t* __restrict__ key_bytes, c
 // CTAs [0, g_claim): KVCache.set of every miss (all known absent).  Last n_chunks CTAs: LRU victim window.
 // CTAs in between: PACK + hit copy.
 __global__ void __launch_bounds__(PT)
-pipe_claim_pack_kernel(KvView kv, PipeBufs pb, const uint4* __restrict__ digests, int B, double now,
-                       unsigned long long t_set, int g_claim, const int4* __restrict__ payload,
-                       const int4* __restrict__ arena, int vin, int vout, int4* __restrict__ packed_in,
-                       int4* __restrict__ out) {
+pipe_claim_pack_kernel(KvView kv, PipeBufs pb, const uint4* __restrict__ digests, int B,
+                       const uint32_t* __restrict__ n_req_dev, double now, unsigned long long t_set, int g_claim,
+                       const int4* __restrict__ payload, const int4* __restrict__ arena, int vin, int vout,
+                       int4* __restrict__ packed_in, int4* __restrict__ out) {
+    if (n_req_dev) B = min(B, (int)*n_req_dev);
     if ((int)blockIdx.x < g_claim) {
         __shared__ bool s_last;
         const int i = blockIdx.x * PT + threadIdx.x;
@@ -292,7 +295,9 @@ pipe_claim_pack_kernel(KvView kv, PipeBufs pb, const uint4* __restrict__ digests
 // CTAs [0, g_evict): evict the e_final least-recently-used entries.  Rest: UNPACK + store the cached rows.
 __global__ void __launch_bounds__(PT)
 pipe_unpack_evict_kernel(KvView kv, PipeBufs pb, const int4* __restrict__ packed_out, unsigned long long t_set, int B,
-                         int g_evict, int vout, int4* __restrict__ out, int4* __restrict__ arena) {
+                         const uint32_t* __restrict__ n_req_dev, int g_evict, int vout, int4* __restrict__ out,
+                         int4* __restrict__ arena) {
+    if (n_req_dev) B = min(B, (int)*n_req_dev);
     if ((int)blockIdx.x < g_evict) {
         pipe_evict_cta(kv, pb, (int)blockIdx.x, t_set);
         return;
@@ -425,7 +430,8 @@ static PipeBufs bufs_of(die_pipeline* p, uint8_t* code) {
 // key_off != nullptr: hash the keys in the get kernel (digests are written to `digests`);
 // otherwise `digests` are inputs.
 static die_status_t run_fast(die_pipeline* p, const uint8_t* key_bytes, const int64_t* key_off, uint32_t* digests,
-                             int B, const float* payload, double now, float* out, uint8_t* hit_out, cudaStream_t s) {
+                             int B, const uint32_t* n_req_dev, const float* payload, double now, float* out,
+                             uint8_t* hit_out, cudaStream_t s) {
     const die_pipeline_config_t& c = p->cfg;
     die_kv* kv = p->kv;
     const int vin = c.dim_in / 4, vout = c.dim_out / 4;
@@ -439,12 +445,12 @@ static die_status_t run_fast(die_pipeline* p, const uint8_t* key_bytes, const in
     const int g = ceil_div(B, PT);
     uint4* dg = reinterpret_cast<uint4*>(digests);
     if (key_off)
-        DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<true><<<g, PT, 0, s>>>(v, pb, key_bytes, key_off, dg, B, now, t_get, t_set));
+        DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<true><<<g, PT, 0, s>>>(v, pb, key_bytes, key_off, dg, B, n_req_dev, now, t_get, t_set));
     else
-        DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<false><<<g, PT, 0, s>>>(v, pb, nullptr, nullptr, dg, B, now, t_get, t_set));
+        DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<false><<<g, PT, 0, s>>>(v, pb, nullptr, nullptr, dg, B, n_req_dev, now, t_get, t_set));
     const int g_pack = grid_256((long long)B * std::max(vin, vout));
     DIE_LAUNCH(ST_KV_CLAIM, s, pipe_claim_pack_kernel<<<g + g_pack + p->n_chunks, PT, 0, s>>>(
-        v, pb, dg, B, now, t_set, g, reinterpret_cast<const int4*>(payload), reinterpret_cast<const int4*>(p->arena),
+        v, pb, dg, B, n_req_dev, now, t_set, g, reinterpret_cast<const int4*>(payload), reinterpret_cast<const int4*>(p->arena),
         vin, vout, reinterpret_cast<int4*>(p->packed_in), reinterpret_cast<int4*>(out)));
     if (c.model == DIE_MODEL_LINEAR_TF32) {
         // third and last launch: tensor-core GEMM whose epilogue is the UNPACK, plus the eviction CTAs
@@ -471,7 +477,7 @@ static die_status_t run_fast(die_pipeline* p, const uint8_t* key_bytes, const in
     const int g_unpack = grid_256((long long)B * vout);
     const int g_evict = p->n_chunks * (WCHUNK / PT);
     DIE_LAUNCH(ST_UNPACK_STORE, s, pipe_unpack_evict_kernel<<<g_evict + g_unpack, PT, 0, s>>>(
-        v, pb, reinterpret_cast<const int4*>(result), t_set, B, g_evict, vout, reinterpret_cast<int4*>(out),
+        v, pb, reinterpret_cast<const int4*>(result), t_set, B, n_req_dev, g_evict, vout, reinterpret_cast<int4*>(out),
         reinterpret_cast<int4*>(p->arena)));
     return DIE_OK;
 }
@@ -602,8 +608,21 @@ extern "C" die_status_t die_pipeline_run_owner_device(die_pipeline_t* p, const u
     if (B == 0) return DIE_OK;
     if (!digests || !payload || !out) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_owner_device: null buffer");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    if (p->fast) return run_fast(p, nullptr, nullptr, const_cast<uint32_t*>(digests), B, payload, now, out, hit_out, s);
+    if (p->fast) return run_fast(p, nullptr, nullptr, const_cast<uint32_t*>(digests), B, nullptr, payload, now, out, hit_out, s);
     return run_general(p, digests, B, payload, now, out, hit_out, s);
+}
+
+// Owner-side pass whose request count lives on the device (*n_req_dev <= B_max): what a rank runs on the
+// requests its peers just wrote into its receive buffer, without reading the count back to the host.
+extern "C" die_status_t die_pipeline_run_owner_device_n(die_pipeline_t* p, const uint32_t* digests, int32_t B_max,
+                                                        const uint32_t* n_req_dev, const float* payload, double now,
+                                                        float* out, uint8_t* hit_out, die_stream_t stream) {
+    if (!p || B_max <= 0 || B_max > p->cfg.max_batch || !n_req_dev)
+        DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_owner_device_n: bad arguments");
+    if (!digests || !payload || !out) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_owner_device_n: null buffer");
+    if (!p->fast) DIE_FAIL(DIE_ERR_UNSUPPORTED, "die_pipeline_run_owner_device_n: needs max_batch <= kv_max_size");
+    return run_fast(p, nullptr, nullptr, const_cast<uint32_t*>(digests), B_max, n_req_dev, payload, now, out, hit_out,
+                    static_cast<cudaStream_t>(stream));
 }
 
 extern "C" die_status_t die_pipeline_run_device(die_pipeline_t* p, const uint8_t* key_bytes, const int64_t* key_off,
@@ -614,7 +633,7 @@ extern "C" die_status_t die_pipeline_run_device(die_pipeline_t* p, const uint8_t
     if (!key_off || !payload || !out) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_device: null buffer");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     uint32_t* dg = digest_out ? digest_out : p->digests;
-    if (p->fast) return run_fast(p, key_bytes, key_off, dg, B, payload, now, out, hit_out, s);
+    if (p->fast) return run_fast(p, key_bytes, key_off, dg, B, nullptr, payload, now, out, hit_out, s);
     DIE_TRY(die_route_md5(key_bytes, key_off, B, 1, nullptr, nullptr, 0, 0, p->shard, dg, nullptr, stream));
     return run_general(p, dg, B, payload, now, out, hit_out, s);
 }

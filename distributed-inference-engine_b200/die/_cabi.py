@@ -69,6 +69,11 @@ SIGNATURES = {
     "die_pipeline_debug_marks_sync": (c_int32, [P, POINTER(c_uint64)]),
     "die_pipeline_run_device": (c_int32, [P, P, P, c_int32, P, c_double, P, P, P, P]),
     "die_pipeline_run_owner_device": (c_int32, [P, P, c_int32, P, c_double, P, P, P]),
+    "die_pipeline_run_owner_device_n": (c_int32, [P, P, c_int32, P, P, c_double, P, P, P]),
+    "die_xchg_dispatch": (c_int32, [P, P, P, P, c_int32, c_int32, c_int32, c_int32, c_int32, P, P, P]),
+    "die_xchg_compact": (c_int32, [P, P, c_int32, c_int32, c_int32, P, P, P, P, P]),
+    "die_xchg_return": (c_int32, [P, P, P, c_int32, c_int32, c_int32, c_int32, P, P]),
+    "die_xchg_scatter": (c_int32, [P, P, P, c_int32, c_int32, c_int32, c_int32, P, P, P]),
     "die_pipeline_run_host": (c_int32, [P, P, P, c_int32, P, c_double, P, P, P]),
     "die_pipeline_run_device_many": (c_int32, [P, c_int32, P, c_int64, P, c_int64, c_int32, P, c_double, c_double, P, P,
                                                c_int32, P]),

@@ -125,3 +125,73 @@ class ShardedDispatcher:
             hit.copy_(hit2.reshape(-1))
             return out, hit, shard
         return out, hit2.reshape(-1), shard
+
+
+class PeerDispatcher:
+    """The same dispatch over NVLink by direct peer stores (csrc/exchange.cu): no collective, no host sync.
+
+    Every rank owns a receive window and a return window inside one symmetric allocation
+    (torch.distributed._symmetric_memory); `die_xchg_dispatch` packs and writes each request row straight
+    into its owner's window, a device-side barrier separates the phases, the owner runs the fused pipeline on
+    a batch whose size it only knows on the device, and `die_xchg_return` / `die_xchg_scatter` bring the
+    results back to request order.  Owners see the sources in rank order (same contract as ShardedDispatcher)."""
+
+    def __init__(self, world: int, rank: int, kv_max_size: int, max_batch: int, dim: int, weight, bias, default_ttl,
+                 model: str = "linear_tf32", group=None):
+        import ctypes
+        import torch.distributed._symmetric_memory as symm
+        from . import _cabi, ops
+        from .pipeline import DispatchPipeline
+        self._cabi, self.ops, self._ct = _cabi, ops, ctypes
+        self.lib = _cabi.require_cuda()
+        self.world, self.rank, self.B, self.dim = world, rank, max_batch, dim
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        self.cap = max_batch
+        self.bmax = world * self.cap  # the most an owner can receive in one step
+        self.pipe = DispatchPipeline(kv_max_size, self.bmax, dim, dim, model, weight, bias, default_ttl)
+        row_in, row_out = dim + 4, dim + 4
+        n_rows = world * self.cap
+        words = n_rows * row_in + n_rows * row_out + 64
+        self.sym = symm.empty(words, dtype=torch.float32, device=self.dev)
+        self.sym.zero_()
+        self.hdl = symm.rendezvous(self.sym, group if group is not None else dist.group.WORLD)
+        base = [int(p) for p in self.hdl.buffer_ptrs]
+        off_back = n_rows * row_in * 4
+        off_cnt = off_back + n_rows * row_out * 4
+        arr = ctypes.c_void_p * world
+        self.peer_rows = arr(*[b for b in base])
+        self.peer_back = arr(*[b + off_back for b in base])
+        self.peer_cnt = arr(*[b + off_cnt for b in base])
+        self.my_rows = base[rank]
+        self.my_back = base[rank] + off_back
+        self.my_cnt = base[rank] + off_cnt
+        e = lambda shape, dt: torch.empty(shape, dtype=dt, device=self.dev)  # noqa: E731
+        self.recv_dig = e((self.bmax, 4), torch.int32)
+        self.recv_pay = e((self.bmax, dim), torch.float32)
+        self.recv_out = e((self.bmax, dim), torch.float32)
+        self.recv_hit = e((self.bmax,), torch.uint8)
+        self.n_dev = torch.zeros(1, dtype=torch.int32, device=self.dev)
+        self.prefix = torch.zeros(world + 1, dtype=torch.int32, device=self.dev)
+        torch.cuda.synchronize()
+        self.hdl.barrier(channel=0)
+
+    def step(self, keys, payload: torch.Tensor, now: float, out: Optional[torch.Tensor] = None,
+             hit: Optional[torch.Tensor] = None):
+        lib, check, ptr, st = self.lib, self._cabi.check, self._cabi.ptr, self._cabi.stream_ptr
+        W, B, D = self.world, payload.shape[0], self.dim
+        shard, digests, _ = self.ops.route_md5(keys, W)
+        offsets, perm, _pos = self.ops.bucket_by_shard(shard, W)
+        check(lib.die_xchg_dispatch(ptr(digests), ptr(payload), ptr(perm), ptr(offsets), B, D, W, self.rank, self.cap,
+                                    self.peer_rows, self.peer_cnt, st()))
+        self.hdl.barrier(channel=0)  # every rank's rows have landed in their owners' windows
+        check(lib.die_xchg_compact(self.my_rows, self.my_cnt, W, self.cap, D, ptr(self.recv_dig), ptr(self.recv_pay),
+                                   ptr(self.n_dev), ptr(self.prefix), st()))
+        check(lib.die_pipeline_run_owner_device_n(self.pipe._h, ptr(self.recv_dig), self.bmax, ptr(self.n_dev),
+                                                  ptr(self.recv_pay), now, ptr(self.recv_out), ptr(self.recv_hit), st()))
+        check(lib.die_xchg_return(ptr(self.recv_out), ptr(self.recv_hit), ptr(self.prefix), W, self.rank, self.cap, D,
+                                  self.peer_back, st()))
+        self.hdl.barrier(channel=0)  # every owner's results are back in the sources' windows
+        out = torch.empty((B, D), dtype=torch.float32, device=self.dev) if out is None else out
+        hit = torch.empty(B, dtype=torch.uint8, device=self.dev) if hit is None else hit
+        check(lib.die_xchg_scatter(self.my_back, ptr(perm), ptr(offsets), B, W, self.cap, D, ptr(out), ptr(hit), st()))
+        return out, hit, shard

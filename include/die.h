@@ -261,6 +261,36 @@ die_status_t die_pipeline_run_host(die_pipeline_t* p, const uint8_t* key_bytes /
                                    const float* payload /*[host]*/, double now, float* out /*[host]*/,
                                    uint8_t* hit_out /*[host]*/, die_stream_t stream);
 
+/* The owner-side pass when the request count is only known on the device (*n_req_dev <= B_max), i.e. right
+ * after peers have written their requests into this rank's receive window. */
+die_status_t die_pipeline_run_owner_device_n(die_pipeline_t* p, const uint32_t* digests, int32_t B_max,
+                                             const uint32_t* n_req_dev, const float* payload, double now, float* out,
+                                             uint8_t* hit_out, die_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Dispatch / return between the GPUs of one NVSwitch box by direct peer stores.  Replaces the reference's
+ * TCP + JSON hop, one request per connection (src/worker.py:84-133).  peer_* are [host] arrays of `world`
+ * device pointers into a symmetric allocation (one window per rank, see csrc/exchange.cu for the layout);
+ * the caller separates the phases with a device-side barrier of that allocation.
+ *   die_xchg_dispatch : PACK (bucket order = perm/offsets of die_bucket_by_shard) + SEND rows [digest | payload]
+ *                       into each owner's receive window, and the per-owner counts
+ *   die_xchg_compact  : owner: window regions -> contiguous digests / payload in (source rank, request) order,
+ *                       *n_out = number of requests received, prefix_out[world+1] = per-source starts
+ *   die_xchg_return   : owner: results + hit flags -> each source's return window
+ *   die_xchg_scatter  : source: return window -> out / hit in request order (requests routed to None get zeros)
+ * ------------------------------------------------------------------------------------------ */
+die_status_t die_xchg_dispatch(const uint32_t* digests, const float* payload, const int32_t* perm,
+                               const int64_t* offsets, int32_t B, int32_t dim, int32_t world, int32_t rank, int32_t cap,
+                               void* const* peer_rows /*[host]*/, void* const* peer_counts /*[host]*/,
+                               die_stream_t stream);
+die_status_t die_xchg_compact(const float* rows, const int32_t* counts, int32_t world, int32_t cap, int32_t dim,
+                              uint32_t* digests_out, float* payload_out, uint32_t* n_out, int32_t* prefix_out,
+                              die_stream_t stream);
+die_status_t die_xchg_return(const float* out, const uint8_t* hit, const int32_t* prefix, int32_t world, int32_t rank,
+                             int32_t cap, int32_t dim_out, void* const* peer_back /*[host]*/, die_stream_t stream);
+die_status_t die_xchg_scatter(const float* back, const int32_t* perm, const int64_t* offsets, int32_t B, int32_t world,
+                              int32_t cap, int32_t dim_out, float* out, uint8_t* hit, die_stream_t stream);
+
 /* A queue of n flushed batches in one call (each batch is still one pass of the path, applied strictly in
  * order): batch j reads key_bytes + j*key_bytes_stride, key_off + j*key_off_stride (0 = shared offsets),
  * payload + j*B*dim_in; device form writes out + (j % out_ring)*B*dim_out and hit_out + (j % out_ring)*B. */

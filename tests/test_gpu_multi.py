@@ -24,7 +24,7 @@ def test_bucket_by_shard_is_a_stable_partition(B, n):
     assert offsets.cpu().tolist() == [0] + np.cumsum(counts).tolist()
 
 
-def _worker(rank, world, port, ret):
+def _worker(rank, world, port, ret, peer=False):
     sys.path[:0] = [ROOT, os.path.join(ROOT, "distributed-inference-engine_b200")]
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
@@ -32,14 +32,15 @@ def _worker(rank, world, port, ret):
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
         from die import ops
-        from die.exchange import ShardedDispatcher
+        from die.exchange import PeerDispatcher, ShardedDispatcher
         from oracle import models
         from oracle.pipeline import OraclePipeline
         B, D, steps, max_size, ttl = 1024, 128, 8, 3000, 7.0
         rng = np.random.default_rng(5)
         w = (rng.standard_normal((D, D)) / np.sqrt(D)).astype(np.float32)
         b = rng.standard_normal(D).astype(np.float32)
-        disp = ShardedDispatcher(world, rank, max_size, B, D, w, b, ttl, model="linear")
+        cls = PeerDispatcher if peer else ShardedDispatcher
+        disp = cls(world, rank, max_size, B, D, w, b, ttl, model="linear")
 
         def fn(rows):
             y = models.linear_f64(np.stack(rows), w, b) if rows else []
@@ -66,11 +67,12 @@ def _worker(rank, world, port, ret):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (run with gpurun --gpus 2)")
-def test_two_gpu_sharded_dispatch_matches_oracle():
+@pytest.mark.parametrize("peer", [False, True], ids=["nccl_all_to_all", "nvlink_peer_stores"])
+def test_two_gpu_sharded_dispatch_matches_oracle(peer):
     import torch.multiprocessing as mp
     world = 2
-    port = 29600 + (os.getpid() % 2000)
+    port = 29600 + (os.getpid() % 2000) + (7 if peer else 0)
     with mp.Manager() as m:
         ret = m.dict()
-        mp.spawn(_worker, args=(world, port, ret), nprocs=world, join=True)
+        mp.spawn(_worker, args=(world, port, ret, peer), nprocs=world, join=True)
         assert dict(ret) == {0: "ok", 1: "ok"}
