@@ -241,6 +241,8 @@ def main():
         n = kd.shape[0]
         if runner is None:  # one C-ABI call submits the whole queue (each batch is still its own pass)
             pipe.run_device_many(kd, off_d, xd, now0, DT, out_ring, hit_ring)
+        elif hasattr(runner, "step_many"):
+            runner.step_many(kd, off_d, xd, now0, DT, out_ring, hit_ring)
         else:
             for i in range(n):
                 runner.step(ops.KeyBatch(kd[i], off_d), xd[i], now0 + i * DT, out_ring[i % RING], hit_ring[i % RING])
@@ -317,7 +319,7 @@ def main():
 
     # ---- per-stage device time (CUDA events on the launching stream) and roofline -------------------------------
     stages, roofline = {}, None
-    if world == 1:
+    if world == 1 or os.environ.get("DIE_BENCH_PROFILE_ALL"):
         n_prof = min(K, 50)
         _, keys, _, x = make_batches(rng, n_prof)
         kd2, xd2 = to_device(keys, x)

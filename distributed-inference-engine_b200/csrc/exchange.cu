@@ -16,6 +16,8 @@
 // process_exchange applies.
 #include "common.cuh"
 
+struct die_pipeline;
+
 namespace die {
 
 constexpr int XCHG_MAX_WORLD = 16;
@@ -209,5 +211,182 @@ extern "C" die_status_t die_xchg_scatter(const float* back, const int32_t* perm,
     const int vout = dim_out / 4;
     DIE_LAUNCH(ST_XCHG, s, xchg_scatter_kernel<<<grid_for_vectors((long long)B * (vout + 1)), 256, 0, s>>>(
         reinterpret_cast<const int4*>(back), perm, offsets, B, world, cap, vout, reinterpret_cast<int4*>(out), hit));
+    return DIE_OK;
+}
+
+// ================================================================================================
+// One call per flushed batch: the whole sharded step enqueued from C (route, bucket, dispatch, barrier,
+// compact, owner pipeline, return, barrier, scatter) so that the host cost is a handful of launches.
+// ================================================================================================
+namespace die {
+
+// Cross-GPU barrier on flags inside the symmetric window: rank r stores `epoch` into flag[r] of every peer
+// and waits until all of its own flags reach `epoch`.  One rank per GPU (never launch two ranks' barriers on
+// the same device: they would wait on each other inside one GPU).  Gives up after ~4 s and reports.
+__global__ void xchg_barrier_kernel(PeerPtrs flags, unsigned int* my_flags, int world, int rank, unsigned int epoch,
+                                    unsigned int* error_flag) {
+    const int p = threadIdx.x;
+    if (p >= world) return;
+    __threadfence_system();
+    unsigned int* dst = static_cast<unsigned int*>(flags.p[p]) + rank;
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst), "r"(epoch) : "memory");
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+        unsigned int v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(my_flags + p) : "memory");
+        if ((int)(v - epoch) >= 0) break;
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t - t0 > 4000000000ull) {
+            *error_flag = 1u;
+            break;
+        }
+    }
+}
+
+}  // namespace die
+
+struct die_xchg {
+    int world, rank, cap, dim;
+    PeerPtrs rows, back, counts, flags;
+    float* my_rows;
+    float* my_back;
+    int32_t* my_cnt;
+    unsigned int* my_flags;
+    die_pipeline_t* pipe;
+    int32_t* shard;
+    uint32_t* digests;
+    int64_t* offsets;
+    int32_t* perm;
+    int32_t* pos;
+    uint32_t* recv_dig;
+    float* recv_pay;
+    float* recv_out;
+    uint8_t* recv_hit;
+    uint32_t* n_dev;
+    int32_t* prefix;
+    unsigned int* error_flag;
+    unsigned int epoch;
+};
+
+static size_t xchg_rows_bytes(int world, int cap, int dim) { return (size_t)world * cap * (dim + 4) * sizeof(float); }
+
+extern "C" uint64_t die_xchg_window_bytes(int32_t world, int32_t cap, int32_t dim) {
+    // receive rows + return rows + counts + barrier flags
+    return 2 * xchg_rows_bytes(world, cap, dim) + 256 + 256;
+}
+
+extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap, int32_t dim, die_pipeline_t* pipe,
+                                        void* const* peer_windows, die_xchg_t** out) {
+    if (!out || !pipe || !peer_windows || world < 1 || world > XCHG_MAX_WORLD || rank < 0 || rank >= world || cap <= 0 ||
+        dim <= 0 || (dim & 3))
+        DIE_FAIL(DIE_ERR_INVALID, "die_xchg_create: bad arguments");
+    die_xchg* x = new die_xchg();
+    memset(x, 0, sizeof(*x));
+    x->world = world;
+    x->rank = rank;
+    x->cap = cap;
+    x->dim = dim;
+    x->pipe = pipe;
+    const size_t rb = xchg_rows_bytes(world, cap, dim);
+    for (int i = 0; i < XCHG_MAX_WORLD; ++i) {
+        char* base = i < world ? static_cast<char*>(peer_windows[i]) : nullptr;
+        if (i < world && !base) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_create: null window for rank %d", i);
+        x->rows.p[i] = base;
+        x->back.p[i] = base ? base + rb : nullptr;
+        x->counts.p[i] = base ? base + 2 * rb : nullptr;
+        x->flags.p[i] = base ? base + 2 * rb + 256 : nullptr;
+    }
+    x->my_rows = static_cast<float*>(x->rows.p[rank]);
+    x->my_back = static_cast<float*>(x->back.p[rank]);
+    x->my_cnt = static_cast<int32_t*>(x->counts.p[rank]);
+    x->my_flags = static_cast<unsigned int*>(x->flags.p[rank]);
+    const size_t bmax = (size_t)world * cap;
+    DIE_CUDA(cudaMalloc(&x->shard, cap * sizeof(int32_t)));
+    DIE_CUDA(cudaMalloc(&x->digests, (size_t)cap * 16));
+    DIE_CUDA(cudaMalloc(&x->offsets, (world + 2) * sizeof(int64_t)));
+    DIE_CUDA(cudaMalloc(&x->perm, cap * sizeof(int32_t)));
+    DIE_CUDA(cudaMalloc(&x->pos, cap * sizeof(int32_t)));
+    DIE_CUDA(cudaMalloc(&x->recv_dig, bmax * 16));
+    DIE_CUDA(cudaMalloc(&x->recv_pay, bmax * dim * sizeof(float)));
+    DIE_CUDA(cudaMalloc(&x->recv_out, bmax * dim * sizeof(float)));
+    DIE_CUDA(cudaMalloc(&x->recv_hit, bmax));
+    DIE_CUDA(cudaMalloc(&x->n_dev, sizeof(uint32_t)));
+    DIE_CUDA(cudaMalloc(&x->prefix, (world + 1) * sizeof(int32_t)));
+    DIE_CUDA(cudaMalloc(&x->error_flag, sizeof(unsigned int)));
+    DIE_CUDA(cudaMemset(x->error_flag, 0, sizeof(unsigned int)));
+    *out = x;
+    return DIE_OK;
+}
+
+extern "C" die_status_t die_xchg_destroy(die_xchg_t* x) {
+    if (!x) return DIE_OK;
+    void* bufs[] = {x->shard, x->digests, x->offsets, x->perm, x->pos, x->recv_dig, x->recv_pay, x->recv_out,
+                    x->recv_hit, x->n_dev, x->prefix, x->error_flag};
+    for (void* b : bufs) cudaFree(b);
+    delete x;
+    return DIE_OK;
+}
+
+static die_status_t xchg_barrier(die_xchg* x, cudaStream_t s) {
+    x->epoch += 1;
+    DIE_LAUNCH(ST_XCHG, s, xchg_barrier_kernel<<<1, 32, 0, s>>>(x->flags, x->my_flags, x->world, x->rank, x->epoch, x->error_flag));
+    return DIE_OK;
+}
+
+// One flushed batch ingested on this rank; results in request order.  Every rank of the group must make the
+// same sequence of calls (the barriers inside are collective).
+extern "C" die_status_t die_xchg_step(die_xchg_t* x, const uint8_t* key_bytes, const int64_t* key_off, int32_t B,
+                                      const float* payload, double now, float* out, uint8_t* hit_out,
+                                      int32_t* shard_out, die_stream_t stream) {
+    if (!x || B < 0 || B > x->cap) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_step: B must be in [0, cap]");
+    if (!key_off || !payload || !out || !hit_out) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_step: null buffer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int W = x->world, D = x->dim, vdim = D / 4;
+    int32_t* shard = shard_out ? shard_out : x->shard;
+    DIE_TRY(die_route_md5(key_bytes, key_off, B, W, nullptr, nullptr, 0, 0, shard, x->digests, nullptr, stream));
+    DIE_TRY(die_bucket_by_shard(shard, B, W, x->offsets, x->perm, x->pos, stream));
+    DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_vectors((long long)B * (vdim + 1)), 256, 0, s>>>(
+        reinterpret_cast<const int4*>(x->digests), reinterpret_cast<const int4*>(payload), x->perm, x->offsets, B, vdim, W,
+        x->rank, x->cap, x->rows, x->counts));
+    DIE_TRY(xchg_barrier(x, s));  // every rank's rows have landed in their owners' windows
+    DIE_LAUNCH(ST_XCHG, s, xchg_compact_kernel<<<grid_for_vectors((long long)2 * x->cap * (vdim + 1)), 256, 0, s>>>(
+        reinterpret_cast<const int4*>(x->my_rows), x->my_cnt, W, x->cap, vdim, reinterpret_cast<int4*>(x->recv_dig),
+        reinterpret_cast<int4*>(x->recv_pay), x->n_dev, x->prefix));
+    DIE_TRY(die_pipeline_run_owner_device_n(x->pipe, x->recv_dig, W * x->cap, x->n_dev, x->recv_pay, now, x->recv_out,
+                                            x->recv_hit, stream));
+    DIE_LAUNCH(ST_XCHG, s, xchg_return_kernel<<<grid_for_vectors((long long)2 * x->cap * (vdim + 1)), 256, 0, s>>>(
+        reinterpret_cast<const int4*>(x->recv_out), x->recv_hit, x->prefix, W, x->rank, x->cap, vdim, x->back));
+    DIE_TRY(xchg_barrier(x, s));  // every owner's results are back in the sources' windows
+    DIE_LAUNCH(ST_XCHG, s, xchg_scatter_kernel<<<grid_for_vectors((long long)B * (vdim + 1)), 256, 0, s>>>(
+        reinterpret_cast<const int4*>(x->my_back), x->perm, x->offsets, B, W, x->cap, vdim, reinterpret_cast<int4*>(out),
+        hit_out));
+    return DIE_OK;
+}
+
+extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, const uint8_t* key_bytes,
+                                           int64_t key_bytes_stride, const int64_t* key_off, int64_t key_off_stride,
+                                           int32_t B, const float* payload, double now0, double now_step, float* out,
+                                           uint8_t* hit_out, int32_t out_ring, die_stream_t stream) {
+    if (!x || n_batches < 0 || out_ring < 1) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_step_many: bad arguments");
+    const size_t row = (size_t)B * x->dim;
+    for (int32_t j = 0; j < n_batches; ++j) {
+        const int r = j % out_ring;
+        DIE_TRY(die_xchg_step(x, key_bytes + (size_t)j * key_bytes_stride, key_off + (size_t)j * key_off_stride, B,
+                              payload + (size_t)j * row, now0 + j * now_step, out + (size_t)r * row,
+                              hit_out + (size_t)r * B, nullptr, stream));
+    }
+    return DIE_OK;
+}
+
+// Synchronises and reports whether a barrier of this context ever timed out (a peer stopped calling).
+extern "C" die_status_t die_xchg_check_sync(die_xchg_t* x, die_stream_t stream) {
+    if (!x) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_check_sync: null context");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    unsigned int e = 0;
+    DIE_CUDA(cudaMemcpyAsync(&e, x->error_flag, sizeof(e), cudaMemcpyDeviceToHost, s));
+    DIE_CUDA(cudaStreamSynchronize(s));
+    if (e) DIE_FAIL(DIE_ERR_CUDA, "die_xchg: a cross-GPU barrier timed out (a peer rank stopped making calls)");
     return DIE_OK;
 }

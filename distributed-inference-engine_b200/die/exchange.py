@@ -131,13 +131,15 @@ class PeerDispatcher:
     """The same dispatch over NVLink by direct peer stores (csrc/exchange.cu): no collective, no host sync.
 
     Every rank owns a receive window and a return window inside one symmetric allocation
-    (torch.distributed._symmetric_memory); `die_xchg_dispatch` packs and writes each request row straight
-    into its owner's window, a device-side barrier separates the phases, the owner runs the fused pipeline on
-    a batch whose size it only knows on the device, and `die_xchg_return` / `die_xchg_scatter` bring the
-    results back to request order.  Owners see the sources in rank order (same contract as ShardedDispatcher)."""
+    (torch.distributed._symmetric_memory); the dispatch kernel packs and writes each request row straight into
+    its owner's window, a flag barrier inside the window separates the phases, the owner runs the fused
+    pipeline on a batch whose size it only knows on the device, and the return / scatter kernels bring the
+    results back to request order.  Owners see the sources in rank order (same contract as ShardedDispatcher).
+    One `die_xchg_step` call enqueues the whole step; `single_call=False` drives the same kernels phase by
+    phase from Python with torch's symmetric-memory barrier instead (used by the tests as a cross-check)."""
 
     def __init__(self, world: int, rank: int, kv_max_size: int, max_batch: int, dim: int, weight, bias, default_ttl,
-                 model: str = "linear_tf32", group=None):
+                 model: str = "linear_tf32", group=None, single_call: bool = True):
         import ctypes
         import torch.distributed._symmetric_memory as symm
         from . import _cabi, ops
@@ -145,26 +147,27 @@ class PeerDispatcher:
         self._cabi, self.ops, self._ct = _cabi, ops, ctypes
         self.lib = _cabi.require_cuda()
         self.world, self.rank, self.B, self.dim = world, rank, max_batch, dim
+        self.single_call = single_call
         self.dev = torch.device("cuda", torch.cuda.current_device())
         self.cap = max_batch
         self.bmax = world * self.cap  # the most an owner can receive in one step
         self.pipe = DispatchPipeline(kv_max_size, self.bmax, dim, dim, model, weight, bias, default_ttl)
-        row_in, row_out = dim + 4, dim + 4
-        n_rows = world * self.cap
-        words = n_rows * row_in + n_rows * row_out + 64
-        self.sym = symm.empty(words, dtype=torch.float32, device=self.dev)
+        nbytes = int(self.lib.die_xchg_window_bytes(world, self.cap, dim))
+        self.sym = symm.empty((nbytes + 3) // 4, dtype=torch.float32, device=self.dev)
         self.sym.zero_()
+        torch.cuda.synchronize()
         self.hdl = symm.rendezvous(self.sym, group if group is not None else dist.group.WORLD)
         base = [int(p) for p in self.hdl.buffer_ptrs]
-        off_back = n_rows * row_in * 4
-        off_cnt = off_back + n_rows * row_out * 4
         arr = ctypes.c_void_p * world
-        self.peer_rows = arr(*[b for b in base])
-        self.peer_back = arr(*[b + off_back for b in base])
-        self.peer_cnt = arr(*[b + off_cnt for b in base])
-        self.my_rows = base[rank]
-        self.my_back = base[rank] + off_back
-        self.my_cnt = base[rank] + off_cnt
+        self.peer_windows = arr(*base)
+        rb = world * self.cap * (dim + 4) * 4
+        self.peer_rows = arr(*base)
+        self.peer_back = arr(*[b + rb for b in base])
+        self.peer_cnt = arr(*[b + 2 * rb for b in base])
+        self.my_rows, self.my_back, self.my_cnt = base[rank], base[rank] + rb, base[rank] + 2 * rb
+        h = ctypes.c_void_p()
+        _cabi.check(self.lib.die_xchg_create(world, rank, self.cap, dim, self.pipe._h, self.peer_windows, ctypes.byref(h)))
+        self._x = h.value
         e = lambda shape, dt: torch.empty(shape, dtype=dt, device=self.dev)  # noqa: E731
         self.recv_dig = e((self.bmax, 4), torch.int32)
         self.recv_pay = e((self.bmax, dim), torch.float32)
@@ -174,11 +177,24 @@ class PeerDispatcher:
         self.prefix = torch.zeros(world + 1, dtype=torch.int32, device=self.dev)
         torch.cuda.synchronize()
         self.hdl.barrier(channel=0)
+        torch.cuda.synchronize()
+
+    def __del__(self):
+        if getattr(self, "_x", None):
+            self.lib.die_xchg_destroy(self._x)
+            self._x = None
 
     def step(self, keys, payload: torch.Tensor, now: float, out: Optional[torch.Tensor] = None,
              hit: Optional[torch.Tensor] = None):
         lib, check, ptr, st = self.lib, self._cabi.check, self._cabi.ptr, self._cabi.stream_ptr
         W, B, D = self.world, payload.shape[0], self.dim
+        out = torch.empty((B, D), dtype=torch.float32, device=self.dev) if out is None else out
+        hit = torch.empty(B, dtype=torch.uint8, device=self.dev) if hit is None else hit
+        if self.single_call:
+            shard = torch.empty(B, dtype=torch.int32, device=self.dev)
+            check(lib.die_xchg_step(self._x, ptr(keys.key_bytes), ptr(keys.key_off), B, ptr(payload), now, ptr(out),
+                                    ptr(hit), ptr(shard), st()))
+            return out, hit, shard
         shard, digests, _ = self.ops.route_md5(keys, W)
         offsets, perm, _pos = self.ops.bucket_by_shard(shard, W)
         check(lib.die_xchg_dispatch(ptr(digests), ptr(payload), ptr(perm), ptr(offsets), B, D, W, self.rank, self.cap,
@@ -191,7 +207,19 @@ class PeerDispatcher:
         check(lib.die_xchg_return(ptr(self.recv_out), ptr(self.recv_hit), ptr(self.prefix), W, self.rank, self.cap, D,
                                   self.peer_back, st()))
         self.hdl.barrier(channel=0)  # every owner's results are back in the sources' windows
-        out = torch.empty((B, D), dtype=torch.float32, device=self.dev) if out is None else out
-        hit = torch.empty(B, dtype=torch.uint8, device=self.dev) if hit is None else hit
         check(lib.die_xchg_scatter(self.my_back, ptr(perm), ptr(offsets), B, W, self.cap, D, ptr(out), ptr(hit), st()))
         return out, hit, shard
+
+    def step_many(self, key_bytes: torch.Tensor, key_off: torch.Tensor, payload: torch.Tensor, now0: float,
+                  now_step: float, out: torch.Tensor, hit: torch.Tensor) -> None:
+        """A queue of flushed batches (key_bytes [n, stride], key_off [B+1] shared or [n, B+1], payload [n, B, dim]);
+        out [ring, B, dim] / hit [ring, B] are reused round-robin.  Every rank must submit the same n."""
+        n, B = payload.shape[0], payload.shape[1]
+        shared = key_off.dim() == 1
+        ptr = self._cabi.ptr
+        self._cabi.check(self.lib.die_xchg_step_many(self._x, n, ptr(key_bytes), key_bytes.stride(0), ptr(key_off),
+                                                     0 if shared else key_off.stride(0), B, ptr(payload), now0, now_step,
+                                                     ptr(out), ptr(hit), out.shape[0], self._cabi.stream_ptr()))
+
+    def check(self) -> None:
+        self._cabi.check(self.lib.die_xchg_check_sync(self._x, self._cabi.stream_ptr()))

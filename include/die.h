@@ -291,6 +291,25 @@ die_status_t die_xchg_return(const float* out, const uint8_t* hit, const int32_t
 die_status_t die_xchg_scatter(const float* back, const int32_t* perm, const int64_t* offsets, int32_t B, int32_t world,
                               int32_t cap, int32_t dim_out, float* out, uint8_t* hit, die_stream_t stream);
 
+/* The whole sharded step in one call (same kernels as above plus a flag barrier inside the window), so that the
+ * host pays a handful of launches per flushed batch.  The caller allocates one symmetric window of
+ * die_xchg_window_bytes() per rank (zero-filled), exchanges the addresses and passes all of them as
+ * peer_windows [host, world entries].  Every rank must make the same sequence of calls: the barriers are collective.
+ * Requires one rank per GPU.  die_xchg_check_sync reports a barrier that timed out. */
+typedef struct die_xchg die_xchg_t;
+uint64_t die_xchg_window_bytes(int32_t world, int32_t cap, int32_t dim);
+die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap, int32_t dim, die_pipeline_t* pipe,
+                             void* const* peer_windows /*[host]*/, die_xchg_t** out);
+die_status_t die_xchg_destroy(die_xchg_t* x);
+die_status_t die_xchg_step(die_xchg_t* x, const uint8_t* key_bytes, const int64_t* key_off, int32_t B,
+                           const float* payload, double now, float* out, uint8_t* hit_out, int32_t* shard_out,
+                           die_stream_t stream);
+die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, const uint8_t* key_bytes, int64_t key_bytes_stride,
+                                const int64_t* key_off, int64_t key_off_stride, int32_t B, const float* payload,
+                                double now0, double now_step, float* out, uint8_t* hit_out, int32_t out_ring,
+                                die_stream_t stream);
+die_status_t die_xchg_check_sync(die_xchg_t* x, die_stream_t stream);
+
 /* A queue of n flushed batches in one call (each batch is still one pass of the path, applied strictly in
  * order): batch j reads key_bytes + j*key_bytes_stride, key_off + j*key_off_stride (0 = shared offsets),
  * payload + j*B*dim_in; device form writes out + (j % out_ring)*B*dim_out and hit_out + (j % out_ring)*B. */

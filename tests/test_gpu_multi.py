@@ -24,7 +24,7 @@ def test_bucket_by_shard_is_a_stable_partition(B, n):
     assert offsets.cpu().tolist() == [0] + np.cumsum(counts).tolist()
 
 
-def _worker(rank, world, port, ret, peer=False):
+def _worker(rank, world, port, ret, mode="nccl"):
     sys.path[:0] = [ROOT, os.path.join(ROOT, "distributed-inference-engine_b200")]
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
@@ -39,8 +39,10 @@ def _worker(rank, world, port, ret, peer=False):
         rng = np.random.default_rng(5)
         w = (rng.standard_normal((D, D)) / np.sqrt(D)).astype(np.float32)
         b = rng.standard_normal(D).astype(np.float32)
-        cls = PeerDispatcher if peer else ShardedDispatcher
-        disp = cls(world, rank, max_size, B, D, w, b, ttl, model="linear")
+        if mode == "nccl":
+            disp = ShardedDispatcher(world, rank, max_size, B, D, w, b, ttl, model="linear")
+        else:
+            disp = PeerDispatcher(world, rank, max_size, B, D, w, b, ttl, model="linear", single_call=mode == "peer_one_call")
 
         def fn(rows):
             y = models.linear_f64(np.stack(rows), w, b) if rows else []
@@ -61,18 +63,20 @@ def _worker(rank, world, port, ret, peer=False):
             assert np.all(np.abs(out.cpu().numpy() - np.stack(want["out"])) <= 1e-5 * np.abs(np.stack(want["out"])) + 2e-4)
         st, mine = disp.pipe.kv.stats(), ref.state()[rank]
         assert (st["hits"], st["misses"], st["evictions"], st["size"]) == (mine["hits"], mine["misses"], mine["evictions"], mine["size"])
+        if mode != "nccl":
+            disp.check()
         ret[rank] = "ok"
     finally:
         dist.destroy_process_group()
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (run with gpurun --gpus 2)")
-@pytest.mark.parametrize("peer", [False, True], ids=["nccl_all_to_all", "nvlink_peer_stores"])
-def test_two_gpu_sharded_dispatch_matches_oracle(peer):
+@pytest.mark.parametrize("mode", ["nccl", "peer_phases", "peer_one_call"])
+def test_two_gpu_sharded_dispatch_matches_oracle(mode):
     import torch.multiprocessing as mp
     world = 2
-    port = 29600 + (os.getpid() % 2000) + (7 if peer else 0)
+    port = 29600 + (os.getpid() % 2000) + len(mode)
     with mp.Manager() as m:
         ret = m.dict()
-        mp.spawn(_worker, args=(world, port, ret, peer), nprocs=world, join=True)
+        mp.spawn(_worker, args=(world, port, ret, mode), nprocs=world, join=True)
         assert dict(ret) == {0: "ok", 1: "ok"}
