@@ -233,3 +233,72 @@ def test_contains_delete_len_clear_batched():
     assert dkv.stats()["size"] == 0 and dkv.len_sync(0.0)[0] == 0
     hit, _ = dkv.get_batch(md5_words(keys[:4]), 0.0)
     assert hit.tolist() == [0, 0, 0, 0]
+
+
+def test_c4_full_size_probe_and_fill_by_construction():
+    """BASELINE.json configs[3]: 10M-entry table (LRU, default_ttl 300 s), probe batch 65536 at 90 % resident keys,
+    then set the misses.  Too big for the Python oracle, so the expected result is built into the inputs:
+    entries are inserted in id order (so LRU order == id order), the oldest 1 % are created 301 s before the
+    probe (expired at probe time, strict '>'), the rest 1 s before."""
+    from die import ops
+    from die.kvstore import DeviceKV
+    import bench
+    N, B = 10_000_000, 65536
+    kv = DeviceKV(N, 300.0)
+
+    def dig(ids):
+        kb = torch.from_numpy(bench.key_bytes_of(ids).reshape(-1)).cuda()
+        off = torch.arange(ids.size + 1, dtype=torch.int64, device="cuda") * 15
+        return ops.route_md5(ops.KeyBatch(kb, off), 1)[1]
+
+    n_old = N // 100
+    chunk = 1 << 20
+    for a in range(0, N, chunk):
+        m = min(chunk, N - a)
+        ids = np.arange(a, a + m, dtype=np.int64)
+        # ids < n_old are created at t=0, the others at t=300 (chunks never straddle: n_old < chunk handled by split)
+        if a < n_old < a + m:
+            cut = n_old - a
+            kv.set_batch(dig(ids[:cut]), torch.from_numpy(ids[:cut]).cuda(), 0.0)
+            kv.set_batch(dig(ids[cut:]), torch.from_numpy(ids[cut:]).cuda(), 300.0)
+        else:
+            kv.set_batch(dig(ids), torch.from_numpy(ids).cuda(), 0.0 if a + m <= n_old else 300.0)
+    assert kv.sync_status()[0] == 0
+    st = kv.stats()
+    assert (st["size"], st["evictions"]) == (N, 0)
+
+    rng = np.random.default_rng(4)
+    resident = rng.integers(0, N, int(B * 0.9))
+    absent = rng.integers(N, 2 * N, B - resident.size)
+    ids = np.concatenate([resident, absent])
+    rng.shuffle(ids)
+    now = 301.0                                   # age of the old 1 %: 301 s > ttl 300 s -> expired; others: 1 s
+    hit, value = kv.get_batch(dig(ids), now)
+    hit, value = hit.cpu().numpy(), value.cpu().numpy()
+    want_hit = (ids < N) & (ids >= n_old)
+    assert np.array_equal(hit == 1, want_hit)
+    assert np.array_equal(value[want_hit], ids[want_hit])                       # the stored handle is the id
+    expired_ids = np.unique(ids[(ids < n_old)])
+    assert int((hit == 2).sum()) == expired_ids.size                          # each expired entry deleted exactly once
+    st = kv.stats()
+    assert st["hits"] == int(want_hit.sum()) and st["misses"] == B - int(want_hit.sum())
+    assert st["size"] == N - expired_ids.size
+
+    # fill: set every miss (request order, duplicates included) -> the table is full again after expired.size inserts,
+    # every further new key evicts the LRU head: untouched ids in increasing order (hits moved to MRU, expired gone)
+    miss_ids = ids[~want_hit]
+    kv.set_batch(dig(miss_ids), torch.from_numpy(miss_ids).cuda(), now)
+    status, _, slow = kv.sync_status()
+    assert status == 0 and slow == 0
+    n_new = np.unique(miss_ids).size
+    want_evictions = n_new - expired_ids.size
+    st = kv.stats()
+    assert st["size"] == N and st["evictions"] == want_evictions
+    touched = np.zeros(N, dtype=bool)
+    touched[ids[want_hit]] = True
+    touched[:n_old][np.isin(np.arange(n_old), expired_ids)] = True             # deleted, not evictable
+    untouched_order = np.nonzero(~touched)[0]                                   # LRU order of the evictable entries
+    victims, survivors = untouched_order[:want_evictions], untouched_order[want_evictions:want_evictions + 4096]
+    gone, _ = kv.contains_batch(dig(victims[-4096:]), now)
+    kept, _ = kv.contains_batch(dig(survivors), now)
+    assert not gone.any() and bool((kept.cpu().numpy()[survivors >= n_old] == 1).all())

@@ -80,3 +80,53 @@ def test_two_gpu_sharded_dispatch_matches_oracle(mode):
         ret = m.dict()
         mp.spawn(_worker, args=(world, port, ret, mode), nprocs=world, join=True)
         assert dict(ret) == {0: "ok", 1: "ok"}
+
+
+def _ragged_worker(rank, world, port, ret):
+    """BASELINE.json configs[2]: ragged 16..2048-element payloads, max_batch 256, hash-sharded with the all-to-all
+    dispatch; echo model (the reference's).  Batcher pack -> sharded dispatch -> unpack, vs the oracle."""
+    sys.path[:0] = [ROOT, os.path.join(ROOT, "distributed-inference-engine_b200")]
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from die import ops
+        from die.batcher import PackedBatch, pack_requests, unpack_results
+        from die.exchange import ShardedDispatcher
+        from oracle.pipeline import OraclePipeline
+        B, Lpad, steps, max_size = 256, 2048, 6, 400
+        rng = np.random.default_rng(17)
+        disp = ShardedDispatcher(world, rank, max_size, B, Lpad, None, None, 50.0, model="echo")
+        ref = OraclePipeline(world, max_size, 50.0, lambda rows: list(rows))
+        now = 1.0
+        for _ in range(steps):
+            now += 1.0
+            per_rank = []
+            for _r in range(world):
+                keys = ["sess-%06d" % i for i in rng.integers(0, 700, B)]
+                pays = [rng.standard_normal(int(n)).astype(np.float32) for n in rng.integers(16, 2049, B)]
+                per_rank.append((keys, pays))
+            keys, pays = per_rank[rank]
+            packed = pack_requests(pays, Lpad=Lpad)                     # K4: ragged -> [256, 2048] zero padded
+            out, hit, shard = disp.step(ops.KeyBatch.from_strings(keys), packed.data, now)
+            # a hit returns the cached result of an EARLIER request with the same key: its length is the cached row's
+            want = ref.process_exchange(per_rank, now)[rank]
+            lens = [len(w) for w in want["out"]]
+            got = unpack_results(PackedBatch(out, None, lens))          # K5: padded rows -> ragged results
+            assert shard.tolist() == want["shard"] and hit.tolist() == want["hit"]
+            for g, w_ in zip(got, want["out"]):
+                assert np.array_equal(g.cpu().numpy(), w_)
+        ret[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (run with gpurun --gpus 2)")
+def test_two_gpu_ragged_c3_dispatch_matches_oracle():
+    import torch.multiprocessing as mp
+    port = 29700 + (os.getpid() % 2000)
+    with mp.Manager() as m:
+        ret = m.dict()
+        mp.spawn(_ragged_worker, args=(2, port, ret), nprocs=2, join=True)
+        assert dict(ret) == {0: "ok", 1: "ok"}
