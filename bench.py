@@ -30,6 +30,7 @@ import numpy as np  # noqa: E402
 B, D = 4096, 128
 KV_MAX, ID_SPACE, TTL = 1 << 20, 10 ** 7, 300.0
 KEY_LEN = 15
+WORLD = int(os.environ.get("WORLD_SIZE", "1"))
 METRIC = "requests/sec, batched route->probe->pack->infer->unpack"
 MODEL = os.environ.get("DIE_BENCH_MODEL", "linear_tf32")  # tcgen05 kind::tf32 GEMM, fp32 accumulate
 
@@ -46,7 +47,8 @@ def key_bytes_of(ids: np.ndarray) -> np.ndarray:
     return out
 
 
-def make_batches(rng, n_batches, id_space=ID_SPACE, payload=True):
+def make_batches(rng, n_batches, id_space=None, payload=True):
+    id_space = id_space or ID_SPACE * WORLD  # weak scaling: the key population grows with the number of shards
     ids = rng.integers(0, id_space, (n_batches, B), dtype=np.int64)
     keys = key_bytes_of(ids.reshape(-1)).reshape(n_batches, B * KEY_LEN)
     off = np.arange(B + 1, dtype=np.int64) * KEY_LEN
@@ -136,9 +138,10 @@ def run_reference(args):
 
 
 def workload_config(n_gpus):
-    return {"workload": "C2: 4096-request flushed batches, key 'user-%010d' (ids uniform in [0,1e7)), 128-dim fp32 "
-                        "payload, mock linear 128->128, LRU+TTL cache of 2^20 entries per GPU (~10% hits, evicting)",
-            "batch": B, "dim": D, "kv_max_size": KV_MAX, "id_space": ID_SPACE, "default_ttl": TTL,
+    return {"workload": "C2: 4096-request flushed batches per GPU, key 'user-%010d' (ids uniform in [0,1e7 x n_gpus)), "
+                        "128-dim fp32 payload, mock linear 128->128, LRU+TTL cache of 2^20 entries per GPU "
+                        "(~10% hits, evicting)",
+            "batch": B, "dim": D, "kv_max_size": KV_MAX, "id_space": ID_SPACE * n_gpus, "default_ttl": TTL,
             "parallelism": f"hash-shard x{n_gpus}", "l2_policy": "every step reads fresh inputs; K steps x 2.2 MB"}
 
 

@@ -61,14 +61,19 @@ xchg_dispatch_kernel(const int4* __restrict__ digests, const int4* __restrict__ 
 // Owner: regions -> contiguous digests / payload in (source rank, request) order + the device-side count.
 __global__ void __launch_bounds__(256)
 xchg_compact_kernel(const int4* __restrict__ rows, const int32_t* __restrict__ counts, int world, int cap, int vdim,
-                    int4* __restrict__ digests_out, int4* __restrict__ payload_out, uint32_t* __restrict__ n_out,
-                    int32_t* __restrict__ prefix_out /*[world+1]*/) {
+                    long long bmax, int4* __restrict__ digests_out, int4* __restrict__ payload_out,
+                    uint32_t* __restrict__ n_out, int32_t* __restrict__ prefix_out /*[world+1]*/,
+                    unsigned int* __restrict__ error_flag) {
     __shared__ long long s_pre[XCHG_MAX_WORLD + 1];
     if (threadIdx.x == 0) {
         long long acc = 0;
         for (int s = 0; s < world; ++s) {
             s_pre[s] = acc;
             acc += counts[s];
+            if (acc > bmax) {  // more than the owner pipeline was sized for (hot-key skew): refuse loudly
+                if (error_flag) *error_flag = 2u;
+                acc = bmax;
+            }
         }
         s_pre[world] = acc;
         if (blockIdx.x == 0) {
@@ -178,13 +183,14 @@ extern "C" die_status_t die_xchg_dispatch(const uint32_t* digests, const float* 
 extern "C" die_status_t die_xchg_compact(const float* rows, const int32_t* counts, int32_t world, int32_t cap, int32_t dim,
                                          uint32_t* digests_out, float* payload_out, uint32_t* n_out, int32_t* prefix_out,
                                          die_stream_t stream) {
+    const long long bmax = (long long)world * cap;
     if (world < 1 || world > XCHG_MAX_WORLD || dim <= 0 || (dim & 3) || cap <= 0)
         DIE_FAIL(DIE_ERR_INVALID, "die_xchg_compact: bad sizes");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int vdim = dim / 4;
     DIE_LAUNCH(ST_XCHG, s, xchg_compact_kernel<<<grid_for_vectors((long long)2 * cap * (vdim + 1)), 256, 0, s>>>(
-        reinterpret_cast<const int4*>(rows), counts, world, cap, vdim, reinterpret_cast<int4*>(digests_out),
-        reinterpret_cast<int4*>(payload_out), n_out, prefix_out));
+        reinterpret_cast<const int4*>(rows), counts, world, cap, vdim, bmax, reinterpret_cast<int4*>(digests_out),
+        reinterpret_cast<int4*>(payload_out), n_out, prefix_out, nullptr));
     return DIE_OK;
 }
 
@@ -249,6 +255,7 @@ __global__ void xchg_barrier_kernel(PeerPtrs flags, unsigned int* my_flags, int 
 
 struct die_xchg {
     int world, rank, cap, dim;
+    int bmax;  // most requests the owner side handles per step (the pipeline's max_batch)
     PeerPtrs rows, back, counts, flags;
     float* my_rows;
     float* my_back;
@@ -277,8 +284,8 @@ extern "C" uint64_t die_xchg_window_bytes(int32_t world, int32_t cap, int32_t di
     return 2 * xchg_rows_bytes(world, cap, dim) + 256 + 256;
 }
 
-extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap, int32_t dim, die_pipeline_t* pipe,
-                                        void* const* peer_windows, die_xchg_t** out) {
+extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap, int32_t dim, int32_t owner_max,
+                                        die_pipeline_t* pipe, void* const* peer_windows, die_xchg_t** out) {
     if (!out || !pipe || !peer_windows || world < 1 || world > XCHG_MAX_WORLD || rank < 0 || rank >= world || cap <= 0 ||
         dim <= 0 || (dim & 3))
         DIE_FAIL(DIE_ERR_INVALID, "die_xchg_create: bad arguments");
@@ -289,6 +296,7 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
     x->cap = cap;
     x->dim = dim;
     x->pipe = pipe;
+    x->bmax = owner_max > 0 && owner_max < world * cap ? owner_max : world * cap;
     const size_t rb = xchg_rows_bytes(world, cap, dim);
     for (int i = 0; i < XCHG_MAX_WORLD; ++i) {
         char* base = i < world ? static_cast<char*>(peer_windows[i]) : nullptr;
@@ -302,7 +310,7 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
     x->my_back = static_cast<float*>(x->back.p[rank]);
     x->my_cnt = static_cast<int32_t*>(x->counts.p[rank]);
     x->my_flags = static_cast<unsigned int*>(x->flags.p[rank]);
-    const size_t bmax = (size_t)world * cap;
+    const size_t bmax = (size_t)x->bmax;
     DIE_CUDA(cudaMalloc(&x->shard, cap * sizeof(int32_t)));
     DIE_CUDA(cudaMalloc(&x->digests, (size_t)cap * 16));
     DIE_CUDA(cudaMalloc(&x->offsets, (world + 2) * sizeof(int64_t)));
@@ -352,9 +360,9 @@ extern "C" die_status_t die_xchg_step(die_xchg_t* x, const uint8_t* key_bytes, c
         x->rank, x->cap, x->rows, x->counts));
     DIE_TRY(xchg_barrier(x, s));  // every rank's rows have landed in their owners' windows
     DIE_LAUNCH(ST_XCHG, s, xchg_compact_kernel<<<grid_for_vectors((long long)2 * x->cap * (vdim + 1)), 256, 0, s>>>(
-        reinterpret_cast<const int4*>(x->my_rows), x->my_cnt, W, x->cap, vdim, reinterpret_cast<int4*>(x->recv_dig),
-        reinterpret_cast<int4*>(x->recv_pay), x->n_dev, x->prefix));
-    DIE_TRY(die_pipeline_run_owner_device_n(x->pipe, x->recv_dig, W * x->cap, x->n_dev, x->recv_pay, now, x->recv_out,
+        reinterpret_cast<const int4*>(x->my_rows), x->my_cnt, W, x->cap, vdim, (long long)x->bmax,
+        reinterpret_cast<int4*>(x->recv_dig), reinterpret_cast<int4*>(x->recv_pay), x->n_dev, x->prefix, x->error_flag));
+    DIE_TRY(die_pipeline_run_owner_device_n(x->pipe, x->recv_dig, x->bmax, x->n_dev, x->recv_pay, now, x->recv_out,
                                             x->recv_hit, stream));
     DIE_LAUNCH(ST_XCHG, s, xchg_return_kernel<<<grid_for_vectors((long long)2 * x->cap * (vdim + 1)), 256, 0, s>>>(
         reinterpret_cast<const int4*>(x->recv_out), x->recv_hit, x->prefix, W, x->rank, x->cap, vdim, x->back));
@@ -387,6 +395,7 @@ extern "C" die_status_t die_xchg_check_sync(die_xchg_t* x, die_stream_t stream) 
     unsigned int e = 0;
     DIE_CUDA(cudaMemcpyAsync(&e, x->error_flag, sizeof(e), cudaMemcpyDeviceToHost, s));
     DIE_CUDA(cudaStreamSynchronize(s));
+    if (e == 2) DIE_FAIL(DIE_ERR_TOO_LARGE, "die_xchg: an owner received more requests in one step than owner_max");
     if (e) DIE_FAIL(DIE_ERR_CUDA, "die_xchg: a cross-GPU barrier timed out (a peer rank stopped making calls)");
     return DIE_OK;
 }

@@ -75,7 +75,7 @@ SIGNATURES = {
     "die_xchg_return": (c_int32, [P, P, P, c_int32, c_int32, c_int32, c_int32, P, P]),
     "die_xchg_scatter": (c_int32, [P, P, P, c_int32, c_int32, c_int32, c_int32, P, P, P]),
     "die_xchg_window_bytes": (c_uint64, [c_int32, c_int32, c_int32]),
-    "die_xchg_create": (c_int32, [c_int32, c_int32, c_int32, c_int32, P, P, POINTER(c_void_p)]),
+    "die_xchg_create": (c_int32, [c_int32, c_int32, c_int32, c_int32, c_int32, P, P, POINTER(c_void_p)]),
     "die_xchg_destroy": (c_int32, [P]),
     "die_xchg_step": (c_int32, [P, P, P, c_int32, P, c_double, P, P, P, P]),
     "die_xchg_step_many": (c_int32, [P, c_int32, P, c_int64, P, c_int64, c_int32, P, c_double, c_double, P, P, c_int32, P]),

@@ -150,7 +150,9 @@ class PeerDispatcher:
         self.single_call = single_call
         self.dev = torch.device("cuda", torch.cuda.current_device())
         self.cap = max_batch
-        self.bmax = world * self.cap  # the most an owner can receive in one step
+        # hash sharding spreads every batch evenly over the owners: two batches' worth is far beyond any
+        # fluctuation (sigma ~ sqrt(B)); a step that exceeds it raises in check() instead of being truncated silently
+        self.bmax = (min(world, 2) if single_call else world) * self.cap
         self.pipe = DispatchPipeline(kv_max_size, self.bmax, dim, dim, model, weight, bias, default_ttl)
         nbytes = int(self.lib.die_xchg_window_bytes(world, self.cap, dim))
         self.sym = symm.empty((nbytes + 3) // 4, dtype=torch.float32, device=self.dev)
@@ -166,7 +168,8 @@ class PeerDispatcher:
         self.peer_cnt = arr(*[b + 2 * rb for b in base])
         self.my_rows, self.my_back, self.my_cnt = base[rank], base[rank] + rb, base[rank] + 2 * rb
         h = ctypes.c_void_p()
-        _cabi.check(self.lib.die_xchg_create(world, rank, self.cap, dim, self.pipe._h, self.peer_windows, ctypes.byref(h)))
+        _cabi.check(self.lib.die_xchg_create(world, rank, self.cap, dim, self.bmax, self.pipe._h, self.peer_windows,
+                                             ctypes.byref(h)))
         self._x = h.value
         e = lambda shape, dt: torch.empty(shape, dtype=dt, device=self.dev)  # noqa: E731
         self.recv_dig = e((self.bmax, 4), torch.int32)

@@ -298,8 +298,10 @@ die_status_t die_xchg_scatter(const float* back, const int32_t* perm, const int6
  * Requires one rank per GPU.  die_xchg_check_sync reports a barrier that timed out. */
 typedef struct die_xchg die_xchg_t;
 uint64_t die_xchg_window_bytes(int32_t world, int32_t cap, int32_t dim);
-die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap, int32_t dim, die_pipeline_t* pipe,
-                             void* const* peer_windows /*[host]*/, die_xchg_t** out);
+/* owner_max: the most requests one owner handles per step (= max_batch of `pipe`); 0 = world*cap.  Hash sharding
+ * spreads a batch evenly, so 2*cap is ample; a step that exceeds it sets an error die_xchg_check_sync reports. */
+die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap, int32_t dim, int32_t owner_max,
+                             die_pipeline_t* pipe, void* const* peer_windows /*[host]*/, die_xchg_t** out);
 die_status_t die_xchg_destroy(die_xchg_t* x);
 die_status_t die_xchg_step(die_xchg_t* x, const uint8_t* key_bytes, const int64_t* key_off, int32_t B,
                            const float* payload, double now, float* out, uint8_t* hit_out, int32_t* shard_out,
