@@ -273,7 +273,9 @@ def main():
     launches0 = lib.die_launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
+    t_host = time.perf_counter()
     now = run_steps(kd[W:], xd[W:], now)
+    t_host = time.perf_counter() - t_host  # host time to enqueue the queue (no wait on the GPU)
     ev1.record()
     torch.cuda.synchronize()
     if world > 1:
@@ -379,7 +381,8 @@ def main():
                 "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "tf32" if MODEL == "linear_tf32" else "f32",
                 "data": "synthetic", "config": dict(workload_config(world), hit_rate=round(hit_rate, 4), model=MODEL),
-                "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e, "roofline": roofline, "stages": stages,
+                "gpu_launches": int(launches), "host_enqueue_us_per_step": round(1e6 * t_host / K, 2),
+                "clocks": clocks, "e2e": e2e, "roofline": roofline, "stages": stages,
                 "cpu_baseline": cpu}
         print(json.dumps(line))
     if world > 1:

@@ -17,6 +17,7 @@ enum Stage {
 };
 void prof_before(int stage, cudaStream_t s);
 void prof_after(int stage, cudaStream_t s);
+bool prof_active();                   // per-launch events are being recorded: replays from graphs are off
 char* err_buf();                       // thread-local, 512 bytes
 void count_launch(unsigned n = 1);     // gpu_launches accounting for bench.py
 

@@ -14,9 +14,8 @@
 // cap = the ingest batch size, so no bucket can overflow whatever the key distribution or health state.
 // Owners see the sources in rank order, request order kept inside each source: the order the CPU oracle's
 // process_exchange applies.
-#include "common.cuh"
-
-struct die_pipeline;
+#include "pipeline_internal.cuh"
+#include "route_device.cuh"
 
 namespace die {
 
@@ -34,10 +33,11 @@ __device__ __forceinline__ int bucket_of(const long long* off, int world, long l
 
 // PACK + SEND: send position j (bucket order) = request perm[j]; row -> peer window of its owner.
 __global__ void __launch_bounds__(256)
-xchg_dispatch_kernel(const int4* __restrict__ digests, const int4* __restrict__ payload, const int32_t* __restrict__ perm,
+xchg_dispatch_kernel(StepRef sr, const int4* __restrict__ digests, const int32_t* __restrict__ perm,
                      const int64_t* __restrict__ offsets, int B, int vdim /*payload vectors per row*/, int world, int rank,
                      int cap, PeerPtrs rows, PeerPtrs counts) {
     __shared__ long long s_off[XCHG_MAX_WORLD + 2];
+    const int4* __restrict__ payload = reinterpret_cast<const int4*>(step_resolve(sr).payload);
     if (threadIdx.x < world + 2) s_off[threadIdx.x] = offsets[threadIdx.x];
     __syncthreads();
     const int rv = vdim + 1;  // vectors per window row
@@ -125,9 +125,12 @@ xchg_return_kernel(const int4* __restrict__ out, const uint8_t* __restrict__ hit
 
 // Source: return window -> results in request order (UNPACK of the exchange).
 __global__ void __launch_bounds__(256)
-xchg_scatter_kernel(const int4* __restrict__ back, const int32_t* __restrict__ perm, const int64_t* __restrict__ offsets,
-                    int B, int world, int cap, int vout, int4* __restrict__ out, uint8_t* __restrict__ hit) {
+xchg_scatter_kernel(StepRef sr, const int4* __restrict__ back, const int32_t* __restrict__ perm,
+                    const int64_t* __restrict__ offsets, int B, int world, int cap, int vout) {
     __shared__ long long s_off[XCHG_MAX_WORLD + 2];
+    const StepArgs a = step_resolve(sr);
+    int4* __restrict__ out = reinterpret_cast<int4*>(a.out);
+    uint8_t* __restrict__ hit = a.code;
     if (threadIdx.x < world + 2) s_off[threadIdx.x] = offsets[threadIdx.x];
     __syncthreads();
     const int rv = vout + 1;
@@ -143,6 +146,19 @@ xchg_scatter_kernel(const int4* __restrict__ back, const int32_t* __restrict__ p
             stg_stream(out + (long long)q * vout + c, val);
         else
             hit[q] = (uint8_t)val.x;
+    }
+}
+
+// ROUTE of the sharded step: MD5 of every key of the ingested batch -> owner rank (model_registry.py:159).
+__global__ void __launch_bounds__(ROUTE_THREADS)
+xchg_route_kernel(StepRef sr, int B, int world, int32_t* __restrict__ shard_out, uint4* __restrict__ digests) {
+    __shared__ __align__(16) uint8_t stage[ROUTE_STAGE_BYTES + 32];
+    const StepArgs a = step_resolve(sr);
+    const Md5State st = cta_hash_keys(a.key_bytes, a.key_off, B, stage);
+    const int i = blockIdx.x * ROUTE_THREADS + threadIdx.x;
+    if (i < B) {
+        digests[i] = make_uint4(st.a, st.b, st.c, st.d);
+        shard_out[i] = (int32_t)md5_mod(st, (uint32_t)world);
     }
 }
 
@@ -174,9 +190,11 @@ extern "C" die_status_t die_xchg_dispatch(const uint32_t* digests, const float* 
     DIE_TRY(fill_peers(&counts, peer_counts, world, "counts"));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int vdim = dim / 4;
+    StepRef sr;
+    memset(&sr, 0, sizeof(sr));
+    sr.a.payload = payload;
     DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_vectors((long long)B * (vdim + 1)), 256, 0, s>>>(
-        reinterpret_cast<const int4*>(digests), reinterpret_cast<const int4*>(payload), perm, offsets, B, vdim, world, rank, cap,
-        rows, counts));
+        sr, reinterpret_cast<const int4*>(digests), perm, offsets, B, vdim, world, rank, cap, rows, counts));
     return DIE_OK;
 }
 
@@ -215,8 +233,12 @@ extern "C" die_status_t die_xchg_scatter(const float* back, const int32_t* perm,
     if (B == 0) return DIE_OK;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int vout = dim_out / 4;
+    StepRef sr;
+    memset(&sr, 0, sizeof(sr));
+    sr.a.out = out;
+    sr.a.code = hit;
     DIE_LAUNCH(ST_XCHG, s, xchg_scatter_kernel<<<grid_for_vectors((long long)B * (vout + 1)), 256, 0, s>>>(
-        reinterpret_cast<const int4*>(back), perm, offsets, B, world, cap, vout, reinterpret_cast<int4*>(out), hit));
+        sr, reinterpret_cast<const int4*>(back), perm, offsets, B, world, cap, vout));
     return DIE_OK;
 }
 
@@ -229,10 +251,12 @@ namespace die {
 // Cross-GPU barrier on flags inside the symmetric window: rank r stores `epoch` into flag[r] of every peer
 // and waits until all of its own flags reach `epoch`.  One rank per GPU (never launch two ranks' barriers on
 // the same device: they would wait on each other inside one GPU).  Gives up after ~4 s and reports.
+// Replayed from a graph, epoch = the lane's epoch before the replay (descriptor) + the barrier's fixed rank in it.
 __global__ void xchg_barrier_kernel(PeerPtrs flags, unsigned int* my_flags, int world, int rank, unsigned int epoch,
-                                    unsigned int* error_flag) {
+                                    const QueueDesc* q, int lane, unsigned int* error_flag) {
     const int p = threadIdx.x;
     if (p >= world) return;
+    if (q) epoch += q->epoch0[lane];
     __threadfence_system();
     unsigned int* dst = static_cast<unsigned int*>(flags.p[p]) + rank;
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst), "r"(epoch) : "memory");
@@ -253,15 +277,15 @@ __global__ void xchg_barrier_kernel(PeerPtrs flags, unsigned int* my_flags, int 
 
 }  // namespace die
 
-struct die_xchg {
-    int world, rank, cap, dim;
-    int bmax;  // most requests the owner side handles per step (the pipeline's max_batch)
+// Everything one in-flight step touches.  Two lanes (step parity) let step b+1's ingest half (route, bucket,
+// dispatch) and step b's return half overlap the owner pipeline of the neighbouring step: each lane has its
+// own stream, its own half of the symmetric window (rows, back, counts, barrier flags) and its own scratch.
+struct XchgLane {
     PeerPtrs rows, back, counts, flags;
     float* my_rows;
     float* my_back;
     int32_t* my_cnt;
     unsigned int* my_flags;
-    die_pipeline_t* pipe;
     int32_t* shard;
     uint32_t* digests;
     int64_t* offsets;
@@ -273,15 +297,40 @@ struct die_xchg {
     uint8_t* recv_hit;
     uint32_t* n_dev;
     int32_t* prefix;
-    unsigned int* error_flag;
     unsigned int epoch;
+    cudaStream_t stream;
+    cudaEvent_t done;  // the lane's last enqueued kernel
+};
+
+struct die_xchg {
+    int world, rank, cap, dim;
+    int bmax;  // most requests the owner side handles per step (the pipeline's max_batch)
+    die_pipeline_t* pipe;
+    XchgLane lane[2];
+    unsigned int* error_flag;
+    unsigned long long steps;  // steps enqueued so far: parity picks the lane
+    cudaEvent_t owner_done;    // end of the latest owner pass: the KV table sees batches in step order
+    bool owner_pending;
+    cudaEvent_t entry;
+    // captured replays of K steps
+    struct Replay {
+        int B, K, lane0;
+        cudaGraphExec_t exec;
+    };
+    static constexpr int MAX_GRAPHS = 8;
+    Replay graphs[MAX_GRAPHS];
+    int n_graphs;
+    int graph_steps;
+    cudaStream_t cap_stream;
+    QueueDesc* qdesc;  // device: [0] the ingested queue, [1] the owner passes
 };
 
 static size_t xchg_rows_bytes(int world, int cap, int dim) { return (size_t)world * cap * (dim + 4) * sizeof(float); }
+static size_t xchg_lane_bytes(int world, int cap, int dim) { return 2 * xchg_rows_bytes(world, cap, dim) + 256 + 256; }
 
 extern "C" uint64_t die_xchg_window_bytes(int32_t world, int32_t cap, int32_t dim) {
-    // receive rows + return rows + counts + barrier flags
-    return 2 * xchg_rows_bytes(world, cap, dim) + 256 + 256;
+    // per lane: receive rows + return rows + counts + barrier flags
+    return 2 * xchg_lane_bytes(world, cap, dim);
 }
 
 extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap, int32_t dim, int32_t owner_max,
@@ -289,6 +338,8 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
     if (!out || !pipe || !peer_windows || world < 1 || world > XCHG_MAX_WORLD || rank < 0 || rank >= world || cap <= 0 ||
         dim <= 0 || (dim & 3))
         DIE_FAIL(DIE_ERR_INVALID, "die_xchg_create: bad arguments");
+    for (int i = 0; i < world; ++i)
+        if (!peer_windows[i]) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_create: null window for rank %d", i);
     die_xchg* x = new die_xchg();
     memset(x, 0, sizeof(*x));
     x->world = world;
@@ -298,49 +349,207 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
     x->pipe = pipe;
     x->bmax = owner_max > 0 && owner_max < world * cap ? owner_max : world * cap;
     const size_t rb = xchg_rows_bytes(world, cap, dim);
-    for (int i = 0; i < XCHG_MAX_WORLD; ++i) {
-        char* base = i < world ? static_cast<char*>(peer_windows[i]) : nullptr;
-        if (i < world && !base) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_create: null window for rank %d", i);
-        x->rows.p[i] = base;
-        x->back.p[i] = base ? base + rb : nullptr;
-        x->counts.p[i] = base ? base + 2 * rb : nullptr;
-        x->flags.p[i] = base ? base + 2 * rb + 256 : nullptr;
-    }
-    x->my_rows = static_cast<float*>(x->rows.p[rank]);
-    x->my_back = static_cast<float*>(x->back.p[rank]);
-    x->my_cnt = static_cast<int32_t*>(x->counts.p[rank]);
-    x->my_flags = static_cast<unsigned int*>(x->flags.p[rank]);
+    const size_t lb = xchg_lane_bytes(world, cap, dim);
     const size_t bmax = (size_t)x->bmax;
-    DIE_CUDA(cudaMalloc(&x->shard, cap * sizeof(int32_t)));
-    DIE_CUDA(cudaMalloc(&x->digests, (size_t)cap * 16));
-    DIE_CUDA(cudaMalloc(&x->offsets, (world + 2) * sizeof(int64_t)));
-    DIE_CUDA(cudaMalloc(&x->perm, cap * sizeof(int32_t)));
-    DIE_CUDA(cudaMalloc(&x->pos, cap * sizeof(int32_t)));
-    DIE_CUDA(cudaMalloc(&x->recv_dig, bmax * 16));
-    DIE_CUDA(cudaMalloc(&x->recv_pay, bmax * dim * sizeof(float)));
-    DIE_CUDA(cudaMalloc(&x->recv_out, bmax * dim * sizeof(float)));
-    DIE_CUDA(cudaMalloc(&x->recv_hit, bmax));
-    DIE_CUDA(cudaMalloc(&x->n_dev, sizeof(uint32_t)));
-    DIE_CUDA(cudaMalloc(&x->prefix, (world + 1) * sizeof(int32_t)));
+    for (int l = 0; l < 2; ++l) {
+        XchgLane& L = x->lane[l];
+        for (int i = 0; i < XCHG_MAX_WORLD; ++i) {
+            char* base = i < world ? static_cast<char*>(peer_windows[i]) + l * lb : nullptr;
+            L.rows.p[i] = base;
+            L.back.p[i] = base ? base + rb : nullptr;
+            L.counts.p[i] = base ? base + 2 * rb : nullptr;
+            L.flags.p[i] = base ? base + 2 * rb + 256 : nullptr;
+        }
+        L.my_rows = static_cast<float*>(L.rows.p[rank]);
+        L.my_back = static_cast<float*>(L.back.p[rank]);
+        L.my_cnt = static_cast<int32_t*>(L.counts.p[rank]);
+        L.my_flags = static_cast<unsigned int*>(L.flags.p[rank]);
+        DIE_CUDA(cudaMalloc(&L.shard, cap * sizeof(int32_t)));
+        DIE_CUDA(cudaMalloc(&L.digests, (size_t)cap * 16));
+        DIE_CUDA(cudaMalloc(&L.offsets, (world + 2) * sizeof(int64_t)));
+        DIE_CUDA(cudaMalloc(&L.perm, cap * sizeof(int32_t)));
+        DIE_CUDA(cudaMalloc(&L.pos, cap * sizeof(int32_t)));
+        DIE_CUDA(cudaMalloc(&L.recv_dig, bmax * 16));
+        DIE_CUDA(cudaMalloc(&L.recv_pay, bmax * dim * sizeof(float)));
+        DIE_CUDA(cudaMalloc(&L.recv_out, bmax * dim * sizeof(float)));
+        DIE_CUDA(cudaMalloc(&L.recv_hit, bmax));
+        DIE_CUDA(cudaMalloc(&L.n_dev, sizeof(uint32_t)));
+        DIE_CUDA(cudaMalloc(&L.prefix, (world + 1) * sizeof(int32_t)));
+        DIE_CUDA(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+        DIE_CUDA(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
+    }
+    DIE_CUDA(cudaEventCreateWithFlags(&x->owner_done, cudaEventDisableTiming));
+    DIE_CUDA(cudaEventCreateWithFlags(&x->entry, cudaEventDisableTiming));
     DIE_CUDA(cudaMalloc(&x->error_flag, sizeof(unsigned int)));
     DIE_CUDA(cudaMemset(x->error_flag, 0, sizeof(unsigned int)));
+    DIE_CUDA(cudaMalloc(&x->qdesc, 2 * sizeof(QueueDesc)));
+    DIE_CUDA(cudaStreamCreateWithFlags(&x->cap_stream, cudaStreamNonBlocking));
+    x->graph_steps = 8;
+    if (const char* e = getenv("DIE_GRAPH_STEPS")) x->graph_steps = atoi(e);
     *out = x;
     return DIE_OK;
 }
 
 extern "C" die_status_t die_xchg_destroy(die_xchg_t* x) {
     if (!x) return DIE_OK;
-    void* bufs[] = {x->shard, x->digests, x->offsets, x->perm, x->pos, x->recv_dig, x->recv_pay, x->recv_out,
-                    x->recv_hit, x->n_dev, x->prefix, x->error_flag};
-    for (void* b : bufs) cudaFree(b);
+    for (int l = 0; l < 2; ++l) {
+        XchgLane& L = x->lane[l];
+        if (L.stream) cudaStreamSynchronize(L.stream);
+        void* bufs[] = {L.shard, L.digests, L.offsets, L.perm, L.pos, L.recv_dig, L.recv_pay, L.recv_out,
+                        L.recv_hit, L.n_dev, L.prefix};
+        for (void* b : bufs) cudaFree(b);
+        if (L.done) cudaEventDestroy(L.done);
+        if (L.stream) cudaStreamDestroy(L.stream);
+    }
+    for (int g = 0; g < x->n_graphs; ++g) cudaGraphExecDestroy(x->graphs[g].exec);
+    if (x->cap_stream) cudaStreamDestroy(x->cap_stream);
+    cudaFree(x->qdesc);
+    if (x->owner_done) cudaEventDestroy(x->owner_done);
+    if (x->entry) cudaEventDestroy(x->entry);
+    cudaFree(x->error_flag);
     delete x;
     return DIE_OK;
 }
 
-static die_status_t xchg_barrier(die_xchg* x, cudaStream_t s) {
-    x->epoch += 1;
-    DIE_LAUNCH(ST_XCHG, s, xchg_barrier_kernel<<<1, 32, 0, s>>>(x->flags, x->my_flags, x->world, x->rank, x->epoch, x->error_flag));
+// qd != nullptr: the launch is being captured for replay; `epoch_off` is the barrier's rank on its lane inside
+// the replay and the lane's epoch before the replay comes from the descriptor.
+static die_status_t xchg_barrier(die_xchg* x, XchgLane& L, int lane, const QueueDesc* qd, unsigned int epoch) {
+    DIE_LAUNCH(ST_XCHG, L.stream, xchg_barrier_kernel<<<1, 32, 0, L.stream>>>(L.flags, L.my_flags, x->world, x->rank, epoch,
+                                                                             qd, lane, x->error_flag));
     return DIE_OK;
+}
+
+// The launches of one step on lane `lane`.  user: keys / payload / out / hit of the ingested batch;
+// owner: table view, clock and stamps of the owner pass (its buffers are the lane's).
+// reserve_now != nullptr (stream-launched step): the owner pass's host bookkeeping happens here, after the
+// ingest half is enqueued, so that table maintenance -- when due -- is ordered behind the previous owner pass
+// without holding back this step's ingest.
+static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user, StepRef owner, int32_t B,
+                                     int32_t* shard_out, const QueueDesc* qd, unsigned int epoch_first,
+                                     const double* reserve_now) {
+    XchgLane& L = x->lane[lane];
+    cudaStream_t s = L.stream;
+    const int W = x->world, D = x->dim, vdim = D / 4;
+    int32_t* shard = shard_out ? shard_out : L.shard;
+    DIE_LAUNCH(ST_ROUTE, s, xchg_route_kernel<<<ceil_div(B, ROUTE_THREADS), ROUTE_THREADS, 0, s>>>(
+        user, B, W, shard, reinterpret_cast<uint4*>(L.digests)));
+    DIE_TRY(die_bucket_by_shard(shard, B, W, L.offsets, L.perm, L.pos, static_cast<die_stream_t>(s)));
+    DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_vectors((long long)B * (vdim + 1)), 256, 0, s>>>(
+        user, reinterpret_cast<const int4*>(L.digests), L.perm, L.offsets, B, vdim, W, x->rank, x->cap, L.rows, L.counts));
+    DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first));  // every rank's rows have landed in their owners' windows
+    DIE_LAUNCH(ST_XCHG, s, xchg_compact_kernel<<<grid_for_vectors((long long)2 * x->cap * (vdim + 1)), 256, 0, s>>>(
+        reinterpret_cast<const int4*>(L.my_rows), L.my_cnt, W, x->cap, vdim, (long long)x->bmax,
+        reinterpret_cast<int4*>(L.recv_dig), reinterpret_cast<int4*>(L.recv_pay), L.n_dev, L.prefix, x->error_flag));
+    if (x->owner_pending) DIE_CUDA(cudaStreamWaitEvent(s, x->owner_done, 0));  // the table sees batches in step order
+    if (reserve_now) {
+        unsigned long long tail0;
+        DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, 1, s, &owner.a.kv, &tail0));
+        owner.a.now = *reserve_now;
+        owner.a.t_get = tail0;
+        owner.a.t_set = tail0 + (unsigned long long)x->bmax;
+    }
+    owner.a.payload = L.recv_pay;
+    owner.a.out = L.recv_out;
+    owner.a.code = L.recv_hit;
+    DIE_TRY(pipeline_owner_launch(x->pipe, owner, L.recv_dig, x->bmax, L.n_dev, s));
+    DIE_CUDA(cudaEventRecord(x->owner_done, s));
+    x->owner_pending = true;
+    DIE_LAUNCH(ST_XCHG, s, xchg_return_kernel<<<grid_for_vectors((long long)2 * x->cap * (vdim + 1)), 256, 0, s>>>(
+        reinterpret_cast<const int4*>(L.recv_out), L.recv_hit, L.prefix, W, x->rank, x->cap, vdim, L.back));
+    DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first + 1));  // every owner's results are back in the sources' windows
+    DIE_LAUNCH(ST_XCHG, s, xchg_scatter_kernel<<<grid_for_vectors((long long)B * (vdim + 1)), 256, 0, s>>>(
+        user, reinterpret_cast<const int4*>(L.my_back), L.perm, L.offsets, B, W, x->cap, vdim));
+    return DIE_OK;
+}
+
+// Lanes start after the work already on `from` and `from` continues after both lanes have drained.
+static die_status_t xchg_fork(die_xchg* x, cudaStream_t from) {
+    DIE_CUDA(cudaEventRecord(x->entry, from));
+    for (int l = 0; l < 2; ++l) DIE_CUDA(cudaStreamWaitEvent(x->lane[l].stream, x->entry, 0));
+    x->owner_pending = false;  // everything earlier is ordered through `from`
+    return DIE_OK;
+}
+static die_status_t xchg_join(die_xchg* x, cudaStream_t to) {
+    for (int l = 0; l < 2; ++l) {
+        DIE_CUDA(cudaEventRecord(x->lane[l].done, x->lane[l].stream));
+        DIE_CUDA(cudaStreamWaitEvent(to, x->lane[l].done, 0));
+    }
+    return DIE_OK;
+}
+
+// One stream-launched step: host bookkeeping of the owner pass, then the launches with their values by value.
+static die_status_t xchg_enqueue_step(die_xchg* x, const uint8_t* key_bytes, const int64_t* key_off, int32_t B,
+                                      const float* payload, double now, float* out, uint8_t* hit_out,
+                                      int32_t* shard_out) {
+    const int lane = (int)(x->steps & 1);
+    XchgLane& L = x->lane[lane];
+    x->steps += 1;
+    StepRef user, owner;
+    memset(&user, 0, sizeof(user));
+    memset(&owner, 0, sizeof(owner));
+    user.a.key_bytes = key_bytes;
+    user.a.key_off = key_off;
+    user.a.payload = payload;
+    user.a.out = out;
+    user.a.code = hit_out;
+    const unsigned int e = L.epoch + 1;
+    L.epoch += 2;
+    return xchg_launch_step(x, lane, user, owner, B, shard_out, nullptr, e, &now);
+}
+
+// K steps captured once per (B, K, first lane); qd[0] describes the ingested queue, qd[1] the owner passes.
+static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_t* out) {
+    const int lane0 = (int)(x->steps & 1);
+    for (int g = 0; g < x->n_graphs; ++g)
+        if (x->graphs[g].B == B && x->graphs[g].K == K && x->graphs[g].lane0 == lane0) {
+            *out = x->graphs[g].exec;
+            return DIE_OK;
+        }
+    if (x->n_graphs == die_xchg::MAX_GRAPHS) {
+        cudaGraphExecDestroy(x->graphs[0].exec);
+        for (int g = 1; g < x->n_graphs; ++g) x->graphs[g - 1] = x->graphs[g];
+        x->n_graphs -= 1;
+    }
+    cudaGraph_t graph = nullptr;
+    DIE_CUDA(cudaStreamBeginCapture(x->cap_stream, cudaStreamCaptureModeThreadLocal));
+    die_status_t st = xchg_fork(x, x->cap_stream);
+    unsigned int off[2] = {1u, 1u};
+    for (int i = 0; i < K && st == DIE_OK; ++i) {
+        const int lane = (lane0 + i) & 1;
+        StepRef user, owner;
+        memset(&user, 0, sizeof(user));
+        memset(&owner, 0, sizeof(owner));
+        user.q = x->qdesc;
+        user.i = i;
+        owner.q = x->qdesc + 1;
+        owner.i = i;
+        st = xchg_launch_step(x, lane, user, owner, B, nullptr, x->qdesc, off[lane], nullptr);
+        off[lane] += 2;
+    }
+    if (st == DIE_OK) st = xchg_join(x, x->cap_stream);
+    const cudaError_t e = cudaStreamEndCapture(x->cap_stream, &graph);
+    x->owner_pending = false;
+    if (st != DIE_OK) {
+        if (graph) cudaGraphDestroy(graph);
+        return st;
+    }
+    DIE_CUDA(e);
+    cudaGraphExec_t exec = nullptr;
+    const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    DIE_CUDA(ei);
+    die_xchg::Replay& r = x->graphs[x->n_graphs++];
+    r.B = B;
+    r.K = K;
+    r.lane0 = lane0;
+    r.exec = exec;
+    *out = exec;
+    return DIE_OK;
+}
+
+__global__ void xchg_desc_set_kernel(QueueDesc* dst, QueueDesc user, QueueDesc owner) {
+    dst[0] = user;
+    dst[1] = owner;
 }
 
 // One flushed batch ingested on this rank; results in request order.  Every rank of the group must make the
@@ -350,42 +559,73 @@ extern "C" die_status_t die_xchg_step(die_xchg_t* x, const uint8_t* key_bytes, c
                                       int32_t* shard_out, die_stream_t stream) {
     if (!x || B < 0 || B > x->cap) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_step: B must be in [0, cap]");
     if (!key_off || !payload || !out || !hit_out) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_step: null buffer");
-    cudaStream_t s = static_cast<cudaStream_t>(stream);
-    const int W = x->world, D = x->dim, vdim = D / 4;
-    int32_t* shard = shard_out ? shard_out : x->shard;
-    DIE_TRY(die_route_md5(key_bytes, key_off, B, W, nullptr, nullptr, 0, 0, shard, x->digests, nullptr, stream));
-    DIE_TRY(die_bucket_by_shard(shard, B, W, x->offsets, x->perm, x->pos, stream));
-    DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_vectors((long long)B * (vdim + 1)), 256, 0, s>>>(
-        reinterpret_cast<const int4*>(x->digests), reinterpret_cast<const int4*>(payload), x->perm, x->offsets, B, vdim, W,
-        x->rank, x->cap, x->rows, x->counts));
-    DIE_TRY(xchg_barrier(x, s));  // every rank's rows have landed in their owners' windows
-    DIE_LAUNCH(ST_XCHG, s, xchg_compact_kernel<<<grid_for_vectors((long long)2 * x->cap * (vdim + 1)), 256, 0, s>>>(
-        reinterpret_cast<const int4*>(x->my_rows), x->my_cnt, W, x->cap, vdim, (long long)x->bmax,
-        reinterpret_cast<int4*>(x->recv_dig), reinterpret_cast<int4*>(x->recv_pay), x->n_dev, x->prefix, x->error_flag));
-    DIE_TRY(die_pipeline_run_owner_device_n(x->pipe, x->recv_dig, x->bmax, x->n_dev, x->recv_pay, now, x->recv_out,
-                                            x->recv_hit, stream));
-    DIE_LAUNCH(ST_XCHG, s, xchg_return_kernel<<<grid_for_vectors((long long)2 * x->cap * (vdim + 1)), 256, 0, s>>>(
-        reinterpret_cast<const int4*>(x->recv_out), x->recv_hit, x->prefix, W, x->rank, x->cap, vdim, x->back));
-    DIE_TRY(xchg_barrier(x, s));  // every owner's results are back in the sources' windows
-    DIE_LAUNCH(ST_XCHG, s, xchg_scatter_kernel<<<grid_for_vectors((long long)B * (vdim + 1)), 256, 0, s>>>(
-        reinterpret_cast<const int4*>(x->my_back), x->perm, x->offsets, B, W, x->cap, vdim, reinterpret_cast<int4*>(out),
-        hit_out));
-    return DIE_OK;
+    cudaStream_t user = static_cast<cudaStream_t>(stream);
+    DIE_TRY(xchg_fork(x, user));
+    DIE_TRY(xchg_enqueue_step(x, key_bytes, key_off, B, payload, now, out, hit_out, shard_out));
+    return xchg_join(x, user);
 }
 
+// A queue of flushed batches.  Consecutive steps run on alternating lanes, so a step's ingest and return
+// halves overlap its neighbours' owner passes; groups of K steps are replayed from one captured graph (host
+// cost: two launches per K steps).  out / hit_out are rings of out_ring slots (>= 2 when n_batches > 1).
 extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, const uint8_t* key_bytes,
                                            int64_t key_bytes_stride, const int64_t* key_off, int64_t key_off_stride,
                                            int32_t B, const float* payload, double now0, double now_step, float* out,
                                            uint8_t* hit_out, int32_t out_ring, die_stream_t stream) {
     if (!x || n_batches < 0 || out_ring < 1) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_step_many: bad arguments");
+    if (B < 0 || B > x->cap) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_step_many: B must be in [0, cap]");
+    if (!key_off || !payload || !out || !hit_out) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_step_many: null buffer");
+    if (n_batches > 1 && out_ring < 2) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_step_many: out_ring must be >= 2");
+    cudaStream_t user = static_cast<cudaStream_t>(stream);
     const size_t row = (size_t)B * x->dim;
-    for (int32_t j = 0; j < n_batches; ++j) {
-        const int r = j % out_ring;
-        DIE_TRY(die_xchg_step(x, key_bytes + (size_t)j * key_bytes_stride, key_off + (size_t)j * key_off_stride, B,
-                              payload + (size_t)j * row, now0 + j * now_step, out + (size_t)r * row,
-                              hit_out + (size_t)r * B, nullptr, stream));
+    int32_t j = 0;
+    const int K = x->graph_steps;
+    if (K >= 2 && B > 0 && pipeline_graph_fits(x->pipe, x->bmax, K)) {
+        QueueDesc du, dw;
+        memset(&du, 0, sizeof(du));
+        memset(&dw, 0, sizeof(dw));
+        du.key_bytes = key_bytes;
+        du.key_off = key_off;
+        du.payload = payload;
+        du.out = out;
+        du.hit = hit_out;
+        du.key_bytes_stride = key_bytes_stride;
+        du.key_off_stride = key_off_stride;
+        du.payload_stride = (long long)row;
+        du.out_stride = (long long)row;
+        du.hit_stride = B;
+        du.ring = out_ring;
+        dw.ring = 1;
+        dw.batch = x->bmax;
+        dw.now0 = now0;
+        dw.now_step = now_step;
+        for (; n_batches - j >= K; j += K) {
+            cudaGraphExec_t exec;
+            DIE_TRY(xchg_graph_get(x, B, K, &exec));
+            unsigned long long tail0;
+            DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, K, user, &dw.kv, &tail0));
+            dw.tail0 = tail0;
+            du.j0 = dw.j0 = j;
+            for (int l = 0; l < 2; ++l) du.epoch0[l] = x->lane[l].epoch;
+            xchg_desc_set_kernel<<<1, 1, 0, user>>>(x->qdesc, du, dw);
+            DIE_LAUNCH_CHECK();
+            DIE_CUDA(cudaGraphLaunch(exec, user));
+            count_launch((unsigned)(K * (8 + pipeline_launches_per_step(x->pipe))));
+            const int lane0 = (int)(x->steps & 1);
+            x->lane[lane0].epoch += 2u * (unsigned)((K + 1) / 2);
+            x->lane[lane0 ^ 1].epoch += 2u * (unsigned)(K / 2);
+            x->steps += (unsigned long long)K;
+        }
     }
-    return DIE_OK;
+    if (j == n_batches) return DIE_OK;
+    DIE_TRY(xchg_fork(x, user));
+    for (; j < n_batches; ++j) {
+        const int r = j % out_ring;
+        DIE_TRY(xchg_enqueue_step(x, key_bytes + (size_t)j * key_bytes_stride, key_off + (size_t)j * key_off_stride, B,
+                                  payload + (size_t)j * row, now0 + j * now_step, out + (size_t)r * row,
+                                  hit_out + (size_t)r * B, nullptr));
+    }
+    return xchg_join(x, user);
 }
 
 // Synchronises and reports whether a barrier of this context ever timed out (a peer stopped calling).

@@ -38,6 +38,7 @@ static cudaEvent_t get_event() {
     return e;
 }
 
+bool prof_active() { return g_prof_on; }
 void prof_before(int stage, cudaStream_t s) {
     if (!g_prof_on) return;
     ProfRec r{stage, get_event(), get_event()};

@@ -15,16 +15,13 @@ die_status_t linear_tf32_launch(const float* X, const float* W, const float* b, 
 // Fused pipeline epilogue of the TF32 linear kernel (see model_tc.cu): scatter results to request order and to
 // the cached rows, and evict the batch's LRU victims in the same launch.
 struct TcScatter {
-    KvView kv;
+    StepRef sr;                // table view, stamps, out and hit codes of the step
     const int32_t* miss_req;   // rank -> request index
     const int32_t* set_row;    // request -> cached-row handle (-1: ask the slot)
     const int32_t* set_slot;   // request -> table slot
     PipeBufs pb;               // victim window + control block of the batch
     const unsigned int* any_dup;
-    unsigned long long t_set;
-    float* out;                // [B, N]
     float* arena;              // [n_rows, N]
-    uint8_t* code;             // [B]
     int tiles;
 };
 die_status_t linear_tf32_scatter_launch(const float* X, const float* W, const float* b, int B, int K, int N,

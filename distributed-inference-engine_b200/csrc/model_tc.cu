@@ -38,8 +38,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, const float* __restrict__ bias,
                    float* __restrict__ Y, int B, int K, int N, int Nc, const uint32_t* __restrict__ n_rows_dev,
                    TcScatter sc) {
+    StepArgs step;
+    if (SCATTER) {
+        step = step_resolve(sc.sr);
+        sc.pb.code = step.code;
+    }
     if (SCATTER && (int)blockIdx.x >= sc.tiles) {  // eviction CTAs (kvstore.py:82-93), 256 window records each
-        pipe_evict_cta(sc.kv, sc.pb, (int)((blockIdx.x - sc.tiles) * gridDim.y + blockIdx.y), sc.t_set);
+        pipe_evict_cta(step.kv, sc.pb, (int)((blockIdx.x - sc.tiles) * gridDim.y + blockIdx.y), step.t_set);
         return;
     }
     extern __shared__ uint8_t smem_raw[];
@@ -131,12 +136,12 @@ linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, con
             stg_stream(reinterpret_cast<int4*>(Y + (size_t)(m0 + r) * N + n0) + c, o);
         } else {
             const int q = sc.miss_req[m0 + r];
-            stg_stream(reinterpret_cast<int4*>(sc.out + (size_t)q * N + n0) + c, o);
-            if (c == 0 && blockIdx.y == 0) sc.code[q] = 0;  // callers see 1 = served from the cache, 0 = computed
+            stg_stream(reinterpret_cast<int4*>(step.out + (size_t)q * N + n0) + c, o);
+            if (c == 0 && blockIdx.y == 0) step.code[q] = 0;  // callers see 1 = served from the cache, 0 = computed
             long long row = sc.set_row[q];
             if (any_dup) {  // same key twice in the batch: only the last op's result is cached
-                const Slot* sl = &sc.kv.slots[sc.set_slot[q]];
-                row = sl->stamp == sc.t_set + (unsigned long long)q ? (long long)sl->value : -1;
+                const Slot* sl = &step.kv.slots[sc.set_slot[q]];
+                row = sl->stamp == step.t_set + (unsigned long long)q ? (long long)sl->value : -1;
             }
             if (row >= 0) stg_stream(reinterpret_cast<int4*>(sc.arena + (size_t)row * N + n0) + c, o);
         }
@@ -196,7 +201,7 @@ die_status_t linear_tf32_launch(const float* X, const float* W, const float* b, 
 
 die_status_t linear_tf32_scatter_launch(const float* X, const float* W, const float* b, int B, int K, int N,
                                         const uint32_t* n_rows_dev, const TcScatter& sc, cudaStream_t s) {
-    return tf32_launch(X, W, b, sc.out, B, K, N, n_rows_dev, &sc, s);
+    return tf32_launch(X, W, b, nullptr, B, K, N, n_rows_dev, &sc, s);  // results go to the step's `out`
 }
 
 }  // namespace die

@@ -16,6 +16,7 @@
 // General sequence (tiny caches): the stand-alone kernels of kvstore.cu, 9 launches.
 #include "model_internal.cuh"
 #include "pipeline_device.cuh"
+#include "pipeline_internal.cuh"
 #include "route_device.cuh"
 
 struct die_pipeline {
@@ -51,6 +52,21 @@ struct die_pipeline {
     size_t key_stage_stride;
     cudaStream_t s_in, s_out;
     cudaEvent_t ev_in[NBUF], ev_done[NBUF], ev_out[NBUF];
+    // captured replays of K steps (see replay_fast)
+    struct Replay {
+        int B, K;
+        bool from_keys;
+        const uint32_t* digests;
+        const uint32_t* n_req_dev;
+        const die::QueueDesc* qd;
+        cudaGraphExec_t exec;
+    };
+    static constexpr int MAX_GRAPHS = 8;
+    Replay graphs[MAX_GRAPHS];
+    int n_graphs;
+    int graph_steps;          // K; 0 = always launch from the stream
+    cudaStream_t cap_stream;  // capture only: the caller's stream may be the legacy stream, which cannot capture
+    die::QueueDesc* qdesc;    // device
 };
 
 namespace die {
@@ -180,11 +196,16 @@ __device__ void pipe_window_chunk(const KvView& kv, const PipeBufs& pb, int chun
 
 template <bool FROM_KEYS>
 __global__ void __launch_bounds__(PT)
-pipe_get_kernel(KvView kv, PipeBufs pb, const uint8_t* __restrict__ key_bytes, const int64_t* __restrict__ key_off,
-                uint4* __restrict__ digests, int B, const uint32_t* __restrict__ n_req_dev, double now,
-                unsigned long long t_get, unsigned long long t_set) {
+pipe_get_kernel(StepRef sr, PipeBufs pb, uint4* __restrict__ digests, int B, const uint32_t* __restrict__ n_req_dev) {
     __shared__ __align__(16) uint8_t stage[FROM_KEYS ? ROUTE_STAGE_BYTES + 32 : 16];
     __shared__ bool s_last;
+    const StepArgs a = step_resolve(sr);
+    const KvView& kv = a.kv;
+    const uint8_t* __restrict__ key_bytes = a.key_bytes;
+    const int64_t* __restrict__ key_off = a.key_off;
+    const double now = a.now;
+    const unsigned long long t_get = a.t_get;
+    pb.code = a.code;
     if (n_req_dev) B = min(B, (int)*n_req_dev);  // batch size known only on the device (after an exchange)
     const int i = blockIdx.x * PT + threadIdx.x;
     const bool active = i < B;
@@ -228,10 +249,16 @@ pipe_get_kernel(KvView kv, PipeBufs pb, const uint8_t* __restrict__ key_bytes, c
 // CTAs [0, g_claim): KVCache.set of every miss (all known absent).  Last n_chunks CTAs: LRU victim window.
 // CTAs in between: PACK + hit copy.
 __global__ void __launch_bounds__(PT)
-pipe_claim_pack_kernel(KvView kv, PipeBufs pb, const uint4* __restrict__ digests, int B,
-                       const uint32_t* __restrict__ n_req_dev, double now, unsigned long long t_set, int g_claim,
-                       const int4* __restrict__ payload, const int4* __restrict__ arena, int vin, int vout,
-                       int4* __restrict__ packed_in, int4* __restrict__ out) {
+pipe_claim_pack_kernel(StepRef sr, PipeBufs pb, const uint4* __restrict__ digests, int B,
+                       const uint32_t* __restrict__ n_req_dev, int g_claim, const int4* __restrict__ arena, int vin,
+                       int vout, int4* __restrict__ packed_in) {
+    const StepArgs a = step_resolve(sr);
+    const KvView& kv = a.kv;
+    const double now = a.now;
+    const unsigned long long t_set = a.t_set;
+    const int4* __restrict__ payload = reinterpret_cast<const int4*>(a.payload);
+    int4* __restrict__ out = reinterpret_cast<int4*>(a.out);
+    pb.code = a.code;
     if (n_req_dev) B = min(B, (int)*n_req_dev);
     if ((int)blockIdx.x < g_claim) {
         __shared__ bool s_last;
@@ -294,9 +321,13 @@ pipe_claim_pack_kernel(KvView kv, PipeBufs pb, const uint4* __restrict__ digests
 
 // CTAs [0, g_evict): evict the e_final least-recently-used entries.  Rest: UNPACK + store the cached rows.
 __global__ void __launch_bounds__(PT)
-pipe_unpack_evict_kernel(KvView kv, PipeBufs pb, const int4* __restrict__ packed_out, unsigned long long t_set, int B,
-                         const uint32_t* __restrict__ n_req_dev, int g_evict, int vout, int4* __restrict__ out,
-                         int4* __restrict__ arena) {
+pipe_unpack_evict_kernel(StepRef sr, PipeBufs pb, const int4* __restrict__ packed_out, int B,
+                         const uint32_t* __restrict__ n_req_dev, int g_evict, int vout, int4* __restrict__ arena) {
+    const StepArgs a = step_resolve(sr);
+    const KvView& kv = a.kv;
+    const unsigned long long t_set = a.t_set;
+    int4* __restrict__ out = reinterpret_cast<int4*>(a.out);
+    pb.code = a.code;
     if (n_req_dev) B = min(B, (int)*n_req_dev);
     if ((int)blockIdx.x < g_evict) {
         pipe_evict_cta(kv, pb, (int)blockIdx.x, t_set);
@@ -427,44 +458,33 @@ static PipeBufs bufs_of(die_pipeline* p, uint8_t* code) {
     return pb;
 }
 
-// key_off != nullptr: hash the keys in the get kernel (digests are written to `digests`);
+// The launches of one step.  from_keys: hash the keys in the get kernel (digests are written to `digests`);
 // otherwise `digests` are inputs.
-static die_status_t run_fast(die_pipeline* p, const uint8_t* key_bytes, const int64_t* key_off, uint32_t* digests,
-                             int B, const uint32_t* n_req_dev, const float* payload, double now, float* out,
-                             uint8_t* hit_out, cudaStream_t s) {
+static die_status_t launch_fast(die_pipeline* p, const StepRef& sr, bool from_keys, uint32_t* digests, int B,
+                                const uint32_t* n_req_dev, cudaStream_t s) {
     const die_pipeline_config_t& c = p->cfg;
-    die_kv* kv = p->kv;
     const int vin = c.dim_in / 4, vout = c.dim_out / 4;
-    uint8_t* code = hit_out ? hit_out : p->code;
-    DIE_TRY(kv_reserve(kv, (uint64_t)B, false, s));
-    DIE_TRY(kv_reserve(kv, (uint64_t)B, true, s));
-    const unsigned long long t_get = kv->tail, t_set = kv->tail + (unsigned long long)B;
-    kv->tail += 2ull * (unsigned long long)B;
-    const KvView v = view_of(kv);
-    const PipeBufs pb = bufs_of(p, code);
+    const PipeBufs pb = bufs_of(p, nullptr);  // the kernels take the hit codes' address from the step
     const int g = ceil_div(B, PT);
     uint4* dg = reinterpret_cast<uint4*>(digests);
-    if (key_off)
-        DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<true><<<g, PT, 0, s>>>(v, pb, key_bytes, key_off, dg, B, n_req_dev, now, t_get, t_set));
+    if (from_keys)
+        DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<true><<<g, PT, 0, s>>>(sr, pb, dg, B, n_req_dev));
     else
-        DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<false><<<g, PT, 0, s>>>(v, pb, nullptr, nullptr, dg, B, n_req_dev, now, t_get, t_set));
+        DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<false><<<g, PT, 0, s>>>(sr, pb, dg, B, n_req_dev));
     const int g_pack = grid_256((long long)B * std::max(vin, vout));
     DIE_LAUNCH(ST_KV_CLAIM, s, pipe_claim_pack_kernel<<<g + g_pack + p->n_chunks, PT, 0, s>>>(
-        v, pb, dg, B, n_req_dev, now, t_set, g, reinterpret_cast<const int4*>(payload), reinterpret_cast<const int4*>(p->arena),
-        vin, vout, reinterpret_cast<int4*>(p->packed_in), reinterpret_cast<int4*>(out)));
+        sr, pb, dg, B, n_req_dev, g, reinterpret_cast<const int4*>(p->arena), vin, vout,
+        reinterpret_cast<int4*>(p->packed_in)));
     if (c.model == DIE_MODEL_LINEAR_TF32) {
         // third and last launch: tensor-core GEMM whose epilogue is the UNPACK, plus the eviction CTAs
         TcScatter sc;
-        sc.kv = v;
+        sc.sr = sr;
         sc.miss_req = p->miss_req;
         sc.set_row = p->set_row;
         sc.set_slot = p->set_slot;
         sc.pb = pb;
         sc.any_dup = &p->ctrl->any_dup;
-        sc.t_set = t_set;
-        sc.out = out;
         sc.arena = p->arena;
-        sc.code = code;
         sc.tiles = 0;
         return linear_tf32_scatter_launch(p->packed_in, p->W, p->bias, B, c.dim_in, c.dim_out, &p->ctrl->n_miss, sc, s);
     }
@@ -477,10 +497,130 @@ static die_status_t run_fast(die_pipeline* p, const uint8_t* key_bytes, const in
     const int g_unpack = grid_256((long long)B * vout);
     const int g_evict = p->n_chunks * (WCHUNK / PT);
     DIE_LAUNCH(ST_UNPACK_STORE, s, pipe_unpack_evict_kernel<<<g_evict + g_unpack, PT, 0, s>>>(
-        v, pb, reinterpret_cast<const int4*>(result), t_set, B, n_req_dev, g_evict, vout, reinterpret_cast<int4*>(out),
-        reinterpret_cast<int4*>(p->arena)));
+        sr, pb, reinterpret_cast<const int4*>(result), B, n_req_dev, g_evict, vout, reinterpret_cast<int4*>(p->arena)));
     return DIE_OK;
 }
+
+static die_status_t run_fast(die_pipeline* p, const uint8_t* key_bytes, const int64_t* key_off, uint32_t* digests,
+                             int B, const uint32_t* n_req_dev, const float* payload, double now, float* out,
+                             uint8_t* hit_out, cudaStream_t s) {
+    die_kv* kv = p->kv;
+    DIE_TRY(kv_reserve(kv, (uint64_t)B, false, s));
+    DIE_TRY(kv_reserve(kv, (uint64_t)B, true, s));
+    StepRef sr;
+    sr.q = nullptr;
+    sr.i = 0;
+    sr.a.kv = view_of(kv);
+    sr.a.key_bytes = key_bytes;
+    sr.a.key_off = key_off;
+    sr.a.payload = payload;
+    sr.a.out = out;
+    sr.a.code = hit_out ? hit_out : p->code;
+    sr.a.now = now;
+    sr.a.t_get = kv->tail;
+    sr.a.t_set = kv->tail + (unsigned long long)B;
+    kv->tail += 2ull * (unsigned long long)B;
+    return launch_fast(p, sr, key_off != nullptr, digests, B, n_req_dev, s);
+}
+
+// ---- replay of K steps from a CUDA graph -----------------------------------------------------------------
+// The host cost of a step is its launches; a queue of batches pays it once per K steps instead: the K steps
+// are captured once (their arguments come from the device-resident QueueDesc, see pipeline_device.cuh) and
+// replayed with one graph launch after a one-thread kernel has rewritten the descriptor.
+__global__ void queue_desc_set_kernel(QueueDesc* dst, QueueDesc v) { *dst = v; }
+
+static bool graph_fits(const die_pipeline* p, int B, int K) {
+    const die_kv* kv = p->kv;
+    // the conservative host bounds of kv_reserve are taken for K steps at once: keep that a small part of
+    // the LRU ring and of the EMPTY-slot reserve, or maintenance would run at every replay
+    return p->fast && K > 0 && (uint64_t)2 * K * B <= kv->ring_cap / 8 && (uint64_t)K * B <= kv->capacity / 32;
+}
+
+static die_status_t graph_get(die_pipeline* p, bool from_keys, uint32_t* digests, int B, const uint32_t* n_req_dev,
+                              QueueDesc* qd, int K, cudaGraphExec_t* out) {
+    for (int g = 0; g < p->n_graphs; ++g) {
+        const die_pipeline::Replay& r = p->graphs[g];
+        if (r.B == B && r.K == K && r.from_keys == from_keys && r.digests == digests && r.n_req_dev == n_req_dev && r.qd == qd) {
+            *out = r.exec;
+            return DIE_OK;
+        }
+    }
+    if (p->n_graphs == die_pipeline::MAX_GRAPHS) {  // recycle the oldest
+        cudaGraphExecDestroy(p->graphs[0].exec);
+        for (int g = 1; g < p->n_graphs; ++g) p->graphs[g - 1] = p->graphs[g];
+        p->n_graphs -= 1;
+    }
+    if (!p->cap_stream) DIE_CUDA(cudaStreamCreateWithFlags(&p->cap_stream, cudaStreamNonBlocking));
+    cudaGraph_t graph = nullptr;
+    DIE_CUDA(cudaStreamBeginCapture(p->cap_stream, cudaStreamCaptureModeThreadLocal));
+    die_status_t st = DIE_OK;
+    for (int i = 0; i < K && st == DIE_OK; ++i) {
+        StepRef sr;
+        memset(&sr, 0, sizeof(sr));
+        sr.q = qd;
+        sr.i = i;
+        st = launch_fast(p, sr, from_keys, digests, B, n_req_dev, p->cap_stream);
+    }
+    const cudaError_t e = cudaStreamEndCapture(p->cap_stream, &graph);
+    if (st != DIE_OK) {
+        if (graph) cudaGraphDestroy(graph);
+        return st;
+    }
+    DIE_CUDA(e);
+    cudaGraphExec_t exec = nullptr;
+    const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    DIE_CUDA(ei);
+    die_pipeline::Replay& r = p->graphs[p->n_graphs++];
+    r.B = B;
+    r.K = K;
+    r.from_keys = from_keys;
+    r.digests = digests;
+    r.n_req_dev = n_req_dev;
+    r.qd = qd;
+    r.exec = exec;
+    *out = exec;
+    return DIE_OK;
+}
+
+// Run K steps described by `d` (everything but kv / tail0 filled in by the caller) as one replay.
+static die_status_t replay_fast(die_pipeline* p, QueueDesc d, QueueDesc* qd, bool from_keys, uint32_t* digests, int B,
+                                const uint32_t* n_req_dev, int K, cudaStream_t s) {
+    die_kv* kv = p->kv;
+    cudaGraphExec_t exec;
+    DIE_TRY(graph_get(p, from_keys, digests, B, n_req_dev, qd, K, &exec));
+    DIE_TRY(kv_reserve(kv, (uint64_t)2 * K * B, false, s));
+    DIE_TRY(kv_reserve(kv, (uint64_t)K * B, true, s));
+    d.kv = view_of(kv);
+    d.batch = B;
+    d.tail0 = kv->tail;
+    kv->tail += 2ull * (unsigned long long)K * (unsigned long long)B;
+    queue_desc_set_kernel<<<1, 1, 0, s>>>(qd, d);
+    DIE_LAUNCH_CHECK();
+    DIE_CUDA(cudaGraphLaunch(exec, s));
+    count_launch((unsigned)(K * pipeline_launches_per_step(p)));
+    return DIE_OK;
+}
+
+bool pipeline_graph_fits(const die_pipeline* p, int B_max, int K) { return graph_fits(p, B_max, K) && !prof_active(); }
+
+die_status_t pipeline_owner_reserve(die_pipeline* p, int B_max, int K, cudaStream_t s, KvView* view,
+                                    unsigned long long* tail0) {
+    die_kv* kv = p->kv;
+    DIE_TRY(kv_reserve(kv, (uint64_t)2 * K * B_max, false, s));
+    DIE_TRY(kv_reserve(kv, (uint64_t)K * B_max, true, s));
+    *view = view_of(kv);
+    *tail0 = kv->tail;
+    kv->tail += 2ull * (unsigned long long)K * (unsigned long long)B_max;
+    return DIE_OK;
+}
+
+die_status_t pipeline_owner_launch(die_pipeline* p, const StepRef& sr, uint32_t* digests, int B_max,
+                                   const uint32_t* n_req_dev, cudaStream_t s) {
+    return launch_fast(p, sr, false, digests, B_max, n_req_dev, s);
+}
+
+int pipeline_launches_per_step(const die_pipeline* p) { return p->cfg.model == DIE_MODEL_LINEAR_FP32 ? 4 : 3; }
 
 static die_status_t run_general(die_pipeline* p, const uint32_t* digests, int B, const float* payload, double now,
                                 float* out, uint8_t* hit_out, cudaStream_t s) {
@@ -568,6 +708,9 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
         DIE_CUDA(cudaEventCreateWithFlags(&p->ev_done[i], cudaEventDisableTiming));
         DIE_CUDA(cudaEventCreateWithFlags(&p->ev_out[i], cudaEventDisableTiming));
     }
+    DIE_CUDA(cudaMalloc(&p->qdesc, sizeof(QueueDesc)));
+    p->graph_steps = 8;
+    if (const char* e = getenv("DIE_GRAPH_STEPS")) p->graph_steps = atoi(e);  // 0: every step launched from the stream
     *out = p;
     return DIE_OK;
 }
@@ -579,6 +722,9 @@ extern "C" die_status_t die_pipeline_destroy(die_pipeline_t* p) {
                     p->set_slot, p->set_row, p->wmask, p->wcount, p->ctrl, p->packed_in, p->packed_out, p->d_key_bytes,
                     p->d_key_off, p->d_payload, p->d_out, p->d_hit};
     for (void* b : bufs) cudaFree(b);
+    cudaFree(p->qdesc);
+    for (int g = 0; g < p->n_graphs; ++g) cudaGraphExecDestroy(p->graphs[g].exec);
+    if (p->cap_stream) cudaStreamDestroy(p->cap_stream);
     if (p->s_in) cudaStreamDestroy(p->s_in);
     if (p->s_out) cudaStreamDestroy(p->s_out);
     for (int i = 0; i < die_pipeline::NBUF; ++i) {
@@ -670,8 +816,34 @@ extern "C" die_status_t die_pipeline_run_device_many(die_pipeline_t* p, int32_t 
                                                      double now0, double now_step, float* out, uint8_t* hit_out,
                                                      int32_t out_ring, die_stream_t stream) {
     if (!p || n_batches < 0 || out_ring < 1) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_device_many: bad arguments");
+    if (B < 0 || B > p->cfg.max_batch) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_device_many: bad B");
+    if (B == 0 || n_batches == 0) return DIE_OK;
+    if (!key_off || !payload || !out) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_run_device_many: null buffer");
     const size_t in_row = (size_t)B * p->cfg.dim_in, out_row = (size_t)B * p->cfg.dim_out;
-    for (int32_t j = 0; j < n_batches; ++j) {
+    int32_t j = 0;
+    const int K = p->graph_steps;
+    if (graph_fits(p, B, K) && !prof_active()) {
+        QueueDesc d;
+        memset(&d, 0, sizeof(d));
+        d.key_bytes = key_bytes;
+        d.key_off = key_off;
+        d.payload = payload;
+        d.out = out;
+        d.hit = hit_out ? hit_out : p->code;
+        d.key_bytes_stride = key_bytes_stride;
+        d.key_off_stride = key_off_stride;
+        d.payload_stride = (long long)in_row;
+        d.out_stride = (long long)out_row;
+        d.hit_stride = hit_out ? B : 0;
+        d.ring = out_ring;
+        d.now0 = now0;
+        d.now_step = now_step;
+        for (; n_batches - j >= K; j += K) {
+            d.j0 = j;
+            DIE_TRY(replay_fast(p, d, p->qdesc, true, p->digests, B, nullptr, K, static_cast<cudaStream_t>(stream)));
+        }
+    }
+    for (; j < n_batches; ++j) {
         const int r = j % out_ring;
         DIE_TRY(die_pipeline_run_device(p, key_bytes + (size_t)j * key_bytes_stride, key_off + (size_t)j * key_off_stride,
                                         B, payload + (size_t)j * in_row, now0 + j * now_step, out + (size_t)r * out_row,

@@ -12,6 +12,66 @@ struct PipeCtrl {
 
 namespace die {
 
+// ---- what changes from one flushed batch to the next ---------------------------------------------------
+// A step's kernels take a StepRef.  Launched from a stream, the values travel in the launch itself (`a`).
+// Replayed from a CUDA graph, the launch arguments are frozen, so node i of the graph derives its values
+// from a device-resident QueueDesc the host rewrites before every replay (`q`, `i`): the batches of a queue
+// sit at regular strides, the injected clock advances by a fixed step and every batch consumes the same
+// number of LRU stamps, so one descriptor describes all K steps of a replay.
+struct StepArgs {
+    KvView kv;
+    const uint8_t* key_bytes;
+    const int64_t* key_off;
+    const float* payload;
+    float* out;
+    uint8_t* code;  // hit / miss per request
+    double now;
+    unsigned long long t_get, t_set;  // first LRU stamp of the batch's gets / of its sets
+};
+
+struct QueueDesc {
+    KvView kv;
+    const uint8_t* key_bytes;
+    const int64_t* key_off;
+    const float* payload;
+    float* out;
+    uint8_t* hit;
+    long long key_bytes_stride, key_off_stride, payload_stride, out_stride, hit_stride;  // elements per batch
+    long long j0;  // queue index of the replay's first batch
+    int ring;      // out / hit slots, reused round-robin
+    int batch;     // stamps per get (= per set) pass of one step
+    double now0, now_step;
+    unsigned long long tail0;  // LRU stamp of the replay's first op
+    unsigned int epoch0[2];    // exchange only: barrier epoch of each lane before the replay
+};
+
+struct StepRef {
+    const QueueDesc* q;  // nullptr: use `a`
+    int i;               // step index inside the replay
+    StepArgs a;
+};
+
+#ifdef __CUDACC__
+__device__ __forceinline__ StepArgs step_resolve(const StepRef& r) {
+    if (!r.q) return r.a;
+    const QueueDesc& q = *r.q;
+    const long long j = q.j0 + r.i;
+    const long long slot = j % q.ring;
+    StepArgs a;
+    a.kv = q.kv;
+    // buffers the descriptor leaves null are fixed ones, frozen in the launch (the exchange's lane buffers)
+    a.key_bytes = q.key_bytes ? q.key_bytes + j * q.key_bytes_stride : r.a.key_bytes;
+    a.key_off = q.key_off ? q.key_off + j * q.key_off_stride : r.a.key_off;
+    a.payload = q.payload ? q.payload + j * q.payload_stride : r.a.payload;
+    a.out = q.out ? q.out + slot * q.out_stride : r.a.out;
+    a.code = q.hit ? q.hit + slot * q.hit_stride : r.a.code;
+    a.now = __dadd_rn(q.now0, __dmul_rn((double)j, q.now_step));  // the host's now0 + j * now_step, no fma
+    a.t_get = q.tail0 + 2ull * (unsigned long long)q.batch * (unsigned long long)r.i;
+    a.t_set = a.t_get + (unsigned long long)q.batch;
+    return a;
+}
+#endif
+
 constexpr int PT = 256;  // threads per CTA of the pipeline kernels (== ROUTE_THREADS)
 constexpr int WCHUNK = 1024;  // log records per victim-window chunk
 

@@ -35,14 +35,16 @@ def _worker(rank, world, port, ret, mode="nccl"):
         from die.exchange import PeerDispatcher, ShardedDispatcher
         from oracle import models
         from oracle.pipeline import OraclePipeline
-        B, D, steps, max_size, ttl = 1024, 128, 8, 3000, 7.0
+        B, D, steps, max_size, ttl, n_ids = 1024, 128, 8, 3000, 7.0, 5000
+        if mode == "peer_queue":  # a table large enough for the captured replays of 8 steps, filled to eviction
+            steps, max_size, ttl, n_ids = 93, 60000, 60.0, 400000
         rng = np.random.default_rng(5)
         w = (rng.standard_normal((D, D)) / np.sqrt(D)).astype(np.float32)
         b = rng.standard_normal(D).astype(np.float32)
         if mode == "nccl":
             disp = ShardedDispatcher(world, rank, max_size, B, D, w, b, ttl, model="linear")
         else:
-            disp = PeerDispatcher(world, rank, max_size, B, D, w, b, ttl, model="linear", single_call=mode == "peer_one_call")
+            disp = PeerDispatcher(world, rank, max_size, B, D, w, b, ttl, model="linear", single_call=mode != "peer_phases")
 
         def fn(rows):
             y = models.linear_f64(np.stack(rows), w, b) if rows else []
@@ -50,6 +52,29 @@ def _worker(rank, world, port, ret, mode="nccl"):
 
         ref = OraclePipeline(world, max_size, ttl, fn)
         now = 3.0
+        if mode == "peer_queue":
+            # a queue of batches through the two-lane step: neighbouring steps overlap on the GPU, the KV
+            # table must still see them in step order (evictions and TTL expiry depend on it)
+            dt = 0.9
+            batches = []
+            for _ in range(steps):
+                batches.append([(["user-%010d" % i for i in rng.integers(0, n_ids, B)],
+                                 rng.standard_normal((B, D)).astype(np.float32)) for _r in range(world)])
+            kb = [ops.KeyBatch.from_strings(bt[rank][0]) for bt in batches]
+            key_bytes = torch.stack([k.key_bytes for k in kb])
+            key_off = torch.stack([k.key_off for k in kb])
+            pay = torch.from_numpy(np.stack([bt[rank][1] for bt in batches])).cuda()
+            out = torch.empty((steps, B, D), dtype=torch.float32, device="cuda")
+            hit = torch.empty((steps, B), dtype=torch.uint8, device="cuda")
+            disp.step_many(key_bytes, key_off, pay, now, dt, out, hit)
+            torch.cuda.synchronize()
+            for j, bt in enumerate(batches):
+                want = ref.process_exchange([(k, [r for r in p]) for k, p in bt], now + j * dt)[rank]
+                assert hit[j].tolist() == want["hit"], j
+                o = np.stack(want["out"])
+                assert np.all(np.abs(out[j].cpu().numpy() - o) <= 1e-5 * np.abs(o) + 2e-4), j
+            assert ref.state()[rank]["evictions"] > 0
+            steps = 0
         for _ in range(steps):
             now += float(rng.choice([0.5, 2.0, 4.0]))
             per_rank = []
@@ -71,7 +96,7 @@ def _worker(rank, world, port, ret, mode="nccl"):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (run with gpurun --gpus 2)")
-@pytest.mark.parametrize("mode", ["nccl", "peer_phases", "peer_one_call"])
+@pytest.mark.parametrize("mode", ["nccl", "peer_phases", "peer_one_call", "peer_queue"])
 def test_two_gpu_sharded_dispatch_matches_oracle(mode):
     import torch.multiprocessing as mp
     world = 2

@@ -157,3 +157,44 @@ def test_queue_entry_points_equal_per_batch_calls():
     c.run_host_many(kbp, torch.from_numpy(off).pin_memory(), torch.from_numpy(x).pin_memory(), 5.0, 1.5, hout, hhit)
     assert np.array_equal(hout.numpy(), np.stack(want_out)) and np.array_equal(hhit.numpy(), np.stack(want_hit))
     assert a.kv.stats() == b.kv.stats() == c.kv.stats()
+
+
+@pytest.mark.parametrize("model", ["echo", "linear_tf32"])
+def test_graph_replayed_queue_equals_stream_launched_steps(model):
+    """A long queue goes through captured replays of 8 steps (csrc/pipeline.cu replay_fast) whose per-step
+    arguments come from a device-resident descriptor; a twin pipeline gets the same batches one stream-launched
+    call at a time.  Results, counters and the whole table (LRU order, timestamps) must be identical, through
+    evictions, TTL expiry and table maintenance."""
+    from die import ops
+    from die.pipeline import DispatchPipeline
+    rng = np.random.default_rng(33)
+    n, B, D, max_size = 141, 256, 32, 20000  # 17 replays + 5 stream steps; the table fills after ~100 batches
+    ids = rng.integers(0, 60000, (n, B))
+    ids[:, :16] = ids[:, 16:32]              # duplicate keys inside every batch
+    kb = np.stack([np.frombuffer("".join("q%08d" % i for i in row).encode(), dtype=np.uint8) for row in ids])
+    off = torch.from_numpy(np.arange(B + 1, dtype=np.int64) * 9).cuda()
+    x = rng.standard_normal((n, B, D)).astype(np.float32)
+    w = (rng.standard_normal((D, D)) / np.sqrt(D)).astype(np.float32)
+    bias = rng.standard_normal(D).astype(np.float32)
+    a = DispatchPipeline(max_size, B, D, D, model, w, bias, default_ttl=150.0)
+    b = DispatchPipeline(max_size, B, D, D, model, w, bias, default_ttl=150.0)
+    kd, xd = torch.from_numpy(kb).cuda(), torch.from_numpy(x).cuda()
+    out = torch.empty((n, B, D), device="cuda")
+    hit = torch.empty((n, B), dtype=torch.uint8, device="cuda")
+    launches0 = a._lib.die_launch_count()
+    a.run_device_many(kd, off, xd, 5.0, 1.5, out, hit)
+    torch.cuda.synchronize()
+    assert a._lib.die_launch_count() - launches0 >= 3 * n
+    for j in range(n):
+        o, h = b.run_device(ops.KeyBatch(kd[j], off), xd[j], 5.0 + j * 1.5)
+        assert torch.equal(h, hit[j]), j
+        assert torch.equal(o, out[j]), j
+    sa, sb = a.kv.stats(), b.kv.stats()
+    for k in ("hits", "misses", "evictions", "size"):
+        assert sa[k] == sb[k], k
+    assert sa["evictions"] > 0 and sa["hits"] > 0
+    da, db = a.kv.dump(), b.kv.dump()
+    for name in da:
+        if name == "values":
+            continue  # result-row handles come from a free list: which row a key gets is not part of the contract
+        assert torch.equal(da[name], db[name]), name
