@@ -152,6 +152,10 @@ class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
         self.samples, self.reasons, self.stop_flag, self.max_mhz = [], set(), False, None
+        # the recipe's period (nvidia-smi -lms 200); the first sample is taken as soon as the region starts.
+        # NVML queries are not free: on some boxes one query stalls graph launches for over a millisecond
+        self.period = float(os.environ.get("DIE_BENCH_SAMPLER_MS", "200")) / 1e3
+        self.query_s = 0.0
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -162,7 +166,7 @@ class ClockSampler(threading.Thread):
             self.nv = None
 
     def run(self):
-        if self.nv is None:
+        if self.nv is None or self.period <= 0:
             return
         nv = self.nv
         names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
@@ -171,6 +175,7 @@ class ClockSampler(threading.Thread):
                  "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
         while not self.stop_flag:
             try:
+                t_q = time.perf_counter()
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
                 try:
                     mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
@@ -179,16 +184,20 @@ class ClockSampler(threading.Thread):
                 for k, bit in names.items():
                     if mask & bit:
                         self.reasons.add(k)
+                self.query_s += time.perf_counter() - t_q
             except Exception:  # noqa: BLE001
                 pass
-            time.sleep(0.002)
+            t_next = time.perf_counter() + self.period
+            while not self.stop_flag and time.perf_counter() < t_next:
+                time.sleep(0.005)
 
     def result(self):
         self.stop_flag = True
         self.join(timeout=1.0)
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+                "samples": len(s), "period_ms": 1e3 * self.period,
+                "nvml_ms_per_sample": round(1e3 * self.query_s / len(s), 3) if s else None}
 
 
 # ----------------------------------------------------------------------------------------------------------------

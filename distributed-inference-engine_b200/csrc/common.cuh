@@ -13,12 +13,14 @@ namespace die {
 enum Stage {
     ST_ROUTE = 0, ST_KV_GET, ST_KV_CONTAINS, ST_KV_DELETE, ST_KV_PURGE, ST_KV_PRECHECK, ST_KV_WINDOW, ST_KV_CLAIM,
     ST_KV_FINALIZE, ST_KV_EVICT, ST_KV_MAINT, ST_MISS_SCAN, ST_PACK_HITS, ST_MODEL, ST_UNPACK_STORE, ST_PACK,
-    ST_UNPACK, ST_BUCKET, ST_XCHG, ST_COUNT
+    ST_UNPACK, ST_BUCKET, ST_XCHG, ST_XCHG_BARRIER, ST_XCHG_COMPACT, ST_XCHG_RETURN, ST_XCHG_SCATTER, ST_COUNT
 };
 void prof_before(int stage, cudaStream_t s);
 void prof_after(int stage, cudaStream_t s);
 bool prof_active();                   // per-launch events are being recorded: replays from graphs are off
+unsigned long long* trace_buffer();   // device log of replayed kernels' start times, or nullptr (diagnostics)
 char* err_buf();                       // thread-local, 512 bytes
+void count_replay();                   // graph replays launched (tests check that the replay path ran)
 void count_launch(unsigned n = 1);     // gpu_launches accounting for bench.py
 
 #define DIE_FAIL(code, ...)                                   \

@@ -31,31 +31,35 @@ __device__ __forceinline__ int bucket_of(const long long* off, int world, long l
     return d;  // == world for unroutable requests
 }
 
+// All four data-movement kernels give one warp to one request row (rv = 1 + vdim 16-byte vectors): the row's
+// bucket, rank and permutation entry are looked up once per warp, the lanes move the vectors.
+
 // PACK + SEND: send position j (bucket order) = request perm[j]; row -> peer window of its owner.
+// No fence here: the stores are complete at system scope when the kernel ends, and the barrier kernel that
+// follows on the stream publishes them (fence + st.release.sys).
 __global__ void __launch_bounds__(256)
 xchg_dispatch_kernel(StepRef sr, const int4* __restrict__ digests, const int32_t* __restrict__ perm,
                      const int64_t* __restrict__ offsets, int B, int vdim /*payload vectors per row*/, int world, int rank,
                      int cap, PeerPtrs rows, PeerPtrs counts) {
     __shared__ long long s_off[XCHG_MAX_WORLD + 2];
     const int4* __restrict__ payload = reinterpret_cast<const int4*>(step_resolve(sr).payload);
+    trace_mark(sr, TR_DISPATCH);
     if (threadIdx.x < world + 2) s_off[threadIdx.x] = offsets[threadIdx.x];
     __syncthreads();
     const int rv = vdim + 1;  // vectors per window row
     const long long n_send = s_off[world];
-    const long long total = n_send * rv;
     if (blockIdx.x == 0 && threadIdx.x < world)
         static_cast<int32_t*>(counts.p[threadIdx.x])[rank] = (int32_t)(s_off[threadIdx.x + 1] - s_off[threadIdx.x]);
-    for (long long v = blockIdx.x * 256ll + threadIdx.x; v < total; v += (long long)gridDim.x * 256) {
-        const long long j = v / rv;
-        const int c = (int)(v - j * rv);
+    const int lane = threadIdx.x & 31;
+    const long long warps = (long long)gridDim.x * 8;
+    for (long long j = blockIdx.x * 8ll + (threadIdx.x >> 5); j < n_send; j += warps) {
         const int d = bucket_of(s_off, world, j);
         const long long i = j - s_off[d];
         const int q = perm[j];
-        const int4 val = c == 0 ? digests[q] : ldg_stream(payload + (long long)q * vdim + (c - 1));
-        int4* dst = static_cast<int4*>(rows.p[d]) + ((long long)rank * cap + i) * rv + c;
-        *dst = val;  // NVLink store into the owner's HBM
+        int4* dst = static_cast<int4*>(rows.p[d]) + ((long long)rank * cap + i) * rv;  // NVLink stores into the owner's HBM
+        if (lane == 0) dst[0] = digests[q];
+        for (int c = lane; c < vdim; c += 32) dst[1 + c] = ldg_stream(payload + (long long)q * vdim + c);
     }
-    __threadfence_system();
 }
 
 // Owner: regions -> contiguous digests / payload in (source rank, request) order + the device-side count.
@@ -83,18 +87,14 @@ xchg_compact_kernel(const int4* __restrict__ rows, const int32_t* __restrict__ c
     }
     __syncthreads();
     const int rv = vdim + 1;
-    const long long total = s_pre[world] * rv;
-    for (long long v = blockIdx.x * 256ll + threadIdx.x; v < total; v += (long long)gridDim.x * 256) {
-        const long long g = v / rv;
-        const int c = (int)(v - g * rv);
+    const int lane = threadIdx.x & 31;
+    const long long warps = (long long)gridDim.x * 8;
+    for (long long g = blockIdx.x * 8ll + (threadIdx.x >> 5); g < s_pre[world]; g += warps) {
         int s = 0;
         while (g >= s_pre[s + 1]) ++s;
-        const long long i = g - s_pre[s];
-        const int4 val = __ldcg(rows + ((long long)s * cap + i) * rv + c);  // written by a peer this step: read at L2
-        if (c == 0)
-            digests_out[g] = val;
-        else
-            stg_stream(payload_out + g * vdim + (c - 1), val);
+        const int4* src = rows + ((long long)s * cap + (g - s_pre[s])) * rv;  // written by a peer this step: read at L2
+        if (lane == 0) digests_out[g] = __ldcg(src);
+        for (int c = lane; c < vdim; c += 32) stg_stream(payload_out + g * vdim + c, __ldcg(src + 1 + c));
     }
 }
 
@@ -106,21 +106,15 @@ xchg_return_kernel(const int4* __restrict__ out, const uint8_t* __restrict__ hit
     if (threadIdx.x <= world) s_pre[threadIdx.x] = prefix[threadIdx.x];
     __syncthreads();
     const int rv = vout + 1;
-    const long long total = (long long)s_pre[world] * rv;
-    for (long long v = blockIdx.x * 256ll + threadIdx.x; v < total; v += (long long)gridDim.x * 256) {
-        const long long g = v / rv;
-        const int c = (int)(v - g * rv);
+    const int lane = threadIdx.x & 31;
+    const long long warps = (long long)gridDim.x * 8;
+    for (long long g = blockIdx.x * 8ll + (threadIdx.x >> 5); g < s_pre[world]; g += warps) {
         int s = 0;
         while (g >= s_pre[s + 1]) ++s;
-        const long long i = g - s_pre[s];
-        int4 val;
-        if (c < vout)
-            val = ldg_stream(out + g * vout + c);
-        else
-            val = make_int4((int)hit[g], 0, 0, 0);
-        *(static_cast<int4*>(back.p[s]) + ((long long)rank * cap + i) * rv + c) = val;
+        int4* dst = static_cast<int4*>(back.p[s]) + ((long long)rank * cap + (g - s_pre[s])) * rv;
+        for (int c = lane; c < vout; c += 32) dst[c] = ldg_stream(out + g * vout + c);
+        if (lane == 0) dst[vout] = make_int4((int)hit[g], 0, 0, 0);
     }
-    __threadfence_system();
 }
 
 // Source: return window -> results in request order (UNPACK of the exchange).
@@ -129,23 +123,22 @@ xchg_scatter_kernel(StepRef sr, const int4* __restrict__ back, const int32_t* __
                     const int64_t* __restrict__ offsets, int B, int world, int cap, int vout) {
     __shared__ long long s_off[XCHG_MAX_WORLD + 2];
     const StepArgs a = step_resolve(sr);
+    trace_mark(sr, TR_SCATTER);
     int4* __restrict__ out = reinterpret_cast<int4*>(a.out);
     uint8_t* __restrict__ hit = a.code;
     if (threadIdx.x < world + 2) s_off[threadIdx.x] = offsets[threadIdx.x];
     __syncthreads();
     const int rv = vout + 1;
-    const long long total = (long long)B * rv;
-    for (long long v = blockIdx.x * 256ll + threadIdx.x; v < total; v += (long long)gridDim.x * 256) {
-        const long long j = v / rv;
-        const int c = (int)(v - j * rv);
+    const int lane = threadIdx.x & 31;
+    const long long warps = (long long)gridDim.x * 8;
+    for (long long j = blockIdx.x * 8ll + (threadIdx.x >> 5); j < B; j += warps) {
         const int d = bucket_of(s_off, world, j);
         const int q = perm[j];
-        int4 val = make_int4(0, 0, 0, 0);  // requests the router returned None for have no result
-        if (d < world) val = __ldcg(back + ((long long)d * cap + (j - s_off[d])) * rv + c);  // peer-written: read at L2
-        if (c < vout)
-            stg_stream(out + (long long)q * vout + c, val);
-        else
-            hit[q] = (uint8_t)val.x;
+        const int4* src = d < world ? back + ((long long)d * cap + (j - s_off[d])) * rv : nullptr;  // peer-written: read at L2
+        // requests the router returned None for have no result
+        for (int c = lane; c < vout; c += 32)
+            stg_stream(out + (long long)q * vout + c, src ? __ldcg(src + c) : make_int4(0, 0, 0, 0));
+        if (lane == 0) hit[q] = src ? (uint8_t)__ldcg(src + vout).x : (uint8_t)0;
     }
 }
 
@@ -154,6 +147,7 @@ __global__ void __launch_bounds__(ROUTE_THREADS)
 xchg_route_kernel(StepRef sr, int B, int world, int32_t* __restrict__ shard_out, uint4* __restrict__ digests) {
     __shared__ __align__(16) uint8_t stage[ROUTE_STAGE_BYTES + 32];
     const StepArgs a = step_resolve(sr);
+    trace_mark(sr, TR_ROUTE);
     const Md5State st = cta_hash_keys(a.key_bytes, a.key_off, B, stage);
     const int i = blockIdx.x * ROUTE_THREADS + threadIdx.x;
     if (i < B) {
@@ -162,8 +156,8 @@ xchg_route_kernel(StepRef sr, int B, int world, int32_t* __restrict__ shard_out,
     }
 }
 
-static int grid_for_vectors(long long items) {
-    const long long blocks = (items + 255) / 256;
+static int grid_for_rows(long long rows) {  // 8 warps per CTA, one row per warp and pass
+    const long long blocks = (rows + 7) / 8;
     const long long cap = (long long)num_sms() * 8;
     return (int)(blocks < 1 ? 1 : (blocks < cap ? blocks : cap));
 }
@@ -193,7 +187,7 @@ extern "C" die_status_t die_xchg_dispatch(const uint32_t* digests, const float* 
     StepRef sr;
     memset(&sr, 0, sizeof(sr));
     sr.a.payload = payload;
-    DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_vectors((long long)B * (vdim + 1)), 256, 0, s>>>(
+    DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_rows(B), 256, 0, s>>>(
         sr, reinterpret_cast<const int4*>(digests), perm, offsets, B, vdim, world, rank, cap, rows, counts));
     return DIE_OK;
 }
@@ -206,7 +200,7 @@ extern "C" die_status_t die_xchg_compact(const float* rows, const int32_t* count
         DIE_FAIL(DIE_ERR_INVALID, "die_xchg_compact: bad sizes");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int vdim = dim / 4;
-    DIE_LAUNCH(ST_XCHG, s, xchg_compact_kernel<<<grid_for_vectors((long long)2 * cap * (vdim + 1)), 256, 0, s>>>(
+    DIE_LAUNCH(ST_XCHG_COMPACT, s, xchg_compact_kernel<<<grid_for_rows(2ll * cap), 256, 0, s>>>(
         reinterpret_cast<const int4*>(rows), counts, world, cap, vdim, bmax, reinterpret_cast<int4*>(digests_out),
         reinterpret_cast<int4*>(payload_out), n_out, prefix_out, nullptr));
     return DIE_OK;
@@ -220,7 +214,7 @@ extern "C" die_status_t die_xchg_return(const float* out, const uint8_t* hit, co
     DIE_TRY(fill_peers(&back, peer_back, world, "back"));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int vout = dim_out / 4;
-    DIE_LAUNCH(ST_XCHG, s, xchg_return_kernel<<<grid_for_vectors((long long)2 * cap * (vout + 1)), 256, 0, s>>>(
+    DIE_LAUNCH(ST_XCHG_RETURN, s, xchg_return_kernel<<<grid_for_rows(2ll * cap), 256, 0, s>>>(
         reinterpret_cast<const int4*>(out), hit, prefix, world, rank, cap, vout, back));
     return DIE_OK;
 }
@@ -237,7 +231,7 @@ extern "C" die_status_t die_xchg_scatter(const float* back, const int32_t* perm,
     memset(&sr, 0, sizeof(sr));
     sr.a.out = out;
     sr.a.code = hit;
-    DIE_LAUNCH(ST_XCHG, s, xchg_scatter_kernel<<<grid_for_vectors((long long)B * (vout + 1)), 256, 0, s>>>(
+    DIE_LAUNCH(ST_XCHG_SCATTER, s, xchg_scatter_kernel<<<grid_for_rows(B), 256, 0, s>>>(
         sr, reinterpret_cast<const int4*>(back), perm, offsets, B, world, cap, vout));
     return DIE_OK;
 }
@@ -257,6 +251,7 @@ __global__ void xchg_barrier_kernel(PeerPtrs flags, unsigned int* my_flags, int 
     const int p = threadIdx.x;
     if (p >= world) return;
     if (q) epoch += q->epoch0[lane];
+    if (p == 0) trace_mark_q(q, (int)epoch, TR_BAR_IN);
     __threadfence_system();
     unsigned int* dst = static_cast<unsigned int*>(flags.p[p]) + rank;
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst), "r"(epoch) : "memory");
@@ -273,6 +268,8 @@ __global__ void xchg_barrier_kernel(PeerPtrs flags, unsigned int* my_flags, int 
             break;
         }
     }
+    __syncwarp();
+    if (p == 0) trace_mark_q(q, (int)epoch, TR_BAR_OUT);
 }
 
 }  // namespace die
@@ -384,7 +381,7 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
     DIE_CUDA(cudaMemset(x->error_flag, 0, sizeof(unsigned int)));
     DIE_CUDA(cudaMalloc(&x->qdesc, 2 * sizeof(QueueDesc)));
     DIE_CUDA(cudaStreamCreateWithFlags(&x->cap_stream, cudaStreamNonBlocking));
-    x->graph_steps = 8;
+    x->graph_steps = 16;
     if (const char* e = getenv("DIE_GRAPH_STEPS")) x->graph_steps = atoi(e);
     *out = x;
     return DIE_OK;
@@ -414,7 +411,7 @@ extern "C" die_status_t die_xchg_destroy(die_xchg_t* x) {
 // qd != nullptr: the launch is being captured for replay; `epoch_off` is the barrier's rank on its lane inside
 // the replay and the lane's epoch before the replay comes from the descriptor.
 static die_status_t xchg_barrier(die_xchg* x, XchgLane& L, int lane, const QueueDesc* qd, unsigned int epoch) {
-    DIE_LAUNCH(ST_XCHG, L.stream, xchg_barrier_kernel<<<1, 32, 0, L.stream>>>(L.flags, L.my_flags, x->world, x->rank, epoch,
+    DIE_LAUNCH(ST_XCHG_BARRIER, L.stream, xchg_barrier_kernel<<<1, 32, 0, L.stream>>>(L.flags, L.my_flags, x->world, x->rank, epoch,
                                                                              qd, lane, x->error_flag));
     return DIE_OK;
 }
@@ -434,16 +431,16 @@ static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user,
     DIE_LAUNCH(ST_ROUTE, s, xchg_route_kernel<<<ceil_div(B, ROUTE_THREADS), ROUTE_THREADS, 0, s>>>(
         user, B, W, shard, reinterpret_cast<uint4*>(L.digests)));
     DIE_TRY(die_bucket_by_shard(shard, B, W, L.offsets, L.perm, L.pos, static_cast<die_stream_t>(s)));
-    DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_vectors((long long)B * (vdim + 1)), 256, 0, s>>>(
+    DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_rows(B), 256, 0, s>>>(
         user, reinterpret_cast<const int4*>(L.digests), L.perm, L.offsets, B, vdim, W, x->rank, x->cap, L.rows, L.counts));
     DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first));  // every rank's rows have landed in their owners' windows
-    DIE_LAUNCH(ST_XCHG, s, xchg_compact_kernel<<<grid_for_vectors((long long)2 * x->cap * (vdim + 1)), 256, 0, s>>>(
+    DIE_LAUNCH(ST_XCHG_COMPACT, s, xchg_compact_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, s>>>(
         reinterpret_cast<const int4*>(L.my_rows), L.my_cnt, W, x->cap, vdim, (long long)x->bmax,
         reinterpret_cast<int4*>(L.recv_dig), reinterpret_cast<int4*>(L.recv_pay), L.n_dev, L.prefix, x->error_flag));
     if (x->owner_pending) DIE_CUDA(cudaStreamWaitEvent(s, x->owner_done, 0));  // the table sees batches in step order
     if (reserve_now) {
         unsigned long long tail0;
-        DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, 1, s, &owner.a.kv, &tail0));
+        DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, 1, s, &owner.a.kv, &tail0, nullptr));
         owner.a.now = *reserve_now;
         owner.a.t_get = tail0;
         owner.a.t_set = tail0 + (unsigned long long)x->bmax;
@@ -454,10 +451,10 @@ static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user,
     DIE_TRY(pipeline_owner_launch(x->pipe, owner, L.recv_dig, x->bmax, L.n_dev, s));
     DIE_CUDA(cudaEventRecord(x->owner_done, s));
     x->owner_pending = true;
-    DIE_LAUNCH(ST_XCHG, s, xchg_return_kernel<<<grid_for_vectors((long long)2 * x->cap * (vdim + 1)), 256, 0, s>>>(
+    DIE_LAUNCH(ST_XCHG_RETURN, s, xchg_return_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, s>>>(
         reinterpret_cast<const int4*>(L.recv_out), L.recv_hit, L.prefix, W, x->rank, x->cap, vdim, L.back));
     DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first + 1));  // every owner's results are back in the sources' windows
-    DIE_LAUNCH(ST_XCHG, s, xchg_scatter_kernel<<<grid_for_vectors((long long)B * (vdim + 1)), 256, 0, s>>>(
+    DIE_LAUNCH(ST_XCHG_SCATTER, s, xchg_scatter_kernel<<<grid_for_rows(B), 256, 0, s>>>(
         user, reinterpret_cast<const int4*>(L.my_back), L.perm, L.offsets, B, W, x->cap, vdim));
     return DIE_OK;
 }
@@ -547,9 +544,10 @@ static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_
     return DIE_OK;
 }
 
-__global__ void xchg_desc_set_kernel(QueueDesc* dst, QueueDesc user, QueueDesc owner) {
+__global__ void xchg_desc_set_kernel(QueueDesc* dst, QueueDesc user, QueueDesc owner, KvMirrorArgs m) {
     dst[0] = user;
     dst[1] = owner;
+    kv_mirror_write(m.st, m.m, m.ops_seen, m.gen, m.seq);  // state before this replay -> the host's bounds
 }
 
 // One flushed batch ingested on this rank; results in request order.  Every rank of the group must make the
@@ -603,13 +601,16 @@ extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, con
             cudaGraphExec_t exec;
             DIE_TRY(xchg_graph_get(x, B, K, &exec));
             unsigned long long tail0;
-            DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, K, user, &dw.kv, &tail0));
+            KvMirrorArgs mirror;
+            DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, K, user, &dw.kv, &tail0, &mirror));
             dw.tail0 = tail0;
             du.j0 = dw.j0 = j;
             for (int l = 0; l < 2; ++l) du.epoch0[l] = x->lane[l].epoch;
-            xchg_desc_set_kernel<<<1, 1, 0, user>>>(x->qdesc, du, dw);
+            du.trace = dw.trace = trace_buffer();
+            xchg_desc_set_kernel<<<1, 1, 0, user>>>(x->qdesc, du, dw, mirror);
             DIE_LAUNCH_CHECK();
             DIE_CUDA(cudaGraphLaunch(exec, user));
+            count_replay();
             count_launch((unsigned)(K * (8 + pipeline_launches_per_step(x->pipe))));
             const int lane0 = (int)(x->steps & 1);
             x->lane[lane0].epoch += 2u * (unsigned)((K + 1) / 2);

@@ -50,6 +50,13 @@ struct KvState {
     unsigned long long hit_part[16][8], miss_part[16][8];
 };
 
+// Snapshot of the counters the host's maintenance decisions need, written by the device into pinned host
+// memory at every replay boundary (seq0 first, seq1 last: the host retries on a torn read).  With it the host
+// refreshes its conservative bounds without synchronising the stream.
+struct KvMirror {
+    unsigned long long seq0, head, size, n_tomb, ops_seen, gen, seq1;
+};
+
 struct KvView {
     Slot* slots;
     uint32_t* log;
@@ -247,6 +254,12 @@ struct die_kv {
     int32_t* op_slot;     // scratch [op_cap]
     uint64_t op_cap;
     uint64_t dropped_prefix;  // dropped values written by earlier chunks of the last set batch
+    uint32_t* log_spare;      // second LRU-log buffer, allocated at the first compaction and reused
+    unsigned long long* n_kept_dev;
+    die::KvMirror* mirror;    // pinned + mapped host memory (device-visible at the same address)
+    uint64_t ops_enq;         // insert ops reserved so far (monotone)
+    uint64_t mirror_gen;      // bumped by every maintenance: older snapshots describe a table that is gone
+    uint64_t mirror_seq;
 };
 
 namespace die {
@@ -268,6 +281,31 @@ inline KvView view_of(const die_kv* kv) {
 // min_batch: the table is sized so that one launch sequence can take a batch of this many ops.
 die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_rows, uint64_t min_batch,
                             die_kv** out);
+
+#ifdef __CUDACC__
+// One thread: snapshot -> pinned host mirror.  ops_seen = insert ops the host had reserved when it enqueued
+// the kernel this runs in (all of them are stream-ordered before it).
+__device__ __forceinline__ void kv_mirror_write(const KvState* st, KvMirror* m, unsigned long long ops_seen,
+                                                unsigned long long gen, unsigned long long seq) {
+    volatile KvMirror* vm = m;
+    vm->seq0 = seq;
+    __threadfence_system();
+    vm->head = st->head;
+    vm->size = st->size;
+    vm->n_tomb = st->n_tomb;
+    vm->ops_seen = ops_seen;
+    vm->gen = gen;
+    __threadfence_system();
+    vm->seq1 = seq;
+}
+#endif
+// Arguments of kv_mirror_write for a kernel enqueued now.
+struct KvMirrorArgs {
+    const KvState* st;
+    KvMirror* m;
+    unsigned long long ops_seen, gen, seq;
+};
+KvMirrorArgs kv_mirror_args(die_kv* kv);
 
 // Host-side guard run before a batch of n ops: keeps the LRU ring and the EMPTY-slot reserve safe
 // using conservative host bounds (synchronises only when a bound is about to be crossed).

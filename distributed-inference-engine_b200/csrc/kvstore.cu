@@ -3,6 +3,8 @@
 #include <algorithm>
 #include <vector>
 
+#include <atomic>
+
 #include "kv_internal.cuh"
 
 namespace die {
@@ -514,6 +516,10 @@ die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_ro
     DIE_CUDA(cudaMemset(kv->slots, 0, kv->capacity * sizeof(Slot)));
     DIE_CUDA(cudaMemset(kv->log, 0xff, kv->ring_cap * sizeof(uint32_t)));
     DIE_CUDA(cudaMemset(kv->st, 0, sizeof(KvState)));
+    DIE_CUDA(cudaMalloc(&kv->n_kept_dev, sizeof(unsigned long long)));
+    DIE_CUDA(cudaHostAlloc(&kv->mirror, sizeof(KvMirror), cudaHostAllocMapped | cudaHostAllocPortable));
+    memset(kv->mirror, 0, sizeof(KvMirror));
+    kv->mirror_gen = 1;
     DIE_LAUNCH(ST_KV_MAINT, (cudaStream_t)0, kv_state_init_kernel<<<n_rows ? 256 : 1, 256>>>(view_of(kv), 1ull, n_rows));
     DIE_CUDA(cudaDeviceSynchronize());
     *out = kv;
@@ -537,18 +543,18 @@ static die_status_t kv_maintain(die_kv* kv, int force, cudaStream_t s) {
     DIE_CUDA(cudaStreamSynchronize(s));
     kv->head_lb = h.head;
     const uint64_t span = kv->tail - h.head;
-    if (force || span > kv->ring_cap / 2) {
-        uint32_t* new_log = nullptr;
-        unsigned long long* n_kept = nullptr;
-        DIE_CUDA(cudaMalloc(&new_log, kv->ring_cap * sizeof(uint32_t)));
-        DIE_CUDA(cudaMalloc(&n_kept, sizeof(unsigned long long)));
+    // compaction walks the whole span in one CTA (milliseconds for millions of records): only when the ring is
+    // really filling up.  A table that evicts consumes its log as fast as it appends and never gets here.
+    if (force || span > kv->ring_cap / 4 * 3) {
+        uint32_t* new_log = kv->log_spare;  // kept between compactions: no cudaMalloc / cudaFree on the serving path
+        unsigned long long* n_kept = kv->n_kept_dev;
+        if (!new_log) DIE_CUDA(cudaMalloc(&new_log, kv->ring_cap * sizeof(uint32_t)));
         DIE_CUDA(cudaMemsetAsync(new_log, 0xff, kv->ring_cap * sizeof(uint32_t), s));
         DIE_LAUNCH(ST_KV_MAINT, s, kv_compact_kernel<<<1, WIN_THREADS, 0, s>>>(view_of(kv), new_log, kv->tail, n_kept));
         unsigned long long kept = 0;
         DIE_CUDA(cudaMemcpyAsync(&kept, n_kept, sizeof(kept), cudaMemcpyDeviceToHost, s));
         DIE_CUDA(cudaStreamSynchronize(s));
-        cudaFree(kv->log);
-        cudaFree(n_kept);
+        kv->log_spare = kv->log;
         kv->log = new_log;
         kv->head_lb = kv->tail;
         kv->tail += kept;
@@ -573,16 +579,52 @@ static die_status_t kv_maintain(die_kv* kv, int force, cudaStream_t s) {
         kv->live_at_rebuild = h.size + h.n_tomb;  // tighten the conservative bound with the real count
     }
     kv->claims_ub = 0;
+    kv->mirror_gen += 1;
     return DIE_OK;
+}
+
+KvMirrorArgs kv_mirror_args(die_kv* kv) {
+    KvMirrorArgs a;
+    a.st = kv->st;
+    a.m = kv->mirror;
+    a.ops_seen = kv->ops_enq;
+    a.gen = kv->mirror_gen;
+    a.seq = ++kv->mirror_seq;
+    return a;
+}
+
+// Tighten the host bounds from the device's latest snapshot, if one of this table generation is there.
+static void kv_mirror_refresh(die_kv* kv) {
+    const volatile KvMirror* m = kv->mirror;
+    if (!m) return;
+    for (int attempt = 0; attempt < 4; ++attempt) {
+        const unsigned long long s1 = m->seq1;
+        std::atomic_thread_fence(std::memory_order_acquire);
+        const unsigned long long head = m->head, size = m->size, tomb = m->n_tomb, seen = m->ops_seen, gen = m->gen;
+        std::atomic_thread_fence(std::memory_order_acquire);
+        if (m->seq0 != s1) continue;  // torn: the device is writing
+        if (s1 == 0 || gen != kv->mirror_gen) return;
+        if (head > kv->head_lb) kv->head_lb = head;  // the head only moves forward between compactions
+        const uint64_t used = size + tomb, since = kv->ops_enq - seen;
+        if (used + since < kv->live_at_rebuild + kv->claims_ub) {
+            kv->live_at_rebuild = used;
+            kv->claims_ub = since;
+        }
+        return;
+    }
 }
 
 // Called before a batch of n ops: keeps the ring and the EMPTY-slot reserve safe using host bounds only.
 die_status_t kv_reserve(die_kv* kv, uint64_t n, bool inserts, cudaStream_t s) {
+    kv_mirror_refresh(kv);
     bool need = (kv->tail + n - kv->head_lb) > kv->ring_cap - 16;
     if (inserts && kv->live_at_rebuild + kv->claims_ub + n > kv->capacity / 8 * 3) need = true;
     if (need) DIE_TRY(kv_maintain(kv, 0, s));
     if ((kv->tail + n - kv->head_lb) > kv->ring_cap - 16) DIE_TRY(kv_maintain(kv, 1, s));
-    if (inserts) kv->claims_ub += n;
+    if (inserts) {
+        kv->claims_ub += n;
+        kv->ops_enq += n;
+    }
     return DIE_OK;
 }
 
@@ -676,6 +718,9 @@ extern "C" die_status_t die_kv_destroy(die_kv_t* kv) {
     cudaFree(kv->slots);
     cudaFree(kv->slots_spare);
     cudaFree(kv->log);
+    cudaFree(kv->log_spare);
+    cudaFree(kv->n_kept_dev);
+    if (kv->mirror) cudaFreeHost(kv->mirror);
     cudaFree(kv->st);
     cudaFree(kv->op_slot);
     cudaFree(kv->free_rows);

@@ -1,4 +1,5 @@
 // Library-wide plumbing: version, thread-local error text, launch accounting, per-stage timers.
+#include <algorithm>
 #include <atomic>
 #include <vector>
 
@@ -10,6 +11,8 @@ static thread_local char g_err[512] = "";
 static std::atomic<unsigned long long> g_launches{0};
 
 char* err_buf() { return g_err; }
+static std::atomic<unsigned long long> g_replays{0};
+void count_replay() { g_replays.fetch_add(1, std::memory_order_relaxed); }
 void count_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 // Optional per-stage device timing: while enabled every kernel launch is bracketed by two CUDA
@@ -17,11 +20,13 @@ void count_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxe
 static const char* const kStageNames[ST_COUNT] = {
     "route_md5",   "kv_get",      "kv_contains", "kv_delete",  "kv_purge", "kv_set_precheck",
     "kv_set_window", "kv_set_claim", "kv_set_finalize", "kv_set_evict", "kv_maintenance", "miss_scan",
-    "pack_hits",   "model",       "unpack_store", "pack_ragged", "unpack_ragged", "bucket_by_shard", "exchange"};
+    "pack_hits",   "model",       "unpack_store", "pack_ragged", "unpack_ragged", "bucket_by_shard", "xchg_dispatch",
+    "xchg_barrier", "xchg_compact", "xchg_return", "xchg_scatter"};
 
 struct ProfRec {
     int stage;
     cudaEvent_t e0, e1;
+    cudaStream_t stream;
 };
 static bool g_prof_on = false;
 static std::vector<ProfRec> g_prof;
@@ -38,10 +43,14 @@ static cudaEvent_t get_event() {
     return e;
 }
 
+static unsigned long long* g_trace = nullptr;
+static unsigned long long g_trace_cap = 0;
+unsigned long long* trace_buffer() { return g_trace; }
+
 bool prof_active() { return g_prof_on; }
 void prof_before(int stage, cudaStream_t s) {
     if (!g_prof_on) return;
-    ProfRec r{stage, get_event(), get_event()};
+    ProfRec r{stage, get_event(), get_event(), s};
     cudaEventRecord(r.e0, s);
     g_prof.push_back(r);
 }
@@ -57,6 +66,7 @@ using namespace die;
 extern "C" int32_t die_abi_version(void) { return DIE_ABI_VERSION; }
 extern "C" const char* die_last_error(void) { return die::g_err; }
 extern "C" uint64_t die_launch_count(void) { return die::g_launches.load(std::memory_order_relaxed); }
+extern "C" uint64_t die_replay_count(void) { return die::g_replays.load(std::memory_order_relaxed); }
 extern "C" die_status_t die_set_device(int32_t device) {
     DIE_CUDA(cudaSetDevice(device));
     return DIE_OK;
@@ -65,6 +75,33 @@ extern "C" die_status_t die_set_device(int32_t device) {
 extern "C" die_status_t die_profile_begin(void) {
     g_prof.clear();
     g_prof_on = true;
+    return DIE_OK;
+}
+
+// Diagnostics: the recorded launches as a timeline (start / end in microseconds after the first recorded
+// launch began, and a small integer per distinct stream).  Call before die_profile_end, which frees the records.
+extern "C" die_status_t die_profile_timeline(int32_t cap, int32_t* stage_out, int32_t* stream_out, double* start_us,
+                                             double* end_us, int32_t* n_out) {
+    g_prof_on = false;
+    DIE_CUDA(cudaDeviceSynchronize());
+    std::vector<cudaStream_t> streams;
+    int n = 0;
+    for (const ProfRec& r : g_prof) {
+        if (n >= cap) break;
+        float t0 = 0.f, t1 = 0.f;
+        if (cudaEventElapsedTime(&t0, g_prof.front().e0, r.e0) != cudaSuccess) continue;
+        if (cudaEventElapsedTime(&t1, g_prof.front().e0, r.e1) != cudaSuccess) continue;
+        int si = 0;
+        for (; si < (int)streams.size(); ++si)
+            if (streams[si] == r.stream) break;
+        if (si == (int)streams.size()) streams.push_back(r.stream);
+        stage_out[n] = r.stage;
+        stream_out[n] = si;
+        start_us[n] = 1e3 * t0;
+        end_us[n] = 1e3 * t1;
+        ++n;
+    }
+    if (n_out) *n_out = n;
     return DIE_OK;
 }
 
@@ -88,6 +125,36 @@ extern "C" die_status_t die_profile_end(int32_t cap, double* ms_out, uint64_t* c
         if (count_out) count_out[i] = cnt[i];
     }
     if (n_stages) *n_stages = ST_COUNT;
+    return DIE_OK;
+}
+
+// Diagnostics: kernels replayed from a graph log (tag, %globaltimer ns) at their start into a device buffer.
+extern "C" die_status_t die_debug_trace_enable(uint64_t n_records) {
+    if (g_trace) cudaFree(g_trace);
+    g_trace = nullptr;
+    g_trace_cap = n_records;
+    if (n_records == 0) return DIE_OK;
+    DIE_CUDA(cudaMalloc(&g_trace, (2 + 2 * n_records) * sizeof(unsigned long long)));
+    const unsigned long long head[2] = {0ull, n_records};
+    DIE_CUDA(cudaMemcpy(g_trace, head, sizeof(head), cudaMemcpyHostToDevice));
+    return DIE_OK;
+}
+
+extern "C" die_status_t die_debug_trace_read_sync(uint64_t cap, uint64_t* tag_out, uint64_t* ns_out, uint64_t* n_out) {
+    if (!g_trace) DIE_FAIL(DIE_ERR_INVALID, "die_debug_trace_read_sync: tracing is not enabled");
+    DIE_CUDA(cudaDeviceSynchronize());
+    unsigned long long head[2];
+    DIE_CUDA(cudaMemcpy(head, g_trace, sizeof(head), cudaMemcpyDeviceToHost));
+    const uint64_t n = std::min<uint64_t>(std::min<uint64_t>(head[0], head[1]), cap);
+    std::vector<unsigned long long> buf(2 * n);
+    if (n) DIE_CUDA(cudaMemcpy(buf.data(), g_trace + 2, 2 * n * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    for (uint64_t i = 0; i < n; ++i) {
+        tag_out[i] = buf[2 * i];
+        ns_out[i] = buf[2 * i + 1];
+    }
+    if (n_out) *n_out = n;
+    const unsigned long long zero = 0ull;
+    DIE_CUDA(cudaMemcpy(g_trace, &zero, sizeof(zero), cudaMemcpyHostToDevice));
     return DIE_OK;
 }
 

@@ -41,6 +41,7 @@ linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, con
     StepArgs step;
     if (SCATTER) {
         step = step_resolve(sc.sr);
+        trace_mark(sc.sr, TR_MODEL);
         sc.pb.code = step.code;
     }
     if (SCATTER && (int)blockIdx.x >= sc.tiles) {  // eviction CTAs (kvstore.py:82-93), 256 window records each

@@ -200,6 +200,7 @@ pipe_get_kernel(StepRef sr, PipeBufs pb, uint4* __restrict__ digests, int B, con
     __shared__ __align__(16) uint8_t stage[FROM_KEYS ? ROUTE_STAGE_BYTES + 32 : 16];
     __shared__ bool s_last;
     const StepArgs a = step_resolve(sr);
+    trace_mark(sr, TR_GET);
     const KvView& kv = a.kv;
     const uint8_t* __restrict__ key_bytes = a.key_bytes;
     const int64_t* __restrict__ key_off = a.key_off;
@@ -244,6 +245,7 @@ pipe_get_kernel(StepRef sr, PipeBufs pb, uint4* __restrict__ digests, int B, con
     __threadfence();
     if (threadIdx.x == 0) pb.ctrl->ts[2] = globaltimer_ns();  // all CTAs probed, tail starts
     pipe_scan_tail(kv, pb, B);
+    if (sr.q && threadIdx.x == 0) trace_mark_q(sr.q, sr.i, TR_GET_TAIL);
 }
 
 // CTAs [0, g_claim): KVCache.set of every miss (all known absent).  Last n_chunks CTAs: LRU victim window.
@@ -253,6 +255,7 @@ pipe_claim_pack_kernel(StepRef sr, PipeBufs pb, const uint4* __restrict__ digest
                        const uint32_t* __restrict__ n_req_dev, int g_claim, const int4* __restrict__ arena, int vin,
                        int vout, int4* __restrict__ packed_in) {
     const StepArgs a = step_resolve(sr);
+    trace_mark(sr, TR_CLAIM);
     const KvView& kv = a.kv;
     const double now = a.now;
     const unsigned long long t_set = a.t_set;
@@ -324,6 +327,7 @@ __global__ void __launch_bounds__(PT)
 pipe_unpack_evict_kernel(StepRef sr, PipeBufs pb, const int4* __restrict__ packed_out, int B,
                          const uint32_t* __restrict__ n_req_dev, int g_evict, int vout, int4* __restrict__ arena) {
     const StepArgs a = step_resolve(sr);
+    trace_mark(sr, TR_UNPACK);
     const KvView& kv = a.kv;
     const unsigned long long t_set = a.t_set;
     int4* __restrict__ out = reinterpret_cast<int4*>(a.out);
@@ -527,7 +531,10 @@ static die_status_t run_fast(die_pipeline* p, const uint8_t* key_bytes, const in
 // The host cost of a step is its launches; a queue of batches pays it once per K steps instead: the K steps
 // are captured once (their arguments come from the device-resident QueueDesc, see pipeline_device.cuh) and
 // replayed with one graph launch after a one-thread kernel has rewritten the descriptor.
-__global__ void queue_desc_set_kernel(QueueDesc* dst, QueueDesc v) { *dst = v; }
+__global__ void queue_desc_set_kernel(QueueDesc* dst, QueueDesc v, KvMirrorArgs m) {
+    *dst = v;
+    kv_mirror_write(m.st, m.m, m.ops_seen, m.gen, m.seq);  // state before this replay -> the host's bounds
+}
 
 static bool graph_fits(const die_pipeline* p, int B, int K) {
     const die_kv* kv = p->kv;
@@ -589,15 +596,18 @@ static die_status_t replay_fast(die_pipeline* p, QueueDesc d, QueueDesc* qd, boo
     die_kv* kv = p->kv;
     cudaGraphExec_t exec;
     DIE_TRY(graph_get(p, from_keys, digests, B, n_req_dev, qd, K, &exec));
+    const KvMirrorArgs mirror = kv_mirror_args(kv);  // before this replay's ops are reserved
     DIE_TRY(kv_reserve(kv, (uint64_t)2 * K * B, false, s));
     DIE_TRY(kv_reserve(kv, (uint64_t)K * B, true, s));
     d.kv = view_of(kv);
     d.batch = B;
+    d.trace = trace_buffer();
     d.tail0 = kv->tail;
     kv->tail += 2ull * (unsigned long long)K * (unsigned long long)B;
-    queue_desc_set_kernel<<<1, 1, 0, s>>>(qd, d);
+    queue_desc_set_kernel<<<1, 1, 0, s>>>(qd, d, mirror);
     DIE_LAUNCH_CHECK();
     DIE_CUDA(cudaGraphLaunch(exec, s));
+    count_replay();
     count_launch((unsigned)(K * pipeline_launches_per_step(p)));
     return DIE_OK;
 }
@@ -605,8 +615,9 @@ static die_status_t replay_fast(die_pipeline* p, QueueDesc d, QueueDesc* qd, boo
 bool pipeline_graph_fits(const die_pipeline* p, int B_max, int K) { return graph_fits(p, B_max, K) && !prof_active(); }
 
 die_status_t pipeline_owner_reserve(die_pipeline* p, int B_max, int K, cudaStream_t s, KvView* view,
-                                    unsigned long long* tail0) {
+                                    unsigned long long* tail0, KvMirrorArgs* mirror) {
     die_kv* kv = p->kv;
+    if (mirror) *mirror = kv_mirror_args(kv);
     DIE_TRY(kv_reserve(kv, (uint64_t)2 * K * B_max, false, s));
     DIE_TRY(kv_reserve(kv, (uint64_t)K * B_max, true, s));
     *view = view_of(kv);
@@ -709,7 +720,7 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
         DIE_CUDA(cudaEventCreateWithFlags(&p->ev_out[i], cudaEventDisableTiming));
     }
     DIE_CUDA(cudaMalloc(&p->qdesc, sizeof(QueueDesc)));
-    p->graph_steps = 8;
+    p->graph_steps = 16;
     if (const char* e = getenv("DIE_GRAPH_STEPS")) p->graph_steps = atoi(e);  // 0: every step launched from the stream
     *out = p;
     return DIE_OK;

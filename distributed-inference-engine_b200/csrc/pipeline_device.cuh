@@ -43,6 +43,7 @@ struct QueueDesc {
     double now0, now_step;
     unsigned long long tail0;  // LRU stamp of the replay's first op
     unsigned int epoch0[2];    // exchange only: barrier epoch of each lane before the replay
+    unsigned long long* trace; // diagnostics (die_debug_trace_enable): [0] cursor, [1] capacity, then (tag, ns) pairs
 };
 
 struct StepRef {
@@ -52,6 +53,23 @@ struct StepRef {
 };
 
 #ifdef __CUDACC__
+// Diagnostics: thread 0 of CTA 0 of a replayed kernel logs (step << 8 | id, %globaltimer).
+enum TraceId { TR_ROUTE = 1, TR_DISPATCH, TR_BAR_IN, TR_BAR_OUT, TR_GET, TR_GET_TAIL, TR_CLAIM, TR_MODEL, TR_UNPACK, TR_SCATTER };
+__device__ __forceinline__ void trace_mark_q(const QueueDesc* q, int i, int id) {
+    if (!q || !q->trace) return;
+    unsigned long long* t = q->trace;
+    const unsigned long long k = atomicAdd(t, 1ull);
+    if (k < t[1]) {
+        unsigned long long ns;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+        t[2 + 2 * k] = ((unsigned long long)i << 8) | (unsigned long long)id;
+        t[3 + 2 * k] = ns;
+    }
+}
+__device__ __forceinline__ void trace_mark(const StepRef& r, int id) {
+    if (r.q && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) trace_mark_q(r.q, r.i, id);
+}
+
 __device__ __forceinline__ StepArgs step_resolve(const StepRef& r) {
     if (!r.q) return r.a;
     const QueueDesc& q = *r.q;

@@ -11,8 +11,9 @@ namespace die {
 // True when K steps of up to B_max requests may be reserved at once on this pipeline's table.
 bool pipeline_graph_fits(const die_pipeline* p, int B_max, int K);
 // Host side of K owner steps: table maintenance if a bound is near, LRU stamps handed out.
+// mirror (optional): arguments of kv_mirror_write for the kernel the caller enqueues before the K steps.
 die_status_t pipeline_owner_reserve(die_pipeline* p, int B_max, int K, cudaStream_t s, KvView* view,
-                                    unsigned long long* tail0);
+                                    unsigned long long* tail0, KvMirrorArgs* mirror);
 // Device side of one owner step (no host state touched): digests in, results to the step's out / code.
 die_status_t pipeline_owner_launch(die_pipeline* p, const StepRef& sr, uint32_t* digests, int B_max,
                                    const uint32_t* n_req_dev, cudaStream_t s);

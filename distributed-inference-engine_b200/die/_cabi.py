@@ -11,7 +11,7 @@ import os
 from ctypes import POINTER, c_char_p, c_double, c_int32, c_int64, c_uint8, c_uint32, c_uint64, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_lib", "libdie.so")
+LIB_PATH = os.environ.get("DIE_LIB_PATH") or os.path.join(_HERE, "_lib", "libdie.so")  # override: A/B diagnostics only
 
 DIE_OK, DIE_ERR_INVALID, DIE_ERR_CUDA, DIE_ERR_NOMEM, DIE_ERR_STOP_ITERATION, DIE_ERR_TOO_LARGE, \
     DIE_ERR_UNSUPPORTED = range(7)
@@ -39,8 +39,13 @@ SIGNATURES = {
     "die_last_error": (c_char_p, []),
     "die_set_device": (c_int32, [c_int32]),
     "die_launch_count": (c_uint64, []),
+    "die_replay_count": (c_uint64, []),
     "die_profile_begin": (c_int32, []),
     "die_profile_end": (c_int32, [c_int32, POINTER(c_double), POINTER(c_uint64), POINTER(c_int32)]),
+    "die_debug_trace_enable": (c_int32, [c_uint64]),
+    "die_debug_trace_read_sync": (c_int32, [c_uint64, POINTER(c_uint64), POINTER(c_uint64), POINTER(c_uint64)]),
+    "die_profile_timeline": (c_int32, [c_int32, POINTER(c_int32), POINTER(c_int32), POINTER(c_double), POINTER(c_double),
+                                       POINTER(c_int32)]),
     "die_profile_stage_name": (c_char_p, [c_int32]),
     "die_debug_random_read": (c_int32, [P, c_uint64, c_int32, c_int32, c_int32, c_uint64, P, P]),
     "die_route_md5": (c_int32, [P, P, c_int32, c_int32, P, P, c_int32, c_int32, P, P, P, P]),

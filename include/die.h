@@ -47,6 +47,8 @@ const char* die_last_error(void);
 die_status_t die_set_device(int32_t device);
 /* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
 uint64_t die_launch_count(void);
+/* Number of CUDA-graph replays (groups of steps of a queue, see die_pipeline_run_device_many) launched so far. */
+uint64_t die_replay_count(void);
 
 /* Diagnostics with no counterpart in the reference: while a profile is open every kernel this
  * library launches is bracketed by CUDA events on the kernel's own stream; die_profile_end()
@@ -57,6 +59,16 @@ die_status_t die_profile_begin(void);
 die_status_t die_profile_end(int32_t cap, double* ms_out /*[host]*/, uint64_t* count_out /*[host]*/,
                              int32_t* n_stages /*[host]*/);
 const char* die_profile_stage_name(int32_t stage);
+/* The open profile as a timeline, one record per launch (call before die_profile_end): stage, a small
+ * integer per distinct stream, start / end in microseconds after the first recorded launch began. */
+die_status_t die_profile_timeline(int32_t cap, int32_t* stage_out /*[host]*/, int32_t* stream_out /*[host]*/,
+                                  double* start_us /*[host]*/, double* end_us /*[host]*/, int32_t* n_out /*[host]*/);
+
+/* Diagnostics (no reference counterpart): while enabled, the kernels of steps replayed from a CUDA graph log
+ * (step << 8 | kernel id, %globaltimer ns) when they start; read_sync returns and clears the log. */
+die_status_t die_debug_trace_enable(uint64_t n_records);
+die_status_t die_debug_trace_read_sync(uint64_t cap, uint64_t* tag_out /*[host]*/, uint64_t* ns_out /*[host]*/,
+                                       uint64_t* n_out /*[host]*/);
 
 /* Calibration (no reference counterpart): n_threads threads each issue per_thread independent random reads of
  * bytes_each (16/32/64) bytes over buf[0..bytes).  bench.py times it to obtain the random-sector ceiling the

@@ -36,8 +36,9 @@ def _worker(rank, world, port, ret, mode="nccl"):
         from oracle import models
         from oracle.pipeline import OraclePipeline
         B, D, steps, max_size, ttl, n_ids = 1024, 128, 8, 3000, 7.0, 5000
-        if mode == "peer_queue":  # a table large enough for the captured replays of 8 steps, filled to eviction
-            steps, max_size, ttl, n_ids = 93, 60000, 60.0, 400000
+        if mode == "peer_queue":  # a table large enough for captured replays of 8 steps, filled to eviction
+            steps, max_size, ttl, n_ids = 93, 70000, 60.0, 400000
+            os.environ["DIE_GRAPH_STEPS"] = "8"
         rng = np.random.default_rng(5)
         w = (rng.standard_normal((D, D)) / np.sqrt(D)).astype(np.float32)
         b = rng.standard_normal(D).astype(np.float32)
@@ -66,8 +67,10 @@ def _worker(rank, world, port, ret, mode="nccl"):
             pay = torch.from_numpy(np.stack([bt[rank][1] for bt in batches])).cuda()
             out = torch.empty((steps, B, D), dtype=torch.float32, device="cuda")
             hit = torch.empty((steps, B), dtype=torch.uint8, device="cuda")
+            replays0 = disp.lib.die_replay_count()
             disp.step_many(key_bytes, key_off, pay, now, dt, out, hit)
             torch.cuda.synchronize()
+            assert disp.lib.die_replay_count() - replays0 == steps // 8
             for j, bt in enumerate(batches):
                 want = ref.process_exchange([(k, [r for r in p]) for k, p in bt], now + j * dt)[rank]
                 assert hit[j].tolist() == want["hit"], j

@@ -168,7 +168,7 @@ def test_graph_replayed_queue_equals_stream_launched_steps(model):
     from die import ops
     from die.pipeline import DispatchPipeline
     rng = np.random.default_rng(33)
-    n, B, D, max_size = 141, 256, 32, 20000  # 17 replays + 5 stream steps; the table fills after ~100 batches
+    n, B, D, max_size = 141, 256, 32, 20000  # 8 replays of 16 + 13 stream steps; the table fills after ~100 batches
     ids = rng.integers(0, 60000, (n, B))
     ids[:, :16] = ids[:, 16:32]              # duplicate keys inside every batch
     kb = np.stack([np.frombuffer("".join("q%08d" % i for i in row).encode(), dtype=np.uint8) for row in ids])
@@ -181,10 +181,11 @@ def test_graph_replayed_queue_equals_stream_launched_steps(model):
     kd, xd = torch.from_numpy(kb).cuda(), torch.from_numpy(x).cuda()
     out = torch.empty((n, B, D), device="cuda")
     hit = torch.empty((n, B), dtype=torch.uint8, device="cuda")
-    launches0 = a._lib.die_launch_count()
+    launches0, replays0 = a._lib.die_launch_count(), a._lib.die_replay_count()
     a.run_device_many(kd, off, xd, 5.0, 1.5, out, hit)
     torch.cuda.synchronize()
     assert a._lib.die_launch_count() - launches0 >= 3 * n
+    assert a._lib.die_replay_count() - replays0 == n // 16
     for j in range(n):
         o, h = b.run_device(ops.KeyBatch(kd[j], off), xd[j], 5.0 + j * 1.5)
         assert torch.equal(h, hit[j]), j
