@@ -210,6 +210,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-kernels", action="store_true",
+                    help="skip the per-kernel rooflines at C3 / C4 sizes (tools/bench_kernels.py, about 30 s)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -381,6 +383,16 @@ def main():
                     "note": "a 4096-request batch carries ~5 MB of algorithmic traffic (<1 us at peak): every kernel of the "
                             "step sits on its launch + dependent-DRAM-latency floor, see DESIGN.md section 5"}
 
+    # ---- every kernel of the path alone, at sizes where bandwidth (not launch latency) is the limit -------------
+    kernels = None
+    if world == 1 and not args.no_kernels:
+        del kd, xd, out_ring, hit_ring
+        runner = pipe = None
+        torch.cuda.empty_cache()
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_kernels
+        kernels = bench_kernels.run()
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline_single()
@@ -392,7 +404,7 @@ def main():
                 "data": "synthetic", "config": dict(workload_config(world), hit_rate=round(hit_rate, 4), model=MODEL),
                 "gpu_launches": int(launches), "host_enqueue_us_per_step": round(1e6 * t_host / K, 2),
                 "clocks": clocks, "e2e": e2e, "roofline": roofline, "stages": stages,
-                "cpu_baseline": cpu}
+                "kernels": kernels, "cpu_baseline": cpu}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

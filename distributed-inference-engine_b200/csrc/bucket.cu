@@ -6,7 +6,7 @@
 // One CTA of 1024 threads walks the batch in tiles of 4096 requests; for every destination it ranks the
 // tile's requests with a block scan, so positions are deterministic (no atomics).  Requests routed to
 // None (-1) form a last bucket.  Sized for dispatch fan-outs (n_shards <= 64), not for general sorting.
-#include "common.cuh"
+#include "bucket_device.cuh"
 
 namespace die {
 
@@ -74,6 +74,14 @@ bucket_by_shard_kernel(const int32_t* __restrict__ shard, int B, int n_shards, i
     }
 }
 
+// Fan-outs of one box (<= 19 shards): packed-count ranking, see bucket_device.cuh.
+__global__ void __launch_bounds__(BKT_THREADS)
+bucket_small_kernel(const int32_t* __restrict__ shard, int B, int n_shards, int64_t* __restrict__ offsets,
+                    int32_t* __restrict__ perm, int32_t* __restrict__ pos) {
+    __shared__ BktSmem sm;
+    bucket_cta(shard, B, n_shards, offsets, perm, pos, sm);
+}
+
 }  // namespace die
 
 extern "C" die_status_t die_bucket_by_shard(const int32_t* shard, int32_t B, int32_t n_shards, int64_t* offsets_out,
@@ -84,6 +92,9 @@ extern "C" die_status_t die_bucket_by_shard(const int32_t* shard, int32_t B, int
     if (!offsets_out || (B > 0 && (!shard || !perm_out || !pos_out)))
         DIE_FAIL(DIE_ERR_INVALID, "die_bucket_by_shard: null buffer");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    DIE_LAUNCH(ST_BUCKET, s, bucket_by_shard_kernel<<<1, BK_THREADS, 0, s>>>(shard, B, n_shards, offsets_out, perm_out, pos_out));
+    if (n_shards <= BKT_MAX_SHARDS)
+        DIE_LAUNCH(ST_BUCKET, s, bucket_small_kernel<<<1, BKT_THREADS, 0, s>>>(shard, B, n_shards, offsets_out, perm_out, pos_out));
+    else
+        DIE_LAUNCH(ST_BUCKET, s, bucket_by_shard_kernel<<<1, BK_THREADS, 0, s>>>(shard, B, n_shards, offsets_out, perm_out, pos_out));
     return DIE_OK;
 }

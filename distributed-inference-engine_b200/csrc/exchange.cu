@@ -38,7 +38,7 @@ __device__ __forceinline__ int bucket_of(const long long* off, int world, long l
 // No fence here: the stores are complete at system scope when the kernel ends, and the barrier kernel that
 // follows on the stream publishes them (fence + st.release.sys).
 __global__ void __launch_bounds__(256)
-xchg_dispatch_kernel(StepRef sr, const int4* __restrict__ digests, const int32_t* __restrict__ perm,
+xchg_dispatch_perm_kernel(StepRef sr, const int4* __restrict__ digests, const int32_t* __restrict__ perm,
                      const int64_t* __restrict__ offsets, int B, int vdim /*payload vectors per row*/, int world, int rank,
                      int cap, PeerPtrs rows, PeerPtrs counts) {
     __shared__ long long s_off[XCHG_MAX_WORLD + 2];
@@ -119,7 +119,7 @@ xchg_return_kernel(const int4* __restrict__ out, const uint8_t* __restrict__ hit
 
 // Source: return window -> results in request order (UNPACK of the exchange).
 __global__ void __launch_bounds__(256)
-xchg_scatter_kernel(StepRef sr, const int4* __restrict__ back, const int32_t* __restrict__ perm,
+xchg_scatter_perm_kernel(StepRef sr, const int4* __restrict__ back, const int32_t* __restrict__ perm,
                     const int64_t* __restrict__ offsets, int B, int world, int cap, int vout) {
     __shared__ long long s_off[XCHG_MAX_WORLD + 2];
     const StepArgs a = step_resolve(sr);
@@ -142,17 +142,113 @@ xchg_scatter_kernel(StepRef sr, const int4* __restrict__ back, const int32_t* __
     }
 }
 
-// ROUTE of the sharded step: MD5 of every key of the ingested batch -> owner rank (model_registry.py:159).
+// ---- the step's own ingest kernels: no bucket pass, no permutation ---------------------------------------
+// ROUTE: MD5 of every key of the ingested batch -> owner rank (model_registry.py:159), and in the same kernel
+// the request's rank among the requests of ITS route CTA that go to the same owner (warp match + a count per
+// warp), plus the CTA's count per owner.  A request's slot in its owner's window is then
+//     (requests for that owner in earlier CTAs) + (rank inside its CTA)         -- request order, as the
+// oracle's process_exchange applies -- and the dispatch and scatter kernels work in request order straight from
+// these two small arrays: nothing is sorted, nothing is gathered through a permutation.
 __global__ void __launch_bounds__(ROUTE_THREADS)
-xchg_route_kernel(StepRef sr, int B, int world, int32_t* __restrict__ shard_out, uint4* __restrict__ digests) {
+xchg_route_kernel(StepRef sr, int B, int world, int32_t* __restrict__ shard_out, uint4* __restrict__ digests,
+                  int32_t* __restrict__ loc, int32_t* __restrict__ cta_cnt /*[gridDim.x][XCHG_MAX_WORLD]*/) {
     __shared__ __align__(16) uint8_t stage[ROUTE_STAGE_BYTES + 32];
+    __shared__ int wcnt[ROUTE_THREADS / 32][XCHG_MAX_WORLD];
     const StepArgs a = step_resolve(sr);
     trace_mark(sr, TR_ROUTE);
-    const Md5State st = cta_hash_keys(a.key_bytes, a.key_off, B, stage);
-    const int i = blockIdx.x * ROUTE_THREADS + threadIdx.x;
-    if (i < B) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < (ROUTE_THREADS / 32) * XCHG_MAX_WORLD) (&wcnt[0][0])[tid] = 0;
+    __syncthreads();
+    const Md5State st = cta_hash_keys(a.key_bytes, a.key_off, B, stage);  // contains __syncthreads
+    const int i = blockIdx.x * ROUTE_THREADS + tid;
+    const bool active = i < B;
+    int d = -1;
+    if (active) {
         digests[i] = make_uint4(st.a, st.b, st.c, st.d);
-        shard_out[i] = (int32_t)md5_mod(st, (uint32_t)world);
+        d = (int)md5_mod(st, (uint32_t)world);
+        shard_out[i] = d;
+    }
+    const unsigned peers = __match_any_sync(0xffffffffu, d);  // lanes of this warp with the same owner
+    const int rank_w = __popc(peers & ((1u << lane) - 1u));
+    if (active && rank_w == 0) wcnt[warp][d] = __popc(peers);
+    __syncthreads();
+    if (active) {
+        int r = rank_w;
+        for (int w = 0; w < warp; ++w) r += wcnt[w][d];
+        loc[i] = (d << 16) | r;
+    }
+    if (tid < world) {
+        int c = 0;
+        for (int w = 0; w < ROUTE_THREADS / 32; ++w) c += wcnt[w][tid];
+        cta_cnt[blockIdx.x * XCHG_MAX_WORLD + tid] = c;
+    }
+}
+
+// Exclusive prefix over the route CTAs of the per-owner counts -> s_off[cta * world + d]; returns nothing,
+// fills s_tot[d].  Every CTA of the dispatch / scatter kernels redoes this tiny scan in shared memory.
+__device__ __forceinline__ void xchg_cta_offsets(const int32_t* __restrict__ cta_cnt, int n_cta, int world, int* s_off,
+                                                 int* s_tot) {
+    for (int e = threadIdx.x; e < n_cta * world; e += blockDim.x)
+        s_off[e] = cta_cnt[(e / world) * XCHG_MAX_WORLD + (e % world)];
+    __syncthreads();
+    if ((int)threadIdx.x < world) {
+        int acc = 0;
+        for (int c = 0; c < n_cta; ++c) {
+            const int v = s_off[c * world + threadIdx.x];
+            s_off[c * world + threadIdx.x] = acc;
+            acc += v;
+        }
+        s_tot[threadIdx.x] = acc;
+    }
+    __syncthreads();
+}
+
+// PACK + SEND in request order: one warp per request row -> its slot in the owner's window (NVLink stores).
+// No fence: the stores are complete at system scope when the kernel ends and the barrier kernel publishes them.
+__global__ void __launch_bounds__(256)
+xchg_dispatch_kernel(StepRef sr, const int4* __restrict__ digests, const int32_t* __restrict__ loc,
+                     const int32_t* __restrict__ cta_cnt, int n_cta, int B, int vdim, int world, int rank, int cap,
+                     PeerPtrs rows, PeerPtrs counts) {
+    extern __shared__ int s_off[];
+    __shared__ int s_tot[XCHG_MAX_WORLD];
+    const int4* __restrict__ payload = reinterpret_cast<const int4*>(step_resolve(sr).payload);
+    trace_mark(sr, TR_DISPATCH);
+    xchg_cta_offsets(cta_cnt, n_cta, world, s_off, s_tot);
+    if (blockIdx.x == 0 && (int)threadIdx.x < world) static_cast<int32_t*>(counts.p[threadIdx.x])[rank] = s_tot[threadIdx.x];
+    const int rv = vdim + 1;
+    const int lane = threadIdx.x & 31;
+    const long long warps = (long long)gridDim.x * 8;
+    for (long long q = blockIdx.x * 8ll + (threadIdx.x >> 5); q < B; q += warps) {
+        const int l = loc[q];
+        const int d = l >> 16;
+        const long long i = s_off[(q >> 8) * world + d] + (l & 0xffff);
+        int4* dst = static_cast<int4*>(rows.p[d]) + ((long long)rank * cap + i) * rv;
+        if (lane == 0) dst[0] = digests[q];
+        for (int c = lane; c < vdim; c += 32) dst[1 + c] = ldg_stream(payload + q * vdim + c);
+    }
+}
+
+// UNPACK of the exchange in request order: the request's row of the return window -> out[q], hit[q].
+__global__ void __launch_bounds__(256)
+xchg_scatter_kernel(StepRef sr, const int4* __restrict__ back, const int32_t* __restrict__ loc,
+                    const int32_t* __restrict__ cta_cnt, int n_cta, int B, int world, int cap, int vout) {
+    extern __shared__ int s_off[];
+    __shared__ int s_tot[XCHG_MAX_WORLD];
+    const StepArgs a = step_resolve(sr);
+    trace_mark(sr, TR_SCATTER);
+    int4* __restrict__ out = reinterpret_cast<int4*>(a.out);
+    uint8_t* __restrict__ hit = a.code;
+    xchg_cta_offsets(cta_cnt, n_cta, world, s_off, s_tot);
+    const int rv = vout + 1;
+    const int lane = threadIdx.x & 31;
+    const long long warps = (long long)gridDim.x * 8;
+    for (long long q = blockIdx.x * 8ll + (threadIdx.x >> 5); q < B; q += warps) {
+        const int l = loc[q];
+        const int d = l >> 16;
+        const long long i = s_off[(q >> 8) * world + d] + (l & 0xffff);
+        const int4* src = back + ((long long)d * cap + i) * rv;  // peer-written: read at L2
+        for (int c = lane; c < vout; c += 32) stg_stream(out + q * vout + c, __ldcg(src + c));
+        if (lane == 0) hit[q] = (uint8_t)__ldcg(src + vout).x;
     }
 }
 
@@ -187,7 +283,7 @@ extern "C" die_status_t die_xchg_dispatch(const uint32_t* digests, const float* 
     StepRef sr;
     memset(&sr, 0, sizeof(sr));
     sr.a.payload = payload;
-    DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_rows(B), 256, 0, s>>>(
+    DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_perm_kernel<<<grid_for_rows(B), 256, 0, s>>>(
         sr, reinterpret_cast<const int4*>(digests), perm, offsets, B, vdim, world, rank, cap, rows, counts));
     return DIE_OK;
 }
@@ -231,7 +327,7 @@ extern "C" die_status_t die_xchg_scatter(const float* back, const int32_t* perm,
     memset(&sr, 0, sizeof(sr));
     sr.a.out = out;
     sr.a.code = hit;
-    DIE_LAUNCH(ST_XCHG_SCATTER, s, xchg_scatter_kernel<<<grid_for_rows(B), 256, 0, s>>>(
+    DIE_LAUNCH(ST_XCHG_SCATTER, s, xchg_scatter_perm_kernel<<<grid_for_rows(B), 256, 0, s>>>(
         sr, reinterpret_cast<const int4*>(back), perm, offsets, B, world, cap, vout));
     return DIE_OK;
 }
@@ -285,15 +381,14 @@ struct XchgLane {
     unsigned int* my_flags;
     int32_t* shard;
     uint32_t* digests;
-    int64_t* offsets;
-    int32_t* perm;
-    int32_t* pos;
     uint32_t* recv_dig;
     float* recv_pay;
     float* recv_out;
     uint8_t* recv_hit;
     uint32_t* n_dev;
     int32_t* prefix;
+    int32_t* loc;      // [cap] owner << 16 | rank among the route CTA's requests for that owner
+    int32_t* cta_cnt;  // [ceil(cap / 256)][XCHG_MAX_WORLD] requests per owner of every route CTA
     unsigned int epoch;
     cudaStream_t stream;
     cudaEvent_t done;  // the lane's last enqueued kernel
@@ -335,6 +430,7 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
     if (!out || !pipe || !peer_windows || world < 1 || world > XCHG_MAX_WORLD || rank < 0 || rank >= world || cap <= 0 ||
         dim <= 0 || (dim & 3))
         DIE_FAIL(DIE_ERR_INVALID, "die_xchg_create: bad arguments");
+    if (cap > 131072) DIE_FAIL(DIE_ERR_TOO_LARGE, "die_xchg_create: cap %d > 131072 requests per ingested batch", cap);
     for (int i = 0; i < world; ++i)
         if (!peer_windows[i]) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_create: null window for rank %d", i);
     die_xchg* x = new die_xchg();
@@ -363,15 +459,14 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
         L.my_flags = static_cast<unsigned int*>(L.flags.p[rank]);
         DIE_CUDA(cudaMalloc(&L.shard, cap * sizeof(int32_t)));
         DIE_CUDA(cudaMalloc(&L.digests, (size_t)cap * 16));
-        DIE_CUDA(cudaMalloc(&L.offsets, (world + 2) * sizeof(int64_t)));
-        DIE_CUDA(cudaMalloc(&L.perm, cap * sizeof(int32_t)));
-        DIE_CUDA(cudaMalloc(&L.pos, cap * sizeof(int32_t)));
         DIE_CUDA(cudaMalloc(&L.recv_dig, bmax * 16));
         DIE_CUDA(cudaMalloc(&L.recv_pay, bmax * dim * sizeof(float)));
         DIE_CUDA(cudaMalloc(&L.recv_out, bmax * dim * sizeof(float)));
         DIE_CUDA(cudaMalloc(&L.recv_hit, bmax));
         DIE_CUDA(cudaMalloc(&L.n_dev, sizeof(uint32_t)));
         DIE_CUDA(cudaMalloc(&L.prefix, (world + 1) * sizeof(int32_t)));
+        DIE_CUDA(cudaMalloc(&L.loc, cap * sizeof(int32_t)));
+        DIE_CUDA(cudaMalloc(&L.cta_cnt, (size_t)ceil_div(cap, ROUTE_THREADS) * XCHG_MAX_WORLD * sizeof(int32_t)));
         DIE_CUDA(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
         DIE_CUDA(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
     }
@@ -392,8 +487,8 @@ extern "C" die_status_t die_xchg_destroy(die_xchg_t* x) {
     for (int l = 0; l < 2; ++l) {
         XchgLane& L = x->lane[l];
         if (L.stream) cudaStreamSynchronize(L.stream);
-        void* bufs[] = {L.shard, L.digests, L.offsets, L.perm, L.pos, L.recv_dig, L.recv_pay, L.recv_out,
-                        L.recv_hit, L.n_dev, L.prefix};
+        void* bufs[] = {L.shard, L.digests, L.recv_dig, L.recv_pay, L.recv_out,
+                        L.recv_hit, L.n_dev, L.prefix, L.loc, L.cta_cnt};
         for (void* b : bufs) cudaFree(b);
         if (L.done) cudaEventDestroy(L.done);
         if (L.stream) cudaStreamDestroy(L.stream);
@@ -428,11 +523,13 @@ static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user,
     cudaStream_t s = L.stream;
     const int W = x->world, D = x->dim, vdim = D / 4;
     int32_t* shard = shard_out ? shard_out : L.shard;
-    DIE_LAUNCH(ST_ROUTE, s, xchg_route_kernel<<<ceil_div(B, ROUTE_THREADS), ROUTE_THREADS, 0, s>>>(
-        user, B, W, shard, reinterpret_cast<uint4*>(L.digests)));
-    DIE_TRY(die_bucket_by_shard(shard, B, W, L.offsets, L.perm, L.pos, static_cast<die_stream_t>(s)));
-    DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_rows(B), 256, 0, s>>>(
-        user, reinterpret_cast<const int4*>(L.digests), L.perm, L.offsets, B, vdim, W, x->rank, x->cap, L.rows, L.counts));
+    const int n_cta = std::max(1, ceil_div(B, ROUTE_THREADS));
+    const size_t off_bytes = (size_t)n_cta * W * sizeof(int);
+    DIE_LAUNCH(ST_ROUTE, s, xchg_route_kernel<<<n_cta, ROUTE_THREADS, 0, s>>>(
+        user, B, W, shard, reinterpret_cast<uint4*>(L.digests), L.loc, L.cta_cnt));
+    DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_rows(B), 256, off_bytes, s>>>(
+        user, reinterpret_cast<const int4*>(L.digests), L.loc, L.cta_cnt, n_cta, B, vdim, W, x->rank, x->cap, L.rows,
+        L.counts));
     DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first));  // every rank's rows have landed in their owners' windows
     DIE_LAUNCH(ST_XCHG_COMPACT, s, xchg_compact_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, s>>>(
         reinterpret_cast<const int4*>(L.my_rows), L.my_cnt, W, x->cap, vdim, (long long)x->bmax,
@@ -454,8 +551,8 @@ static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user,
     DIE_LAUNCH(ST_XCHG_RETURN, s, xchg_return_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, s>>>(
         reinterpret_cast<const int4*>(L.recv_out), L.recv_hit, L.prefix, W, x->rank, x->cap, vdim, L.back));
     DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first + 1));  // every owner's results are back in the sources' windows
-    DIE_LAUNCH(ST_XCHG_SCATTER, s, xchg_scatter_kernel<<<grid_for_rows(B), 256, 0, s>>>(
-        user, reinterpret_cast<const int4*>(L.my_back), L.perm, L.offsets, B, W, x->cap, vdim));
+    DIE_LAUNCH(ST_XCHG_SCATTER, s, xchg_scatter_kernel<<<grid_for_rows(B), 256, off_bytes, s>>>(
+        user, reinterpret_cast<const int4*>(L.my_back), L.loc, L.cta_cnt, n_cta, B, W, x->cap, vdim));
     return DIE_OK;
 }
 
@@ -611,7 +708,7 @@ extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, con
             DIE_LAUNCH_CHECK();
             DIE_CUDA(cudaGraphLaunch(exec, user));
             count_replay();
-            count_launch((unsigned)(K * (8 + pipeline_launches_per_step(x->pipe))));
+            count_launch((unsigned)(K * (7 + pipeline_launches_per_step(x->pipe))));
             const int lane0 = (int)(x->steps & 1);
             x->lane[lane0].epoch += 2u * (unsigned)((K + 1) / 2);
             x->lane[lane0 ^ 1].epoch += 2u * (unsigned)(K / 2);

@@ -504,7 +504,10 @@ die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_ro
     kv->max_size = max_size;
     kv->default_ttl = default_ttl;
     kv->capacity = next_pow2(std::max<uint64_t>(std::max<uint64_t>(4 * max_size, 16 * min_batch), 4096));
-    kv->ring_cap = next_pow2(std::max<uint64_t>(std::max<uint64_t>(4 * max_size, 8 * min_batch), 1ull << 20));
+    // LRU log: 4 bytes per position.  Positions are handed out per batch *slot* (an owner step of the exchange
+    // stamps its whole capacity, not only the requests that arrived), so the log is sparse; 16 positions per
+    // entry keeps compaction (kv_maintain) out of the steady state of a table that evicts.
+    kv->ring_cap = next_pow2(std::max<uint64_t>(std::max<uint64_t>(16 * max_size, 8 * min_batch), 1ull << 20));
     kv->max_chunk = std::min<uint64_t>(kv->capacity / 16, std::min<uint64_t>(kv->ring_cap / 4, 1ull << 22));
     kv->tail = 1;
     kv->head_lb = 1;
