@@ -67,6 +67,14 @@ struct die_pipeline {
     int graph_steps;          // K; 0 = always launch from the stream
     cudaStream_t cap_stream;  // capture only: the caller's stream may be the legacy stream, which cannot capture
     die::QueueDesc* qdesc;    // device
+    // staging of die_pipeline_run_host_many's grouped form: NBUF sets of graph_steps batches each, so that one
+    // copy per array moves a whole group and one replay computes it
+    uint8_t* g_keys;
+    int64_t* g_off;
+    float* g_pay;
+    float* g_out;
+    uint8_t* g_hit;
+    int g_steps;  // batches per set the buffers were sized for (0: not allocated)
 };
 
 namespace die {
@@ -734,6 +742,7 @@ extern "C" die_status_t die_pipeline_destroy(die_pipeline_t* p) {
                     p->d_key_off, p->d_payload, p->d_out, p->d_hit};
     for (void* b : bufs) cudaFree(b);
     cudaFree(p->qdesc);
+    cudaFree(p->g_keys); cudaFree(p->g_off); cudaFree(p->g_pay); cudaFree(p->g_out); cudaFree(p->g_hit);
     for (int g = 0; g < p->n_graphs; ++g) cudaGraphExecDestroy(p->graphs[g].exec);
     if (p->cap_stream) cudaStreamDestroy(p->cap_stream);
     if (p->s_in) cudaStreamDestroy(p->s_in);
@@ -878,6 +887,85 @@ extern "C" die_status_t die_pipeline_run_host_many(die_pipeline_t* p, int32_t n_
     const die_pipeline_config_t& c = p->cfg;
     constexpr int NB = die_pipeline::NBUF;
     const size_t in_row = (size_t)B * c.dim_in, out_row = (size_t)B * c.dim_out;
+    for (int32_t j = 0; j < n_batches; ++j) {
+        const int64_t* ko = key_off + (size_t)j * key_off_stride;
+        const int64_t nbytes = ko[B] - ko[0];
+        if (ko[0] != 0 || nbytes < 0 || nbytes > c.max_key_bytes)
+            DIE_FAIL(DIE_ERR_TOO_LARGE, "die_pipeline_run_host_many: batch %d has %lld key bytes (limit %d)", j,
+                     (long long)nbytes, c.max_key_bytes);
+    }
+    // Grouped form: G consecutive batches are contiguous in the caller's arrays, so one copy per array moves a
+    // group, one graph replay computes it, and the copy engines work on the neighbouring groups meanwhile.
+    const int G = p->graph_steps;
+    if (n_batches >= 2 && G >= 2 && pipeline_graph_fits(p, B, std::min<int>(G, n_batches)) &&
+        (n_batches == 1 || (size_t)key_bytes_stride <= p->key_stage_stride) &&
+        (key_off_stride == 0 || key_off_stride == B + 1)) {
+        if (p->g_steps < G) {
+            const size_t mb = (size_t)c.max_batch;
+            cudaFree(p->g_keys); cudaFree(p->g_off); cudaFree(p->g_pay); cudaFree(p->g_out); cudaFree(p->g_hit);
+            p->g_steps = 0;
+            DIE_CUDA(cudaMalloc(&p->g_keys, (size_t)NB * G * p->key_stage_stride));
+            DIE_CUDA(cudaMalloc(&p->g_off, (size_t)NB * G * (mb + 1) * sizeof(int64_t)));
+            DIE_CUDA(cudaMalloc(&p->g_pay, (size_t)NB * G * mb * c.dim_in * sizeof(float)));
+            DIE_CUDA(cudaMalloc(&p->g_out, (size_t)NB * G * mb * c.dim_out * sizeof(float)));
+            DIE_CUDA(cudaMalloc(&p->g_hit, (size_t)NB * G * mb));
+            p->g_steps = G;
+        }
+        const size_t mb = (size_t)c.max_batch;
+        int set = 0;
+        for (int32_t j = 0; j < n_batches; j += G, ++set) {
+            const int K = std::min<int>(G, n_batches - j);
+            const int b = set % NB;
+            uint8_t* dk = p->g_keys + (size_t)b * G * p->key_stage_stride;
+            int64_t* dko = p->g_off + (size_t)b * G * (mb + 1);
+            float* dp = p->g_pay + (size_t)b * G * mb * c.dim_in;
+            float* dout = p->g_out + (size_t)b * G * mb * c.dim_out;
+            uint8_t* dh = p->g_hit + (size_t)b * G * mb;
+            if (set >= NB) {  // set b is free once group set-NB has been computed (inputs) and copied out (outputs)
+                DIE_CUDA(cudaStreamWaitEvent(p->s_in, p->ev_done[b], 0));
+                DIE_CUDA(cudaStreamWaitEvent(s, p->ev_out[b], 0));
+            }
+            const int64_t* ko_last = key_off + (size_t)(j + K - 1) * key_off_stride;
+            const size_t key_span = (size_t)(K - 1) * key_bytes_stride + (size_t)(ko_last[B] - ko_last[0]);
+            if (key_span)
+                DIE_CUDA(cudaMemcpyAsync(dk, key_bytes + (size_t)j * key_bytes_stride, key_span, cudaMemcpyHostToDevice, p->s_in));
+            DIE_CUDA(cudaMemcpyAsync(dko, key_off + (size_t)j * key_off_stride,
+                                     (size_t)(key_off_stride ? K : 1) * (B + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, p->s_in));
+            DIE_CUDA(cudaMemcpyAsync(dp, payload + (size_t)j * in_row, (size_t)K * in_row * sizeof(float), cudaMemcpyHostToDevice, p->s_in));
+            DIE_CUDA(cudaEventRecord(p->ev_in[b], p->s_in));
+            DIE_CUDA(cudaStreamWaitEvent(s, p->ev_in[b], 0));
+            QueueDesc d;
+            memset(&d, 0, sizeof(d));
+            d.key_bytes = dk;
+            d.key_off = dko;
+            d.payload = dp;
+            d.out = dout;
+            d.hit = dh;
+            d.key_bytes_stride = key_bytes_stride;
+            d.key_off_stride = key_off_stride;
+            d.payload_stride = (long long)in_row;
+            d.out_stride = (long long)out_row;
+            d.hit_stride = B;
+            d.ring = K;
+            d.j0 = 0;
+            d.jt = j;
+            d.now0 = now0;
+            d.now_step = now_step;
+            if (K >= 2) {
+                DIE_TRY(replay_fast(p, d, p->qdesc, true, p->digests, B, nullptr, K, s));
+            } else {
+                DIE_TRY(die_pipeline_run_device(p, dk, dko, B, dp, now0 + j * now_step, dout, dh, nullptr, stream));
+            }
+            DIE_CUDA(cudaEventRecord(p->ev_done[b], s));
+            DIE_CUDA(cudaStreamWaitEvent(p->s_out, p->ev_done[b], 0));
+            DIE_CUDA(cudaMemcpyAsync(out + (size_t)j * out_row, dout, (size_t)K * out_row * sizeof(float), cudaMemcpyDeviceToHost, p->s_out));
+            if (hit_out) DIE_CUDA(cudaMemcpyAsync(hit_out + (size_t)j * B, dh, (size_t)K * B, cudaMemcpyDeviceToHost, p->s_out));
+            DIE_CUDA(cudaEventRecord(p->ev_out[b], p->s_out));
+        }
+        DIE_CUDA(cudaStreamSynchronize(p->s_out));
+        DIE_CUDA(cudaStreamSynchronize(s));
+        return DIE_OK;
+    }
     for (int32_t j = 0; j < n_batches; ++j) {
         const int b = j % NB;
         const int64_t* ko = key_off + (size_t)j * key_off_stride;

@@ -37,7 +37,8 @@ struct QueueDesc {
     float* out;
     uint8_t* hit;
     long long key_bytes_stride, key_off_stride, payload_stride, out_stride, hit_stride;  // elements per batch
-    long long j0;  // queue index of the replay's first batch
+    long long j0;  // queue index of the replay's first batch (for the buffers)
+    long long jt;  // added to j0 for the clock: the batches of a staged group are a window of a longer queue
     int ring;      // out / hit slots, reused round-robin
     int batch;     // stamps per get (= per set) pass of one step
     double now0, now_step;
@@ -83,7 +84,7 @@ __device__ __forceinline__ StepArgs step_resolve(const StepRef& r) {
     a.payload = q.payload ? q.payload + j * q.payload_stride : r.a.payload;
     a.out = q.out ? q.out + slot * q.out_stride : r.a.out;
     a.code = q.hit ? q.hit + slot * q.hit_stride : r.a.code;
-    a.now = __dadd_rn(q.now0, __dmul_rn((double)j, q.now_step));  // the host's now0 + j * now_step, no fma
+    a.now = __dadd_rn(q.now0, __dmul_rn((double)(j + q.jt), q.now_step));  // the host's now0 + j * now_step, no fma
     a.t_get = q.tail0 + 2ull * (unsigned long long)q.batch * (unsigned long long)r.i;
     a.t_set = a.t_get + (unsigned long long)q.batch;
     return a;

@@ -190,9 +190,18 @@ def test_graph_replayed_queue_equals_stream_launched_steps(model):
         o, h = b.run_device(ops.KeyBatch(kd[j], off), xd[j], 5.0 + j * 1.5)
         assert torch.equal(h, hit[j]), j
         assert torch.equal(o, out[j]), j
-    sa, sb = a.kv.stats(), b.kv.stats()
+    # the same queue from pinned host buffers: groups of 16 batches per copy and per replay
+    c = DispatchPipeline(max_size, B, D, D, model, w, bias, default_ttl=150.0)
+    hout = torch.empty((n, B, D)).pin_memory()
+    hhit = torch.empty((n, B), dtype=torch.uint8).pin_memory()
+    kbp = torch.from_numpy(np.concatenate([kb, np.zeros((n, 16), np.uint8)], axis=1)).pin_memory()
+    replays0 = c._lib.die_replay_count()
+    c.run_host_many(kbp, off.cpu().pin_memory(), torch.from_numpy(x).pin_memory(), 5.0, 1.5, hout, hhit)
+    assert c._lib.die_replay_count() - replays0 == (n + 15) // 16
+    assert torch.equal(hhit, hit.cpu()) and torch.equal(hout, out.cpu())
+    sa, sb, sc = a.kv.stats(), b.kv.stats(), c.kv.stats()
     for k in ("hits", "misses", "evictions", "size"):
-        assert sa[k] == sb[k], k
+        assert sa[k] == sb[k] == sc[k], k
     assert sa["evictions"] > 0 and sa["hits"] > 0
     da, db = a.kv.dump(), b.kv.dump()
     for name in da:
