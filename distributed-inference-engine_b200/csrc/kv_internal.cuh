@@ -158,22 +158,41 @@ __device__ __forceinline__ SlotLine ld_slot_line(const Slot* s) {
 
 // One KVCache.get (kvstore.py:136-164) / __contains__ (:221-228) probe.  Returns the code
 // (1 hit, 0 absent, 2 expired-and-deleted-by-this-op).
+constexpr int PROBE_AHEAD = 4;
 template <bool CONTAINS>
 __device__ __forceinline__ int kv_get_one(const KvView& kv, u128 key, double now, unsigned long long stamp,
                                           unsigned long long& value, long long& slot) {
     value = 0;
     slot = -1;
     unsigned long long cur = key.lo & kv.mask;
-    SlotLine l;
-    bool found = false;
-    for (unsigned long long n = 0; n <= kv.mask; ++n) {
-        l = ld_slot_line(&kv.slots[cur]);
-        if (fp_eq(l.fp, key)) {
-            found = true;
-            break;
-        }
-        if (fp_empty(l.fp)) break;
+    SlotLine l = ld_slot_line(&kv.slots[cur]);
+    bool found = fp_eq(l.fp, key);
+    if (!found && !fp_empty(l.fp)) {
+        // The home slot is somebody else's: walk the chain PROBE_AHEAD slots per round trip (their fingerprints
+        // are fetched together), so that the longest chain of a batch costs a few DRAM latencies, not one each.
         cur = (cur + 1) & kv.mask;
+        for (unsigned long long n = 1; n <= kv.mask && !found; n += PROBE_AHEAD) {
+            u128 f[PROBE_AHEAD];
+#pragma unroll
+            for (int k = 0; k < PROBE_AHEAD; ++k) f[k] = ld_fp(&kv.slots[(cur + k) & kv.mask]);
+            int at = -1;
+            bool end = false;
+#pragma unroll
+            for (int k = 0; k < PROBE_AHEAD; ++k) {
+                if (at < 0 && !end) {
+                    if (fp_eq(f[k], key)) at = k;
+                    else if (fp_empty(f[k])) end = true;
+                }
+            }
+            if (at >= 0) {
+                cur = (cur + at) & kv.mask;
+                l = ld_slot_line(&kv.slots[cur]);
+                found = fp_eq(l.fp, key);  // false: an op of this launch deleted it (expired) in the meantime
+                break;
+            }
+            if (end) break;
+            cur = (cur + PROBE_AHEAD) & kv.mask;
+        }
     }
     if (!found) return 0;
     Slot* sl = &kv.slots[cur];
@@ -207,18 +226,31 @@ __device__ __forceinline__ long long kv_claim_absent(const KvView& kv, u128 key,
         unsigned long long cur = key.lo & kv.mask;
         long long first_free = -1;
         bool first_free_empty = false;
-        for (unsigned long long n = 0; n <= kv.mask; ++n) {
-            const u128 fp = ld_fp(&kv.slots[cur]);
-            if (fp_eq(fp, key)) return (long long)cur;  // a duplicate op of this batch already inserted it
-            if (fp_tomb(fp) && first_free < 0) first_free = (long long)cur;
-            if (fp_empty(fp)) {
-                if (first_free < 0) {
-                    first_free = (long long)cur;
-                    first_free_empty = true;
+        // first the home slot alone (most chains end there), then PROBE_AHEAD fingerprints per round trip
+        bool done = false;
+        for (unsigned long long n = 0; n <= kv.mask && !done;) {
+            const int width = n == 0 ? 1 : PROBE_AHEAD;
+            u128 f[PROBE_AHEAD];
+#pragma unroll
+            for (int k = 0; k < PROBE_AHEAD; ++k)
+                if (k < width) f[k] = ld_fp(&kv.slots[(cur + k) & kv.mask]);
+#pragma unroll
+            for (int k = 0; k < PROBE_AHEAD; ++k) {
+                if (k < width && !done) {
+                    const long long at = (long long)((cur + k) & kv.mask);
+                    if (fp_eq(f[k], key)) return at;  // a duplicate op of this batch already inserted it
+                    if (fp_tomb(f[k]) && first_free < 0) first_free = at;
+                    if (fp_empty(f[k])) {
+                        if (first_free < 0) {
+                            first_free = at;
+                            first_free_empty = true;
+                        }
+                        done = true;
+                    }
                 }
-                break;
             }
-            cur = (cur + 1) & kv.mask;
+            cur = (cur + width) & kv.mask;
+            n += width;
         }
         if (first_free < 0) continue;  // cannot happen: the host keeps >= capacity/4 EMPTY slots
         const u128 expect = first_free_empty ? u128{0ull, 0ull} : u128{FP_TOMB_WORD, FP_TOMB_WORD};

@@ -31,7 +31,10 @@ struct die_pipeline {
     int32_t* shard;      // [B]
     uint8_t* code;       // [B]
     uint64_t* value;     // [B] result-row handle of a hit
-    int32_t* miss_rank;  // [B]
+    int32_t* miss_rank;  // [B] (general sequence)
+    uint8_t* lrank;      // [B] fast sequence: rank inside the get CTA, see PipeBufs
+    int32_t* cta_miss;
+    int32_t* cta_base;
     int32_t* miss_req;   // [B] inverse of miss_rank
     int32_t* set_slot;   // [B]
     int32_t* set_row;    // [B]
@@ -118,36 +121,19 @@ __device__ __forceinline__ unsigned ld_u8_cg(const uint8_t* p) {
     return r;
 }
 
-// Tail of the get kernel, run by the last CTA: rank the misses of the batch in request order.
-__device__ void pipe_scan_tail(const KvView& kv, const PipeBufs& pb, int B) {
+// Tail of the get kernel, run by the last CTA.  Every CTA has ranked its own misses (request order inside the
+// CTA) and published their count; the tail only scans those counts -- one value per CTA, not one per request --
+// and resets the batch's control block.  rank of miss q = cta_base[q / PT] + lrank[q]  (batcher.py:211 order).
+__device__ void pipe_rank_tail(const KvView& kv, const PipeBufs& pb, int B, int n_cta) {
     __shared__ unsigned s_warp[PT / 32];
     const int tid = threadIdx.x;
-    constexpr int ITEMS = 16;  // 4096 requests per pass of the CTA
     unsigned base = 0;
-    for (int pos = 0; pos < B; pos += PT * ITEMS) {
-        const int q0 = pos + tid * ITEMS;
-        bool miss[ITEMS];
-        unsigned cnt = 0;
-        if (q0 + ITEMS <= B && (reinterpret_cast<uintptr_t>(pb.code + q0) & 15) == 0) {
-            const uint4 c4 = __ldcg(reinterpret_cast<const uint4*>(pb.code + q0));  // 16 hit codes at once
-            const unsigned w[4] = {c4.x, c4.y, c4.z, c4.w};
-#pragma unroll
-            for (int k = 0; k < ITEMS; ++k) miss[k] = ((w[k >> 2] >> (8 * (k & 3))) & 0xffu) != 1u;
-        } else {
-#pragma unroll
-            for (int k = 0; k < ITEMS; ++k) miss[k] = q0 + k < B && ld_u8_cg(pb.code + q0 + k) != 1u;
-        }
-#pragma unroll
-        for (int k = 0; k < ITEMS; ++k) cnt += miss[k];
+    for (int c0 = 0; c0 < n_cta; c0 += PT) {
+        const int c = c0 + tid;
+        const unsigned cnt = c < n_cta ? (unsigned)__ldcg(pb.cta_miss + c) : 0u;
         unsigned excl;
         const unsigned total = block_scan_pt(cnt, excl, s_warp);
-        unsigned r = base + excl;
-#pragma unroll
-        for (int k = 0; k < ITEMS; ++k) {
-            if (q0 + k >= B) continue;
-            pb.miss_rank[q0 + k] = miss[k] ? (int32_t)r : -1;
-            if (miss[k]) pb.miss_req[r++] = q0 + k;  // rank -> request, for the fused GEMM epilogue
-        }
+        if (c < n_cta) pb.cta_base[c] = (int32_t)(base + excl);
         base += total;
         __syncthreads();
     }
@@ -239,6 +225,22 @@ pipe_get_kernel(StepRef sr, PipeBufs pb, uint4* __restrict__ digests, int B, con
         pb.code[i] = (uint8_t)code;
         pb.value[i] = value;
     }
+    {   // rank of this miss among the misses of the CTA
+        __shared__ unsigned s_wmiss[PT / 32];
+        const bool miss = active && code != 1;
+        const unsigned m = __ballot_sync(0xffffffffu, miss);
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        if (lane == 0) s_wmiss[warp] = __popc(m);
+        __syncthreads();
+        unsigned r = __popc(m & ((1u << lane) - 1u)), tot = 0;
+#pragma unroll
+        for (int w = 0; w < PT / 32; ++w) {
+            r += w < warp ? s_wmiss[w] : 0u;
+            tot += s_wmiss[w];
+        }
+        if (active) pb.lrank[i] = (uint8_t)r;
+        if (threadIdx.x == 0) pb.cta_miss[blockIdx.x] = (int32_t)tot;
+    }
     const bool deleted = active && code == 2;  // rare: only expired entries
     if (__any_sync(0xffffffffu, deleted)) {
         warp_sub(&kv.st->size, deleted);
@@ -252,7 +254,7 @@ pipe_get_kernel(StepRef sr, PipeBufs pb, uint4* __restrict__ digests, int B, con
     if (!s_last) return;
     __threadfence();
     if (threadIdx.x == 0) pb.ctrl->ts[2] = globaltimer_ns();  // all CTAs probed, tail starts
-    pipe_scan_tail(kv, pb, B);
+    pipe_rank_tail(kv, pb, B, (int)gridDim.x);
     if (sr.q && threadIdx.x == 0) trace_mark_q(sr.q, sr.i, TR_GET_TAIL);
 }
 
@@ -324,8 +326,10 @@ pipe_claim_pack_kernel(StepRef sr, PipeBufs pb, const uint4* __restrict__ digest
         const int c = (int)(v - q * vmax);
         if (pb.code[q] == 1) {
             if (c < vout) stg_stream(out + q * vout + c, ldg_stream(arena + (long long)pb.value[q] * vout + c));
-        } else if (c < vin) {
-            stg_stream(packed_in + (long long)pb.miss_rank[q] * vin + c, ldg_stream(payload + q * vin + c));
+        } else {
+            const int rank = pb.cta_base[q / PT] + (int)pb.lrank[q];
+            if (c < vin) stg_stream(packed_in + (long long)rank * vin + c, ldg_stream(payload + q * vin + c));
+            if (c == 0) pb.miss_req[rank] = (int32_t)q;  // rank -> request, for the fused GEMM epilogue
         }
     }
 }
@@ -352,7 +356,7 @@ pipe_unpack_evict_kernel(StepRef sr, PipeBufs pb, const int4* __restrict__ packe
         const long long q = v / vout;
         const int c = (int)(v - q * vout);
         if (pb.code[q] == 1) continue;
-        const int4 y = ldg_stream(packed_out + (long long)pb.miss_rank[q] * vout + c);
+        const int4 y = ldg_stream(packed_out + (long long)(pb.cta_base[q / PT] + (int)pb.lrank[q]) * vout + c);
         stg_stream(out + v, y);
         if (c == 0) pb.code[q] = 0;  // callers see 1 = served from the cache, 0 = computed (2 -> 0)
         long long row = pb.set_row[q];
@@ -459,7 +463,9 @@ static PipeBufs bufs_of(die_pipeline* p, uint8_t* code) {
     PipeBufs pb;
     pb.code = code;
     pb.value = reinterpret_cast<unsigned long long*>(p->value);
-    pb.miss_rank = p->miss_rank;
+    pb.lrank = p->lrank;
+    pb.cta_miss = p->cta_miss;
+    pb.cta_base = p->cta_base;
     pb.miss_req = p->miss_req;
     pb.set_slot = p->set_slot;
     pb.set_row = p->set_row;
@@ -702,6 +708,9 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
     DIE_CUDA(cudaMalloc(&p->value, B * sizeof(uint64_t)));
     DIE_CUDA(cudaMalloc(&p->miss_rank, B * sizeof(int32_t)));
     DIE_CUDA(cudaMalloc(&p->miss_req, B * sizeof(int32_t)));
+    DIE_CUDA(cudaMalloc(&p->lrank, B));
+    DIE_CUDA(cudaMalloc(&p->cta_miss, (B / PT + 1) * sizeof(int32_t)));
+    DIE_CUDA(cudaMalloc(&p->cta_base, (B / PT + 1) * sizeof(int32_t)));
     DIE_CUDA(cudaMalloc(&p->set_slot, B * sizeof(int32_t)));
     DIE_CUDA(cudaMalloc(&p->set_row, B * sizeof(int32_t)));
     p->n_chunks = (int)((4 * B + WCHUNK - 1) / WCHUNK);  // window = 4 log records per request of the largest batch
@@ -737,7 +746,7 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
 extern "C" die_status_t die_pipeline_destroy(die_pipeline_t* p) {
     if (!p) return DIE_OK;
     die_kv_destroy(p->kv);
-    void* bufs[] = {p->arena, p->W, p->bias, p->digests, p->shard, p->code, p->value, p->miss_rank, p->miss_req,
+    void* bufs[] = {p->arena, p->W, p->bias, p->digests, p->shard, p->code, p->value, p->miss_rank, p->miss_req, p->lrank, p->cta_miss, p->cta_base,
                     p->set_slot, p->set_row, p->wmask, p->wcount, p->ctrl, p->packed_in, p->packed_out, p->d_key_bytes,
                     p->d_key_off, p->d_payload, p->d_out, p->d_hit};
     for (void* b : bufs) cudaFree(b);

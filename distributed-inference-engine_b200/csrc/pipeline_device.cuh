@@ -97,8 +97,10 @@ constexpr int WCHUNK = 1024;  // log records per victim-window chunk
 struct PipeBufs {
     uint8_t* code;
     unsigned long long* value;
-    int32_t* miss_rank;
-    int32_t* miss_req;
+    uint8_t* lrank;     // [B] rank of a miss among the misses of its get CTA (PT requests per CTA)
+    int32_t* cta_miss;  // [ceil(B / PT)] misses per get CTA
+    int32_t* cta_base;  // [ceil(B / PT)] exclusive prefix of cta_miss: rank of a miss = cta_base[q / PT] + lrank[q]
+    int32_t* miss_req;  // rank -> request (written by the pack CTAs, read by the GEMM epilogue)
     int32_t* set_slot;
     int32_t* set_row;
     uint32_t* wmask;   // [n_chunks][32]: which of a chunk's 1024 log records are current
