@@ -70,6 +70,7 @@ struct die_pipeline {
     int graph_steps;          // K; 0 = always launch from the stream
     cudaStream_t cap_stream;  // capture only: the caller's stream may be the legacy stream, which cannot capture
     die::QueueDesc* qdesc;    // device
+    uint32_t* digests_all;    // [graph_steps][max_batch][4]: the digests of all batches of a replay
     // staging of die_pipeline_run_host_many's grouped form: NBUF sets of graph_steps batches each, so that one
     // copy per array moves a whole group and one replay computes it
     uint8_t* g_keys;
@@ -256,6 +257,20 @@ pipe_get_kernel(StepRef sr, PipeBufs pb, uint4* __restrict__ digests, int B, con
     if (threadIdx.x == 0) pb.ctrl->ts[2] = globaltimer_ns();  // all CTAs probed, tail starts
     pipe_rank_tail(kv, pb, B, (int)gridDim.x);
     if (sr.q && threadIdx.x == 0) trace_mark_q(sr.q, sr.i, TR_GET_TAIL);
+}
+
+// ROUTE of all K batches of a replay in one launch (grid.y = step): hashing a batch's keys does not depend on
+// the batches before it, so it leaves the step's critical path; the get kernels then start from the digests.
+__global__ void __launch_bounds__(PT)
+pipe_hash_all_kernel(const QueueDesc* __restrict__ q, uint4* __restrict__ digests, int B) {
+    __shared__ __align__(16) uint8_t stage[ROUTE_STAGE_BYTES + 32];
+    StepRef sr;
+    sr.q = q;
+    sr.i = (int)blockIdx.y;
+    const StepArgs a = step_resolve(sr);
+    const Md5State st = cta_hash_keys(a.key_bytes, a.key_off, B, stage);
+    const int i = blockIdx.x * PT + threadIdx.x;
+    if (i < B) digests[(size_t)blockIdx.y * B + i] = make_uint4(st.a, st.b, st.c, st.d);
 }
 
 // CTAs [0, g_claim): KVCache.set of every miss (all known absent).  Last n_chunks CTAs: LRU victim window.
@@ -572,15 +587,26 @@ static die_status_t graph_get(die_pipeline* p, bool from_keys, uint32_t* digests
         p->n_graphs -= 1;
     }
     if (!p->cap_stream) DIE_CUDA(cudaStreamCreateWithFlags(&p->cap_stream, cudaStreamNonBlocking));
+    if (from_keys && !p->digests_all)  // before the capture starts: no allocation inside one
+        DIE_CUDA(cudaMalloc(&p->digests_all, (size_t)std::max(p->graph_steps, K) * p->cfg.max_batch * 16));
     cudaGraph_t graph = nullptr;
     DIE_CUDA(cudaStreamBeginCapture(p->cap_stream, cudaStreamCaptureModeThreadLocal));
     die_status_t st = DIE_OK;
+    if (from_keys) {  // one hash launch for the whole replay
+        if (p->digests_all) {
+            pipe_hash_all_kernel<<<dim3(ceil_div(B, PT), K), PT, 0, p->cap_stream>>>(qd, reinterpret_cast<uint4*>(p->digests_all), B);
+            if (cudaGetLastError() != cudaSuccess) st = DIE_ERR_CUDA;
+        }
+    }
     for (int i = 0; i < K && st == DIE_OK; ++i) {
         StepRef sr;
         memset(&sr, 0, sizeof(sr));
         sr.q = qd;
         sr.i = i;
-        st = launch_fast(p, sr, from_keys, digests, B, n_req_dev, p->cap_stream);
+        if (from_keys && p->digests_all)
+            st = launch_fast(p, sr, false, p->digests_all + (size_t)i * B * 4, B, n_req_dev, p->cap_stream);
+        else
+            st = launch_fast(p, sr, from_keys, digests, B, n_req_dev, p->cap_stream);
     }
     const cudaError_t e = cudaStreamEndCapture(p->cap_stream, &graph);
     if (st != DIE_OK) {
@@ -622,7 +648,7 @@ static die_status_t replay_fast(die_pipeline* p, QueueDesc d, QueueDesc* qd, boo
     DIE_LAUNCH_CHECK();
     DIE_CUDA(cudaGraphLaunch(exec, s));
     count_replay();
-    count_launch((unsigned)(K * pipeline_launches_per_step(p)));
+    count_launch((unsigned)(K * pipeline_launches_per_step(p)) + (from_keys ? 1u : 0u));
     return DIE_OK;
 }
 
@@ -751,6 +777,7 @@ extern "C" die_status_t die_pipeline_destroy(die_pipeline_t* p) {
                     p->d_key_off, p->d_payload, p->d_out, p->d_hit};
     for (void* b : bufs) cudaFree(b);
     cudaFree(p->qdesc);
+    cudaFree(p->digests_all);
     cudaFree(p->g_keys); cudaFree(p->g_off); cudaFree(p->g_pay); cudaFree(p->g_out); cudaFree(p->g_hit);
     for (int g = 0; g < p->n_graphs; ++g) cudaGraphExecDestroy(p->graphs[g].exec);
     if (p->cap_stream) cudaStreamDestroy(p->cap_stream);
