@@ -20,6 +20,7 @@
 namespace die {
 
 constexpr int XCHG_MAX_WORLD = 16;
+constexpr int XCHG_SETS = 4;  // buffer sets: steps in flight between ingest and scatter
 struct PeerPtrs {
     void* p[XCHG_MAX_WORLD];
 };
@@ -370,9 +371,12 @@ __global__ void xchg_barrier_kernel(PeerPtrs flags, unsigned int* my_flags, int 
 
 }  // namespace die
 
-// Everything one in-flight step touches.  Two lanes (step parity) let step b+1's ingest half (route, bucket,
-// dispatch) and step b's return half overlap the owner pipeline of the neighbouring step: each lane has its
-// own stream, its own half of the symmetric window (rows, back, counts, barrier flags) and its own scratch.
+// Everything one in-flight step touches: its part of the symmetric window (rows, back, counts, barrier flags)
+// and its scratch.  Step b uses set b % XCHG_SETS, so up to XCHG_SETS steps are in flight between ingest and
+// scatter.  Reuse is safe without extra synchronisation across ranks: a peer's dispatch of step b+SETS follows
+// its barrier of step b+SETS-1, which the owner only reaches after it compacted step b (and the same one stage
+// later for the return windows); on this rank the set's `done` event orders its own reuse.
+static_assert(XCHG_SETS == 4, "QueueDesc::epoch0 has one entry per buffer set");
 struct XchgLane {
     PeerPtrs rows, back, counts, flags;
     float* my_rows;
@@ -390,23 +394,28 @@ struct XchgLane {
     int32_t* loc;      // [cap] owner << 16 | rank among the route CTA's requests for that owner
     int32_t* cta_cnt;  // [ceil(cap / 256)][XCHG_MAX_WORLD] requests per owner of every route CTA
     unsigned int epoch;
-    cudaStream_t stream;
-    cudaEvent_t done;  // the lane's last enqueued kernel
+    bool used;             // `done` was recorded since the last fork: the next user of the set waits for it
+    cudaEvent_t done;      // the step that used this set last has scattered its results
+    cudaEvent_t ingested;  // the step's requests are compacted: the owner pass may start
+    cudaEvent_t owned;     // the owner pass is done: the results may go back
 };
 
 struct die_xchg {
     int world, rank, cap, dim;
     int bmax;  // most requests the owner side handles per step (the pipeline's max_batch)
     die_pipeline_t* pipe;
-    XchgLane lane[2];
+    XchgLane lane[XCHG_SETS];
     unsigned int* error_flag;
-    unsigned long long steps;  // steps enqueued so far: parity picks the lane
-    cudaEvent_t owner_done;    // end of the latest owner pass: the KV table sees batches in step order
-    bool owner_pending;
-    cudaEvent_t entry;
+    unsigned long long steps;  // steps enqueued so far: step b uses set b % XCHG_SETS
+    // One in-order stream per stage, every step passes through all three: while the owner pass of step b runs,
+    // step b+1 is being ingested and step b-1 is on its way back.
+    cudaStream_t s_in;   // route, dispatch, barrier, compact
+    cudaStream_t s_own;  // the pipeline on the received batch (the only stage that touches the table); high priority
+    cudaStream_t s_ret;  // return, barrier, scatter
+    cudaEvent_t entry, exit_ev;
     // captured replays of K steps
     struct Replay {
-        int B, K, lane0;
+        int B, K, set0;
         cudaGraphExec_t exec;
     };
     static constexpr int MAX_GRAPHS = 8;
@@ -421,8 +430,8 @@ static size_t xchg_rows_bytes(int world, int cap, int dim) { return (size_t)worl
 static size_t xchg_lane_bytes(int world, int cap, int dim) { return 2 * xchg_rows_bytes(world, cap, dim) + 256 + 256; }
 
 extern "C" uint64_t die_xchg_window_bytes(int32_t world, int32_t cap, int32_t dim) {
-    // per lane: receive rows + return rows + counts + barrier flags
-    return 2 * xchg_lane_bytes(world, cap, dim);
+    // per buffer set: receive rows + return rows + counts + barrier flags
+    return XCHG_SETS * xchg_lane_bytes(world, cap, dim);
 }
 
 extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap, int32_t dim, int32_t owner_max,
@@ -444,7 +453,9 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
     const size_t rb = xchg_rows_bytes(world, cap, dim);
     const size_t lb = xchg_lane_bytes(world, cap, dim);
     const size_t bmax = (size_t)x->bmax;
-    for (int l = 0; l < 2; ++l) {
+    int prio_low = 0, prio_high = 0;  // numerically lower = higher priority
+    DIE_CUDA(cudaDeviceGetStreamPriorityRange(&prio_low, &prio_high));
+    for (int l = 0; l < XCHG_SETS; ++l) {
         XchgLane& L = x->lane[l];
         for (int i = 0; i < XCHG_MAX_WORLD; ++i) {
             char* base = i < world ? static_cast<char*>(peer_windows[i]) + l * lb : nullptr;
@@ -467,10 +478,14 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
         DIE_CUDA(cudaMalloc(&L.prefix, (world + 1) * sizeof(int32_t)));
         DIE_CUDA(cudaMalloc(&L.loc, cap * sizeof(int32_t)));
         DIE_CUDA(cudaMalloc(&L.cta_cnt, (size_t)ceil_div(cap, ROUTE_THREADS) * XCHG_MAX_WORLD * sizeof(int32_t)));
-        DIE_CUDA(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
         DIE_CUDA(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
+        DIE_CUDA(cudaEventCreateWithFlags(&L.ingested, cudaEventDisableTiming));
+        DIE_CUDA(cudaEventCreateWithFlags(&L.owned, cudaEventDisableTiming));
     }
-    DIE_CUDA(cudaEventCreateWithFlags(&x->owner_done, cudaEventDisableTiming));
+    DIE_CUDA(cudaStreamCreateWithPriority(&x->s_in, cudaStreamNonBlocking, prio_low));
+    DIE_CUDA(cudaStreamCreateWithPriority(&x->s_own, cudaStreamNonBlocking, prio_high));
+    DIE_CUDA(cudaStreamCreateWithPriority(&x->s_ret, cudaStreamNonBlocking, prio_low));
+    DIE_CUDA(cudaEventCreateWithFlags(&x->exit_ev, cudaEventDisableTiming));
     DIE_CUDA(cudaEventCreateWithFlags(&x->entry, cudaEventDisableTiming));
     DIE_CUDA(cudaMalloc(&x->error_flag, sizeof(unsigned int)));
     DIE_CUDA(cudaMemset(x->error_flag, 0, sizeof(unsigned int)));
@@ -484,19 +499,24 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
 
 extern "C" die_status_t die_xchg_destroy(die_xchg_t* x) {
     if (!x) return DIE_OK;
-    for (int l = 0; l < 2; ++l) {
+    for (cudaStream_t st : {x->s_in, x->s_own, x->s_ret})
+        if (st) {
+            cudaStreamSynchronize(st);
+            cudaStreamDestroy(st);
+        }
+    if (x->exit_ev) cudaEventDestroy(x->exit_ev);
+    for (int l = 0; l < XCHG_SETS; ++l) {
         XchgLane& L = x->lane[l];
-        if (L.stream) cudaStreamSynchronize(L.stream);
         void* bufs[] = {L.shard, L.digests, L.recv_dig, L.recv_pay, L.recv_out,
                         L.recv_hit, L.n_dev, L.prefix, L.loc, L.cta_cnt};
         for (void* b : bufs) cudaFree(b);
         if (L.done) cudaEventDestroy(L.done);
-        if (L.stream) cudaStreamDestroy(L.stream);
+        if (L.ingested) cudaEventDestroy(L.ingested);
+        if (L.owned) cudaEventDestroy(L.owned);
     }
     for (int g = 0; g < x->n_graphs; ++g) cudaGraphExecDestroy(x->graphs[g].exec);
     if (x->cap_stream) cudaStreamDestroy(x->cap_stream);
     cudaFree(x->qdesc);
-    if (x->owner_done) cudaEventDestroy(x->owner_done);
     if (x->entry) cudaEventDestroy(x->entry);
     cudaFree(x->error_flag);
     delete x;
@@ -505,9 +525,10 @@ extern "C" die_status_t die_xchg_destroy(die_xchg_t* x) {
 
 // qd != nullptr: the launch is being captured for replay; `epoch_off` is the barrier's rank on its lane inside
 // the replay and the lane's epoch before the replay comes from the descriptor.
-static die_status_t xchg_barrier(die_xchg* x, XchgLane& L, int lane, const QueueDesc* qd, unsigned int epoch) {
-    DIE_LAUNCH(ST_XCHG_BARRIER, L.stream, xchg_barrier_kernel<<<1, 32, 0, L.stream>>>(L.flags, L.my_flags, x->world, x->rank, epoch,
-                                                                             qd, lane, x->error_flag));
+static die_status_t xchg_barrier(die_xchg* x, XchgLane& L, int lane, const QueueDesc* qd, unsigned int epoch,
+                                 cudaStream_t s) {
+    DIE_LAUNCH(ST_XCHG_BARRIER, s, xchg_barrier_kernel<<<1, 32, 0, s>>>(L.flags, L.my_flags, x->world, x->rank, epoch, qd,
+                                                                        lane, x->error_flag));
     return DIE_OK;
 }
 
@@ -520,24 +541,29 @@ static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user,
                                      int32_t* shard_out, const QueueDesc* qd, unsigned int epoch_first,
                                      const double* reserve_now) {
     XchgLane& L = x->lane[lane];
-    cudaStream_t s = L.stream;
     const int W = x->world, D = x->dim, vdim = D / 4;
     int32_t* shard = shard_out ? shard_out : L.shard;
     const int n_cta = std::max(1, ceil_div(B, ROUTE_THREADS));
     const size_t off_bytes = (size_t)n_cta * W * sizeof(int);
+    // ---- stage 1, ingest: this set's scratch and windows are free once its previous step has scattered
+    cudaStream_t s = x->s_in;
+    if (L.used) DIE_CUDA(cudaStreamWaitEvent(s, L.done, 0));
     DIE_LAUNCH(ST_ROUTE, s, xchg_route_kernel<<<n_cta, ROUTE_THREADS, 0, s>>>(
         user, B, W, shard, reinterpret_cast<uint4*>(L.digests), L.loc, L.cta_cnt));
     DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_rows(B), 256, off_bytes, s>>>(
         user, reinterpret_cast<const int4*>(L.digests), L.loc, L.cta_cnt, n_cta, B, vdim, W, x->rank, x->cap, L.rows,
         L.counts));
-    DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first));  // every rank's rows have landed in their owners' windows
+    DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first, s));  // every rank's rows have landed in their owners' windows
     DIE_LAUNCH(ST_XCHG_COMPACT, s, xchg_compact_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, s>>>(
         reinterpret_cast<const int4*>(L.my_rows), L.my_cnt, W, x->cap, vdim, (long long)x->bmax,
         reinterpret_cast<int4*>(L.recv_dig), reinterpret_cast<int4*>(L.recv_pay), L.n_dev, L.prefix, x->error_flag));
-    if (x->owner_pending) DIE_CUDA(cudaStreamWaitEvent(s, x->owner_done, 0));  // the table sees batches in step order
+    DIE_CUDA(cudaEventRecord(L.ingested, s));
+    // ---- stage 2, owner pass: one in-order stream, so the table sees the batches in step order
+    cudaStream_t so = x->s_own;
+    DIE_CUDA(cudaStreamWaitEvent(so, L.ingested, 0));
     if (reserve_now) {
         unsigned long long tail0;
-        DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, 1, s, &owner.a.kv, &tail0, nullptr));
+        DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, 1, so, &owner.a.kv, &tail0, nullptr));
         owner.a.now = *reserve_now;
         owner.a.t_get = tail0;
         owner.a.t_set = tail0 + (unsigned long long)x->bmax;
@@ -545,29 +571,37 @@ static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user,
     owner.a.payload = L.recv_pay;
     owner.a.out = L.recv_out;
     owner.a.code = L.recv_hit;
-    DIE_TRY(pipeline_owner_launch(x->pipe, owner, L.recv_dig, x->bmax, L.n_dev, s));
-    DIE_CUDA(cudaEventRecord(x->owner_done, s));
-    x->owner_pending = true;
-    DIE_LAUNCH(ST_XCHG_RETURN, s, xchg_return_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, s>>>(
+    DIE_TRY(pipeline_owner_launch(x->pipe, owner, L.recv_dig, x->bmax, L.n_dev, so));
+    DIE_CUDA(cudaEventRecord(L.owned, so));
+    // ---- stage 3, way back
+    cudaStream_t sr = x->s_ret;
+    DIE_CUDA(cudaStreamWaitEvent(sr, L.owned, 0));
+    DIE_LAUNCH(ST_XCHG_RETURN, sr, xchg_return_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, sr>>>(
         reinterpret_cast<const int4*>(L.recv_out), L.recv_hit, L.prefix, W, x->rank, x->cap, vdim, L.back));
-    DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first + 1));  // every owner's results are back in the sources' windows
-    DIE_LAUNCH(ST_XCHG_SCATTER, s, xchg_scatter_kernel<<<grid_for_rows(B), 256, off_bytes, s>>>(
+    DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first + 1, sr));  // every owner's results are back in the sources' windows
+    DIE_LAUNCH(ST_XCHG_SCATTER, sr, xchg_scatter_kernel<<<grid_for_rows(B), 256, off_bytes, sr>>>(
         user, reinterpret_cast<const int4*>(L.my_back), L.loc, L.cta_cnt, n_cta, B, W, x->cap, vdim));
+    DIE_CUDA(cudaEventRecord(L.done, sr));
+    L.used = true;
     return DIE_OK;
 }
 
-// Lanes start after the work already on `from` and `from` continues after both lanes have drained.
+// The stage streams start after the work already on `from`; `to` continues after the last step has scattered
+// (s_ret is in order and every step ends there, so its tail covers all three streams).
 static die_status_t xchg_fork(die_xchg* x, cudaStream_t from) {
     DIE_CUDA(cudaEventRecord(x->entry, from));
-    for (int l = 0; l < 2; ++l) DIE_CUDA(cudaStreamWaitEvent(x->lane[l].stream, x->entry, 0));
-    x->owner_pending = false;  // everything earlier is ordered through `from`
+    for (cudaStream_t st : {x->s_in, x->s_own, x->s_ret}) DIE_CUDA(cudaStreamWaitEvent(st, x->entry, 0));
+    for (int l = 0; l < XCHG_SETS; ++l) x->lane[l].used = false;  // everything earlier is ordered through `from`
     return DIE_OK;
 }
 static die_status_t xchg_join(die_xchg* x, cudaStream_t to) {
-    for (int l = 0; l < 2; ++l) {
-        DIE_CUDA(cudaEventRecord(x->lane[l].done, x->lane[l].stream));
-        DIE_CUDA(cudaStreamWaitEvent(to, x->lane[l].done, 0));
-    }
+    // s_in and s_own first: a stream pulled into a capture must be joined back even if it did no work
+    DIE_CUDA(cudaEventRecord(x->exit_ev, x->s_in));
+    DIE_CUDA(cudaStreamWaitEvent(x->s_own, x->exit_ev, 0));
+    DIE_CUDA(cudaEventRecord(x->exit_ev, x->s_own));
+    DIE_CUDA(cudaStreamWaitEvent(x->s_ret, x->exit_ev, 0));
+    DIE_CUDA(cudaEventRecord(x->exit_ev, x->s_ret));
+    DIE_CUDA(cudaStreamWaitEvent(to, x->exit_ev, 0));
     return DIE_OK;
 }
 
@@ -575,7 +609,7 @@ static die_status_t xchg_join(die_xchg* x, cudaStream_t to) {
 static die_status_t xchg_enqueue_step(die_xchg* x, const uint8_t* key_bytes, const int64_t* key_off, int32_t B,
                                       const float* payload, double now, float* out, uint8_t* hit_out,
                                       int32_t* shard_out) {
-    const int lane = (int)(x->steps & 1);
+    const int lane = (int)(x->steps % XCHG_SETS);
     XchgLane& L = x->lane[lane];
     x->steps += 1;
     StepRef user, owner;
@@ -591,11 +625,11 @@ static die_status_t xchg_enqueue_step(die_xchg* x, const uint8_t* key_bytes, con
     return xchg_launch_step(x, lane, user, owner, B, shard_out, nullptr, e, &now);
 }
 
-// K steps captured once per (B, K, first lane); qd[0] describes the ingested queue, qd[1] the owner passes.
+// K steps captured once per (B, K, first buffer set); qd[0] describes the ingested queue, qd[1] the owner passes.
 static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_t* out) {
-    const int lane0 = (int)(x->steps & 1);
+    const int lane0 = (int)(x->steps % XCHG_SETS);
     for (int g = 0; g < x->n_graphs; ++g)
-        if (x->graphs[g].B == B && x->graphs[g].K == K && x->graphs[g].lane0 == lane0) {
+        if (x->graphs[g].B == B && x->graphs[g].K == K && x->graphs[g].set0 == lane0) {
             *out = x->graphs[g].exec;
             return DIE_OK;
         }
@@ -607,9 +641,10 @@ static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_
     cudaGraph_t graph = nullptr;
     DIE_CUDA(cudaStreamBeginCapture(x->cap_stream, cudaStreamCaptureModeThreadLocal));
     die_status_t st = xchg_fork(x, x->cap_stream);
-    unsigned int off[2] = {1u, 1u};
+    unsigned int off[XCHG_SETS];
+    for (int l = 0; l < XCHG_SETS; ++l) off[l] = 1u;
     for (int i = 0; i < K && st == DIE_OK; ++i) {
-        const int lane = (lane0 + i) & 1;
+        const int lane = (lane0 + i) % XCHG_SETS;
         StepRef user, owner;
         memset(&user, 0, sizeof(user));
         memset(&owner, 0, sizeof(owner));
@@ -622,7 +657,6 @@ static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_
     }
     if (st == DIE_OK) st = xchg_join(x, x->cap_stream);
     const cudaError_t e = cudaStreamEndCapture(x->cap_stream, &graph);
-    x->owner_pending = false;
     if (st != DIE_OK) {
         if (graph) cudaGraphDestroy(graph);
         return st;
@@ -635,7 +669,7 @@ static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_
     die_xchg::Replay& r = x->graphs[x->n_graphs++];
     r.B = B;
     r.K = K;
-    r.lane0 = lane0;
+    r.set0 = lane0;
     r.exec = exec;
     *out = exec;
     return DIE_OK;
@@ -660,8 +694,8 @@ extern "C" die_status_t die_xchg_step(die_xchg_t* x, const uint8_t* key_bytes, c
     return xchg_join(x, user);
 }
 
-// A queue of flushed batches.  Consecutive steps run on alternating lanes, so a step's ingest and return
-// halves overlap its neighbours' owner passes; groups of K steps are replayed from one captured graph (host
+// A queue of flushed batches.  Consecutive steps use different buffer sets and every stage has its own stream,
+// so a step's ingest and return overlap its neighbours' owner passes; groups of K steps are replayed from one captured graph (host
 // cost: two launches per K steps).  out / hit_out are rings of out_ring slots (>= 2 when n_batches > 1).
 extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, const uint8_t* key_bytes,
                                            int64_t key_bytes_stride, const int64_t* key_off, int64_t key_off_stride,
@@ -702,16 +736,15 @@ extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, con
             DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, K, user, &dw.kv, &tail0, &mirror));
             dw.tail0 = tail0;
             du.j0 = dw.j0 = j;
-            for (int l = 0; l < 2; ++l) du.epoch0[l] = x->lane[l].epoch;
+            for (int l = 0; l < XCHG_SETS; ++l) du.epoch0[l] = x->lane[l].epoch;
             du.trace = dw.trace = trace_buffer();
             xchg_desc_set_kernel<<<1, 1, 0, user>>>(x->qdesc, du, dw, mirror);
             DIE_LAUNCH_CHECK();
             DIE_CUDA(cudaGraphLaunch(exec, user));
             count_replay();
             count_launch((unsigned)(K * (7 + pipeline_launches_per_step(x->pipe))));
-            const int lane0 = (int)(x->steps & 1);
-            x->lane[lane0].epoch += 2u * (unsigned)((K + 1) / 2);
-            x->lane[lane0 ^ 1].epoch += 2u * (unsigned)(K / 2);
+            const int set0 = (int)(x->steps % XCHG_SETS);
+            for (int i = 0; i < K; ++i) x->lane[(set0 + i) % XCHG_SETS].epoch += 2u;  // two barriers per step
             x->steps += (unsigned long long)K;
         }
     }

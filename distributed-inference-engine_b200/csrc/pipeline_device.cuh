@@ -43,7 +43,7 @@ struct QueueDesc {
     int batch;     // stamps per get (= per set) pass of one step
     double now0, now_step;
     unsigned long long tail0;  // LRU stamp of the replay's first op
-    unsigned int epoch0[2];    // exchange only: barrier epoch of each lane before the replay
+    unsigned int epoch0[4];    // exchange only: barrier epoch of each buffer set before the replay
     unsigned long long* trace; // diagnostics (die_debug_trace_enable): [0] cursor, [1] capacity, then (tag, ns) pairs
 };
 
