@@ -200,6 +200,25 @@ class ClockSampler(threading.Thread):
                 "nvml_ms_per_sample": round(1e3 * self.query_s / len(s), 3) if s else None}
 
 
+def ncu_traffic(kernel_name):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel_name`, from the committed
+    `ncu --set full` capture of this bench command (profiles/ncu_full_r01_pipeline_kernels.csv)."""
+    import csv
+    path = os.path.join(ROOT, "profiles", "ncu_full_r01_pipeline_kernels.csv")
+    try:
+        rows = list(csv.reader(open(path)))
+        hdr, units = rows[0], rows[1]
+        i_name, i_r, i_w = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        vals = [float(r[i_r]) * scale[units[i_r]] + float(r[i_w]) * scale[units[i_w]]
+                for r in rows[2:] if len(r) == len(hdr) and kernel_name in r[i_name]]
+        if vals:
+            return round(sum(vals) / len(vals)), "profiles/ncu_full_r01_pipeline_kernels.csv (mean of %d launches)" % len(vals)
+    except Exception:  # noqa: BLE001
+        pass
+    return None, None
+
+
 # ----------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------------------------
@@ -377,8 +396,10 @@ def main():
                             "alg_bytes_per_launch": round(alg.get(name, 0)), "gbs": round(gbs, 1),
                             "frac_of_hbm_peak": round(gbs / peak, 4)}
         dom = max(stages, key=lambda n: stages[n]["share"])
+        traffic, traffic_src = ncu_traffic(stages[dom]["kernel"])
         roofline = {"kernel": stages[dom]["kernel"], "bound": "hbm", "achieved": stages[dom]["gbs"], "peak": peak,
-                    "unit": "GB/s", "frac": stages[dom]["frac_of_hbm_peak"], "traffic": None, "peak_source": peak_src,
+                    "unit": "GB/s", "frac": stages[dom]["frac_of_hbm_peak"], "traffic": traffic, "traffic_source": traffic_src,
+                    "peak_source": peak_src,
                     "us_per_launch": stages[dom]["us_per_launch"], "alg_bytes_per_launch": stages[dom]["alg_bytes_per_launch"],
                     "note": "a 4096-request batch carries ~5 MB of algorithmic traffic (<1 us at peak): every kernel of the "
                             "step sits on its launch + dependent-DRAM-latency floor, see DESIGN.md section 5"}

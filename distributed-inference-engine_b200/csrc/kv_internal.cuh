@@ -287,6 +287,7 @@ struct die_kv {
     uint64_t op_cap;
     uint64_t dropped_prefix;  // dropped values written by earlier chunks of the last set batch
     uint32_t* log_spare;      // second LRU-log buffer, allocated at the first compaction and reused
+    unsigned int* tile_cnt;   // compaction scratch: current records per tile of 4096 log positions
     unsigned long long* n_kept_dev;
     die::KvMirror* mirror;    // pinned + mapped host memory (device-visible at the same address)
     uint64_t ops_enq;         // insert ops reserved so far (monotone)

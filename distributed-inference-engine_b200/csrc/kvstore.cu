@@ -407,28 +407,79 @@ kv_set_evict_kernel(KvView kv, const uint4* __restrict__ digests, const unsigned
 // ------------------------------------------------------------------------------------------------
 // maintenance: re-append the current LRU records at the tail of a fresh ring (order kept)
 // ------------------------------------------------------------------------------------------------
+// Three launches over tiles of WIN_THREADS * WIN_ITEMS log positions, any number of CTAs:
+//   count   current records per tile
+//   scan    exclusive prefix of the tile counts (one CTA; one value per 4096 positions)
+//   move    record r of the old log -> position tail + (current records before it), its slot re-stamped
+// Whether position p is current depends only on the stamp of the slot log[p] names, and a slot that is moved
+// was current at some other position p' != p, so moving stamps never changes the verdict of another
+// position: the passes need no ordering beyond the kernel boundaries, and `move` may recompute the verdicts.
+__device__ __forceinline__ unsigned compact_tile_flags(const KvView& kv, unsigned long long pos, unsigned long long tail,
+                                                       bool (&valid)[WIN_ITEMS], uint32_t (&slot)[WIN_ITEMS]) {
+    unsigned cnt = 0;
+#pragma unroll
+    for (int k = 0; k < WIN_ITEMS; ++k) {
+        const unsigned long long p = pos + (unsigned long long)threadIdx.x * WIN_ITEMS + k;
+        valid[k] = p < tail && record_current(kv, p, slot[k]);
+        cnt += valid[k];
+    }
+    return cnt;
+}
+
 __global__ void __launch_bounds__(WIN_THREADS)
-kv_compact_kernel(KvView kv, uint32_t* __restrict__ new_log, unsigned long long tail,
-                  unsigned long long* __restrict__ n_kept) {
-    __shared__ unsigned int s_warp[32];
-    const int tid = threadIdx.x;
-    unsigned long long kept = 0;
-    const unsigned long long head = kv.st->head;
-    __syncthreads();
-    for (unsigned long long pos = head; pos < tail; pos += (unsigned long long)WIN_THREADS * WIN_ITEMS) {
+kv_compact_count_kernel(KvView kv, unsigned long long head, unsigned long long tail, unsigned long long n_tiles,
+                        unsigned int* __restrict__ tile_cnt) {
+    constexpr unsigned long long TILE = (unsigned long long)WIN_THREADS * WIN_ITEMS;
+    for (unsigned long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
         bool valid[WIN_ITEMS];
         uint32_t slot[WIN_ITEMS];
-        unsigned cnt = 0;
+        const unsigned cnt = compact_tile_flags(kv, head + t * TILE, tail, valid, slot);
+        __shared__ unsigned int s_sum;
+        if (threadIdx.x == 0) s_sum = 0u;
+        __syncthreads();
+        unsigned w = cnt;
 #pragma unroll
-        for (int k = 0; k < WIN_ITEMS; ++k) {
-            const unsigned long long p = pos + (unsigned long long)tid * WIN_ITEMS + k;
-            valid[k] = p < tail && record_current(kv, p, slot[k]);
-            cnt += valid[k];
-        }
+        for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
+        if ((threadIdx.x & 31) == 0 && w) atomicAdd(&s_sum, w);
+        __syncthreads();
+        if (threadIdx.x == 0) tile_cnt[t] = s_sum;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+kv_compact_scan_kernel(KvView kv, unsigned int* __restrict__ tile_cnt, unsigned long long n_tiles,
+                       unsigned long long tail, unsigned long long* __restrict__ n_kept) {
+    __shared__ unsigned int s_warp[32];
+    unsigned long long base = 0;
+    for (unsigned long long t0 = 0; t0 < n_tiles; t0 += 1024) {
+        const unsigned long long t = t0 + threadIdx.x;
+        const unsigned cnt = t < n_tiles ? tile_cnt[t] : 0u;
         unsigned excl;
         const unsigned total = block_scan_1024(cnt, excl, s_warp);
-        unsigned long long rank = kept + excl;
-        __syncthreads();  // every validity check of this tile is done before any stamp moves
+        // live records never exceed the table's capacity (< 2^32), so 32-bit prefixes are exact
+        if (t < n_tiles) tile_cnt[t] = (unsigned)(base + excl);
+        base += total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        *n_kept = base;
+        kv.st->head = tail;
+    }
+}
+
+__global__ void __launch_bounds__(WIN_THREADS)
+kv_compact_move_kernel(KvView kv, uint32_t* __restrict__ new_log, unsigned long long head, unsigned long long tail,
+                       unsigned long long n_tiles, const unsigned int* __restrict__ tile_base) {
+    __shared__ unsigned int s_warp[32];
+    constexpr unsigned long long TILE = (unsigned long long)WIN_THREADS * WIN_ITEMS;
+    for (unsigned long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        bool valid[WIN_ITEMS];
+        uint32_t slot[WIN_ITEMS];
+        const unsigned cnt = compact_tile_flags(kv, head + t * TILE, tail, valid, slot);
+        unsigned excl;
+        block_scan_1024(cnt, excl, s_warp);
+        unsigned long long rank = (unsigned long long)tile_base[t] + excl;
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; ++k) {
             if (!valid[k]) continue;
@@ -437,12 +488,7 @@ kv_compact_kernel(KvView kv, uint32_t* __restrict__ new_log, unsigned long long 
             kv.slots[slot[k]].stamp = np;
             ++rank;
         }
-        kept += total;
         __syncthreads();
-    }
-    if (tid == 0) {
-        *n_kept = kept;
-        kv.st->head = tail;
     }
 }
 
@@ -553,7 +599,17 @@ static die_status_t kv_maintain(die_kv* kv, int force, cudaStream_t s) {
         unsigned long long* n_kept = kv->n_kept_dev;
         if (!new_log) DIE_CUDA(cudaMalloc(&new_log, kv->ring_cap * sizeof(uint32_t)));
         DIE_CUDA(cudaMemsetAsync(new_log, 0xff, kv->ring_cap * sizeof(uint32_t), s));
-        DIE_LAUNCH(ST_KV_MAINT, s, kv_compact_kernel<<<1, WIN_THREADS, 0, s>>>(view_of(kv), new_log, kv->tail, n_kept));
+        const unsigned long long n_tiles = (span + (unsigned long long)WIN_THREADS * WIN_ITEMS - 1) / ((unsigned long long)WIN_THREADS * WIN_ITEMS);
+        if (!kv->tile_cnt)
+            DIE_CUDA(cudaMalloc(&kv->tile_cnt, (kv->ring_cap / ((uint64_t)WIN_THREADS * WIN_ITEMS) + 2) * sizeof(unsigned int)));
+        if (n_tiles) {
+            const int grid = (int)std::min<unsigned long long>(n_tiles, (unsigned long long)num_sms() * 2);
+            DIE_LAUNCH(ST_KV_MAINT, s, kv_compact_count_kernel<<<grid, WIN_THREADS, 0, s>>>(view_of(kv), h.head, kv->tail, n_tiles, kv->tile_cnt));
+            DIE_LAUNCH(ST_KV_MAINT, s, kv_compact_scan_kernel<<<1, 1024, 0, s>>>(view_of(kv), kv->tile_cnt, n_tiles, kv->tail, n_kept));
+            DIE_LAUNCH(ST_KV_MAINT, s, kv_compact_move_kernel<<<grid, WIN_THREADS, 0, s>>>(view_of(kv), new_log, h.head, kv->tail, n_tiles, kv->tile_cnt));
+        } else {
+            DIE_LAUNCH(ST_KV_MAINT, s, kv_compact_scan_kernel<<<1, 1024, 0, s>>>(view_of(kv), kv->tile_cnt, 0ull, kv->tail, n_kept));
+        }
         unsigned long long kept = 0;
         DIE_CUDA(cudaMemcpyAsync(&kept, n_kept, sizeof(kept), cudaMemcpyDeviceToHost, s));
         DIE_CUDA(cudaStreamSynchronize(s));
@@ -722,6 +778,7 @@ extern "C" die_status_t die_kv_destroy(die_kv_t* kv) {
     cudaFree(kv->slots_spare);
     cudaFree(kv->log);
     cudaFree(kv->log_spare);
+    cudaFree(kv->tile_cnt);
     cudaFree(kv->n_kept_dev);
     if (kv->mirror) cudaFreeHost(kv->mirror);
     cudaFree(kv->st);
