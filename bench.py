@@ -149,13 +149,21 @@ def workload_config(n_gpus):
 # clocks
 # ----------------------------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
+    """SM clock and throttle reasons while the timed region executes (pynvml = what nvidia-smi reads).
+
+    An NVML query is not free here: it takes 2-3 ms and, on these boxes, CUDA-graph launches issued meanwhile
+    wait for it (a 2 ms polling period slowed the step 6x).  So the sampler never queries while the host is
+    still submitting work: the bench calls sample_now() right after the last step of the timed region is
+    enqueued, i.e. while the GPU is still executing that region, and again every `period` (the recipe's 200 ms)
+    only if the region lasts that long."""
+
     def __init__(self, index):
         super().__init__(daemon=True)
         self.samples, self.reasons, self.stop_flag, self.max_mhz = [], set(), False, None
-        # the recipe's period (nvidia-smi -lms 200); the first sample is taken as soon as the region starts.
-        # NVML queries are not free: on some boxes one query stalls graph launches for over a millisecond
         self.period = float(os.environ.get("DIE_BENCH_SAMPLER_MS", "200")) / 1e3
         self.query_s = 0.0
+        self.wake = threading.Event()
+        self.requested = self.served = 0
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -165,39 +173,54 @@ class ClockSampler(threading.Thread):
         except Exception:  # noqa: BLE001
             self.nv = None
 
-    def run(self):
-        if self.nv is None or self.period <= 0:
-            return
+    def _query(self):
         nv = self.nv
         names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
                  "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
                  "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
                  "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
-        while not self.stop_flag:
+        try:
+            t_q = time.perf_counter()
+            self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
             try:
-                t_q = time.perf_counter()
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
-                try:
-                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
-                except Exception:  # noqa: BLE001
-                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                for k, bit in names.items():
-                    if mask & bit:
-                        self.reasons.add(k)
-                self.query_s += time.perf_counter() - t_q
+                mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
             except Exception:  # noqa: BLE001
-                pass
-            t_next = time.perf_counter() + self.period
-            while not self.stop_flag and time.perf_counter() < t_next:
-                time.sleep(0.005)
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            for k, bit in names.items():
+                if mask & bit:
+                    self.reasons.add(k)
+            self.query_s += time.perf_counter() - t_q
+        except Exception:  # noqa: BLE001
+            pass
+
+    def run(self):
+        if self.nv is None or self.period <= 0:
+            return
+        while not self.stop_flag:
+            self.wake.wait(timeout=self.period)
+            if self.stop_flag:
+                break
+            self.wake.clear()
+            want = self.requested
+            self._query()           # periodic (timeout) or on demand (sample_now)
+            self.served = max(self.served, want)
+
+    def sample_now(self):
+        self.requested += 1
+        self.wake.set()
 
     def result(self):
+        t_end = time.perf_counter() + 1.0
+        while self.nv is not None and self.period > 0 and self.served < self.requested and time.perf_counter() < t_end:
+            time.sleep(0.0005)   # the requested query is still in flight
         self.stop_flag = True
+        self.wake.set()
         self.join(timeout=1.0)
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
                 "samples": len(s), "period_ms": 1e3 * self.period,
-                "nvml_ms_per_sample": round(1e3 * self.query_s / len(s), 3) if s else None}
+                "nvml_ms_per_sample": round(1e3 * self.query_s / len(s), 3) if s else None,
+                "when": "after the last step of the timed region was enqueued, while the GPU was still executing it"}
 
 
 def ncu_traffic(kernel_name):
@@ -219,14 +242,83 @@ def ncu_traffic(kernel_name):
     return None, None
 
 
+def e2e_sharded(runner, rng, K, now, off_d, world):
+    """End to end at N > 1: every rank's batches start in pinned host memory and its results end there.  Groups of
+    16 batches: one H2D copy per array, one die_xchg_step_many call (one graph replay), one D2H copy per array;
+    three device staging sets on three streams keep the copy engines on the neighbouring groups.  Wall clock
+    between two barriers, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    G = 16
+    n_groups = max(2, K // G)
+    n = n_groups * G
+    _, keys, _, x = make_batches(rng, n)
+    hk = torch.from_numpy(keys).pin_memory()
+    hx = torch.from_numpy(x).pin_memory()
+    hout = torch.empty((n, B, D), dtype=torch.float32).pin_memory()
+    hhit = torch.empty((n, B), dtype=torch.uint8).pin_memory()
+    NS = 3
+    dk = [torch.zeros((G + 1, B * KEY_LEN), dtype=torch.uint8, device="cuda") for _ in range(NS)]  # +1 row of slack
+    dx = [torch.empty((G, B, D), dtype=torch.float32, device="cuda") for _ in range(NS)]
+    dout = [torch.empty((G, B, D), dtype=torch.float32, device="cuda") for _ in range(NS)]
+    dhit = [torch.empty((G, B), dtype=torch.uint8, device="cuda") for _ in range(NS)]
+    s_in, s_out, cur = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.current_stream()
+    ev_in = [torch.cuda.Event() for _ in range(NS)]
+    ev_done = [torch.cuda.Event() for _ in range(NS)]
+    ev_out = [torch.cuda.Event() for _ in range(NS)]
+
+    def run(first_group, count, now0):
+        for g in range(first_group, first_group + count):
+            b = g % NS
+            lo, hi = (g % n_groups) * G, (g % n_groups) * G + G
+            with torch.cuda.stream(s_in):
+                if g - first_group >= NS:
+                    s_in.wait_event(ev_done[b])
+                dk[b][:G].copy_(hk[lo:hi], non_blocking=True)
+                dx[b].copy_(hx[lo:hi], non_blocking=True)
+                ev_in[b].record(s_in)
+            cur.wait_event(ev_in[b])
+            if g - first_group >= NS:
+                cur.wait_event(ev_out[b])
+            runner.step_many(dk[b][:G], off_d, dx[b], now0 + (g - first_group) * G * DT_E2E, DT_E2E, dout[b], dhit[b])
+            ev_done[b].record(cur)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev_done[b])
+                hout[lo:hi].copy_(dout[b], non_blocking=True)
+                hhit[lo:hi].copy_(dhit[b], non_blocking=True)
+                ev_out[b].record(s_out)
+        s_out.synchronize()
+        cur.synchronize()
+
+    run(0, 2, now)                         # warm the staging path and the graphs
+    now += 2 * G * DT_E2E
+    torch.cuda.synchronize()
+    dist.barrier()
+    t0 = time.perf_counter()
+    run(0, n_groups, now)
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dt = float(t[0])
+    runner.check()
+    return {"value": world * n * B / dt, "unit": "requests/s",
+            "h2d_bytes_per_step": B * KEY_LEN + B * D * 4, "d2h_bytes_per_step": B * D * 4 + B,
+            "ms_per_step": 1e3 * dt / n, "steps": n,
+            "api": "PeerDispatcher.step_many (die_xchg_step_many) on groups of 16 batches staged from / to pinned host "
+                   "buffers on every rank; copy-in, sharded steps and copy-out of consecutive groups overlap"}, now + n * DT_E2E
+
+
+DT_E2E = 0.01
+
+
 # ----------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernels", action="store_true",
@@ -307,6 +399,7 @@ def main():
     now = run_steps(kd[W:], xd[W:], now)
     t_host = time.perf_counter() - t_host  # host time to enqueue the queue (no wait on the GPU)
     ev1.record()
+    sampler.sample_now()  # everything is enqueued: the query can no longer hold up a launch
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -323,6 +416,11 @@ def main():
 
     # ---- e2e: host buffers through the C-ABI (H2D + kernels + D2H inside the timed region) ---------------------
     e2e = None
+    if world > 1 and hasattr(runner, "step_many"):
+        try:
+            e2e, now = e2e_sharded(runner, rng, K, now, off_d, world)
+        except Exception as exc:  # noqa: BLE001  (the device-resident number above stands on its own)
+            e2e = {"value": None, "unit": "requests/s", "error": repr(exc)[:300]}
     if world == 1:
         _, keys, off, x = make_batches(rng, K + 3)
         hk = torch.from_numpy(np.concatenate([keys, np.zeros((K + 3, 16), np.uint8)], axis=1)).pin_memory()

@@ -110,7 +110,7 @@ def test_two_gpu_sharded_dispatch_matches_oracle(mode):
         assert dict(ret) == {0: "ok", 1: "ok"}
 
 
-def _ragged_worker(rank, world, port, ret):
+def _ragged_worker(rank, world, port, ret, peer=False):
     """BASELINE.json configs[2]: ragged 16..2048-element payloads, max_batch 256, hash-sharded with the all-to-all
     dispatch; echo model (the reference's).  Batcher pack -> sharded dispatch -> unpack, vs the oracle."""
     sys.path[:0] = [ROOT, os.path.join(ROOT, "distributed-inference-engine_b200")]
@@ -121,11 +121,16 @@ def _ragged_worker(rank, world, port, ret):
     try:
         from die import ops
         from die.batcher import PackedBatch, pack_requests, unpack_results
-        from die.exchange import ShardedDispatcher
+        from die.exchange import PeerDispatcher, ShardedDispatcher
         from oracle.pipeline import OraclePipeline
         B, Lpad, steps, max_size = 256, 2048, 6, 400
+        if peer:
+            max_size = 600  # the fused owner pipeline needs max_size >= its batch capacity (2 x 256)
         rng = np.random.default_rng(17)
-        disp = ShardedDispatcher(world, rank, max_size, B, Lpad, None, None, 50.0, model="echo")
+        if peer:   # 8 KB rows through the NVLink peer-store step
+            disp = PeerDispatcher(world, rank, max_size, B, Lpad, None, None, 50.0, model="echo")
+        else:
+            disp = ShardedDispatcher(world, rank, max_size, B, Lpad, None, None, 50.0, model="echo")
         ref = OraclePipeline(world, max_size, 50.0, lambda rows: list(rows))
         now = 1.0
         for _ in range(steps):
@@ -145,16 +150,19 @@ def _ragged_worker(rank, world, port, ret):
             assert shard.tolist() == want["shard"] and hit.tolist() == want["hit"]
             for g, w_ in zip(got, want["out"]):
                 assert np.array_equal(g.cpu().numpy(), w_)
+        if peer:
+            disp.check()
         ret[rank] = "ok"
     finally:
         dist.destroy_process_group()
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (run with gpurun --gpus 2)")
-def test_two_gpu_ragged_c3_dispatch_matches_oracle():
+@pytest.mark.parametrize("peer", [False, True], ids=["nccl", "peer"])
+def test_two_gpu_ragged_c3_dispatch_matches_oracle(peer):
     import torch.multiprocessing as mp
-    port = 29700 + (os.getpid() % 2000)
+    port = 29700 + (os.getpid() % 2000) + (7 if peer else 0)
     with mp.Manager() as m:
         ret = m.dict()
-        mp.spawn(_ragged_worker, args=(2, port, ret), nprocs=2, join=True)
+        mp.spawn(_ragged_worker, args=(2, port, ret, peer), nprocs=2, join=True)
         assert dict(ret) == {0: "ok", 1: "ok"}

@@ -133,6 +133,26 @@ def run(kv_entries=10_000_000, quick=False):
     K.append(entry("linear_tf32_kernel", s, rows * 1024 + 65536, rows, "rows", peak, "131072 x 128 -> 128, tcgen05 kind::tf32"))
     del xs
 
+    # ---- bf16 MLP (C5: hidden 4096, batch 8192): the tensor-bound kernel of the path --------------------------------
+    try:
+        tf_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
+        tf_src = "MEASURED_PEAKS.json bf16_tflops (cuBLAS 8192^3, burst)"
+    except Exception:  # noqa: BLE001
+        tf_peak, tf_src = 2250.0, "nominal dense bf16 2.25 PFLOP/s"
+    Bm, Dm, Hm = 8192, 4096, 4096
+    xs = [torch.empty((Bm, Dm), dtype=torch.bfloat16, device="cuda").normal_() for _ in range(2)]
+    w1 = torch.empty((Hm, Dm), dtype=torch.bfloat16, device="cuda").normal_(0, Dm ** -0.5)
+    w2 = torch.empty((Dm, Hm), dtype=torch.bfloat16, device="cuda").normal_(0, Hm ** -0.5)
+    b1 = torch.zeros(Hm, dtype=torch.float32, device="cuda")
+    b2 = torch.zeros(Dm, dtype=torch.float32, device="cuda")
+    s = timed(lambda i: ops.mlp_fwd_bf16(xs[i % 2], w1, b1, w2, b2), 5)
+    flops = 2 * 2.0 * Bm * Dm * Hm
+    out["mlp_bf16"] = {"kernel": "mlp_gemm_kernel x2 (tcgen05 kind::f16, TMA, TMEM)", "batch": Bm, "dim": Dm, "hidden": Hm,
+                       "ms_per_forward": round(s * 1e3, 4), "tflops": round(flops / s / 1e12, 1), "peak_tflops": tf_peak,
+                       "peak_source": tf_src, "frac_of_tensor_peak": round(flops / s / 1e12 / tf_peak, 4),
+                       "rows_per_s": round(Bm / s, 1)}
+    del xs, w1, w2
+
     # ---- KV probe / fill on a large table (C4: 10M entries, LRU + TTL, 90 % hits) -----------------------------------
     n_entries = kv_entries if not quick else 1_000_000
     kv = DeviceKV(n_entries, 300.0)
