@@ -55,6 +55,30 @@ void count_launch(unsigned n = 1);     // gpu_launches accounting for bench.py
         DIE_LAUNCH_CHECK();                        \
     } while (0)
 
+// ---- programmatic dependent launch ---------------------------------------------------------------------
+// The step is a chain of short kernels; with this attribute a kernel's CTAs are scheduled while the previous
+// kernel of the stream drains, run their prologue (argument / descriptor loads, independent operand fetches)
+// and block in pdl_wait() until that kernel has completed and its writes are visible.  Every CTA of such a
+// kernel calls pdl_wait() before it touches anything a predecessor wrote.  DIE_PDL=0 launches them normally.
+bool pdl_enabled();
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+
 #define DIE_TRY(expr)                        \
     do {                                     \
         die_status_t s__ = (expr);           \

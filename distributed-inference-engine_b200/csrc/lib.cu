@@ -48,6 +48,14 @@ static unsigned long long g_trace_cap = 0;
 unsigned long long* trace_buffer() { return g_trace; }
 
 bool prof_active() { return g_prof_on; }
+bool pdl_enabled() {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("DIE_PDL");
+        on = e ? (atoi(e) != 0) : 1;
+    }
+    return on != 0;
+}
 void prof_before(int stage, cudaStream_t s) {
     if (!g_prof_on) return;
     ProfRec r{stage, get_event(), get_event(), s};

@@ -45,6 +45,7 @@ linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, con
         sc.pb.code = step.code;
     }
     if (SCATTER && (int)blockIdx.x >= sc.tiles) {  // eviction CTAs (kvstore.py:82-93), 256 window records each
+        pdl_wait();
         pipe_evict_cta(step.kv, sc.pb, (int)((blockIdx.x - sc.tiles) * gridDim.y + blockIdx.y), step.t_set);
         return;
     }
@@ -53,9 +54,7 @@ linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, con
     uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
     __shared__ __align__(8) uint64_t bar;
     __shared__ uint32_t tmem_base;
-    if (n_rows_dev) B = min(B, (int)*n_rows_dev);
     const int m0 = blockIdx.x * TC_M, n0 = blockIdx.y * Nc;
-    if (m0 >= B) return;  // uniform for the CTA
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int KB = K / 32;             // 128-byte (32 x tf32) blocks along K
     const int chunks_per_row = K / 4;  // 16-byte chunks per operand row
@@ -68,17 +67,21 @@ linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, con
 
     // operands -> shared memory with cp.async (LDGSTS): a warp owns a row, lanes own its 16-byte chunks, so
     // every request is one contiguous 512-byte row segment and nothing is staged in registers
-    for (int r = warp; r < TC_M; r += TC_THREADS / 32) {
+    // the weights do not depend on the step: their tile is fetched while the previous kernel is still draining
+    for (int r = warp; r < Nc; r += TC_THREADS / 32) {
+        const float* src = W + (size_t)(n0 + r) * K;
+        for (int ck = lane; ck < chunks_per_row; ck += 32)
+            cp_async16(b_base + (size_t)(ck >> 3) * ((size_t)Nc * 128) + tc::sw128_offset(r, ck & 7), src + ck * 4, 16u);
+    }
+    pdl_wait();  // the packed rows and their count come from the previous kernels
+    if (n_rows_dev) B = min(B, (int)*n_rows_dev);
+    const bool idle = m0 >= B;  // uniform for the CTA: nothing to compute, but the TMEM columns must be returned
+    for (int r = warp; r < TC_M && !idle; r += TC_THREADS / 32) {
         const bool live = m0 + r < B;
         const float* src = X + (size_t)(live ? m0 + r : 0) * K;
         for (int ck = lane; ck < chunks_per_row; ck += 32)
             cp_async16(a_base + (size_t)(ck >> 3) * (TC_M * 128) + tc::sw128_offset(r, ck & 7), src + ck * 4,
                        live ? 16u : 0u);  // src-size 0 zero-fills rows past the end of the batch
-    }
-    for (int r = warp; r < Nc; r += TC_THREADS / 32) {
-        const float* src = W + (size_t)(n0 + r) * K;
-        for (int ck = lane; ck < chunks_per_row; ck += 32)
-            cp_async16(b_base + (size_t)(ck >> 3) * ((size_t)Nc * 128) + tc::sw128_offset(r, ck & 7), src + ck * 4, 16u);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -87,6 +90,10 @@ linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, con
     __syncthreads();
     tc::fence_after_thread_sync();
     const uint32_t taddr = tmem_base;
+    if (idle) {  // tile past the end of the batch (its size is only known on the device)
+        if (warp == 0) tc::tmem_dealloc(taddr, ncols);
+        return;
+    }
 
     if (tid == 0) {
         const uint32_t idesc = tc::instr_desc(tc::FMT_TF32, TC_M, (uint32_t)Nc);
@@ -187,7 +194,8 @@ static die_status_t tf32_launch(const float* X, const float* W, const float* b, 
         sc.tiles = tiles;
         const int evict_ctas = sc.pb.n_chunks * (WCHUNK / PT);
         dim3 grid(tiles + ceil_div(evict_ctas, n_split), n_split);
-        DIE_LAUNCH(ST_MODEL, s, linear_tf32_kernel<true><<<grid, TC_THREADS, smem, s>>>(X, W, b, Y, B, K, N, Nc, n_rows_dev, sc));
+        DIE_LAUNCH(ST_MODEL, s, launch_pdl(linear_tf32_kernel<true>, grid, dim3(TC_THREADS), smem, s, X, W, b, Y, B, K, N, Nc,
+                                           n_rows_dev, sc));
     } else {
         dim3 grid(tiles, n_split);
         DIE_LAUNCH(ST_MODEL, s, linear_tf32_kernel<false><<<grid, TC_THREADS, smem, s>>>(X, W, b, Y, B, K, N, Nc, n_rows_dev, TcScatter{}));

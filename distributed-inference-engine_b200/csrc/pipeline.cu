@@ -205,7 +205,6 @@ pipe_get_kernel(StepRef sr, PipeBufs pb, uint4* __restrict__ digests, int B, con
     if (n_req_dev) B = min(B, (int)*n_req_dev);  // batch size known only on the device (after an exchange)
     const int i = blockIdx.x * PT + threadIdx.x;
     const bool active = i < B;
-    if (i == 0) pb.ctrl->ts[0] = globaltimer_ns();  // kernel start (CTA 0)
     u128 key{0ull, 0ull};
     if (FROM_KEYS) {
         const Md5State st = cta_hash_keys(key_bytes, key_off, B, stage);
@@ -214,11 +213,11 @@ pipe_get_kernel(StepRef sr, PipeBufs pb, uint4* __restrict__ digests, int B, con
             digests[i] = d;
             key = fp_of(d);
         }
-    } else if (active) {
-        key = fp_of(digests[i]);
     }
+    pdl_wait();  // the table, the control block and (when precomputed) the digests belong to earlier kernels
+    if (!FROM_KEYS && active) key = fp_of(digests[i]);
     int code = 0;
-    if (i == 0) pb.ctrl->ts[1] = globaltimer_ns();  // keys hashed (CTA 0)
+    if (i == 0) pb.ctrl->ts[0] = pb.ctrl->ts[1] = globaltimer_ns();  // predecessor done, keys hashed (CTA 0)
     if (active) {
         unsigned long long value;
         long long s;
@@ -280,6 +279,7 @@ pipe_claim_pack_kernel(StepRef sr, PipeBufs pb, const uint4* __restrict__ digest
                        const uint32_t* __restrict__ n_req_dev, int g_claim, const int4* __restrict__ arena, int vin,
                        int vout, int4* __restrict__ packed_in) {
     const StepArgs a = step_resolve(sr);
+    pdl_wait();
     trace_mark(sr, TR_CLAIM);
     const KvView& kv = a.kv;
     const double now = a.now;
@@ -354,6 +354,7 @@ __global__ void __launch_bounds__(PT)
 pipe_unpack_evict_kernel(StepRef sr, PipeBufs pb, const int4* __restrict__ packed_out, int B,
                          const uint32_t* __restrict__ n_req_dev, int g_evict, int vout, int4* __restrict__ arena) {
     const StepArgs a = step_resolve(sr);
+    pdl_wait();
     trace_mark(sr, TR_UNPACK);
     const KvView& kv = a.kv;
     const unsigned long long t_set = a.t_set;
@@ -501,13 +502,14 @@ static die_status_t launch_fast(die_pipeline* p, const StepRef& sr, bool from_ke
     const int g = ceil_div(B, PT);
     uint4* dg = reinterpret_cast<uint4*>(digests);
     if (from_keys)
-        DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<true><<<g, PT, 0, s>>>(sr, pb, dg, B, n_req_dev));
+        DIE_LAUNCH(ST_KV_GET, s, launch_pdl(pipe_get_kernel<true>, dim3(g), dim3(PT), 0, s, sr, pb, dg, B, n_req_dev));
     else
-        DIE_LAUNCH(ST_KV_GET, s, pipe_get_kernel<false><<<g, PT, 0, s>>>(sr, pb, dg, B, n_req_dev));
+        DIE_LAUNCH(ST_KV_GET, s, launch_pdl(pipe_get_kernel<false>, dim3(g), dim3(PT), 0, s, sr, pb, dg, B, n_req_dev));
     const int g_pack = grid_256((long long)B * std::max(vin, vout));
-    DIE_LAUNCH(ST_KV_CLAIM, s, pipe_claim_pack_kernel<<<g + g_pack + p->n_chunks, PT, 0, s>>>(
-        sr, pb, dg, B, n_req_dev, g, reinterpret_cast<const int4*>(p->arena), vin, vout,
-        reinterpret_cast<int4*>(p->packed_in)));
+    DIE_LAUNCH(ST_KV_CLAIM, s, launch_pdl(pipe_claim_pack_kernel, dim3(g + g_pack + p->n_chunks), dim3(PT), 0, s, sr, pb,
+                                          static_cast<const uint4*>(dg), B, n_req_dev, g,
+                                          reinterpret_cast<const int4*>(p->arena), vin, vout,
+                                          reinterpret_cast<int4*>(p->packed_in)));
     if (c.model == DIE_MODEL_LINEAR_TF32) {
         // third and last launch: tensor-core GEMM whose epilogue is the UNPACK, plus the eviction CTAs
         TcScatter sc;
@@ -529,8 +531,9 @@ static die_status_t launch_fast(die_pipeline* p, const StepRef& sr, bool from_ke
     }
     const int g_unpack = grid_256((long long)B * vout);
     const int g_evict = p->n_chunks * (WCHUNK / PT);
-    DIE_LAUNCH(ST_UNPACK_STORE, s, pipe_unpack_evict_kernel<<<g_evict + g_unpack, PT, 0, s>>>(
-        sr, pb, reinterpret_cast<const int4*>(result), B, n_req_dev, g_evict, vout, reinterpret_cast<int4*>(p->arena)));
+    DIE_LAUNCH(ST_UNPACK_STORE, s, launch_pdl(pipe_unpack_evict_kernel, dim3(g_evict + g_unpack), dim3(PT), 0, s, sr, pb,
+                                              reinterpret_cast<const int4*>(result), B, n_req_dev, g_evict, vout,
+                                              reinterpret_cast<int4*>(p->arena)));
     return DIE_OK;
 }
 
