@@ -2,7 +2,8 @@
 //
 // The reference moves every request to its worker over TCP + JSON, one connection each
 // (src/worker.py:84-133).  Here rank r writes the rows it routed to shard d straight into d's receive
-// window over NVLink: one kernel packs (gather by bucket order) AND sends, no staging copy, no collective,
+// window over NVLink: one kernel packs AND sends (in request order; the slot inside the owner's region is
+// computed in the route kernel, there is no bucket pass and no permutation), no staging copy, no collective,
 // no host round trip.  Peer addresses come from a symmetric allocation the host exchanged once
 // (torch.distributed._symmetric_memory); a device-side barrier of that allocation separates the phases.
 //
@@ -14,6 +15,11 @@
 // cap = the ingest batch size, so no bucket can overflow whatever the key distribution or health state.
 // Owners see the sources in rank order, request order kept inside each source: the order the CPU oracle's
 // process_exchange applies.
+//
+// die_xchg_step / die_xchg_step_many run the step as a three-stage pipeline (ingest | owner pass | way back, one
+// in-order stream each) over XCHG_SETS buffer sets, and replay groups of steps from one CUDA graph; the
+// stand-alone phase entry points (die_xchg_dispatch / compact / return / scatter, bucket order from
+// die_bucket_by_shard) stay as a cross-check driven from Python.
 #include "pipeline_internal.cuh"
 #include "route_device.cuh"
 

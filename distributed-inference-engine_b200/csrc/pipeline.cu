@@ -3,17 +3,21 @@
 // but never wrote.  Cached values are result rows in `arena`; the table hands out row handles.
 //
 // Fast sequence (max_batch <= kv_max_size, so a batch can never need more victims than the table
-// holds and the sequential replay of kvstore.cu is unreachable) -- 4 launches per flushed batch:
-//   1 pipe_get_kernel         MD5 of the keys (model_registry.py:159) + KVCache.get per request
-//                             (kvstore.py:136-164); the last CTA to finish then ranks the misses in
-//                             request order (batcher.py:211) and walks the LRU log for the victim
-//                             candidates of this batch's inserts (kvstore.py:82-93)
-//   2 pipe_claim_pack_kernel  misses: insert key (kvstore.py:104-134) | PACK payload -> packed[rank];
-//                             hits: cached result row -> out
-//   3 model forward           packed -> packed_out (echo / linear)            (fake_model.py:52)
-//   4 pipe_unpack_evict_kernel UNPACK packed_out[rank] -> out[q] (batcher.py:225-227) and -> the
-//                             cached row of the op that owns the slot | evict the LRU victims
+// holds and the sequential replay of kvstore.cu is unreachable) -- 3 launches per flushed batch:
+//   1 pipe_get_kernel         MD5 of the keys (model_registry.py:159; hoisted into pipe_hash_all_kernel when
+//                             a queue is replayed) + KVCache.get per request (kvstore.py:136-164); every CTA
+//                             ranks its own misses in request order (batcher.py:211), the last CTA to finish
+//                             scans the per-CTA counts and resets the batch's control block
+//   2 pipe_claim_pack_kernel  CTAs side by side: insert the missing keys (kvstore.py:104-134) | PACK payload ->
+//                             packed[rank], hits: cached result row -> out | bitmap of the still-current LRU-log
+//                             records in the victim window (kvstore.py:82-93)
+//   3 linear_tf32_kernel<SCATTER> (model_tc.cu)  packed -> GEMM -> UNPACK in the epilogue: out[q] and the cached
+//                             row (batcher.py:225-227); extra CTAs evict the batch's LRU victims.
+//     echo / fp32 models: model kernel + pipe_unpack_evict_kernel instead (4 launches)
 // General sequence (tiny caches): the stand-alone kernels of kvstore.cu, 9 launches.
+//
+// Queues of batches (die_pipeline_run_device_many / run_host_many) are processed in groups of graph_steps
+// steps replayed from one CUDA graph: see StepRef / QueueDesc in pipeline_device.cuh and replay_fast() below.
 #include "model_internal.cuh"
 #include "pipeline_device.cuh"
 #include "pipeline_internal.cuh"

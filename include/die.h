@@ -303,9 +303,11 @@ die_status_t die_xchg_return(const float* out, const uint8_t* hit, const int32_t
 die_status_t die_xchg_scatter(const float* back, const int32_t* perm, const int64_t* offsets, int32_t B, int32_t world,
                               int32_t cap, int32_t dim_out, float* out, uint8_t* hit, die_stream_t stream);
 
-/* The whole sharded step in one call (same kernels as above plus a flag barrier inside the window), so that the
- * host pays a handful of launches per flushed batch.  The caller allocates one symmetric window of
- * die_xchg_window_bytes() per rank (zero-filled), exchanges the addresses and passes all of them as
+/* The whole sharded step in one call: route (+ slot ranking), dispatch, flag barrier inside the window, compact,
+ * owner pipeline, return, barrier, scatter -- three in-order stage streams over four buffer sets, so consecutive
+ * steps overlap; die_xchg_step_many replays groups of steps from one CUDA graph (host: two launches per group).
+ * The caller allocates one symmetric window of die_xchg_window_bytes() per rank (zero-filled; it holds four
+ * buffer sets), exchanges the addresses and passes all of them as
  * peer_windows [host, world entries].  Every rank must make the same sequence of calls: the barriers are collective.
  * Requires one rank per GPU.  die_xchg_check_sync reports a barrier that timed out. */
 typedef struct die_xchg die_xchg_t;
@@ -326,13 +328,17 @@ die_status_t die_xchg_check_sync(die_xchg_t* x, die_stream_t stream);
 
 /* A queue of n flushed batches in one call (each batch is still one pass of the path, applied strictly in
  * order): batch j reads key_bytes + j*key_bytes_stride, key_off + j*key_off_stride (0 = shared offsets),
- * payload + j*B*dim_in; device form writes out + (j % out_ring)*B*dim_out and hit_out + (j % out_ring)*B. */
+ * payload + j*B*dim_in; device form writes out + (j % out_ring)*B*dim_out and hit_out + (j % out_ring)*B.
+ * Groups of 16 batches (environment DIE_GRAPH_STEPS; 0 = off) are replayed from one captured CUDA graph whose
+ * kernels read their per-batch arguments from a device-resident descriptor: same results as n single calls
+ * (tests/test_gpu_pipeline.py), host cost two launches per group. */
 die_status_t die_pipeline_run_device_many(die_pipeline_t* p, int32_t n_batches, const uint8_t* key_bytes,
                                           int64_t key_bytes_stride, const int64_t* key_off, int64_t key_off_stride,
                                           int32_t B, const float* payload, double now0, double now_step, float* out,
                                           uint8_t* hit_out, int32_t out_ring, die_stream_t stream);
-/* Host-buffer form ([host] pinned pointers; out [n,B,dim_out], hit_out [n,B]): copy-in, kernels and copy-out of
- * consecutive batches overlap on three streams.  Synchronises before returning. */
+/* Host-buffer form ([host] pinned pointers; out [n,B,dim_out], hit_out [n,B]): one copy per array and one
+ * replay per group of batches; copy-in, kernels and copy-out of consecutive groups overlap on three streams
+ * over three staging sets.  Synchronises before returning. */
 die_status_t die_pipeline_run_host_many(die_pipeline_t* p, int32_t n_batches, const uint8_t* key_bytes /*[host]*/,
                                         int64_t key_bytes_stride, const int64_t* key_off /*[host]*/,
                                         int64_t key_off_stride, int32_t B, const float* payload /*[host]*/,
