@@ -14,7 +14,7 @@ from .mock_models import FakeModel, LinearModel, MLPModel, mock_batch_inference
 __all__ = ["Batch", "BatchedRequest", "Batcher", "PackedBatch", "ModelConfig", "ModelRegistry", "ModelShard",
            "ModelStatus", "ModelVersion", "Router", "WorkerHealth", "WorkerInfo", "Worker", "FakeModel",
            "LinearModel", "MLPModel", "mock_batch_inference", "KVCache", "KVStore", "create_kv_store", "CacheEntry",
-           "DispatchPipeline"]
+           "DispatchPipeline", "Coordinator"]
 
 
 def __getattr__(name):  # torch-dependent modules load lazily
@@ -24,4 +24,7 @@ def __getattr__(name):  # torch-dependent modules load lazily
     if name == "DispatchPipeline":
         from .pipeline import DispatchPipeline
         return DispatchPipeline
+    if name == "Coordinator":
+        from .coordinator import Coordinator
+        return Coordinator
     raise AttributeError(name)

@@ -74,6 +74,39 @@ def test_reference_composition_goldens(name):
             assert lru_digests(pipes[s]) == [hashlib.md5(k.encode()).digest() for k in want["lru"]]
 
 
+@pytest.mark.parametrize("name", sorted(load_golden("pipeline.json").keys()))
+def test_coordinator_matches_reference_compositions(name):
+    """die.Coordinator = the composition the reference's README describes (Router -> per-shard cache -> batcher ->
+    model) as product code: same golden runs of the reference's own classes, grouping by shard done by the
+    bucket kernel instead of by the test, health-aware routing and failover included."""
+    from die import Coordinator, ModelRegistry, Router
+    c = load_golden("pipeline.json")[name]
+    n = c["n_shards"]
+    reg = ModelRegistry()
+    reg.register_model("m", "1", "/p", {}, {})
+    router = Router(reg)
+    for s in range(n):
+        reg.add_shard("m", "1", s, f"w{s}")
+        router.register_worker(f"w{s}", f"127.0.0.1:{9000 + s}")
+        router.mark_worker_success(f"w{s}")
+    for s in c["unhealthy"]:
+        for _ in range(3):
+            router.mark_worker_failure(f"w{s}")
+    co = Coordinator(router, "m", "1", c["max_size"], 512, WIDTH, model="echo", default_ttl=c["default_ttl"])
+    for step in c["steps"]:
+        keys = [k for ks, _ in step["per_rank"] for k in ks]
+        pays = [p for _, ps in step["per_rank"] for p in ps]
+        out, hit, shard = co.process(keys, torch.from_numpy(pad(pays)).cuda(), step["now"])
+        assert shard.tolist() == step["shard"] and hit.tolist() == step["hit"]
+        out = out.cpu().numpy()
+        for i, want in enumerate(step["out"]):
+            assert out[i, :len(want)].tolist() == [float(v) for v in want], i
+        for s in range(n):
+            st, want = co.pipes[s].kv.stats(), step["state"][s]
+            assert (st["hits"], st["misses"], st["evictions"], st["size"]) == (want["hits"], want["misses"], want["evictions"], want["size"])
+            assert lru_digests(co.pipes[s]) == [hashlib.md5(k.encode()).digest() for k in want["lru"]]
+
+
 @pytest.mark.parametrize("model,B,kv_size,space,steps", [("echo", 4096, 20000, 30000, 16), ("linear", 4096, 6000, 9000, 12),
                                                          ("linear", 1000, 300, 500, 20), ("linear_tf32", 4096, 6000, 9000, 10)])
 def test_seeded_batches_vs_oracle(model, B, kv_size, space, steps):
