@@ -549,6 +549,34 @@ def main():
                     "note": "a 4096-request batch carries ~5 MB of algorithmic traffic (<1 us at peak): every kernel of the "
                             "step sits on its launch + dependent-DRAM-latency floor, see DESIGN.md section 5"}
 
+    # ---- host-side API edge of the drop-in classes: str -> bytes -> device, list of rows -> padded device batch ----
+    api_edge = None
+    if world == 1:
+        try:
+            from die.batcher import pack_requests
+            ids1, _, _, x1 = make_batches(rng, 1)
+            strs = ["user-%010d" % i for i in ids1[0]]
+            rows = [x1[0][i] for i in range(B)]
+            ops.KeyBatch.from_strings(strs)
+            pack_requests(rows, Lpad=D)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(5):
+                ops.KeyBatch.from_strings(strs)
+            torch.cuda.synchronize()
+            t_keys = (time.perf_counter() - t0) / 5
+            t0 = time.perf_counter()
+            for _ in range(5):
+                pack_requests(rows, Lpad=D)
+            torch.cuda.synchronize()
+            t_pack = (time.perf_counter() - t0) / 5
+            api_edge = {"keys_str_to_device_us_per_batch": round(1e6 * t_keys, 1),
+                        "payload_rows_to_packed_device_us_per_batch": round(1e6 * t_pack, 1),
+                        "note": "Python-object edge of Router.route(keys) / Batcher (encode + H2D + pack kernel) for one "
+                                "4096-request batch; never part of value, e2e or the kernel rooflines"}
+        except Exception as exc:  # noqa: BLE001
+            api_edge = {"error": repr(exc)[:200]}
+
     # ---- every kernel of the path alone, at sizes where bandwidth (not launch latency) is the limit -------------
     kernels = None
     if world == 1 and not args.no_kernels:
@@ -570,7 +598,7 @@ def main():
                 "data": "synthetic", "config": dict(workload_config(world), hit_rate=round(hit_rate, 4), model=MODEL),
                 "gpu_launches": int(launches), "host_enqueue_us_per_step": round(1e6 * t_host / K, 2),
                 "clocks": clocks, "e2e": e2e, "roofline": roofline, "stages": stages,
-                "kernels": kernels, "cpu_baseline": cpu}
+                "kernels": kernels, "api_edge": api_edge, "cpu_baseline": cpu}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
