@@ -285,3 +285,27 @@ def test_kv_constructor_surface_without_gpu():
     assert KVStore is KVCache and create_kv_store is KVCache
     e = CacheEntry(value=1, created_at=2.0, last_accessed=3.0)
     assert (e.access_count, e.ttl) == (0, None)
+
+
+def test_header_is_c99_and_the_c_example_links(tmp_path):
+    """The boundary is a C ABI: include/die.h must compile as plain C, and a plain-C caller (examples/pipeline_host.c)
+    must build and link against libdie.so.  Without a GPU it has to fail loudly at its first device call."""
+    import subprocess
+    import torch
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    libdir = os.path.join(root, "distributed-inference-engine_b200", "die", "_lib")
+    if not os.path.exists(os.path.join(libdir, "libdie.so")):
+        import __graft_entry__ as g
+        g.build()
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-fsyntax-only", "-x", "c",
+                    os.path.join(root, "include", "die.h")], check=True)
+    exe = str(tmp_path / "pipeline_host")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(root, "include"),
+                    os.path.join(root, "examples", "pipeline_host.c"), "-o", exe, "-L" + libdir, "-ldie",
+                    "-Wl,-rpath," + libdir], check=True)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    if torch.cuda.is_available():
+        assert r.returncode == 0, r.stderr
+        assert "pass 0 hits: 0 0 0 0 0 0 0 0" in r.stdout and "pass 1 hits: 1 1 1 1 1 1 1 1" in r.stdout
+    else:
+        assert r.returncode == 1 and "die_set_device" in r.stderr
