@@ -6,6 +6,7 @@ import hashlib
 import os
 import random
 import re
+import sys
 
 import numpy as np
 import pytest
@@ -309,3 +310,24 @@ def test_header_is_c99_and_the_c_example_links(tmp_path):
         assert "pass 0 hits: 0 0 0 0 0 0 0 0" in r.stdout and "pass 1 hits: 1 1 1 1 1 1 1 1" in r.stdout
     else:
         assert r.returncode == 1 and "die_set_device" in r.stderr
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` (the reference's pure-Python path on the host cores) needs no GPU and must print
+    one JSON line with the keys the driver reads; under torchrun only rank 0 prints."""
+    import json
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-500:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+              "vs_baseline", "dtype", "data", "config", "impl", "cpu_baseline", "e2e"):
+        assert k in line, k
+    assert line["impl"] == "reference" and line["value"] > 0 and line["cpu_baseline"]["kind"] == "port"
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and "workload" in line["config"]
+    env = dict(os.environ, RANK="1", WORLD_SIZE="2")
+    r1 = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2"],
+                        capture_output=True, text=True, timeout=120, env=env)
+    assert r1.returncode == 0 and r1.stdout.strip() == ""
