@@ -45,6 +45,8 @@ struct KvState {
     unsigned long long status, slow_batches, n_dropped_last;
     // per set-batch scratch (reset by the last kernel of each batch)
     unsigned long long n_pre, n_absent, min_prev, n_new, conflict, n_dropped;
+    // victim window of the stand-alone set path: 0 none / sequential, 1 tiles (parallel), 2 one-CTA walk
+    unsigned long long win_mode, win_origin, win_hnew;
     // hit / miss counters of the batched get, spread over 16 x 64-byte lines so that thousands of CTAs do not
     // serialise on one L2 atomic unit; readers add them to hits / misses
     unsigned long long hit_part[16][8], miss_part[16][8];

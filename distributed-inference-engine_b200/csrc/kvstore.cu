@@ -182,28 +182,152 @@ __device__ unsigned long long lru_window_select(const KvView& kv, unsigned long 
     return s_hnew;
 }
 
+// ------------------------------------------------------------------------------------------------
 // set, phase B: can the batch's evictions reach a key of this batch, or run out of victims?
-__global__ void __launch_bounds__(WIN_THREADS)
-kv_set_window_kernel(KvView kv, unsigned long long t, const uint32_t* __restrict__ n_active_dev, int deferred) {
-    KvState* st = kv.st;
-    __shared__ unsigned long long s_first;
-    if (deferred == 2) {  // set(..., batch=True) on its own: entries stay outside the LRU order
-        if (threadIdx.x == 0) st->conflict = 1;
-        return;
+// The LRU log is read from `head` in tiles of WIN_TILE positions by independent CTAs (B1: current records per
+// tile); one CTA then scans the tile counts, finds the tile that holds the e_ub-th current record and walks only
+// that tile (B2).  The evictions after the claims reuse the same tiles and prefixes (phase D).  A window of
+// WIN_FACTOR positions per op that turns out too short (sparse log) falls back to the one-CTA walk, exactly.
+// ------------------------------------------------------------------------------------------------
+constexpr unsigned long long WIN_TILE = (unsigned long long)WIN_THREADS * WIN_ITEMS;
+constexpr int WIN_FACTOR = 8;
+
+__device__ __forceinline__ unsigned win_tile_flags(const KvView& kv, unsigned long long pos, unsigned long long limit,
+                                                   bool (&valid)[WIN_ITEMS], uint32_t (&slot)[WIN_ITEMS]) {
+    unsigned cnt = 0;
+#pragma unroll
+    for (int k = 0; k < WIN_ITEMS; ++k) {
+        const unsigned long long p = pos + (unsigned long long)threadIdx.x * WIN_ITEMS + k;
+        valid[k] = p < limit && record_current(kv, p, slot[k]);
+        cnt += valid[k];
     }
+    return cnt;
+}
+
+__device__ __forceinline__ unsigned long long set_e_ub(const KvView& kv, const uint32_t* n_active_dev) {
+    const KvState* st = kv.st;
     const unsigned long long size = st->size;
     const unsigned long long n_absent = n_active_dev ? (unsigned long long)*n_active_dev : st->n_absent;
+    return size + n_absent > kv.max_size ? size + n_absent - kv.max_size : 0ull;
+}
+
+// B1: tile_cnt[tile] = current records among the tile's positions (before `t`, the batch's first stamp)
+__global__ void __launch_bounds__(WIN_THREADS)
+kv_set_window_count_kernel(KvView kv, unsigned long long t, const uint32_t* __restrict__ n_active_dev, int deferred,
+                           unsigned int* __restrict__ tile_cnt) {
+    __shared__ unsigned int s_sum;
+    if (deferred == 2 || set_e_ub(kv, n_active_dev) == 0) return;  // uniform for the whole grid
+    if (threadIdx.x == 0) s_sum = 0u;
+    __syncthreads();
+    bool valid[WIN_ITEMS];
+    uint32_t slot[WIN_ITEMS];
+    unsigned w = win_tile_flags(kv, kv.st->head + blockIdx.x * WIN_TILE, t, valid, slot);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
+    if ((threadIdx.x & 31) == 0 && w) atomicAdd(&s_sum, w);
+    __syncthreads();
+    if (threadIdx.x == 0) tile_cnt[blockIdx.x] = s_sum;
+}
+
+// Position of the record with rank k (0-based) among the current records of one tile; ~0 if there is none.
+__device__ unsigned long long win_tile_select(const KvView& kv, unsigned long long pos, unsigned long long limit,
+                                              unsigned k, unsigned int* s_warp, unsigned long long* s_res) {
+    if (threadIdx.x == 0) *s_res = ~0ull;
+    __syncthreads();
+    bool valid[WIN_ITEMS];
+    uint32_t slot[WIN_ITEMS];
+    const unsigned cnt = win_tile_flags(kv, pos, limit, valid, slot);
+    unsigned excl;
+    block_scan_1024(cnt, excl, s_warp);
+    unsigned rank = excl;
+#pragma unroll
+    for (int j = 0; j < WIN_ITEMS; ++j) {
+        if (!valid[j]) continue;
+        if (rank == k) *s_res = pos + (unsigned long long)threadIdx.x * WIN_ITEMS + j;
+        ++rank;
+    }
+    __syncthreads();
+    return *s_res;
+}
+
+// B2: one CTA.  tile_cnt becomes its exclusive prefix.
+__global__ void __launch_bounds__(WIN_THREADS)
+kv_set_window_decide_kernel(KvView kv, unsigned long long t, const uint32_t* __restrict__ n_active_dev, int deferred,
+                            int n_tiles, unsigned int* __restrict__ tile_cnt) {
+    KvState* st = kv.st;
+    __shared__ unsigned int s_warp[32];
+    __shared__ unsigned long long s_res, s_first;
+    __shared__ int s_tile_e, s_tile_f;
+    __shared__ unsigned s_rank_e;
+    const int tid = threadIdx.x;
+    if (deferred == 2) {  // set(..., batch=True) on its own: entries stay outside the LRU order
+        if (tid == 0) {
+            st->conflict = 1;
+            st->win_mode = 0;
+        }
+        return;
+    }
+    const unsigned long long e_ub = set_e_ub(kv, n_active_dev);
     const unsigned long long n_pre = n_active_dev ? 0ull : st->n_pre;
     const unsigned long long min_prev = st->min_prev;
     const unsigned long long head = st->head;
-    const unsigned long long e_ub = size + n_absent > kv.max_size ? size + n_absent - kv.max_size : 0ull;
-    if (e_ub == 0) return;  // conflict stays 0
-    const unsigned long long h_ub = lru_window_select(kv, head, t, e_ub, false, nullptr, &s_first);
-    if (threadIdx.x == 0) {
+    if (e_ub == 0) {  // conflict stays 0, nothing to evict
+        if (tid == 0) st->win_mode = 0;
+        return;
+    }
+    if (tid == 0) {
+        s_tile_e = -1;
+        s_tile_f = 0x7fffffff;
+        s_first = ~0ull;
+    }
+    __syncthreads();
+    unsigned long long base = 0;
+    for (int t0 = 0; t0 < n_tiles; t0 += WIN_THREADS) {
+        const int tile = t0 + tid;
+        const unsigned cnt = tile < n_tiles ? tile_cnt[tile] : 0u;
+        unsigned excl;
+        const unsigned total = block_scan_1024(cnt, excl, s_warp);
+        const unsigned long long pre = base + excl;
+        if (tile < n_tiles) {
+            tile_cnt[tile] = (unsigned)pre;  // live entries < 2^32
+            if (cnt) atomicMin(&s_tile_f, tile);
+            if (pre < e_ub && e_ub <= pre + cnt) {
+                s_tile_e = tile;
+                s_rank_e = (unsigned)(e_ub - 1 - pre);
+            }
+        }
+        base += total;
+        __syncthreads();
+    }
+    const bool covered_all = head + (unsigned long long)n_tiles * WIN_TILE >= t;
+    unsigned long long h_ub = ~0ull;
+    unsigned long long mode = 1;
+    if (base >= e_ub) {
+        h_ub = win_tile_select(kv, head + (unsigned long long)s_tile_e * WIN_TILE, t, s_rank_e, s_warp, &s_res) + 1ull;
+        __syncthreads();
+        if (s_tile_f != 0x7fffffff) {
+            const unsigned long long f = win_tile_select(kv, head + (unsigned long long)s_tile_f * WIN_TILE, t, 0u, s_warp, &s_res);
+            if (tid == 0) s_first = f;
+        }
+    } else if (covered_all) {
+        mode = 0;  // fewer stamped pre-batch entries than evictions that may be needed: h_ub stays ~0
+        if (s_tile_f != 0x7fffffff) {
+            const unsigned long long f = win_tile_select(kv, head + (unsigned long long)s_tile_f * WIN_TILE, t, 0u, s_warp, &s_res);
+            if (tid == 0) s_first = f;
+        }
+    } else {
+        mode = 2;  // the window was too short for this log: exact one-CTA walk, now and in phase D
+        h_ub = lru_window_select(kv, head, t, e_ub, false, nullptr, &s_first);
+    }
+    __syncthreads();
+    if (tid == 0) {
         if (h_ub == ~0ull)
             st->conflict = 1;  // fewer stamped pre-batch entries than evictions that may be needed
         else if (n_pre > 0 && min_prev < h_ub)
             st->conflict = 1;  // an entry this batch re-sets is within reach of its evictions
+        st->win_mode = mode;
+        st->win_origin = head;
+        st->win_hnew = ~0ull;
         if (s_first != ~0ull && s_first > head) st->head = s_first;  // drop leading stale records
     }
 }
@@ -372,14 +496,44 @@ __device__ void kv_set_sequential(const KvView& kv, const uint4* digests, const 
     st->slow_batches += 1;
 }
 
-// set, phase D: evict the E least-recently-used entries, or run the sequential replay.
+// set, phase D1: evict the E least-recently-used entries, tile by tile (tiles and prefixes of phase B; the claims
+// only touched records beyond the window's reach, or the batch went to the sequential path).
+__global__ void __launch_bounds__(WIN_THREADS)
+kv_set_evict_tiles_kernel(KvView kv, unsigned long long t, const unsigned int* __restrict__ tile_pre,
+                          unsigned long long* __restrict__ dropped_out) {
+    __shared__ unsigned int s_warp[32];
+    KvState* st = kv.st;
+    if (st->conflict || st->win_mode != 1ull) return;
+    const unsigned long long size = st->size;  // not modified by this kernel (phase D2 applies the counters)
+    const unsigned long long E = size > kv.max_size ? size - kv.max_size : 0ull;
+    const unsigned long long base = tile_pre[blockIdx.x];
+    if (E == 0 || base >= E) return;
+    const unsigned long long pos = st->win_origin + blockIdx.x * WIN_TILE;
+    bool valid[WIN_ITEMS];
+    uint32_t slot[WIN_ITEMS];
+    const unsigned cnt = win_tile_flags(kv, pos, t, valid, slot);
+    unsigned excl;
+    block_scan_1024(cnt, excl, s_warp);
+    unsigned long long rank = base + excl;
+#pragma unroll
+    for (int k = 0; k < WIN_ITEMS; ++k) {
+        if (!valid[k]) continue;
+        if (rank < E) {
+            evict_slot(kv, slot[k], dropped_out);
+            if (rank == E - 1) st->win_hnew = pos + (unsigned long long)threadIdx.x * WIN_ITEMS + k + 1ull;
+        }
+        ++rank;
+    }
+}
+
+// set, phase D2 (one CTA): counters of the evictions, or the one-CTA walk, or the sequential replay.
 __global__ void __launch_bounds__(WIN_THREADS)
 kv_set_evict_kernel(KvView kv, const uint4* __restrict__ digests, const unsigned long long* __restrict__ values,
                     const double* __restrict__ ttl, int M, double now, unsigned long long t, int deferred,
                     const uint8_t* __restrict__ skip, int32_t* __restrict__ slot_out,
                     unsigned long long* __restrict__ dropped_out) {
     KvState* st = kv.st;
-    const unsigned long long conflict = st->conflict, size = st->size, head = st->head;
+    const unsigned long long conflict = st->conflict, size = st->size, head = st->head, mode = st->win_mode;
     __syncthreads();
     if (conflict) {
         if (threadIdx.x == 0)
@@ -387,7 +541,11 @@ kv_set_evict_kernel(KvView kv, const uint4* __restrict__ digests, const unsigned
     } else {
         const unsigned long long E = size > kv.max_size ? size - kv.max_size : 0ull;
         if (E > 0) {
-            const unsigned long long hnew = lru_window_select(kv, head, t, E, true, dropped_out, nullptr);
+            unsigned long long hnew;
+            if (mode == 1ull)
+                hnew = st->win_hnew;  // the tiles of phase D1 did the evictions
+            else
+                hnew = lru_window_select(kv, head, t, E, true, dropped_out, nullptr);
             if (threadIdx.x == 0) {
                 st->size = size - E;
                 st->evictions += E;
@@ -401,6 +559,8 @@ kv_set_evict_kernel(KvView kv, const uint4* __restrict__ digests, const unsigned
         st->n_dropped_last = st->n_dropped;
         st->n_pre = st->n_absent = st->n_new = st->conflict = st->n_dropped = 0ull;
         st->min_prev = ~0ull;
+        st->win_mode = 0ull;
+        st->win_hnew = ~0ull;
     }
 }
 
@@ -529,6 +689,8 @@ __global__ void kv_state_init_kernel(KvView kv, unsigned long long head, unsigne
         st->free_top = n_rows;
         st->n_pre = st->n_absent = st->n_new = st->conflict = st->n_dropped = 0ull;
         st->min_prev = ~0ull;
+        st->win_mode = st->win_origin = 0ull;
+        st->win_hnew = ~0ull;
     }
     for (unsigned long long r = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; r < n_rows;
          r += (unsigned long long)gridDim.x * blockDim.x)
@@ -566,6 +728,7 @@ die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_ro
     DIE_CUDA(cudaMemset(kv->log, 0xff, kv->ring_cap * sizeof(uint32_t)));
     DIE_CUDA(cudaMemset(kv->st, 0, sizeof(KvState)));
     DIE_CUDA(cudaMalloc(&kv->n_kept_dev, sizeof(unsigned long long)));
+    DIE_CUDA(cudaMalloc(&kv->tile_cnt, (kv->ring_cap / ((uint64_t)WIN_THREADS * WIN_ITEMS) + 2) * sizeof(unsigned int)));
     DIE_CUDA(cudaHostAlloc(&kv->mirror, sizeof(KvMirror), cudaHostAllocMapped | cudaHostAllocPortable));
     memset(kv->mirror, 0, sizeof(KvMirror));
     kv->mirror_gen = 1;
@@ -573,6 +736,13 @@ die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_ro
     DIE_CUDA(cudaDeviceSynchronize());
     *out = kv;
     return DIE_OK;
+}
+
+// Tiles of the victim window of a set batch of n ops (WIN_FACTOR log positions per op, at least one tile).
+static int set_window_tiles(const die_kv* kv, int64_t n) {
+    const uint64_t cap = kv->ring_cap / WIN_TILE + 1;
+    uint64_t tiles = ((uint64_t)WIN_FACTOR * (uint64_t)std::max<int64_t>(n, 1) + WIN_TILE - 1) / WIN_TILE;
+    return (int)std::max<uint64_t>(1, std::min<uint64_t>(tiles, cap));
 }
 
 static die_status_t ensure_scratch(die_kv* kv, uint64_t n) {
@@ -600,8 +770,6 @@ static die_status_t kv_maintain(die_kv* kv, int force, cudaStream_t s) {
         if (!new_log) DIE_CUDA(cudaMalloc(&new_log, kv->ring_cap * sizeof(uint32_t)));
         DIE_CUDA(cudaMemsetAsync(new_log, 0xff, kv->ring_cap * sizeof(uint32_t), s));
         const unsigned long long n_tiles = (span + (unsigned long long)WIN_THREADS * WIN_ITEMS - 1) / ((unsigned long long)WIN_THREADS * WIN_ITEMS);
-        if (!kv->tile_cnt)
-            DIE_CUDA(cudaMalloc(&kv->tile_cnt, (kv->ring_cap / ((uint64_t)WIN_THREADS * WIN_ITEMS) + 2) * sizeof(unsigned int)));
         if (n_tiles) {
             const int grid = (int)std::min<unsigned long long>(n_tiles, (unsigned long long)num_sms() * 2);
             DIE_LAUNCH(ST_KV_MAINT, s, kv_compact_count_kernel<<<grid, WIN_THREADS, 0, s>>>(view_of(kv), h.head, kv->tail, n_tiles, kv->tile_cnt));
@@ -732,12 +900,16 @@ die_status_t kv_set_batch_impl(die_kv* kv, const uint32_t* digests, const uint64
         if (!known_absent) {
             DIE_LAUNCH(ST_KV_PRECHECK, s, kv_set_precheck_kernel<<<grid, KV_THREADS, 0, s>>>(v, dg, n, sk, kv->op_slot));
         }
-        DIE_LAUNCH(ST_KV_WINDOW, s, kv_set_window_kernel<<<1, WIN_THREADS, 0, s>>>(v, kv->tail, known_absent ? n_active_dev : nullptr, deferred));
+        const int n_tiles = set_window_tiles(kv, n);
+        const uint32_t* n_act = known_absent ? n_active_dev : nullptr;
+        DIE_LAUNCH(ST_KV_WINDOW, s, kv_set_window_count_kernel<<<n_tiles, WIN_THREADS, 0, s>>>(v, kv->tail, n_act, deferred, kv->tile_cnt));
+        DIE_LAUNCH(ST_KV_WINDOW, s, kv_set_window_decide_kernel<<<1, WIN_THREADS, 0, s>>>(v, kv->tail, n_act, deferred, n_tiles, kv->tile_cnt));
         DIE_LAUNCH(ST_KV_CLAIM, s, kv_set_claim_kernel<<<grid, KV_THREADS, 0, s>>>(v, dg, n, now, kv->tail, own_values, sk,
                                                         known_absent ? 0 : 1, kv->op_slot, so, dr));
         if (values || ttl) {
             DIE_LAUNCH(ST_KV_FINALIZE, s, kv_set_finalize_kernel<<<grid, KV_THREADS, 0, s>>>(v, n, kv->tail, vals, tt, sk, kv->op_slot));
         }
+        DIE_LAUNCH(ST_KV_EVICT, s, kv_set_evict_tiles_kernel<<<n_tiles, WIN_THREADS, 0, s>>>(v, kv->tail, kv->tile_cnt, dr));
         DIE_LAUNCH(ST_KV_EVICT, s, kv_set_evict_kernel<<<1, WIN_THREADS, 0, s>>>(v, dg, vals, tt, n, now, kv->tail, deferred, sk, so, dr));
         kv->tail += n;
         done += n;
@@ -1006,12 +1178,15 @@ extern "C" die_status_t die_kv_set_batch_noalloc(die_kv_t* kv, const uint32_t* d
     // Nothing in the scratch has to start at zero: the precheck writes op_slot[i] for every op before any
     // later kernel of this call reads it.  What the previous call left there is simply overwritten.
     DIE_LAUNCH(ST_KV_PRECHECK, s, kv_set_precheck_kernel<<<grid, KV_THREADS, 0, s>>>(v, dg, M, nullptr, scratch));
-    DIE_LAUNCH(ST_KV_WINDOW, s, kv_set_window_kernel<<<1, WIN_THREADS, 0, s>>>(v, kv->tail, nullptr, deferred_stamp));
+    const int n_tiles = set_window_tiles(kv, M);
+    DIE_LAUNCH(ST_KV_WINDOW, s, kv_set_window_count_kernel<<<n_tiles, WIN_THREADS, 0, s>>>(v, kv->tail, nullptr, deferred_stamp, kv->tile_cnt));
+    DIE_LAUNCH(ST_KV_WINDOW, s, kv_set_window_decide_kernel<<<1, WIN_THREADS, 0, s>>>(v, kv->tail, nullptr, deferred_stamp, n_tiles, kv->tile_cnt));
     DIE_LAUNCH(ST_KV_CLAIM, s, kv_set_claim_kernel<<<grid, KV_THREADS, 0, s>>>(v, dg, M, now, kv->tail, values ? 0 : 1,
                                                                               nullptr, 1, scratch, slot_out, dr));
     if (values || ttl)
         DIE_LAUNCH(ST_KV_FINALIZE, s, kv_set_finalize_kernel<<<grid, KV_THREADS, 0, s>>>(v, M, kv->tail, vals, ttl,
                                                                                          nullptr, scratch));
+    DIE_LAUNCH(ST_KV_EVICT, s, kv_set_evict_tiles_kernel<<<n_tiles, WIN_THREADS, 0, s>>>(v, kv->tail, kv->tile_cnt, dr));
     DIE_LAUNCH(ST_KV_EVICT, s, kv_set_evict_kernel<<<1, WIN_THREADS, 0, s>>>(v, dg, vals, ttl, M, now, kv->tail,
                                                                              deferred_stamp, nullptr, slot_out, dr));
     kv->tail += n;
