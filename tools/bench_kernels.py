@@ -208,7 +208,7 @@ def run(kv_entries=10_000_000, quick=False):
         s = timed(do_set, 6, warm=2)
         now = tick[0]
         K.append(entry("kv_set (precheck+window+claim+finalize+evict)", s, M * 288, M, "inserts", peak,
-                       f"{M} new keys into the full table: {M} evictions; 5 launches"))
+                       f"{M} new keys into the full table: {M} evictions; 7 launches (window and evictions over parallel tiles)"))
     assert kv.sync_status()[0] == 0
     st = kv.stats()
     out["kv_table"] = {"entries": st["size"], "capacity": st["capacity"], "evictions": st["evictions"]}
