@@ -135,8 +135,10 @@ class PeerDispatcher:
     its owner's window, a flag barrier inside the window separates the phases, the owner runs the fused
     pipeline on a batch whose size it only knows on the device, and the return / scatter kernels bring the
     results back to request order.  Owners see the sources in rank order (same contract as ShardedDispatcher).
-    One `die_xchg_step` call enqueues the whole step; `single_call=False` drives the same kernels phase by
-    phase from Python with torch's symmetric-memory barrier instead (used by the tests as a cross-check)."""
+    One `die_xchg_step` call enqueues the whole step (three in-order stage streams over four buffer sets inside
+    the library, so consecutive steps overlap); `step_many` hands over a queue of batches, replayed in groups of
+    16 steps from one CUDA graph.  `single_call=False` drives the stand-alone phase kernels from Python with
+    torch's symmetric-memory barrier instead (used by the tests as a cross-check)."""
 
     def __init__(self, world: int, rank: int, kv_max_size: int, max_batch: int, dim: int, weight, bias, default_ttl,
                  model: str = "linear_tf32", group=None, single_call: bool = True):
