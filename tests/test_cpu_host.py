@@ -331,3 +331,16 @@ def test_bench_reference_arm_prints_the_contract_line():
     r1 = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2"],
                         capture_output=True, text=True, timeout=120, env=env)
     assert r1.returncode == 0 and r1.stdout.strip() == ""
+
+
+def test_bench_gpu_arm_has_no_cpu_fallback():
+    """Without a GPU the product arm of bench.py must stop with an error, not produce a number some other way."""
+    import subprocess
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--steps", "1", "--warmup", "1"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode != 0
+    assert not any(line.startswith("{") for line in r.stdout.splitlines())
