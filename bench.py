@@ -6,12 +6,14 @@
 Workload (BASELINE.json configs[1], "C2"): flushed batches of 4096 requests, key "user-%010d" with ids
 uniform in [0, 1e7), payload 128 fp32, mock linear model 128->128, one owner KV cache of 2^20 entries
 per GPU (LRU, default_ttl 300 s), so about 10 % of the requests hit the cache and every batch evicts.
-One step = one flushed batch through the whole path.  Every step has its own freshly drawn inputs
-(resident in HBM before the timed region; K steps x 2.2 MB, larger than L2 for K >= 60).
+One STEP = a queue of G = 128 flushed batches (524 288 requests) handed to the path in one call; every batch
+is still its own pass of the path, applied strictly in order (">= 200 back-to-back
+batches").  Keys are freshly drawn for every batch; payload rows come from a pool of two steps' worth of
+batches (537 MB, larger than L2) used alternately.  All inputs are resident in HBM before the timed region.
 
 Prints ONE JSON line (see the contract in the task description): `value` is device-resident
 throughput, `e2e` goes through the C-ABI with host buffers, `roofline` describes the dominant kernel
-timed with CUDA events on its own stream, `cpu_baseline` is the CPU oracle port timed on this host.
+timed with CUDA events on its own stream, `cpu_baseline` is the reference's CPU path timed on this host.
 """
 import argparse
 import json
@@ -19,6 +21,12 @@ import os
 import sys
 import threading
 import time
+
+# The CPU arms are one Python process per core: a BLAS thread pool inside each of them oversubscribes the host
+# (round 1: 8-12x slower reference numbers).  Must be set before numpy is imported.
+if "--impl" in sys.argv and "reference" in sys.argv:
+    for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS", "NUMEXPR_NUM_THREADS"):
+        os.environ[_v] = "1"
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 for _p in (ROOT, os.path.join(ROOT, "distributed-inference-engine_b200")):
@@ -28,11 +36,13 @@ for _p in (ROOT, os.path.join(ROOT, "distributed-inference-engine_b200")):
 import numpy as np  # noqa: E402
 
 B, D = 4096, 128
+G = int(os.environ.get("DIE_BENCH_BATCHES_PER_STEP", "128"))  # flushed batches per step (one queue call)
 KV_MAX, ID_SPACE, TTL = 1 << 20, 10 ** 7, 300.0
 KEY_LEN = 15
 WORLD = int(os.environ.get("WORLD_SIZE", "1"))
 METRIC = "requests/sec, batched route->probe->pack->infer->unpack"
 MODEL = os.environ.get("DIE_BENCH_MODEL", "linear_tf32")  # tcgen05 kind::tf32 GEMM, fp32 accumulate
+DT = 0.01  # seconds of injected clock per flushed batch
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -64,14 +74,26 @@ def model_weights():
 
 
 # ----------------------------------------------------------------------------------------------------------------
-# CPU baseline (oracle port of the reference's pure-Python path) -- the one place bench.py may run oracle/
+# CPU arms: the reference's pure-Python path on the host cores -- the one place bench.py may run oracle/
 # ----------------------------------------------------------------------------------------------------------------
-def cpu_worker(seed, n_timed, scale=8):
-    """Prefill a scaled-down cache (1/scale of the entries and of the id space: same ~10 % hit rate),
-    then time n_timed flushed batches through the composed reference port.  Returns (requests, seconds)."""
-    from oracle.pipeline import BaselinePipeline
+def cpu_kind():
+    """"reference": the reference's own classes (verbatim copy under oracle/_ref, see oracle/fetch_ref.py);
+    "port": the restatement in oracle/ref_port.py when that copy is absent."""
+    from oracle import refrun
+    return "reference" if refrun.available() else "port"
+
+
+def cpu_worker(seed, n_timed):
+    """One single-threaded replica of the path at the GPU arm's configuration: a 2^20-entry cache prefilled to
+    capacity from ids in [0, 1e7) (same ~10 % hit rate, every batch evicts), then n_timed flushed batches of
+    4096 requests timed.  Returns (requests, seconds, kind)."""
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=1)   # numpy's BLAS stays on this process's one core
+    except Exception:  # noqa: BLE001
+        pass
+    from oracle import refrun
     w, b = model_weights()
-    w64 = w.astype(np.float64)
 
     def model(rows):
         if not rows:
@@ -79,34 +101,38 @@ def cpu_worker(seed, n_timed, scale=8):
         y = (np.stack(rows) @ w.T + b).astype(np.float32)
         return [y[i] for i in range(len(rows))]
 
-    kv_max, space = KV_MAX // scale, ID_SPACE // scale
-    pipe = BaselinePipeline(1, kv_max, TTL, model, max_batch_size=B)
+    kind = cpu_kind()
+    if kind == "reference":
+        pipe = refrun.ReferencePipeline(1, KV_MAX, TTL, model, max_batch_size=B)
+    else:
+        from oracle.pipeline import BaselinePipeline
+        pipe = BaselinePipeline(1, KV_MAX, TTL, model, max_batch_size=B)
     rng = np.random.default_rng(1000 + seed)
-    n_fill = int(kv_max * 1.15 / B) + 1
+    n_fill = int(KV_MAX * 1.15 / B) + 1
     now = 1000.0
+    # prefill without the model (untimed): the cached value's content does not matter to the timed region
+    fill_row = np.zeros(D, dtype=np.float32)
+    pipe_model, pipe.model = pipe.model, (lambda rows: [fill_row] * len(rows))
     for _ in range(n_fill):
-        ids = rng.integers(0, space, B)
-        keys = ["user-%010d" % i for i in ids]
-        x = rng.standard_normal((B, D), dtype=np.float32)
-        now += 0.01
-        pipe.process(keys, list(x), now)
+        keys = ["user-%010d" % i for i in rng.integers(0, ID_SPACE, B)]
+        now += DT
+        pipe.process(keys, [fill_row] * B, now)
+    pipe.model = pipe_model
     batches = []
     for _ in range(n_timed):
-        ids = rng.integers(0, space, B)
+        ids = rng.integers(0, ID_SPACE, B)
         batches.append((["user-%010d" % i for i in ids], list(rng.standard_normal((B, D), dtype=np.float32))))
     t0 = time.perf_counter()
     for keys, rows in batches:
-        now += 0.01
+        now += DT
         pipe.process(keys, rows, now)
     dt = time.perf_counter() - t0
-    del w64
-    return n_timed * B, dt
+    return n_timed * B, dt, kind
 
 
 def cpu_stage_times(n_rep=3):
     """Per-stage time of the reference's path on one host core (oracle port), one 4096-request batch each:
     the CPU column beside the per-kernel GPU numbers."""
-    import hashlib
     from oracle.ref_port import PortKVCache, PortRegistry
     rng = np.random.default_rng(4242)
     w, b = model_weights()
@@ -131,7 +157,6 @@ def cpu_stage_times(n_rep=3):
     timed("fill (KVCache.set + LRU eviction, kvstore.py:104)", lambda: [cache.set(k + "x", 1) for k in keys])
     timed("pack + unpack (list gather / zip, batcher.py:211,225)", lambda: [r for r, _ in zip([q for q in rows], rows)])
     timed("infer (numpy fp32 linear on the packed batch)", lambda: (np.stack(rows) @ w.T + b))
-    del hashlib
     return best
 
 
@@ -142,44 +167,61 @@ def _time_once(fn):
 
 
 def cpu_baseline_single(n_timed=24):
-    n, dt = cpu_worker(0, n_timed)
+    n, dt, kind = cpu_worker(0, n_timed)
     per_batch = dt / n_timed
     try:
         stages = cpu_stage_times()
     except Exception as exc:  # noqa: BLE001
         stages = {"error": repr(exc)[:200]}
-    return {"value": n / dt, "unit": "requests/s", "cores": 1, "kind": "port",
+    return {"value": n / dt, "unit": "requests/s", "cores": 1, "kind": kind,
             "as_shipped": {"value": B / (per_batch + 0.1), "unit": "requests/s",
                            "note": "the same path with the reference's own sleep left in: mock_batch_inference waits "
                                    "100 ms per batch (mock_inference.py:12-73), added analytically to the measured batch time"},
             "stages": stages,
-            "sample": f"{n_timed} batches x {B} requests after prefill; cache 2^17 entries and id space 1.25e6 "
-                      f"(both 1/8 of the GPU run, same ~10% hit rate); oracle/pipeline.py BaselinePipeline "
-                      f"(hashlib.md5 + dict/OrderedDict + asyncio batcher + numpy fp32 linear), sleeps removed"}
+            "sample": f"{n_timed} batches x {B} requests after prefilling the 2^20-entry cache (ids in [0,1e7), the GPU "
+                      f"arm's configuration); {_cpu_path_text(kind)}, sleeps removed, one thread"}
+
+
+def _cpu_path_text(kind):
+    if kind == "reference":
+        return ("the reference's own Router + KVCache + Batcher classes (oracle/_ref, verbatim copy) composed by "
+                "oracle/refrun.py, numpy fp32 linear as the batch callback")
+    return ("oracle/pipeline.py BaselinePipeline (restatement: hashlib.md5 + dict/OrderedDict + asyncio batcher + numpy "
+            "fp32 linear)")
+
+
+def usable_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:  # noqa: BLE001
+        return os.cpu_count() or 1
 
 
 def run_reference(args):
-    """`--impl reference`: the reference's pure-Python path (oracle port; the Python reference itself cannot
-    travel to the GPU box) on all usable host cores, as independent one-shard replicas."""
+    """`--impl reference`: the reference's pure-Python path on all usable host cores (at most 32), one
+    single-threaded one-shard replica process per core, each at the GPU arm's per-shard configuration."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import multiprocessing as mp
-    cores = max(1, min(os.cpu_count() or 1, 32))
-    n_timed = max(4, min(args.steps, 24))
+    cores = max(1, min(usable_cores(), 32))
+    n_timed = 24          # a bounded sample: 24 batches x 4096 requests per replica, whatever --steps says
     t0 = time.perf_counter()
     with mp.get_context("fork").Pool(cores) as pool:
         res = pool.starmap(cpu_worker, [(s, n_timed) for s in range(cores)])
     total = sum(r[0] for r in res)
     slowest = max(r[1] for r in res)
+    kind = res[0][2]
     value = total / slowest
     line = {"metric": METRIC, "value": value, "unit": "requests/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * slowest / n_timed, "higher_is_better": True,
+            "warmup": args.warmup, "ms_per_step": 1e3 * G * B / value, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
             "config": workload_config(args.gpus),
-            "cpu_baseline": {"value": value, "unit": "requests/s", "cores": cores, "kind": "port",
-                             "sample": f"{cores} replica processes x {n_timed} batches x {B} requests after prefill, "
-                                       f"cache and id space scaled 1/8; wall {time.perf_counter() - t0:.1f}s"},
+            "cpu_baseline": {"value": value, "unit": "requests/s", "cores": cores, "kind": kind,
+                             "sample": f"{cores} single-threaded replica processes x {n_timed} batches x {B} requests, each "
+                                       f"after prefilling its own 2^20-entry cache; {_cpu_path_text(kind)}; ms_per_step = "
+                                       f"time for one step's {G * B} requests at the aggregate rate; "
+                                       f"wall {time.perf_counter() - t0:.1f}s"},
             "e2e": {"value": value, "unit": "requests/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -189,7 +231,10 @@ def workload_config(n_gpus):
                         "128-dim fp32 payload, mock linear 128->128, LRU+TTL cache of 2^20 entries per GPU "
                         "(~10% hits, evicting)",
             "batch": B, "dim": D, "kv_max_size": KV_MAX, "id_space": ID_SPACE * n_gpus, "default_ttl": TTL,
-            "parallelism": f"hash-shard x{n_gpus}", "l2_policy": "every step reads fresh inputs; K steps x 2.2 MB"}
+            "model": "linear 128->128 (GPU arm: tf32 tensor-core inputs, fp32 accumulate; CPU arm: numpy fp32)",
+            "batches_per_step": G, "requests_per_step": G * B,
+            "parallelism": f"hash-shard x{n_gpus}",
+            "l2_policy": "inputs larger than L2: fresh keys every batch, payload pool of 2 steps (537 MB) alternated"}
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -252,8 +297,11 @@ class ClockSampler(threading.Thread):
             self._query()           # periodic (timeout) or on demand (sample_now)
             self.served = max(self.served, want)
 
-    def sample_now(self):
+    def sample_now(self, burst_period=0.015):
+        """Everything of the timed region is enqueued: from here on a query cannot hold up a launch, so sample
+        now and then every `burst_period` seconds until result() is called (>= 3 samples for a region >= 50 ms)."""
         self.requested += 1
+        self.period = burst_period
         self.wake.set()
 
     def result(self):
@@ -267,7 +315,8 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
                 "samples": len(s), "period_ms": 1e3 * self.period,
                 "nvml_ms_per_sample": round(1e3 * self.query_s / len(s), 3) if s else None,
-                "when": "after the last step of the timed region was enqueued, while the GPU was still executing it"}
+                "when": "from the moment the last step of the timed region was enqueued, every 15 ms while the GPU was "
+                        "still executing it (an NVML query stalls CUDA-graph launches issued meanwhile)"}
 
 
 def ncu_traffic(kernel_name):
@@ -289,6 +338,64 @@ def ncu_traffic(kernel_name):
     return None, None
 
 
+def stage_rooflines(lib, ms_arr, cnt_arr, n_stages, n_prof, s0, s1, step_ms_per_batch):
+    """Per-stage device time of n_prof stream-launched batches (CUDA events on the launching stream, see
+    die_profile_begin) -> (stages, roofline of the dominant kernel).  Algorithmic bytes per launch = SURVEY.md
+    section 8(d)'s per-request figures x the requests one launch processes."""
+    hits = (s1["hits"] - s0["hits"]) / n_prof
+    miss = (s1["misses"] - s0["misses"]) / n_prof
+    evic = (s1["evictions"] - s0["evictions"]) / n_prof
+    row = D * 4
+    route_b = B * (KEY_LEN + 8 + 16)
+    probe_b = hits * 121 + miss * 89
+    alg = {
+        "kv_get": route_b + probe_b + B * 5 + evic * 12,                                  # route + probe + rank + window
+        "kv_set_claim": miss * 160 + B * 2 * row + B * 13,                                # insert + pack / hit copy
+        "model": miss * (2 * row + 16),
+        "unpack_store": miss * 3 * row + B * 9 + evic * 128,                              # unpack + cached row + evict
+        # the fused step kernel: everything above once -- keys in, probe, insert (+ eviction), payload row in,
+        # result row out, cached row out (misses) / cached row in (hits), weights amortised over the batch
+        "fused_step": route_b + probe_b + miss * 160 + evic * 128 + miss * (3 * row) + hits * (2 * row) + 64 * 1024 / 16,
+    }
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:  # noqa: BLE001
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    total_ms = sum(ms_arr[i] for i in range(n_stages))
+    kernel_of = {"kv_get": "pipe_get_kernel", "kv_set_claim": "pipe_claim_pack_kernel", "model": "linear_tf32_kernel",
+                 "unpack_store": "pipe_unpack_evict_kernel", "fused_step": "pipe_step_kernel"}
+    stages = {}
+    for i in range(n_stages):
+        if cnt_arr[i] == 0:
+            continue
+        name = lib.die_profile_stage_name(i).decode()
+        per = ms_arr[i] / cnt_arr[i]
+        gbs = alg.get(name, 0) / (per * 1e-3) / 1e9 if per > 0 else 0.0
+        stages[name] = {"kernel": kernel_of.get(name, name), "us_per_launch": round(per * 1e3, 3),
+                        "launches_per_batch": cnt_arr[i] / n_prof, "share": round(ms_arr[i] / total_ms, 4),
+                        "alg_bytes_per_launch": round(alg.get(name, 0)), "gbs": round(gbs, 1),
+                        "frac_of_hbm_peak": round(gbs / peak, 4)}
+    dom = max(stages, key=lambda n: stages[n]["share"])
+    traffic, traffic_src = ncu_traffic(stages[dom]["kernel"])
+    fused_alg = B * (KEY_LEN + 8 + 4) + probe_b + 2 * B * row     # SURVEY 8(d) fused C2 lower bound: 1.17 KB / request
+    roofline = {"kernel": stages[dom]["kernel"], "bound": "hbm", "achieved": stages[dom]["gbs"], "peak": peak,
+                "unit": "GB/s", "frac": stages[dom]["frac_of_hbm_peak"], "traffic": traffic, "traffic_source": traffic_src,
+                "peak_source": peak_src,
+                "us_per_launch": stages[dom]["us_per_launch"], "alg_bytes_per_launch": stages[dom]["alg_bytes_per_launch"],
+                "whole_step_fused_accounting": {
+                    "alg_bytes_per_batch": round(fused_alg), "us_per_batch": round(step_ms_per_batch * 1e3, 3),
+                    "gbs": round(fused_alg / (step_ms_per_batch * 1e-3) / 1e9, 1),
+                    "frac": round(fused_alg / (step_ms_per_batch * 1e-3) / 1e9 / peak, 4),
+                    "note": "SURVEY 8(d) north-star denominator (payload read once, result written once, route + probe) "
+                            "over the device-timed batch of `value`"},
+                "note": "a 4096-request batch carries ~5 MB of algorithmic traffic (<1 us at peak): the step sits on its "
+                        "chain of dependent DRAM round trips and grid-wide barriers, see DESIGN.md section 5"}
+    return stages, roofline
+
+
 def e2e_sharded(runner, rng, K, now, off_d, world):
     """End to end at N > 1: every rank's batches start in pinned host memory and its results end there.  Groups of
     16 batches: one H2D copy per array, one die_xchg_step_many call (one graph replay), one D2H copy per array;
@@ -296,19 +403,20 @@ def e2e_sharded(runner, rng, K, now, off_d, world):
     between two barriers, max over ranks."""
     import torch
     import torch.distributed as dist
-    G = 16
-    n_groups = max(2, K // G)
-    n = n_groups * G
-    _, keys, _, x = make_batches(rng, n)
+    GS = 16
+    n_groups = max(2, K * G // GS)
+    n = n_groups * GS
+    n_pool = 2 * G                                    # payload pool (537 MB pinned per rank), keys fresh per batch
+    _, keys, _, _ = make_batches(rng, n, payload=False)
     hk = torch.from_numpy(keys).pin_memory()
-    hx = torch.from_numpy(x).pin_memory()
-    hout = torch.empty((n, B, D), dtype=torch.float32).pin_memory()
+    hx = torch.from_numpy(rng.standard_normal((n_pool, B, D), dtype=np.float32)).pin_memory()
+    hout = torch.empty((n_pool, B, D), dtype=torch.float32).pin_memory()
     hhit = torch.empty((n, B), dtype=torch.uint8).pin_memory()
     NS = 3
-    dk = [torch.zeros((G + 1, B * KEY_LEN), dtype=torch.uint8, device="cuda") for _ in range(NS)]  # +1 row of slack
-    dx = [torch.empty((G, B, D), dtype=torch.float32, device="cuda") for _ in range(NS)]
-    dout = [torch.empty((G, B, D), dtype=torch.float32, device="cuda") for _ in range(NS)]
-    dhit = [torch.empty((G, B), dtype=torch.uint8, device="cuda") for _ in range(NS)]
+    dk = [torch.zeros((GS + 1, B * KEY_LEN), dtype=torch.uint8, device="cuda") for _ in range(NS)]  # +1 row of slack
+    dx = [torch.empty((GS, B, D), dtype=torch.float32, device="cuda") for _ in range(NS)]
+    dout = [torch.empty((GS, B, D), dtype=torch.float32, device="cuda") for _ in range(NS)]
+    dhit = [torch.empty((GS, B), dtype=torch.uint8, device="cuda") for _ in range(NS)]
     s_in, s_out, cur = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.current_stream()
     ev_in = [torch.cuda.Event() for _ in range(NS)]
     ev_done = [torch.cuda.Event() for _ in range(NS)]
@@ -317,28 +425,29 @@ def e2e_sharded(runner, rng, K, now, off_d, world):
     def run(first_group, count, now0):
         for g in range(first_group, first_group + count):
             b = g % NS
-            lo, hi = (g % n_groups) * G, (g % n_groups) * G + G
+            lo, hi = (g % n_groups) * GS, (g % n_groups) * GS + GS
+            plo = (g * GS) % n_pool
             with torch.cuda.stream(s_in):
                 if g - first_group >= NS:
                     s_in.wait_event(ev_done[b])
-                dk[b][:G].copy_(hk[lo:hi], non_blocking=True)
-                dx[b].copy_(hx[lo:hi], non_blocking=True)
+                dk[b][:GS].copy_(hk[lo:hi], non_blocking=True)
+                dx[b].copy_(hx[plo:plo + GS], non_blocking=True)
                 ev_in[b].record(s_in)
             cur.wait_event(ev_in[b])
             if g - first_group >= NS:
                 cur.wait_event(ev_out[b])
-            runner.step_many(dk[b][:G], off_d, dx[b], now0 + (g - first_group) * G * DT_E2E, DT_E2E, dout[b], dhit[b])
+            runner.step_many(dk[b][:GS], off_d, dx[b], now0 + (g - first_group) * GS * DT, DT, dout[b], dhit[b])
             ev_done[b].record(cur)
             with torch.cuda.stream(s_out):
                 s_out.wait_event(ev_done[b])
-                hout[lo:hi].copy_(dout[b], non_blocking=True)
+                hout[plo:plo + GS].copy_(dout[b], non_blocking=True)
                 hhit[lo:hi].copy_(dhit[b], non_blocking=True)
                 ev_out[b].record(s_out)
         s_out.synchronize()
         cur.synchronize()
 
     run(0, 2, now)                         # warm the staging path and the graphs
-    now += 2 * G * DT_E2E
+    now += 2 * GS * DT
     torch.cuda.synchronize()
     dist.barrier()
     t0 = time.perf_counter()
@@ -349,13 +458,72 @@ def e2e_sharded(runner, rng, K, now, off_d, world):
     dt = float(t[0])
     runner.check()
     return {"value": world * n * B / dt, "unit": "requests/s",
-            "h2d_bytes_per_step": B * KEY_LEN + B * D * 4, "d2h_bytes_per_step": B * D * 4 + B,
-            "ms_per_step": 1e3 * dt / n, "steps": n,
+            "h2d_bytes_per_step": G * (B * KEY_LEN + B * D * 4), "d2h_bytes_per_step": G * (B * D * 4 + B),
+            "ms_per_step": 1e3 * dt / n * G, "steps": n / G,
             "api": "PeerDispatcher.step_many (die_xchg_step_many) on groups of 16 batches staged from / to pinned host "
-                   "buffers on every rank; copy-in, sharded steps and copy-out of consecutive groups overlap"}, now + n * DT_E2E
+                   "buffers on every rank; copy-in, sharded steps and copy-out of consecutive groups overlap"}, now + n * DT
 
 
-DT_E2E = 0.01
+def sharded_self_check(runner, rank, world, off_d):
+    """The N > 1 arm checks itself before anything is timed (there is no multi-GPU pytest on a one-GPU test box):
+    one stream-launched sharded step and one graph-replayed group of 16 on the empty owner tables, every rank's
+    out / hit / shard compared with oracle.pipeline.OraclePipeline.process_exchange -- hit flags and shard ids
+    bit-exact, outputs within 2**-10 * sum|x w| + 1e-6, owner counters equal.  A mismatch fails the run."""
+    import torch
+    from die import ops
+    from oracle import models
+    from oracle.pipeline import OraclePipeline
+    w, b = model_weights()
+    rel = 2.0 ** -10 if MODEL == "linear_tf32" else 1e-5
+
+    def fn(rows):
+        if not rows:
+            return []
+        xs = np.stack(rows)
+        y, bound = models.linear_f64(xs, w, b), models.linear_abs_bound(xs, w)
+        return [np.stack([y[i], bound[i]]) for i in range(len(rows))]
+
+    ref = OraclePipeline(world, KV_MAX, TTL, fn)
+    rng = np.random.default_rng(99)          # same stream on every rank: each rank knows all ranks' batches
+    n = 17
+    ids = rng.integers(0, 30000 * world, (n, world, B), dtype=np.int64)
+    x = rng.standard_normal((n, world, B, D), dtype=np.float32)
+    keys_of = lambda j, r: ["user-%010d" % i for i in ids[j, r]]  # noqa: E731
+    now = 500.0
+
+    def compare(j, out, hit, shard):
+        want = ref.process_exchange([(keys_of(j, r), [row for row in x[j, r]]) for r in range(world)], now + j * DT)[rank]
+        if shard is not None and shard.tolist() != want["shard"]:
+            raise AssertionError(f"self-check: shard ids differ from the oracle at batch {j} on rank {rank}")
+        if hit.tolist() != want["hit"]:
+            raise AssertionError(f"self-check: hit flags differ from the oracle at batch {j} on rank {rank}")
+        wv = np.stack(want["out"])
+        if not np.all(np.abs(out.cpu().numpy().astype(np.float64) - wv[:, 0]) <= rel * wv[:, 1] + 1e-6):
+            raise AssertionError(f"self-check: outputs outside tolerance at batch {j} on rank {rank}")
+
+    kd = torch.from_numpy(key_bytes_of(ids[:, rank].reshape(-1)).reshape(n, B * KEY_LEN)).cuda()
+    xd = torch.from_numpy(np.ascontiguousarray(x[:, rank])).cuda()
+    out, hit, shard = runner.step(ops.KeyBatch(kd[0], off_d), xd[0], now)
+    torch.cuda.synchronize()
+    compare(0, out, hit, shard if isinstance(shard, torch.Tensor) else None)
+    outs = torch.empty((n - 1, B, D), dtype=torch.float32, device="cuda")
+    hits = torch.empty((n - 1, B), dtype=torch.uint8, device="cuda")
+    if hasattr(runner, "step_many"):
+        runner.step_many(kd[1:], off_d, xd[1:], now + DT, DT, outs, hits)
+    else:
+        for j in range(1, n):
+            runner.step(ops.KeyBatch(kd[j], off_d), xd[j], now + j * DT, outs[j - 1], hits[j - 1])
+    torch.cuda.synchronize()
+    for j in range(1, n):
+        compare(j, outs[j - 1], hits[j - 1], None)
+    if hasattr(runner, "check"):
+        runner.check()
+    st, mine = runner.pipe.kv.stats(), ref.state()[rank]
+    got, want = (st["hits"], st["misses"], st["evictions"], st["size"]), (mine["hits"], mine["misses"], mine["evictions"], mine["size"])
+    if got != want:
+        raise AssertionError(f"self-check: owner counters {got} != oracle {want} on rank {rank}")
+    return {"batches": n, "requests_per_rank": n * B, "hits": int(mine["hits"]), "vs": "oracle.pipeline.OraclePipeline.process_exchange",
+            "result": "ok"}
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -364,8 +532,8 @@ DT_E2E = 0.01
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=2000)
-    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernels", action="store_true",
@@ -403,13 +571,14 @@ def main():
     RING = 64
     out_ring = torch.empty((RING, B, D), dtype=torch.float32, device="cuda")
     hit_ring = torch.empty((RING, B), dtype=torch.uint8, device="cuda")
-    DT = 0.01  # seconds of injected clock per flushed batch
 
-    def to_device(keys, x):
-        return torch.from_numpy(keys).cuda(), torch.from_numpy(x).cuda()
+    self_check = None
+    if world > 1:
+        self_check = sharded_self_check(runner, rank, world, off_d)
+        dist.barrier()
 
     def run_steps(kd, xd, now0):
-        """kd [n, B*15] uint8, xd [n, B, D]: n flushed batches, applied in order."""
+        """kd [n, B*15] uint8, xd [n, B, D]: a queue of n flushed batches, applied in order."""
         n = kd.shape[0]
         if runner is None:  # one C-ABI call submits the whole queue (each batch is still its own pass)
             pipe.run_device_many(kd, off_d, xd, now0, DT, out_ring, hit_ring)
@@ -420,18 +589,24 @@ def main():
                 runner.step(ops.KeyBatch(kd[i], off_d), xd[i], now0 + i * DT, out_ring[i % RING], hit_ring[i % RING])
         return now0 + n * DT
 
+    # ---- inputs: fresh keys for every batch; payload pool of two steps' worth of batches, larger than L2 ----------
+    pool = torch.from_numpy(rng.standard_normal((2 * G, B, D), dtype=np.float32)).cuda()
+    n_fill = int(KV_MAX * 1.15 / B) + 1
+    _, keys, _, _ = make_batches(rng, n_fill + (W + K) * G, payload=False)
+    kd_all = torch.from_numpy(keys).cuda()
+    del keys
+
     # ---- prefill the cache to capacity (untimed) -------------------------------------------------------------
     now = 1000.0
-    n_fill = int(KV_MAX * 1.15 / B) + 1
-    for c in range(0, n_fill, 64):
-        _, keys, _, x = make_batches(rng, min(64, n_fill - c))
-        now = run_steps(*to_device(keys, x), now)
+    for c in range(0, n_fill, G):
+        m = min(G, n_fill - c)
+        now = run_steps(kd_all[c:c + m], pool[:m], now)
     torch.cuda.synchronize()
+    kd_steps = kd_all[n_fill:].view(W + K, G, B * KEY_LEN)
 
     # ---- timed: inputs resident in HBM ------------------------------------------------------------------------
-    _, keys, _, x = make_batches(rng, W + K)
-    kd, xd = to_device(keys, x)
-    now = run_steps(kd[:W], xd[:W], now)
+    for s_ in range(W):
+        now = run_steps(kd_steps[s_], pool[(s_ & 1) * G:(s_ & 1) * G + G], now)
     torch.cuda.synchronize()
     stats0 = pipe.kv.stats()
     if world > 1:
@@ -443,10 +618,11 @@ def main():
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     t_host = time.perf_counter()
-    now = run_steps(kd[W:], xd[W:], now)
-    t_host = time.perf_counter() - t_host  # host time to enqueue the queue (no wait on the GPU)
+    for s_ in range(W, W + K):
+        now = run_steps(kd_steps[s_], pool[(s_ & 1) * G:(s_ & 1) * G + G], now)
+    t_host = time.perf_counter() - t_host  # host time to enqueue the queues (no wait on the GPU)
     ev1.record()
-    sampler.sample_now()  # everything is enqueued: the query can no longer hold up a launch
+    sampler.sample_now()  # everything is enqueued: the queries can no longer hold up a launch
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -458,8 +634,10 @@ def main():
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t[0])
-    value = world * K * B / (ms / 1e3)
+        runner.check() if hasattr(runner, "check") else None
+    value = world * K * G * B / (ms / 1e3)
     hit_rate = (stats1["hits"] - stats0["hits"]) / max(1, (stats1["hits"] - stats0["hits"]) + (stats1["misses"] - stats0["misses"]))
+    del kd_all, kd_steps
 
     # ---- e2e: host buffers through the C-ABI (H2D + kernels + D2H inside the timed region) ---------------------
     e2e = None
@@ -469,40 +647,44 @@ def main():
         except Exception as exc:  # noqa: BLE001  (the device-resident number above stands on its own)
             e2e = {"value": None, "unit": "requests/s", "error": repr(exc)[:300]}
     if world == 1:
-        _, keys, off, x = make_batches(rng, K + 3)
-        hk = torch.from_numpy(np.concatenate([keys, np.zeros((K + 3, 16), np.uint8)], axis=1)).pin_memory()
+        _, keys, off, _ = make_batches(rng, (K + 1) * G, payload=False)
+        hk = torch.from_numpy(np.concatenate([keys, np.zeros(((K + 1) * G, 16), np.uint8)], axis=1)).pin_memory()
+        del keys
         ho = torch.from_numpy(off).pin_memory()
-        hx = torch.from_numpy(x).pin_memory()
-        hout = torch.empty((K, B, D), dtype=torch.float32).pin_memory()
-        hhit = torch.empty((K, B), dtype=torch.uint8).pin_memory()
-        pipe.run_host_many(hk[K:], ho, hx[K:], now, DT, hout[:3], hhit[:3])  # warm the staging path
-        now += 3 * DT
+        hx = pool.cpu().pin_memory()                       # the payload pool, in pinned host memory
+        hout = torch.empty((G, B, D), dtype=torch.float32).pin_memory()
+        hhit = torch.empty((G, B), dtype=torch.uint8).pin_memory()
+        pipe.run_host_many(hk[K * G:], ho, hx[:G], now, DT, hout, hhit)  # warm the staging path
+        now += G * DT
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        pipe.run_host_many(hk[:K], ho, hx[:K], now, DT, hout, hhit)   # returns after the last result is on the host
+        for s_ in range(K):    # one call per step: a queue of G batches, returns after the last result is on the host
+            pipe.run_host_many(hk[s_ * G:(s_ + 1) * G], ho, hx[(s_ & 1) * G:(s_ & 1) * G + G], now, DT, hout, hhit)
+            now += G * DT
         dt = time.perf_counter() - t0
-        now += K * DT
         # the unpipelined form of the same call, one synchronous batch at a time
         t0 = time.perf_counter()
-        n_sync = min(K, 50)
+        n_sync = 50
         for i in range(n_sync):
             pipe.run_host(hk[i], ho, hx[i], now + i * DT, hout[i], hhit[i])
         dt_sync = time.perf_counter() - t0
         now += n_sync * DT
-        e2e = {"value": K * B / dt, "unit": "requests/s",
-               "h2d_bytes_per_step": B * KEY_LEN + (B + 1) * 8 + B * D * 4, "d2h_bytes_per_step": B * D * 4 + B,
+        e2e = {"value": K * G * B / dt, "unit": "requests/s",
+               "h2d_bytes_per_step": G * (B * KEY_LEN + B * D * 4) + (B + 1) * 8, "d2h_bytes_per_step": G * (B * D * 4 + B),
                "ms_per_step": 1e3 * dt / K,
-               "api": "die_pipeline_run_host_many (C-ABI, pinned host buffers; copy-in / kernels / copy-out of "
-                      "consecutive batches overlap)",
-               "per_call_sync": {"value": n_sync * B / dt_sync, "ms_per_step": 1e3 * dt_sync / n_sync,
+               "api": "die_pipeline_run_host_many (C-ABI, pinned host buffers), one call per step of G batches; copy-in / "
+                      "kernels / copy-out of consecutive groups of 16 batches overlap; each call returns with its results "
+                      "on the host",
+               "per_call_sync": {"value": n_sync * B / dt_sync, "ms_per_batch": 1e3 * dt_sync / n_sync,
                                  "api": "die_pipeline_run_host, one blocking call per batch"}}
+        del hk, hx, hout, hhit
 
     # ---- per-stage device time (CUDA events on the launching stream) and roofline -------------------------------
     stages, roofline = {}, None
     if world == 1 or os.environ.get("DIE_BENCH_PROFILE_ALL"):
-        n_prof = min(K, 50)
-        _, keys, _, x = make_batches(rng, n_prof)
-        kd2, xd2 = to_device(keys, x)
+        n_prof = 50
+        _, keys, _, _ = make_batches(rng, n_prof, payload=False)
+        kd2, xd2 = torch.from_numpy(keys).cuda(), pool[:n_prof]
         s0 = pipe.kv.stats()
         _cabi.check(lib.die_profile_begin())
         now = run_steps(kd2, xd2, now)
@@ -510,44 +692,7 @@ def main():
         ms_arr, cnt_arr, n_st = (ctypes.c_double * 32)(), (ctypes.c_uint64 * 32)(), ctypes.c_int32()
         _cabi.check(lib.die_profile_end(32, ms_arr, cnt_arr, ctypes.byref(n_st)))
         s1 = pipe.kv.stats()
-        hits = (s1["hits"] - s0["hits"]) / n_prof
-        miss = (s1["misses"] - s0["misses"]) / n_prof
-        evic = (s1["evictions"] - s0["evictions"]) / n_prof
-        row = D * 4
-        alg = {  # algorithmic bytes per launch (SURVEY.md section 8(d) per-request figures x requests per launch)
-            "kv_get": B * (KEY_LEN + 8 + 16) + hits * 121 + miss * 89 + B * 5 + evic * 12,   # route + probe + rank + window
-            "kv_set_claim": miss * 160 + B * 2 * row + B * 13,                                # insert + pack / hit copy
-            "model": miss * (2 * row + 16),
-            "unpack_store": miss * 3 * row + B * 9 + evic * 128,                              # unpack + cached row + evict
-        }
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:  # noqa: BLE001
-            pass
-        peak = float(peaks.get("hbm_gbs", 6650.0))
-        peak_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-        total_ms = sum(ms_arr[i] for i in range(n_st.value))
-        kernel_of = {"kv_get": "pipe_get_kernel", "kv_set_claim": "pipe_claim_pack_kernel", "model": "linear_tf32_kernel",
-                     "unpack_store": "pipe_unpack_evict_kernel"}
-        for i in range(n_st.value):
-            if cnt_arr[i] == 0:
-                continue
-            name = lib.die_profile_stage_name(i).decode()
-            per = ms_arr[i] / cnt_arr[i]
-            gbs = alg.get(name, 0) / (per * 1e-3) / 1e9 if per > 0 else 0.0
-            stages[name] = {"kernel": kernel_of.get(name, name), "us_per_launch": round(per * 1e3, 3),
-                            "launches_per_step": cnt_arr[i] / n_prof, "share": round(ms_arr[i] / total_ms, 4),
-                            "alg_bytes_per_launch": round(alg.get(name, 0)), "gbs": round(gbs, 1),
-                            "frac_of_hbm_peak": round(gbs / peak, 4)}
-        dom = max(stages, key=lambda n: stages[n]["share"])
-        traffic, traffic_src = ncu_traffic(stages[dom]["kernel"])
-        roofline = {"kernel": stages[dom]["kernel"], "bound": "hbm", "achieved": stages[dom]["gbs"], "peak": peak,
-                    "unit": "GB/s", "frac": stages[dom]["frac_of_hbm_peak"], "traffic": traffic, "traffic_source": traffic_src,
-                    "peak_source": peak_src,
-                    "us_per_launch": stages[dom]["us_per_launch"], "alg_bytes_per_launch": stages[dom]["alg_bytes_per_launch"],
-                    "note": "a 4096-request batch carries ~5 MB of algorithmic traffic (<1 us at peak): every kernel of the "
-                            "step sits on its launch + dependent-DRAM-latency floor, see DESIGN.md section 5"}
+        stages, roofline = stage_rooflines(lib, ms_arr, cnt_arr, n_st.value, n_prof, s0, s1, ms / (K * G))
 
     # ---- host-side API edge of the drop-in classes: str -> bytes -> device, list of rows -> padded device batch ----
     api_edge = None
@@ -580,7 +725,7 @@ def main():
     # ---- every kernel of the path alone, at sizes where bandwidth (not launch latency) is the limit -------------
     kernels = None
     if world == 1 and not args.no_kernels:
-        del kd, xd, out_ring, hit_ring
+        del out_ring, hit_ring, pool
         runner = pipe = None
         torch.cuda.empty_cache()
         sys.path.insert(0, os.path.join(ROOT, "tools"))
@@ -593,12 +738,13 @@ def main():
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "requests/s", "n_gpus": world, "steps": K, "warmup": W,
-                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "ms_per_step": ms / K, "us_per_batch": round(1e3 * ms / (K * G), 3), "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None,
                 "dtype": "tf32" if MODEL == "linear_tf32" else "f32",
-                "data": "synthetic", "config": dict(workload_config(world), hit_rate=round(hit_rate, 4), model=MODEL),
+                "data": "synthetic", "config": workload_config(world), "hit_rate": round(hit_rate, 4),
                 "gpu_launches": int(launches), "host_enqueue_us_per_step": round(1e6 * t_host / K, 2),
                 "clocks": clocks, "e2e": e2e, "roofline": roofline, "stages": stages,
-                "kernels": kernels, "api_edge": api_edge, "cpu_baseline": cpu}
+                "kernels": kernels, "api_edge": api_edge, "self_check": self_check, "cpu_baseline": cpu}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

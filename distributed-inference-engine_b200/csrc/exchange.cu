@@ -12,7 +12,11 @@
 //                            count [world] int32                 how many rows source s wrote this step
 // Return window of a rank:   back  [world][cap][dim_out + 4]    region d is written only by owner d:
 //                                   result row, then one 16-byte tail whose first word is the hit flag
-// cap = the ingest batch size, so no bucket can overflow whatever the key distribution or health state.
+// cap = the ingest batch size, so no (source, owner) region can overflow whatever the key distribution.
+// The fused step routes with md5 mod world only: it assumes every rank of the group is up (a rank that is not
+// cannot run its barriers either).  Router's health gate and failover (router.py:165-221) are served by
+// die_route_md5 + die_bucket_by_shard and the stand-alone phase entry points below; an owner is sized for
+// owner_max requests per step and a step that exceeds it raises the error die_xchg_check_sync reports.
 // Owners see the sources in rank order, request order kept inside each source: the order the CPU oracle's
 // process_exchange applies.
 //

@@ -1012,8 +1012,7 @@ extern "C" die_status_t die_kv_len_sync(die_kv_t* kv, double now, uint64_t* purg
                                         uint64_t* n_purged, uint64_t* len_out, die_stream_t stream) {
     if (!kv || !len_out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_len_sync: bad arguments");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    unsigned long long* d_n = nullptr;
-    DIE_CUDA(cudaMalloc(&d_n, sizeof(unsigned long long)));
+    unsigned long long* d_n = kv->n_kept_dev;  // the handle's one-word device counter (also used by compaction)
     DIE_CUDA(cudaMemsetAsync(d_n, 0, sizeof(unsigned long long), s));
     DIE_LAUNCH(ST_KV_PURGE, s, kv_purge_kernel<<<num_sms() * 8, KV_THREADS, 0, s>>>(view_of(kv), now,
                                                          reinterpret_cast<unsigned long long*>(purged_out),
@@ -1022,7 +1021,6 @@ extern "C" die_status_t die_kv_len_sync(die_kv_t* kv, double now, uint64_t* purg
     DIE_CUDA(cudaMemcpyAsync(&n, d_n, sizeof(n), cudaMemcpyDeviceToHost, s));
     DIE_CUDA(cudaMemcpyAsync(&size, &kv->st->size, sizeof(size), cudaMemcpyDeviceToHost, s));
     DIE_CUDA(cudaStreamSynchronize(s));
-    cudaFree(d_n);
     if (n_purged) *n_purged = n;
     *len_out = size;
     return DIE_OK;
@@ -1166,9 +1164,7 @@ extern "C" die_status_t die_kv_set_batch_noalloc(die_kv_t* kv, const uint32_t* d
         kv->live_at_rebuild + kv->claims_ub + n > kv->capacity / 8 * 3)
         DIE_FAIL(DIE_ERR_NOMEM,
                  "die_kv_set_batch_noalloc: table housekeeping is due and would allocate; call die_kv_maintain_sync "
-                 "(or any die_kv_*_sync) at a point where allocation is allowed, then retry");
-    kv->claims_ub += n;
-    kv->dropped_prefix = 0;
+                 "at a point where allocation is allowed, then retry");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const KvView v = view_of(kv);
     const uint4* dg = reinterpret_cast<const uint4*>(digests);
@@ -1189,6 +1185,12 @@ extern "C" die_status_t die_kv_set_batch_noalloc(die_kv_t* kv, const uint32_t* d
     DIE_LAUNCH(ST_KV_EVICT, s, kv_set_evict_tiles_kernel<<<n_tiles, WIN_THREADS, 0, s>>>(v, kv->tail, kv->tile_cnt, dr));
     DIE_LAUNCH(ST_KV_EVICT, s, kv_set_evict_kernel<<<1, WIN_THREADS, 0, s>>>(v, dg, vals, ttl, M, now, kv->tail,
                                                                              deferred_stamp, nullptr, slot_out, dr));
+    // Host bookkeeping only once every launch of the batch is enqueued (a failed launch returned above and left
+    // the bounds untouched): the same three fields kv_reserve() advances for die_kv_set_batch.  ops_enq feeds
+    // kv_mirror_refresh(): without it a pipeline-owned table would under-count the inserts in flight.
+    kv->claims_ub += n;
+    kv->ops_enq += n;
+    kv->dropped_prefix = 0;
     kv->tail += n;
     return DIE_OK;
 }

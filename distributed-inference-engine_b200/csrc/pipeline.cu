@@ -206,19 +206,23 @@ pipe_get_kernel(StepRef sr, PipeBufs pb, uint4* __restrict__ digests, int B, con
     const double now = a.now;
     const unsigned long long t_get = a.t_get;
     pb.code = a.code;
-    if (n_req_dev) B = min(B, (int)*n_req_dev);  // batch size known only on the device (after an exchange)
+    // What this kernel reads BEFORE griddepcontrol.wait, and why that is ordered: the step descriptor (written by
+    // queue_desc_set_kernel, which is followed by a full kernel boundary -- the graph launch -- never by a PDL
+    // edge) and, when FROM_KEYS, the key bytes (host-to-device copies or another stream behind an event, never the
+    // same-stream predecessor kernel).  Everything a predecessor kernel may have written -- the device-side batch
+    // size, digests, table, control block -- is read after the wait.
     const int i = blockIdx.x * PT + threadIdx.x;
-    const bool active = i < B;
     u128 key{0ull, 0ull};
-    if (FROM_KEYS) {
-        const Md5State st = cta_hash_keys(key_bytes, key_off, B, stage);
-        if (active) {
-            const uint4 d = make_uint4(st.a, st.b, st.c, st.d);
-            digests[i] = d;
-            key = fp_of(d);
-        }
+    Md5State st{};
+    if (FROM_KEYS) st = cta_hash_keys(key_bytes, key_off, B, stage);  // rows past a device-side count are hashed and dropped
+    pdl_wait();
+    if (n_req_dev) B = min(B, (int)*n_req_dev);  // batch size known only on the device (after an exchange)
+    const bool active = i < B;
+    if (FROM_KEYS && active) {
+        const uint4 d = make_uint4(st.a, st.b, st.c, st.d);
+        digests[i] = d;
+        key = fp_of(d);
     }
-    pdl_wait();  // the table, the control block and (when precomputed) the digests belong to earlier kernels
     if (!FROM_KEYS && active) key = fp_of(digests[i]);
     int code = 0;
     if (i == 0) pb.ctrl->ts[0] = pb.ctrl->ts[1] = globaltimer_ns();  // predecessor done, keys hashed (CTA 0)

@@ -228,3 +228,92 @@ class PeerDispatcher:
 
     def check(self) -> None:
         self._cabi.check(self.lib.die_xchg_check_sync(self._x, self._cabi.stream_ptr()))
+
+
+class LoopbackPeerGroup:
+    """All `world` ranks of the peer exchange inside ONE process on ONE GPU.
+
+    Each rank gets its own owner pipeline (its own KV shard), its own `die_xchg_t` and its own window; the
+    windows are ordinary device allocations of the same GPU, so "peer stores" land in local HBM.  The code that
+    runs is exactly csrc/exchange.cu's sharded step -- route, dispatch, flag barrier, owner pass, return, scatter --
+    which makes the N > 1 path checkable on a one-GPU box (tests/test_gpu_loopback.py, __graft_entry__.smoke()).
+
+    The flag barriers of the ranks wait on one another, so every rank's call of a step must be enqueued before
+    any of them is synchronised, and the ranks' streams must not share a hardware queue: set
+    CUDA_DEVICE_MAX_CONNECTIONS=32 before CUDA is initialised (tests/conftest.py and smoke() do).  Table
+    housekeeping synchronises one rank's streams: call `maintain()` between steps instead of letting a step
+    trigger it while its peers' work is not enqueued yet."""
+
+    def __init__(self, world: int, kv_max_size: int, max_batch: int, dim: int, weight, bias, default_ttl,
+                 model: str = "linear_tf32"):
+        import ctypes
+        from . import _cabi, ops
+        from .pipeline import DispatchPipeline
+        self._cabi, self.ops = _cabi, ops
+        self.lib = _cabi.require_cuda()
+        self.world, self.cap, self.dim = world, max_batch, dim
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        self.bmax = min(world, 2) * max_batch
+        self.pipes = [DispatchPipeline(kv_max_size, self.bmax, dim, dim, model, weight, bias, default_ttl)
+                      for _ in range(world)]
+        nbytes = int(self.lib.die_xchg_window_bytes(world, self.cap, dim))
+        self.windows = [torch.zeros((nbytes + 3) // 4, dtype=torch.float32, device=self.dev) for _ in range(world)]
+        self._peers = (ctypes.c_void_p * world)(*[w.data_ptr() for w in self.windows])
+        self._x = []
+        for r in range(world):
+            h = ctypes.c_void_p()
+            _cabi.check(self.lib.die_xchg_create(world, r, self.cap, dim, self.bmax, self.pipes[r]._h, self._peers,
+                                                 ctypes.byref(h)))
+            self._x.append(h.value)
+        self.streams = [torch.cuda.Stream() for _ in range(world)]
+        torch.cuda.synchronize()
+
+    def __del__(self):
+        for h in getattr(self, "_x", []):
+            self.lib.die_xchg_destroy(h)
+        self._x = []
+
+    def _sync_and_check(self):
+        for s in self.streams:
+            s.synchronize()
+        torch.cuda.synchronize()
+        for r, h in enumerate(self._x):
+            self._cabi.check(self.lib.die_xchg_check_sync(h, self.streams[r].cuda_stream))
+
+    def maintain(self):
+        for p in self.pipes:
+            p.kv.maintain(force=False)
+
+    def step(self, keys, payloads, now: float):
+        """keys[r] / payloads[r]: the batch rank r ingests.  -> [(out, hit, shard)] per rank."""
+        check, ptr = self._cabi.check, self._cabi.ptr
+        res = []
+        cur = torch.cuda.current_stream()
+        for r in range(self.world):
+            B = payloads[r].shape[0]
+            out = torch.empty((B, self.dim), dtype=torch.float32, device=self.dev)
+            hit = torch.empty(B, dtype=torch.uint8, device=self.dev)
+            shard = torch.empty(B, dtype=torch.int32, device=self.dev)
+            self.streams[r].wait_stream(cur)
+            check(self.lib.die_xchg_step(self._x[r], ptr(keys[r].key_bytes), ptr(keys[r].key_off), B, ptr(payloads[r]),
+                                         now, ptr(out), ptr(hit), ptr(shard), self.streams[r].cuda_stream))
+            res.append((out, hit, shard))
+        self._sync_and_check()
+        return res
+
+    def step_many(self, key_bytes, key_off, payloads, now0: float, now_step: float):
+        """key_bytes[r] [n, stride], key_off[r] [n, B+1], payloads[r] [n, B, dim] -> [(out [n,B,dim], hit [n,B])]."""
+        check, ptr = self._cabi.check, self._cabi.ptr
+        res = []
+        cur = torch.cuda.current_stream()
+        for r in range(self.world):
+            n, B = payloads[r].shape[0], payloads[r].shape[1]
+            out = torch.empty((max(n, 2), B, self.dim), dtype=torch.float32, device=self.dev)
+            hit = torch.empty((max(n, 2), B), dtype=torch.uint8, device=self.dev)
+            self.streams[r].wait_stream(cur)
+            check(self.lib.die_xchg_step_many(self._x[r], n, ptr(key_bytes[r]), key_bytes[r].stride(0), ptr(key_off[r]),
+                                              key_off[r].stride(0), B, ptr(payloads[r]), now0, now_step, ptr(out), ptr(hit),
+                                              out.shape[0], self.streams[r].cuda_stream))
+            res.append((out[:n], hit[:n]))
+        self._sync_and_check()
+        return res

@@ -325,7 +325,11 @@ def test_bench_reference_arm_prints_the_contract_line():
     for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
               "vs_baseline", "dtype", "data", "config", "impl", "cpu_baseline", "e2e"):
         assert k in line, k
-    assert line["impl"] == "reference" and line["value"] > 0 and line["cpu_baseline"]["kind"] == "port"
+    from oracle import refrun
+    assert line["impl"] == "reference" and line["value"] > 0
+    # the reference's own classes when oracle/_ref holds the verbatim copy (oracle/fetch_ref.py), else the port
+    assert line["cpu_baseline"]["kind"] == ("reference" if refrun.available() else "port")
+    assert line["config"]["kv_max_size"] == 1 << 20 and line["config"]["id_space"] == 10 ** 7  # the GPU arm's configuration
     assert line["e2e"]["h2d_bytes_per_step"] == 0 and "workload" in line["config"]
     env = dict(os.environ, RANK="1", WORLD_SIZE="2")
     r1 = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2"],
@@ -344,3 +348,30 @@ def test_bench_gpu_arm_has_no_cpu_fallback():
                        capture_output=True, text=True, timeout=300)
     assert r.returncode != 0
     assert not any(line.startswith("{") for line in r.stdout.splitlines())
+
+
+def test_reference_classes_composed_by_refrun_agree_with_the_port():
+    """oracle/refrun.py chains the reference's OWN Router / KVCache / Batcher (verbatim copy under oracle/_ref, made
+    by oracle/fetch_ref.py wherever /root/reference exists); the restatement in oracle/pipeline.py must give the
+    same shard ids, hit flags, results and per-owner LRU state on a seeded run with evictions and TTL expiry."""
+    from oracle import refrun
+    from oracle.pipeline import OraclePipeline
+    if not refrun.available():
+        pytest.skip("oracle/_ref is absent on this box (the reference checkout does not travel)")
+    import random
+    rng = random.Random(3)
+    model = lambda rows: [[2 * v for v in r] for r in rows]  # noqa: E731
+    a = refrun.ReferencePipeline(3, 40, 5.0, model, max_batch_size=64)
+    b = OraclePipeline(3, 40, 5.0, model)
+    now = 10.0
+    for _ in range(30):
+        now += rng.choice([0.0, 0.5, 3.0, 6.0])
+        keys = ["user-%010d" % rng.randrange(200) for _ in range(64)]
+        pays = [[rng.randrange(100) for _ in range(3)] for _ in range(64)]
+        ra, rb = a.process(keys, pays, now), b.process(keys, pays, now)
+        assert ra == rb
+    sa, sb = a.state(), b.state()
+    for x, y in zip(sa, sb):
+        assert x["lru"] == y["lru"]
+        assert (x["hits"], x["misses"], x["evictions"], x["size"]) == (y["hits"], y["misses"], y["evictions"], y["size"])
+    assert sum(x["evictions"] for x in sa) > 0 and sum(x["hits"] for x in sa) > 0

@@ -4,8 +4,9 @@ serving (all HBM reserved at start-up, or a section that cannot afford cudaMallo
 The entry point keeps its per-op scratch in a fixed array inside the library instead of a cudaMalloc'd
 buffer.  This test drives it through the C-ABI twice in a row and requires exactly what the regular
 die_kv_set_batch produces on a twin table: same dropped values, same LRU order, same entry
-metadata and counters (bit-exact, like every other cache test here).  The second call is smaller than the
-first, so it runs over whatever the first call left in the shared scratch.  Collected last on purpose."""
+metadata and counters (bit-exact, like every other cache test here), and what the CPU restatement of the
+reference's KVCache.set holds after the same ops.  The second call is smaller than the first, so it runs over
+whatever the first call left in the shared scratch.  Collected last on purpose."""
 import ctypes
 import hashlib
 import math
@@ -40,7 +41,10 @@ def test_noalloc_set_matches_regular_set_on_two_calls_in_a_row():
     from die import _cabi
     from die.kvstore import DeviceKV
     lib = _cabi.require_cuda()
+    from oracle import ref_port as rp
     ref, sut = DeviceKV(5000, 30.0), DeviceKV(5000, 30.0)   # per-launch limit of such a table: 2048 ops
+    clock = [0.0]
+    port = rp.PortKVCache(5000, 30.0, clock=lambda: clock[0])  # kvstore.py:104-134 applied op by op
     rng = np.random.default_rng(42)
     now, next_val = 10.0, 1
     # back-to-back calls: fill (duplicates inside each batch), overflow the 5000 entries (evictions),
@@ -68,6 +72,16 @@ def test_noalloc_set_matches_regular_set_on_two_calls_in_a_row():
         assert sorted(drop_a[:nd_a].tolist()) == sorted(drop_b[:nd_b].tolist())
         assert ref.stats() == sut.stats()
         assert state_of(ref) == state_of(sut)
+        # ... and against the oracle directly, not only against the twin: LRU order, values, counters
+        clock[0] = now
+        for k, v, t in zip(keys, values.tolist(), ttl.tolist()):
+            port.set(k, v, ttl=None if math.isnan(t) else t)
+        d = sut.dump()
+        order = [bytes(x) for x in d["digests"].numpy().view(np.uint8).reshape(-1, 16)]
+        assert order == [hashlib.md5(k.encode()).digest() for k in port.lru_order()]
+        assert d["values"].tolist() == [port.cache[k].value for k in port.lru_order()]
+        ps, ss = port.stats(), sut.stats()
+        assert (ss["size"], ss["evictions"]) == (ps["size"], ps["evictions"])
         # and the filled table answers like its twin
         probe = md5_words(["na%d" % i for i in rng.integers(0, space, 300)])
         now += 0.5
@@ -91,3 +105,37 @@ def test_noalloc_set_rejects_batches_beyond_its_fixed_scratch():
     rc, slot, _ = call_set(lib, "die_kv_set_batch_noalloc", kv, ok, None, None, 2.0)
     assert rc == 0, lib.die_last_error()
     assert kv.sync_status()[0] == 0 and kv.stats()["size"] == 65536 and int(slot.min()) >= 0
+
+
+def test_noalloc_sets_interleaved_with_replayed_pipeline_steps_keep_the_host_bounds_sound():
+    """A pipeline-owned table (die_pipeline_kv) refreshes its free-slot bound from a device snapshot that counts the
+    inserts enqueued since (`ops_enq`).  No-alloc sets on that table must be part of the count: interleave them with
+    graph-replayed queues of batches and require that housekeeping still keeps the table under its load limit."""
+    from die import _cabi
+    from die.pipeline import DispatchPipeline
+    lib = _cabi.require_cuda()
+    B, D, kv_max = 256, 32, 1 << 16   # table of 2^18 slots: 16-step replays fit its reserve
+    rng = np.random.default_rng(5)
+    pipe = DispatchPipeline(kv_max, B, D, model="echo", default_ttl=None)
+    off = torch.arange(B + 1, dtype=torch.int64, device="cuda") * 15
+    out = torch.empty((4, B, D), dtype=torch.float32, device="cuda")
+    hit = torch.empty((4, B), dtype=torch.uint8, device="cuda")
+    now = 1.0
+    for rnd in range(40):
+        ids = rng.integers(0, 10 ** 9, (32, B))
+        kb = np.frombuffer("".join("user-%010d" % i for i in ids.reshape(-1)).encode(), dtype=np.uint8).reshape(32, B * 15)
+        keys = torch.from_numpy(np.concatenate([kb, np.zeros((32, 16), np.uint8)], axis=1)).cuda()
+        x = torch.from_numpy(rng.standard_normal((32, B, D), dtype=np.float32)).cuda()
+        pipe.run_device_many(keys, off, x, now, 0.01, out, hit)
+        now += 1.0
+        for _ in range(4):
+            # no values passed: the pipeline's table hands out its own result rows, B spare rows per batch
+            dig = md5_words(["na-%d-%d" % (rnd, i) for i in rng.integers(0, 10 ** 9, B)])
+            rc, _, _ = call_set(lib, "die_kv_set_batch_noalloc", pipe.kv, dig, None, None, now)
+            if rc == _cabi.DIE_ERR_NOMEM:         # housekeeping due: run it where allocation is allowed, retry
+                pipe.kv.maintain(force=False)
+                rc, _, _ = call_set(lib, "die_kv_set_batch_noalloc", pipe.kv, dig, None, None, now)
+            assert rc == 0, lib.die_last_error()
+        st = pipe.kv.stats()
+        assert st["size"] + st["tombstones"] <= st["capacity"] * 3 // 8, (rnd, st)  # the load limit the bounds protect
+    assert pipe.kv.sync_status()[0] == 0 and pipe.kv.stats()["size"] == kv_max
