@@ -13,7 +13,7 @@ namespace die {
 enum Stage {
     ST_ROUTE = 0, ST_KV_GET, ST_KV_CONTAINS, ST_KV_DELETE, ST_KV_PURGE, ST_KV_PRECHECK, ST_KV_WINDOW, ST_KV_CLAIM,
     ST_KV_FINALIZE, ST_KV_EVICT, ST_KV_MAINT, ST_MISS_SCAN, ST_PACK_HITS, ST_MODEL, ST_UNPACK_STORE, ST_PACK,
-    ST_UNPACK, ST_BUCKET, ST_XCHG, ST_XCHG_BARRIER, ST_XCHG_COMPACT, ST_XCHG_RETURN, ST_XCHG_SCATTER, ST_COUNT
+    ST_UNPACK, ST_BUCKET, ST_XCHG, ST_XCHG_BARRIER, ST_XCHG_COMPACT, ST_XCHG_RETURN, ST_XCHG_SCATTER, ST_FUSED_STEP, ST_COUNT
 };
 void prof_before(int stage, cudaStream_t s);
 void prof_after(int stage, cudaStream_t s);

@@ -779,6 +779,18 @@ extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, con
     return xchg_join(x, user);
 }
 
+// Builds (captures + instantiates) the replay die_xchg_step_many(B, n_batches >= graph steps) would use next, without
+// launching anything: instantiation may allocate and synchronise the device, which a serving loop wants out of its
+// first timed call -- and which a group of ranks sharing ONE device (loopback tests) cannot afford while a peer's
+// barrier is already spinning on that device.
+extern "C" die_status_t die_xchg_prepare(die_xchg_t* x, int32_t B) {
+    if (!x || B <= 0 || B > x->cap) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_prepare: B must be in [1, cap]");
+    const int K = x->graph_steps;
+    if (K < 2 || !pipeline_graph_fits(x->pipe, x->bmax, K)) return DIE_OK;  // steps will be stream-launched
+    cudaGraphExec_t exec;
+    return xchg_graph_get(x, B, K, &exec);
+}
+
 // Synchronises and reports whether a barrier of this context ever timed out (a peer stopped calling).
 extern "C" die_status_t die_xchg_check_sync(die_xchg_t* x, die_stream_t stream) {
     if (!x) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_check_sync: null context");

@@ -21,7 +21,7 @@ static const char* const kStageNames[ST_COUNT] = {
     "route_md5",   "kv_get",      "kv_contains", "kv_delete",  "kv_purge", "kv_set_precheck",
     "kv_set_window", "kv_set_claim", "kv_set_finalize", "kv_set_evict", "kv_maintenance", "miss_scan",
     "pack_hits",   "model",       "unpack_store", "pack_ragged", "unpack_ragged", "bucket_by_shard", "xchg_dispatch",
-    "xchg_barrier", "xchg_compact", "xchg_return", "xchg_scatter"};
+    "xchg_barrier", "xchg_compact", "xchg_return", "xchg_scatter", "fused_step"};
 
 struct ProfRec {
     int stage;

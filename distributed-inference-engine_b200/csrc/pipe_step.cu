@@ -1,0 +1,592 @@
+// The composed hot path as ONE persistent kernel per group of flushed batches (SURVEY.md call-stack (E)):
+// route -> probe -> pack -> infer -> unpack -> fill, batch after batch, with grid-wide barriers where the
+// reference's "applied in request order" contract needs one and nowhere else.
+//
+// A 4096-request batch moves ~5 MB (< 1 us of HBM time); what a step costs is its chain of dependent DRAM
+// round trips plus, in the three-kernel form (pipeline.cu), two kernel boundaries and a serial "last CTA" tail.
+// Here the chain is all that is left:
+//
+//   grid = n_req request CTAs + n_chunks window CTAs, all co-resident (cooperative launch), 256 threads each
+//   request CTA c owns requests [c*R, c*R+R) of every batch (R = 32..96):
+//     its payload rows ARE its packed tile: cp.async straight into the SWIZZLE_128B A tile of a tcgen05 GEMM
+//     (batcher.py:211's gather never touches HBM), prefetched one batch ahead; W stays in shared memory
+//     for the whole launch; results leave TMEM for out[q] and the cached row (batcher.py:225-227) directly
+//   window CTA k owns chunk k (1024 records) of the LRU log behind the head (kvstore.py:82-93)
+//
+//   per batch:  A  probe (kvstore.py:136-164), one request per thread            | window CTAs idle
+//               -- barrier 1: every get of the batch precedes every set (call-stack (E))
+//               B  insert the misses (kvstore.py:104-134) | hit rows -> out | MMA | bitmap of current log records
+//               -- barrier 2: the arriving CTA that completes it fixes E = size - max_size (_evict_if_needed)
+//               C  GEMM epilogue: out[q], cached row                             | evict the E oldest records
+//               -- barrier 3: the next batch's probes see this batch's evictions (request CTAs arrive before
+//                  their epilogue and wait after it, so the epilogue overlaps the evictions)
+//
+// MD5 of all the launch's keys (model_registry.py:159) is a prologue over every CTA.  Results are identical to the
+// three-kernel sequence (same stamps, same claim / evict rules); tests/test_gpu_pipeline.py compares both with the
+// oracle and with each other.
+#include "model_internal.cuh"
+#include "pipeline_device.cuh"
+#include "pipeline_internal.cuh"
+#include "route_device.cuh"
+#include "tc_common.cuh"
+
+namespace die {
+
+constexpr int PS_THREADS = 256;
+constexpr int PS_M = 128;           // MMA tile rows (rows >= the CTA's request count are never read back)
+constexpr int PS_MAX_R = 96;        // requests per request CTA (staging R x (N+4) floats must fit the A tile)
+constexpr int PS_MAX_CHUNKS = 64;   // window CTAs
+
+// Device-resident control block of the persistent kernel (one per pipeline, zero-initialised).
+struct StepGrid {
+    unsigned int bar_count;   // arrivals at the current barrier
+    unsigned int bar_gen;     // completed barriers (monotone across launches)
+    unsigned int abort;       // a barrier timed out: every later barrier falls through, status is raised
+    unsigned int any_dup;     // a key occurs twice among the misses of the current batch
+    unsigned long long e_final;  // evictions the current batch needs (set when barrier 2 completes)
+    unsigned int wcount[PS_MAX_CHUNKS];  // current records per window chunk of the current batch
+    // %globaltimer marks of the last batch, CTA 0 (diagnostics): [0] start, [4] probes issued, [1] barrier 1 passed,
+    // [5] inserts done, [2] barrier 2 passed, [6] epilogue done, [3] barrier 3 passed
+    unsigned long long ts[8];
+};
+
+struct StepParams {
+    StepRef sr;                 // first batch of the launch (stream launch: values; replay: descriptor + index)
+    int n_steps;                // batches this launch processes
+    int B;                      // requests per batch (upper bound when n_req_dev is set)
+    int R;                      // requests per request CTA (multiple of 32)
+    int n_req;                  // request CTAs
+    int n_chunks;               // window CTAs
+    int K, N;                   // linear layer: Y[., N] = X[., K] @ W[N, K]^T + bias
+    int from_keys;              // 1: hash the keys in the prologue into `digests`; 0: `digests` are inputs
+    const uint32_t* n_req_dev;  // optional device-side batch size (owner pass of the exchange)
+    uint4* digests;             // [n_steps][B]
+    const float* W;
+    const float* bias;
+    float* arena;               // [n_rows, N] cached result rows
+    StepGrid* g;
+    KvMirrorArgs mirror;        // m.m != nullptr: snapshot the table counters for the host before the first batch
+};
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned int* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned int* p, unsigned v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ps_timer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// Split grid barrier.  arrive(): the whole CTA has finished what the barrier protects; the thread that completes
+// the barrier runs `leader` (it observes every CTA's writes) before it releases the others.  wait(): returns when
+// the barrier has completed.  `gen` is the CTA's count of barriers passed (uniform across the grid).
+template <typename F>
+__device__ __forceinline__ void grid_arrive(StepGrid* g, unsigned n_cta, unsigned gen, F leader) {
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned prev = atomicAdd(&g->bar_count, 1u);
+        if (prev == n_cta - 1) {
+            __threadfence();
+            leader();
+            g->bar_count = 0u;
+            __threadfence();
+            st_release_u32(&g->bar_gen, gen + 1u);
+        }
+    }
+}
+__device__ __forceinline__ void grid_wait(StepGrid* g, unsigned gen, KvState* st) {
+    if (threadIdx.x == 0) {
+        const unsigned long long t0 = ps_timer();
+        unsigned spins = 0;
+        while ((int)(ld_acquire_u32(&g->bar_gen) - (gen + 1u)) < 0) {
+            if ((++spins & 1023u) == 0u) {
+                if (ld_acquire_u32(&g->abort)) break;
+                if (ps_timer() - t0 > 2000000000ull) {  // 2 s: a CTA of the grid is gone; fail loudly, never hang
+                    atomicExch(&g->abort, 1u);
+                    st->status = DIE_ERR_CUDA;
+                    break;
+                }
+            }
+        }
+        __threadfence();
+    }
+    __syncthreads();
+    tc::fence_after_thread_sync();
+}
+
+__device__ __forceinline__ void ps_cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tc::smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+
+// Rows [q0, q0+nq) of the batch's payload -> rows [0, nq) of a K-major SWIZZLE_128B A tile (blocks of
+// [128 rows x 32 tf32]).  This is PACK: the CTA's requests, in request order, become the rows of its GEMM tile.
+__device__ __forceinline__ void ps_load_tile(uint8_t* a_base, const float* __restrict__ payload, int q0, int nq, int K) {
+    const int chunks_per_row = K / 4;
+    const int total = nq * chunks_per_row;
+    for (int e = threadIdx.x; e < total; e += PS_THREADS) {
+        const int r = e / chunks_per_row, ck = e - r * chunks_per_row;
+        ps_cp_async16(a_base + (size_t)(ck >> 3) * (PS_M * 128) + tc::sw128_offset((uint32_t)r, (uint32_t)(ck & 7)),
+                      payload + (size_t)(q0 + r) * K + ck * 4);
+    }
+}
+
+// Window CTA, phase B: bitmap of the chunk's log records that are still current (= entries of the reference's
+// _access_order, kvstore.py:71-78) among positions [head + chunk*1024, ...) below t_set.  Word w of s_mask covers
+// records [32w, 32w+32) of the chunk.  Returns the chunk's count to thread 0.
+__device__ __forceinline__ unsigned ps_window_bitmap(const KvView& kv, unsigned long long base, unsigned long long t_set,
+                                                     unsigned* s_mask, unsigned* s_cnt) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int PER = WCHUNK / PS_THREADS;
+    uint32_t slot[PER];
+    unsigned long long stamp[PER];
+    if (tid == 0) *s_cnt = 0u;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+        const unsigned long long p = base + (unsigned long long)(k * PS_THREADS + tid);
+        slot[k] = p < t_set ? __ldcg(&kv.log[p & kv.rmask]) : 0xffffffffu;
+    }
+#pragma unroll
+    for (int k = 0; k < PER; ++k)
+        stamp[k] = (unsigned long long)slot[k] <= kv.mask ? ld_u64_cg(&kv.slots[slot[k]].stamp) : 0ull;
+    unsigned cnt = 0;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+        const unsigned long long p = base + (unsigned long long)(k * PS_THREADS + tid);
+        const unsigned m = __ballot_sync(0xffffffffu, p < t_set && stamp[k] == p);
+        if (lane == 0) {
+            s_mask[k * (PS_THREADS / 32) + warp] = m;
+            cnt += __popc(m);
+        }
+    }
+    if (lane == 0 && cnt) atomicAdd(s_cnt, cnt);
+    __syncthreads();
+    return *s_cnt;
+}
+
+// Window CTA, phase C: evict the chunk's current records whose rank among all current records of the window is
+// below e (oldest first, kvstore.py:89-91).  The thread that evicts the newest victim settles the counters.
+__device__ __forceinline__ void ps_window_evict(const KvView& kv, const StepGrid* g, int chunk, int n_chunks,
+                                                unsigned long long base, unsigned long long t_set, unsigned long long e,
+                                                const unsigned* s_mask) {
+    const int tid = threadIdx.x;
+    if (e == 0) return;
+    unsigned long long before = 0;
+    for (int c = 0; c < chunk; ++c) before += __ldcg(&g->wcount[c]);
+    if (before < e) {
+        constexpr int PER = WCHUNK / PS_THREADS;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            const int rec = k * PS_THREADS + tid;  // record index inside the chunk
+            const int w = rec >> 5, b = rec & 31;
+            const unsigned word = s_mask[w];
+            if (!((word >> b) & 1u)) continue;
+            unsigned long long rank = before + __popc(word & ((1u << b) - 1u));
+            for (int ww = 0; ww < w; ++ww) rank += __popc(s_mask[ww]);
+            if (rank >= e) continue;
+            const unsigned long long pos = base + (unsigned long long)rec;
+            Slot* sl = &kv.slots[kv.log[pos & kv.rmask]];
+            release_row(kv, sl->value);
+            st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+            sl->stamp = 0ull;
+            if (rank == e - 1) {  // the newest victim: nobody else touches these counters in this phase
+                KvState* st = kv.st;
+                st->size -= e;
+                st->evictions += e;
+                st->n_tomb += e;
+                st->head = pos + 1;
+            }
+        }
+    }
+    // window too short for this log (fewer than e current records in it): finish the walk sequentially, exactly
+    if (chunk == 0 && tid == 0) {
+        unsigned long long total = 0;
+        for (int c = 0; c < n_chunks; ++c) total += __ldcg(&g->wcount[c]);
+        if (total < e) {
+            unsigned long long p = base + (unsigned long long)n_chunks * WCHUNK, left = e - total;
+            while (left > 0 && p < t_set) {
+                const uint32_t sidx = kv.log[p & kv.rmask];
+                if ((unsigned long long)sidx <= kv.mask && ld_u64_cg(&kv.slots[sidx].stamp) == p) {
+                    Slot* sl = &kv.slots[sidx];
+                    release_row(kv, sl->value);
+                    st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+                    sl->stamp = 0ull;
+                    --left;
+                }
+                ++p;
+            }
+            KvState* st = kv.st;
+            if (left > 0) st->status = DIE_ERR_INVALID;  // unreachable while max_batch <= max_size
+            st->size -= e;
+            st->evictions += e;
+            st->n_tomb += e;
+            st->head = p;
+        }
+    }
+}
+
+__device__ __forceinline__ void warp_count_add(unsigned long long* ctr, bool pred, bool negative = false) {
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m && lane_id() == 0)
+        atomicAdd(ctr, negative ? (unsigned long long)(-(long long)__popc(m)) : (unsigned long long)__popc(m));
+}
+
+__global__ void __launch_bounds__(PS_THREADS, 1)
+pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ QueueDesc qv, int use_qv) {
+    extern __shared__ uint8_t ps_smem_raw[];
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ uint32_t s_tmem;
+    __shared__ unsigned s_mask[WCHUNK / 32];
+    __shared__ unsigned s_cnt;
+    __shared__ unsigned long long s_value[PS_MAX_R];
+    __shared__ int s_slot[PS_MAX_R];
+    __shared__ int s_row[PS_MAX_R];
+    __shared__ uint8_t s_code[PS_MAX_R];
+
+    StepRef sr = P.sr;
+    if (use_qv) sr.q = &qv;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int cta = (int)blockIdx.x;
+    const bool is_req = cta < P.n_req;
+    const int chunk = cta - P.n_req;
+    const unsigned n_cta = gridDim.x;
+    StepGrid* g = P.g;
+    unsigned gen = ld_acquire_u32(&g->bar_gen);
+    const int K = P.K, N = P.N, R = P.R;
+    const int KB = K / 32;
+    const int vout = N / 4;
+
+    uint8_t* smem = ps_smem_raw + ((1024u - (tc::smem_u32(ps_smem_raw) & 1023u)) & 1023u);
+    uint8_t* b_base = smem;                                    // W: KB blocks of [N rows x 128 B]
+    uint8_t* a_base0 = smem + (size_t)N * K * 4;               // two A tiles: KB blocks of [128 rows x 128 B] each
+    const size_t a_bytes = (size_t)PS_M * K * 4;
+
+    const StepArgs a_first = step_resolve(sr);
+    const KvView kv = a_first.kv;
+    KvState* st = kv.st;
+    if (cta == 0 && tid == 0 && P.mirror.m)
+        kv_mirror_write(P.mirror.st, P.mirror.m, P.mirror.ops_seen, P.mirror.gen, P.mirror.seq);
+
+    // ---- prologue: TMEM + weights (request CTAs), MD5 of every key of the launch (all CTAs) -------------------
+    const uint32_t ncols = N <= 32 ? 32u : (N <= 64 ? 64u : (N <= 128 ? 128u : 256u));
+    if (is_req) {
+        if (warp == 0) tc::tmem_alloc(&s_tmem, ncols);
+        if (tid == 32) tc::mbar_init(&s_bar, 1);
+    }
+    if (P.from_keys) {
+        const int cps = (P.B + ROUTE_THREADS - 1) / ROUTE_THREADS;
+        const int total = P.n_steps * cps;
+        uint8_t* stage = a_base0;  // the A tiles are not in use yet
+        for (int task = cta; task < total; task += (int)n_cta) {
+            const int s = task / cps, c = task - s * cps;
+            StepRef r = sr;
+            r.i += s;
+            const StepArgs a = step_resolve(r);
+            const Md5State h = cta_hash_keys_at(a.key_bytes, a.key_off, P.B, c * ROUTE_THREADS, stage);
+            const int i = c * ROUTE_THREADS + tid;
+            if (i < P.B) P.digests[(size_t)s * P.B + i] = make_uint4(h.a, h.b, h.c, h.d);
+            __syncthreads();  // the staging buffer is reused by the next chunk
+        }
+        grid_arrive(g, n_cta, gen, [] {});
+        grid_wait(g, gen, st);
+        ++gen;
+    }
+    if (is_req) {
+        const int chunks_per_row = K / 4;
+        for (int e = tid; e < N * chunks_per_row; e += PS_THREADS) {
+            const int r = e / chunks_per_row, ck = e - r * chunks_per_row;
+            ps_cp_async16(b_base + (size_t)(ck >> 3) * ((size_t)N * 128) + tc::sw128_offset((uint32_t)r, (uint32_t)(ck & 7)),
+                          P.W + (size_t)r * K + ck * 4);
+        }
+        const int nq0 = max(0, min(R, P.B - cta * R));
+        ps_load_tile(a_base0, a_first.payload, cta * R, nq0, K);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    unsigned mma_phase = 0;
+
+    for (int s = 0; s < P.n_steps; ++s) {
+        StepRef r = sr;
+        r.i += s;
+        const StepArgs a = step_resolve(r);
+        int Bs = P.B;
+        if (P.n_req_dev) Bs = min(Bs, (int)__ldcg(P.n_req_dev));
+        const int q0 = cta * R;
+        const int nq = is_req ? max(0, min(R, Bs - q0)) : 0;
+        uint8_t* a_cur = a_base0 + (size_t)(s & 1) * a_bytes;
+        const uint4* dig = P.digests + (size_t)s * P.B;
+        u128 key{0ull, 0ull};
+        int code = 3;  // 3 = no request in this row
+        if (cta == 0 && tid == 0) g->ts[0] = ps_timer();
+
+        // ================= phase A: probe =================
+        if (is_req) {
+            if (s + 1 < P.n_steps) {  // PACK of the next batch: its rows travel while this batch is processed
+                StepRef r2 = sr;
+                r2.i += s + 1;
+                ps_load_tile(a_base0 + (size_t)((s + 1) & 1) * a_bytes, step_resolve(r2).payload, q0,
+                             max(0, min(R, P.B - q0)), K);
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            if (tid < R) {
+                const bool active = tid < nq;
+                if (active) {
+                    const int q = q0 + tid;
+                    key = fp_of(__ldcg(dig + q));
+                    unsigned long long value;
+                    long long slot;
+                    code = kv_get_one<false>(kv, key, a.now, a.t_get + (unsigned long long)q, value, slot);
+                    a.code[q] = code == 1 ? (uint8_t)1 : (uint8_t)0;  // callers see 1 = served from the cache
+                    s_value[tid] = value;
+                }
+                s_code[tid] = (uint8_t)code;
+                warp_count_add(&st->hit_part[cta & 15][0], active && code == 1);
+                warp_count_add(&st->miss_part[cta & 15][0], active && code != 1);
+                const bool deleted = active && code == 2;  // expired: this op deleted the entry (kvstore.py:153-156)
+                if (__any_sync(0xffffffffu, deleted)) {
+                    warp_count_add(&st->size, deleted, true);
+                    warp_count_add(&st->n_tomb, deleted);
+                }
+            }
+            if (cta == 0 && tid == 0) g->ts[4] = ps_timer();
+            asm volatile("cp.async.wait_group 1;" ::: "memory");  // this batch's tile (and W) have landed
+            tc::fence_proxy_async_smem();
+        }
+        grid_arrive(g, n_cta, gen, [] {});
+        grid_wait(g, gen, st);
+        ++gen;
+        if (cta == 0 && tid == 0) g->ts[1] = ps_timer();
+
+        // ================= phase B: insert the misses | hit rows | MMA | victim bitmap =================
+        unsigned long long wbase = 0;
+        if (is_req) {
+            if (tid == 4 * 32 && nq > 0) {  // INFER: one thread issues the tile's MMAs, accumulators in TMEM
+                const uint32_t idesc = tc::instr_desc(tc::FMT_TF32, PS_M, (uint32_t)N);
+                const uint32_t a_s = tc::smem_u32(a_cur), b_s = tc::smem_u32(b_base);
+                for (int kb = 0; kb < KB; ++kb) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint64_t ad = tc::smem_desc_k_major_sw128(a_s + kb * (PS_M * 128) + j * 32);
+                        const uint64_t bd = tc::smem_desc_k_major_sw128(b_s + kb * (N * 128) + j * 32);
+                        tc::mma_tf32(s_tmem, ad, bd, idesc, (kb | j) != 0);
+                    }
+                }
+                tc::mma_commit(&s_bar);
+            }
+            if (tid < R) {
+                const bool miss = tid < nq && code != 1;
+                bool claimed = false, from_empty = false;
+                if (miss) {  // KVCache.set of a key the get above found absent (kvstore.py:104-134)
+                    const int q = q0 + tid;
+                    const long long sidx = kv_claim_absent(kv, key, claimed, from_empty);
+                    Slot* sl = &kv.slots[sidx];
+                    const unsigned long long stamp = a.t_set + (unsigned long long)q;
+                    atomicMax(&sl->stamp, stamp);
+                    int row = -1;
+                    if (claimed) {
+                        row = (int)acquire_row(kv);
+                        sl->value = (unsigned long long)row;
+                        sl->created_at = a.now;
+                        sl->ttl = kv.default_ttl;
+                        sl->last_accessed = a.now;
+                        sl->access_count = 0u;
+                    } else {
+                        g->any_dup = 1u;  // same key twice among the misses: the later op owns the cached row
+                    }
+                    kv.log[stamp & kv.rmask] = (uint32_t)sidx;
+                    s_slot[tid] = (int)sidx;
+                    s_row[tid] = row;
+                }
+                warp_count_add(&st->size, miss && claimed);
+                warp_count_add(&st->n_empty_claimed, miss && claimed && from_empty);
+                warp_count_add(&st->n_tomb, miss && claimed && !from_empty, true);
+            } else if (warp >= 4) {  // hits: cached result row -> out[q]
+                __syncwarp();
+                const int4* arena = reinterpret_cast<const int4*>(P.arena);
+                int4* out = reinterpret_cast<int4*>(a.out);
+                for (int t = warp - 4; t < nq; t += 4) {
+                    if (s_code[t] != 1) continue;
+                    const long long row = (long long)s_value[t];
+                    for (int c = lane; c < vout; c += 32)
+                        stg_stream(out + (long long)(q0 + t) * vout + c, ldg_stream(arena + row * vout + c));
+                }
+            }
+        } else {
+            wbase = ld_u64_cg(&st->head) + (unsigned long long)chunk * WCHUNK;
+            const unsigned cnt = ps_window_bitmap(kv, wbase, a.t_set, s_mask, &s_cnt);
+            if (tid == 0) g->wcount[chunk] = cnt;
+        }
+        if (cta == 0 && tid == 0) g->ts[5] = ps_timer();
+        grid_arrive(g, n_cta, gen, [&] {  // every insert is in: _evict_if_needed's count for the whole batch
+            const unsigned long long size = ld_u64_cg(&st->size);
+            g->e_final = size > kv.max_size ? size - kv.max_size : 0ull;
+        });
+        grid_wait(g, gen, st);
+        ++gen;
+        if (cta == 0 && tid == 0) g->ts[2] = ps_timer();
+
+        // ================= phase C: epilogue (UNPACK) | evictions =================
+        if (is_req) {
+            const bool any_dup = __ldcg(&g->any_dup) != 0u;  // read before arriving: barrier 3 resets it
+            grid_arrive(g, n_cta, gen, [&] { g->any_dup = 0u; });  // nothing barrier 3 protects is written below
+            if (nq > 0) {
+                if (tid < nq && s_code[tid] != 1) {  // which cached row this op's result goes to (-1: none)
+                    int row = s_row[tid];
+                    if (any_dup) {  // only the last op on a slot (largest stamp) owns its value
+                        const Slot* sl = &kv.slots[s_slot[tid]];
+                        row = ld_u64_cg(&sl->stamp) == a.t_set + (unsigned long long)(q0 + tid) ? (int)ld_u64_cg(&sl->value) : -1;
+                    }
+                    s_row[tid] = row;
+                }
+                tc::mbar_wait(&s_bar, mma_phase & 1u);
+                ++mma_phase;
+                tc::fence_after_thread_sync();
+                float* stage = reinterpret_cast<float*>(a_cur);  // the MMAs have consumed the tile
+                const int pitch = N + 4;
+                if (warp < 4 && warp * 32 < nq) {
+                    const int row = warp * 32 + lane;
+                    for (int c0 = 0; c0 < N; c0 += 32) {
+                        uint32_t v[32];
+                        tc::tmem_ld_32x32(s_tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            if (c0 + j < N) {
+                                float4 o;
+                                o.x = __uint_as_float(v[j + 0]) + (P.bias ? __ldg(P.bias + c0 + j + 0) : 0.f);
+                                o.y = __uint_as_float(v[j + 1]) + (P.bias ? __ldg(P.bias + c0 + j + 1) : 0.f);
+                                o.z = __uint_as_float(v[j + 2]) + (P.bias ? __ldg(P.bias + c0 + j + 2) : 0.f);
+                                o.w = __uint_as_float(v[j + 3]) + (P.bias ? __ldg(P.bias + c0 + j + 3) : 0.f);
+                                *reinterpret_cast<float4*>(stage + (size_t)row * pitch + c0 + j) = o;
+                            }
+                        }
+                    }
+                }
+                tc::fence_before_thread_sync();
+                __syncthreads();
+                int4* out = reinterpret_cast<int4*>(a.out);
+                int4* arena = reinterpret_cast<int4*>(P.arena);
+                for (int e = tid; e < nq * vout; e += PS_THREADS) {
+                    const int rr = e / vout, c = e - rr * vout;
+                    if (s_code[rr] == 1) continue;
+                    const int4 o = *reinterpret_cast<const int4*>(stage + (size_t)rr * pitch + c * 4);
+                    stg_stream(out + (long long)(q0 + rr) * vout + c, o);
+                    const int row = s_row[rr];
+                    if (row >= 0) stg_stream(arena + (long long)row * vout + c, o);
+                }
+            }
+            if (cta == 0 && tid == 0) g->ts[6] = ps_timer();
+            grid_wait(g, gen, st);
+            ++gen;
+        } else {
+            const unsigned long long e = ld_u64_cg(&g->e_final);
+            ps_window_evict(kv, g, chunk, P.n_chunks, wbase, a.t_set, e, s_mask);
+            grid_arrive(g, n_cta, gen, [&] { g->any_dup = 0u; });
+            grid_wait(g, gen, st);
+            ++gen;
+        }
+        if (cta == 0 && tid == 0) g->ts[3] = ps_timer();
+    }
+    if (is_req && warp == 0) {
+        tc::fence_after_thread_sync();
+        tc::tmem_dealloc(s_tmem, ncols);
+    }
+}
+
+// ---- host side ------------------------------------------------------------------------------------------
+static size_t ps_smem_bytes(int K, int N) { return (size_t)N * K * 4 + 2 * (size_t)PS_M * K * 4 + 1024; }
+
+die_status_t pipe_step_grid_alloc(void** out) {
+    StepGrid* g = nullptr;
+    DIE_CUDA(cudaMalloc(&g, sizeof(StepGrid)));
+    DIE_CUDA(cudaMemset(g, 0, sizeof(StepGrid)));
+    *out = g;
+    return DIE_OK;
+}
+
+die_status_t pipe_step_marks(void* grid, unsigned long long out[8]) {
+    StepGrid h;
+    DIE_CUDA(cudaMemcpy(&h, grid, sizeof(h), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 8; ++i) out[i] = h.ts[i];
+    return DIE_OK;
+}
+
+// Shape of the persistent launch for batches of up to B requests, or false when this (B, K, N, window) does not
+// fit one co-resident grid -- the caller then uses the three-kernel sequence.
+bool pipe_step_shape(int B, int K, int N, int n_chunks, int* R_out, int* n_req_out) {
+    static int enabled = -1, max_ctas = 0, forced_r = 0;
+    if (enabled < 0) {
+        const char* e = getenv("DIE_PERSISTENT");
+        enabled = e ? atoi(e) : 1;
+        if (const char* r = getenv("DIE_STEP_R")) forced_r = atoi(r);
+    }
+    if (!enabled || B <= 0) return false;
+    if (K % 32 != 0 || N % 16 != 0 || N < 16 || N > 256 || n_chunks < 1 || n_chunks > PS_MAX_CHUNKS) return false;
+    const size_t smem = ps_smem_bytes(K, N);
+    if (smem > 220 * 1024 || (size_t)2 * PS_M * K * 4 < (size_t)ROUTE_STAGE_BYTES + 32) return false;
+    if (max_ctas == 0) {
+        if (cudaFuncSetAttribute(pipe_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024) != cudaSuccess) {
+            cudaGetLastError();
+            max_ctas = -1;
+        } else {
+            max_ctas = num_sms();  // one CTA per SM: the tiles take most of an SM's shared memory
+        }
+    }
+    if (max_ctas < 0) return false;
+    for (int R = 32; R <= PS_MAX_R; R += 32) {
+        if (forced_r && R != forced_r) continue;
+        if ((size_t)R * (N + 4) * 4 > (size_t)PS_M * K * 4) break;  // epilogue staging lives in the consumed A tile
+        const int n_req = ceil_div(B, R);
+        if (n_req + n_chunks <= max_ctas) {
+            *R_out = R;
+            *n_req_out = n_req;
+            return true;
+        }
+    }
+    return false;
+}
+
+die_status_t pipe_step_launch(const StepRef& sr, const QueueDesc* qv, int n_steps, int B, int n_chunks, int K, int N,
+                              bool from_keys, const uint32_t* n_req_dev, uint32_t* digests, const float* W,
+                              const float* bias, float* arena, void* grid, const KvMirrorArgs* mirror, cudaStream_t s) {
+    StepParams P;
+    memset(&P, 0, sizeof(P));
+    if (!pipe_step_shape(B, K, N, n_chunks, &P.R, &P.n_req))
+        DIE_FAIL(DIE_ERR_UNSUPPORTED, "pipe_step_launch: shape B=%d K=%d N=%d does not fit the persistent step kernel", B, K, N);
+    P.sr = sr;
+    P.n_steps = n_steps;
+    P.B = B;
+    P.n_chunks = n_chunks;
+    P.K = K;
+    P.N = N;
+    P.from_keys = from_keys ? 1 : 0;
+    P.n_req_dev = n_req_dev;
+    P.digests = reinterpret_cast<uint4*>(digests);
+    P.W = W;
+    P.bias = bias;
+    P.arena = arena;
+    P.g = static_cast<StepGrid*>(grid);
+    if (mirror) P.mirror = *mirror;
+    QueueDesc q;
+    memset(&q, 0, sizeof(q));
+    if (qv) q = *qv;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(P.n_req + n_chunks);
+    cfg.blockDim = dim3(PS_THREADS);
+    cfg.dynamicSmemBytes = ps_smem_bytes(K, N);
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeCooperative;  // the grid barriers need every CTA resident
+    at[0].val.cooperative = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    DIE_LAUNCH(ST_FUSED_STEP, s, cudaLaunchKernelEx(&cfg, pipe_step_kernel, P, q, qv ? 1 : 0));
+    return DIE_OK;
+}
+
+}  // namespace die

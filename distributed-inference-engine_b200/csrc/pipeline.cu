@@ -83,6 +83,9 @@ struct die_pipeline {
     float* g_out;
     uint8_t* g_hit;
     int g_steps;  // batches per set the buffers were sized for (0: not allocated)
+    // the persistent step kernel (pipe_step.cu): TF32 linear model, batches that fit one co-resident grid
+    bool persistent;
+    void* sgrid;  // its device-resident control block
 };
 
 namespace die {
@@ -506,6 +509,10 @@ static die_status_t launch_fast(die_pipeline* p, const StepRef& sr, bool from_ke
                                 const uint32_t* n_req_dev, cudaStream_t s) {
     const die_pipeline_config_t& c = p->cfg;
     const int vin = c.dim_in / 4, vout = c.dim_out / 4;
+    int ps_r, ps_n;
+    if (p->persistent && pipe_step_shape(B, c.dim_in, c.dim_out, p->n_chunks, &ps_r, &ps_n))  // the whole step in one launch
+        return pipe_step_launch(sr, nullptr, 1, B, p->n_chunks, c.dim_in, c.dim_out, from_keys, n_req_dev, digests, p->W,
+                                p->bias, p->arena, p->sgrid, nullptr, s);
     const PipeBufs pb = bufs_of(p, nullptr);  // the kernels take the hit codes' address from the step
     const int g = ceil_div(B, PT);
     uint4* dg = reinterpret_cast<uint4*>(digests);
@@ -645,6 +652,26 @@ static die_status_t graph_get(die_pipeline* p, bool from_keys, uint32_t* digests
 static die_status_t replay_fast(die_pipeline* p, QueueDesc d, QueueDesc* qd, bool from_keys, uint32_t* digests, int B,
                                 const uint32_t* n_req_dev, int K, cudaStream_t s) {
     die_kv* kv = p->kv;
+    int ps_r, ps_n;
+    if (p->persistent && from_keys && K <= p->graph_steps &&
+        pipe_step_shape(B, p->cfg.dim_in, p->cfg.dim_out, p->n_chunks, &ps_r, &ps_n)) {
+        // One persistent launch processes the K batches; its arguments travel in the launch itself, so there is
+        // neither a graph nor a descriptor kernel: host cost = one launch per K batches.
+        const KvMirrorArgs mirror = kv_mirror_args(kv);  // before this group's ops are reserved
+        DIE_TRY(kv_reserve(kv, (uint64_t)2 * K * B, false, s));
+        DIE_TRY(kv_reserve(kv, (uint64_t)K * B, true, s));
+        d.kv = view_of(kv);
+        d.batch = B;
+        d.trace = trace_buffer();
+        d.tail0 = kv->tail;
+        kv->tail += 2ull * (unsigned long long)K * (unsigned long long)B;
+        StepRef sr;
+        memset(&sr, 0, sizeof(sr));
+        DIE_TRY(pipe_step_launch(sr, &d, K, B, p->n_chunks, p->cfg.dim_in, p->cfg.dim_out, true, n_req_dev,
+                                 p->digests_all, p->W, p->bias, p->arena, p->sgrid, &mirror, s));
+        count_replay();
+        return DIE_OK;
+    }
     cudaGraphExec_t exec;
     DIE_TRY(graph_get(p, from_keys, digests, B, n_req_dev, qd, K, &exec));
     const KvMirrorArgs mirror = kv_mirror_args(kv);  // before this replay's ops are reserved
@@ -682,7 +709,9 @@ die_status_t pipeline_owner_launch(die_pipeline* p, const StepRef& sr, uint32_t*
     return launch_fast(p, sr, false, digests, B_max, n_req_dev, s);
 }
 
-int pipeline_launches_per_step(const die_pipeline* p) { return p->cfg.model == DIE_MODEL_LINEAR_FP32 ? 4 : 3; }
+int pipeline_launches_per_step(const die_pipeline* p) {
+    return p->persistent ? 1 : (p->cfg.model == DIE_MODEL_LINEAR_FP32 ? 4 : 3);
+}
 
 static die_status_t run_general(die_pipeline* p, const uint32_t* digests, int B, const float* payload, double now,
                                 float* out, uint8_t* hit_out, cudaStream_t s) {
@@ -776,6 +805,13 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
     DIE_CUDA(cudaMalloc(&p->qdesc, sizeof(QueueDesc)));
     p->graph_steps = 16;
     if (const char* e = getenv("DIE_GRAPH_STEPS")) p->graph_steps = atoi(e);  // 0: every step launched from the stream
+    int ps_r, ps_n;
+    p->persistent = p->fast && cfg->model == DIE_MODEL_LINEAR_TF32 &&
+                    pipe_step_shape(cfg->max_batch, cfg->dim_in, cfg->dim_out, p->n_chunks, &ps_r, &ps_n);
+    if (p->persistent) {
+        DIE_TRY(pipe_step_grid_alloc(&p->sgrid));
+        if (p->graph_steps > 0) DIE_CUDA(cudaMalloc(&p->digests_all, (size_t)p->graph_steps * B * 16));
+    }
     *out = p;
     return DIE_OK;
 }
@@ -788,6 +824,7 @@ extern "C" die_status_t die_pipeline_destroy(die_pipeline_t* p) {
                     p->d_key_off, p->d_payload, p->d_out, p->d_hit};
     for (void* b : bufs) cudaFree(b);
     cudaFree(p->qdesc);
+    cudaFree(p->sgrid);
     cudaFree(p->digests_all);
     cudaFree(p->g_keys); cudaFree(p->g_off); cudaFree(p->g_pay); cudaFree(p->g_out); cudaFree(p->g_hit);
     for (int g = 0; g < p->n_graphs; ++g) cudaGraphExecDestroy(p->graphs[g].exec);
@@ -808,6 +845,12 @@ extern "C" die_kv_t* die_pipeline_kv(die_pipeline_t* p) { return p ? p->kv : nul
 extern "C" die_status_t die_pipeline_debug_marks_sync(die_pipeline_t* p, uint64_t out[8]) {
     if (!p || !out) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_debug_marks_sync: null argument");
     DIE_CUDA(cudaDeviceSynchronize());
+    if (p->persistent) {  // marks of the last batch of the persistent kernel: [0] start, [1..3] after barriers 1..3
+        unsigned long long t[8];
+        DIE_TRY(pipe_step_marks(p->sgrid, t));
+        for (int i = 0; i < 8; ++i) out[i] = t[i];
+        return DIE_OK;
+    }
     PipeCtrl h;
     DIE_CUDA(cudaMemcpy(&h, p->ctrl, sizeof(h), cudaMemcpyDeviceToHost));
     for (int i = 0; i < 8; ++i) out[i] = h.ts[i];

@@ -19,4 +19,16 @@ die_status_t pipeline_owner_launch(die_pipeline* p, const StepRef& sr, uint32_t*
                                    const uint32_t* n_req_dev, cudaStream_t s);
 int pipeline_launches_per_step(const die_pipeline* p);
 
+// ---- the persistent step kernel (pipe_step.cu) ------------------------------------------------------------
+die_status_t pipe_step_grid_alloc(void** out);
+die_status_t pipe_step_marks(void* grid, unsigned long long out[8]);
+// True (and the launch shape) when batches of up to B requests of a K -> N TF32 linear layer with an n_chunks
+// victim window fit one co-resident grid.
+bool pipe_step_shape(int B, int K, int N, int n_chunks, int* R_out, int* n_req_out);
+// n_steps consecutive batches starting at `sr` in one launch.  qv (optional): the queue descriptor, passed by value
+// in the launch (stream launches); otherwise sr.q is device-resident or null (values in sr.a).
+die_status_t pipe_step_launch(const StepRef& sr, const QueueDesc* qv, int n_steps, int B, int n_chunks, int K, int N,
+                              bool from_keys, const uint32_t* n_req_dev, uint32_t* digests, const float* W,
+                              const float* bias, float* arena, void* grid, const KvMirrorArgs* mirror, cudaStream_t s);
+
 }  // namespace die

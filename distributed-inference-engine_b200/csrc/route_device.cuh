@@ -32,10 +32,12 @@ struct GlobalKeySrc {
 // Hash key i (= blockIdx.x * ROUTE_THREADS + threadIdx.x) of a CSR key batch.  All ROUTE_THREADS threads
 // of the CTA must call this (it contains __syncthreads); `stage` is ROUTE_STAGE_BYTES + 32 bytes of
 // 16-byte aligned shared memory.  Threads with i >= B return an unspecified state.
-__device__ __forceinline__ Md5State cta_hash_keys(const uint8_t* __restrict__ key_bytes,
-                                                  const int64_t* __restrict__ key_off, int B, uint8_t* stage) {
+// cta_hash_keys_at: the same for the ROUTE_THREADS keys starting at k0 (persistent kernels walk the chunks
+// themselves); a chunk that starts past the end (k0 >= B) is a no-op for every thread.
+__device__ __forceinline__ Md5State cta_hash_keys_at(const uint8_t* __restrict__ key_bytes,
+                                                     const int64_t* __restrict__ key_off, int B, int k0, uint8_t* stage) {
     const int tid = threadIdx.x;
-    const int k0 = blockIdx.x * ROUTE_THREADS;
+    k0 = min(k0, B);
     const int k1 = min(B, k0 + ROUTE_THREADS);
     const int64_t b0 = key_off[k0], b1 = key_off[k1];
     const uintptr_t g0 = reinterpret_cast<uintptr_t>(key_bytes) + (uintptr_t)b0;
@@ -61,6 +63,11 @@ __device__ __forceinline__ Md5State cta_hash_keys(const uint8_t* __restrict__ ke
             st = md5_key(GlobalKeySrc{key_bytes + off}, len);
     }
     return st;
+}
+
+__device__ __forceinline__ Md5State cta_hash_keys(const uint8_t* __restrict__ key_bytes,
+                                                  const int64_t* __restrict__ key_off, int B, uint8_t* stage) {
+    return cta_hash_keys_at(key_bytes, key_off, B, (int)blockIdx.x * ROUTE_THREADS, stage);
 }
 
 }  // namespace die

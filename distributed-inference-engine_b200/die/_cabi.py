@@ -85,6 +85,7 @@ SIGNATURES = {
     "die_xchg_step": (c_int32, [P, P, P, c_int32, P, c_double, P, P, P, P]),
     "die_xchg_step_many": (c_int32, [P, c_int32, P, c_int64, P, c_int64, c_int32, P, c_double, c_double, P, P, c_int32, P]),
     "die_xchg_check_sync": (c_int32, [P, P]),
+    "die_xchg_prepare": (c_int32, [P, c_int32]),
     "die_pipeline_run_host": (c_int32, [P, P, P, c_int32, P, c_double, P, P, P]),
     "die_pipeline_run_device_many": (c_int32, [P, c_int32, P, c_int64, P, c_int64, c_int32, P, c_double, c_double, P, P,
                                                c_int32, P]),

@@ -239,13 +239,14 @@ class LoopbackPeerGroup:
     which makes the N > 1 path checkable on a one-GPU box (tests/test_gpu_loopback.py, __graft_entry__.smoke()).
 
     The flag barriers of the ranks wait on one another, so every rank's call of a step must be enqueued before
-    any of them is synchronised, and the ranks' streams must not share a hardware queue: set
-    CUDA_DEVICE_MAX_CONNECTIONS=32 before CUDA is initialised (tests/conftest.py and smoke() do).  Table
+    any of them is synchronised, the ranks' streams must not share a hardware queue (CUDA_DEVICE_MAX_CONNECTIONS=32
+    before CUDA is initialised; tests/conftest.py and smoke() set it) and no kernel may be loaded for the first time
+    while a barrier spins (the constructor runs a world-1 warm-up).  Table
     housekeeping synchronises one rank's streams: call `maintain()` between steps instead of letting a step
     trigger it while its peers' work is not enqueued yet."""
 
     def __init__(self, world: int, kv_max_size: int, max_batch: int, dim: int, weight, bias, default_ttl,
-                 model: str = "linear_tf32"):
+                 model: str = "linear_tf32", _warm: bool = True):
         import ctypes
         from . import _cabi, ops
         from .pipeline import DispatchPipeline
@@ -267,6 +268,18 @@ class LoopbackPeerGroup:
             self._x.append(h.value)
         self.streams = [torch.cuda.Stream() for _ in range(world)]
         torch.cuda.synchronize()
+        if _warm:
+            # CUDA loads a kernel at its first launch, and that load synchronises the context: with a peer's barrier
+            # already spinning on this device it would wait for the barrier's time-out.  A world-1 group (whose
+            # barriers wait for nobody) launches every kernel of the step once, stream-launched and replayed.
+            warm = LoopbackPeerGroup(1, kv_max_size, max_batch, dim, weight, bias, default_ttl, model, _warm=False)
+            kb = self.ops.KeyBatch.from_strings(["warm-%d" % i for i in range(max_batch)])
+            x = torch.zeros((max_batch, dim), dtype=torch.float32, device=self.dev)
+            warm.step([kb], [x], 0.0)
+            n = max(2, warm.pipes[0]._graph_steps())
+            warm.step_many([kb.key_bytes.repeat(n, 1)], [kb.key_off.repeat(n, 1)], [x.repeat(n, 1, 1)], 1.0, 1.0)
+            del warm
+            torch.cuda.synchronize()
 
     def __del__(self):
         for h in getattr(self, "_x", []):
@@ -287,30 +300,32 @@ class LoopbackPeerGroup:
     def step(self, keys, payloads, now: float):
         """keys[r] / payloads[r]: the batch rank r ingests.  -> [(out, hit, shard)] per rank."""
         check, ptr = self._cabi.check, self._cabi.ptr
-        res = []
-        cur = torch.cuda.current_stream()
+        # every allocation first: a cudaMalloc synchronises the device and would wait for a peer's spinning barrier
+        res = [(torch.empty((p.shape[0], self.dim), dtype=torch.float32, device=self.dev),
+                torch.empty(p.shape[0], dtype=torch.uint8, device=self.dev),
+                torch.empty(p.shape[0], dtype=torch.int32, device=self.dev)) for p in payloads]
+        torch.cuda.synchronize()
         for r in range(self.world):
-            B = payloads[r].shape[0]
-            out = torch.empty((B, self.dim), dtype=torch.float32, device=self.dev)
-            hit = torch.empty(B, dtype=torch.uint8, device=self.dev)
-            shard = torch.empty(B, dtype=torch.int32, device=self.dev)
-            self.streams[r].wait_stream(cur)
-            check(self.lib.die_xchg_step(self._x[r], ptr(keys[r].key_bytes), ptr(keys[r].key_off), B, ptr(payloads[r]),
-                                         now, ptr(out), ptr(hit), ptr(shard), self.streams[r].cuda_stream))
-            res.append((out, hit, shard))
+            out, hit, shard = res[r]
+            check(self.lib.die_xchg_step(self._x[r], ptr(keys[r].key_bytes), ptr(keys[r].key_off), payloads[r].shape[0],
+                                         ptr(payloads[r]), now, ptr(out), ptr(hit), ptr(shard), self.streams[r].cuda_stream))
         self._sync_and_check()
         return res
 
     def step_many(self, key_bytes, key_off, payloads, now0: float, now_step: float):
         """key_bytes[r] [n, stride], key_off[r] [n, B+1], payloads[r] [n, B, dim] -> [(out [n,B,dim], hit [n,B])]."""
         check, ptr = self._cabi.check, self._cabi.ptr
+        bufs = []
+        for r in range(self.world):   # allocations and graph instantiation before any rank's barriers are enqueued
+            n, B = payloads[r].shape[0], payloads[r].shape[1]
+            bufs.append((torch.empty((max(n, 2), B, self.dim), dtype=torch.float32, device=self.dev),
+                         torch.empty((max(n, 2), B), dtype=torch.uint8, device=self.dev)))
+            check(self.lib.die_xchg_prepare(self._x[r], B))
+        torch.cuda.synchronize()
         res = []
-        cur = torch.cuda.current_stream()
         for r in range(self.world):
             n, B = payloads[r].shape[0], payloads[r].shape[1]
-            out = torch.empty((max(n, 2), B, self.dim), dtype=torch.float32, device=self.dev)
-            hit = torch.empty((max(n, 2), B), dtype=torch.uint8, device=self.dev)
-            self.streams[r].wait_stream(cur)
+            out, hit = bufs[r]
             check(self.lib.die_xchg_step_many(self._x[r], n, ptr(key_bytes[r]), key_bytes[r].stride(0), ptr(key_off[r]),
                                               key_off[r].stride(0), B, ptr(payloads[r]), now0, now_step, ptr(out), ptr(hit),
                                               out.shape[0], self.streams[r].cuda_stream))

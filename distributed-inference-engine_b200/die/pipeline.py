@@ -44,6 +44,12 @@ class DispatchPipeline:
             self._lib.die_pipeline_destroy(self._h)
             self._h = None
 
+    @staticmethod
+    def _graph_steps() -> int:
+        """Batches per replayed group (environment DIE_GRAPH_STEPS, default 16; 0 = off)."""
+        import os
+        return int(os.environ.get("DIE_GRAPH_STEPS", "16"))
+
     def run_device(self, keys: ops.KeyBatch, payload: torch.Tensor, now: float, out: Optional[torch.Tensor] = None,
                    hit: Optional[torch.Tensor] = None):
         """Inputs resident in HBM -> (out [B, dim_out] fp32, hit uint8 [B]); asynchronous on the current stream."""

@@ -325,6 +325,10 @@ die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, const uint8_t*
                                 double now0, double now_step, float* out, uint8_t* hit_out, int32_t out_ring,
                                 die_stream_t stream);
 die_status_t die_xchg_check_sync(die_xchg_t* x, die_stream_t stream);
+/* No reference counterpart.  Captures and instantiates, without launching, the replay the next
+ * die_xchg_step_many(B, ...) of this context would use: keeps graph instantiation (which may allocate and
+ * synchronise the device) out of the first serving call. */
+die_status_t die_xchg_prepare(die_xchg_t* x, int32_t B);
 
 /* A queue of n flushed batches in one call (each batch is still one pass of the path, applied strictly in
  * order): batch j reads key_bytes + j*key_bytes_stride, key_off + j*key_off_stride (0 = shared offsets),

@@ -7,6 +7,7 @@ import pytest
 # The one-GPU loopback tests of the sharded step run several ranks' streams on one device and their flag barriers
 # wait on each other: give every stream its own hardware queue (must be set before CUDA is initialised).
 os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")  # a kernel's first launch must not wait for a spinning barrier
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG_DIR = os.path.join(ROOT, "distributed-inference-engine_b200")

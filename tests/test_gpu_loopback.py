@@ -62,7 +62,7 @@ def test_loopback_sharded_steps_match_oracle(world, model):
     and across the ranks' batches."""
     from die import ops
     from die.exchange import LoopbackPeerGroup
-    B, D, max_size, ttl, n_ids, steps = 256, 128, 700, 6.0, 2500, 14
+    B, D, max_size, ttl, n_ids, steps = 256, 128, 700, 6.0, 1250 * world, 14
     rng = np.random.default_rng(100 + world)
     w, b, fn = make_model(model, D, rng)
     group = LoopbackPeerGroup(world, max_size, B, D, w, b, ttl, model=model)

@@ -223,7 +223,8 @@ def test_graph_replayed_queue_equals_stream_launched_steps(model):
     launches0, replays0 = a._lib.die_launch_count(), a._lib.die_replay_count()
     a.run_device_many(kd, off, xd, 5.0, 1.5, out, hit)
     torch.cuda.synchronize()
-    assert a._lib.die_launch_count() - launches0 >= 3 * n
+    # echo: three kernels per batch from a replayed graph; linear_tf32: one persistent kernel per group of 16 batches
+    assert a._lib.die_launch_count() - launches0 >= (3 * n if model == "echo" else n // 16 + n % 16)
     assert a._lib.die_replay_count() - replays0 == n // 16
     for j in range(n):
         o, h = b.run_device(ops.KeyBatch(kd[j], off), xd[j], 5.0 + j * 1.5)
