@@ -41,7 +41,8 @@ static_assert(sizeof(Slot) == 64, "slot must be one 64-byte record");
 
 struct KvState {
     // persistent counters
-    unsigned long long size, hits, misses, evictions, head, n_tomb, n_empty_claimed, free_top;
+    unsigned long long size, hits, misses, evictions, head, n_tomb, n_empty_claimed;
+    unsigned long long free_head, free_tail;  // result-row queue: pops at free_head, pushes at free_tail (monotone)
     unsigned long long status, slow_batches, n_dropped_last;
     // per set-batch scratch (reset by the last kernel of each batch)
     unsigned long long n_pre, n_absent, min_prev, n_new, conflict, n_dropped;
@@ -64,6 +65,7 @@ struct KvView {
     uint32_t* log;
     KvState* st;
     uint32_t* free_rows;       // nullptr unless the table manages result rows
+    unsigned long long n_rows; // entries of the free_rows ring
     unsigned long long mask;   // capacity - 1
     unsigned long long rmask;  // ring_cap - 1
     unsigned long long max_size;
@@ -133,13 +135,35 @@ __device__ __forceinline__ void block_sub(unsigned long long* ctr, bool pred) {
     if (threadIdx.x == 0 && n) atomicAdd(ctr, (unsigned long long)(-(long long)n));
 }
 
-// result-row handles (pipeline mode).  A kernel either pushes or pops, never both, except the
-// single-threaded sequential replay.
+// result-row handles (pipeline mode): a ring queue of n_rows entries, popped at free_head, pushed at free_tail.
+// Pushes and pops may run side by side as long as the pops of a phase never outnumber the handles that were free
+// when the phase began (a pop then never reaches an entry whose push is still in flight): the table owns
+// max_batch + 64 more rows than entries, and a phase pops at most one row per request of a batch.
 __device__ __forceinline__ void release_row(const KvView& kv, unsigned long long value) {
-    if (kv.free_rows) kv.free_rows[atomicAdd(&kv.st->free_top, 1ull)] = (uint32_t)value;
+    if (kv.free_rows) kv.free_rows[atomicAdd(&kv.st->free_tail, 1ull) % kv.n_rows] = (uint32_t)value;
 }
 __device__ __forceinline__ unsigned long long acquire_row(const KvView& kv) {
-    return kv.free_rows[atomicAdd(&kv.st->free_top, (unsigned long long)(-1ll)) - 1ull];
+    return kv.free_rows[atomicAdd(&kv.st->free_head, 1ull) % kv.n_rows];
+}
+// The same for a whole warp with one atomic (all 32 lanes call; lanes with !want get 0 / do nothing).
+__device__ __forceinline__ unsigned long long warp_acquire_row(const KvView& kv, bool want) {
+    const unsigned m = __ballot_sync(0xffffffffu, want);
+    if (!m) return 0ull;
+    const int leader = __ffs(m) - 1;
+    unsigned long long base = 0;
+    if ((int)lane_id() == leader) base = atomicAdd(&kv.st->free_head, (unsigned long long)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (!want) return 0ull;
+    return kv.free_rows[(base + __popc(m & ((1u << lane_id()) - 1u))) % kv.n_rows];
+}
+__device__ __forceinline__ void warp_release_row(const KvView& kv, bool have, unsigned long long value) {
+    const unsigned m = __ballot_sync(0xffffffffu, have);
+    if (!m || !kv.free_rows) return;
+    const int leader = __ffs(m) - 1;
+    unsigned long long base = 0;
+    if ((int)lane_id() == leader) base = atomicAdd(&kv.st->free_tail, (unsigned long long)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (have) kv.free_rows[(base + __popc(m & ((1u << lane_id()) - 1u))) % kv.n_rows] = (uint32_t)value;
 }
 // One KVCache.get (kvstore.py:136-164) / __contains__ (:221-228) probe.  Returns the code
 // (1 hit, 0 absent, 2 expired-and-deleted-by-this-op); `deleted` tells the caller to account for it.
@@ -305,6 +329,7 @@ inline KvView view_of(const die_kv* kv) {
     v.log = kv->log;
     v.st = kv->st;
     v.free_rows = kv->free_rows;
+    v.n_rows = kv->n_rows ? kv->n_rows : 1;
     v.mask = kv->capacity - 1;
     v.rmask = kv->ring_cap - 1;
     v.max_size = kv->max_size;

@@ -686,7 +686,8 @@ __global__ void kv_state_init_kernel(KvView kv, unsigned long long head, unsigne
         st->size = 0ull;
         st->head = head;
         st->n_tomb = st->n_empty_claimed = 0ull;
-        st->free_top = n_rows;
+        st->free_head = 0ull;
+        st->free_tail = n_rows;
         st->n_pre = st->n_absent = st->n_new = st->conflict = st->n_dropped = 0ull;
         st->min_prev = ~0ull;
         st->win_mode = st->win_origin = 0ull;
@@ -694,7 +695,7 @@ __global__ void kv_state_init_kernel(KvView kv, unsigned long long head, unsigne
     }
     for (unsigned long long r = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; r < n_rows;
          r += (unsigned long long)gridDim.x * blockDim.x)
-        kv.free_rows[r] = (uint32_t)(n_rows - 1 - r);  // row 0 is popped first
+        kv.free_rows[r] = (uint32_t)r;  // row 0 is popped first
 }
 
 static uint64_t next_pow2(uint64_t x) {
@@ -786,8 +787,8 @@ static die_status_t kv_maintain(die_kv* kv, int force, cudaStream_t s) {
         kv->head_lb = kv->tail;
         kv->tail += kept;
     }
-    // probe chains stay short while used slots (live + tombstones) stay under 3/8 of the capacity
-    if (force || h.size + h.n_tomb + kv->max_chunk > kv->capacity / 8 * 3) {
+    // probe chains stay short while used slots (live + tombstones) stay under half of the capacity
+    if (force || h.size + h.n_tomb + kv->max_chunk > kv->capacity / 2) {
         Slot* fresh = kv->slots_spare;
         if (!fresh) DIE_CUDA(cudaMalloc(&fresh, kv->capacity * sizeof(Slot)));
         DIE_CUDA(cudaMemsetAsync(fresh, 0, kv->capacity * sizeof(Slot), s));
@@ -845,7 +846,7 @@ static void kv_mirror_refresh(die_kv* kv) {
 die_status_t kv_reserve(die_kv* kv, uint64_t n, bool inserts, cudaStream_t s) {
     kv_mirror_refresh(kv);
     bool need = (kv->tail + n - kv->head_lb) > kv->ring_cap - 16;
-    if (inserts && kv->live_at_rebuild + kv->claims_ub + n > kv->capacity / 8 * 3) need = true;
+    if (inserts && kv->live_at_rebuild + kv->claims_ub + n > kv->capacity / 2) need = true;
     if (need) DIE_TRY(kv_maintain(kv, 0, s));
     if ((kv->tail + n - kv->head_lb) > kv->ring_cap - 16) DIE_TRY(kv_maintain(kv, 1, s));
     if (inserts) {
@@ -1161,7 +1162,7 @@ extern "C" die_status_t die_kv_set_batch_noalloc(die_kv_t* kv, const uint32_t* d
     // conservative host-side bounds say it is due, the caller is told to run it where allocation is allowed.
     const uint64_t n = (uint64_t)M;
     if ((kv->tail + n - kv->head_lb) > kv->ring_cap - 16 ||
-        kv->live_at_rebuild + kv->claims_ub + n > kv->capacity / 8 * 3)
+        kv->live_at_rebuild + kv->claims_ub + n > kv->capacity / 2)
         DIE_FAIL(DIE_ERR_NOMEM,
                  "die_kv_set_batch_noalloc: table housekeeping is due and would allocate; call die_kv_maintain_sync "
                  "at a point where allocation is allowed, then retry");

@@ -16,7 +16,7 @@
 //   per batch:  A  probe (kvstore.py:136-164), one request per thread            | window CTAs idle
 //               -- barrier 1: every get of the batch precedes every set (call-stack (E))
 //               B  insert the misses (kvstore.py:104-134) | hit rows -> out | MMA | bitmap of current log records
-//               -- barrier 2: the arriving CTA that completes it fixes E = size - max_size (_evict_if_needed)
+//               -- barrier 2: every insert is in, so E = size - max_size (_evict_if_needed) is known to all
 //               C  GEMM epilogue: out[q], cached row                             | evict the E oldest records
 //               -- barrier 3: the next batch's probes see this batch's evictions (request CTAs arrive before
 //                  their epilogue and wait after it, so the epilogue overlaps the evictions)
@@ -39,15 +39,19 @@ constexpr int PS_MAX_CHUNKS = 64;   // window CTAs
 
 // Device-resident control block of the persistent kernel (one per pipeline, zero-initialised).
 struct StepGrid {
-    unsigned int bar_count;   // arrivals at the current barrier
-    unsigned int bar_gen;     // completed barriers (monotone across launches)
+    unsigned int bar_count;   // arrivals at all barriers so far (monotone: barrier k of a launch completes at
+                              // bar_base + (k+1) * n_cta; nothing is ever reset while CTAs may still be polling)
+    unsigned int bar_base;    // bar_count when the current launch began (written by the previous launch's last act)
     unsigned int abort;       // a barrier timed out: every later barrier falls through, status is raised
-    unsigned int any_dup;     // a key occurs twice among the misses of the current batch
-    unsigned long long e_final;  // evictions the current batch needs (set when barrier 2 completes)
+    unsigned int pad;
+    unsigned long long dup_tag;  // == t_set of the batch in which a key occurred twice among the misses
+    unsigned long long hnew;     // LRU-log position just past the newest victim of the current batch
     unsigned int wcount[PS_MAX_CHUNKS];  // current records per window chunk of the current batch
     // %globaltimer marks of the last batch, CTA 0 (diagnostics): [0] start, [4] probes issued, [1] barrier 1 passed,
     // [5] inserts done, [2] barrier 2 passed, [6] epilogue done, [3] barrier 3 passed
+    // ... and the same marks of every CTA ([7]: request CTAs, accumulators ready / window CTAs, bitmap done)
     unsigned long long ts[8];
+    unsigned long long cta_ts[160][8];
 };
 
 struct StepParams {
@@ -66,6 +70,7 @@ struct StepParams {
     float* arena;               // [n_rows, N] cached result rows
     StepGrid* g;
     KvMirrorArgs mirror;        // m.m != nullptr: snapshot the table counters for the host before the first batch
+    int dbg;                    // diagnostics (DIE_STEP_DEBUG): 1 = barriers only, no work (measures the barriers)
 };
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned int* p) {
@@ -73,39 +78,47 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned int* p) {
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void st_release_u32(unsigned int* p, unsigned v) {
-    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 __device__ __forceinline__ unsigned long long ps_timer() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
 
-// Split grid barrier.  arrive(): the whole CTA has finished what the barrier protects; the thread that completes
-// the barrier runs `leader` (it observes every CTA's writes) before it releases the others.  wait(): returns when
-// the barrier has completed.  `gen` is the CTA's count of barriers passed (uniform across the grid).
-template <typename F>
-__device__ __forceinline__ void grid_arrive(StepGrid* g, unsigned n_cta, unsigned gen, F leader) {
+// Split grid barrier on one monotone counter.  arrive(): the whole CTA has finished what the barrier protects --
+// one release-add by the CTA's last thread (a thread no phase puts on its critical path).  wait(): that thread polls
+// until the count reaches `target`, then releases the CTA.  No thread "completes" the barrier and nothing is reset,
+// so an arrival is visible to the pollers after a single L2 round trip.
+constexpr int PS_BAR_THREAD = PS_THREADS - 1;
+__device__ int g_ps_bar_mode = 1;  // 1: release-add + acquire polls (one fence per side; measured 1.2 us vs 1.7 us per barrier); DIE_STEP_BAR_MODE
+__device__ __forceinline__ void grid_arrive(StepGrid* g) {
     tc::fence_before_thread_sync();
     __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        const unsigned prev = atomicAdd(&g->bar_count, 1u);
-        if (prev == n_cta - 1) {
+    if (threadIdx.x == PS_BAR_THREAD) {
+        if (g_ps_bar_mode == 0) {
+            __threadfence();  // cumulative: everything the CTA wrote before the bar.sync above
+            asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&g->bar_count) : "memory");
+        } else if (g_ps_bar_mode == 1) {
+            asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&g->bar_count) : "memory");
+        } else {
             __threadfence();
-            leader();
-            g->bar_count = 0u;
-            __threadfence();
-            st_release_u32(&g->bar_gen, gen + 1u);
+            asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(&g->bar_count) : "memory");
         }
     }
 }
-__device__ __forceinline__ void grid_wait(StepGrid* g, unsigned gen, KvState* st) {
-    if (threadIdx.x == 0) {
+__device__ __forceinline__ unsigned ld_relaxed_u32(const unsigned int* p) {
+    unsigned v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ int g_ps_poll_ns = 0;  // pause between polls of the barrier counter (tuning knob, DIE_STEP_POLL_NS)
+__device__ __forceinline__ void grid_wait(StepGrid* g, unsigned target, KvState* st) {
+    if (threadIdx.x == PS_BAR_THREAD) {
         const unsigned long long t0 = ps_timer();
         unsigned spins = 0;
-        while ((int)(ld_acquire_u32(&g->bar_gen) - (gen + 1u)) < 0) {
+        const int pause = g_ps_poll_ns;
+        const int mode = g_ps_bar_mode;
+        while ((int)((mode == 1 ? ld_acquire_u32(&g->bar_count) : ld_relaxed_u32(&g->bar_count)) - target) < 0) {
+            if (pause) __nanosleep(pause);
             if ((++spins & 1023u) == 0u) {
                 if (ld_acquire_u32(&g->abort)) break;
                 if (ps_timer() - t0 > 2000000000ull) {  // 2 s: a CTA of the grid is gone; fail loudly, never hang
@@ -115,7 +128,7 @@ __device__ __forceinline__ void grid_wait(StepGrid* g, unsigned gen, KvState* st
                 }
             }
         }
-        __threadfence();
+        if (mode != 1) asm volatile("fence.acq_rel.gpu;" ::: "memory");
     }
     __syncthreads();
     tc::fence_after_thread_sync();
@@ -172,64 +185,99 @@ __device__ __forceinline__ unsigned ps_window_bitmap(const KvView& kv, unsigned 
 }
 
 // Window CTA, phase C: evict the chunk's current records whose rank among all current records of the window is
-// below e (oldest first, kvstore.py:89-91).  The thread that evicts the newest victim settles the counters.
-__device__ __forceinline__ void ps_window_evict(const KvView& kv, const StepGrid* g, int chunk, int n_chunks,
-                                                unsigned long long base, unsigned long long t_set, unsigned long long e,
-                                                const unsigned* s_mask) {
+// below e (oldest first, kvstore.py:89-91).
+//   - a victim whose successor slot is EMPTY becomes EMPTY itself instead of a tombstone: no probe chain can continue
+//     through it (it would stop at the successor anyway) and nobody inserts during this phase; fewer tombstones =
+//     fewer table rebuilds;
+//   - the victim's result row goes back to the free queue at position free_tail + rank: ranks are unique, so the
+//     evictions need no atomic, and the counters (size, evictions, head) are settled by one thread after
+//     barrier 3 (ps_settle_evictions) so that nobody reads them while they change;
+//   - a thread's four records are handled together: their loads are in flight side by side (two round trips in all).
+__device__ __forceinline__ void ps_window_evict(const KvView& kv, StepGrid* g, int chunk, int n_chunks,
+                                                unsigned long long base, unsigned long long tail0, unsigned long long t_set,
+                                                unsigned long long e, const unsigned* s_mask) {
     const int tid = threadIdx.x;
-    if (e == 0) return;
-    unsigned long long before = 0;
-    for (int c = 0; c < chunk; ++c) before += __ldcg(&g->wcount[c]);
-    if (before < e) {
-        constexpr int PER = WCHUNK / PS_THREADS;
+    if (e == 0) return;  // uniform for the grid
+    // tail0 = free_tail as every window CTA read it in phase B (nothing pushes between that read and barrier 3 except
+    // these evictions); the queue's tail moves past them here, before any push of the next batch can happen
+    if (chunk == 0 && tid == 0) kv.st->free_tail = tail0 + e;
+    unsigned long long before = 0, total = 0;
+    for (int c = 0; c < n_chunks; ++c) {
+        const unsigned long long w = __ldcg(&g->wcount[c]);
+        if (c < chunk) before += w;
+        total += w;
+    }
+    constexpr int PER = WCHUNK / PS_THREADS;
+    bool victim[PER];
+    unsigned long long rank[PER];
+    uint32_t sidx[PER];
 #pragma unroll
-        for (int k = 0; k < PER; ++k) {
-            const int rec = k * PS_THREADS + tid;  // record index inside the chunk
-            const int w = rec >> 5, b = rec & 31;
-            const unsigned word = s_mask[w];
-            if (!((word >> b) & 1u)) continue;
-            unsigned long long rank = before + __popc(word & ((1u << b) - 1u));
-            for (int ww = 0; ww < w; ++ww) rank += __popc(s_mask[ww]);
-            if (rank >= e) continue;
-            const unsigned long long pos = base + (unsigned long long)rec;
-            Slot* sl = &kv.slots[kv.log[pos & kv.rmask]];
-            release_row(kv, sl->value);
-            st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});
-            sl->stamp = 0ull;
-            if (rank == e - 1) {  // the newest victim: nobody else touches these counters in this phase
-                KvState* st = kv.st;
-                st->size -= e;
-                st->evictions += e;
-                st->n_tomb += e;
-                st->head = pos + 1;
-            }
+    for (int k = 0; k < PER; ++k) {
+        const int rec = k * PS_THREADS + tid;  // record index inside the chunk
+        const int w = rec >> 5, b = rec & 31;
+        const unsigned word = s_mask[w];
+        victim[k] = before < e && ((word >> b) & 1u);
+        rank[k] = 0;
+        if (victim[k]) {
+            rank[k] = before + __popc(word & ((1u << b) - 1u));
+            for (int ww = 0; ww < w; ++ww) rank[k] += __popc(s_mask[ww]);
+            victim[k] = rank[k] < e;
+        }
+        sidx[k] = victim[k] ? __ldcg(&kv.log[(base + (unsigned long long)rec) & kv.rmask]) : 0u;
+    }
+    unsigned long long row[PER];
+    u128 next[PER];
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+        if (victim[k]) {
+            row[k] = ld_u64_cg(&kv.slots[sidx[k]].value);
+            next[k] = ld_fp(&kv.slots[((unsigned long long)sidx[k] + 1ull) & kv.mask]);
         }
     }
+    unsigned n_tomb = 0;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+        if (!victim[k]) continue;
+        Slot* sl = &kv.slots[sidx[k]];
+        const bool tomb = !fp_empty(next[k]);
+        st128(sl, tomb ? u128{FP_TOMB_WORD, FP_TOMB_WORD} : u128{0ull, 0ull});
+        sl->stamp = 0ull;
+        n_tomb += tomb;
+        if (kv.free_rows) kv.free_rows[(tail0 + rank[k]) % kv.n_rows] = (uint32_t)row[k];
+        if (rank[k] == e - 1) g->hnew = base + (unsigned long long)(k * PS_THREADS + tid) + 1;  // the newest victim
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n_tomb += __shfl_xor_sync(0xffffffffu, n_tomb, o);
+    if ((tid & 31) == 0 && n_tomb) atomicAdd(&kv.st->n_tomb, (unsigned long long)n_tomb);
     // window too short for this log (fewer than e current records in it): finish the walk sequentially, exactly
-    if (chunk == 0 && tid == 0) {
-        unsigned long long total = 0;
-        for (int c = 0; c < n_chunks; ++c) total += __ldcg(&g->wcount[c]);
-        if (total < e) {
-            unsigned long long p = base + (unsigned long long)n_chunks * WCHUNK, left = e - total;
-            while (left > 0 && p < t_set) {
-                const uint32_t sidx = kv.log[p & kv.rmask];
-                if ((unsigned long long)sidx <= kv.mask && ld_u64_cg(&kv.slots[sidx].stamp) == p) {
-                    Slot* sl = &kv.slots[sidx];
-                    release_row(kv, sl->value);
-                    st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});
-                    sl->stamp = 0ull;
-                    --left;
-                }
-                ++p;
+    if (chunk == 0 && tid == 0 && total < e) {
+        unsigned long long p = base + (unsigned long long)n_chunks * WCHUNK, r = total;
+        while (r < e && p < t_set) {
+            const uint32_t si = kv.log[p & kv.rmask];
+            if ((unsigned long long)si <= kv.mask && ld_u64_cg(&kv.slots[si].stamp) == p) {
+                Slot* sl = &kv.slots[si];
+                const unsigned long long v = ld_u64_cg(&sl->value);
+                const bool tomb = !fp_empty(ld_fp(&kv.slots[((unsigned long long)si + 1ull) & kv.mask]));
+                st128(sl, tomb ? u128{FP_TOMB_WORD, FP_TOMB_WORD} : u128{0ull, 0ull});
+                sl->stamp = 0ull;
+                if (tomb) atomicAdd(&kv.st->n_tomb, 1ull);
+                if (kv.free_rows) kv.free_rows[(tail0 + r) % kv.n_rows] = (uint32_t)v;
+                ++r;
             }
-            KvState* st = kv.st;
-            if (left > 0) st->status = DIE_ERR_INVALID;  // unreachable while max_batch <= max_size
-            st->size -= e;
-            st->evictions += e;
-            st->n_tomb += e;
-            st->head = p;
+            ++p;
         }
+        if (r < e) kv.st->status = DIE_ERR_INVALID;  // unreachable while max_batch <= max_size
+        g->hnew = p;
     }
+}
+
+// After barrier 3, one thread: the batch's evictions leave the counters (kvstore.py:87-93).
+__device__ __forceinline__ void ps_settle_evictions(const KvView& kv, const StepGrid* g, unsigned long long e) {
+    if (e == 0) return;
+    KvState* st = kv.st;
+    atomicAdd(&st->size, (unsigned long long)(-(long long)e));  // atomic: the next batch's probes may delete expired entries
+    st->evictions += e;
+    st->head = ld_u64_cg(&g->hnew);
 }
 
 __device__ __forceinline__ void warp_count_add(unsigned long long* ctr, bool pred, bool negative = false) {
@@ -258,7 +306,7 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
     const int chunk = cta - P.n_req;
     const unsigned n_cta = gridDim.x;
     StepGrid* g = P.g;
-    unsigned gen = ld_acquire_u32(&g->bar_gen);
+    unsigned target = ld_acquire_u32(&g->bar_base);  // barrier k of this launch completes at bar_base + (k+1) * n_cta
     const int K = P.K, N = P.N, R = P.R;
     const int KB = K / 32;
     const int vout = N / 4;
@@ -294,9 +342,9 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
             if (i < P.B) P.digests[(size_t)s * P.B + i] = make_uint4(h.a, h.b, h.c, h.d);
             __syncthreads();  // the staging buffer is reused by the next chunk
         }
-        grid_arrive(g, n_cta, gen, [] {});
-        grid_wait(g, gen, st);
-        ++gen;
+        grid_arrive(g);
+        target += n_cta;
+        grid_wait(g, target, st);
     }
     if (is_req) {
         const int chunks_per_row = K / 4;
@@ -309,7 +357,16 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
         ps_load_tile(a_base0, a_first.payload, cta * R, nq0, K);
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
+#define PS_MARK(i)                                             \
+    do {                                                       \
+        if (tid == 0) {                                        \
+            const unsigned long long t__ = ps_timer();         \
+            if (cta < 160) g->cta_ts[cta][i] = t__;            \
+            if (cta == 0) g->ts[i] = t__;                      \
+        }                                                      \
+    } while (0)
     unsigned mma_phase = 0;
+    int spare_row = -1;  // a row popped for a miss whose key another op of the batch inserted: pushed back in the next phase A
 
     for (int s = 0; s < P.n_steps; ++s) {
         StepRef r = sr;
@@ -318,16 +375,17 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
         int Bs = P.B;
         if (P.n_req_dev) Bs = min(Bs, (int)__ldcg(P.n_req_dev));
         const int q0 = cta * R;
-        const int nq = is_req ? max(0, min(R, Bs - q0)) : 0;
+        const int nq = is_req && !(P.dbg & 1) ? max(0, min(R, Bs - q0)) : 0;
         uint8_t* a_cur = a_base0 + (size_t)(s & 1) * a_bytes;
         const uint4* dig = P.digests + (size_t)s * P.B;
         u128 key{0ull, 0ull};
         int code = 3;  // 3 = no request in this row
-        if (cta == 0 && tid == 0) g->ts[0] = ps_timer();
+        int my_row = -1;  // result row popped for this thread's miss
+        PS_MARK(0);
 
         // ================= phase A: probe =================
         if (is_req) {
-            if (s + 1 < P.n_steps) {  // PACK of the next batch: its rows travel while this batch is processed
+            if (s + 1 < P.n_steps && !(P.dbg & 1)) {  // PACK of the next batch: its rows travel while this batch is processed
                 StepRef r2 = sr;
                 r2.i += s + 1;
                 ps_load_tile(a_base0 + (size_t)((s + 1) & 1) * a_bytes, step_resolve(r2).payload, q0,
@@ -336,6 +394,8 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
             asm volatile("cp.async.commit_group;" ::: "memory");
             if (tid < R) {
                 const bool active = tid < nq;
+                warp_release_row(kv, spare_row >= 0, (unsigned long long)spare_row);  // phase A: atomic pushes and pops only
+                spare_row = -1;
                 if (active) {
                     const int q = q0 + tid;
                     key = fp_of(__ldcg(dig + q));
@@ -346,6 +406,9 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
                     s_value[tid] = value;
                 }
                 s_code[tid] = (uint8_t)code;
+                // a miss will be inserted in phase B: its result row is popped now, off that phase's chain (the
+                // queue holds max_batch + 64 handles more than the table has entries, see release_row)
+                my_row = (int)warp_acquire_row(kv, active && code != 1);
                 warp_count_add(&st->hit_part[cta & 15][0], active && code == 1);
                 warp_count_add(&st->miss_part[cta & 15][0], active && code != 1);
                 const bool deleted = active && code == 2;  // expired: this op deleted the entry (kvstore.py:153-156)
@@ -354,17 +417,17 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
                     warp_count_add(&st->n_tomb, deleted);
                 }
             }
-            if (cta == 0 && tid == 0) g->ts[4] = ps_timer();
+            PS_MARK(4);
             asm volatile("cp.async.wait_group 1;" ::: "memory");  // this batch's tile (and W) have landed
             tc::fence_proxy_async_smem();
         }
-        grid_arrive(g, n_cta, gen, [] {});
-        grid_wait(g, gen, st);
-        ++gen;
-        if (cta == 0 && tid == 0) g->ts[1] = ps_timer();
+        grid_arrive(g);
+        target += n_cta;
+        grid_wait(g, target, st);
+        PS_MARK(1);
 
         // ================= phase B: insert the misses | hit rows | MMA | victim bitmap =================
-        unsigned long long wbase = 0;
+        unsigned long long wbase = 0, wtail = 0;
         if (is_req) {
             if (tid == 4 * 32 && nq > 0) {  // INFER: one thread issues the tile's MMAs, accumulators in TMEM
                 const uint32_t idesc = tc::instr_desc(tc::FMT_TF32, PS_M, (uint32_t)N);
@@ -390,19 +453,20 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
                     atomicMax(&sl->stamp, stamp);
                     int row = -1;
                     if (claimed) {
-                        row = (int)acquire_row(kv);
+                        row = my_row;
                         sl->value = (unsigned long long)row;
                         sl->created_at = a.now;
                         sl->ttl = kv.default_ttl;
                         sl->last_accessed = a.now;
                         sl->access_count = 0u;
                     } else {
-                        g->any_dup = 1u;  // same key twice among the misses: the later op owns the cached row
+                        g->dup_tag = a.t_set;  // same key twice among the misses: the later op owns the cached row
                     }
                     kv.log[stamp & kv.rmask] = (uint32_t)sidx;
                     s_slot[tid] = (int)sidx;
                     s_row[tid] = row;
                 }
+                if (miss && !claimed) spare_row = my_row;  // a duplicate's spare row goes back in the next phase A
                 warp_count_add(&st->size, miss && claimed);
                 warp_count_add(&st->n_empty_claimed, miss && claimed && from_empty);
                 warp_count_add(&st->n_tomb, miss && claimed && !from_empty, true);
@@ -417,25 +481,27 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
                         stg_stream(out + (long long)(q0 + t) * vout + c, ldg_stream(arena + row * vout + c));
                 }
             }
-        } else {
+        } else if (!(P.dbg & 1)) {
             wbase = ld_u64_cg(&st->head) + (unsigned long long)chunk * WCHUNK;
+            wtail = ld_u64_cg(&st->free_tail);  // stable from barrier 1 to barrier 3 but for the evictions themselves
             const unsigned cnt = ps_window_bitmap(kv, wbase, a.t_set, s_mask, &s_cnt);
             if (tid == 0) g->wcount[chunk] = cnt;
+            PS_MARK(7);
         }
-        if (cta == 0 && tid == 0) g->ts[5] = ps_timer();
-        grid_arrive(g, n_cta, gen, [&] {  // every insert is in: _evict_if_needed's count for the whole batch
-            const unsigned long long size = ld_u64_cg(&st->size);
-            g->e_final = size > kv.max_size ? size - kv.max_size : 0ull;
-        });
-        grid_wait(g, gen, st);
-        ++gen;
-        if (cta == 0 && tid == 0) g->ts[2] = ps_timer();
+        PS_MARK(5);
+        grid_arrive(g);
+        target += n_cta;
+        grid_wait(g, target, st);
+        PS_MARK(2);
 
         // ================= phase C: epilogue (UNPACK) | evictions =================
         if (is_req) {
-            const bool any_dup = __ldcg(&g->any_dup) != 0u;  // read before arriving: barrier 3 resets it
-            grid_arrive(g, n_cta, gen, [&] { g->any_dup = 0u; });  // nothing barrier 3 protects is written below
-            if (nq > 0) {
+            const bool any_dup = ld_u64_cg(&g->dup_tag) == a.t_set;
+            grid_arrive(g);  // barrier 3 protects the evictions: nothing it orders is written below
+            target += n_cta;
+            // warp 7 carries the barrier thread (its release fence waits for the CTA's outstanding writes): the epilogue
+            // runs on warps 0-6 and synchronises among them only
+            if (nq > 0 && warp < 7) {
                 if (tid < nq && s_code[tid] != 1) {  // which cached row this op's result goes to (-1: none)
                     int row = s_row[tid];
                     if (any_dup) {  // only the last op on a slot (largest stamp) owns its value
@@ -447,6 +513,7 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
                 tc::mbar_wait(&s_bar, mma_phase & 1u);
                 ++mma_phase;
                 tc::fence_after_thread_sync();
+                PS_MARK(7);
                 float* stage = reinterpret_cast<float*>(a_cur);  // the MMAs have consumed the tile
                 const int pitch = N + 4;
                 if (warp < 4 && warp * 32 < nq) {
@@ -468,10 +535,10 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
                     }
                 }
                 tc::fence_before_thread_sync();
-                __syncthreads();
+                asm volatile("bar.sync 1, 224;" ::: "memory");
                 int4* out = reinterpret_cast<int4*>(a.out);
                 int4* arena = reinterpret_cast<int4*>(P.arena);
-                for (int e = tid; e < nq * vout; e += PS_THREADS) {
+                for (int e = tid; e < nq * vout; e += PS_THREADS - 32) {
                     const int rr = e / vout, c = e - rr * vout;
                     if (s_code[rr] == 1) continue;
                     const int4 o = *reinterpret_cast<const int4*>(stage + (size_t)rr * pitch + c * 4);
@@ -480,18 +547,23 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
                     if (row >= 0) stg_stream(arena + (long long)row * vout + c, o);
                 }
             }
-            if (cta == 0 && tid == 0) g->ts[6] = ps_timer();
-            grid_wait(g, gen, st);
-            ++gen;
+            PS_MARK(6);
+            grid_wait(g, target, st);
         } else {
-            const unsigned long long e = ld_u64_cg(&g->e_final);
-            ps_window_evict(kv, g, chunk, P.n_chunks, wbase, a.t_set, e, s_mask);
-            grid_arrive(g, n_cta, gen, [&] { g->any_dup = 0u; });
-            grid_wait(g, gen, st);
-            ++gen;
+            // every insert is in: _evict_if_needed's count for the whole batch (size is not written in this phase)
+            const unsigned long long size = ld_u64_cg(&st->size);
+            const unsigned long long e = size > kv.max_size && !(P.dbg & 1) ? size - kv.max_size : 0ull;
+            ps_window_evict(kv, g, chunk, P.n_chunks, wbase, wtail, a.t_set, e, s_mask);
+            grid_arrive(g);
+            target += n_cta;
+            grid_wait(g, target, st);
+            if (chunk == 0 && tid == 0) ps_settle_evictions(kv, g, e);  // before this CTA arrives at the next barrier
         }
-        if (cta == 0 && tid == 0) g->ts[3] = ps_timer();
+        PS_MARK(3);
     }
+    if (is_req && tid < R) warp_release_row(kv, spare_row >= 0, (unsigned long long)spare_row);
+    // every CTA has passed the last barrier once CTA 0 has: the next launch starts counting from here
+    if (cta == 0 && tid == PS_BAR_THREAD) g->bar_base = target;
     if (is_req && warp == 0) {
         tc::fence_after_thread_sync();
         tc::tmem_dealloc(s_tmem, ncols);
@@ -510,9 +582,13 @@ die_status_t pipe_step_grid_alloc(void** out) {
 }
 
 die_status_t pipe_step_marks(void* grid, unsigned long long out[8]) {
-    StepGrid h;
-    DIE_CUDA(cudaMemcpy(&h, grid, sizeof(h), cudaMemcpyDeviceToHost));
-    for (int i = 0; i < 8; ++i) out[i] = h.ts[i];
+    DIE_CUDA(cudaMemcpy(out, &static_cast<StepGrid*>(grid)->ts[0], 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    return DIE_OK;
+}
+die_status_t pipe_step_cta_marks(void* grid, int n_cta, unsigned long long* out) {
+    if (n_cta > 160) n_cta = 160;
+    DIE_CUDA(cudaMemcpy(out, &static_cast<StepGrid*>(grid)->cta_ts[0][0], (size_t)n_cta * 8 * sizeof(unsigned long long),
+                        cudaMemcpyDeviceToHost));
     return DIE_OK;
 }
 
@@ -572,6 +648,19 @@ die_status_t pipe_step_launch(const StepRef& sr, const QueueDesc* qv, int n_step
     P.arena = arena;
     P.g = static_cast<StepGrid*>(grid);
     if (mirror) P.mirror = *mirror;
+    static int dbg = -1;
+    if (dbg < 0) {
+        dbg = getenv("DIE_STEP_DEBUG") ? atoi(getenv("DIE_STEP_DEBUG")) : 0;
+        if (const char* e = getenv("DIE_STEP_POLL_NS")) {
+            const int ns = atoi(e);
+            cudaMemcpyToSymbol(g_ps_poll_ns, &ns, sizeof(ns));
+        }
+        if (const char* e = getenv("DIE_STEP_BAR_MODE")) {
+            const int m = atoi(e);
+            cudaMemcpyToSymbol(g_ps_bar_mode, &m, sizeof(m));
+        }
+    }
+    P.dbg = dbg;
     QueueDesc q;
     memset(&q, 0, sizeof(q));
     if (qv) q = *qv;

@@ -755,7 +755,7 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
     p->cfg.bias = nullptr;
     const uint64_t B = (uint64_t)cfg->max_batch;
     p->fast = B <= cfg->kv_max_size;
-    p->n_rows = cfg->kv_max_size + B + 64;
+    p->n_rows = cfg->kv_max_size + 2 * B + 64;  // spare rows: see release_row (kv_internal.cuh) and pipe_step.cu
     DIE_TRY(kv_create_impl(cfg->kv_max_size, cfg->default_ttl, p->n_rows, B, &p->kv));
     if ((uint64_t)cfg->max_batch > p->kv->max_chunk)
         DIE_FAIL(DIE_ERR_TOO_LARGE, "die_pipeline_create: max_batch %d exceeds the table's batch limit %llu",
@@ -855,6 +855,13 @@ extern "C" die_status_t die_pipeline_debug_marks_sync(die_pipeline_t* p, uint64_
     DIE_CUDA(cudaMemcpy(&h, p->ctrl, sizeof(h), cudaMemcpyDeviceToHost));
     for (int i = 0; i < 8; ++i) out[i] = h.ts[i];
     return DIE_OK;
+}
+
+extern "C" die_status_t die_pipeline_debug_cta_marks_sync(die_pipeline_t* p, int32_t n_cta, uint64_t* out) {
+    if (!p || !out || n_cta < 1) DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_debug_cta_marks_sync: bad arguments");
+    if (!p->persistent) DIE_FAIL(DIE_ERR_UNSUPPORTED, "die_pipeline_debug_cta_marks_sync: this pipeline does not use the persistent step kernel");
+    DIE_CUDA(cudaDeviceSynchronize());
+    return pipe_step_cta_marks(p->sgrid, n_cta, reinterpret_cast<unsigned long long*>(out));
 }
 
 extern "C" die_status_t die_pipeline_run_owner_device(die_pipeline_t* p, const uint32_t* digests, int32_t B,

@@ -22,6 +22,7 @@ int pipeline_launches_per_step(const die_pipeline* p);
 // ---- the persistent step kernel (pipe_step.cu) ------------------------------------------------------------
 die_status_t pipe_step_grid_alloc(void** out);
 die_status_t pipe_step_marks(void* grid, unsigned long long out[8]);
+die_status_t pipe_step_cta_marks(void* grid, int n_cta, unsigned long long* out);
 // True (and the launch shape) when batches of up to B requests of a K -> N TF32 linear layer with an n_chunks
 // victim window fit one co-resident grid.
 bool pipe_step_shape(int B, int K, int N, int n_chunks, int* R_out, int* n_req_out);

@@ -72,6 +72,7 @@ SIGNATURES = {
     "die_pipeline_destroy": (c_int32, [P]),
     "die_pipeline_kv": (c_void_p, [P]),
     "die_pipeline_debug_marks_sync": (c_int32, [P, POINTER(c_uint64)]),
+    "die_pipeline_debug_cta_marks_sync": (c_int32, [P, c_int32, POINTER(c_uint64)]),
     "die_pipeline_run_device": (c_int32, [P, P, P, c_int32, P, c_double, P, P, P, P]),
     "die_pipeline_run_owner_device": (c_int32, [P, P, c_int32, P, c_double, P, P, P]),
     "die_pipeline_run_owner_device_n": (c_int32, [P, P, c_int32, P, P, c_double, P, P, P]),

@@ -256,6 +256,11 @@ die_kv_t* die_pipeline_kv(die_pipeline_t* p);
 /* Diagnostics (no reference counterpart): %globaltimer marks (ns) written by the last fused get kernel:
  * [0] start, [1] keys hashed, [2] all probes done, [3] misses ranked, [4] victim window done, [5] victims found. */
 die_status_t die_pipeline_debug_marks_sync(die_pipeline_t* p, uint64_t out[8] /*[host]*/);
+/* Diagnostics of the persistent step kernel (no reference counterpart): the same marks of the last batch for the first
+ * n_cta (<= 160) CTAs of its grid, out[n_cta][8]: [0] batch start, [4] probes issued, [1] barrier 1 passed, [5] inserts
+ * done, [7] accumulators ready (request CTAs) / victim bitmap done (window CTAs), [2] barrier 2 passed, [6] epilogue
+ * done, [3] barrier 3 passed. */
+die_status_t die_pipeline_debug_cta_marks_sync(die_pipeline_t* p, int32_t n_cta, uint64_t* out /*[host]*/);
 /* Inputs already resident in HBM.  payload [B, dim_in] fp32; out [B, dim_out] fp32;
  * hit_out [B] uint8 (1 = served from the cache); digest_out optional [B,4]. */
 die_status_t die_pipeline_run_device(die_pipeline_t* p, const uint8_t* key_bytes, const int64_t* key_off,

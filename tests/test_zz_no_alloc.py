@@ -83,11 +83,15 @@ def test_noalloc_set_matches_regular_set_on_two_calls_in_a_row():
         ps, ss = port.stats(), sut.stats()
         assert (ss["size"], ss["evictions"]) == (ps["size"], ps["evictions"])
         # and the filled table answers like its twin
-        probe = md5_words(["na%d" % i for i in rng.integers(0, space, 300)])
+        probe_keys = ["na%d" % i for i in rng.integers(0, space, 300)]
+        probe = md5_words(probe_keys)
         now += 0.5
         hit_a, val_a = ref.get_batch(probe, now)
         hit_b, val_b = sut.get_batch(probe, now)
         assert torch.equal(hit_a, hit_b) and torch.equal(val_a, val_b)
+        clock[0] = now
+        want = [port.get(k, None) for k in probe_keys]   # the gets move their hits to the MRU end in the oracle too
+        assert [v if h == 1 else None for h, v in zip(hit_b.tolist(), val_b.tolist())] == want
 
 
 def test_noalloc_set_rejects_batches_beyond_its_fixed_scratch():
@@ -137,5 +141,5 @@ def test_noalloc_sets_interleaved_with_replayed_pipeline_steps_keep_the_host_bou
                 rc, _, _ = call_set(lib, "die_kv_set_batch_noalloc", pipe.kv, dig, None, None, now)
             assert rc == 0, lib.die_last_error()
         st = pipe.kv.stats()
-        assert st["size"] + st["tombstones"] <= st["capacity"] * 3 // 8, (rnd, st)  # the load limit the bounds protect
+        assert st["size"] + st["tombstones"] <= st["capacity"] // 2, (rnd, st)  # the load limit the bounds protect
     assert pipe.kv.sync_status()[0] == 0 and pipe.kv.stats()["size"] == kv_max

@@ -37,4 +37,15 @@ for rep in range(6):
     us = lambda a, b_: (m[b_] - m[a]) / 1e3
     print("%.2f us/batch | last batch: probe issue %.2f  wait B1 %.2f | insert %.2f  wait B2 %.2f | epilogue %.2f  wait B3 %.2f | total %.2f" % (
         1e3 * e0.elapsed_time(e1) / 128, us(0, 4), us(4, 1), us(1, 5), us(5, 2), us(2, 6), us(6, 3), us(0, 3)))
+NC = 144
+cm = (ctypes.c_uint64 * (NC * 8))()
+lib.die_pipeline_debug_cta_marks_sync(pipe._h, NC, cm)
+t = np.array(list(cm), dtype=np.float64).reshape(NC, 8)
+t0 = t[:, 0].min()
+names = {0: "start", 4: "probes issued", 1: "B1 passed", 5: "inserts done", 7: "acc ready / bitmap", 2: "B2 passed", 6: "epilogue done", 3: "B3 passed"}
+for role, sl in (("request CTAs", slice(0, 128)), ("window CTAs", slice(128, 144))):
+    print(role)
+    for i in (0, 4, 1, 5, 7, 2, 6, 3):
+        v = (t[sl, i] - t0) / 1e3
+        print("  %-20s min %6.2f  med %6.2f  max %6.2f us" % (names[i], v.min(), np.median(v), v.max()))
 print(pipe.kv.stats())
