@@ -65,7 +65,7 @@ struct KvView {
     uint32_t* log;
     KvState* st;
     uint32_t* free_rows;       // nullptr unless the table manages result rows
-    unsigned long long n_rows; // entries of the free_rows ring
+    unsigned long long row_mask; // free_rows ring size - 1 (a power of two >= the number of rows)
     unsigned long long mask;   // capacity - 1
     unsigned long long rmask;  // ring_cap - 1
     unsigned long long max_size;
@@ -135,15 +135,15 @@ __device__ __forceinline__ void block_sub(unsigned long long* ctr, bool pred) {
     if (threadIdx.x == 0 && n) atomicAdd(ctr, (unsigned long long)(-(long long)n));
 }
 
-// result-row handles (pipeline mode): a ring queue of n_rows entries, popped at free_head, pushed at free_tail.
+// result-row handles (pipeline mode): a power-of-two ring queue, popped at free_head, pushed at free_tail.
 // Pushes and pops may run side by side as long as the pops of a phase never outnumber the handles that were free
 // when the phase began (a pop then never reaches an entry whose push is still in flight): the table owns
 // max_batch + 64 more rows than entries, and a phase pops at most one row per request of a batch.
 __device__ __forceinline__ void release_row(const KvView& kv, unsigned long long value) {
-    if (kv.free_rows) kv.free_rows[atomicAdd(&kv.st->free_tail, 1ull) % kv.n_rows] = (uint32_t)value;
+    if (kv.free_rows) kv.free_rows[atomicAdd(&kv.st->free_tail, 1ull) & kv.row_mask] = (uint32_t)value;
 }
 __device__ __forceinline__ unsigned long long acquire_row(const KvView& kv) {
-    return kv.free_rows[atomicAdd(&kv.st->free_head, 1ull) % kv.n_rows];
+    return kv.free_rows[atomicAdd(&kv.st->free_head, 1ull) & kv.row_mask];
 }
 // The same for a whole warp with one atomic (all 32 lanes call; lanes with !want get 0 / do nothing).
 __device__ __forceinline__ unsigned long long warp_acquire_row(const KvView& kv, bool want) {
@@ -154,7 +154,7 @@ __device__ __forceinline__ unsigned long long warp_acquire_row(const KvView& kv,
     if ((int)lane_id() == leader) base = atomicAdd(&kv.st->free_head, (unsigned long long)__popc(m));
     base = __shfl_sync(0xffffffffu, base, leader);
     if (!want) return 0ull;
-    return kv.free_rows[(base + __popc(m & ((1u << lane_id()) - 1u))) % kv.n_rows];
+    return kv.free_rows[(base + __popc(m & ((1u << lane_id()) - 1u))) & kv.row_mask];
 }
 __device__ __forceinline__ void warp_release_row(const KvView& kv, bool have, unsigned long long value) {
     const unsigned m = __ballot_sync(0xffffffffu, have);
@@ -163,7 +163,7 @@ __device__ __forceinline__ void warp_release_row(const KvView& kv, bool have, un
     unsigned long long base = 0;
     if ((int)lane_id() == leader) base = atomicAdd(&kv.st->free_tail, (unsigned long long)__popc(m));
     base = __shfl_sync(0xffffffffu, base, leader);
-    if (have) kv.free_rows[(base + __popc(m & ((1u << lane_id()) - 1u))) % kv.n_rows] = (uint32_t)value;
+    if (have) kv.free_rows[(base + __popc(m & ((1u << lane_id()) - 1u))) & kv.row_mask] = (uint32_t)value;
 }
 // One KVCache.get (kvstore.py:136-164) / __contains__ (:221-228) probe.  Returns the code
 // (1 hit, 0 absent, 2 expired-and-deleted-by-this-op); `deleted` tells the caller to account for it.
@@ -185,13 +185,14 @@ __device__ __forceinline__ SlotLine ld_slot_line(const Slot* s) {
 // One KVCache.get (kvstore.py:136-164) / __contains__ (:221-228) probe.  Returns the code
 // (1 hit, 0 absent, 2 expired-and-deleted-by-this-op).
 constexpr int PROBE_AHEAD = 4;
+// kv_get_one_from: the same with the key's home slot (key.lo & mask) already fetched by the caller as `l`, so that
+// the caller can overlap that round trip with other work.
 template <bool CONTAINS>
-__device__ __forceinline__ int kv_get_one(const KvView& kv, u128 key, double now, unsigned long long stamp,
-                                          unsigned long long& value, long long& slot) {
+__device__ __forceinline__ int kv_get_one_from(const KvView& kv, u128 key, SlotLine l, double now, unsigned long long stamp,
+                                               unsigned long long& value, long long& slot) {
     value = 0;
     slot = -1;
     unsigned long long cur = key.lo & kv.mask;
-    SlotLine l = ld_slot_line(&kv.slots[cur]);
     bool found = fp_eq(l.fp, key);
     if (!found && !fp_empty(l.fp)) {
         // The home slot is somebody else's: walk the chain PROBE_AHEAD slots per round trip (their fingerprints
@@ -240,6 +241,12 @@ __device__ __forceinline__ int kv_get_one(const KvView& kv, u128 key, double now
         sl->last_accessed = now;
     }
     return 1;
+}
+
+template <bool CONTAINS>
+__device__ __forceinline__ int kv_get_one(const KvView& kv, u128 key, double now, unsigned long long stamp,
+                                          unsigned long long& value, long long& slot) {
+    return kv_get_one_from<CONTAINS>(kv, key, ld_slot_line(&kv.slots[key.lo & kv.mask]), now, stamp, value, slot);
 }
 
 // Insert of a key that is known not to live in the table before this batch: claim the first free
@@ -304,6 +311,7 @@ struct die_kv {
     die::KvState* st;
     uint32_t* free_rows;  // pipeline mode only
     uint64_t n_rows;
+    uint64_t row_ring;    // size of the free_rows ring (power of two >= n_rows)
     uint64_t tail;        // next LRU stamp to hand out (host-tracked: every batch op consumes one)
     uint64_t head_lb;     // host lower bound of the device-side head
     uint64_t claims_ub;   // upper bound of EMPTY slots consumed since the last rebuild
@@ -329,7 +337,7 @@ inline KvView view_of(const die_kv* kv) {
     v.log = kv->log;
     v.st = kv->st;
     v.free_rows = kv->free_rows;
-    v.n_rows = kv->n_rows ? kv->n_rows : 1;
+    v.row_mask = kv->row_ring ? kv->row_ring - 1 : 0;
     v.mask = kv->capacity - 1;
     v.rmask = kv->ring_cap - 1;
     v.max_size = kv->max_size;

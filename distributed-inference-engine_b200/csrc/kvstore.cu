@@ -724,7 +724,8 @@ die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_ro
     DIE_CUDA(cudaMalloc(&kv->slots, kv->capacity * sizeof(Slot)));
     DIE_CUDA(cudaMalloc(&kv->log, kv->ring_cap * sizeof(uint32_t)));
     DIE_CUDA(cudaMalloc(&kv->st, sizeof(KvState)));
-    if (n_rows) DIE_CUDA(cudaMalloc(&kv->free_rows, n_rows * sizeof(uint32_t)));
+    kv->row_ring = n_rows ? next_pow2(n_rows) : 0;
+    if (n_rows) DIE_CUDA(cudaMalloc(&kv->free_rows, kv->row_ring * sizeof(uint32_t)));
     DIE_CUDA(cudaMemset(kv->slots, 0, kv->capacity * sizeof(Slot)));
     DIE_CUDA(cudaMemset(kv->log, 0xff, kv->ring_cap * sizeof(uint32_t)));
     DIE_CUDA(cudaMemset(kv->st, 0, sizeof(KvState)));

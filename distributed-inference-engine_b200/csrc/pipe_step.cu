@@ -70,7 +70,8 @@ struct StepParams {
     float* arena;               // [n_rows, N] cached result rows
     StepGrid* g;
     KvMirrorArgs mirror;        // m.m != nullptr: snapshot the table counters for the host before the first batch
-    int dbg;                    // diagnostics (DIE_STEP_DEBUG): 1 = barriers only, no work (measures the barriers)
+    int dbg;                    // diagnostics (DIE_STEP_DEBUG): 1 = barriers only, no work; 2 = no L2 prefetch of the next
+                                // batch's slots (timing experiments)
 };
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned int* p) {
@@ -150,36 +151,72 @@ __device__ __forceinline__ void ps_load_tile(uint8_t* a_base, const float* __res
     }
 }
 
+constexpr int PS_PER = WCHUNK / PS_THREADS;     // log records per thread of a window CTA
+constexpr uint32_t PS_LOG_NONE = 0xffffffffu;   // no record (beyond t_set, or never written)
+constexpr uint32_t PS_LOG_LATE = 0xfffffffeu;   // record of this batch's own gets: read after barrier 1
+
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
+// Window CTA, phase A (idle otherwise): the chunk's log entries into registers and the slots they name towards L2,
+// so that the stamp reads after barrier 1 are L2 hits instead of random DRAM round trips.  Positions at or beyond
+// t_get are being written by this batch's probes right now: they are read after the barrier.
+__device__ __forceinline__ void ps_window_preload(const KvView& kv, unsigned long long base, unsigned long long t_get,
+                                                  uint32_t (&slot)[PS_PER]) {
+#pragma unroll
+    for (int k = 0; k < PS_PER; ++k) {
+        const unsigned long long p = base + (unsigned long long)(k * PS_THREADS + (int)threadIdx.x);
+        slot[k] = p < t_get ? __ldcg(&kv.log[p & kv.rmask]) : PS_LOG_LATE;
+    }
+#pragma unroll
+    for (int k = 0; k < PS_PER; ++k)
+        if ((unsigned long long)slot[k] <= kv.mask) prefetch_l2(&kv.slots[slot[k]].stamp);
+}
+
 // Window CTA, phase B: bitmap of the chunk's log records that are still current (= entries of the reference's
 // _access_order, kvstore.py:71-78) among positions [head + chunk*1024, ...) below t_set.  Word w of s_mask covers
-// records [32w, 32w+32) of the chunk.  Returns the chunk's count to thread 0.
+// records [32w, 32w+32) of the chunk, s_pref[w] = current records in the words before w.  Returns the chunk's count.
 __device__ __forceinline__ unsigned ps_window_bitmap(const KvView& kv, unsigned long long base, unsigned long long t_set,
-                                                     unsigned* s_mask, unsigned* s_cnt) {
+                                                     uint32_t (&slot)[PS_PER], unsigned* s_mask, unsigned* s_pref,
+                                                     unsigned* s_cnt) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int PER = WCHUNK / PS_THREADS;
-    uint32_t slot[PER];
-    unsigned long long stamp[PER];
+    unsigned long long stamp[PS_PER];
     if (tid == 0) *s_cnt = 0u;
     __syncthreads();
 #pragma unroll
-    for (int k = 0; k < PER; ++k) {
+    for (int k = 0; k < PS_PER; ++k) {
         const unsigned long long p = base + (unsigned long long)(k * PS_THREADS + tid);
-        slot[k] = p < t_set ? __ldcg(&kv.log[p & kv.rmask]) : 0xffffffffu;
+        if (slot[k] == PS_LOG_LATE) slot[k] = p < t_set ? __ldcg(&kv.log[p & kv.rmask]) : PS_LOG_NONE;
     }
 #pragma unroll
-    for (int k = 0; k < PER; ++k)
+    for (int k = 0; k < PS_PER; ++k)
         stamp[k] = (unsigned long long)slot[k] <= kv.mask ? ld_u64_cg(&kv.slots[slot[k]].stamp) : 0ull;
     unsigned cnt = 0;
 #pragma unroll
-    for (int k = 0; k < PER; ++k) {
+    for (int k = 0; k < PS_PER; ++k) {
         const unsigned long long p = base + (unsigned long long)(k * PS_THREADS + tid);
-        const unsigned m = __ballot_sync(0xffffffffu, p < t_set && stamp[k] == p);
+        const bool cur = p < t_set && stamp[k] == p;
+        // a current record may be evicted in phase C, which looks at the successor slot: bring it to L2 now
+        if (cur) prefetch_l2(&kv.slots[((unsigned long long)slot[k] + 1ull) & kv.mask]);
+        const unsigned m = __ballot_sync(0xffffffffu, cur);
         if (lane == 0) {
             s_mask[k * (PS_THREADS / 32) + warp] = m;
             cnt += __popc(m);
         }
     }
     if (lane == 0 && cnt) atomicAdd(s_cnt, cnt);
+    __syncthreads();
+    if (warp == 0) {
+        const unsigned v = __popc(s_mask[lane]);
+        unsigned incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        s_pref[lane] = incl - v;
+    }
     __syncthreads();
     return *s_cnt;
 }
@@ -195,19 +232,25 @@ __device__ __forceinline__ unsigned ps_window_bitmap(const KvView& kv, unsigned 
 //   - a thread's four records are handled together: their loads are in flight side by side (two round trips in all).
 __device__ __forceinline__ void ps_window_evict(const KvView& kv, StepGrid* g, int chunk, int n_chunks,
                                                 unsigned long long base, unsigned long long tail0, unsigned long long t_set,
-                                                unsigned long long e, const unsigned* s_mask) {
+                                                unsigned long long e, const uint32_t (&slot)[PS_PER], const unsigned* s_mask,
+                                                const unsigned* s_pref) {
     const int tid = threadIdx.x;
     if (e == 0) return;  // uniform for the grid
     // tail0 = free_tail as every window CTA read it in phase B (nothing pushes between that read and barrier 3 except
     // these evictions); the queue's tail moves past them here, before any push of the next batch can happen
     if (chunk == 0 && tid == 0) kv.st->free_tail = tail0 + e;
-    unsigned long long before = 0, total = 0;
-    for (int c = 0; c < n_chunks; ++c) {
-        const unsigned long long w = __ldcg(&g->wcount[c]);
-        if (c < chunk) before += w;
-        total += w;
+    // current records in the chunks before this one / in the whole window: two loads per lane, side by side
+    const int lane_ = tid & 31;
+    const unsigned w0 = lane_ < n_chunks ? __ldcg(&g->wcount[lane_]) : 0u;
+    const unsigned w1 = lane_ + 32 < n_chunks ? __ldcg(&g->wcount[lane_ + 32]) : 0u;
+    unsigned bsum = (lane_ < chunk ? w0 : 0u) + (lane_ + 32 < chunk ? w1 : 0u), tsum = w0 + w1;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        bsum += __shfl_xor_sync(0xffffffffu, bsum, o);
+        tsum += __shfl_xor_sync(0xffffffffu, tsum, o);
     }
-    constexpr int PER = WCHUNK / PS_THREADS;
+    const unsigned long long before = bsum, total = tsum;
+    constexpr int PER = PS_PER;
     bool victim[PER];
     unsigned long long rank[PER];
     uint32_t sidx[PER];
@@ -219,11 +262,10 @@ __device__ __forceinline__ void ps_window_evict(const KvView& kv, StepGrid* g, i
         victim[k] = before < e && ((word >> b) & 1u);
         rank[k] = 0;
         if (victim[k]) {
-            rank[k] = before + __popc(word & ((1u << b) - 1u));
-            for (int ww = 0; ww < w; ++ww) rank[k] += __popc(s_mask[ww]);
+            rank[k] = before + s_pref[w] + __popc(word & ((1u << b) - 1u));
             victim[k] = rank[k] < e;
         }
-        sidx[k] = victim[k] ? __ldcg(&kv.log[(base + (unsigned long long)rec) & kv.rmask]) : 0u;
+        sidx[k] = victim[k] ? slot[k] : 0u;  // the log entry read for the bitmap
     }
     unsigned long long row[PER];
     u128 next[PER];
@@ -243,7 +285,7 @@ __device__ __forceinline__ void ps_window_evict(const KvView& kv, StepGrid* g, i
         st128(sl, tomb ? u128{FP_TOMB_WORD, FP_TOMB_WORD} : u128{0ull, 0ull});
         sl->stamp = 0ull;
         n_tomb += tomb;
-        if (kv.free_rows) kv.free_rows[(tail0 + rank[k]) % kv.n_rows] = (uint32_t)row[k];
+        if (kv.free_rows) kv.free_rows[(tail0 + rank[k]) & kv.row_mask] = (uint32_t)row[k];
         if (rank[k] == e - 1) g->hnew = base + (unsigned long long)(k * PS_THREADS + tid) + 1;  // the newest victim
     }
 #pragma unroll
@@ -261,7 +303,7 @@ __device__ __forceinline__ void ps_window_evict(const KvView& kv, StepGrid* g, i
                 st128(sl, tomb ? u128{FP_TOMB_WORD, FP_TOMB_WORD} : u128{0ull, 0ull});
                 sl->stamp = 0ull;
                 if (tomb) atomicAdd(&kv.st->n_tomb, 1ull);
-                if (kv.free_rows) kv.free_rows[(tail0 + r) % kv.n_rows] = (uint32_t)v;
+                if (kv.free_rows) kv.free_rows[(tail0 + r) & kv.row_mask] = (uint32_t)v;
                 ++r;
             }
             ++p;
@@ -278,6 +320,38 @@ __device__ __forceinline__ void ps_settle_evictions(const KvView& kv, const Step
     atomicAdd(&st->size, (unsigned long long)(-(long long)e));  // atomic: the next batch's probes may delete expired entries
     st->evictions += e;
     st->head = ld_u64_cg(&g->hnew);
+}
+
+// Request CTA's private stock of result rows: the inserts of a batch take their rows from shared memory, and one idle
+// warp tops the stock up to R handles with a single pop on the table's free queue per batch, in phase C, where nobody
+// waits for it.  (In phase C the queue only grows -- evicted rows are appended beyond its tail -- and it holds at least
+// max_batch handles that were free before the phase, see release_row.)
+__device__ __forceinline__ void ps_stash_refill(const KvView& kv, int* s_stash, int* s_nstash, int R) {
+    const int lane = (int)lane_id();
+    const int have = *s_nstash;
+    __syncwarp();
+    const int need = R - have;
+    if (need > 0) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(&kv.st->free_head, (unsigned long long)need);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        for (int i = lane; i < need; i += 32) s_stash[have + i] = (int)kv.free_rows[(base + (unsigned long long)i) & kv.row_mask];
+        __syncwarp();
+        if (lane == 0) *s_nstash = R;
+    }
+}
+__device__ __forceinline__ void ps_stash_return(const KvView& kv, const int* s_stash, int* s_nstash) {
+    const int lane = (int)lane_id();
+    const int have = *s_nstash;
+    __syncwarp();
+    if (have > 0) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(&kv.st->free_tail, (unsigned long long)have);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        for (int i = lane; i < have; i += 32) kv.free_rows[(base + (unsigned long long)i) & kv.row_mask] = (uint32_t)s_stash[i];
+        __syncwarp();
+        if (lane == 0) *s_nstash = 0;
+    }
 }
 
 __device__ __forceinline__ void warp_count_add(unsigned long long* ctr, bool pred, bool negative = false) {
@@ -297,6 +371,10 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
     __shared__ int s_slot[PS_MAX_R];
     __shared__ int s_row[PS_MAX_R];
     __shared__ uint8_t s_code[PS_MAX_R];
+    __shared__ unsigned s_pref[WCHUNK / 32];
+    __shared__ int s_stash[2 * PS_MAX_R];  // result-row handles this CTA holds for its next misses
+    __shared__ int s_nstash;
+    __shared__ __align__(16) float s_bias[256];
 
     StepRef sr = P.sr;
     if (use_qv) sr.q = &qv;
@@ -324,7 +402,11 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
 
     // ---- prologue: TMEM + weights (request CTAs), MD5 of every key of the launch (all CTAs) -------------------
     const uint32_t ncols = N <= 32 ? 32u : (N <= 64 ? 64u : (N <= 128 ? 128u : 256u));
+    if (tid < N) s_bias[tid] = P.bias ? P.bias[tid] : 0.f;  // N <= 256 = the CTA's thread count
+    if (tid == 0) s_nstash = 0;
+    __syncthreads();
     if (is_req) {
+        if (warp == 3 && !(P.dbg & 1)) ps_stash_refill(kv, s_stash, &s_nstash, R);  // nothing pushes before the first batch
         if (warp == 0) tc::tmem_alloc(&s_tmem, ncols);
         if (tid == 32) tc::mbar_init(&s_bar, 1);
     }
@@ -366,7 +448,11 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
         }                                                      \
     } while (0)
     unsigned mma_phase = 0;
-    int spare_row = -1;  // a row popped for a miss whose key another op of the batch inserted: pushed back in the next phase A
+    u128 key_next{0ull, 0ull};   // this thread's key of the next batch, fetched one batch ahead
+    bool have_next = false;
+    uint32_t wslot[PS_PER];      // window CTAs: the chunk's log entries of the current batch
+    unsigned long long cur_head = 0;  // window CTAs: LRU head, tracked locally (st->head is settled by one thread)
+    if (!is_req) cur_head = ld_u64_cg(&st->head);
 
     for (int s = 0; s < P.n_steps; ++s) {
         StepRef r = sr;
@@ -394,21 +480,39 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
             asm volatile("cp.async.commit_group;" ::: "memory");
             if (tid < R) {
                 const bool active = tid < nq;
-                warp_release_row(kv, spare_row >= 0, (unsigned long long)spare_row);  // phase A: atomic pushes and pops only
-                spare_row = -1;
+                SlotLine home{};
+                if (active) {  // the key was fetched during the previous batch (its home slot prefetched to L2)
+                    key = have_next ? key_next : fp_of(__ldcg(dig + q0 + tid));
+                    home = ld_slot_line(&kv.slots[key.lo & kv.mask]);
+                }
+                have_next = s + 1 < P.n_steps && q0 + tid < P.B && !(P.dbg & 1);
+                if (have_next) key_next = fp_of(__ldcg(dig + P.B + q0 + tid));
                 if (active) {
                     const int q = q0 + tid;
-                    key = fp_of(__ldcg(dig + q));
                     unsigned long long value;
                     long long slot;
-                    code = kv_get_one<false>(kv, key, a.now, a.t_get + (unsigned long long)q, value, slot);
+                    code = kv_get_one_from<false>(kv, key, home, a.now, a.t_get + (unsigned long long)q, value, slot);
                     a.code[q] = code == 1 ? (uint8_t)1 : (uint8_t)0;  // callers see 1 = served from the cache
                     s_value[tid] = value;
                 }
                 s_code[tid] = (uint8_t)code;
-                // a miss will be inserted in phase B: its result row is popped now, off that phase's chain (the
-                // queue holds max_batch + 64 handles more than the table has entries, see release_row)
-                my_row = (int)warp_acquire_row(kv, active && code != 1);
+                {   // a miss will insert in phase B: it takes its result row from the CTA's stock now
+                    const bool want = active && code != 1;
+                    const unsigned m = __ballot_sync(0xffffffffu, want);
+                    if (m) {
+                        const int leader = __ffs(m) - 1;
+                        int top = 0;
+                        if (lane == leader) top = atomicSub(&s_nstash, __popc(m));
+                        top = __shfl_sync(0xffffffffu, top, leader);
+                        if (want) my_row = s_stash[top - 1 - __popc(m & ((1u << lane) - 1u))];
+                    }
+                }
+                if (have_next && !(P.dbg & 2)) {  // next batch's home slot and where its probe chain continues -> L2
+                    const Slot* nh = &kv.slots[key_next.lo & kv.mask];
+                    prefetch_l2(nh);
+                    prefetch_l2(&nh->stamp);
+                    prefetch_l2(&kv.slots[(key_next.lo + 2ull) & kv.mask]);
+                }
                 warp_count_add(&st->hit_part[cta & 15][0], active && code == 1);
                 warp_count_add(&st->miss_part[cta & 15][0], active && code != 1);
                 const bool deleted = active && code == 2;  // expired: this op deleted the entry (kvstore.py:153-156)
@@ -420,6 +524,8 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
             PS_MARK(4);
             asm volatile("cp.async.wait_group 1;" ::: "memory");  // this batch's tile (and W) have landed
             tc::fence_proxy_async_smem();
+        } else if (!(P.dbg & 1)) {
+            ps_window_preload(kv, cur_head + (unsigned long long)chunk * WCHUNK, a.t_get, wslot);
         }
         grid_arrive(g);
         target += n_cta;
@@ -466,7 +572,7 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
                     s_slot[tid] = (int)sidx;
                     s_row[tid] = row;
                 }
-                if (miss && !claimed) spare_row = my_row;  // a duplicate's spare row goes back in the next phase A
+                if (miss && !claimed) s_stash[atomicAdd(&s_nstash, 1)] = my_row;  // a duplicate's spare row goes back
                 warp_count_add(&st->size, miss && claimed);
                 warp_count_add(&st->n_empty_claimed, miss && claimed && from_empty);
                 warp_count_add(&st->n_tomb, miss && claimed && !from_empty, true);
@@ -482,9 +588,9 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
                 }
             }
         } else if (!(P.dbg & 1)) {
-            wbase = ld_u64_cg(&st->head) + (unsigned long long)chunk * WCHUNK;
+            wbase = cur_head + (unsigned long long)chunk * WCHUNK;
             wtail = ld_u64_cg(&st->free_tail);  // stable from barrier 1 to barrier 3 but for the evictions themselves
-            const unsigned cnt = ps_window_bitmap(kv, wbase, a.t_set, s_mask, &s_cnt);
+            const unsigned cnt = ps_window_bitmap(kv, wbase, a.t_set, wslot, s_mask, s_pref, &s_cnt);
             if (tid == 0) g->wcount[chunk] = cnt;
             PS_MARK(7);
         }
@@ -501,6 +607,7 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
             target += n_cta;
             // warp 7 carries the barrier thread (its release fence waits for the CTA's outstanding writes): the epilogue
             // runs on warps 0-6 and synchronises among them only
+            if (warp == 3 && !(P.dbg & 1)) ps_stash_refill(kv, s_stash, &s_nstash, R);  // after barrier 2: takes and returns are done
             if (nq > 0 && warp < 7) {
                 if (tid < nq && s_code[tid] != 1) {  // which cached row this op's result goes to (-1: none)
                     int row = s_row[tid];
@@ -525,10 +632,11 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
                         for (int j = 0; j < 32; j += 4) {
                             if (c0 + j < N) {
                                 float4 o;
-                                o.x = __uint_as_float(v[j + 0]) + (P.bias ? __ldg(P.bias + c0 + j + 0) : 0.f);
-                                o.y = __uint_as_float(v[j + 1]) + (P.bias ? __ldg(P.bias + c0 + j + 1) : 0.f);
-                                o.z = __uint_as_float(v[j + 2]) + (P.bias ? __ldg(P.bias + c0 + j + 2) : 0.f);
-                                o.w = __uint_as_float(v[j + 3]) + (P.bias ? __ldg(P.bias + c0 + j + 3) : 0.f);
+                                const float4 bv = *reinterpret_cast<const float4*>(s_bias + c0 + j);
+                                o.x = __uint_as_float(v[j + 0]) + bv.x;
+                                o.y = __uint_as_float(v[j + 1]) + bv.y;
+                                o.z = __uint_as_float(v[j + 2]) + bv.z;
+                                o.w = __uint_as_float(v[j + 3]) + bv.w;
                                 *reinterpret_cast<float4*>(stage + (size_t)row * pitch + c0 + j) = o;
                             }
                         }
@@ -553,15 +661,16 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
             // every insert is in: _evict_if_needed's count for the whole batch (size is not written in this phase)
             const unsigned long long size = ld_u64_cg(&st->size);
             const unsigned long long e = size > kv.max_size && !(P.dbg & 1) ? size - kv.max_size : 0ull;
-            ps_window_evict(kv, g, chunk, P.n_chunks, wbase, wtail, a.t_set, e, s_mask);
+            ps_window_evict(kv, g, chunk, P.n_chunks, wbase, wtail, a.t_set, e, wslot, s_mask, s_pref);
             grid_arrive(g);
             target += n_cta;
             grid_wait(g, target, st);
+            if (e > 0) cur_head = ld_u64_cg(&g->hnew);  // the head every window CTA uses for the next batch
             if (chunk == 0 && tid == 0) ps_settle_evictions(kv, g, e);  // before this CTA arrives at the next barrier
         }
         PS_MARK(3);
     }
-    if (is_req && tid < R) warp_release_row(kv, spare_row >= 0, (unsigned long long)spare_row);
+    if (is_req && warp == 3) ps_stash_return(kv, s_stash, &s_nstash);  // the unused stock goes back to the table's queue
     // every CTA has passed the last barrier once CTA 0 has: the next launch starts counting from here
     if (cta == 0 && tid == PS_BAR_THREAD) g->bar_base = target;
     if (is_req && warp == 0) {

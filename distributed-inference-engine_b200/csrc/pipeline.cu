@@ -755,7 +755,7 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
     p->cfg.bias = nullptr;
     const uint64_t B = (uint64_t)cfg->max_batch;
     p->fast = B <= cfg->kv_max_size;
-    p->n_rows = cfg->kv_max_size + 2 * B + 64;  // spare rows: see release_row (kv_internal.cuh) and pipe_step.cu
+    p->n_rows = cfg->kv_max_size + 2 * B + 256;  // spare rows: see release_row (kv_internal.cuh) and pipe_step.cu
     DIE_TRY(kv_create_impl(cfg->kv_max_size, cfg->default_ttl, p->n_rows, B, &p->kv));
     if ((uint64_t)cfg->max_batch > p->kv->max_chunk)
         DIE_FAIL(DIE_ERR_TOO_LARGE, "die_pipeline_create: max_batch %d exceeds the table's batch limit %llu",
