@@ -706,13 +706,17 @@ static uint64_t next_pow2(uint64_t x) {
 
 die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_rows, uint64_t min_batch,
                             die_kv** out) {
-    if (max_size > (1ull << 30)) DIE_FAIL(DIE_ERR_TOO_LARGE, "die_kv_create: max_size > 2^30");
+    if (max_size > (1ull << 28)) DIE_FAIL(DIE_ERR_TOO_LARGE, "die_kv_create: max_size > 2^28 (slot indices are 32-bit)");
     die_kv* kv = new die_kv();
     memset(kv, 0, sizeof(*kv));
     DIE_CUDA(cudaGetDevice(&kv->device));
     kv->max_size = max_size;
     kv->default_ttl = default_ttl;
-    kv->capacity = next_pow2(std::max<uint64_t>(std::max<uint64_t>(4 * max_size, 16 * min_batch), 4096));
+    // slots per entry (power-of-two capacity >= factor * max_size): 8 keeps the live load at 1/8, so probe chains stay at
+    // one or two slots and most evicted slots have an EMPTY successor (they become EMPTY, not tombstones)
+    static int factor = 0;
+    if (factor == 0) factor = getenv("DIE_KV_SLOTS_PER_ENTRY") ? std::max(2, atoi(getenv("DIE_KV_SLOTS_PER_ENTRY"))) : 8;
+    kv->capacity = next_pow2(std::max<uint64_t>(std::max<uint64_t>((uint64_t)factor * max_size, 16 * min_batch), 4096));
     // LRU log: 4 bytes per position.  Positions are handed out per batch *slot* (an owner step of the exchange
     // stamps its whole capacity, not only the requests that arrived), so the log is sparse; 16 positions per
     // entry keeps compaction (kv_maintain) out of the steady state of a table that evicts.

@@ -30,8 +30,11 @@ for rep in range(6):
     lo = n_fill + rep * 128
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    th = time.perf_counter()
     pipe.run_device_many(kd[lo:lo + 128], off_d, pool, now, 0.01, out, hit); now += 1.28
+    th = time.perf_counter() - th
     e1.record(); torch.cuda.synchronize()
+    print("host enqueue %.1f us for 128 batches |" % (1e6 * th), end=" ")
     lib.die_pipeline_debug_marks_sync(pipe._h, marks)
     m = list(marks)
     us = lambda a, b_: (m[b_] - m[a]) / 1e3
