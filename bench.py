@@ -373,10 +373,13 @@ def stage_rooflines(lib, ms_arr, cnt_arr, n_stages, n_prof, s0, s1, step_ms_per_
             continue
         name = lib.die_profile_stage_name(i).decode()
         per = ms_arr[i] / cnt_arr[i]
-        gbs = alg.get(name, 0) / (per * 1e-3) / 1e9 if per > 0 else 0.0
+        batches_per_launch = n_prof / cnt_arr[i] if name == "fused_step" else 1.0  # the persistent kernel: a group per launch
+        alg_launch = alg.get(name, 0) * batches_per_launch
+        gbs = alg_launch / (per * 1e-3) / 1e9 if per > 0 else 0.0
         stages[name] = {"kernel": kernel_of.get(name, name), "us_per_launch": round(per * 1e3, 3),
-                        "launches_per_batch": cnt_arr[i] / n_prof, "share": round(ms_arr[i] / total_ms, 4),
-                        "alg_bytes_per_launch": round(alg.get(name, 0)), "gbs": round(gbs, 1),
+                        "launches_per_batch": cnt_arr[i] / n_prof, "batches_per_launch": round(batches_per_launch, 2),
+                        "share": round(ms_arr[i] / total_ms, 4),
+                        "alg_bytes_per_launch": round(alg_launch), "gbs": round(gbs, 1),
                         "frac_of_hbm_peak": round(gbs / peak, 4)}
     dom = max(stages, key=lambda n: stages[n]["share"])
     traffic, traffic_src = ncu_traffic(stages[dom]["kernel"])
@@ -682,7 +685,7 @@ def main():
     # ---- per-stage device time (CUDA events on the launching stream) and roofline -------------------------------
     stages, roofline = {}, None
     if world == 1 or os.environ.get("DIE_BENCH_PROFILE_ALL"):
-        n_prof = 50
+        n_prof = 64   # four groups of 16 batches
         _, keys, _, _ = make_batches(rng, n_prof, payload=False)
         kd2, xd2 = torch.from_numpy(keys).cuda(), pool[:n_prof]
         s0 = pipe.kv.stats()

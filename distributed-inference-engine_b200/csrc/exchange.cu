@@ -78,7 +78,8 @@ __global__ void __launch_bounds__(256)
 xchg_compact_kernel(const int4* __restrict__ rows, const int32_t* __restrict__ counts, int world, int cap, int vdim,
                     long long bmax, int4* __restrict__ digests_out, int4* __restrict__ payload_out,
                     uint32_t* __restrict__ n_out, int32_t* __restrict__ prefix_out /*[world+1]*/,
-                    unsigned int* __restrict__ error_flag) {
+                    unsigned int* __restrict__ error_flag, unsigned int* __restrict__ ticket,
+                    unsigned int* __restrict__ ing_seq, const QueueDesc* __restrict__ q, int step) {
     __shared__ long long s_pre[XCHG_MAX_WORLD + 1];
     if (threadIdx.x == 0) {
         long long acc = 0;
@@ -107,13 +108,42 @@ xchg_compact_kernel(const int4* __restrict__ rows, const int32_t* __restrict__ c
         if (lane == 0) digests_out[g] = __ldcg(src);
         for (int c = lane; c < vdim; c += 32) stg_stream(payload_out + g * vdim + c, __ldcg(src + 1 + c));
     }
+    if (ing_seq) {  // replayed group: the owner's persistent kernel waits for this flag, not for a stream event
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0 && atomicAdd(ticket, 1u) == gridDim.x - 1) {  // the last CTA: the whole batch is in place
+            *ticket = 0u;
+            __threadfence();
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(ing_seq), "r"(q->seq0 + (unsigned)step + 1u) : "memory");
+        }
+    }
 }
 
 // Owner: result g (source s, position i) -> return window of s.
 __global__ void __launch_bounds__(256)
 xchg_return_kernel(const int4* __restrict__ out, const uint8_t* __restrict__ hit, const int32_t* __restrict__ prefix,
-                   int world, int rank, int cap, int vout, PeerPtrs back) {
+                   int world, int rank, int cap, int vout, PeerPtrs back, const unsigned int* __restrict__ own_seq,
+                   const QueueDesc* __restrict__ q, int step, unsigned int* __restrict__ error_flag) {
     __shared__ int s_pre[XCHG_MAX_WORLD + 1];
+    if (own_seq) {  // replayed group: wait until the owner's persistent kernel has published this step's results
+        if (threadIdx.x == 0) {
+            const unsigned want = q->seq0 + (unsigned)step + 1u;
+            unsigned long long t0;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            for (;;) {
+                unsigned v;
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(own_seq) : "memory");
+                if ((int)(v - want) >= 0) break;
+                unsigned long long t;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                if (t - t0 > 4000000000ull) {
+                    *error_flag = 1u;
+                    break;
+                }
+            }
+        }
+        __syncthreads();
+    }
     if (threadIdx.x <= world) s_pre[threadIdx.x] = prefix[threadIdx.x];
     __syncthreads();
     const int rv = vout + 1;
@@ -319,7 +349,7 @@ extern "C" die_status_t die_xchg_compact(const float* rows, const int32_t* count
     const int vdim = dim / 4;
     DIE_LAUNCH(ST_XCHG_COMPACT, s, xchg_compact_kernel<<<grid_for_rows(2ll * cap), 256, 0, s>>>(
         reinterpret_cast<const int4*>(rows), counts, world, cap, vdim, bmax, reinterpret_cast<int4*>(digests_out),
-        reinterpret_cast<int4*>(payload_out), n_out, prefix_out, nullptr));
+        reinterpret_cast<int4*>(payload_out), n_out, prefix_out, nullptr, nullptr, nullptr, nullptr, 0));
     return DIE_OK;
 }
 
@@ -332,7 +362,7 @@ extern "C" die_status_t die_xchg_return(const float* out, const uint8_t* hit, co
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int vout = dim_out / 4;
     DIE_LAUNCH(ST_XCHG_RETURN, s, xchg_return_kernel<<<grid_for_rows(2ll * cap), 256, 0, s>>>(
-        reinterpret_cast<const int4*>(out), hit, prefix, world, rank, cap, vout, back));
+        reinterpret_cast<const int4*>(out), hit, prefix, world, rank, cap, vout, back, nullptr, nullptr, 0, nullptr));
     return DIE_OK;
 }
 
@@ -444,6 +474,15 @@ struct die_xchg {
     int graph_steps;
     cudaStream_t cap_stream;
     QueueDesc* qdesc;  // device: [0] the ingested queue, [1] the owner passes
+    // the lanes' receive-side buffers are one allocation each (lane l at base + l * stride), so that one persistent
+    // owner kernel can walk them as rings over the steps of a replayed group
+    uint32_t* ring_dig;
+    float* ring_pay;
+    float* ring_out;
+    uint8_t* ring_hit;
+    uint32_t* ring_ndev;
+    unsigned int* flags;  // device: [0] ingested steps, [1] owned steps, [2] ticket of the compact kernel
+    bool owner_group;     // replayed groups run their K owner steps as ONE persistent launch
 };
 
 static size_t xchg_rows_bytes(int world, int cap, int dim) { return (size_t)world * cap * (dim + 4) * sizeof(float); }
@@ -490,11 +529,18 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
         L.my_flags = static_cast<unsigned int*>(L.flags.p[rank]);
         DIE_CUDA(cudaMalloc(&L.shard, cap * sizeof(int32_t)));
         DIE_CUDA(cudaMalloc(&L.digests, (size_t)cap * 16));
-        DIE_CUDA(cudaMalloc(&L.recv_dig, bmax * 16));
-        DIE_CUDA(cudaMalloc(&L.recv_pay, bmax * dim * sizeof(float)));
-        DIE_CUDA(cudaMalloc(&L.recv_out, bmax * dim * sizeof(float)));
-        DIE_CUDA(cudaMalloc(&L.recv_hit, bmax));
-        DIE_CUDA(cudaMalloc(&L.n_dev, sizeof(uint32_t)));
+        if (l == 0) {
+            DIE_CUDA(cudaMalloc(&x->ring_dig, XCHG_SETS * bmax * 16));
+            DIE_CUDA(cudaMalloc(&x->ring_pay, XCHG_SETS * bmax * dim * sizeof(float)));
+            DIE_CUDA(cudaMalloc(&x->ring_out, XCHG_SETS * bmax * dim * sizeof(float)));
+            DIE_CUDA(cudaMalloc(&x->ring_hit, XCHG_SETS * bmax));
+            DIE_CUDA(cudaMalloc(&x->ring_ndev, XCHG_SETS * sizeof(uint32_t)));
+        }
+        L.recv_dig = x->ring_dig + (size_t)l * bmax * 4;
+        L.recv_pay = x->ring_pay + (size_t)l * bmax * dim;
+        L.recv_out = x->ring_out + (size_t)l * bmax * dim;
+        L.recv_hit = x->ring_hit + (size_t)l * bmax;
+        L.n_dev = x->ring_ndev + l;
         DIE_CUDA(cudaMalloc(&L.prefix, (world + 1) * sizeof(int32_t)));
         DIE_CUDA(cudaMalloc(&L.loc, cap * sizeof(int32_t)));
         DIE_CUDA(cudaMalloc(&L.cta_cnt, (size_t)ceil_div(cap, ROUTE_THREADS) * XCHG_MAX_WORLD * sizeof(int32_t)));
@@ -510,6 +556,9 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
     DIE_CUDA(cudaMalloc(&x->error_flag, sizeof(unsigned int)));
     DIE_CUDA(cudaMemset(x->error_flag, 0, sizeof(unsigned int)));
     DIE_CUDA(cudaMalloc(&x->qdesc, 2 * sizeof(QueueDesc)));
+    DIE_CUDA(cudaMalloc(&x->flags, 4 * sizeof(unsigned int)));
+    DIE_CUDA(cudaMemset(x->flags, 0, 4 * sizeof(unsigned int)));
+    x->owner_group = pipeline_owner_group_supported(pipe, x->bmax);
     DIE_CUDA(cudaStreamCreateWithFlags(&x->cap_stream, cudaStreamNonBlocking));
     x->graph_steps = 16;
     if (const char* e = getenv("DIE_GRAPH_STEPS")) x->graph_steps = atoi(e);
@@ -527,8 +576,7 @@ extern "C" die_status_t die_xchg_destroy(die_xchg_t* x) {
     if (x->exit_ev) cudaEventDestroy(x->exit_ev);
     for (int l = 0; l < XCHG_SETS; ++l) {
         XchgLane& L = x->lane[l];
-        void* bufs[] = {L.shard, L.digests, L.recv_dig, L.recv_pay, L.recv_out,
-                        L.recv_hit, L.n_dev, L.prefix, L.loc, L.cta_cnt};
+        void* bufs[] = {L.shard, L.digests, L.prefix, L.loc, L.cta_cnt};
         for (void* b : bufs) cudaFree(b);
         if (L.done) cudaEventDestroy(L.done);
         if (L.ingested) cudaEventDestroy(L.ingested);
@@ -537,6 +585,8 @@ extern "C" die_status_t die_xchg_destroy(die_xchg_t* x) {
     for (int g = 0; g < x->n_graphs; ++g) cudaGraphExecDestroy(x->graphs[g].exec);
     if (x->cap_stream) cudaStreamDestroy(x->cap_stream);
     cudaFree(x->qdesc);
+    cudaFree(x->flags);
+    cudaFree(x->ring_dig); cudaFree(x->ring_pay); cudaFree(x->ring_out); cudaFree(x->ring_hit); cudaFree(x->ring_ndev);
     if (x->entry) cudaEventDestroy(x->entry);
     cudaFree(x->error_flag);
     delete x;
@@ -559,7 +609,7 @@ static die_status_t xchg_barrier(die_xchg* x, XchgLane& L, int lane, const Queue
 // without holding back this step's ingest.
 static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user, StepRef owner, int32_t B,
                                      int32_t* shard_out, const QueueDesc* qd, unsigned int epoch_first,
-                                     const double* reserve_now) {
+                                     const double* reserve_now, int group_step = -1) {
     XchgLane& L = x->lane[lane];
     const int W = x->world, D = x->dim, vdim = D / 4;
     int32_t* shard = shard_out ? shard_out : L.shard;
@@ -576,10 +626,26 @@ static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user,
     DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first, s));  // every rank's rows have landed in their owners' windows
     DIE_LAUNCH(ST_XCHG_COMPACT, s, xchg_compact_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, s>>>(
         reinterpret_cast<const int4*>(L.my_rows), L.my_cnt, W, x->cap, vdim, (long long)x->bmax,
-        reinterpret_cast<int4*>(L.recv_dig), reinterpret_cast<int4*>(L.recv_pay), L.n_dev, L.prefix, x->error_flag));
+        reinterpret_cast<int4*>(L.recv_dig), reinterpret_cast<int4*>(L.recv_pay), L.n_dev, L.prefix, x->error_flag,
+        x->flags + 2, group_step >= 0 ? x->flags : nullptr, qd ? qd + 1 : nullptr, group_step));
     DIE_CUDA(cudaEventRecord(L.ingested, s));
     // ---- stage 2, owner pass: one in-order stream, so the table sees the batches in step order
     cudaStream_t so = x->s_own;
+    cudaStream_t sr = x->s_ret;
+    const int vout_ = D / 4;
+    if (group_step >= 0) {
+        // The group's K owner steps are ONE persistent launch on s_own (xchg_graph_get): it picks this step up when
+        // the compact kernel above raises the ingested flag, and the return kernel waits for its owned flag.
+        DIE_LAUNCH(ST_XCHG_RETURN, sr, xchg_return_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, sr>>>(
+            reinterpret_cast<const int4*>(L.recv_out), L.recv_hit, L.prefix, W, x->rank, x->cap, vout_, L.back,
+            x->flags + 1, qd + 1, group_step, x->error_flag));
+        DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first + 1, sr));
+        DIE_LAUNCH(ST_XCHG_SCATTER, sr, xchg_scatter_kernel<<<grid_for_rows(B), 256, off_bytes, sr>>>(
+            user, reinterpret_cast<const int4*>(L.my_back), L.loc, L.cta_cnt, n_cta, B, W, x->cap, vout_));
+        DIE_CUDA(cudaEventRecord(L.done, sr));
+        L.used = true;
+        return DIE_OK;
+    }
     DIE_CUDA(cudaStreamWaitEvent(so, L.ingested, 0));
     if (reserve_now) {
         unsigned long long tail0;
@@ -594,10 +660,10 @@ static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user,
     DIE_TRY(pipeline_owner_launch(x->pipe, owner, L.recv_dig, x->bmax, L.n_dev, so));
     DIE_CUDA(cudaEventRecord(L.owned, so));
     // ---- stage 3, way back
-    cudaStream_t sr = x->s_ret;
     DIE_CUDA(cudaStreamWaitEvent(sr, L.owned, 0));
     DIE_LAUNCH(ST_XCHG_RETURN, sr, xchg_return_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, sr>>>(
-        reinterpret_cast<const int4*>(L.recv_out), L.recv_hit, L.prefix, W, x->rank, x->cap, vdim, L.back));
+        reinterpret_cast<const int4*>(L.recv_out), L.recv_hit, L.prefix, W, x->rank, x->cap, vdim, L.back, nullptr, nullptr,
+        0, nullptr));
     DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first + 1, sr));  // every owner's results are back in the sources' windows
     DIE_LAUNCH(ST_XCHG_SCATTER, sr, xchg_scatter_kernel<<<grid_for_rows(B), 256, off_bytes, sr>>>(
         user, reinterpret_cast<const int4*>(L.my_back), L.loc, L.cta_cnt, n_cta, B, W, x->cap, vdim));
@@ -661,6 +727,14 @@ static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_
     cudaGraph_t graph = nullptr;
     DIE_CUDA(cudaStreamBeginCapture(x->cap_stream, cudaStreamCaptureModeThreadLocal));
     die_status_t st = xchg_fork(x, x->cap_stream);
+    if (st == DIE_OK && x->owner_group) {
+        StepLanes ln;
+        ln.lanes = XCHG_SETS;
+        ln.lane0 = lane0;
+        ln.ing_seq = x->flags;
+        ln.own_seq = x->flags + 1;
+        st = pipeline_owner_launch_group(x->pipe, x->qdesc + 1, K, x->ring_dig, x->bmax, x->ring_ndev, ln, x->s_own);
+    }
     unsigned int off[XCHG_SETS];
     for (int l = 0; l < XCHG_SETS; ++l) off[l] = 1u;
     for (int i = 0; i < K && st == DIE_OK; ++i) {
@@ -672,7 +746,7 @@ static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_
         user.i = i;
         owner.q = x->qdesc + 1;
         owner.i = i;
-        st = xchg_launch_step(x, lane, user, owner, B, nullptr, x->qdesc, off[lane], nullptr);
+        st = xchg_launch_step(x, lane, user, owner, B, nullptr, x->qdesc, off[lane], nullptr, x->owner_group ? i : -1);
         off[lane] += 2;
     }
     if (st == DIE_OK) st = xchg_join(x, x->cap_stream);
@@ -756,13 +830,25 @@ extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, con
             DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, K, user, &dw.kv, &tail0, &mirror));
             dw.tail0 = tail0;
             du.j0 = dw.j0 = j;
+            if (x->owner_group) {  // the owner's persistent kernel walks the lanes' buffers as rings of XCHG_SETS steps
+                const long long lane0 = (long long)(x->steps % XCHG_SETS);
+                dw.payload = x->ring_pay;
+                dw.out = x->ring_out;
+                dw.hit = x->ring_hit;
+                dw.payload_stride = dw.out_stride = (long long)x->bmax * x->dim;
+                dw.hit_stride = x->bmax;
+                dw.ring = dw.pay_ring = XCHG_SETS;
+                dw.j0 = lane0;            // buffers: step i of the group uses lane (lane0 + i) % XCHG_SETS
+                dw.jt = (long long)j - lane0;  // clock: still batch j + i of the queue
+                dw.seq0 = (unsigned int)x->steps;
+            }
             for (int l = 0; l < XCHG_SETS; ++l) du.epoch0[l] = x->lane[l].epoch;
             du.trace = dw.trace = trace_buffer();
             xchg_desc_set_kernel<<<1, 1, 0, user>>>(x->qdesc, du, dw, mirror);
             DIE_LAUNCH_CHECK();
             DIE_CUDA(cudaGraphLaunch(exec, user));
             count_replay();
-            count_launch((unsigned)(K * (7 + pipeline_launches_per_step(x->pipe))));
+            count_launch(x->owner_group ? (unsigned)(K * 7 + 1) : (unsigned)(K * (7 + pipeline_launches_per_step(x->pipe))));
             const int set0 = (int)(x->steps % XCHG_SETS);
             for (int i = 0; i < K; ++i) x->lane[(set0 + i) % XCHG_SETS].epoch += 2u;  // two barriers per step
             x->steps += (unsigned long long)K;

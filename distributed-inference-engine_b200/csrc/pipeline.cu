@@ -709,6 +709,22 @@ die_status_t pipeline_owner_launch(die_pipeline* p, const StepRef& sr, uint32_t*
     return launch_fast(p, sr, false, digests, B_max, n_req_dev, s);
 }
 
+bool pipeline_owner_group_supported(const die_pipeline* p, int B_max) {
+    int r, n;
+    static int on = -1;
+    if (on < 0) on = getenv("DIE_XCHG_OWNER_GROUP") ? atoi(getenv("DIE_XCHG_OWNER_GROUP")) : 1;
+    return on && p->persistent && pipe_step_shape(B_max, p->cfg.dim_in, p->cfg.dim_out, p->n_chunks, &r, &n);
+}
+
+die_status_t pipeline_owner_launch_group(die_pipeline* p, const QueueDesc* qd_dev, int K, uint32_t* digests_ring, int B_max,
+                                         const uint32_t* n_dev_ring, const StepLanes& lanes, cudaStream_t s) {
+    StepRef sr;
+    memset(&sr, 0, sizeof(sr));
+    sr.q = qd_dev;  // device-resident descriptor, rewritten before every replay
+    return pipe_step_launch(sr, nullptr, K, B_max, p->n_chunks, p->cfg.dim_in, p->cfg.dim_out, false, n_dev_ring,
+                            digests_ring, p->W, p->bias, p->arena, p->sgrid, nullptr, s, &lanes);
+}
+
 int pipeline_launches_per_step(const die_pipeline* p) {
     return p->persistent ? 1 : (p->cfg.model == DIE_MODEL_LINEAR_FP32 ? 4 : 3);
 }
@@ -939,7 +955,7 @@ extern "C" die_status_t die_pipeline_run_device_many(die_pipeline_t* p, int32_t 
     const size_t in_row = (size_t)B * p->cfg.dim_in, out_row = (size_t)B * p->cfg.dim_out;
     int32_t j = 0;
     const int K = p->graph_steps;
-    if (graph_fits(p, B, K) && !prof_active()) {
+    if (graph_fits(p, B, K) && (!prof_active() || p->persistent)) {  // one persistent launch per group can be event-timed
         QueueDesc d;
         memset(&d, 0, sizeof(d));
         d.key_bytes = key_bytes;

@@ -40,6 +40,8 @@ struct QueueDesc {
     long long j0;  // queue index of the replay's first batch (for the buffers)
     long long jt;  // added to j0 for the clock: the batches of a staged group are a window of a longer queue
     int ring;      // out / hit slots, reused round-robin
+    int pay_ring;  // payload slots, reused round-robin (0: one per batch of the queue)
+    unsigned int seq0;  // exchange only: global number of the replay's first step (ingested / owned flags count steps)
     int batch;     // stamps per get (= per set) pass of one step
     double now0, now_step;
     unsigned long long tail0;  // LRU stamp of the replay's first op
@@ -81,7 +83,7 @@ __device__ __forceinline__ StepArgs step_resolve(const StepRef& r) {
     // buffers the descriptor leaves null are fixed ones, frozen in the launch (the exchange's lane buffers)
     a.key_bytes = q.key_bytes ? q.key_bytes + j * q.key_bytes_stride : r.a.key_bytes;
     a.key_off = q.key_off ? q.key_off + j * q.key_off_stride : r.a.key_off;
-    a.payload = q.payload ? q.payload + j * q.payload_stride : r.a.payload;
+    a.payload = q.payload ? q.payload + (q.pay_ring ? j % q.pay_ring : j) * q.payload_stride : r.a.payload;
     a.out = q.out ? q.out + slot * q.out_stride : r.a.out;
     a.code = q.hit ? q.hit + slot * q.hit_stride : r.a.code;
     a.now = __dadd_rn(q.now0, __dmul_rn((double)(j + q.jt), q.now_step));  // the host's now0 + j * now_step, no fma
