@@ -28,6 +28,10 @@ if "--impl" in sys.argv and "reference" in sys.argv:
     for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS", "NUMEXPR_NUM_THREADS"):
         os.environ[_v] = "1"
 
+# The sharded step keeps one persistent owner kernel resident per replayed group while its ingest / return kernels run
+# beside it on other streams: every stream needs its own hardware queue (must be set before CUDA is initialised).
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 for _p in (ROOT, os.path.join(ROOT, "distributed-inference-engine_b200")):
     if _p not in sys.path:

@@ -468,7 +468,7 @@ struct die_xchg {
         int B, K, set0;
         cudaGraphExec_t exec;
     };
-    static constexpr int MAX_GRAPHS = 8;
+    static constexpr int MAX_GRAPHS = 16;
     Replay graphs[MAX_GRAPHS];
     int n_graphs;
     int graph_steps;
@@ -873,8 +873,16 @@ extern "C" die_status_t die_xchg_prepare(die_xchg_t* x, int32_t B) {
     if (!x || B <= 0 || B > x->cap) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_prepare: B must be in [1, cap]");
     const int K = x->graph_steps;
     if (K < 2 || !pipeline_graph_fits(x->pipe, x->bmax, K)) return DIE_OK;  // steps will be stream-launched
-    cudaGraphExec_t exec;
-    return xchg_graph_get(x, B, K, &exec);
+    // one graph per buffer set a group can start on (stream-launched remainders of a queue shift it)
+    const unsigned long long steps = x->steps;
+    die_status_t st = DIE_OK;
+    for (int l = 0; l < XCHG_SETS && st == DIE_OK; ++l) {
+        cudaGraphExec_t exec;
+        x->steps = steps + (unsigned long long)l;
+        st = xchg_graph_get(x, B, K, &exec);
+    }
+    x->steps = steps;
+    return st;
 }
 
 // Synchronises and reports whether a barrier of this context ever timed out (a peer stopped calling).

@@ -173,6 +173,7 @@ class PeerDispatcher:
         _cabi.check(self.lib.die_xchg_create(world, rank, self.cap, dim, self.bmax, self.pipe._h, self.peer_windows,
                                              ctypes.byref(h)))
         self._x = h.value
+        self._prepared = set()
         e = lambda shape, dt: torch.empty(shape, dtype=dt, device=self.dev)  # noqa: E731
         self.recv_dig = e((self.bmax, 4), torch.int32)
         self.recv_pay = e((self.bmax, dim), torch.float32)
@@ -222,6 +223,9 @@ class PeerDispatcher:
         n, B = payload.shape[0], payload.shape[1]
         shared = key_off.dim() == 1
         ptr = self._cabi.ptr
+        if B not in self._prepared:  # capture + instantiate the replays before the first queue, not inside it
+            self._cabi.check(self.lib.die_xchg_prepare(self._x, B))
+            self._prepared.add(B)
         self._cabi.check(self.lib.die_xchg_step_many(self._x, n, ptr(key_bytes), key_bytes.stride(0), ptr(key_off),
                                                      0 if shared else key_off.stride(0), B, ptr(payload), now0, now_step,
                                                      ptr(out), ptr(hit), out.shape[0], self._cabi.stream_ptr()))

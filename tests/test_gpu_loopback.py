@@ -88,12 +88,15 @@ def test_loopback_sharded_steps_match_oracle(world, model):
     assert sum(s["evictions"] for s in ref.state()) > 0 and sum(s["hits"] for s in ref.state()) > 0
 
 
-def test_loopback_replayed_queue_matches_oracle(monkeypatch):
+@pytest.mark.parametrize("owner_group", ["0", "1"])
+def test_loopback_replayed_queue_matches_oracle(monkeypatch, owner_group):
     """die_xchg_step_many: groups of steps replayed from one captured graph per rank (three stage streams, four
-    buffer sets, epochs from the device descriptor), until the owners' tables evict."""
+    buffer sets, epochs from the device descriptor), until the owners' tables evict.  owner_group=1: the opt-in form
+    in which the K owner passes of a group are one persistent launch driven by ingested / owned flags."""
     from die import ops
     from die.exchange import LoopbackPeerGroup
     monkeypatch.setenv("DIE_GRAPH_STEPS", "4")
+    monkeypatch.setenv("DIE_XCHG_OWNER_GROUP", owner_group)
     world, B, D, max_size, ttl, n_ids, K, groups = 2, 128, 128, 8192, 40.0, 60000, 4, 40
     rng = np.random.default_rng(77)
     model = "linear_tf32"
