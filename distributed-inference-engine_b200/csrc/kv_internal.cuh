@@ -35,7 +35,7 @@ struct __align__(64) Slot {
     unsigned long long value;
     double last_accessed;
     unsigned int access_count;
-    unsigned int pad;
+    unsigned int lfu_count;    // LFU policy: the reference's _access_count[key] (kvstore.py:79-80); unused otherwise
 };
 static_assert(sizeof(Slot) == 64, "slot must be one 64-byte record");
 
@@ -70,6 +70,7 @@ struct KvView {
     unsigned long long rmask;  // ring_cap - 1
     unsigned long long max_size;
     double default_ttl;
+    int policy;                // DIE_KV_POLICY_*
 };
 
 #ifdef __CUDACC__
@@ -235,8 +236,24 @@ __device__ __forceinline__ int kv_get_one_from(const KvView& kv, u128 key, SlotL
     slot = (long long)cur;
     value = l.value;
     if (!CONTAINS) {
-        atomicMax(&sl->stamp, stamp);  // move_to_end: the last toucher of the batch wins
-        kv.log[stamp & kv.rmask] = (uint32_t)slot;
+        if (kv.policy == DIE_KV_POLICY_LRU) {
+            atomicMax(&sl->stamp, stamp);  // move_to_end: the last toucher of the batch wins
+            kv.log[stamp & kv.rmask] = (uint32_t)slot;
+        } else if (kv.policy == DIE_KV_POLICY_LFU) {
+            // _access_count[key] = get(key, 0) + 1 (kvstore.py:79-80).  An entry that is not counted yet (inserted with
+            // batch=True) enters the dict now: its place in the tie-break order is this access -- the earliest one
+            // when several ops of the batch touch it.
+            atomicAdd(&sl->lfu_count, 1u);
+            if (l.stamp == 0ull) {
+                unsigned long long cur = 0ull;
+                for (;;) {
+                    const unsigned long long old = atomicCAS(&sl->stamp, cur, stamp);
+                    if (old == cur || (old != 0ull && old <= stamp)) break;
+                    cur = old;
+                }
+                kv.log[stamp & kv.rmask] = (uint32_t)slot;
+            }
+        }  // FIFO: an access changes nothing in the eviction order (kvstore.py:99-102)
         atomicAdd(&sl->access_count, 1u);
         sl->last_accessed = now;
     }
@@ -303,6 +320,7 @@ __device__ __forceinline__ long long kv_claim_absent(const KvView& kv, u128 key,
 
 struct die_kv {
     int device;
+    int policy;  // DIE_KV_POLICY_*
     uint64_t max_size, capacity, ring_cap;
     double default_ttl;
     die::Slot* slots;
@@ -342,13 +360,14 @@ inline KvView view_of(const die_kv* kv) {
     v.rmask = kv->ring_cap - 1;
     v.max_size = kv->max_size;
     v.default_ttl = kv->default_ttl;
+    v.policy = kv->policy;
     return v;
 }
 
 // n_rows > 0: the table hands out result-row handles in [0, n_rows) as values (pipeline mode).
 // min_batch: the table is sized so that one launch sequence can take a batch of this many ops.
 die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_rows, uint64_t min_batch,
-                            die_kv** out);
+                            die_kv** out, int policy = DIE_KV_POLICY_LRU);
 
 #ifdef __CUDACC__
 // One thread: snapshot -> pinned host mirror.  ops_seen = insert ops the host had reserved when it enqueued

@@ -565,6 +565,164 @@ kv_set_evict_kernel(KvView kv, const uint4* __restrict__ digests, const unsigned
 }
 
 // ------------------------------------------------------------------------------------------------
+// LFU policy (kvstore.py:67-69,79-80,94-98): a set batch is applied op by op by one CTA.  The reference picks its
+// victim with min() over the whole _access_count dict (O(n), first key with the smallest count in the order the keys
+// were first counted); here the CTA's 1024 threads scan the table for the smallest (count, stamp) pair per eviction.
+// New entries start with count 1, i.e. below every entry that was ever read, so a burst of inserts evicts its own
+// earlier inserts: the result depends on the order of the ops, which is why nothing here runs in parallel across ops.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024)
+kv_set_lfu_kernel(KvView kv, const uint4* __restrict__ digests, const unsigned long long* __restrict__ values,
+                  const double* __restrict__ ttl, int M, double now, unsigned long long t, int deferred,
+                  int32_t* __restrict__ slot_out, unsigned long long* __restrict__ dropped_out) {
+    __shared__ unsigned long long s_cnt_stamp[32][2];
+    __shared__ unsigned int s_slot[32];
+    __shared__ int s_need, s_abort;
+    __shared__ unsigned long long s_size;
+    KvState* st = kv.st;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
+        s_size = st->size;
+        s_abort = 0;
+    }
+    __syncthreads();
+    const unsigned long long cap = kv.mask + 1;
+    int i = 0;
+    for (; i < M; ++i) {
+        if (tid == 0) {
+            const u128 key = fp_of(digests[i]);
+            const long long s = kv_find(kv, key);
+            if (s >= 0) {  // if key in self.cache: self.delete(key)
+                Slot* sl = &kv.slots[s];
+                if (dropped_out && values) dropped_out[st->n_dropped++] = sl->value;
+                st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+                sl->stamp = 0ull;
+                --s_size;
+                st->n_tomb += 1;
+            }
+            s_need = s_size >= kv.max_size;
+            if (s_need) st->evictions += 1;  // counted before min() can raise (kvstore.py:87)
+            __threadfence_block();
+        }
+        __syncthreads();
+        if (s_need) {
+            unsigned long long best_c = ~0ull, best_s = ~0ull;
+            unsigned int best_slot = 0xffffffffu;
+            for (unsigned long long o = tid; o < cap; o += 1024) {
+                const Slot* sl = &kv.slots[o];
+                const u128 fp = ld_fp(sl);
+                if (fp_empty(fp) || fp_tomb(fp)) continue;
+                const unsigned long long stamp = ld_u64_cg(&sl->stamp);
+                if (stamp == 0ull) continue;  // not in _access_count: never a candidate
+                const unsigned long long c = (unsigned long long)__ldcg(&sl->lfu_count);
+                if (c < best_c || (c == best_c && stamp < best_s)) {
+                    best_c = c;
+                    best_s = stamp;
+                    best_slot = (unsigned int)o;
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const unsigned long long c2 = __shfl_xor_sync(0xffffffffu, best_c, o);
+                const unsigned long long s2 = __shfl_xor_sync(0xffffffffu, best_s, o);
+                const unsigned int sl2 = __shfl_xor_sync(0xffffffffu, best_slot, o);
+                if (c2 < best_c || (c2 == best_c && s2 < best_s)) {
+                    best_c = c2;
+                    best_s = s2;
+                    best_slot = sl2;
+                }
+            }
+            if (lane == 0) {
+                s_cnt_stamp[warp][0] = best_c;
+                s_cnt_stamp[warp][1] = best_s;
+                s_slot[warp] = best_slot;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                for (int w = 1; w < 32; ++w)
+                    if (s_cnt_stamp[w][0] < best_c || (s_cnt_stamp[w][0] == best_c && s_cnt_stamp[w][1] < best_s)) {
+                        best_c = s_cnt_stamp[w][0];
+                        best_s = s_cnt_stamp[w][1];
+                        best_slot = s_slot[w];
+                    }
+                if (best_slot == 0xffffffffu) {  // min() of an empty _access_count -> ValueError
+                    st->status = DIE_ERR_VALUE_ERROR;
+                    s_abort = 1;
+                } else {
+                    Slot* v = &kv.slots[best_slot];
+                    if (dropped_out) dropped_out[st->n_dropped++] = v->value;
+                    st128(v, u128{FP_TOMB_WORD, FP_TOMB_WORD});
+                    v->stamp = 0ull;
+                    --s_size;
+                    st->n_tomb += 1;
+                }
+                __threadfence_block();
+            }
+            __syncthreads();
+            if (s_abort) break;
+        }
+        if (tid == 0) {
+            const u128 key = fp_of(digests[i]);
+            unsigned long long cur = key.lo & kv.mask;
+            for (;;) {
+                const u128 fp = ld_fp(&kv.slots[cur]);
+                if (fp_empty(fp)) {
+                    st->n_empty_claimed += 1;
+                    break;
+                }
+                if (fp_tomb(fp)) {
+                    st->n_tomb -= 1;
+                    break;
+                }
+                cur = (cur + 1) & kv.mask;
+            }
+            Slot* sl = &kv.slots[cur];
+            const double x = ttl ? ttl[i] : NAN;
+            sl->created_at = now;
+            sl->ttl = isnan(x) ? kv.default_ttl : x;
+            sl->value = values ? values[i] : cur;
+            sl->last_accessed = now;
+            sl->access_count = 0u;
+            if (deferred) {
+                sl->stamp = 0ull;
+                sl->lfu_count = 0u;
+            } else {  // self._update_access(key): count 0 + 1, appended to _access_count
+                const unsigned long long stamp = t + (unsigned long long)i;
+                sl->stamp = stamp;
+                sl->lfu_count = 1u;
+                kv.log[stamp & kv.rmask] = (uint32_t)cur;
+            }
+            st128(sl, key);
+            ++s_size;
+            if (slot_out) slot_out[i] = (int32_t)cur;
+            __threadfence_block();
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        if (s_abort && slot_out)
+            for (int j = i; j < M; ++j) slot_out[j] = -1;
+        if (deferred == 1 && !s_abort) {  // for key in items: self._update_access(key)
+            for (int j = 0; j < M; ++j) {
+                const long long s = kv_find(kv, fp_of(digests[j]));
+                if (s < 0) continue;
+                Slot* sl = &kv.slots[s];
+                const unsigned long long stamp = t + (unsigned long long)j;
+                sl->lfu_count += 1u;
+                if (sl->stamp == 0ull) {
+                    sl->stamp = stamp;
+                    kv.log[stamp & kv.rmask] = (uint32_t)s;
+                }
+            }
+        }
+        st->size = s_size;
+        st->slow_batches += 1;
+        st->n_dropped_last = st->n_dropped;
+        st->n_dropped = 0ull;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // maintenance: re-append the current LRU records at the tail of a fresh ring (order kept)
 // ------------------------------------------------------------------------------------------------
 // Three launches over tiles of WIN_THREADS * WIN_ITEMS log positions, any number of CTAs:
@@ -674,6 +832,7 @@ kv_rehash_kernel(KvView kv, const Slot* __restrict__ old_slots, unsigned long lo
         dst->value = src->value;
         dst->last_accessed = src->last_accessed;
         dst->access_count = src->access_count;
+        dst->lfu_count = src->lfu_count;
         if (stamp) kv.log[stamp & kv.rmask] = (uint32_t)cur;
     }
 }
@@ -705,12 +864,13 @@ static uint64_t next_pow2(uint64_t x) {
 }
 
 die_status_t kv_create_impl(uint64_t max_size, double default_ttl, uint64_t n_rows, uint64_t min_batch,
-                            die_kv** out) {
+                            die_kv** out, int policy) {
     if (max_size > (1ull << 28)) DIE_FAIL(DIE_ERR_TOO_LARGE, "die_kv_create: max_size > 2^28 (slot indices are 32-bit)");
     die_kv* kv = new die_kv();
     memset(kv, 0, sizeof(*kv));
     DIE_CUDA(cudaGetDevice(&kv->device));
     kv->max_size = max_size;
+    kv->policy = policy;
     kv->default_ttl = default_ttl;
     // slots per entry (power-of-two capacity >= factor * max_size): 8 keeps the live load at 1/8, so probe chains stay at
     // one or two slots and most evicted slots have an EMPTY successor (they become EMPTY, not tombstones)
@@ -876,10 +1036,30 @@ die_status_t kv_get_batch_impl(die_kv* kv, const uint32_t* digests, int32_t B, d
     return DIE_OK;
 }
 
+// LFU: the whole batch in one launch of the op-by-op kernel (no scratch, no housekeeping beyond kv_reserve's).
+static die_status_t kv_set_lfu(die_kv* kv, const uint32_t* digests, const uint64_t* values, const double* ttl, int32_t M,
+                               double now, int32_t deferred, int32_t* slot_out, uint64_t* dropped_out, cudaStream_t s) {
+    if ((int64_t)M > (int64_t)kv->max_chunk)
+        DIE_FAIL(DIE_ERR_TOO_LARGE, "kv_set_batch (lfu): %d ops exceed this table's per-call limit of %llu", M,
+                 (unsigned long long)kv->max_chunk);
+    kv->dropped_prefix = 0;
+    DIE_LAUNCH(ST_KV_EVICT, s, kv_set_lfu_kernel<<<1, 1024, 0, s>>>(
+        view_of(kv), reinterpret_cast<const uint4*>(digests), reinterpret_cast<const unsigned long long*>(values), ttl, M, now,
+        kv->tail, deferred, slot_out, reinterpret_cast<unsigned long long*>(dropped_out)));
+    kv->tail += (uint64_t)M;
+    return DIE_OK;
+}
+
 die_status_t kv_set_batch_impl(die_kv* kv, const uint32_t* digests, const uint64_t* values, const double* ttl,
                                int32_t M, double now, int32_t deferred, const uint8_t* skip, int known_absent,
                                const uint32_t* n_active_dev, int32_t* slot_out, uint64_t* dropped_out,
                                cudaStream_t s) {
+    if (kv->policy == DIE_KV_POLICY_FIFO) deferred = 0;  // the eviction order is the insertion order: stamped at insert
+    if (kv->policy == DIE_KV_POLICY_LFU) {
+        if (skip || known_absent) DIE_FAIL(DIE_ERR_UNSUPPORTED, "kv_set_batch: the composed pipeline runs on LRU tables");
+        DIE_TRY(kv_reserve(kv, (uint64_t)M, true, s));
+        return kv_set_lfu(kv, digests, values, ttl, M, now, deferred, slot_out, dropped_out, s);
+    }
     if (known_absent && ((int64_t)M > (int64_t)kv->max_chunk || !n_active_dev))
         DIE_FAIL(DIE_ERR_TOO_LARGE, "kv_set_batch: known_absent batches must fit one chunk (%d > %llu)", M,
                  (unsigned long long)kv->max_chunk);
@@ -945,9 +1125,9 @@ using namespace die;
 
 extern "C" die_status_t die_kv_create(uint64_t max_size, int32_t policy, double default_ttl, die_kv_t** out) {
     if (!out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_create: null out");
-    if (policy != DIE_KV_POLICY_LRU)
-        DIE_FAIL(DIE_ERR_UNSUPPORTED, "die_kv_create: only eviction_policy='lru' is built (policy=%d)", policy);
-    return kv_create_impl(max_size, default_ttl, 0, 0, out);
+    if (policy != DIE_KV_POLICY_LRU && policy != DIE_KV_POLICY_LFU && policy != DIE_KV_POLICY_FIFO)
+        DIE_FAIL(DIE_ERR_INVALID, "die_kv_create: unknown eviction policy %d", policy);
+    return kv_create_impl(max_size, default_ttl, 0, 0, out, policy);
 }
 
 extern "C" die_status_t die_kv_destroy(die_kv_t* kv) {
@@ -1086,7 +1266,8 @@ extern "C" die_status_t die_kv_sync_status(die_kv_t* kv, int32_t* status, uint64
 
 extern "C" die_status_t die_kv_dump_sync(die_kv_t* kv, uint64_t cap, uint32_t* digests, uint64_t* values,
                                          double* created_at, double* last_accessed, uint32_t* access_count,
-                                         double* ttl, uint8_t* stamped, uint64_t* n_out, die_stream_t stream) {
+                                         double* ttl, uint8_t* stamped, uint64_t* n_out, die_stream_t stream,
+                                         uint32_t* lfu_count) {
     if (!kv || !n_out) DIE_FAIL(DIE_ERR_INVALID, "die_kv_dump_sync: bad arguments");
     if (kv->capacity > (1ull << 24)) DIE_FAIL(DIE_ERR_TOO_LARGE, "die_kv_dump_sync: parity dump is for small tables");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -1118,7 +1299,84 @@ extern "C" die_status_t die_kv_dump_sync(die_kv_t* kv, uint64_t cap, uint32_t* d
         if (access_count) access_count[k] = sl->access_count;
         if (ttl) ttl[k] = sl->ttl;
         if (stamped) stamped[k] = sl->stamp ? 1 : 0;
+        if (lfu_count) lfu_count[k] = sl->lfu_count;
     }
+    return DIE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Snapshot / restore (the reference's README.md:14 promises "optional persistence" and never wrote it): the table as
+// one flat image -- header, counters, slots.  The LRU log is not stored: it is rebuilt from the slots' stamps.
+// ------------------------------------------------------------------------------------------------
+namespace die {
+struct KvImageHeader {
+    uint64_t magic, version, max_size, capacity, ring_cap, policy, tail;
+    double default_ttl;
+    KvState st;
+};
+constexpr uint64_t KV_IMAGE_MAGIC = 0x314d494b45494444ull;  // "DDIEKIM1"
+
+__global__ void __launch_bounds__(KV_THREADS)
+kv_relog_kernel(KvView kv) {  // log[stamp] = slot for every entry that is in the eviction order
+    const unsigned long long cap = kv.mask + 1;
+    for (unsigned long long o = blockIdx.x * (unsigned long long)KV_THREADS + threadIdx.x; o < cap;
+         o += (unsigned long long)gridDim.x * KV_THREADS) {
+        const Slot* sl = &kv.slots[o];
+        const u128 fp{sl->fp_lo, sl->fp_hi};
+        if (fp_empty(fp) || fp_tomb(fp)) continue;
+        if (sl->stamp) kv.log[sl->stamp & kv.rmask] = (uint32_t)o;
+    }
+}
+}  // namespace die
+
+extern "C" uint64_t die_kv_snapshot_bytes(die_kv_t* kv) {
+    return kv ? sizeof(KvImageHeader) + kv->capacity * sizeof(Slot) : 0;
+}
+
+extern "C" die_status_t die_kv_snapshot_sync(die_kv_t* kv, void* image, uint64_t image_bytes, die_stream_t stream) {
+    if (!kv || !image) DIE_FAIL(DIE_ERR_INVALID, "die_kv_snapshot_sync: null argument");
+    if (kv->free_rows) DIE_FAIL(DIE_ERR_UNSUPPORTED, "die_kv_snapshot_sync: a pipeline-owned table holds result-row handles, not values");
+    if (image_bytes < die_kv_snapshot_bytes(kv))
+        DIE_FAIL(DIE_ERR_TOO_LARGE, "die_kv_snapshot_sync: the image needs %llu bytes", (unsigned long long)die_kv_snapshot_bytes(kv));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    KvImageHeader* h = static_cast<KvImageHeader*>(image);
+    h->magic = KV_IMAGE_MAGIC;
+    h->version = 1;
+    h->max_size = kv->max_size;
+    h->capacity = kv->capacity;
+    h->ring_cap = kv->ring_cap;
+    h->policy = (uint64_t)kv->policy;
+    h->tail = kv->tail;
+    h->default_ttl = kv->default_ttl;
+    DIE_CUDA(cudaMemcpyAsync(&h->st, kv->st, sizeof(KvState), cudaMemcpyDeviceToHost, s));
+    DIE_CUDA(cudaMemcpyAsync(h + 1, kv->slots, kv->capacity * sizeof(Slot), cudaMemcpyDeviceToHost, s));
+    DIE_CUDA(cudaStreamSynchronize(s));
+    return DIE_OK;
+}
+
+extern "C" die_status_t die_kv_restore_sync(die_kv_t* kv, const void* image, uint64_t image_bytes, die_stream_t stream) {
+    if (!kv || !image) DIE_FAIL(DIE_ERR_INVALID, "die_kv_restore_sync: null argument");
+    if (kv->free_rows) DIE_FAIL(DIE_ERR_UNSUPPORTED, "die_kv_restore_sync: not for pipeline-owned tables");
+    const KvImageHeader* h = static_cast<const KvImageHeader*>(image);
+    if (image_bytes < sizeof(KvImageHeader) || h->magic != KV_IMAGE_MAGIC || h->version != 1)
+        DIE_FAIL(DIE_ERR_INVALID, "die_kv_restore_sync: not a table image");
+    if (h->max_size != kv->max_size || h->capacity != kv->capacity || h->ring_cap != kv->ring_cap ||
+        h->policy != (uint64_t)kv->policy || image_bytes < sizeof(KvImageHeader) + kv->capacity * sizeof(Slot))
+        DIE_FAIL(DIE_ERR_INVALID, "die_kv_restore_sync: the image was taken from a table of another shape "
+                                  "(max_size %llu, policy %llu)", (unsigned long long)h->max_size, (unsigned long long)h->policy);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    DIE_CUDA(cudaMemcpyAsync(kv->slots, h + 1, kv->capacity * sizeof(Slot), cudaMemcpyHostToDevice, s));
+    DIE_CUDA(cudaMemcpyAsync(kv->st, &h->st, sizeof(KvState), cudaMemcpyHostToDevice, s));
+    DIE_CUDA(cudaMemsetAsync(kv->log, 0xff, kv->ring_cap * sizeof(uint32_t), s));
+    DIE_LAUNCH(ST_KV_MAINT, s, kv_relog_kernel<<<num_sms() * 8, KV_THREADS, 0, s>>>(view_of(kv)));
+    DIE_CUDA(cudaStreamSynchronize(s));
+    kv->tail = h->tail;
+    kv->default_ttl = h->default_ttl;
+    kv->head_lb = h->st.head;
+    kv->live_at_rebuild = h->st.size + h->st.n_tomb;
+    kv->claims_ub = 0;
+    kv->dropped_prefix = 0;
+    kv->mirror_gen += 1;  // snapshots of the table that was here describe something else
     return DIE_OK;
 }
 
@@ -1153,6 +1411,7 @@ extern "C" die_status_t die_kv_set_batch_noalloc(die_kv_t* kv, const uint32_t* d
     if ((uint64_t)M > kv->max_chunk)
         DIE_FAIL(DIE_ERR_TOO_LARGE, "die_kv_set_batch_noalloc: %d ops exceed this table's per-launch limit of %llu", M,
                  (unsigned long long)kv->max_chunk);
+    if (kv->policy == DIE_KV_POLICY_FIFO) deferred_stamp = 0;
     int dev = -1;
     DIE_CUDA(cudaGetDevice(&dev));
     if (dev != kv->device || dev < 0 || dev >= KV_NOALLOC_MAX_DEVICES)
@@ -1172,6 +1431,12 @@ extern "C" die_status_t die_kv_set_batch_noalloc(die_kv_t* kv, const uint32_t* d
                  "die_kv_set_batch_noalloc: table housekeeping is due and would allocate; call die_kv_maintain_sync "
                  "at a point where allocation is allowed, then retry");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (kv->policy == DIE_KV_POLICY_LFU) {  // the op-by-op LFU kernel uses no scratch at all
+        DIE_TRY(kv_set_lfu(kv, digests, values, ttl, M, now, deferred_stamp, slot_out, dropped_out, s));
+        kv->claims_ub += n;
+        kv->ops_enq += n;
+        return DIE_OK;
+    }
     const KvView v = view_of(kv);
     const uint4* dg = reinterpret_cast<const uint4*>(digests);
     const unsigned long long* vals = reinterpret_cast<const unsigned long long*>(values);

@@ -14,7 +14,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("DIE_LIB_PATH") or os.path.join(_HERE, "_lib", "libdie.so")  # override: A/B diagnostics only
 
 DIE_OK, DIE_ERR_INVALID, DIE_ERR_CUDA, DIE_ERR_NOMEM, DIE_ERR_STOP_ITERATION, DIE_ERR_TOO_LARGE, \
-    DIE_ERR_UNSUPPORTED = range(7)
+    DIE_ERR_UNSUPPORTED, DIE_ERR_VALUE_ERROR = range(8)
+POLICY_IDS = {"lru": 0, "lfu": 1, "fifo": 2}
 LINEAR_FP32, LINEAR_TF32 = 0, 1
 MODEL_ECHO, MODEL_LINEAR_FP32, MODEL_LINEAR_TF32 = 0, 1, 2
 
@@ -61,7 +62,10 @@ SIGNATURES = {
     "die_kv_clear": (c_int32, [P, P]),
     "die_kv_stats_sync": (c_int32, [P, POINTER(c_uint64), P]),
     "die_kv_sync_status": (c_int32, [P, POINTER(c_int32), POINTER(c_uint64), POINTER(c_uint32), P]),
-    "die_kv_dump_sync": (c_int32, [P, c_uint64, P, P, P, P, P, P, P, POINTER(c_uint64), P]),
+    "die_kv_dump_sync": (c_int32, [P, c_uint64, P, P, P, P, P, P, P, POINTER(c_uint64), P, P]),
+    "die_kv_snapshot_bytes": (c_uint64, [P]),
+    "die_kv_snapshot_sync": (c_int32, [P, P, c_uint64, P]),
+    "die_kv_restore_sync": (c_int32, [P, P, c_uint64, P]),
     "die_kv_maintain_sync": (c_int32, [P, c_int32, P]),
     "die_pack_ragged": (c_int32, [P, P, P, c_int32, c_int32, c_int32, P, P, P]),
     "die_unpack_ragged": (c_int32, [P, P, P, c_int32, c_int32, c_int32, P, P]),

@@ -39,14 +39,16 @@ class CacheEntry(Generic[T]):
 class DeviceKV:
     """Owns one ``die_kv_t``.  All tensor arguments are CUDA tensors; digests are int32 [B, 4]."""
 
-    def __init__(self, max_size: int, default_ttl: Optional[float] = None, _handle: Optional[int] = None):
+    def __init__(self, max_size: int, default_ttl: Optional[float] = None, _handle: Optional[int] = None,
+                 policy: str = "lru"):
         self._lib = require_cuda()
         self.max_size = max_size
+        self.policy = policy
         self._owned = _handle is None
         if _handle is None:
             h = ctypes.c_void_p()
-            check(self._lib.die_kv_create(max_size, 0, math.nan if default_ttl is None else float(default_ttl),
-                                          ctypes.byref(h)))
+            check(self._lib.die_kv_create(max_size, _cabi.POLICY_IDS[policy],
+                                          math.nan if default_ttl is None else float(default_ttl), ctypes.byref(h)))
             _handle = h.value
         self._h = _handle
 
@@ -127,12 +129,28 @@ class DeviceKV:
         cnt = torch.empty(cap, dtype=torch.int32)
         ttl = torch.empty(cap, dtype=torch.float64)
         stamped = torch.empty(cap, dtype=torch.uint8)
+        lfu = torch.empty(cap, dtype=torch.int32)
         n = ctypes.c_uint64()
         check(self._lib.die_kv_dump_sync(self._h, cap, ptr(dig), ptr(val), ptr(created), ptr(last), ptr(cnt), ptr(ttl),
-                                         ptr(stamped), ctypes.byref(n), stream_ptr()))
+                                         ptr(stamped), ctypes.byref(n), stream_ptr(), ptr(lfu)))
         k = int(n.value)
-        return {"digests": dig[:k], "values": val[:k], "created_at": created[:k], "last_accessed": last[:k],
-                "access_count": cnt[:k], "ttl": ttl[:k], "stamped": stamped[:k]}
+        out = {"digests": dig[:k], "values": val[:k], "created_at": created[:k], "last_accessed": last[:k],
+               "access_count": cnt[:k], "ttl": ttl[:k], "stamped": stamped[:k]}
+        if self.policy == "lfu":
+            out["lfu_count"] = lfu[:k]
+        return out
+
+    def snapshot(self) -> torch.Tensor:
+        """The whole table (entries, eviction order, counters) as one flat uint8 host tensor (die_kv_snapshot_sync)."""
+        nbytes = int(self._lib.die_kv_snapshot_bytes(self._h))
+        image = torch.empty(nbytes, dtype=torch.uint8)
+        check(self._lib.die_kv_snapshot_sync(self._h, ptr(image), nbytes, stream_ptr()))
+        return image
+
+    def restore(self, image: torch.Tensor) -> None:
+        """Load an image taken from a table of the same max_size and policy."""
+        image = image.contiguous()
+        check(self._lib.die_kv_restore_sync(self._h, ptr(image), image.numel(), stream_ptr()))
 
 
 def digests_of(keys: Sequence[str]) -> torch.Tensor:
@@ -143,20 +161,20 @@ def digests_of(keys: Sequence[str]) -> torch.Tensor:
 
 class KVCache:
     """Same constructor, methods, attributes and error behaviour as the reference's KVCache
-    (src/kvstore.py:26-236) for ``eviction_policy="lru"``.  Extra keyword-only ``clock`` replaces
-    ``time.time`` (used by the parity tests)."""
+    (src/kvstore.py:26-236), for the three eviction policies "lru", "lfu" and "fifo".  Extra keyword-only ``clock``
+    replaces ``time.time`` (used by the parity tests); ``save`` / ``load`` are the persistence the reference's
+    README.md:14 promises and never wrote."""
 
     def __init__(self, max_size: int = 1000, eviction_policy: str = "lru", default_ttl: Optional[float] = None,
                  *, clock: Optional[Callable[[], float]] = None):
         self.max_size = max_size
         self.eviction_policy = eviction_policy.lower()
         self.default_ttl = default_ttl
-        if self.eviction_policy != "lru":
-            raise NotImplementedError(
-                f"eviction_policy={eviction_policy!r}: only 'lru' is built for the GPU table "
-                "(LFU/FIFO are listed as next work in DESIGN.md)")
+        if self.eviction_policy not in _cabi.POLICY_IDS:
+            # the reference accepts any string and silently behaves as FIFO (kvstore.py:99 "else"); a typo is refused here
+            raise ValueError(f"eviction_policy={eviction_policy!r}: expected 'lru', 'lfu' or 'fifo'")
         self._clock = clock or time.time
-        self._kv = DeviceKV(max_size, default_ttl)
+        self._kv = DeviceKV(max_size, default_ttl, policy=self.eviction_policy)
         self._objects: Dict[int, Any] = {}     # handle -> Python value
         self._keys: Dict[bytes, str] = {}      # digest -> key string (only to present .cache / LRU dumps)
         self._next_handle = 1
@@ -206,7 +224,9 @@ class KVCache:
             if applied[i] < 0 or last_of.get(k) != i:
                 self._objects.pop(handles[i], None)
         if status == _cabi.DIE_ERR_STOP_ITERATION:
-            raise StopIteration  # the reference's next(iter(OrderedDict())) at kvstore.py:89
+            raise StopIteration  # the reference's next(iter(OrderedDict())) at kvstore.py:89 / next(iter(cache)) :101
+        if status == _cabi.DIE_ERR_VALUE_ERROR:
+            raise ValueError("min() arg is an empty sequence")  # LFU with nothing counted, kvstore.py:95
 
     # -- reference API ---------------------------------------------------------------------------------
     def set(self, key: str, value: Any, ttl: Optional[float] = None, batch: bool = False) -> None:
@@ -299,6 +319,32 @@ class KVCache:
     def cache(self) -> Dict[str, CacheEntry]:
         """Snapshot of the table as ``{key: CacheEntry}`` (LRU order, head first)."""
         return {k: e for k, e, _ in self._dump_entries()}
+
+    @property
+    def _access_count(self) -> Dict[str, int]:
+        """LFU: snapshot of the reference's private use-count dict, in the order the keys were first counted."""
+        d = self._kv.dump()
+        raw = d["digests"].numpy().tobytes()
+        return {self._keys.get(raw[16 * i:16 * i + 16]): int(d["lfu_count"][i])
+                for i in range(d["values"].numel()) if bool(d["stamped"][i])}
+
+    def save(self, path: str) -> None:
+        """Persist the cache: the device table's image plus the Python values its handles stand for."""
+        import pickle
+        with open(path, "wb") as f:
+            pickle.dump({"image": self._kv.snapshot().numpy(), "objects": self._objects, "keys": self._keys,
+                         "next_handle": self._next_handle, "max_size": self.max_size,
+                         "eviction_policy": self.eviction_policy, "default_ttl": self.default_ttl}, f)
+
+    def load(self, path: str) -> None:
+        """Restore a cache saved by ``save`` from a KVCache of the same max_size and eviction_policy."""
+        import pickle
+        with open(path, "rb") as f:
+            d = pickle.load(f)
+        if (d["max_size"], d["eviction_policy"]) != (self.max_size, self.eviction_policy):
+            raise ValueError("the saved cache has another max_size / eviction_policy")
+        self._kv.restore(torch.from_numpy(d["image"]))
+        self._objects, self._keys, self._next_handle = d["objects"], d["keys"], d["next_handle"]
 
     @property
     def _access_order(self) -> "OrderedDict[str, float]":

@@ -36,7 +36,8 @@ enum {
     DIE_ERR_NOMEM = 3,
     DIE_ERR_STOP_ITERATION = 4, /* the reference would have raised StopIteration (kvstore.py:89) */
     DIE_ERR_TOO_LARGE = 5,
-    DIE_ERR_UNSUPPORTED = 6
+    DIE_ERR_UNSUPPORTED = 6,
+    DIE_ERR_VALUE_ERROR = 7     /* the reference would have raised ValueError: LFU min() of an empty dict (kvstore.py:95) */
 };
 
 typedef void* die_stream_t; /* cudaStream_t */
@@ -117,8 +118,11 @@ die_status_t die_bucket_by_shard(const int32_t* shard, int32_t B, int32_t n_shar
 typedef struct die_kv die_kv_t;
 
 #define DIE_KV_POLICY_LRU 0
+#define DIE_KV_POLICY_LFU 1  /* victim = fewest uses, ties by the order the keys were first counted (kvstore.py:94-98) */
+#define DIE_KV_POLICY_FIFO 2 /* victim = oldest insertion; accesses do not matter (kvstore.py:99-102) */
 
-/* KVCache.__init__ (kvstore.py:38-61). policy other than LRU -> DIE_ERR_UNSUPPORTED. */
+/* KVCache.__init__ (kvstore.py:38-61).  LFU evicts by a scan of the table per victim (the reference's min() over its
+ * dict is O(n) too): meant for policy caches of modest size, not for the 10^7-entry tables of the LRU path. */
 die_status_t die_kv_create(uint64_t max_size, int32_t policy, double default_ttl, die_kv_t** out);
 die_status_t die_kv_destroy(die_kv_t* kv);
 
@@ -186,7 +190,15 @@ die_status_t die_kv_sync_status(die_kv_t* kv, int32_t* status /*[host]*/, uint64
  * order; arrays are [host] with room for `cap` entries.  Mirrors list(_access_order) + self.cache. */
 die_status_t die_kv_dump_sync(die_kv_t* kv, uint64_t cap, uint32_t* digests /*[cap,4]*/, uint64_t* values,
                               double* created_at, double* last_accessed, uint32_t* access_count,
-                              double* ttl, uint8_t* stamped, uint64_t* n_out, die_stream_t stream);
+                              double* ttl, uint8_t* stamped, uint64_t* n_out, die_stream_t stream,
+                              uint32_t* lfu_count /*optional: _access_count of an LFU table*/);
+/* Persistence (README.md:14 "optional persistence"; the reference never wrote it).  The whole table -- entries,
+ * eviction order, counters -- as one flat [host] image of die_kv_snapshot_bytes(kv) bytes, and back into a table
+ * created with the same max_size and policy.  Values are the caller's 64-bit handles, stored as they are.
+ * Not for tables that belong to a die_pipeline_t (their values are result-row handles).  Both synchronise. */
+uint64_t die_kv_snapshot_bytes(die_kv_t* kv);
+die_status_t die_kv_snapshot_sync(die_kv_t* kv, void* image /*[host]*/, uint64_t image_bytes, die_stream_t stream);
+die_status_t die_kv_restore_sync(die_kv_t* kv, const void* image /*[host]*/, uint64_t image_bytes, die_stream_t stream);
 /* Housekeeping that has no counterpart in the reference: renumber the LRU log and/or rebuild the
  * table when tombstones pile up.  Called automatically by the batch entry points when their
  * conservative host-side bounds require it; force != 0 does both now.  Synchronises. */

@@ -140,17 +140,21 @@ class PortEntry:
 
 
 class PortKVCache:
-    """Restates KVCache with eviction_policy='lru' (kvstore.py:26-236).
+    """Restates KVCache (kvstore.py:26-236) for the three eviction policies: "lru" (OrderedDict of
+    accesses), "lfu" (dict key -> use count; victim = first key with the smallest count, kvstore.py:94-98) and
+    "fifo" (victim = first key of the cache dict itself, kvstore.py:99-102).
 
     ``clock`` replaces ``time.time`` (kvstore.py:78,127,128,159,204)."""
 
     def __init__(self, max_size: int = 1000, default_ttl: Optional[float] = None,
-                 clock: Callable[[], float] = None) -> None:
+                 clock: Callable[[], float] = None, policy: str = "lru") -> None:
         self.max_size = max_size
         self.default_ttl = default_ttl
         self.clock = clock
+        self.policy = policy.lower()
         self.cache: Dict[str, PortEntry] = {}
         self.order: "OrderedDict[str, float]" = OrderedDict()  # LRU list, head = oldest
+        self.counts: Dict[str, int] = {}                        # LFU: _access_count (kvstore.py:67-68)
         self.hits = self.misses = self.evictions = 0
 
     # kvstore.py:200-204 -- strict '>' ; ttl None never expires
@@ -159,18 +163,27 @@ class PortKVCache:
 
     # kvstore.py:71-78
     def _touch(self, key: str) -> None:
-        if key in self.order:
-            self.order.move_to_end(key)
-        else:
-            self.order[key] = self.clock()
+        if self.policy == "lru":
+            if key in self.order:
+                self.order.move_to_end(key)
+            else:
+                self.order[key] = self.clock()
+        elif self.policy == "lfu":  # kvstore.py:79-80
+            self.counts[key] = self.counts.get(key, 0) + 1
 
     # kvstore.py:82-93 -- counter bumped BEFORE the pop, so it counts even if the pop raises
     def _make_room(self) -> None:
         if len(self.cache) < self.max_size:
             return
         self.evictions += 1
-        victim = next(iter(self.order))  # StopIteration when nothing is stamped
-        del self.order[victim]
+        if self.policy == "lru":
+            victim = next(iter(self.order))  # StopIteration when nothing is stamped
+            del self.order[victim]
+        elif self.policy == "lfu":
+            victim = min(self.counts.items(), key=lambda x: x[1])[0]  # ValueError when nothing is counted
+            del self.counts[victim]
+        else:
+            victim = next(iter(self.cache))  # FIFO: insertion order of the cache dict; StopIteration when empty
         del self.cache[victim]
 
     # kvstore.py:104-134
@@ -212,12 +225,14 @@ class PortKVCache:
         if key in self.cache:
             del self.cache[key]
             self.order.pop(key, None)
+            self.counts.pop(key, None)
             return True
         return False
 
     def clear(self) -> None:  # kvstore.py:189-198
         self.cache.clear()
         self.order.clear()
+        self.counts.clear()
         self.hits = self.misses = self.evictions = 0
 
     def contains(self, key: str) -> bool:  # kvstore.py:221-228
@@ -239,7 +254,7 @@ class PortKVCache:
         return {"hits": self.hits, "misses": self.misses,
                 "hit_rate": self.hits / total if total > 0 else 0,
                 "size": len(self.cache), "max_size": self.max_size,
-                "evictions": self.evictions, "eviction_policy": "lru"}
+                "evictions": self.evictions, "eviction_policy": self.policy}
 
     def lru_order(self) -> List[str]:
         return list(self.order)

@@ -135,10 +135,10 @@ def gen_route():
 
 
 # ----------------------------------------------------------------------------- kv traces
-def run_kv_trace(max_size, default_ttl, ops):
+def run_kv_trace(max_size, default_ttl, ops, policy="lru"):
     """ops: list of [op, *args]. Returns results list + final state (all from the reference)."""
     CLOCK[0] = 1000.0
-    kv = ref_kv.KVCache(max_size=max_size, eviction_policy="lru", default_ttl=default_ttl)
+    kv = ref_kv.KVCache(max_size=max_size, eviction_policy=policy, default_ttl=default_ttl)
     res = []
     for op in ops:
         name = op[0]
@@ -171,11 +171,20 @@ def run_kv_trace(max_size, default_ttl, ops):
                 raise AssertionError(name)
         except StopIteration:
             r = "!StopIteration"
+        except ValueError:  # LFU: min() of an empty _access_count (kvstore.py:95)
+            r = "!ValueError"
         res.append(r)
     entries = {k: [e.value, e.created_at, e.last_accessed, e.access_count, e.ttl]
                for k, e in kv.cache.items()}
-    return {"max_size": max_size, "default_ttl": default_ttl, "ops": ops, "results": res,
-            "final": {"lru": list(kv._access_order), "entries": entries, "stats": kv.get_stats()}}
+    final = {"entries": entries, "stats": kv.get_stats(), "cache_order": list(kv.cache)}
+    if policy == "lru":
+        final["lru"] = list(kv._access_order)
+    elif policy == "lfu":
+        final["lfu"] = [[k, c] for k, c in kv._access_count.items()]
+    out = {"max_size": max_size, "default_ttl": default_ttl, "ops": ops, "results": res, "final": final}
+    if policy != "lru":
+        out["policy"] = policy
+    return out
 
 
 def random_kv_ops(seed, n_ops, n_keys, with_batch_set, ttl_choices):
@@ -257,6 +266,34 @@ def gen_kv():
     for seed, ms, dttl, n_ops, n_keys, wbs, ttls in cfgs:
         traces[f"random_{seed}"] = run_kv_trace(ms, dttl, random_kv_ops(seed, n_ops, n_keys, wbs, ttls))
     dump("kv_traces.json", traces)
+
+
+def gen_kv_policies():
+    """LFU and FIFO (src/kvstore.py:67-69,79-80,94-102): constructed cases + random differential traces."""
+    traces = {}
+    fill3 = [["set", "H", 1, None], ["set", "B", 2, None], ["set", "C", 3, None]]
+    for pol in ("lfu", "fifo"):
+        traces[f"{pol}_evict_basic"] = run_kv_trace(3, None, fill3 + [["get", "H"], ["get", "H"], ["get", "C"], ["set", "A", 4, None],
+                                                                     ["stats"], ["set", "D", 5, None], ["get", "B"], ["get", "A"],
+                                                                     ["stats"]], pol)
+        traces[f"{pol}_overwrite_moves"] = run_kv_trace(3, None, fill3 + [["get", "B"], ["set", "H", 9, None], ["set", "X", 4, None],
+                                                                         ["set", "Y", 5, None], ["stats"]], pol)
+        traces[f"{pol}_batch_set_empty"] = run_kv_trace(3, None, [["batch_set", [[f"k{i}", i] for i in range(5)], None], ["stats"]], pol)
+        traces[f"{pol}_batch_set_full"] = run_kv_trace(3, None, fill3 + [["get", "H"], ["batch_set", [["X", 7], ["Y", 8]], None],
+                                                                        ["stats"], ["batch_set", [["P", 1], ["Q", 2], ["R", 3], ["S", 4]], None],
+                                                                        ["stats"], ["get", "S"], ["set", "T", 5, None], ["stats"]], pol)
+        traces[f"{pol}_max_size_0"] = run_kv_trace(0, None, [["set", "a", 1, None], ["stats"]], pol)
+        traces[f"{pol}_ttl"] = run_kv_trace(2, None, [["set", "a", 1, 10.0], ["set", "b", 2, None], ["get", "a"], ["advance", 11.0],
+                                                     ["set", "c", 3, None], ["get", "a"], ["get", "b"], ["len"], ["stats"]], pol)
+        cfgs = [(11, 3, None, 500, 8, True, [None, None, 1.0, 5.0]),
+                (12, 8, 4.0, 800, 20, True, [None, None, 0, 0.5, 2.0, 20.0]),
+                (13, 16, None, 1000, 40, False, [None]),
+                (14, 24, 6.0, 1200, 60, True, [None, None, 2.0, 50.0]),
+                (15, 64, 30.0, 1500, 200, False, [None, None, None, 3.0]),
+                (16, 1, None, 200, 4, True, [None, 1.0])]
+        for seed, ms, dttl, n_ops, n_keys, wbs, ttls in cfgs:
+            traces[f"{pol}_random_{seed}"] = run_kv_trace(ms, dttl, random_kv_ops(seed, n_ops, n_keys, wbs, ttls), pol)
+    dump("kv_policy_traces.json", traces)
 
 
 # ----------------------------------------------------------------------------- batcher
@@ -486,6 +523,7 @@ def gen_pipeline():
 if __name__ == "__main__":
     gen_route()
     gen_kv()
+    gen_kv_policies()
     gen_batcher()
     gen_worker()
     gen_pipeline()

@@ -68,11 +68,105 @@ def test_reference_trace_on_drop_in_kvcache(name):
     assert kv.max_size == t["max_size"] and kv.eviction_policy == "lru"
 
 
-def test_unsupported_policies_raise():
+def replay_policy_trace_on_drop_in(t):
     from die.kvstore import KVCache
-    for pol in ("lfu", "FIFO"):
-        with pytest.raises(NotImplementedError):
-            KVCache(4, pol)
+    clock = [1000.0]
+    kv = KVCache(t["max_size"], t["policy"], t["default_ttl"], clock=lambda: clock[0])
+    res = []
+    for op in t["ops"]:
+        name = op[0]
+        try:
+            if name == "advance":
+                clock[0] += op[1]
+                r = None
+            elif name == "set":
+                r = kv.set(op[1], op[2], ttl=op[3])
+            elif name == "get":
+                r = kv.get(op[1], "DFLT")
+            elif name == "batch_get":
+                r = kv.batch_get(op[1])
+            elif name == "batch_set":
+                r = kv.batch_set(dict((k, v) for k, v in op[1]), ttl=op[2])
+            elif name == "delete":
+                r = kv.delete(op[1])
+            elif name == "contains":
+                r = op[1] in kv
+            elif name == "len":
+                r = len(kv)
+            elif name == "clear":
+                r = kv.clear()
+            elif name == "stats":
+                r = kv.get_stats()
+        except StopIteration:
+            r = "!StopIteration"
+        except ValueError:
+            r = "!ValueError"
+        res.append(r)
+    return kv, res
+
+
+@pytest.mark.parametrize("name", sorted(load_golden("kv_policy_traces.json").keys()))
+def test_reference_lfu_fifo_trace_on_drop_in_kvcache(name):
+    """LFU and FIFO (kvstore.py:67-69,79-80,94-102): traces recorded from the reference's KVCache, replayed on the
+    device table -- every result, the counters, every entry's metadata, the LFU use counts in the order the keys
+    were first counted, the FIFO insertion order.  Bit-exact, including the ValueError / StopIteration cases."""
+    t = load_golden("kv_policy_traces.json")[name]
+    kv, res = replay_policy_trace_on_drop_in(t)
+    assert res == t["results"]
+    assert kv.get_stats() == t["final"]["stats"]
+    got = {k: [e.value, e.created_at, e.last_accessed, e.access_count, e.ttl] for k, e in kv.cache.items()}
+    assert got == t["final"]["entries"]
+    if t["policy"] == "lfu":
+        assert [[k, c] for k, c in kv._access_count.items()] == t["final"]["lfu"]
+    elif not any(r in ("!StopIteration",) for r in t["results"] if isinstance(r, str)):
+        assert list(kv.cache) == t["final"]["cache_order"]  # FIFO: the dict's insertion order is the eviction order
+
+
+def test_unknown_policy_is_refused():
+    from die.kvstore import KVCache
+    with pytest.raises(ValueError):
+        KVCache(4, "mru")
+
+
+@pytest.mark.parametrize("policy", ["lru", "lfu", "fifo"])
+def test_snapshot_restore_round_trip(policy, tmp_path):
+    """save -> fresh cache -> load: the restored table answers, counts and evicts exactly like the original (the
+    twin keeps running beside it as the reference), whatever the policy."""
+    from die.kvstore import KVCache
+    rng = np.random.default_rng(17)
+    clock = [50.0]
+    a = KVCache(40, policy, 30.0, clock=lambda: clock[0])
+
+    def drive(kv, seed, n):
+        r = np.random.default_rng(seed)
+        out = []
+        for _ in range(n):
+            clock_step = float(r.choice([0.0, 0.5, 2.0]))
+            clock[0] += clock_step
+            k = "k%d" % int(r.integers(0, 90))
+            if r.random() < 0.5:
+                out.append(kv.get(k, "DFLT"))
+            else:
+                kv.set(k, int(r.integers(0, 10 ** 6)), ttl=None if r.random() < 0.7 else 5.0)
+        return out
+
+    drive(a, 1, 300)
+    t_saved = clock[0]
+    path = str(tmp_path / "cache.img")
+    a.save(path)
+    b = KVCache(40, policy, 30.0, clock=lambda: clock[0])
+    b.load(path)
+    assert b.get_stats() == a.get_stats() and list(b.cache) == list(a.cache)
+    res_a = drive(a, 2, 300)
+    state_a = (a.get_stats(), {k: (e.value, e.access_count) for k, e in a.cache.items()})
+    clock[0] = t_saved
+    res_b = drive(b, 2, 300)
+    assert res_a == res_b
+    assert state_a == (b.get_stats(), {k: (e.value, e.access_count) for k, e in b.cache.items()})
+    assert a.get_stats()["evictions"] > 0
+    with pytest.raises(Exception):
+        KVCache(41, policy).load(path)  # another shape: refused
+    del rng
 
 
 # ------------------------------------------------------------------ batched device API vs the oracle

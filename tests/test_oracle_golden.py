@@ -79,7 +79,7 @@ def test_health_transitions():
 # ----------------------------------------------------------------------------- kv
 def replay_kv_trace_on_port(t):
     clock = [1000.0]
-    kv = rp.PortKVCache(t["max_size"], t["default_ttl"], clock=lambda: clock[0])
+    kv = rp.PortKVCache(t["max_size"], t["default_ttl"], clock=lambda: clock[0], policy=t.get("policy", "lru"))
     res = []
     for op in t["ops"]:
         name = op[0]
@@ -107,6 +107,8 @@ def replay_kv_trace_on_port(t):
                 r = kv.stats()
         except StopIteration:
             r = "!StopIteration"
+        except ValueError:
+            r = "!ValueError"
         res.append(r)
     return kv, res
 
@@ -121,6 +123,19 @@ def test_kv_trace_matches_reference(name):
     got = {k: [e.value, e.created_at, e.last_accessed, e.access_count, e.ttl] for k, e in kv.cache.items()}
     assert got == t["final"]["entries"]
     assert list(got) == list(t["final"]["entries"])  # dict insertion order too
+
+
+@pytest.mark.parametrize("name", sorted(load_golden("kv_policy_traces.json").keys()))
+def test_kv_policy_trace_matches_reference(name):
+    """LFU / FIFO traces recorded from the reference's KVCache (kvstore.py:67-69,79-80,94-102)."""
+    t = load_golden("kv_policy_traces.json")[name]
+    kv, res = replay_kv_trace_on_port(t)
+    assert res == t["results"]
+    assert kv.stats() == t["final"]["stats"]
+    got = {k: [e.value, e.created_at, e.last_accessed, e.access_count, e.ttl] for k, e in kv.cache.items()}
+    assert got == t["final"]["entries"] and list(got) == t["final"]["cache_order"]
+    if t["policy"] == "lfu":
+        assert [[k, c] for k, c in kv.counts.items()] == t["final"]["lfu"]
 
 
 # ----------------------------------------------------------------------------- batcher / worker
