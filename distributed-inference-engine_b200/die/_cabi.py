@@ -51,6 +51,8 @@ SIGNATURES = {
     "die_debug_random_read": (c_int32, [P, c_uint64, c_int32, c_int32, c_int32, c_uint64, P, P]),
     "die_route_md5": (c_int32, [P, P, c_int32, c_int32, P, P, c_int32, c_int32, P, P, P, P]),
     "die_bucket_by_shard": (c_int32, [P, c_int32, c_int32, P, P, P, P]),
+    "die_bucket_scatter_rows": (c_int32, [P, P, P, P, c_int32, c_int32, c_int32, c_int32, P, P, P]),
+    "die_bucket_gather_rows": (c_int32, [P, P, P, P, c_int32, c_int32, c_int32, c_int32, P, P, P, P]),
     "die_kv_create": (c_int32, [c_uint64, c_int32, c_double, POINTER(c_void_p)]),
     "die_kv_destroy": (c_int32, [P]),
     "die_kv_get_batch": (c_int32, [P, P, c_int32, c_double, P, P, P, P]),

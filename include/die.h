@@ -107,6 +107,18 @@ die_status_t die_route_md5(const uint8_t* key_bytes, const int64_t* key_off, int
  *   pos_out     [B]          : send position of request i (inverse of perm)                                  */
 die_status_t die_bucket_by_shard(const int32_t* shard, int32_t B, int32_t n_shards, int64_t* offsets_out,
                                  int32_t* perm_out, int32_t* pos_out, die_stream_t stream);
+/* Rows to / from per-shard regions after die_bucket_by_shard (same hand-off; used by the single-GPU coordinator):
+ * scatter writes row q of src [B, row_bytes] to dst [n_shards][cap][row_bytes] at (shard[q], pos[q] - offsets[shard[q]])
+ * and counts_out[s] = requests of shard s (uint32, device: the owner pass takes its batch size from there);
+ * gather is the way back to request order (zero rows where shard[q] is -1), with one optional byte per row (the hit
+ * flags) taken along.  row_bytes a multiple of 16, cap >= B. */
+die_status_t die_bucket_scatter_rows(const void* src, const int32_t* shard, const int32_t* pos, const int64_t* offsets,
+                                     int32_t B, int32_t n_shards, int32_t cap, int32_t row_bytes, void* dst,
+                                     uint32_t* counts_out, die_stream_t stream);
+die_status_t die_bucket_gather_rows(const void* src, const int32_t* shard, const int32_t* pos, const int64_t* offsets,
+                                    int32_t B, int32_t n_shards, int32_t cap, int32_t row_bytes, void* dst,
+                                    const uint8_t* flag_src /*optional [n_shards][cap]*/, uint8_t* flag_dst /*[B]*/,
+                                    die_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * K2/K3  KV store: GPU-resident open-addressing table keyed by the 128-bit MD5 of the key,

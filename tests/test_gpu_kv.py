@@ -396,3 +396,43 @@ def test_c4_full_size_probe_and_fill_by_construction():
     gone, _ = kv.contains_batch(dig(victims[-4096:]), now)
     kept, _ = kv.contains_batch(dig(survivors), now)
     assert not gone.any() and bool((kept.cpu().numpy()[survivors >= n_old] == 1).all())
+
+
+@pytest.mark.parametrize("policy,max_size,space,n_batches,max_b", [("fifo", 500, 900, 40, 300), ("fifo", 37, 60, 50, 30),
+                                                                   ("lfu", 64, 120, 40, 40), ("lfu", 9, 20, 40, 12)])
+def test_random_batches_match_oracle_lfu_fifo(policy, max_size, space, n_batches, max_b):
+    """The batched device API (duplicate keys inside a batch included) against the oracle applied op by op, for the
+    FIFO and LFU policies: hit / miss and values per op, counters, and the eviction order at the end."""
+    from die.kvstore import DeviceKV
+    rng = np.random.default_rng(max_size + space)
+    dkv = DeviceKV(max_size, None, policy=policy)
+    clock = [0.0]
+    port = rp.PortKVCache(max_size, None, clock=lambda: clock[0], policy=policy)
+    now, next_val = 10.0, 1
+    for b in range(n_batches):
+        now += 1.0
+        clock[0] = now
+        B = int(rng.integers(1, max_b + 1))
+        keys = ["k%d" % i for i in rng.integers(0, space, B)]
+        dig = md5_words(keys)
+        if rng.random() < 0.5:
+            hit, value = dkv.get_batch(dig, now)
+            want = [port.get(k, None) for k in keys]
+            assert [v if h == 1 else None for h, v in zip(hit.tolist(), value.tolist())] == want, b
+        else:
+            values = list(range(next_val, next_val + B))
+            next_val += B
+            dkv.set_batch(dig, torch.tensor(values, dtype=torch.int64, device="cuda"), now)
+            for k, v in zip(keys, values):
+                port.set(k, v)
+            assert dkv.sync_status()[0] == 0
+        st, ps = dkv.stats(), port.stats()
+        assert (st["hits"], st["misses"], st["evictions"], st["size"]) == (ps["hits"], ps["misses"], ps["evictions"], ps["size"]), b
+    d = dkv.dump()
+    order = [bytes(x) for x in d["digests"].numpy().view(np.uint8).reshape(-1, 16)]
+    if policy == "fifo":
+        assert order == [hashlib.md5(k.encode()).digest() for k in port.cache]
+    else:
+        assert order == [hashlib.md5(k.encode()).digest() for k in port.counts]
+        assert d["lfu_count"].tolist() == list(port.counts.values())
+    assert port.stats()["evictions"] > 0

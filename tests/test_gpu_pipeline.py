@@ -295,3 +295,62 @@ def test_benchmarked_configuration_vs_oracle():
     assert (st["hits"], st["misses"], st["evictions"], st["size"]) == (rs["hits"], rs["misses"], rs["evictions"], rs["size"])
     assert rs["size"] == kv_max and rs["evictions"] > 20 * B and rs["hits"] > 0
     assert lru_digests(pipe) == [hashlib.md5(k.encode()).digest() for k in rs["lru"]]
+
+
+@pytest.mark.parametrize("model", ["echo", "linear_tf32"])
+def test_coordinator_on_device_path_vs_oracle(model):
+    """die.Coordinator with caches larger than a batch: route (health gate + failover, router.py:140-221) -> bucket ->
+    per-shard regions -> each shard's owner pass with its request count taken on the device, on its own stream ->
+    gather.  Nothing of a batch comes back to the host.  Against OraclePipeline with the same unhealthy worker:
+    shard ids, hit flags, per-shard counters and LRU order bit-exact; outputs exact (echo) / within the TF32 bound."""
+    from die import Coordinator, ModelRegistry, Router
+    n, B, D, max_size, ttl = 4, 512, 128, 1500, 9.0
+    rng = np.random.default_rng(404)
+    w = (rng.standard_normal((D, D)) / np.sqrt(D)).astype(np.float32)
+    b = rng.standard_normal(D).astype(np.float32)
+    reg = ModelRegistry()
+    reg.register_model("m", "1", "/p", {}, {})
+    router = Router(reg)
+    for s in range(n):
+        reg.add_shard("m", "1", s, f"w{s}")
+        router.register_worker(f"w{s}", f"127.0.0.1:{9000 + s}")
+        router.mark_worker_success(f"w{s}")
+    for _ in range(3):
+        router.mark_worker_failure("w2")   # its keys fail over to healthy[md5 % 3]
+
+    if model == "echo":
+        fn = lambda rows: [np.stack([r, np.zeros_like(r)]) for r in rows]  # noqa: E731
+        co = Coordinator(router, "m", "1", max_size, B, D, model="echo", default_ttl=ttl)
+    else:
+        def fn(rows):
+            if not rows:
+                return []
+            xs = np.stack(rows)
+            y, bound = models.linear_f64(xs, w, b), models.linear_abs_bound(xs, w)
+            return [np.stack([y[i], bound[i]]) for i in range(len(rows))]
+        co = Coordinator(router, "m", "1", max_size, B, D, D, "linear_tf32", w, b, default_ttl=ttl)
+    assert co.on_device
+    ref = OraclePipeline(n, max_size, ttl, fn)
+    for _ in range(3):
+        ref.router.mark_worker_failure("w2")
+    now = 10.0
+    for step in range(24):
+        now += float(rng.choice([0.5, 2.0, 4.0]))
+        Bs = B if step % 3 else 300
+        keys = ["user-%010d" % i for i in rng.integers(0, 9000, Bs)]
+        x = rng.standard_normal((Bs, D)).astype(np.float32)
+        out, hit, shard = co.process(keys, torch.from_numpy(x).cuda(), now)
+        want = ref.process(keys, [x[i] for i in range(Bs)], now)
+        assert shard.tolist() == want["shard"] and 2 not in want["shard"], step
+        assert hit.tolist() == want["hit"], step
+        wv = np.stack(want["out"])
+        got = out.cpu().numpy()
+        if model == "echo":
+            assert np.array_equal(got, wv[:, 0].astype(np.float32)), step
+        else:
+            assert np.all(np.abs(got.astype(np.float64) - wv[:, 0]) <= 2.0 ** -10 * wv[:, 1] + 1e-6), step
+    for s in range(n):
+        st, ws = co.pipes[s].kv.stats(), ref.state()[s]
+        assert (st["hits"], st["misses"], st["evictions"], st["size"]) == (ws["hits"], ws["misses"], ws["evictions"], ws["size"])
+        assert lru_digests(co.pipes[s]) == [hashlib.md5(k.encode()).digest() for k in ws["lru"]]
+    assert sum(s_["evictions"] for s_ in ref.state()) > 0 and sum(s_["hits"] for s_ in ref.state()) > 0
