@@ -160,6 +160,119 @@ linear_tf32_kernel(const float* __restrict__ X, const float* __restrict__ W, con
     }
 }
 
+// Streaming form for large batches (the layer is HBM-bound: 32 flop per byte): persistent CTAs, one per SM, keep W in
+// shared memory for their whole life and walk the 128-row tiles of X with a two-deep cp.async pipeline -- tile t+1
+// travels while tile t is multiplied (tcgen05, accumulators in TMEM) and written back.  The consumed A buffer doubles
+// as the staging area of the epilogue (XOR-swizzled 16-byte chunks, so neither the row-per-lane writes out of TMEM nor
+// the row-per-warp reads for the 512-byte coalesced stores conflict on banks); all eight warps drain TMEM (warps w and
+// w+4 share a lane quarter and split its columns).
+__global__ void __launch_bounds__(TC_THREADS, 1)
+linear_tf32_stream_kernel(const float* __restrict__ X, const float* __restrict__ W, const float* __restrict__ bias,
+                          float* __restrict__ Y, int B, int K, int N, const uint32_t* __restrict__ n_rows_dev) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base;
+    __shared__ __align__(16) float s_bias[256];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int KB = K / 32, chunks_per_row = K / 4;
+    uint8_t* b_base = smem;                                    // W: KB blocks of [N rows x 128 B]
+    uint8_t* a_base0 = smem + (size_t)N * K * 4;               // two A tiles of KB blocks of [128 rows x 128 B]
+    const size_t a_bytes = (size_t)TC_M * K * 4;
+    const uint32_t ncols = pow2_cols((uint32_t)N);
+    if (n_rows_dev) B = min(B, (int)*n_rows_dev);
+    const int tiles = (B + TC_M - 1) / TC_M;
+    if (warp == 0) tc::tmem_alloc(&tmem_base, ncols);
+    if (tid == 32) tc::mbar_init(&bar, 1);
+    if (tid < N) s_bias[tid] = bias ? bias[tid] : 0.f;
+    for (int e = tid; e < N * chunks_per_row; e += TC_THREADS) {
+        const int r = e / chunks_per_row, ck = e - r * chunks_per_row;
+        cp_async16(b_base + (size_t)(ck >> 3) * ((size_t)N * 128) + tc::sw128_offset(r, ck & 7), W + (size_t)r * K + ck * 4, 16u);
+    }
+    auto load_tile = [&](int t, uint8_t* a_base) {
+        const int m0 = t * TC_M;
+        for (int e = tid; e < TC_M * chunks_per_row; e += TC_THREADS) {
+            const int r = e / chunks_per_row, ck = e - r * chunks_per_row;
+            const bool live = m0 + r < B;
+            cp_async16(a_base + (size_t)(ck >> 3) * (TC_M * 128) + tc::sw128_offset(r, ck & 7),
+                       X + (size_t)(live ? m0 + r : 0) * K + ck * 4, live ? 16u : 0u);
+        }
+    };
+    int t = (int)blockIdx.x;
+    if (t < tiles) load_tile(t, a_base0);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    const uint32_t taddr = tmem_base;
+    const int row_pitch = N * 4, vec_per_row = N / 4;  // N <= K here, so the staged rows fit the tile
+    const int col_half = (N / 2) % 32 == 0 ? N / 2 : N;  // columns per warp of a lane quarter (both warps, or warp < 4 only)
+    unsigned phase = 0;
+    for (int it = 0; t < tiles; t += (int)gridDim.x, ++it) {
+        uint8_t* a_cur = a_base0 + (size_t)(it & 1) * a_bytes;
+        const int t_next = t + (int)gridDim.x;
+        if (t_next < tiles) load_tile(t_next, a_base0 + (size_t)((it + 1) & 1) * a_bytes);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 1;" ::: "memory");  // tile t (and W) have landed
+        tc::fence_proxy_async_smem();
+        tc::fence_before_thread_sync();
+        __syncthreads();
+        tc::fence_after_thread_sync();
+        if (tid == 0) {
+            const uint32_t idesc = tc::instr_desc(tc::FMT_TF32, TC_M, (uint32_t)N);
+            const uint32_t a_s = tc::smem_u32(a_cur), b_s = tc::smem_u32(b_base);
+            for (int kb = 0; kb < KB; ++kb) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    tc::mma_tf32(taddr, tc::smem_desc_k_major_sw128(a_s + kb * (TC_M * 128) + j * 32),
+                                 tc::smem_desc_k_major_sw128(b_s + kb * (N * 128) + j * 32), idesc, (kb | j) != 0);
+            }
+            tc::mma_commit(&bar);
+        }
+        tc::mbar_wait(&bar, phase & 1u);
+        ++phase;
+        tc::fence_after_thread_sync();
+        // epilogue: TMEM -> registers (+bias) -> the consumed A tile (row r, 16-byte chunk c at c ^ (r & 7)) -> global
+        uint8_t* stage = a_cur;
+        {
+            const int q = warp & 3, row = q * 32 + lane;
+            const int c_lo = col_half == N ? 0 : (warp >> 2) * col_half;
+            const int c_hi = col_half == N ? (warp < 4 ? N : 0) : c_lo + col_half;
+            for (int c0 = c_lo; c0 < c_hi; c0 += 32) {
+                uint32_t v[32];
+                tc::tmem_ld_32x32(taddr + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    if (c0 + j < N) {
+                        const float4 bv = *reinterpret_cast<const float4*>(s_bias + c0 + j);
+                        float4 o;
+                        o.x = __uint_as_float(v[j + 0]) + bv.x;
+                        o.y = __uint_as_float(v[j + 1]) + bv.y;
+                        o.z = __uint_as_float(v[j + 2]) + bv.z;
+                        o.w = __uint_as_float(v[j + 3]) + bv.w;
+                        const int chunk = (c0 + j) >> 2;
+                        *reinterpret_cast<float4*>(stage + (size_t)row * row_pitch + (size_t)((chunk ^ (row & 7)) << 4)) = o;
+                    }
+                }
+            }
+        }
+        tc::fence_before_thread_sync();
+        __syncthreads();
+        const int m0 = t * TC_M;
+        const int rows = min(TC_M, B - m0);
+        for (int e = tid; e < rows * vec_per_row; e += TC_THREADS) {
+            const int r = e / vec_per_row, c = e - r * vec_per_row;
+            const int4 o = *reinterpret_cast<const int4*>(stage + (size_t)r * row_pitch + (size_t)((c ^ (r & 7)) << 4));
+            stg_stream(reinterpret_cast<int4*>(Y + (size_t)(m0 + r) * N) + c, o);
+        }
+        __syncthreads();  // the staging reads are done: the next iteration's prefetch may overwrite this buffer
+    }
+    if (warp == 0) {
+        tc::fence_after_thread_sync();
+        tc::tmem_dealloc(taddr, ncols);
+    }
+}
+
 static die_status_t tf32_launch(const float* X, const float* W, const float* b, float* Y, int B, int K, int N,
                                 const uint32_t* n_rows_dev, const TcScatter* scatter, cudaStream_t s) {
     if (B == 0) return DIE_OK;
@@ -167,9 +280,21 @@ static die_status_t tf32_launch(const float* X, const float* W, const float* b, 
         DIE_FAIL(DIE_ERR_UNSUPPORTED, "linear tf32: needs K %% 32 == 0 and N in [16,256] multiple of 16 (K=%d N=%d)", K, N);
     if ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(Y)) & 15)
         DIE_FAIL(DIE_ERR_UNSUPPORTED, "linear tf32: X, W and Y must be 16-byte aligned");
+    const int tiles = ceil_div(B, TC_M);
+    {   // large batches: the persistent streaming form (N a multiple of 32 chunks it can swizzle, rows fit the A tile)
+        const size_t smem_s = (size_t)N * K * 4 + 2 * (size_t)TC_M * K * 4 + 1024;
+        if (!scatter && tiles >= 2 * num_sms() && smem_s <= 200 * 1024 && N <= K && N % 32 == 0) {
+            static bool configured_s = false;
+            if (!configured_s) {
+                DIE_CUDA(cudaFuncSetAttribute(linear_tf32_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+                configured_s = true;
+            }
+            DIE_LAUNCH(ST_MODEL, s, linear_tf32_stream_kernel<<<num_sms(), TC_THREADS, smem_s, s>>>(X, W, b, Y, B, K, N, n_rows_dev));
+            return DIE_OK;
+        }
+    }
     // split the columns over CTAs until the grid covers the SMs (the layer is bandwidth/latency bound:
     // more CTAs = more loads in flight; X tiles are re-read from L2, not from HBM)
-    const int tiles = ceil_div(B, TC_M);
     int n_split = 1;
     while (tiles * n_split * 2 <= num_sms() && (N / (n_split * 2)) >= 32 && (N / (n_split * 2)) % 16 == 0 &&
            N % (n_split * 2) == 0)

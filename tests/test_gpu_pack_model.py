@@ -111,7 +111,8 @@ def test_linear_fp32_within_tolerance_of_f64_oracle(B, K, N):
     assert np.all(np.abs(y.astype(np.float64) - want) <= tol)
 
 
-@pytest.mark.parametrize("B,K,N", [(4096, 128, 128), (1, 128, 128), (129, 32, 16), (1000, 64, 256), (3670, 128, 128), (300, 256, 64)])
+@pytest.mark.parametrize("B,K,N", [(4096, 128, 128), (1, 128, 128), (129, 32, 16), (1000, 64, 256), (3670, 128, 128), (300, 256, 64),
+                                   (37950, 128, 128), (40001, 64, 64), (38000, 128, 32)])  # the last three: streaming form
 def test_linear_tf32_tensor_core_within_tolerance(B, K, N):
     """tcgen05 kind::tf32 path.  Tolerance (oracle/models.py): |d| <= 2**-10 * sum_k |x_k w_k| + 1e-6."""
     from die import _cabi, ops
