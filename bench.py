@@ -245,18 +245,18 @@ def workload_config(n_gpus):
 # clocks
 # ----------------------------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    """SM clock and throttle reasons while the timed region executes (pynvml = what nvidia-smi reads).
+    """SM clock and throttle reasons while the timed region executes (pynvml = what nvidia-smi reads), every
+    `period` (12 ms: a 20-step region of ~55 ms gets 3-4 samples; the recipe's 200 ms would give none).
 
-    An NVML query is not free here: it takes 2-3 ms and, on these boxes, CUDA-graph launches issued meanwhile
-    wait for it (a 2 ms polling period slowed the step 6x).  So the sampler never queries while the host is
-    still submitting work: the bench calls sample_now() right after the last step of the timed region is
-    enqueued, i.e. while the GPU is still executing that region, and again every `period` (the recipe's 200 ms)
-    only if the region lasts that long."""
+    An NVML query takes 2-3 ms during which a kernel launch issued by this process waits.  The timed region is
+    a handful of long launches (one persistent kernel per 16 batches, ~0.3 ms each) that the host enqueues far ahead
+    of the GPU, so a stalled launch call does not reach the device-side clock; bench.py prints the measured cost of the
+    sampler (`nvml_ms_per_sample`) and DIE_BENCH_SAMPLER_MS=0 turns it off for an A/B."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.samples, self.reasons, self.stop_flag, self.max_mhz = [], set(), False, None
-        self.period = float(os.environ.get("DIE_BENCH_SAMPLER_MS", "200")) / 1e3
+        self.period = float(os.environ.get("DIE_BENCH_SAMPLER_MS", "12")) / 1e3
         self.query_s = 0.0
         self.wake = threading.Event()
         self.requested = self.served = 0
@@ -301,11 +301,9 @@ class ClockSampler(threading.Thread):
             self._query()           # periodic (timeout) or on demand (sample_now)
             self.served = max(self.served, want)
 
-    def sample_now(self, burst_period=0.015):
-        """Everything of the timed region is enqueued: from here on a query cannot hold up a launch, so sample
-        now and then every `burst_period` seconds until result() is called (>= 3 samples for a region >= 50 ms)."""
+    def sample_now(self):
+        """One more sample right now (called when the last step of the timed region has been enqueued)."""
         self.requested += 1
-        self.period = burst_period
         self.wake.set()
 
     def result(self):
@@ -319,8 +317,8 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
                 "samples": len(s), "period_ms": 1e3 * self.period,
                 "nvml_ms_per_sample": round(1e3 * self.query_s / len(s), 3) if s else None,
-                "when": "from the moment the last step of the timed region was enqueued, every 15 ms while the GPU was "
-                        "still executing it (an NVML query stalls CUDA-graph launches issued meanwhile)"}
+                "when": "every period_ms from the start of the timed region to its end, plus once when its last step was "
+                        "enqueued"}
 
 
 def ncu_traffic(kernel_name):

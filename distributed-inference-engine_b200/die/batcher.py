@@ -217,10 +217,24 @@ def pack_requests(inputs: List[Any], dtype=None, Lpad: Optional[int] = None) -> 
         values = torch.cat([x.reshape(-1) for x in inputs]) if sum(lens) else torch.zeros(
             4, dtype=dtype or inputs[0].dtype, device="cuda")
     else:
-        arrs = [np.asarray(x, dtype=dtype or np.float32).reshape(-1) for x in inputs]
-        lens = [int(a.size) for a in arrs]
-        flat = np.concatenate(arrs) if sum(lens) else np.zeros(4, dtype=dtype or np.float32)
-        values = torch.from_numpy(flat).pin_memory().to("cuda", non_blocking=True)
+        want = np.dtype(dtype or np.float32)
+        if type(inputs[0]) is np.ndarray and inputs[0].dtype == want and inputs[0].ndim == 1 and \
+                type(inputs[-1]) is np.ndarray and inputs[-1].ndim == 1:
+            arrs = inputs  # the usual case: numpy rows as they are (np.concatenate casts a stray dtype, rejects a stray shape)
+        else:
+            arrs = [np.asarray(x, dtype=want).reshape(-1) for x in inputs]
+        lens = list(map(len, arrs))
+        total = sum(lens)
+        # one concatenate straight into a reusable pinned buffer, one H2D copy
+        stage = ops.pinned_staging("payload", max(total, 4) * want.itemsize)
+        host = stage.numpy()[:max(total, 4) * want.itemsize].view(want)
+        if total:
+            np.concatenate(arrs, out=host[:total])
+        else:
+            host[:] = 0
+        values = torch.empty(max(total, 4), dtype=torch.from_numpy(host[:1]).dtype, device="cuda")
+        values.copy_(torch.from_numpy(host), non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the staging buffer is reused by the next call
     off = np.zeros(len(lens) + 1, dtype=np.int64)
     np.cumsum(lens, out=off[1:])
     per16 = max(16 // values.element_size(), 1)

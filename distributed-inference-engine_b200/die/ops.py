@@ -14,6 +14,20 @@ from . import _cabi
 from ._cabi import check, ptr, require_cuda, stream_ptr
 
 
+_PINNED = {}
+
+
+def pinned_staging(tag: str, nbytes: int) -> torch.Tensor:
+    """A reusable pinned host buffer of at least nbytes (uint8), one per tag: allocating pinned memory costs a
+    millisecond, so the Python-object edge of the drop-in classes stages its one H2D copy per batch through these."""
+    buf = _PINNED.get(tag)
+    if buf is None or buf.numel() < nbytes:
+        cap = 1 << max(int(nbytes - 1).bit_length(), 12)
+        buf = torch.empty(cap, dtype=torch.uint8).pin_memory()
+        _PINNED[tag] = buf
+    return buf
+
+
 class KeyBatch:
     """CSR of UTF-8 key bytes on the device (`key.encode()` of model_registry.py:159)."""
 
@@ -25,20 +39,40 @@ class KeyBatch:
 
     @staticmethod
     def encode_host(keys: Sequence[str]):
-        """-> (uint8[total], int64[B+1]) numpy arrays."""
-        enc = [k.encode() for k in keys]
-        off = np.zeros(len(enc) + 1, dtype=np.int64)
-        if enc:
-            np.cumsum([len(e) for e in enc], out=off[1:])
-        data = np.frombuffer(b"".join(enc), dtype=np.uint8) if off[-1] else np.zeros(0, dtype=np.uint8)
+        """-> (uint8[total], int64[B+1]) numpy arrays: `key.encode()` of every key, back to back.
+
+        ASCII keys (the common case) are encoded with one join + one encode, their byte lengths are their
+        character counts; anything else falls back to one encode per key."""
+        off = np.zeros(len(keys) + 1, dtype=np.int64)
+        if not keys:
+            return np.zeros(0, dtype=np.uint8), off
+        joined = "".join(keys)
+        raw = joined.encode()
+        if len(raw) == len(joined):
+            np.cumsum(np.fromiter(map(len, keys), dtype=np.int64, count=len(keys)), out=off[1:])
+        else:
+            enc = [k.encode() for k in keys]
+            np.cumsum(np.fromiter(map(len, enc), dtype=np.int64, count=len(enc)), out=off[1:])
+            raw = b"".join(enc)
+        data = np.frombuffer(raw, dtype=np.uint8) if off[-1] else np.zeros(0, dtype=np.uint8)
         return data, off
 
     @classmethod
     def from_strings(cls, keys: Sequence[str], device="cuda") -> "KeyBatch":
+        """Key strings -> device CSR with ONE host-to-device copy (bytes and offsets share a pinned staging buffer)."""
         require_cuda()
         data, off = cls.encode_host(keys)
-        kb = torch.from_numpy(data.copy()).to(device) if data.size else torch.zeros(16, dtype=torch.uint8, device=device)
-        return cls(kb, torch.from_numpy(off).to(device))
+        nb, no = int(data.size), off.size * 8
+        pad = (-nb) % 8 + 16                      # 16 bytes of slack after the keys, offsets 8-byte aligned
+        stage = pinned_staging("keys", nb + pad + no)
+        host = stage.numpy()
+        host[:nb] = data
+        host[nb:nb + pad] = 0
+        host[nb + pad:nb + pad + no] = off.view(np.uint8)
+        dev = torch.empty(nb + pad + no, dtype=torch.uint8, device=device)
+        dev.copy_(stage[:nb + pad + no], non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the staging buffer is reused by the next call
+        return cls(dev[:nb + pad], dev[nb + pad:].view(torch.int64))
 
 
 def route_md5(keys: KeyBatch, n_shards: int, routable: Optional[torch.Tensor] = None,
