@@ -117,6 +117,7 @@ __device__ __forceinline__ unsigned ld_relaxed_u32(const unsigned int* p) {
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ int g_ps_dbg = 0;  // DIE_STEP_DEBUG as seen by device helpers (timing experiments)
 __device__ int g_ps_poll_ns = 0;  // pause between polls of the barrier counter (tuning knob, DIE_STEP_POLL_NS)
 __device__ __forceinline__ void grid_wait(StepGrid* g, unsigned target, KvState* st) {
     if (threadIdx.x == PS_BAR_THREAD) {
@@ -222,7 +223,7 @@ __device__ __forceinline__ unsigned ps_window_bitmap(const KvView& kv, unsigned 
     for (int k = 0; k < PS_PER; ++k) {
         const unsigned long long p = base + (unsigned long long)(k * PS_THREADS + tid);
         const bool cur = p < t_set && stamp[k] == p;
-        // a current record may be evicted in phase C, which looks at the successor slot: bring it to L2 now
+        // a current record may be evicted in phase C and its successor slot looked at one phase later: bring it to L2
         if (cur) prefetch_l2(&kv.slots[((unsigned long long)slot[k] + 1ull) & kv.mask]);
         const unsigned m = __ballot_sync(0xffffffffu, cur);
         if (lane == 0) {
@@ -248,9 +249,8 @@ __device__ __forceinline__ unsigned ps_window_bitmap(const KvView& kv, unsigned 
 
 // Window CTA, phase C: evict the chunk's current records whose rank among all current records of the window is
 // below e (oldest first, kvstore.py:89-91).
-//   - a victim whose successor slot is EMPTY becomes EMPTY itself instead of a tombstone: no probe chain can continue
-//     through it (it would stop at the successor anyway) and nobody inserts during this phase; fewer tombstones =
-//     fewer table rebuilds;
+//   - victims become tombstones here; ps_window_relax turns those whose successor slot is EMPTY into EMPTY during the
+//     next batch's phase A (off this phase's critical path);
 //   - the victim's result row goes back to the free queue at position free_tail + rank: ranks are unique, so the
 //     evictions need no atomic, and the counters (size, evictions, head) are settled by one thread after
 //     barrier 3 (ps_settle_evictions) so that nobody reads them while they change;
@@ -258,8 +258,10 @@ __device__ __forceinline__ unsigned ps_window_bitmap(const KvView& kv, unsigned 
 __device__ __forceinline__ void ps_window_evict(const KvView& kv, StepGrid* g, int chunk, int n_chunks,
                                                 unsigned long long base, unsigned long long tail0, unsigned long long t_set,
                                                 unsigned long long e, const uint32_t (&slot)[PS_PER], const unsigned* s_mask,
-                                                const unsigned* s_pref) {
+                                                const unsigned* s_pref, uint32_t (&evicted)[PS_PER]) {
     const int tid = threadIdx.x;
+#pragma unroll
+    for (int k = 0; k < PS_PER; ++k) evicted[k] = PS_LOG_NONE;
     if (e == 0) return;  // uniform for the grid
     // tail0 = free_tail as every window CTA read it in phase B (nothing pushes between that read and barrier 3 except
     // these evictions); the queue's tail moves past them here, before any push of the next batch can happen
@@ -293,23 +295,18 @@ __device__ __forceinline__ void ps_window_evict(const KvView& kv, StepGrid* g, i
         sidx[k] = victim[k] ? slot[k] : 0u;  // the log entry read for the bitmap
     }
     unsigned long long row[PER];
-    u128 next[PER];
 #pragma unroll
-    for (int k = 0; k < PER; ++k) {
-        if (victim[k]) {
-            row[k] = ld_u64_cg(&kv.slots[sidx[k]].value);
-            next[k] = ld_fp(&kv.slots[((unsigned long long)sidx[k] + 1ull) & kv.mask]);
-        }
-    }
+    for (int k = 0; k < PER; ++k)
+        if (victim[k]) row[k] = ld_u64_cg(&kv.slots[sidx[k]].value);  // same sector as the stamp read for the bitmap
     unsigned n_tomb = 0;
 #pragma unroll
     for (int k = 0; k < PER; ++k) {
         if (!victim[k]) continue;
         Slot* sl = &kv.slots[sidx[k]];
-        const bool tomb = !fp_empty(next[k]);
-        st128(sl, tomb ? u128{FP_TOMB_WORD, FP_TOMB_WORD} : u128{0ull, 0ull});
+        st128(sl, u128{FP_TOMB_WORD, FP_TOMB_WORD});  // ps_window_relax turns it into EMPTY later where that is allowed
         sl->stamp = 0ull;
-        n_tomb += tomb;
+        n_tomb += 1u;
+        evicted[k] = sidx[k];
         if (kv.free_rows) kv.free_rows[(tail0 + rank[k]) & kv.row_mask] = (uint32_t)row[k];
         if (rank[k] == e - 1) g->hnew = base + (unsigned long long)(k * PS_THREADS + tid) + 1;  // the newest victim
     }
@@ -336,6 +333,32 @@ __device__ __forceinline__ void ps_window_evict(const KvView& kv, StepGrid* g, i
         if (r < e) kv.st->status = DIE_ERR_INVALID;  // unreachable while max_batch <= max_size
         g->hnew = p;
     }
+}
+
+// Window CTA, next batch's phase A (idle otherwise): an evicted slot whose successor is EMPTY holds no probe chain up
+// (a chain through it would stop at the successor anyway), so it goes back to EMPTY instead of staying a tombstone --
+// most evicted slots do at a live load of 1/8, which is what keeps table rebuilds thousands of batches apart.  Done
+// here rather than in the eviction itself because the successor is a random DRAM line and phase C is on the step's
+// critical path.  Probes of the next batch may run meanwhile: tombstone or EMPTY, they stop at the same slot with the
+// same answer, and nobody inserts in phase A.
+__device__ __forceinline__ void ps_window_relax(const KvView& kv, uint32_t (&evicted)[PS_PER]) {
+    u128 next[PS_PER];
+#pragma unroll
+    for (int k = 0; k < PS_PER; ++k)
+        if (evicted[k] != PS_LOG_NONE) next[k] = ld_fp(&kv.slots[((unsigned long long)evicted[k] + 1ull) & kv.mask]);
+    unsigned relaxed = 0;
+#pragma unroll
+    for (int k = 0; k < PS_PER; ++k) {
+        if (evicted[k] == PS_LOG_NONE) continue;
+        if (fp_empty(next[k])) {
+            st128(&kv.slots[evicted[k]], u128{0ull, 0ull});
+            ++relaxed;
+        }
+        evicted[k] = PS_LOG_NONE;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) relaxed += __shfl_xor_sync(0xffffffffu, relaxed, o);
+    if ((threadIdx.x & 31) == 0 && relaxed) atomicAdd(&kv.st->n_tomb, (unsigned long long)(-(long long)relaxed));
 }
 
 // After barrier 3, one thread: the batch's evictions leave the counters (kvstore.py:87-93).
@@ -481,6 +504,9 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
     u128 key_next{0ull, 0ull};   // this thread's key of the next batch, fetched one batch ahead
     bool have_next = false;
     uint32_t wslot[PS_PER];      // window CTAs: the chunk's log entries of the current batch
+    uint32_t wevicted[PS_PER];   // ... and the slots it evicted (relaxed to EMPTY where possible in the next phase A)
+#pragma unroll
+    for (int k = 0; k < PS_PER; ++k) wevicted[k] = PS_LOG_NONE;
     unsigned long long cur_head = 0;  // window CTAs: LRU head, tracked locally (st->head is settled by one thread)
     if (!is_req) cur_head = ld_u64_cg(&st->head);
 
@@ -571,6 +597,7 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
             tc::fence_proxy_async_smem();
         } else if (!(P.dbg & 1)) {
             ps_window_preload(kv, cur_head + (unsigned long long)chunk * WCHUNK, a.t_get, wslot);
+            ps_window_relax(kv, wevicted);
         }
         grid_arrive(g);
         target += n_cta;
@@ -709,7 +736,7 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
             // every insert is in: _evict_if_needed's count for the whole batch (size is not written in this phase)
             const unsigned long long size = ld_u64_cg(&st->size);
             const unsigned long long e = size > kv.max_size && !(P.dbg & 1) ? size - kv.max_size : 0ull;
-            ps_window_evict(kv, g, chunk, P.n_chunks, wbase, wtail, a.t_set, e, wslot, s_mask, s_pref);
+            ps_window_evict(kv, g, chunk, P.n_chunks, wbase, wtail, a.t_set, e, wslot, s_mask, s_pref, wevicted);
             grid_arrive(g);
             target += n_cta;
             grid_wait(g, target, st);
@@ -725,6 +752,7 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
         if (cta == 0 && tid == PS_BAR_THREAD)
             asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(P.own_seq), "r"(seq0 + (unsigned)P.n_steps) : "memory");
     }
+    if (!is_req && !(P.dbg & 1)) ps_window_relax(kv, wevicted);  // after the last barrier nothing else runs on the table
     if (is_req && warp == 3) ps_stash_return(kv, s_stash, &s_nstash);  // the unused stock goes back to the table's queue
     // every CTA has passed the last barrier once CTA 0 has: the next launch starts counting from here
     if (cta == 0 && tid == PS_BAR_THREAD) g->bar_base = target;
@@ -822,6 +850,7 @@ die_status_t pipe_step_launch(const StepRef& sr, const QueueDesc* qv, int n_step
     static int dbg = -1;
     if (dbg < 0) {
         dbg = getenv("DIE_STEP_DEBUG") ? atoi(getenv("DIE_STEP_DEBUG")) : 0;
+        cudaMemcpyToSymbol(g_ps_dbg, &dbg, sizeof(dbg));
         if (const char* e = getenv("DIE_STEP_POLL_NS")) {
             const int ns = atoi(e);
             cudaMemcpyToSymbol(g_ps_poll_ns, &ns, sizeof(ns));
