@@ -30,7 +30,8 @@
 namespace die {
 
 constexpr int XCHG_MAX_WORLD = 16;
-constexpr int XCHG_SETS = 4;  // buffer sets: steps in flight between ingest and scatter
+constexpr int XCHG_SETS = 8;   // buffer sets: steps in flight between ingest and scatter
+constexpr int XCHG_GROUP = 4;  // owner passes of a replayed group that share one persistent launch
 struct PeerPtrs {
     void* p[XCHG_MAX_WORLD];
 };
@@ -78,8 +79,7 @@ __global__ void __launch_bounds__(256)
 xchg_compact_kernel(const int4* __restrict__ rows, const int32_t* __restrict__ counts, int world, int cap, int vdim,
                     long long bmax, int4* __restrict__ digests_out, int4* __restrict__ payload_out,
                     uint32_t* __restrict__ n_out, int32_t* __restrict__ prefix_out /*[world+1]*/,
-                    unsigned int* __restrict__ error_flag, unsigned int* __restrict__ ticket,
-                    unsigned int* __restrict__ ing_seq, const QueueDesc* __restrict__ q, int step) {
+                    unsigned int* __restrict__ error_flag) {
     __shared__ long long s_pre[XCHG_MAX_WORLD + 1];
     if (threadIdx.x == 0) {
         long long acc = 0;
@@ -108,42 +108,13 @@ xchg_compact_kernel(const int4* __restrict__ rows, const int32_t* __restrict__ c
         if (lane == 0) digests_out[g] = __ldcg(src);
         for (int c = lane; c < vdim; c += 32) stg_stream(payload_out + g * vdim + c, __ldcg(src + 1 + c));
     }
-    if (ing_seq) {  // replayed group: the owner's persistent kernel waits for this flag, not for a stream event
-        __threadfence();
-        __syncthreads();
-        if (threadIdx.x == 0 && atomicAdd(ticket, 1u) == gridDim.x - 1) {  // the last CTA: the whole batch is in place
-            *ticket = 0u;
-            __threadfence();
-            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(ing_seq), "r"(q->seq0 + (unsigned)step + 1u) : "memory");
-        }
-    }
 }
 
 // Owner: result g (source s, position i) -> return window of s.
 __global__ void __launch_bounds__(256)
 xchg_return_kernel(const int4* __restrict__ out, const uint8_t* __restrict__ hit, const int32_t* __restrict__ prefix,
-                   int world, int rank, int cap, int vout, PeerPtrs back, const unsigned int* __restrict__ own_seq,
-                   const QueueDesc* __restrict__ q, int step, unsigned int* __restrict__ error_flag) {
+                   int world, int rank, int cap, int vout, PeerPtrs back) {
     __shared__ int s_pre[XCHG_MAX_WORLD + 1];
-    if (own_seq) {  // replayed group: wait until the owner's persistent kernel has published this step's results
-        if (threadIdx.x == 0) {
-            const unsigned want = q->seq0 + (unsigned)step + 1u;
-            unsigned long long t0;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-            for (;;) {
-                unsigned v;
-                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(own_seq) : "memory");
-                if ((int)(v - want) >= 0) break;
-                unsigned long long t;
-                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-                if (t - t0 > 4000000000ull) {
-                    *error_flag = 1u;
-                    break;
-                }
-            }
-        }
-        __syncthreads();
-    }
     if (threadIdx.x <= world) s_pre[threadIdx.x] = prefix[threadIdx.x];
     __syncthreads();
     const int rv = vout + 1;
@@ -349,7 +320,7 @@ extern "C" die_status_t die_xchg_compact(const float* rows, const int32_t* count
     const int vdim = dim / 4;
     DIE_LAUNCH(ST_XCHG_COMPACT, s, xchg_compact_kernel<<<grid_for_rows(2ll * cap), 256, 0, s>>>(
         reinterpret_cast<const int4*>(rows), counts, world, cap, vdim, bmax, reinterpret_cast<int4*>(digests_out),
-        reinterpret_cast<int4*>(payload_out), n_out, prefix_out, nullptr, nullptr, nullptr, nullptr, 0));
+        reinterpret_cast<int4*>(payload_out), n_out, prefix_out, nullptr));
     return DIE_OK;
 }
 
@@ -362,7 +333,7 @@ extern "C" die_status_t die_xchg_return(const float* out, const uint8_t* hit, co
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int vout = dim_out / 4;
     DIE_LAUNCH(ST_XCHG_RETURN, s, xchg_return_kernel<<<grid_for_rows(2ll * cap), 256, 0, s>>>(
-        reinterpret_cast<const int4*>(out), hit, prefix, world, rank, cap, vout, back, nullptr, nullptr, 0, nullptr));
+        reinterpret_cast<const int4*>(out), hit, prefix, world, rank, cap, vout, back));
     return DIE_OK;
 }
 
@@ -426,7 +397,7 @@ __global__ void xchg_barrier_kernel(PeerPtrs flags, unsigned int* my_flags, int 
 // scatter.  Reuse is safe without extra synchronisation across ranks: a peer's dispatch of step b+SETS follows
 // its barrier of step b+SETS-1, which the owner only reaches after it compacted step b (and the same one stage
 // later for the return windows); on this rank the set's `done` event orders its own reuse.
-static_assert(XCHG_SETS == 4, "QueueDesc::epoch0 has one entry per buffer set");
+static_assert(XCHG_SETS == 8, "QueueDesc::epoch0 has one entry per buffer set");
 struct XchgLane {
     PeerPtrs rows, back, counts, flags;
     float* my_rows;
@@ -481,8 +452,8 @@ struct die_xchg {
     float* ring_out;
     uint8_t* ring_hit;
     uint32_t* ring_ndev;
-    unsigned int* flags;  // device: [0] ingested steps, [1] owned steps, [2] ticket of the compact kernel
-    bool owner_group;     // replayed groups run their K owner steps as ONE persistent launch
+    bool owner_group;     // replayed groups run XCHG_GROUP owner steps per persistent launch
+    cudaEvent_t grp_ing, grp_own;  // capture only: a group's requests are all received / its owner launch is done
 };
 
 static size_t xchg_rows_bytes(int world, int cap, int dim) { return (size_t)world * cap * (dim + 4) * sizeof(float); }
@@ -556,8 +527,8 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
     DIE_CUDA(cudaMalloc(&x->error_flag, sizeof(unsigned int)));
     DIE_CUDA(cudaMemset(x->error_flag, 0, sizeof(unsigned int)));
     DIE_CUDA(cudaMalloc(&x->qdesc, 2 * sizeof(QueueDesc)));
-    DIE_CUDA(cudaMalloc(&x->flags, 4 * sizeof(unsigned int)));
-    DIE_CUDA(cudaMemset(x->flags, 0, 4 * sizeof(unsigned int)));
+    DIE_CUDA(cudaEventCreateWithFlags(&x->grp_ing, cudaEventDisableTiming));
+    DIE_CUDA(cudaEventCreateWithFlags(&x->grp_own, cudaEventDisableTiming));
     x->owner_group = pipeline_owner_group_supported(pipe, x->bmax);
     DIE_CUDA(cudaStreamCreateWithFlags(&x->cap_stream, cudaStreamNonBlocking));
     x->graph_steps = 16;
@@ -585,7 +556,8 @@ extern "C" die_status_t die_xchg_destroy(die_xchg_t* x) {
     for (int g = 0; g < x->n_graphs; ++g) cudaGraphExecDestroy(x->graphs[g].exec);
     if (x->cap_stream) cudaStreamDestroy(x->cap_stream);
     cudaFree(x->qdesc);
-    cudaFree(x->flags);
+    if (x->grp_ing) cudaEventDestroy(x->grp_ing);
+    if (x->grp_own) cudaEventDestroy(x->grp_own);
     cudaFree(x->ring_dig); cudaFree(x->ring_pay); cudaFree(x->ring_out); cudaFree(x->ring_hit); cudaFree(x->ring_ndev);
     if (x->entry) cudaEventDestroy(x->entry);
     cudaFree(x->error_flag);
@@ -607,68 +579,57 @@ static die_status_t xchg_barrier(die_xchg* x, XchgLane& L, int lane, const Queue
 // reserve_now != nullptr (stream-launched step): the owner pass's host bookkeeping happens here, after the
 // ingest half is enqueued, so that table maintenance -- when due -- is ordered behind the previous owner pass
 // without holding back this step's ingest.
+enum XchgPart { XCHG_ALL = 0, XCHG_INGEST = 1, XCHG_RETURN = 2 };
 static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user, StepRef owner, int32_t B,
                                      int32_t* shard_out, const QueueDesc* qd, unsigned int epoch_first,
-                                     const double* reserve_now, int group_step = -1) {
+                                     const double* reserve_now, XchgPart part = XCHG_ALL) {
     XchgLane& L = x->lane[lane];
     const int W = x->world, D = x->dim, vdim = D / 4;
     int32_t* shard = shard_out ? shard_out : L.shard;
     const int n_cta = std::max(1, ceil_div(B, ROUTE_THREADS));
     const size_t off_bytes = (size_t)n_cta * W * sizeof(int);
-    // ---- stage 1, ingest: this set's scratch and windows are free once its previous step has scattered
-    cudaStream_t s = x->s_in;
-    if (L.used) DIE_CUDA(cudaStreamWaitEvent(s, L.done, 0));
-    DIE_LAUNCH(ST_ROUTE, s, xchg_route_kernel<<<n_cta, ROUTE_THREADS, 0, s>>>(
-        user, B, W, shard, reinterpret_cast<uint4*>(L.digests), L.loc, L.cta_cnt));
-    DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_rows(B), 256, off_bytes, s>>>(
-        user, reinterpret_cast<const int4*>(L.digests), L.loc, L.cta_cnt, n_cta, B, vdim, W, x->rank, x->cap, L.rows,
-        L.counts));
-    DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first, s));  // every rank's rows have landed in their owners' windows
-    DIE_LAUNCH(ST_XCHG_COMPACT, s, xchg_compact_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, s>>>(
-        reinterpret_cast<const int4*>(L.my_rows), L.my_cnt, W, x->cap, vdim, (long long)x->bmax,
-        reinterpret_cast<int4*>(L.recv_dig), reinterpret_cast<int4*>(L.recv_pay), L.n_dev, L.prefix, x->error_flag,
-        x->flags + 2, group_step >= 0 ? x->flags : nullptr, qd ? qd + 1 : nullptr, group_step));
-    DIE_CUDA(cudaEventRecord(L.ingested, s));
-    // ---- stage 2, owner pass: one in-order stream, so the table sees the batches in step order
-    cudaStream_t so = x->s_own;
-    cudaStream_t sr = x->s_ret;
-    const int vout_ = D / 4;
-    if (group_step >= 0) {
-        // The group's K owner steps are ONE persistent launch on s_own (xchg_graph_get): it picks this step up when
-        // the compact kernel above raises the ingested flag, and the return kernel waits for its owned flag.
+    cudaStream_t s = x->s_in, so = x->s_own, sr = x->s_ret;
+    if (part != XCHG_RETURN) {
+        // ---- stage 1, ingest: this set's scratch and windows are free once its previous step has scattered
+        if (L.used) DIE_CUDA(cudaStreamWaitEvent(s, L.done, 0));
+        DIE_LAUNCH(ST_ROUTE, s, xchg_route_kernel<<<n_cta, ROUTE_THREADS, 0, s>>>(
+            user, B, W, shard, reinterpret_cast<uint4*>(L.digests), L.loc, L.cta_cnt));
+        DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_rows(B), 256, off_bytes, s>>>(
+            user, reinterpret_cast<const int4*>(L.digests), L.loc, L.cta_cnt, n_cta, B, vdim, W, x->rank, x->cap, L.rows,
+            L.counts));
+        DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first, s));  // every rank's rows have landed in their owners' windows
+        DIE_LAUNCH(ST_XCHG_COMPACT, s, xchg_compact_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, s>>>(
+            reinterpret_cast<const int4*>(L.my_rows), L.my_cnt, W, x->cap, vdim, (long long)x->bmax,
+            reinterpret_cast<int4*>(L.recv_dig), reinterpret_cast<int4*>(L.recv_pay), L.n_dev, L.prefix, x->error_flag));
+        DIE_CUDA(cudaEventRecord(L.ingested, s));
+    }
+    if (part == XCHG_ALL) {
+        // ---- stage 2, owner pass: one in-order stream, so the table sees the batches in step order
+        DIE_CUDA(cudaStreamWaitEvent(so, L.ingested, 0));
+        if (reserve_now) {
+            unsigned long long tail0;
+            DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, 1, so, &owner.a.kv, &tail0, nullptr));
+            owner.a.now = *reserve_now;
+            owner.a.t_get = tail0;
+            owner.a.t_set = tail0 + (unsigned long long)x->bmax;
+        }
+        owner.a.payload = L.recv_pay;
+        owner.a.out = L.recv_out;
+        owner.a.code = L.recv_hit;
+        DIE_TRY(pipeline_owner_launch(x->pipe, owner, L.recv_dig, x->bmax, L.n_dev, so));
+        DIE_CUDA(cudaEventRecord(L.owned, so));
+        DIE_CUDA(cudaStreamWaitEvent(sr, L.owned, 0));
+    }
+    if (part != XCHG_INGEST) {
+        // ---- stage 3, way back (grouped form: the caller has ordered s_ret behind the group's owner launch)
         DIE_LAUNCH(ST_XCHG_RETURN, sr, xchg_return_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, sr>>>(
-            reinterpret_cast<const int4*>(L.recv_out), L.recv_hit, L.prefix, W, x->rank, x->cap, vout_, L.back,
-            x->flags + 1, qd + 1, group_step, x->error_flag));
-        DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first + 1, sr));
+            reinterpret_cast<const int4*>(L.recv_out), L.recv_hit, L.prefix, W, x->rank, x->cap, vdim, L.back));
+        DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first + 1, sr));  // every owner's results are back in the sources' windows
         DIE_LAUNCH(ST_XCHG_SCATTER, sr, xchg_scatter_kernel<<<grid_for_rows(B), 256, off_bytes, sr>>>(
-            user, reinterpret_cast<const int4*>(L.my_back), L.loc, L.cta_cnt, n_cta, B, W, x->cap, vout_));
+            user, reinterpret_cast<const int4*>(L.my_back), L.loc, L.cta_cnt, n_cta, B, W, x->cap, vdim));
         DIE_CUDA(cudaEventRecord(L.done, sr));
         L.used = true;
-        return DIE_OK;
     }
-    DIE_CUDA(cudaStreamWaitEvent(so, L.ingested, 0));
-    if (reserve_now) {
-        unsigned long long tail0;
-        DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, 1, so, &owner.a.kv, &tail0, nullptr));
-        owner.a.now = *reserve_now;
-        owner.a.t_get = tail0;
-        owner.a.t_set = tail0 + (unsigned long long)x->bmax;
-    }
-    owner.a.payload = L.recv_pay;
-    owner.a.out = L.recv_out;
-    owner.a.code = L.recv_hit;
-    DIE_TRY(pipeline_owner_launch(x->pipe, owner, L.recv_dig, x->bmax, L.n_dev, so));
-    DIE_CUDA(cudaEventRecord(L.owned, so));
-    // ---- stage 3, way back
-    DIE_CUDA(cudaStreamWaitEvent(sr, L.owned, 0));
-    DIE_LAUNCH(ST_XCHG_RETURN, sr, xchg_return_kernel<<<grid_for_rows(2ll * x->cap), 256, 0, sr>>>(
-        reinterpret_cast<const int4*>(L.recv_out), L.recv_hit, L.prefix, W, x->rank, x->cap, vdim, L.back, nullptr, nullptr,
-        0, nullptr));
-    DIE_TRY(xchg_barrier(x, L, lane, qd, epoch_first + 1, sr));  // every owner's results are back in the sources' windows
-    DIE_LAUNCH(ST_XCHG_SCATTER, sr, xchg_scatter_kernel<<<grid_for_rows(B), 256, off_bytes, sr>>>(
-        user, reinterpret_cast<const int4*>(L.my_back), L.loc, L.cta_cnt, n_cta, B, W, x->cap, vdim));
-    DIE_CUDA(cudaEventRecord(L.done, sr));
-    L.used = true;
     return DIE_OK;
 }
 
@@ -727,27 +688,53 @@ static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_
     cudaGraph_t graph = nullptr;
     DIE_CUDA(cudaStreamBeginCapture(x->cap_stream, cudaStreamCaptureModeThreadLocal));
     die_status_t st = xchg_fork(x, x->cap_stream);
-    if (st == DIE_OK && x->owner_group) {
-        StepLanes ln;
-        ln.lanes = XCHG_SETS;
-        ln.lane0 = lane0;
-        ln.ing_seq = x->flags;
-        ln.own_seq = x->flags + 1;
-        st = pipeline_owner_launch_group(x->pipe, x->qdesc + 1, K, x->ring_dig, x->bmax, x->ring_ndev, ln, x->s_own);
-    }
     unsigned int off[XCHG_SETS];
     for (int l = 0; l < XCHG_SETS; ++l) off[l] = 1u;
-    for (int i = 0; i < K && st == DIE_OK; ++i) {
-        const int lane = (lane0 + i) % XCHG_SETS;
-        StepRef user, owner;
+    auto refs = [&](int i, StepRef& user, StepRef& owner) {
         memset(&user, 0, sizeof(user));
         memset(&owner, 0, sizeof(owner));
         user.q = x->qdesc;
         user.i = i;
         owner.q = x->qdesc + 1;
         owner.i = i;
-        st = xchg_launch_step(x, lane, user, owner, B, nullptr, x->qdesc, off[lane], nullptr, x->owner_group ? i : -1);
-        off[lane] += 2;
+    };
+    if (x->owner_group && K % XCHG_GROUP == 0) {
+        // Groups of XCHG_GROUP steps: their ingests, ONE persistent owner launch over the group's lanes (no launch,
+        // prologue and drain per step; keys and payload tiles of step i+1 fetched while step i runs), their returns.
+        // With XCHG_SETS = 2 groups of buffer sets, group g+1 is ingested while group g is with its owner.
+        for (int g0 = 0; g0 < K && st == DIE_OK; g0 += XCHG_GROUP) {
+            for (int i = g0; i < g0 + XCHG_GROUP && st == DIE_OK; ++i) {
+                StepRef user, owner;
+                refs(i, user, owner);
+                st = xchg_launch_step(x, (lane0 + i) % XCHG_SETS, user, owner, B, nullptr, x->qdesc, off[(lane0 + i) % XCHG_SETS],
+                                      nullptr, XCHG_INGEST);
+            }
+            if (st != DIE_OK) break;
+            if (cudaEventRecord(x->grp_ing, x->s_in) != cudaSuccess || cudaStreamWaitEvent(x->s_own, x->grp_ing, 0) != cudaSuccess) st = DIE_ERR_CUDA;
+            if (st == DIE_OK) {
+                StepLanes ln;
+                ln.lanes = XCHG_SETS;
+                ln.lane0 = (lane0 + g0) % XCHG_SETS;
+                st = pipeline_owner_launch_group(x->pipe, x->qdesc + 1, g0, XCHG_GROUP, x->ring_dig, x->bmax, x->ring_ndev, ln, x->s_own);
+            }
+            if (st == DIE_OK && (cudaEventRecord(x->grp_own, x->s_own) != cudaSuccess ||
+                                 cudaStreamWaitEvent(x->s_ret, x->grp_own, 0) != cudaSuccess)) st = DIE_ERR_CUDA;
+            for (int i = g0; i < g0 + XCHG_GROUP && st == DIE_OK; ++i) {
+                StepRef user, owner;
+                refs(i, user, owner);
+                const int lane = (lane0 + i) % XCHG_SETS;
+                st = xchg_launch_step(x, lane, user, owner, B, nullptr, x->qdesc, off[lane], nullptr, XCHG_RETURN);
+                off[lane] += 2;
+            }
+        }
+    } else {
+        for (int i = 0; i < K && st == DIE_OK; ++i) {
+            const int lane = (lane0 + i) % XCHG_SETS;
+            StepRef user, owner;
+            refs(i, user, owner);
+            st = xchg_launch_step(x, lane, user, owner, B, nullptr, x->qdesc, off[lane], nullptr);
+            off[lane] += 2;
+        }
     }
     if (st == DIE_OK) st = xchg_join(x, x->cap_stream);
     const cudaError_t e = cudaStreamEndCapture(x->cap_stream, &graph);
@@ -830,7 +817,7 @@ extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, con
             DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, K, user, &dw.kv, &tail0, &mirror));
             dw.tail0 = tail0;
             du.j0 = dw.j0 = j;
-            if (x->owner_group) {  // the owner's persistent kernel walks the lanes' buffers as rings of XCHG_SETS steps
+            if (x->owner_group && K % XCHG_GROUP == 0) {  // the owner's persistent launches walk the lanes' buffers as rings
                 const long long lane0 = (long long)(x->steps % XCHG_SETS);
                 dw.payload = x->ring_pay;
                 dw.out = x->ring_out;
@@ -840,7 +827,6 @@ extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, con
                 dw.ring = dw.pay_ring = XCHG_SETS;
                 dw.j0 = lane0;            // buffers: step i of the group uses lane (lane0 + i) % XCHG_SETS
                 dw.jt = (long long)j - lane0;  // clock: still batch j + i of the queue
-                dw.seq0 = (unsigned int)x->steps;
             }
             for (int l = 0; l < XCHG_SETS; ++l) du.epoch0[l] = x->lane[l].epoch;
             du.trace = dw.trace = trace_buffer();
@@ -848,7 +834,8 @@ extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, con
             DIE_LAUNCH_CHECK();
             DIE_CUDA(cudaGraphLaunch(exec, user));
             count_replay();
-            count_launch(x->owner_group ? (unsigned)(K * 7 + 1) : (unsigned)(K * (7 + pipeline_launches_per_step(x->pipe))));
+            count_launch(x->owner_group && K % XCHG_GROUP == 0 ? (unsigned)(K * 7 + K / XCHG_GROUP)
+                                                               : (unsigned)(K * (7 + pipeline_launches_per_step(x->pipe))));
             const int set0 = (int)(x->steps % XCHG_SETS);
             for (int i = 0; i < K; ++i) x->lane[(set0 + i) % XCHG_SETS].epoch += 2u;  // two barriers per step
             x->steps += (unsigned long long)K;

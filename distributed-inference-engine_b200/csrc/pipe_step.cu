@@ -71,11 +71,8 @@ struct StepParams {
     StepGrid* g;
     KvMirrorArgs mirror;        // m.m != nullptr: snapshot the table counters for the host before the first batch
     // Owner pass of the exchange, several steps in one launch: digests and n_req_dev are rings of `lanes` per-step
-    // buffers (step s uses lane (lane0 + s) % lanes), step s may start once *ing_seq >= seq0 + s + 1 (its requests
-    // have been received and compacted) and *own_seq is advanced to seq0 + s + 1 once its results are complete.
+    // buffers, step s uses lane (lane0 + s) % lanes (0 lanes: one buffer per step of the launch, in order).
     int lanes, lane0;
-    const unsigned int* ing_seq;
-    unsigned int* own_seq;
     int dbg;                    // diagnostics (DIE_STEP_DEBUG): 1 = barriers only, no work; 2 = no L2 prefetch of the next
                                 // batch's slots (timing experiments)
 };
@@ -140,25 +137,6 @@ __device__ __forceinline__ void grid_wait(StepGrid* g, unsigned target, KvState*
     }
     __syncthreads();
     tc::fence_after_thread_sync();
-}
-
-// The whole CTA waits until *flag has reached `value` (the exchange's ingest stream publishes received batches).
-__device__ __forceinline__ void ps_wait_flag(const unsigned int* flag, unsigned value, StepGrid* g, KvState* st) {
-    if (threadIdx.x == PS_BAR_THREAD) {
-        const unsigned long long t0 = ps_timer();
-        unsigned spins = 0;
-        while ((int)(ld_acquire_u32(flag) - value) < 0) {
-            if ((++spins & 1023u) == 0u) {
-                if (ld_acquire_u32(&g->abort)) break;
-                if (ps_timer() - t0 > 4000000000ull) {  // the peers stopped: fail loudly, never hang
-                    atomicExch(&g->abort, 1u);
-                    st->status = DIE_ERR_CUDA;
-                    break;
-                }
-            }
-        }
-    }
-    __syncthreads();
 }
 
 __device__ __forceinline__ void ps_cp_async16(void* smem_dst, const void* gmem_src) {
@@ -483,15 +461,10 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
             ps_cp_async16(b_base + (size_t)(ck >> 3) * ((size_t)N * 128) + tc::sw128_offset((uint32_t)r, (uint32_t)(ck & 7)),
                           P.W + (size_t)r * K + ck * 4);
         }
-        if (!P.ing_seq) {  // (with an ingest flag the first batch may not have arrived yet: loaded after the wait)
-            const int nq0 = max(0, min(R, P.B - cta * R));
-            ps_load_tile(a_base0, a_first.payload, cta * R, nq0, K);
-        }
+        const int nq0 = max(0, min(R, P.B - cta * R));
+        ps_load_tile(a_base0, a_first.payload, cta * R, nq0, K);
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
-    bool tile_loaded = !P.ing_seq;  // the current batch's tile is on its way (CTA-uniform)
-    const unsigned seq0 = sr.q ? sr.q->seq0 : 0u;
-    __shared__ int s_next_ready;
 #define PS_MARK(i)                                             \
     do {                                                       \
         if (tid == 0) {                                        \
@@ -516,13 +489,7 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
         const StepArgs a = step_resolve(r);
         const int lane_s = P.lanes ? (P.lane0 + s) % P.lanes : s;       // which per-step digest / count buffer
         const int lane_n = P.lanes ? (P.lane0 + s + 1) % P.lanes : s + 1;
-        if (P.ing_seq) ps_wait_flag(P.ing_seq, seq0 + (unsigned)s + 1u, g, st);  // this batch has been received
-        bool next_ready = s + 1 < P.n_steps && !(P.dbg & 1);
-        if (P.ing_seq && next_ready) {  // ... and whether the next one has, too (else nothing of it is fetched ahead)
-            if (tid == 0) s_next_ready = (int)(ld_acquire_u32(P.ing_seq) - (seq0 + (unsigned)s + 2u)) >= 0;
-            __syncthreads();
-            next_ready = s_next_ready != 0;
-        }
+        const bool next_ready = s + 1 < P.n_steps && !(P.dbg & 1);
         int Bs = P.B;
         if (P.n_req_dev) Bs = min(Bs, (int)__ldcg(P.n_req_dev + (P.lanes ? lane_s : 0)));
         const int q0 = cta * R;
@@ -537,11 +504,6 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
 
         // ================= phase A: probe =================
         if (is_req) {
-            if (!tile_loaded) {  // not fetched ahead (first batch after a flag wait, or it had not arrived in time)
-                ps_load_tile(a_cur, a.payload, q0, max(0, min(R, P.B - q0)), K);
-                asm volatile("cp.async.commit_group;" ::: "memory");
-            }
-            tile_loaded = next_ready;
             if (next_ready) {  // PACK of the next batch: its rows travel while this batch is processed
                 StepRef r2 = sr;
                 r2.i += s + 1;
@@ -603,9 +565,6 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
         target += n_cta;
         grid_wait(g, target, st);
         PS_MARK(1);
-        // every CTA has finished the previous batch's epilogue before it arrived here: its results are complete
-        if (P.own_seq && s > 0 && cta == 0 && tid == PS_BAR_THREAD)
-            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(P.own_seq), "r"(seq0 + (unsigned)s) : "memory");
 
         // ================= phase B: insert the misses | hit rows | MMA | victim bitmap =================
         unsigned long long wbase = 0, wtail = 0;
@@ -745,13 +704,6 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
         }
         PS_MARK(3);
     }
-    if (P.own_seq) {  // the last batch's results: complete once every CTA is through its epilogue
-        grid_arrive(g);
-        target += n_cta;
-        grid_wait(g, target, st);
-        if (cta == 0 && tid == PS_BAR_THREAD)
-            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(P.own_seq), "r"(seq0 + (unsigned)P.n_steps) : "memory");
-    }
     if (!is_req && !(P.dbg & 1)) ps_window_relax(kv, wevicted);  // after the last barrier nothing else runs on the table
     if (is_req && warp == 3) ps_stash_return(kv, s_stash, &s_nstash);  // the unused stock goes back to the table's queue
     // every CTA has passed the last barrier once CTA 0 has: the next launch starts counting from here
@@ -844,8 +796,6 @@ die_status_t pipe_step_launch(const StepRef& sr, const QueueDesc* qv, int n_step
     if (lanes) {
         P.lanes = lanes->lanes;
         P.lane0 = lanes->lane0;
-        P.ing_seq = lanes->ing_seq;
-        P.own_seq = lanes->own_seq;
     }
     static int dbg = -1;
     if (dbg < 0) {

@@ -711,18 +711,16 @@ die_status_t pipeline_owner_launch(die_pipeline* p, const StepRef& sr, uint32_t*
 
 bool pipeline_owner_group_supported(const die_pipeline* p, int B_max) {
     int r, n;
-    // Off unless DIE_XCHG_OWNER_GROUP=1: the grouped owner pass is bit-exact against the oracle with all ranks on one
-    // GPU (tests/test_gpu_loopback.py) but stalled in cross-GPU barriers on a 2 x B200 run; until that is understood
-    // the owner pass of a replayed group stays one launch per step behind stream events.
-    const int on = getenv("DIE_XCHG_OWNER_GROUP") ? atoi(getenv("DIE_XCHG_OWNER_GROUP")) : 0;  // read at die_xchg_create
+    const int on = getenv("DIE_XCHG_OWNER_GROUP") ? atoi(getenv("DIE_XCHG_OWNER_GROUP")) : 1;  // read at die_xchg_create
     return on && p->persistent && pipe_step_shape(B_max, p->cfg.dim_in, p->cfg.dim_out, p->n_chunks, &r, &n);
 }
 
-die_status_t pipeline_owner_launch_group(die_pipeline* p, const QueueDesc* qd_dev, int K, uint32_t* digests_ring, int B_max,
-                                         const uint32_t* n_dev_ring, const StepLanes& lanes, cudaStream_t s) {
+die_status_t pipeline_owner_launch_group(die_pipeline* p, const QueueDesc* qd_dev, int first, int K, uint32_t* digests_ring,
+                                         int B_max, const uint32_t* n_dev_ring, const StepLanes& lanes, cudaStream_t s) {
     StepRef sr;
     memset(&sr, 0, sizeof(sr));
     sr.q = qd_dev;  // device-resident descriptor, rewritten before every replay
+    sr.i = first;
     return pipe_step_launch(sr, nullptr, K, B_max, p->n_chunks, p->cfg.dim_in, p->cfg.dim_out, false, n_dev_ring,
                             digests_ring, p->W, p->bias, p->arena, p->sgrid, nullptr, s, &lanes);
 }

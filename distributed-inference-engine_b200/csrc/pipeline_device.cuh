@@ -41,11 +41,10 @@ struct QueueDesc {
     long long jt;  // added to j0 for the clock: the batches of a staged group are a window of a longer queue
     int ring;      // out / hit slots, reused round-robin
     int pay_ring;  // payload slots, reused round-robin (0: one per batch of the queue)
-    unsigned int seq0;  // exchange only: global number of the replay's first step (ingested / owned flags count steps)
     int batch;     // stamps per get (= per set) pass of one step
     double now0, now_step;
     unsigned long long tail0;  // LRU stamp of the replay's first op
-    unsigned int epoch0[4];    // exchange only: barrier epoch of each buffer set before the replay
+    unsigned int epoch0[8];    // exchange only: barrier epoch of each buffer set before the replay
     unsigned long long* trace; // diagnostics (die_debug_trace_enable): [0] cursor, [1] capacity, then (tag, ns) pairs
 };
 

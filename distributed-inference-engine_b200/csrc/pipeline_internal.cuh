@@ -29,21 +29,19 @@ bool pipe_step_shape(int B, int K, int N, int n_chunks, int* R_out, int* n_req_o
 // n_steps consecutive batches starting at `sr` in one launch.  qv (optional): the queue descriptor, passed by value
 // in the launch (stream launches); otherwise sr.q is device-resident or null (values in sr.a).
 // lanes (optional, the exchange's owner pass over several steps in one launch): `digests` and `n_req_dev` are rings of
-// `lanes` per-step buffers starting at lane0; step s starts once *ing_seq >= q->seq0 + s + 1 and *own_seq is advanced
-// to q->seq0 + s + 1 when its results are complete.
+// `lanes` per-step buffers, step s of the launch uses lane (lane0 + s) % lanes.
 struct StepLanes {
     int lanes, lane0;
-    const unsigned int* ing_seq;
-    unsigned int* own_seq;
 };
 die_status_t pipe_step_launch(const StepRef& sr, const QueueDesc* qv, int n_steps, int B, int n_chunks, int K, int N,
                               bool from_keys, const uint32_t* n_req_dev, uint32_t* digests, const float* W,
                               const float* bias, float* arena, void* grid, const KvMirrorArgs* mirror, cudaStream_t s,
                               const StepLanes* lanes = nullptr);
-// K owner steps of the exchange in ONE persistent launch (true), or false when this pipeline / shape has no
-// persistent kernel and the caller launches the steps one by one behind stream events.
+// K owner steps of the exchange (steps first .. first+K-1 of the device-resident descriptor) in ONE persistent launch;
+// pipeline_owner_group_supported: false when this pipeline / shape has no persistent kernel (or DIE_XCHG_OWNER_GROUP=0)
+// and the caller launches the steps one by one.
 bool pipeline_owner_group_supported(const die_pipeline* p, int B_max);
-die_status_t pipeline_owner_launch_group(die_pipeline* p, const QueueDesc* qd_dev, int K, uint32_t* digests_ring, int B_max,
-                                         const uint32_t* n_dev_ring, const StepLanes& lanes, cudaStream_t s);
+die_status_t pipeline_owner_launch_group(die_pipeline* p, const QueueDesc* qd_dev, int first, int K, uint32_t* digests_ring,
+                                         int B_max, const uint32_t* n_dev_ring, const StepLanes& lanes, cudaStream_t s);
 
 }  // namespace die
