@@ -323,20 +323,22 @@ class ClockSampler(threading.Thread):
 
 def ncu_traffic(kernel_name):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel_name`, from the committed
-    `ncu --set full` capture of this bench command (profiles/ncu_full_r01_pipeline_kernels.csv)."""
+    `ncu --set full` captures of this bench command (profiles/ncu_full_r02_*.csv; the round-1 capture covers the
+    three-kernel form).  The persistent kernel's launches are groups of 16 batches, in the capture as in the bench."""
     import csv
-    path = os.path.join(ROOT, "profiles", "ncu_full_r01_pipeline_kernels.csv")
-    try:
-        rows = list(csv.reader(open(path)))
-        hdr, units = rows[0], rows[1]
-        i_name, i_r, i_w = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
-        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-        vals = [float(r[i_r]) * scale[units[i_r]] + float(r[i_w]) * scale[units[i_w]]
-                for r in rows[2:] if len(r) == len(hdr) and kernel_name in r[i_name]]
-        if vals:
-            return round(sum(vals) / len(vals)), "profiles/ncu_full_r01_pipeline_kernels.csv (mean of %d launches)" % len(vals)
-    except Exception:  # noqa: BLE001
-        pass
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    for fn in ("ncu_full_r02_bench.csv", "ncu_full_r02_pipe_step_kernel.csv", "ncu_full_r01_pipeline_kernels.csv"):
+        path = os.path.join(ROOT, "profiles", fn)
+        try:
+            rows = list(csv.reader(open(path)))
+            hdr, units = rows[0], rows[1]
+            i_name, i_r, i_w = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+            vals = [float(r[i_r]) * scale[units[i_r]] + float(r[i_w]) * scale[units[i_w]]
+                    for r in rows[2:] if len(r) == len(hdr) and kernel_name in r[i_name]]
+            if vals:
+                return round(sum(vals) / len(vals)), "profiles/%s (mean of %d launches)" % (fn, len(vals))
+        except Exception:  # noqa: BLE001
+            continue
     return None, None
 
 

@@ -24,14 +24,18 @@
 // in-order stream each) over XCHG_SETS buffer sets, and replay groups of steps from one CUDA graph; the
 // stand-alone phase entry points (die_xchg_dispatch / compact / return / scatter, bucket order from
 // die_bucket_by_shard) stay as a cross-check driven from Python.
+#include <vector>
+
 #include "pipeline_internal.cuh"
 #include "route_device.cuh"
 
 namespace die {
 
 constexpr int XCHG_MAX_WORLD = 16;
-constexpr int XCHG_SETS = 8;   // buffer sets: steps in flight between ingest and scatter
-constexpr int XCHG_GROUP = 4;  // owner passes of a replayed group that share one persistent launch
+// XCHG_SETS (pipeline_device.cuh) buffer sets: steps in flight between ingest and scatter
+constexpr int XCHG_GROUP = 16;  // steps per replayed group = owner passes that share one persistent launch
+static_assert(XCHG_SETS == 3 * XCHG_GROUP, "three groups in flight: being ingested, with the owner, on the way back");
+constexpr int XCHG_MAX_WAYS = 8;  // ingest / return streams (DIE_XCHG_WAYS)
 struct PeerPtrs {
     void* p[XCHG_MAX_WORLD];
 };
@@ -397,7 +401,6 @@ __global__ void xchg_barrier_kernel(PeerPtrs flags, unsigned int* my_flags, int 
 // scatter.  Reuse is safe without extra synchronisation across ranks: a peer's dispatch of step b+SETS follows
 // its barrier of step b+SETS-1, which the owner only reaches after it compacted step b (and the same one stage
 // later for the return windows); on this rank the set's `done` event orders its own reuse.
-static_assert(XCHG_SETS == 8, "QueueDesc::epoch0 has one entry per buffer set");
 struct XchgLane {
     PeerPtrs rows, back, counts, flags;
     float* my_rows;
@@ -430,16 +433,20 @@ struct die_xchg {
     unsigned long long steps;  // steps enqueued so far: step b uses set b % XCHG_SETS
     // One in-order stream per stage, every step passes through all three: while the owner pass of step b runs,
     // step b+1 is being ingested and step b-1 is on its way back.
-    cudaStream_t s_in;   // route, dispatch, barrier, compact
-    cudaStream_t s_own;  // the pipeline on the received batch (the only stage that touches the table); high priority
-    cudaStream_t s_ret;  // return, barrier, scatter
+    // Ingest and way back are chains of four / three short dependent kernels (~30 / ~20 us per step end to end, most of
+    // it launch-to-launch latency and the cross-GPU barrier) against ~22 us for the owner pass: steps alternate between
+    // `ways` streams for those stages so that the owner stream -- the only one whose order matters -- is never starved.
+    int ways;
+    cudaStream_t s_in[XCHG_MAX_WAYS];   // route, dispatch, barrier, compact of steps with lane % ways == w
+    cudaStream_t s_own;                 // the pipeline on the received batch (the only stage that touches the table); high priority
+    cudaStream_t s_ret[XCHG_MAX_WAYS];  // return, barrier, scatter
     cudaEvent_t entry, exit_ev;
     // captured replays of K steps
     struct Replay {
-        int B, K, set0;
+        int B, K, set0, parts;
         cudaGraphExec_t exec;
     };
-    static constexpr int MAX_GRAPHS = 16;
+    static constexpr int MAX_GRAPHS = 32;
     Replay graphs[MAX_GRAPHS];
     int n_graphs;
     int graph_steps;
@@ -452,8 +459,7 @@ struct die_xchg {
     float* ring_out;
     uint8_t* ring_hit;
     uint32_t* ring_ndev;
-    bool owner_group;     // replayed groups run XCHG_GROUP owner steps per persistent launch
-    cudaEvent_t grp_ing, grp_own;  // capture only: a group's requests are all received / its owner launch is done
+    bool owner_group;     // the owner pipeline has the persistent form: groups are replayed software-pipelined
 };
 
 static size_t xchg_rows_bytes(int world, int cap, int dim) { return (size_t)world * cap * (dim + 4) * sizeof(float); }
@@ -462,6 +468,14 @@ static size_t xchg_lane_bytes(int world, int cap, int dim) { return 2 * xchg_row
 extern "C" uint64_t die_xchg_window_bytes(int32_t world, int32_t cap, int32_t dim) {
     // per buffer set: receive rows + return rows + counts + barrier flags
     return XCHG_SETS * xchg_lane_bytes(world, cap, dim);
+}
+
+static std::vector<cudaStream_t> xchg_streams(const die_xchg* x) {  // ingest streams, owner stream, return streams
+    std::vector<cudaStream_t> v;
+    for (int w = 0; w < x->ways; ++w) v.push_back(x->s_in[w]);
+    v.push_back(x->s_own);
+    for (int w = 0; w < x->ways; ++w) v.push_back(x->s_ret[w]);
+    return v;
 }
 
 extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap, int32_t dim, int32_t owner_max,
@@ -519,16 +533,19 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
         DIE_CUDA(cudaEventCreateWithFlags(&L.ingested, cudaEventDisableTiming));
         DIE_CUDA(cudaEventCreateWithFlags(&L.owned, cudaEventDisableTiming));
     }
-    DIE_CUDA(cudaStreamCreateWithPriority(&x->s_in, cudaStreamNonBlocking, prio_low));
+    x->ways = 4;
+    if (const char* e = getenv("DIE_XCHG_WAYS")) x->ways = atoi(e);
+    if (x->ways < 1 || x->ways > XCHG_MAX_WAYS) x->ways = 4;
+    for (int w = 0; w < x->ways; ++w) {
+        DIE_CUDA(cudaStreamCreateWithPriority(&x->s_in[w], cudaStreamNonBlocking, prio_low));
+        DIE_CUDA(cudaStreamCreateWithPriority(&x->s_ret[w], cudaStreamNonBlocking, prio_low));
+    }
     DIE_CUDA(cudaStreamCreateWithPriority(&x->s_own, cudaStreamNonBlocking, prio_high));
-    DIE_CUDA(cudaStreamCreateWithPriority(&x->s_ret, cudaStreamNonBlocking, prio_low));
     DIE_CUDA(cudaEventCreateWithFlags(&x->exit_ev, cudaEventDisableTiming));
     DIE_CUDA(cudaEventCreateWithFlags(&x->entry, cudaEventDisableTiming));
     DIE_CUDA(cudaMalloc(&x->error_flag, sizeof(unsigned int)));
     DIE_CUDA(cudaMemset(x->error_flag, 0, sizeof(unsigned int)));
     DIE_CUDA(cudaMalloc(&x->qdesc, 2 * sizeof(QueueDesc)));
-    DIE_CUDA(cudaEventCreateWithFlags(&x->grp_ing, cudaEventDisableTiming));
-    DIE_CUDA(cudaEventCreateWithFlags(&x->grp_own, cudaEventDisableTiming));
     x->owner_group = pipeline_owner_group_supported(pipe, x->bmax);
     DIE_CUDA(cudaStreamCreateWithFlags(&x->cap_stream, cudaStreamNonBlocking));
     x->graph_steps = 16;
@@ -539,7 +556,7 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
 
 extern "C" die_status_t die_xchg_destroy(die_xchg_t* x) {
     if (!x) return DIE_OK;
-    for (cudaStream_t st : {x->s_in, x->s_own, x->s_ret})
+    for (cudaStream_t st : xchg_streams(x))
         if (st) {
             cudaStreamSynchronize(st);
             cudaStreamDestroy(st);
@@ -556,8 +573,6 @@ extern "C" die_status_t die_xchg_destroy(die_xchg_t* x) {
     for (int g = 0; g < x->n_graphs; ++g) cudaGraphExecDestroy(x->graphs[g].exec);
     if (x->cap_stream) cudaStreamDestroy(x->cap_stream);
     cudaFree(x->qdesc);
-    if (x->grp_ing) cudaEventDestroy(x->grp_ing);
-    if (x->grp_own) cudaEventDestroy(x->grp_own);
     cudaFree(x->ring_dig); cudaFree(x->ring_pay); cudaFree(x->ring_out); cudaFree(x->ring_hit); cudaFree(x->ring_ndev);
     if (x->entry) cudaEventDestroy(x->entry);
     cudaFree(x->error_flag);
@@ -588,7 +603,7 @@ static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user,
     int32_t* shard = shard_out ? shard_out : L.shard;
     const int n_cta = std::max(1, ceil_div(B, ROUTE_THREADS));
     const size_t off_bytes = (size_t)n_cta * W * sizeof(int);
-    cudaStream_t s = x->s_in, so = x->s_own, sr = x->s_ret;
+    cudaStream_t s = x->s_in[lane % x->ways], so = x->s_own, sr = x->s_ret[lane % x->ways];
     if (part != XCHG_RETURN) {
         // ---- stage 1, ingest: this set's scratch and windows are free once its previous step has scattered
         if (L.used) DIE_CUDA(cudaStreamWaitEvent(s, L.done, 0));
@@ -633,22 +648,20 @@ static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user,
     return DIE_OK;
 }
 
-// The stage streams start after the work already on `from`; `to` continues after the last step has scattered
-// (s_ret is in order and every step ends there, so its tail covers all three streams).
+// The stage streams start after the work already on `from`; `to` continues after every stage stream's tail.
 static die_status_t xchg_fork(die_xchg* x, cudaStream_t from) {
     DIE_CUDA(cudaEventRecord(x->entry, from));
-    for (cudaStream_t st : {x->s_in, x->s_own, x->s_ret}) DIE_CUDA(cudaStreamWaitEvent(st, x->entry, 0));
+    for (cudaStream_t st : xchg_streams(x)) DIE_CUDA(cudaStreamWaitEvent(st, x->entry, 0));
     for (int l = 0; l < XCHG_SETS; ++l) x->lane[l].used = false;  // everything earlier is ordered through `from`
     return DIE_OK;
 }
 static die_status_t xchg_join(die_xchg* x, cudaStream_t to) {
-    // s_in and s_own first: a stream pulled into a capture must be joined back even if it did no work
-    DIE_CUDA(cudaEventRecord(x->exit_ev, x->s_in));
-    DIE_CUDA(cudaStreamWaitEvent(x->s_own, x->exit_ev, 0));
-    DIE_CUDA(cudaEventRecord(x->exit_ev, x->s_own));
-    DIE_CUDA(cudaStreamWaitEvent(x->s_ret, x->exit_ev, 0));
-    DIE_CUDA(cudaEventRecord(x->exit_ev, x->s_ret));
-    DIE_CUDA(cudaStreamWaitEvent(to, x->exit_ev, 0));
+    // a chain through every stage stream: a stream pulled into a capture must be joined back even if it did no work
+    const std::vector<cudaStream_t> all = xchg_streams(x);
+    for (size_t i = 0; i < all.size(); ++i) {
+        DIE_CUDA(cudaEventRecord(x->exit_ev, all[i]));
+        DIE_CUDA(cudaStreamWaitEvent(i + 1 < all.size() ? all[i + 1] : to, x->exit_ev, 0));
+    }
     return DIE_OK;
 }
 
@@ -672,11 +685,20 @@ static die_status_t xchg_enqueue_step(die_xchg* x, const uint8_t* key_bytes, con
     return xchg_launch_step(x, lane, user, owner, B, shard_out, nullptr, e, &now);
 }
 
-// K steps captured once per (B, K, first buffer set); qd[0] describes the ingested queue, qd[1] the owner passes.
-static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_t* out) {
-    const int lane0 = (int)(x->steps % XCHG_SETS);
+// Captured replays.  qd[0] describes the ingested queue, qd[1] the owner passes.
+//
+// parts == 0: one graph holds K whole steps (ingest | one owner launch per step | way back, fork / join inside); used
+//   when the owner pipeline has no persistent form.  set0 = the first step's buffer set.
+// parts != 0: the software-pipelined form.  A launch is up to three INDEPENDENT branches over three different
+//   thirds of the buffer sets -- XP_INGEST: the 16 ingests of group g; XP_OWNER: ONE persistent owner launch over the
+//   16 batches of group g-1; XP_RETURN: the 16 returns of group g-2 -- and consecutive launches on the caller's stream
+//   provide the order between a group's three stages.  The owner kernel never waits for anything in flight, pays its
+//   launch, prologue and drain once per 16 steps, and the short dependent kernels of ingest / way back (whose latency
+//   is launch-to-launch gaps and the cross-GPU barrier) hide behind it.  set0 = g % 3.
+enum XchgParts { XP_INGEST = 1, XP_OWNER = 2, XP_RETURN = 4 };
+static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, int parts, int set0, cudaGraphExec_t* out) {
     for (int g = 0; g < x->n_graphs; ++g)
-        if (x->graphs[g].B == B && x->graphs[g].K == K && x->graphs[g].set0 == lane0) {
+        if (x->graphs[g].B == B && x->graphs[g].K == K && x->graphs[g].set0 == set0 && x->graphs[g].parts == parts) {
             *out = x->graphs[g].exec;
             return DIE_OK;
         }
@@ -688,8 +710,6 @@ static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_
     cudaGraph_t graph = nullptr;
     DIE_CUDA(cudaStreamBeginCapture(x->cap_stream, cudaStreamCaptureModeThreadLocal));
     die_status_t st = xchg_fork(x, x->cap_stream);
-    unsigned int off[XCHG_SETS];
-    for (int l = 0; l < XCHG_SETS; ++l) off[l] = 1u;
     auto refs = [&](int i, StepRef& user, StepRef& owner) {
         memset(&user, 0, sizeof(user));
         memset(&owner, 0, sizeof(owner));
@@ -698,38 +718,32 @@ static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_
         owner.q = x->qdesc + 1;
         owner.i = i;
     };
-    if (x->owner_group && K % XCHG_GROUP == 0) {
-        // Groups of XCHG_GROUP steps: their ingests, ONE persistent owner launch over the group's lanes (no launch,
-        // prologue and drain per step; keys and payload tiles of step i+1 fetched while step i runs), their returns.
-        // With XCHG_SETS = 2 groups of buffer sets, group g+1 is ingested while group g is with its owner.
-        for (int g0 = 0; g0 < K && st == DIE_OK; g0 += XCHG_GROUP) {
-            for (int i = g0; i < g0 + XCHG_GROUP && st == DIE_OK; ++i) {
+    if (parts) {
+        const int third_in = set0, third_own = (set0 + 2) % 3, third_ret = (set0 + 1) % 3;  // groups g, g-1, g-2
+        if (parts & XP_INGEST)
+            for (int i = 0; i < K && st == DIE_OK; ++i) {
                 StepRef user, owner;
-                refs(i, user, owner);
-                st = xchg_launch_step(x, (lane0 + i) % XCHG_SETS, user, owner, B, nullptr, x->qdesc, off[(lane0 + i) % XCHG_SETS],
-                                      nullptr, XCHG_INGEST);
+                refs(i, user, owner);  // the descriptor's j0 is group g's first batch
+                st = xchg_launch_step(x, third_in * XCHG_GROUP + i, user, owner, B, nullptr, x->qdesc, 1u, nullptr, XCHG_INGEST);
             }
-            if (st != DIE_OK) break;
-            if (cudaEventRecord(x->grp_ing, x->s_in) != cudaSuccess || cudaStreamWaitEvent(x->s_own, x->grp_ing, 0) != cudaSuccess) st = DIE_ERR_CUDA;
-            if (st == DIE_OK) {
-                StepLanes ln;
-                ln.lanes = XCHG_SETS;
-                ln.lane0 = (lane0 + g0) % XCHG_SETS;
-                st = pipeline_owner_launch_group(x->pipe, x->qdesc + 1, g0, XCHG_GROUP, x->ring_dig, x->bmax, x->ring_ndev, ln, x->s_own);
-            }
-            if (st == DIE_OK && (cudaEventRecord(x->grp_own, x->s_own) != cudaSuccess ||
-                                 cudaStreamWaitEvent(x->s_ret, x->grp_own, 0) != cudaSuccess)) st = DIE_ERR_CUDA;
-            for (int i = g0; i < g0 + XCHG_GROUP && st == DIE_OK; ++i) {
-                StepRef user, owner;
-                refs(i, user, owner);
-                const int lane = (lane0 + i) % XCHG_SETS;
-                st = xchg_launch_step(x, lane, user, owner, B, nullptr, x->qdesc, off[lane], nullptr, XCHG_RETURN);
-                off[lane] += 2;
-            }
+        if ((parts & XP_OWNER) && st == DIE_OK) {
+            StepLanes ln;
+            ln.lanes = XCHG_SETS;
+            ln.lane0 = third_own * XCHG_GROUP;
+            st = pipeline_owner_launch_group(x->pipe, x->qdesc + 1, 0, K, x->ring_dig, x->bmax, x->ring_ndev, ln, x->s_own);
         }
+        if (parts & XP_RETURN)
+            for (int i = 0; i < K && st == DIE_OK; ++i) {
+                StepRef user, owner;
+                refs(i - 2 * K, user, owner);  // group g-2's slots of the caller's out / hit rings
+                // the way back's barrier is epoch_first + 1: one past the set's epoch at this launch, like the ingest's
+                st = xchg_launch_step(x, third_ret * XCHG_GROUP + i, user, owner, B, nullptr, x->qdesc, 0u, nullptr, XCHG_RETURN);
+            }
     } else {
+        unsigned int off[XCHG_SETS];
+        for (int l = 0; l < XCHG_SETS; ++l) off[l] = 1u;
         for (int i = 0; i < K && st == DIE_OK; ++i) {
-            const int lane = (lane0 + i) % XCHG_SETS;
+            const int lane = (set0 + i) % XCHG_SETS;
             StepRef user, owner;
             refs(i, user, owner);
             st = xchg_launch_step(x, lane, user, owner, B, nullptr, x->qdesc, off[lane], nullptr);
@@ -750,7 +764,8 @@ static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_
     die_xchg::Replay& r = x->graphs[x->n_graphs++];
     r.B = B;
     r.K = K;
-    r.set0 = lane0;
+    r.set0 = set0;
+    r.parts = parts;
     r.exec = exec;
     *out = exec;
     return DIE_OK;
@@ -759,7 +774,7 @@ static die_status_t xchg_graph_get(die_xchg* x, int32_t B, int K, cudaGraphExec_
 __global__ void xchg_desc_set_kernel(QueueDesc* dst, QueueDesc user, QueueDesc owner, KvMirrorArgs m) {
     dst[0] = user;
     dst[1] = owner;
-    kv_mirror_write(m.st, m.m, m.ops_seen, m.gen, m.seq);  // state before this replay -> the host's bounds
+    if (m.m) kv_mirror_write(m.st, m.m, m.ops_seen, m.gen, m.seq);  // state before this owner launch -> the host's bounds
 }
 
 // One flushed batch ingested on this rank; results in request order.  Every rank of the group must make the
@@ -790,7 +805,7 @@ extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, con
     const size_t row = (size_t)B * x->dim;
     int32_t j = 0;
     const int K = x->graph_steps;
-    if (K >= 2 && B > 0 && pipeline_graph_fits(x->pipe, x->bmax, K)) {
+    if (K >= 2 && B > 0 && n_batches >= K && pipeline_graph_fits(x->pipe, x->bmax, K)) {
         QueueDesc du, dw;
         memset(&du, 0, sizeof(du));
         memset(&dw, 0, sizeof(dw));
@@ -809,36 +824,75 @@ extern "C" die_status_t die_xchg_step_many(die_xchg_t* x, int32_t n_batches, con
         dw.batch = x->bmax;
         dw.now0 = now0;
         dw.now_step = now_step;
-        for (; n_batches - j >= K; j += K) {
-            cudaGraphExec_t exec;
-            DIE_TRY(xchg_graph_get(x, B, K, &exec));
-            unsigned long long tail0;
-            KvMirrorArgs mirror;
-            DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, K, user, &dw.kv, &tail0, &mirror));
-            dw.tail0 = tail0;
-            du.j0 = dw.j0 = j;
-            if (x->owner_group && K % XCHG_GROUP == 0) {  // the owner's persistent launches walk the lanes' buffers as rings
-                const long long lane0 = (long long)(x->steps % XCHG_SETS);
-                dw.payload = x->ring_pay;
-                dw.out = x->ring_out;
-                dw.hit = x->ring_hit;
-                dw.payload_stride = dw.out_stride = (long long)x->bmax * x->dim;
-                dw.hit_stride = x->bmax;
-                dw.ring = dw.pay_ring = XCHG_SETS;
-                dw.j0 = lane0;            // buffers: step i of the group uses lane (lane0 + i) % XCHG_SETS
-                dw.jt = (long long)j - lane0;  // clock: still batch j + i of the queue
+        // replayed groups start on a group boundary of the buffer sets (stream-launched remainders shift the counter;
+        // skipping sets is harmless, every set carries its own barrier epoch)
+        x->steps = (x->steps + (unsigned long long)K - 1) / K * K;
+        // the way back of a group runs on several streams: two batches of one group must not share an out / hit slot
+        if (out_ring < K && n_batches > out_ring)
+            DIE_FAIL(DIE_ERR_INVALID, "die_xchg_step_many: out_ring must hold a group of %d batches (or the whole queue)", K);
+        const bool pipelined = x->owner_group && K <= XCHG_GROUP;
+        const int n_groups = n_batches / K;
+        if (pipelined) {
+            // launch t: ingest of group t | owner launch of group t-1 | way back of group t-2 (see xchg_graph_get)
+            dw.payload = x->ring_pay;  // the owner's persistent launch walks the sets' buffers as rings
+            dw.out = x->ring_out;
+            dw.hit = x->ring_hit;
+            dw.payload_stride = dw.out_stride = (long long)x->bmax * x->dim;
+            dw.hit_stride = x->bmax;
+            dw.ring = dw.pay_ring = XCHG_SETS;
+            for (int t = 0; t < n_groups + 2; ++t) {
+                const unsigned long long g = x->steps / K;  // the group launch t would ingest
+                const int third_in = (int)(g % 3), third_own = (int)((g + 2) % 3), third_ret = (int)((g + 1) % 3);
+                const int parts = (t < n_groups ? XP_INGEST : 0) | (t >= 1 && t - 1 < n_groups ? XP_OWNER : 0) |
+                                  (t >= 2 ? XP_RETURN : 0);
+                cudaGraphExec_t exec;
+                DIE_TRY(xchg_graph_get(x, B, K, parts, third_in, &exec));
+                KvMirrorArgs mirror;
+                memset(&mirror, 0, sizeof(mirror));
+                if (parts & XP_OWNER) {
+                    unsigned long long tail0;
+                    DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, K, user, &dw.kv, &tail0, &mirror));
+                    dw.tail0 = tail0;
+                    dw.j0 = (long long)third_own * XCHG_GROUP;      // buffers: step i of the group uses set third_own * 16 + i
+                    dw.jt = (long long)(t - 1) * K - dw.j0;          // clock: still batch (t-1) * K + i of the queue
+                }
+                du.j0 = (long long)t * K;  // ingest: batch t*K + i; way back (StepRef.i = i - 2K): batch (t-2)*K + i
+                for (int l = 0; l < XCHG_SETS; ++l) du.epoch0[l] = x->lane[l].epoch;
+                du.trace = dw.trace = trace_buffer();
+                xchg_desc_set_kernel<<<1, 1, 0, user>>>(x->qdesc, du, dw, mirror);
+                DIE_LAUNCH_CHECK();
+                DIE_CUDA(cudaGraphLaunch(exec, user));
+                if (parts & XP_INGEST) count_replay();  // groups replayed (the two draining launches carry no new group)
+                count_launch((unsigned)((parts & XP_INGEST ? 4 * K : 0) + (parts & XP_OWNER ? 1 : 0) + (parts & XP_RETURN ? 3 * K : 0)));
+                for (int i = 0; i < K; ++i) {  // one barrier per step and stage
+                    if (parts & XP_INGEST) x->lane[third_in * XCHG_GROUP + i].epoch += 1u;
+                    if (parts & XP_RETURN) x->lane[third_ret * XCHG_GROUP + i].epoch += 1u;
+                }
+                // the counter advances with every launch, so that the three thirds rotate through the drain as well;
+                // the sets the last two launches "ingest" nothing into are simply skipped
+                x->steps += (unsigned long long)K;
             }
-            for (int l = 0; l < XCHG_SETS; ++l) du.epoch0[l] = x->lane[l].epoch;
-            du.trace = dw.trace = trace_buffer();
-            xchg_desc_set_kernel<<<1, 1, 0, user>>>(x->qdesc, du, dw, mirror);
-            DIE_LAUNCH_CHECK();
-            DIE_CUDA(cudaGraphLaunch(exec, user));
-            count_replay();
-            count_launch(x->owner_group && K % XCHG_GROUP == 0 ? (unsigned)(K * 7 + K / XCHG_GROUP)
-                                                               : (unsigned)(K * (7 + pipeline_launches_per_step(x->pipe))));
-            const int set0 = (int)(x->steps % XCHG_SETS);
-            for (int i = 0; i < K; ++i) x->lane[(set0 + i) % XCHG_SETS].epoch += 2u;  // two barriers per step
-            x->steps += (unsigned long long)K;
+            j = n_groups * K;
+        } else {
+            for (; n_batches - j >= K; j += K) {
+                const int set0 = (int)(x->steps % XCHG_SETS);
+                cudaGraphExec_t exec;
+                DIE_TRY(xchg_graph_get(x, B, K, 0, set0, &exec));
+                unsigned long long tail0;
+                KvMirrorArgs mirror;
+                DIE_TRY(pipeline_owner_reserve(x->pipe, x->bmax, K, user, &dw.kv, &tail0, &mirror));
+                dw.tail0 = tail0;
+                du.j0 = dw.j0 = j;
+                for (int l = 0; l < XCHG_SETS; ++l) du.epoch0[l] = x->lane[l].epoch;
+                du.trace = dw.trace = trace_buffer();
+                xchg_desc_set_kernel<<<1, 1, 0, user>>>(x->qdesc, du, dw, mirror);
+                DIE_LAUNCH_CHECK();
+                DIE_CUDA(cudaGraphLaunch(exec, user));
+                count_replay();
+                count_launch((unsigned)(K * (7 + pipeline_launches_per_step(x->pipe))));
+                for (int i = 0; i < K; ++i) x->lane[(set0 + i) % XCHG_SETS].epoch += 2u;  // two barriers per step
+                x->steps += (unsigned long long)K;
+            }
         }
     }
     if (j == n_batches) return DIE_OK;
@@ -860,15 +914,15 @@ extern "C" die_status_t die_xchg_prepare(die_xchg_t* x, int32_t B) {
     if (!x || B <= 0 || B > x->cap) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_prepare: B must be in [1, cap]");
     const int K = x->graph_steps;
     if (K < 2 || !pipeline_graph_fits(x->pipe, x->bmax, K)) return DIE_OK;  // steps will be stream-launched
-    // one graph per buffer set a group can start on (stream-launched remainders of a queue shift it)
-    const unsigned long long steps = x->steps;
     die_status_t st = DIE_OK;
-    for (int l = 0; l < XCHG_SETS && st == DIE_OK; ++l) {
-        cudaGraphExec_t exec;
-        x->steps = steps + (unsigned long long)l;
-        st = xchg_graph_get(x, B, K, &exec);
+    cudaGraphExec_t exec;
+    if (x->owner_group && K <= XCHG_GROUP) {
+        const int all_parts[] = {XP_INGEST, XP_INGEST | XP_OWNER, XP_INGEST | XP_OWNER | XP_RETURN, XP_OWNER | XP_RETURN, XP_RETURN, XP_OWNER};
+        for (int parts : all_parts)
+            for (int third = 0; third < 3 && st == DIE_OK; ++third) st = xchg_graph_get(x, B, K, parts, third, &exec);
+    } else {
+        for (int set0 = 0; set0 < XCHG_SETS && st == DIE_OK; set0 += K) st = xchg_graph_get(x, B, K, 0, set0 % XCHG_SETS, &exec);
     }
-    x->steps = steps;
     return st;
 }
 

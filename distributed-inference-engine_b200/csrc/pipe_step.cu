@@ -386,6 +386,20 @@ __device__ __forceinline__ void warp_count_add(unsigned long long* ctr, bool pre
         atomicAdd(ctr, negative ? (unsigned long long)(-(long long)__popc(m)) : (unsigned long long)__popc(m));
 }
 
+// The requests request CTA `cta` owns in a step: [q0, q0 + nq).  With a host-known batch size every CTA takes R; when
+// the size only exists on the device (owner pass of the exchange, sized for owner_max but holding about half of it)
+// the batch is spread evenly over all request CTAs instead of filling the first ones with R rows each.
+__device__ __forceinline__ void ps_span(const StepParams& P, int lane_idx, int cta, int& Bs, int& q0, int& nq) {
+    Bs = P.B;
+    int Rs = P.R;
+    if (P.n_req_dev) {
+        Bs = min(Bs, (int)__ldcg(P.n_req_dev + (P.lanes ? lane_idx : 0)));
+        Rs = min(P.R, max(4, ((Bs + P.n_req - 1) / P.n_req + 3) & ~3));
+    }
+    q0 = cta * Rs;
+    nq = max(0, min(Rs, Bs - q0));
+}
+
 __global__ void __launch_bounds__(PS_THREADS, 1)
 pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ QueueDesc qv, int use_qv) {
     extern __shared__ uint8_t ps_smem_raw[];
@@ -425,6 +439,7 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
     KvState* st = kv.st;
     if (cta == 0 && tid == 0 && P.mirror.m)
         kv_mirror_write(P.mirror.st, P.mirror.m, P.mirror.ops_seen, P.mirror.gen, P.mirror.seq);
+    trace_mark(sr, TR_GET);
 
     // ---- prologue: TMEM + weights (request CTAs), MD5 of every key of the launch (all CTAs) -------------------
     const uint32_t ncols = N <= 32 ? 32u : (N <= 64 ? 64u : (N <= 128 ? 128u : 256u));
@@ -461,8 +476,9 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
             ps_cp_async16(b_base + (size_t)(ck >> 3) * ((size_t)N * 128) + tc::sw128_offset((uint32_t)r, (uint32_t)(ck & 7)),
                           P.W + (size_t)r * K + ck * 4);
         }
-        const int nq0 = max(0, min(R, P.B - cta * R));
-        ps_load_tile(a_base0, a_first.payload, cta * R, nq0, K);
+        int B0, q00, nq0;
+        ps_span(P, P.lanes ? P.lane0 % P.lanes : 0, cta, B0, q00, nq0);
+        ps_load_tile(a_base0, a_first.payload, q00, nq0, K);
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
 #define PS_MARK(i)                                             \
@@ -490,10 +506,10 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
         const int lane_s = P.lanes ? (P.lane0 + s) % P.lanes : s;       // which per-step digest / count buffer
         const int lane_n = P.lanes ? (P.lane0 + s + 1) % P.lanes : s + 1;
         const bool next_ready = s + 1 < P.n_steps && !(P.dbg & 1);
-        int Bs = P.B;
-        if (P.n_req_dev) Bs = min(Bs, (int)__ldcg(P.n_req_dev + (P.lanes ? lane_s : 0)));
-        const int q0 = cta * R;
-        const int nq = is_req && !(P.dbg & 1) ? max(0, min(R, Bs - q0)) : 0;
+        int Bs, q0, nq, Bn = 0, q0n = 0, nqn = 0;
+        ps_span(P, lane_s, cta, Bs, q0, nq);
+        if (!is_req || (P.dbg & 1)) nq = 0;
+        if (next_ready) ps_span(P, lane_n, cta, Bn, q0n, nqn);
         uint8_t* a_cur = a_base0 + (size_t)(s & 1) * a_bytes;
         const uint4* dig = P.digests + (size_t)lane_s * P.B;
         const uint4* dig_next = P.digests + (size_t)lane_n * P.B;
@@ -507,8 +523,7 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
             if (next_ready) {  // PACK of the next batch: its rows travel while this batch is processed
                 StepRef r2 = sr;
                 r2.i += s + 1;
-                ps_load_tile(a_base0 + (size_t)((s + 1) & 1) * a_bytes, step_resolve(r2).payload, q0,
-                             max(0, min(R, P.B - q0)), K);
+                ps_load_tile(a_base0 + (size_t)((s + 1) & 1) * a_bytes, step_resolve(r2).payload, q0n, nqn, K);
             }
             asm volatile("cp.async.commit_group;" ::: "memory");
             if (tid < R) {
@@ -518,8 +533,8 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
                     key = have_next ? key_next : fp_of(__ldcg(dig + q0 + tid));
                     home = ld_slot_line(&kv.slots[key.lo & kv.mask]);
                 }
-                have_next = next_ready && q0 + tid < P.B;
-                if (have_next) key_next = fp_of(__ldcg(dig_next + q0 + tid));
+                have_next = next_ready && tid < nqn;
+                if (have_next) key_next = fp_of(__ldcg(dig_next + q0n + tid));
                 if (active) {
                     const int q = q0 + tid;
                     unsigned long long value;
@@ -708,6 +723,7 @@ pipe_step_kernel(const __grid_constant__ StepParams P, const __grid_constant__ Q
     if (is_req && warp == 3) ps_stash_return(kv, s_stash, &s_nstash);  // the unused stock goes back to the table's queue
     // every CTA has passed the last barrier once CTA 0 has: the next launch starts counting from here
     if (cta == 0 && tid == PS_BAR_THREAD) g->bar_base = target;
+    trace_mark(sr, TR_STEP_END);
     if (is_req && warp == 0) {
         tc::fence_after_thread_sync();
         tc::tmem_dealloc(s_tmem, ncols);

@@ -711,10 +711,9 @@ die_status_t pipeline_owner_launch(die_pipeline* p, const StepRef& sr, uint32_t*
 
 bool pipeline_owner_group_supported(const die_pipeline* p, int B_max) {
     int r, n;
-    // Opt-in (DIE_XCHG_OWNER_GROUP=1, read at die_xchg_create): measured on 2 x B200 at the C2 workload, four owner passes
-    // per persistent launch gave 40.5 us per step against 36-38 us for one launch per step -- the long-lived owner
-    // grid leaves the concurrent ingest / return kernels too few SM resources -- so one launch per step is the default.
-    const int on = getenv("DIE_XCHG_OWNER_GROUP") ? atoi(getenv("DIE_XCHG_OWNER_GROUP")) : 0;
+    // One persistent launch per group of 16 owner passes (exchange.cu's software-pipelined replays).  On by default;
+    // DIE_XCHG_OWNER_GROUP=0 (read at die_xchg_create) keeps one launch per step inside one graph per group.
+    const int on = getenv("DIE_XCHG_OWNER_GROUP") ? atoi(getenv("DIE_XCHG_OWNER_GROUP")) : 1;
     return on && p->persistent && pipe_step_shape(B_max, p->cfg.dim_in, p->cfg.dim_out, p->n_chunks, &r, &n);
 }
 

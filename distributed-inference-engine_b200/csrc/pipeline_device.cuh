@@ -29,6 +29,8 @@ struct StepArgs {
     unsigned long long t_get, t_set;  // first LRU stamp of the batch's gets / of its sets
 };
 
+constexpr int XCHG_SETS = 48;  // buffer sets of the sharded step (exchange.cu): three groups of 16 steps in flight
+
 struct QueueDesc {
     KvView kv;
     const uint8_t* key_bytes;
@@ -44,7 +46,7 @@ struct QueueDesc {
     int batch;     // stamps per get (= per set) pass of one step
     double now0, now_step;
     unsigned long long tail0;  // LRU stamp of the replay's first op
-    unsigned int epoch0[8];    // exchange only: barrier epoch of each buffer set before the replay
+    unsigned int epoch0[XCHG_SETS];  // exchange only: barrier epoch of each buffer set before the replay
     unsigned long long* trace; // diagnostics (die_debug_trace_enable): [0] cursor, [1] capacity, then (tag, ns) pairs
 };
 
@@ -56,7 +58,7 @@ struct StepRef {
 
 #ifdef __CUDACC__
 // Diagnostics: thread 0 of CTA 0 of a replayed kernel logs (step << 8 | id, %globaltimer).
-enum TraceId { TR_ROUTE = 1, TR_DISPATCH, TR_BAR_IN, TR_BAR_OUT, TR_GET, TR_GET_TAIL, TR_CLAIM, TR_MODEL, TR_UNPACK, TR_SCATTER };
+enum TraceId { TR_ROUTE = 1, TR_DISPATCH, TR_BAR_IN, TR_BAR_OUT, TR_GET, TR_GET_TAIL, TR_CLAIM, TR_MODEL, TR_UNPACK, TR_SCATTER, TR_STEP_END };
 __device__ __forceinline__ void trace_mark_q(const QueueDesc* q, int i, int id) {
     if (!q || !q->trace) return;
     unsigned long long* t = q->trace;

@@ -14,7 +14,7 @@ import bench  # noqa: E402
 from die import _cabi  # noqa: E402
 
 NAMES = {1: "route", 2: "dispatch", 3: "bar_in", 4: "bar_out", 5: "get", 6: "get_tail", 7: "claim", 8: "model",
-         9: "unpack", 10: "scatter"}
+         9: "unpack", 10: "scatter", 11: "step_end"}
 rank = int(os.environ.get("RANK", "0"))
 world = int(os.environ.get("WORLD_SIZE", "1"))
 torch.cuda.set_device(rank)
@@ -35,8 +35,8 @@ off_d = torch.from_numpy(np.arange(B + 1, dtype=np.int64) * 15).cuda()
 NW, NT = int(os.environ.get('NW', '480')), int(os.environ.get('NT', '64'))
 _, keys, _, x = bench.make_batches(rng, NW + NT)
 kd, xd = torch.from_numpy(keys).cuda(), torch.from_numpy(x).cuda()
-out = torch.empty((8, B, D), device="cuda")
-hit = torch.empty((8, B), dtype=torch.uint8, device="cuda")
+out = torch.empty((64, B, D), device="cuda")
+hit = torch.empty((64, B), dtype=torch.uint8, device="cuda")
 for c in range(0, NW, 64):
     run(kd[c:c + 64], off_d, xd[c:c + 64], 1.0 + c * 0.01, 0.01, out, hit)
 torch.cuda.synchronize()
@@ -68,10 +68,15 @@ if rank == 0:
         print("across replays, sorted:", " ".join("%.0f" % v for v in sorted(edge)))
         for k2, v in sorted(acc.items()):
             print(k2, "n", len(v), "mean us %.1f" % (sum(v) / len(v)), "max %.1f" % max(v))
-    # the third replay of 8 steps: records NT/8*2 .. in time order
+    if os.environ.get("ONLY"):  # e.g. ONLY=5,11: every owner launch's start and end over the whole traced queue
+        kinds = {int(v) for v in os.environ["ONLY"].split(",")}
+        for t, i, k in recs:
+            if k in kinds:
+                print(f"{(t - t0) / 1e3:9.1f}  {i & 0xffff:5d} {NAMES.get(k, k)}")
+        sys.exit(0) if world == 1 else None
     lo = recs[len(recs) // 2][0]
     for t, i, k in recs:
-        if lo <= t < lo + 450_000:
+        if lo <= t < lo + int(os.environ.get('WIN', '450')) * 1000:
             step = "ep%-6d" % i if k in (3, 4) else "step%-4d" % i
             print(f"{(t - lo) / 1e3:8.1f}  {step} {NAMES.get(k, k)}")
 if world > 1:
