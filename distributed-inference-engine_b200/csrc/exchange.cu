@@ -20,10 +20,12 @@
 // Owners see the sources in rank order, request order kept inside each source: the order the CPU oracle's
 // process_exchange applies.
 //
-// die_xchg_step / die_xchg_step_many run the step as a three-stage pipeline (ingest | owner pass | way back, one
-// in-order stream each) over XCHG_SETS buffer sets, and replay groups of steps from one CUDA graph; the
-// stand-alone phase entry points (die_xchg_dispatch / compact / return / scatter, bucket order from
-// die_bucket_by_shard) stay as a cross-check driven from Python.
+// die_xchg_step / die_xchg_step_many run the step as a three-stage pipeline (ingest | owner pass | way back) over
+// XCHG_SETS buffer sets.  A single step overlaps its neighbours through per-stage streams; a queue is replayed in
+// groups of 16 steps from captured graphs, software-pipelined across launches so that the owner stage is ONE persistent
+// launch per group that never waits for a transfer (xchg_graph_get).  The stand-alone phase entry points
+// (die_xchg_dispatch / compact / return / scatter, bucket order from die_bucket_by_shard) stay as a cross-check
+// driven from Python.
 #include <vector>
 
 #include "pipeline_internal.cuh"

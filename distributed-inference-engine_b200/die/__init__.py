@@ -4,6 +4,14 @@ Drop-in mirror of the reference's hot-path classes; the compute runs in libdie.s
 bound through ctypes (die/_cabi.py, include/die.h).  Importing this package needs neither torch nor
 a GPU; calling a compute method without the built library or without a CUDA device raises.
 """
+import os as _os
+
+# Spin-waiting kernels (grid barrier of the persistent step, cross-GPU barrier) must not be resident while the driver
+# loads a module lazily at some kernel's first launch; the sharded step wants its streams on separate hardware queues.
+# Both are read when CUDA initialises, so they are set at import unless the process already chose otherwise.
+_os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")
+_os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 from .batcher import Batch, BatchedRequest, Batcher, PackedBatch
 from .config import ModelConfig
 from .model_registry import ModelRegistry, ModelShard, ModelStatus, ModelVersion

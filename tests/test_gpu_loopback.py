@@ -90,9 +90,10 @@ def test_loopback_sharded_steps_match_oracle(world, model):
 
 @pytest.mark.parametrize("owner_group", ["0", "1"])
 def test_loopback_replayed_queue_matches_oracle(monkeypatch, owner_group):
-    """die_xchg_step_many: groups of steps replayed from one captured graph per rank (three stage streams, four
-    buffer sets, epochs from the device descriptor), until the owners' tables evict.  owner_group=1: the opt-in form
-    in which the K owner passes of a group are one persistent launch driven by ingested / owned flags."""
+    """die_xchg_step_many over many calls, until the owners' tables evict.  owner_group=1 (the default): the
+    software-pipelined replays -- per graph launch the ingest of group g, ONE persistent owner launch over group g-1
+    and the way back of group g-2, on three thirds of the buffer sets, barrier epochs from the device descriptor.
+    owner_group=0: whole steps captured into one graph per group, one owner launch per step."""
     from die import ops
     from die.exchange import LoopbackPeerGroup
     monkeypatch.setenv("DIE_GRAPH_STEPS", "4")
