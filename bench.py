@@ -680,8 +680,8 @@ def main():
                "h2d_bytes_per_step": G * (B * KEY_LEN + B * D * 4) + (B + 1) * 8, "d2h_bytes_per_step": G * (B * D * 4 + B),
                "ms_per_step": 1e3 * dt / K,
                "api": "die_pipeline_run_host_many (C-ABI, pinned host buffers), one call per step of G batches; copy-in / "
-                      "kernels / copy-out of consecutive groups of 16 batches overlap; each call returns with its results "
-                      "on the host",
+                      "kernels / copy-out of consecutive groups of %s batches overlap; each call returns with its results "
+                      "on the host" % os.environ.get("DIE_HOST_GROUP", "16"),
                "per_call_sync": {"value": n_sync * B / dt_sync, "ms_per_batch": 1e3 * dt_sync / n_sync,
                                  "api": "die_pipeline_run_host, one blocking call per batch"}}
         del hk, hx, hout, hhit

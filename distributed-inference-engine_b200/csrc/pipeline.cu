@@ -20,6 +20,8 @@
 // steps replayed from one CUDA graph: see StepRef / QueueDesc in pipeline_device.cuh and replay_fast() below.
 #include "model_internal.cuh"
 #include "pipeline_device.cuh"
+#include <vector>
+
 #include "pipeline_internal.cuh"
 #include "route_device.cuh"
 
@@ -1011,7 +1013,11 @@ extern "C" die_status_t die_pipeline_run_host_many(die_pipeline_t* p, int32_t n_
     }
     // Grouped form: G consecutive batches are contiguous in the caller's arrays, so one copy per array moves a
     // group, one graph replay computes it, and the copy engines work on the neighbouring groups meanwhile.
-    const int G = p->graph_steps;
+    // Groups of fewer batches would shorten the call's first copy-in and last copy-out, which nothing overlaps, but
+    // measured the other way round on B200 (C2, 128 batches per call: groups of 2 / 4 / 8 / 16 -> 52.5 / 61.0 / 67.4 /
+    // 70.4 M requests/s): per-copy overheads outweigh the shorter ramp.  DIE_HOST_GROUP overrides.
+    int G = p->graph_steps;
+    if (const char* e = getenv("DIE_HOST_GROUP")) G = std::max(2, std::min(G, atoi(e)));
     if (n_batches >= 2 && G >= 2 && pipeline_graph_fits(p, B, std::min<int>(G, n_batches)) &&
         (n_batches == 1 || (size_t)key_bytes_stride <= p->key_stage_stride) &&
         (key_off_stride == 0 || key_off_stride == B + 1)) {
@@ -1027,9 +1033,32 @@ extern "C" die_status_t die_pipeline_run_host_many(die_pipeline_t* p, int32_t n_
             p->g_steps = G;
         }
         const size_t mb = (size_t)c.max_batch;
+        // Nothing overlaps the call's first copy-in and its last copy-out (and the kernels between them): with uniform
+        // groups that is two whole groups of PCIe time per call (C2: 1.9 of 7.4 ms).  The first and the last G batches are
+        // therefore split G/4 + 3G/4 and 3G/4 + G/4; everything between moves in full groups (fewest copies and replays).
+        const bool ramp = G >= 8 && n_batches >= 3 * G;
+        auto group_at = [&](int32_t j) {
+            const int rem = n_batches - j;
+            if (ramp && j == 0) return G / 4;
+            if (ramp && j == G / 4) return G - G / 4;
+            if (ramp && rem == G) return G - G / 4;
+            return std::min<int>(G, rem);
+        };
+        // DIE_HOST_TRACE=1 (diagnostics): timed events around every group's copy-in, kernels and copy-out, printed
+        // relative to the call's start after the call has drained
+        static const bool host_trace = getenv("DIE_HOST_TRACE") && atoi(getenv("DIE_HOST_TRACE"));
+        std::vector<cudaEvent_t> tev;
+        auto mark = [&](cudaStream_t st) {
+            if (!host_trace) return;
+            cudaEvent_t e;
+            cudaEventCreate(&e);
+            cudaEventRecord(e, st);
+            tev.push_back(e);
+        };
+        mark(s);
         int set = 0;
-        for (int32_t j = 0; j < n_batches; j += G, ++set) {
-            const int K = std::min<int>(G, n_batches - j);
+        for (int32_t j = 0, K = 0; j < n_batches; j += K, ++set) {
+            K = group_at(j);
             const int b = set % NB;
             uint8_t* dk = p->g_keys + (size_t)b * G * p->key_stage_stride;
             int64_t* dko = p->g_off + (size_t)b * G * (mb + 1);
@@ -1042,13 +1071,16 @@ extern "C" die_status_t die_pipeline_run_host_many(die_pipeline_t* p, int32_t n_
             }
             const int64_t* ko_last = key_off + (size_t)(j + K - 1) * key_off_stride;
             const size_t key_span = (size_t)(K - 1) * key_bytes_stride + (size_t)(ko_last[B] - ko_last[0]);
+            mark(p->s_in);
             if (key_span)
                 DIE_CUDA(cudaMemcpyAsync(dk, key_bytes + (size_t)j * key_bytes_stride, key_span, cudaMemcpyHostToDevice, p->s_in));
             DIE_CUDA(cudaMemcpyAsync(dko, key_off + (size_t)j * key_off_stride,
                                      (size_t)(key_off_stride ? K : 1) * (B + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, p->s_in));
             DIE_CUDA(cudaMemcpyAsync(dp, payload + (size_t)j * in_row, (size_t)K * in_row * sizeof(float), cudaMemcpyHostToDevice, p->s_in));
             DIE_CUDA(cudaEventRecord(p->ev_in[b], p->s_in));
+            mark(p->s_in);
             DIE_CUDA(cudaStreamWaitEvent(s, p->ev_in[b], 0));
+            mark(s);
             QueueDesc d;
             memset(&d, 0, sizeof(d));
             d.key_bytes = dk;
@@ -1072,13 +1104,24 @@ extern "C" die_status_t die_pipeline_run_host_many(die_pipeline_t* p, int32_t n_
                 DIE_TRY(die_pipeline_run_device(p, dk, dko, B, dp, now0 + j * now_step, dout, dh, nullptr, stream));
             }
             DIE_CUDA(cudaEventRecord(p->ev_done[b], s));
+            mark(s);
             DIE_CUDA(cudaStreamWaitEvent(p->s_out, p->ev_done[b], 0));
+            mark(p->s_out);
             DIE_CUDA(cudaMemcpyAsync(out + (size_t)j * out_row, dout, (size_t)K * out_row * sizeof(float), cudaMemcpyDeviceToHost, p->s_out));
             if (hit_out) DIE_CUDA(cudaMemcpyAsync(hit_out + (size_t)j * B, dh, (size_t)K * B, cudaMemcpyDeviceToHost, p->s_out));
             DIE_CUDA(cudaEventRecord(p->ev_out[b], p->s_out));
+            mark(p->s_out);
         }
         DIE_CUDA(cudaStreamSynchronize(p->s_out));
         DIE_CUDA(cudaStreamSynchronize(s));
+        if (host_trace) {  // per group: copy-in [start, end], kernels [start, end], copy-out [start, end] in ms
+            for (size_t g = 0; 1 + 6 * g + 5 < tev.size(); ++g) {
+                float t[6];
+                for (int k = 0; k < 6; ++k) cudaEventElapsedTime(&t[k], tev[0], tev[1 + 6 * g + k]);
+                fprintf(stderr, "group %2zu  in %.3f-%.3f  run %.3f-%.3f  out %.3f-%.3f\n", g, t[0], t[1], t[2], t[3], t[4], t[5]);
+            }
+            for (cudaEvent_t e : tev) cudaEventDestroy(e);
+        }
         return DIE_OK;
     }
     for (int32_t j = 0; j < n_batches; ++j) {
