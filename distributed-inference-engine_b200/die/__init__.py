@@ -22,7 +22,7 @@ from .mock_models import FakeModel, LinearModel, MLPModel, mock_batch_inference
 __all__ = ["Batch", "BatchedRequest", "Batcher", "PackedBatch", "ModelConfig", "ModelRegistry", "ModelShard",
            "ModelStatus", "ModelVersion", "Router", "WorkerHealth", "WorkerInfo", "Worker", "FakeModel",
            "LinearModel", "MLPModel", "mock_batch_inference", "KVCache", "KVStore", "create_kv_store", "CacheEntry",
-           "DispatchPipeline", "Coordinator"]
+           "DispatchPipeline", "Coordinator", "DeviceBatcher"]
 
 
 def __getattr__(name):  # torch-dependent modules load lazily
@@ -32,6 +32,9 @@ def __getattr__(name):  # torch-dependent modules load lazily
     if name == "DispatchPipeline":
         from .pipeline import DispatchPipeline
         return DispatchPipeline
+    if name == "DeviceBatcher":
+        from .device_batcher import DeviceBatcher
+        return DeviceBatcher
     if name == "Coordinator":
         from .coordinator import Coordinator
         return Coordinator

@@ -26,6 +26,10 @@ class DieError(RuntimeError):
         self.status = status
 
 
+class FlushDesc(ctypes.Structure):  # die_flush_desc_t
+    _fields_ = [("queue", c_int32), ("count", c_int32), ("trigger", c_int32), ("pad", c_int32), ("opened_at", c_double)]
+
+
 class PipelineConfig(ctypes.Structure):
     _fields_ = [("kv_max_size", c_uint64), ("default_ttl", c_double), ("max_batch", c_int32),
                 ("dim_in", c_int32), ("dim_out", c_int32), ("model", c_int32), ("max_key_bytes", c_int32),
@@ -93,6 +97,11 @@ SIGNATURES = {
     "die_xchg_step_many": (c_int32, [P, c_int32, P, c_int64, P, c_int64, c_int32, P, c_double, c_double, P, P, c_int32, P]),
     "die_xchg_check_sync": (c_int32, [P, P]),
     "die_xchg_prepare": (c_int32, [P, c_int32]),
+    "die_batcher_create": (c_int32, [c_int32, c_int32, c_double, c_int32, c_int32, c_int32, P, P, POINTER(c_void_p)]),
+    "die_batcher_destroy": (c_int32, [P]),
+    "die_batcher_tick": (c_int32, [P, c_double, c_int32, P, P, P, c_int32, P, P, P]),
+    "die_batcher_flushes_sync": (c_int32, [P, POINTER(c_int32), P, P, c_int32, POINTER(c_uint64), P]),
+    "die_batcher_stats_sync": (c_int32, [P, POINTER(c_uint64), POINTER(c_uint64), POINTER(c_uint64), P, P]),
     "die_pipeline_run_host": (c_int32, [P, P, P, c_int32, P, c_double, P, P, P]),
     "die_pipeline_run_device_many": (c_int32, [P, c_int32, P, c_int64, P, c_int64, c_int32, P, c_double, c_double, P, P,
                                                c_int32, P]),

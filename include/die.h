@@ -309,6 +309,48 @@ die_status_t die_pipeline_run_owner_device_n(die_pipeline_t* p, const uint32_t* 
                                              uint8_t* hit_out, die_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Device-resident Batcher: per-key accumulation with size- and latency-triggered flush, for requests that already
+ * live on the GPU.  Replaces Batcher.add_request / _schedule_flush / _flush_batch / _process_batch / stop
+ * (src/batcher.py:70-230) for fixed-width payloads: one open batch per key ("model:version", numbered 0..n_queues-1 by
+ * the host), flushed when it holds max_batch requests (batcher.py:143) or when max_latency has passed since it was
+ * opened (batcher.py:150-166).  Time advances in ticks:
+ *   die_batcher_tick(now, force, arrivals): 1. every open batch with now - opened_at >= max_latency flushes, in the
+ *     order the batches were opened; 2. the arrivals are appended in order, flushing every batch they fill; 3. force != 0
+ *     is stop() (batcher.py:70-100): the batches still open flush in creation order.
+ *   A flushed batch is packed (batcher.py:211), run through the model -- echo (weights NULL, fake_model.py:52) or the
+ *   mock fp32 linear layer with the queue's own weights -- and unpacked (batcher.py:225-227): the result row of request r
+ *   lands in out[request_id[r]], and batch_of[request_id[r]] = the number of the batch it was served in (optional).
+ *   request_id is the caller's handle for the future (batcher.py:118): an index into out.
+ * All on the stream, no host round trip; die_batcher_flushes_sync reads back what the LAST tick flushed (descriptors
+ * in flush order, optionally the request ids of every batch, [cap][max_batch]) and die_batcher_stats_sync the
+ * reference's counters (batcher.py:58-60) plus the open batches' sizes.  A tick that would flush more batches than
+ * max_arrivals / max_batch + 2 * n_queues is dropped and the next *_sync call returns DIE_ERR_TOO_LARGE.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct die_batcher die_batcher_t;
+enum { DIE_FLUSH_LATENCY = 0, DIE_FLUSH_SIZE = 1, DIE_FLUSH_FORCED = 2 };
+typedef struct die_flush_desc {
+    int32_t queue;     /* key of the batch */
+    int32_t count;     /* requests in it */
+    int32_t trigger;   /* DIE_FLUSH_* */
+    int32_t pad;
+    double opened_at;  /* Batch.created_at (batcher.py:127) */
+} die_flush_desc_t;
+die_status_t die_batcher_create(int32_t n_queues, int32_t max_batch, double max_latency_s, int32_t dim_in, int32_t dim_out,
+                                int32_t max_arrivals, const float* weights /*[host] [n_queues][dim_out][dim_in] or NULL*/,
+                                const float* bias /*[host] [n_queues][dim_out] or NULL*/, die_batcher_t** out);
+die_status_t die_batcher_destroy(die_batcher_t* b);
+die_status_t die_batcher_tick(die_batcher_t* b, double now, int32_t force, const int32_t* queue /*[n]*/,
+                              const int32_t* request_id /*[n]*/, const float* payload /*[n, dim_in]*/, int32_t n,
+                              float* out /*[*, dim_out], indexed by request id*/, int32_t* batch_of /*or NULL*/,
+                              die_stream_t stream);
+die_status_t die_batcher_flushes_sync(die_batcher_t* b, int32_t* n_flush /*[host]*/, die_flush_desc_t* desc /*[host] [cap] or NULL*/,
+                                      int32_t* ids /*[host] [cap][max_batch] or NULL*/, int32_t cap,
+                                      uint64_t* first_batch /*[host] or NULL*/, die_stream_t stream);
+die_status_t die_batcher_stats_sync(die_batcher_t* b, uint64_t* total_requests /*[host]*/, uint64_t* total_batches /*[host]*/,
+                                    uint64_t* total_batched_requests /*[host]*/, int32_t* pending /*[host] [n_queues] or NULL*/,
+                                    die_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
  * Dispatch / return between the GPUs of one NVSwitch box by direct peer stores.  Replaces the reference's
  * TCP + JSON hop, one request per connection (src/worker.py:84-133).  peer_* are [host] arrays of `world`
  * device pointers into a symmetric allocation (one window per rank, see csrc/exchange.cu for the layout);

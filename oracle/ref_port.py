@@ -414,6 +414,53 @@ async def port_mock_batch_inference(model: str, version: str, inputs: List[Any],
     return out
 
 
+class PortTickBatcher:
+    """The Batcher's flush schedule restated for time that advances in ticks (the form csrc/batcher.cu implements).
+
+    The reference arms a timer of max_latency when a key's batch is opened (batcher.py:124-135), flushes the batch
+    as soon as it holds max_batch_size requests (:143-146) and flushes whatever is there when the timer fires
+    (:150-166); stop() flushes the open batches in creation order (:70-100).  With no arrivals between two ticks,
+    firing the due timers at the start of a tick (in the order they were armed) gives the same batches in the same
+    order.  tests/golden/make_golden.py::gen_tick_batcher checks exactly that against the reference's own class run
+    on a virtual-time event loop.  Returns flushed batches as (key, [inputs...], trigger)."""
+
+    def __init__(self, max_batch_size: int = 32, max_latency_ms: float = 50.0):
+        if max_batch_size <= 0:
+            raise ValueError("max_batch_size must be positive")
+        if max_latency_ms <= 0:
+            raise ValueError("max_latency_ms must be positive")
+        self.max_batch_size = max_batch_size
+        self.max_latency = max_latency_ms / 1000.0
+        self.open: Dict[str, dict] = {}  # insertion order = creation order (batcher.py:88 iterates it)
+        self.total_batches = self.total_requests = self.total_batched_requests = 0
+
+    def _flush(self, key: str, trigger: str, out: list) -> None:
+        b = self.open.pop(key)
+        self.total_batches += 1                                  # batcher.py:206
+        self.total_batched_requests += len(b["requests"])        # :207
+        out.append((key, list(b["requests"]), trigger))          # PACK: arrival order (:211)
+
+    def tick(self, now: float, arrivals, force: bool = False) -> list:
+        """arrivals: [(key, inputs)] in arrival order."""
+        out: list = []
+        for key in [k for k, b in self.open.items() if now - b["created_at"] >= self.max_latency]:
+            self._flush(key, "latency", out)                     # _schedule_flush (:150-166), oldest timer first
+        for key, inputs in arrivals:
+            if key not in self.open:
+                self.open[key] = {"created_at": now, "requests": []}   # :124-135
+            self.open[key]["requests"].append(inputs)
+            self.total_requests += 1                             # :141
+            if len(self.open[key]["requests"]) >= self.max_batch_size:  # :143
+                self._flush(key, "size", out)
+        if force:                                                # stop() (:84-97)
+            for key in list(self.open):
+                self._flush(key, "forced", out)
+        return out
+
+    def pending(self) -> Dict[str, int]:
+        return {k: len(b["requests"]) for k, b in self.open.items()}
+
+
 class PortFakeModel:
     """Restates FakeModel.predict (fake_model.py:33-67): an echo.  ``sleep`` False
     removes the 50-150 ms simulated latency; timestamp/request_id omitted."""

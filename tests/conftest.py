@@ -36,3 +36,22 @@ def pytest_collection_modifyitems(config, items):
     # GPU tests must fail loudly, not skip, on a GPU box; on a CPU-only box they are
     # deselected with -m "not gpu" by the driver.  Nothing to do here.
     return
+
+
+def replay_ticks(case, tick_fn):
+    """Drives `tick_fn(now, arrivals, force) -> [(key, ids, trigger)]` with a golden case's ticks and checks every
+    flushed batch (key, members in order), when it happened relative to the ticks, and the final stop()."""
+    want = case["flushed"]
+    got = []
+    for t in case["ticks"]:
+        out = tick_fn(t["now"], [(k, rid) for k, rid in t["arrivals"]], False)
+        n_latency = sum(1 for _k, _ids, trig in out if trig == "latency")
+        assert [trig for _k, _ids, trig in out] == ["latency"] * n_latency + ["size"] * (len(out) - n_latency)
+        # the reference's timers had all fired when the tick's first request arrived
+        assert len(got) + n_latency == t["flushed_before"], t["now"]
+        got.extend(out)
+    before_stop = len(got)
+    got.extend(tick_fn(case["ticks"][-1]["now"], [], True))
+    assert all(trig == "forced" for _k, _ids, trig in got[before_stop:])
+    assert [(k, ids) for k, ids, _t in got] == [(w["key"], w["ids"]) for w in want]
+    return before_stop

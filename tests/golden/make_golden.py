@@ -409,6 +409,88 @@ def gen_batcher():
 
 
 # ----------------------------------------------------------------------------- worker / fake model
+class VirtualTimeLoop(asyncio.SelectorEventLoop):
+    """Event loop whose clock is virtual: when nothing is ready it jumps to the next timer instead of waiting, so the
+    reference Batcher's asyncio.sleep(max_latency) timers (batcher.py:152) fire in order at exact, repeatable times."""
+
+    def __init__(self):
+        super().__init__()
+        self._vt = 0.0
+
+    def time(self):
+        # every look at the clock takes a moment, as on a real clock: timers armed one after the other get strictly
+        # increasing deadlines and fire in the order they were armed (equal deadlines would leave it to the heap)
+        self._vt += 1e-12
+        return self._vt
+
+    def _run_once(self):
+        if not self._ready and self._scheduled:
+            when = self._scheduled[0]._when
+            if when > self._vt:
+                self._vt = when
+        super()._run_once()
+
+
+def gen_tick_batcher():
+    """The reference Batcher driven by arrival ticks on virtual time: which batches it flushes, in which order and why.
+    Tick times never coincide with a timer's deadline (ticks on multiples of 1 ms, latencies of x.5 ms)."""
+    import src.batcher as ref_batcher
+
+    def run_case(seed, keys, max_batch, latency_ms, n_ticks, max_per_tick, idle_prob):
+        rng = random.Random(seed)
+        loop = VirtualTimeLoop()
+        asyncio.set_event_loop(loop)
+        real_time = ref_batcher.time
+        ref_batcher.time = types.SimpleNamespace(time=loop.time)
+        ticks, flushed = [], []
+
+        async def scenario():
+            async def cb(model, version, inputs):
+                flushed.append({"key": f"{model}:{version}", "ids": list(inputs), "at": round(loop.time(), 6)})
+                return list(inputs)
+
+            b = Batcher(max_batch_size=max_batch, max_latency_ms=latency_ms, batch_callback=cb)
+            await b.start()
+            t, rid, futs = 0.0, 0, []
+            for _ in range(n_ticks):
+                t += rng.choice([1, 1, 2, 3, 7, 20]) / 1000.0
+                await asyncio.sleep(t - loop.time())       # timers due before the tick fire here, oldest first
+                n0 = len(flushed)
+                arr = []
+                if rng.random() >= idle_prob:
+                    for _i in range(rng.randint(1, max_per_tick)):
+                        k = rng.choice(keys)
+                        arr.append([k, rid])
+                        futs.append(await b.add_request(k.split(":")[0], k.split(":")[1], rid))
+                        rid += 1
+                ticks.append({"now": round(t, 6), "arrivals": arr, "flushed_before": n0})
+            stats_open = await b.get_stats()
+            await b.stop()
+            res = [await f for f in futs]
+            assert res == list(range(rid))
+            stats = await b.get_stats()
+            return stats_open, stats
+
+        try:
+            stats_open, stats = loop.run_until_complete(scenario())
+        finally:
+            ref_batcher.time = real_time
+            loop.close()
+            asyncio.set_event_loop(None)
+        keep = ("total_batches", "total_requests", "total_batched_requests", "pending_requests")
+        return {"keys": keys, "max_batch_size": max_batch, "max_latency_ms": latency_ms, "ticks": ticks, "flushed": flushed,
+                "stats_before_stop": {k: stats_open[k] for k in keep}, "stats": {k: stats[k] for k in keep}}
+
+    cases = {
+        "one_key_small": run_case(1, ["n:1"], 4, 2.5, 60, 3, 0.3),
+        "two_keys": run_case(2, ["n:1", "m:1"], 8, 4.5, 120, 6, 0.2),
+        "five_keys_bursts": run_case(3, ["a:1", "a:2", "b:1", "c:1", "d:9"], 16, 10.5, 200, 40, 0.4),
+        "mostly_latency": run_case(4, ["n:1", "m:2", "k:3"], 32, 1.5, 150, 4, 0.5),
+        "mostly_size": run_case(5, ["n:1", "m:2"], 3, 50.5, 100, 20, 0.0),
+    }
+    dump("tick_batcher.json", cases)
+
+
 def gen_worker():
     ref_fake.asyncio = types.SimpleNamespace(sleep=_no_sleep)
 
@@ -525,5 +607,6 @@ if __name__ == "__main__":
     gen_kv()
     gen_kv_policies()
     gen_batcher()
+    gen_tick_batcher()
     gen_worker()
     gen_pipeline()

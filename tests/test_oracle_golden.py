@@ -6,7 +6,7 @@ import pytest
 
 from oracle import ref_port as rp
 from oracle.pipeline import BaselinePipeline, OraclePipeline
-from conftest import load_golden
+from conftest import load_golden, replay_ticks
 
 
 # ----------------------------------------------------------------------------- routing
@@ -178,6 +178,30 @@ def test_batcher_scenarios_match_reference():
     seen, res = asyncio.run(two_keys())
     assert seen == g["two_keys_70"]["batches"]
     assert res == g["two_keys_70"]["results"]
+
+
+TICK_CASES = ["one_key_small", "two_keys", "five_keys_bursts", "mostly_latency", "mostly_size"]
+
+
+@pytest.mark.parametrize("name", TICK_CASES)
+def test_tick_batcher_matches_reference_on_virtual_time(name):
+    """PortTickBatcher (the schedule csrc/batcher.cu implements) against the reference's own Batcher run on a
+    virtual-time event loop (tests/golden/make_golden.py::gen_tick_batcher)."""
+    case = load_golden("tick_batcher.json")[name]
+    b = rp.PortTickBatcher(case["max_batch_size"], case["max_latency_ms"])
+    state = {}
+
+    def tick(now, arrivals, force):
+        if force:
+            state["before_stop"] = {"total_batches": b.total_batches, "total_requests": b.total_requests,
+                                    "total_batched_requests": b.total_batched_requests,
+                                    "pending_requests": sum(b.pending().values())}
+        return b.tick(now, arrivals, force)
+
+    replay_ticks(case, tick)
+    assert state["before_stop"] == case["stats_before_stop"]
+    assert {"total_batches": b.total_batches, "total_requests": b.total_requests,
+            "total_batched_requests": b.total_batched_requests, "pending_requests": 0} == case["stats"]
 
 
 def test_batcher_errors_match_reference():
