@@ -18,6 +18,8 @@
 //
 // Queues of batches (die_pipeline_run_device_many / run_host_many) are processed in groups of graph_steps
 // steps replayed from one CUDA graph: see StepRef / QueueDesc in pipeline_device.cuh and replay_fast() below.
+#include <cuda_bf16.h>
+
 #include "model_internal.cuh"
 #include "pipeline_device.cuh"
 #include <vector>
@@ -50,6 +52,14 @@ struct die_pipeline {
     PipeCtrl* ctrl;
     float* packed_in;    // [B, dim_in]
     float* packed_out;   // [B, dim_out]
+    // DIE_MODEL_MLP_BF16: bf16 weights (W1 [H, D], W2 [D, H]) and bf16 staging of the packed misses
+    void* mlp_w1;
+    void* mlp_w2;
+    float* mlp_b1;
+    float* mlp_b2;
+    void* mlp_x;         // [B, D] bf16
+    void* mlp_h;         // [B, H] bf16
+    void* mlp_y;         // [B, D] bf16
     // staging for the host-buffer entry points (NBUF sets: copy-in, compute and copy-out of consecutive
     // batches overlap in die_pipeline_run_host_many)
     static constexpr int NBUF = 3;
@@ -474,6 +484,30 @@ static int grid_256(long long items) {
     return (int)(blocks < 1 ? 1 : (blocks < cap ? blocks : cap));
 }
 
+// fp32 rows <-> bf16 rows around the MLP (the interface keeps fp32 payloads and results; the model computes in bf16).
+// n_rows_dev: only the packed misses are converted.
+__global__ void __launch_bounds__(256)
+rows_f32_to_bf16_kernel(const float4* __restrict__ in, uint2* __restrict__ out, long long vec_per_row, long long max_rows,
+                        const uint32_t* __restrict__ n_rows_dev) {
+    const long long n = (n_rows_dev ? min((long long)*n_rows_dev, max_rows) : max_rows) * vec_per_row;
+    for (long long i = blockIdx.x * 256ll + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+        const float4 v = __ldg(in + i);
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        out[i] = make_uint2(*reinterpret_cast<const unsigned*>(&lo), *reinterpret_cast<const unsigned*>(&hi));
+    }
+}
+__global__ void __launch_bounds__(256)
+rows_bf16_to_f32_kernel(const uint2* __restrict__ in, float4* __restrict__ out, long long vec_per_row, long long max_rows,
+                        const uint32_t* __restrict__ n_rows_dev) {
+    const long long n = (n_rows_dev ? min((long long)*n_rows_dev, max_rows) : max_rows) * vec_per_row;
+    for (long long i = blockIdx.x * 256ll + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+        const uint2 v = in[i];
+        const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v.x));
+        const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v.y));
+        out[i] = make_float4(lo.x, lo.y, hi.x, hi.y);
+    }
+}
+
 static die_status_t run_model(die_pipeline* p, int B, cudaStream_t s) {
     const die_pipeline_config_t& c = p->cfg;
     const uint32_t* n_miss = &p->ctrl->n_miss;
@@ -485,6 +519,18 @@ static die_status_t run_model(die_pipeline* p, int B, cudaStream_t s) {
     }
     if (c.model == DIE_MODEL_LINEAR_FP32)
         return linear_f32_launch(p->packed_in, p->W, p->bias, p->packed_out, B, c.dim_in, c.dim_out, n_miss, s);
+    if (c.model == DIE_MODEL_MLP_BF16) {
+        // The GEMMs run over all B rows of the staging buffers (the miss count stays on the device): rows past the
+        // misses hold an earlier batch's values and their results are never read.
+        const long long vec = c.dim_in / 4;
+        const int grid = (int)std::min<long long>(((long long)B * vec + 255) / 256, (long long)num_sms() * 8);
+        DIE_LAUNCH(ST_MODEL, s, rows_f32_to_bf16_kernel<<<grid, 256, 0, s>>>(
+            reinterpret_cast<const float4*>(p->packed_in), static_cast<uint2*>(p->mlp_x), vec, B, n_miss));
+        DIE_TRY(mlp_bf16_launch(p->mlp_x, p->mlp_w1, p->mlp_b1, p->mlp_w2, p->mlp_b2, p->mlp_h, p->mlp_y, B, c.dim_in, c.hidden, s));
+        DIE_LAUNCH(ST_MODEL, s, rows_bf16_to_f32_kernel<<<grid, 256, 0, s>>>(
+            static_cast<const uint2*>(p->mlp_y), reinterpret_cast<float4*>(p->packed_out), vec, B, n_miss));
+        return DIE_OK;
+    }
     return linear_tf32_launch(p->packed_in, p->W, p->bias, p->packed_out, B, c.dim_in, c.dim_out, n_miss, s);
 }
 
@@ -730,6 +776,7 @@ die_status_t pipeline_owner_launch_group(die_pipeline* p, const QueueDesc* qd_de
 }
 
 int pipeline_launches_per_step(const die_pipeline* p) {
+    if (p->cfg.model == DIE_MODEL_MLP_BF16) return 7;  // get, claim + pack, to bf16, two GEMMs, to fp32, unpack + evict
     return p->persistent ? 1 : (p->cfg.model == DIE_MODEL_LINEAR_FP32 ? 4 : 3);
 }
 
@@ -764,8 +811,10 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
         DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_create: max_batch > 0 and dims multiple of 4 fp32 required");
     if (cfg->model == DIE_MODEL_ECHO && cfg->dim_in != cfg->dim_out)
         DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_create: echo needs dim_in == dim_out");
-    if (cfg->model < DIE_MODEL_ECHO || cfg->model > DIE_MODEL_LINEAR_TF32)
+    if (cfg->model < DIE_MODEL_ECHO || cfg->model > DIE_MODEL_MLP_BF16)
         DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_create: unknown model %d", cfg->model);
+    if (cfg->model == DIE_MODEL_MLP_BF16 && (cfg->dim_in != cfg->dim_out || cfg->hidden <= 0 || (cfg->hidden & 7) || (cfg->dim_in & 7)))
+        DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_create: the MLP needs dim_in == dim_out and hidden, both multiples of 8");
     if (cfg->model != DIE_MODEL_ECHO && (!cfg->weight || !cfg->bias))
         DIE_FAIL(DIE_ERR_INVALID, "die_pipeline_create: linear model needs weight and bias");
     die_pipeline* p = new die_pipeline();
@@ -781,7 +830,23 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
         DIE_FAIL(DIE_ERR_TOO_LARGE, "die_pipeline_create: max_batch %d exceeds the table's batch limit %llu",
                  cfg->max_batch, (unsigned long long)p->kv->max_chunk);
     DIE_CUDA(cudaMalloc(&p->arena, p->n_rows * cfg->dim_out * sizeof(float)));
-    if (cfg->model != DIE_MODEL_ECHO) {
+    if (cfg->model == DIE_MODEL_MLP_BF16) {
+        const size_t D = (size_t)cfg->dim_in, H = (size_t)cfg->hidden;
+        std::vector<__nv_bfloat16> w(2 * D * H);
+        for (size_t i = 0; i < 2 * D * H; ++i) w[i] = __float2bfloat16_rn(cfg->weight[i]);
+        DIE_CUDA(cudaMalloc(&p->mlp_w1, H * D * 2));
+        DIE_CUDA(cudaMalloc(&p->mlp_w2, D * H * 2));
+        DIE_CUDA(cudaMemcpy(p->mlp_w1, w.data(), H * D * 2, cudaMemcpyHostToDevice));
+        DIE_CUDA(cudaMemcpy(p->mlp_w2, w.data() + H * D, D * H * 2, cudaMemcpyHostToDevice));
+        DIE_CUDA(cudaMalloc(&p->mlp_b1, H * sizeof(float)));
+        DIE_CUDA(cudaMalloc(&p->mlp_b2, D * sizeof(float)));
+        DIE_CUDA(cudaMemcpy(p->mlp_b1, cfg->bias, H * sizeof(float), cudaMemcpyHostToDevice));
+        DIE_CUDA(cudaMemcpy(p->mlp_b2, cfg->bias + H, D * sizeof(float), cudaMemcpyHostToDevice));
+        DIE_CUDA(cudaMalloc(&p->mlp_x, B * D * 2));
+        DIE_CUDA(cudaMalloc(&p->mlp_h, B * H * 2));
+        DIE_CUDA(cudaMalloc(&p->mlp_y, B * D * 2));
+        DIE_CUDA(cudaMemset(p->mlp_x, 0, B * D * 2));
+    } else if (cfg->model != DIE_MODEL_ECHO) {
         DIE_CUDA(cudaMalloc(&p->W, (size_t)cfg->dim_out * cfg->dim_in * sizeof(float)));
         DIE_CUDA(cudaMalloc(&p->bias, (size_t)cfg->dim_out * sizeof(float)));
         DIE_CUDA(cudaMemcpy(p->W, cfg->weight, (size_t)cfg->dim_out * cfg->dim_in * sizeof(float),
@@ -839,7 +904,7 @@ extern "C" die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, di
 extern "C" die_status_t die_pipeline_destroy(die_pipeline_t* p) {
     if (!p) return DIE_OK;
     die_kv_destroy(p->kv);
-    void* bufs[] = {p->arena, p->W, p->bias, p->digests, p->shard, p->code, p->value, p->miss_rank, p->miss_req, p->lrank, p->cta_miss, p->cta_base,
+    void* bufs[] = {p->mlp_w1, p->mlp_w2, p->mlp_b1, p->mlp_b2, p->mlp_x, p->mlp_h, p->mlp_y, p->arena, p->W, p->bias, p->digests, p->shard, p->code, p->value, p->miss_rank, p->miss_req, p->lrank, p->cta_miss, p->cta_base,
                     p->set_slot, p->set_row, p->wmask, p->wcount, p->ctrl, p->packed_in, p->packed_out, p->d_key_bytes,
                     p->d_key_off, p->d_payload, p->d_out, p->d_hit};
     for (void* b : bufs) cudaFree(b);

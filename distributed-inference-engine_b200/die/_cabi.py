@@ -17,7 +17,7 @@ DIE_OK, DIE_ERR_INVALID, DIE_ERR_CUDA, DIE_ERR_NOMEM, DIE_ERR_STOP_ITERATION, DI
     DIE_ERR_UNSUPPORTED, DIE_ERR_VALUE_ERROR = range(8)
 POLICY_IDS = {"lru": 0, "lfu": 1, "fifo": 2}
 LINEAR_FP32, LINEAR_TF32 = 0, 1
-MODEL_ECHO, MODEL_LINEAR_FP32, MODEL_LINEAR_TF32 = 0, 1, 2
+MODEL_ECHO, MODEL_LINEAR_FP32, MODEL_LINEAR_TF32, MODEL_MLP_BF16 = 0, 1, 2, 3
 
 
 class DieError(RuntimeError):
@@ -33,7 +33,7 @@ class FlushDesc(ctypes.Structure):  # die_flush_desc_t
 class PipelineConfig(ctypes.Structure):
     _fields_ = [("kv_max_size", c_uint64), ("default_ttl", c_double), ("max_batch", c_int32),
                 ("dim_in", c_int32), ("dim_out", c_int32), ("model", c_int32), ("max_key_bytes", c_int32),
-                ("reserved", c_int32), ("weight", c_void_p), ("bias", c_void_p)]
+                ("hidden", c_int32), ("weight", c_void_p), ("bias", c_void_p)]
 
 
 P = c_void_p  # device or host pointer passed as an integer address

@@ -17,7 +17,8 @@ from . import _cabi, ops
 from ._cabi import PipelineConfig, check, ptr, require_cuda, stream_ptr
 from .kvstore import DeviceKV
 
-MODEL_IDS = {"echo": _cabi.MODEL_ECHO, "linear": _cabi.MODEL_LINEAR_FP32, "linear_tf32": _cabi.MODEL_LINEAR_TF32}
+MODEL_IDS = {"echo": _cabi.MODEL_ECHO, "linear": _cabi.MODEL_LINEAR_FP32, "linear_tf32": _cabi.MODEL_LINEAR_TF32,
+             "mlp_bf16": _cabi.MODEL_MLP_BF16}
 
 
 class DispatchPipeline:
@@ -27,11 +28,19 @@ class DispatchPipeline:
         self._lib = require_cuda()
         dim_out = dim_in if dim_out is None else dim_out
         self.max_batch, self.dim_in, self.dim_out, self.model = max_batch, dim_in, dim_out, model
+        hidden = 0
+        if model == "mlp_bf16":  # weight = (W1 [H, D], W2 [D, H]), bias = (b1 [H], b2 [D]): BASELINE.json configs[4]
+            w1, w2 = (np.ascontiguousarray(a, dtype=np.float32) for a in weight)
+            b1, b2 = (np.ascontiguousarray(a, dtype=np.float32) for a in bias)
+            hidden = int(w1.shape[0])
+            if w1.shape != (hidden, dim_in) or w2.shape != (dim_out, hidden) or dim_in != dim_out:
+                raise ValueError("mlp_bf16 needs W1 [H, D], W2 [D, H] and dim_in == dim_out == D")
+            weight, bias = np.concatenate([w1.ravel(), w2.ravel()]), np.concatenate([b1.ravel(), b2.ravel()])
         self._w = None if weight is None else np.ascontiguousarray(weight, dtype=np.float32)
         self._b = None if bias is None else np.ascontiguousarray(bias, dtype=np.float32)
         cfg = PipelineConfig(kv_max_size=kv_max_size, default_ttl=math.nan if default_ttl is None else default_ttl,
                              max_batch=max_batch, dim_in=dim_in, dim_out=dim_out, model=MODEL_IDS[model],
-                             max_key_bytes=max_key_bytes, reserved=0,
+                             max_key_bytes=max_key_bytes, hidden=hidden,
                              weight=None if self._w is None else self._w.ctypes.data,
                              bias=None if self._b is None else self._b.ctypes.data)
         h = ctypes.c_void_p()

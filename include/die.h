@@ -260,6 +260,9 @@ typedef struct die_pipeline die_pipeline_t;
 #define DIE_MODEL_ECHO 0
 #define DIE_MODEL_LINEAR_FP32 1
 #define DIE_MODEL_LINEAR_TF32 2
+#define DIE_MODEL_MLP_BF16 3   /* Y = relu(X W1^T + b1) W2^T + b2, bf16 storage, fp32 accumulation (die_mlp_fwd_bf16); dim_in ==
+                                * dim_out = D, hidden = H; weight = W1 [H,D] then W2 [D,H], bias = b1 [H] then b2 [D], fp32 on
+                                * the host, converted once; payload and result rows stay fp32 at the interface */
 
 typedef struct {
     uint64_t kv_max_size;
@@ -269,9 +272,9 @@ typedef struct {
     int32_t dim_out;        /* elements per result (== dim_in for echo) */
     int32_t model;          /* DIE_MODEL_* */
     int32_t max_key_bytes;  /* upper bound of key bytes per batch (host-buffer entry point) */
-    int32_t reserved;
-    const float* weight;    /* [host] [dim_out, dim_in] (linear) or NULL */
-    const float* bias;      /* [host] [dim_out] or NULL */
+    int32_t hidden;         /* DIE_MODEL_MLP_BF16: H (multiple of 8); other models: 0 */
+    const float* weight;    /* [host] [dim_out, dim_in] (linear), W1 then W2 (MLP), or NULL */
+    const float* bias;      /* [host] [dim_out] (linear), b1 then b2 (MLP), or NULL */
 } die_pipeline_config_t;
 
 die_status_t die_pipeline_create(const die_pipeline_config_t* cfg, die_pipeline_t** out);

@@ -28,6 +28,19 @@ def make_model(model, D, rng):
     b = rng.standard_normal(D).astype(np.float32)
     if model == "echo":
         return None, None, (lambda rows: [np.stack([r, np.zeros_like(r)]) for r in rows])
+    if model == "mlp_bf16":
+        H = 2 * D
+        w1 = models.to_bf16((rng.standard_normal((H, D)) / np.sqrt(D)).astype(np.float32))
+        w2 = models.to_bf16((rng.standard_normal((D, H)) / np.sqrt(H)).astype(np.float32))
+        b1, b2 = rng.standard_normal(H).astype(np.float32), rng.standard_normal(D).astype(np.float32)
+
+        def mlp(rows):  # value = (result, per-row tolerance of oracle/models.py: 2**-7 |y| + 1e-2 max|y|)
+            if not rows:
+                return []
+            y = models.mlp_bf16(models.to_bf16(np.stack(rows)), w1, b1, w2, b2)
+            tol = 2.0 ** -7 * np.abs(y) + 1e-2 * np.abs(y).max(axis=1, keepdims=True)
+            return [np.stack([y[i], tol[i]]) for i in range(len(rows))]
+        return (w1, w2), (b1, b2), mlp
 
     def fn(rows):  # value = (result, error scale sum|x w|): cached rows keep the bound of the payload they came from
         if not rows:
@@ -43,6 +56,8 @@ def check_outputs(model, out, want_rows, where):
     got = out.cpu().numpy()
     if model == "echo":
         assert np.array_equal(got, want[:, 0].astype(np.float32)), where
+    elif model == "mlp_bf16":
+        assert np.all(np.abs(got.astype(np.float64) - want[:, 0]) <= want[:, 1]), where
     else:
         rel = 2.0 ** -10 if model == "linear_tf32" else 1e-5
         assert np.all(np.abs(got.astype(np.float64) - want[:, 0]) <= rel * want[:, 1] + 1e-6), where
@@ -56,13 +71,13 @@ def check_owner_state(group, ref):
         assert lru_digests(group.pipes[r]) == [hashlib.md5(k.encode()).digest() for k in want["lru"]], r
 
 
-@pytest.mark.parametrize("world,model", [(2, "echo"), (2, "linear_tf32"), (4, "linear")])
+@pytest.mark.parametrize("world,model", [(2, "echo"), (2, "linear_tf32"), (4, "linear"), (2, "mlp_bf16")])
 def test_loopback_sharded_steps_match_oracle(world, model):
     """Stream-launched steps (die_xchg_step), small owner tables: evictions, TTL expiry, duplicate keys inside
     and across the ranks' batches."""
     from die import ops
     from die.exchange import LoopbackPeerGroup
-    B, D, max_size, ttl, n_ids, steps = 256, 128, 700, 6.0, 1250 * world, 14
+    B, D, max_size, ttl, n_ids, steps = 256, (256 if model == "mlp_bf16" else 128), 700, 6.0, 1250 * world, 14
     rng = np.random.default_rng(100 + world)
     w, b, fn = make_model(model, D, rng)
     group = LoopbackPeerGroup(world, max_size, B, D, w, b, ttl, model=model)

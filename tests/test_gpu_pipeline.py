@@ -152,6 +152,42 @@ def test_seeded_batches_vs_oracle(model, B, kv_size, space, steps):
     assert pipe.kv.sync_status()[2] == 0 or kv_size < B  # large tables never need the sequential replay
 
 
+@pytest.mark.parametrize("B,D,H,kv_size,space,steps", [(700, 256, 512, 2000, 3000, 10), (1024, 512, 256, 600, 1500, 6)])
+def test_mlp_bf16_is_a_pipeline_model(B, D, H, kv_size, space, steps):
+    """BASELINE.json configs[4] as a path (the model forward of fake_model.py:45-58 replaced by the bf16 tcgen05 MLP):
+    route -> probe -> pack the misses -> bf16 MLP -> unpack -> fill, through die_pipeline_run_host and (second table
+    smaller than a batch) the general sequence.  Hit flags, counters and LRU order exact; results within
+    oracle/models.py's MLP tolerance |d| <= 2**-7 |y| + 1e-2 max_j |y_j| per row, cached rows included."""
+    from die.pipeline import DispatchPipeline
+    rng = np.random.default_rng(B + D)
+    w1 = models.to_bf16((rng.standard_normal((H, D)) / np.sqrt(D)).astype(np.float32))
+    w2 = models.to_bf16((rng.standard_normal((D, H)) / np.sqrt(H)).astype(np.float32))
+    b1, b2 = rng.standard_normal(H).astype(np.float32), rng.standard_normal(D).astype(np.float32)
+    pipe = DispatchPipeline(kv_size, B, D, D, model="mlp_bf16", weight=(w1, w2), bias=(b1, b2), default_ttl=9.0)
+
+    def fn(rows):
+        if not rows:
+            return []
+        y = models.mlp_bf16(models.to_bf16(np.stack(rows)), w1, b1, w2, b2)
+        return [y[i] for i in range(len(rows))]
+    ref = OraclePipeline(1, kv_size, 9.0, fn)
+    now = 50.0
+    for step in range(steps):
+        now += float(rng.choice([0.5, 1.0, 4.0]))
+        keys = ["user-%010d" % i for i in rng.integers(0, space, B)]
+        x = rng.standard_normal((B, D)).astype(np.float32)
+        out, hit = pipe.process(keys, x, now)
+        want = ref.process(keys, [x[i] for i in range(B)], now)
+        assert hit.tolist() == want["hit"], step
+        y = np.stack(want["out"])
+        tol = 2.0 ** -7 * np.abs(y) + 1e-2 * np.abs(y).max(axis=1, keepdims=True)
+        assert np.all(np.abs(out.astype(np.float64) - y) <= tol), step
+    st, rs = pipe.kv.stats(), ref.state()[0]
+    assert (st["hits"], st["misses"], st["evictions"], st["size"]) == (rs["hits"], rs["misses"], rs["evictions"], rs["size"])
+    assert st["hits"] > 0 and st["evictions"] > 0
+    assert lru_digests(pipe) == [hashlib.md5(k.encode()).digest() for k in rs["lru"]]
+
+
 def test_device_resident_entry_point_equals_host_entry_point():
     from die import ops
     from die.pipeline import DispatchPipeline
