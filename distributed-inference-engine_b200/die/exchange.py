@@ -141,7 +141,9 @@ class PeerDispatcher:
     torch's symmetric-memory barrier instead (used by the tests as a cross-check)."""
 
     def __init__(self, world: int, rank: int, kv_max_size: int, max_batch: int, dim: int, weight, bias, default_ttl,
-                 model: str = "linear_tf32", group=None, single_call: bool = True):
+                 model: str = "linear_tf32", group=None, single_call: bool = True, owner_max: int = 0):
+        """owner_max: most requests an owner handles per step (default: two ingested batches' worth); a step that
+        exceeds it raises in check().  Size it tightly when the model's cost grows with it (the bf16 MLP)."""
         import ctypes
         import torch.distributed._symmetric_memory as symm
         from . import _cabi, ops
@@ -155,6 +157,8 @@ class PeerDispatcher:
         # hash sharding spreads every batch evenly over the owners: two batches' worth is far beyond any
         # fluctuation (sigma ~ sqrt(B)); a step that exceeds it raises in check() instead of being truncated silently
         self.bmax = (min(world, 2) if single_call else world) * self.cap
+        if owner_max and single_call:
+            self.bmax = min(self.bmax, int(owner_max))
         self.pipe = DispatchPipeline(kv_max_size, self.bmax, dim, dim, model, weight, bias, default_ttl)
         nbytes = int(self.lib.die_xchg_window_bytes(world, self.cap, dim))
         self.sym = symm.empty((nbytes + 3) // 4, dtype=torch.float32, device=self.dev)
