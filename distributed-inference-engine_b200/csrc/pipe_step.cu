@@ -386,16 +386,13 @@ __device__ __forceinline__ void warp_count_add(unsigned long long* ctr, bool pre
         atomicAdd(ctr, negative ? (unsigned long long)(-(long long)__popc(m)) : (unsigned long long)__popc(m));
 }
 
-// The requests request CTA `cta` owns in a step: [q0, q0 + nq).  With a host-known batch size every CTA takes R; when
-// the size only exists on the device (owner pass of the exchange, sized for owner_max but holding about half of it)
-// the batch is spread evenly over all request CTAs instead of filling the first ones with R rows each.
+// The requests request CTA `cta` owns in a step: [q0, q0 + nq).  The batch -- its size may only exist on the device
+// (owner pass of the exchange, sized for owner_max but holding about half of it) -- is spread evenly over all request
+// CTAs instead of filling the first ones with R rows each.
 __device__ __forceinline__ void ps_span(const StepParams& P, int lane_idx, int cta, int& Bs, int& q0, int& nq) {
     Bs = P.B;
-    int Rs = P.R;
-    if (P.n_req_dev) {
-        Bs = min(Bs, (int)__ldcg(P.n_req_dev + (P.lanes ? lane_idx : 0)));
-        Rs = min(P.R, max(4, ((Bs + P.n_req - 1) / P.n_req + 3) & ~3));
-    }
+    if (P.n_req_dev) Bs = min(Bs, (int)__ldcg(P.n_req_dev + (P.lanes ? lane_idx : 0)));
+    const int Rs = min(P.R, max(4, ((Bs + P.n_req - 1) / P.n_req + 3) & ~3));
     q0 = cta * Rs;
     nq = max(0, min(Rs, Bs - q0));
 }
@@ -774,17 +771,23 @@ bool pipe_step_shape(int B, int K, int N, int n_chunks, int* R_out, int* n_req_o
         }
     }
     if (max_ctas < 0) return false;
-    for (int R = 32; R <= PS_MAX_R; R += 32) {
-        if (forced_r && R != forced_r) continue;
-        if ((size_t)R * (N + 4) * 4 > (size_t)PS_M * K * 4) break;  // epilogue staging lives in the consumed A tile
-        const int n_req = ceil_div(B, R);
-        if (n_req + n_chunks <= max_ctas) {
-            *R_out = R;
-            *n_req_out = n_req;
-            return true;
-        }
+    if (forced_r) {  // DIE_STEP_R: exactly R requests per request CTA (experiments)
+        const int n_req = ceil_div(B, forced_r);
+        if (forced_r > PS_MAX_R || (size_t)forced_r * (N + 4) * 4 > (size_t)PS_M * K * 4 || n_req + n_chunks > max_ctas) return false;
+        *R_out = forced_r;
+        *n_req_out = n_req;
+        return true;
     }
-    return false;
+    // As many request CTAs as the SMs left beside the window CTAs (at most one per 32 requests); R = what each of them
+    // must be able to hold.  A batch smaller than B is spread evenly over them (ps_span), so a grid sized for owner_max
+    // works on the usual half-full batch with ~B / (2 n_req) rows per CTA instead of R.
+    const int n_req = std::min(max_ctas - n_chunks, ceil_div(B, 32));
+    if (n_req < 1) return false;
+    const int R = ceil_div(ceil_div(B, n_req), 32) * 32;
+    if (R > PS_MAX_R || (size_t)R * (N + 4) * 4 > (size_t)PS_M * K * 4) return false;  // epilogue staging lives in the consumed A tile
+    *R_out = R;
+    *n_req_out = n_req;
+    return true;
 }
 
 die_status_t pipe_step_launch(const StepRef& sr, const QueueDesc* qv, int n_steps, int B, int n_chunks, int K, int N,
