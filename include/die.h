@@ -312,6 +312,32 @@ die_status_t die_pipeline_run_owner_device_n(die_pipeline_t* p, const uint32_t* 
                                              uint8_t* hit_out, die_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Ingress data format.  The reference's worker takes one JSON document per TCP connection,
+ * {"model", "version", "inputs", "request_id"} (src/worker.py:92-100: reader.read(4096) + json.loads, so a request
+ * cannot exceed 4096 bytes).  The binary replacement is a length-prefixed frame, little-endian, a multiple of 4 bytes:
+ *     die_frame_header_t | key bytes (UTF-8), zero-padded to 4 | fp32 inputs[n_floats]
+ * The host keeps the transport: it hands over a buffer of frames back to back and frame_off[n+1], where each frame
+ * starts (the receive loop knows that from frame_bytes).  die_frame_decode turns them into what the path consumes:
+ * CSR keys (key_bytes_out, key_off_out[n+1]) for die_route_md5 / the pipeline, fixed-width rows payload_out[n, dim]
+ * zero-padded (PACK, src/batcher.py:211, done at the door), request ids, queue = index of "model:version".
+ * status_out[i]: DIE_FRAME_OK, DIE_FRAME_BAD (magic / lengths inconsistent with the frame's extent: empty key, zero row)
+ * or DIE_FRAME_TOO_WIDE (n_floats > dim); *n_bad_out (device) counts the frames that are not OK.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct die_frame_header {
+    uint32_t magic;        /* 0x31454944, "DIE1" */
+    uint32_t frame_bytes;  /* header + padded key + inputs */
+    uint64_t request_id;
+    uint16_t key_len;
+    uint16_t queue;
+    uint32_t n_floats;
+} die_frame_header_t;
+enum { DIE_FRAME_OK = 0, DIE_FRAME_BAD = 1, DIE_FRAME_TOO_WIDE = 2 };
+die_status_t die_frame_decode(const uint8_t* frames, const int64_t* frame_off /*[n+1]*/, int32_t n, int32_t dim,
+                              uint8_t* key_bytes_out, int64_t* key_off_out /*[n+1]*/, float* payload_out /*[n, dim]*/,
+                              uint64_t* request_id_out /*[n]*/, int32_t* queue_out /*[n]*/, uint8_t* status_out /*[n]*/,
+                              uint32_t* n_bad_out, die_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
  * Device-resident Batcher: per-key accumulation with size- and latency-triggered flush, for requests that already
  * live on the GPU.  Replaces Batcher.add_request / _schedule_flush / _flush_batch / _process_batch / stop
  * (src/batcher.py:70-230) for fixed-width payloads: one open batch per key ("model:version", numbered 0..n_queues-1 by

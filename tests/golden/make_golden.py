@@ -491,6 +491,57 @@ def gen_tick_batcher():
     dump("tick_batcher.json", cases)
 
 
+def gen_load_balancer():
+    """The reference LoadBalancer through one scripted session per strategy: picks, pinned requests, failures that take
+    a worker out, recovery, unregistering, statistics (last_seen stripped)."""
+    import src.load_balancer as ref_lb
+
+    def strip(stats):
+        return {w: {k: v for k, v in s.items() if k != "last_seen"} for w, s in stats.items()}
+
+    async def session(strategy):
+        random.seed(4242)
+        lb = ref_lb.LoadBalancer(strategy=ref_lb.LoadBalancerStrategy(strategy), max_failures=2)
+        log = [await lb.get_worker()]                               # no workers yet
+        for i in range(4):
+            lb.register_worker("w%d" % i, "127.0.0.1:%d" % (9100 + i))
+        rng = random.Random(7)
+        script = []
+        for step in range(60):
+            r = rng.random()
+            if r < 0.55:
+                script.append(["get", None])
+            elif r < 0.65:
+                script.append(["get", "w%d" % rng.randrange(5)])     # pinned, sometimes unknown
+            elif r < 0.9:
+                script.append(["stats", "w%d" % rng.randrange(4), rng.random() < 0.6, round(rng.random() / 10, 4)])
+            elif r < 0.95:
+                script.append(["conn", "w%d" % rng.randrange(4), rng.randrange(5)])
+            else:
+                script.append(["unregister" if rng.random() < 0.5 else "register", "w%d" % rng.randrange(4)])
+        for op in script:
+            if op[0] == "get":
+                got = await lb.get_worker(op[1])
+                log.append(list(got) if got else None)
+            elif op[0] == "stats":
+                await lb.update_stats(op[1], op[2], op[3])
+                log.append("ok")
+            elif op[0] == "conn":
+                if op[1] in lb.worker_stats:
+                    lb.worker_stats[op[1]].active_connections = op[2]
+                log.append("ok")
+            elif op[0] == "unregister":
+                log.append(lb.unregister_worker(op[1]))
+            else:
+                lb.register_worker(op[1], "127.0.0.1:9999")
+                log.append("ok")
+        return {"script": script, "log": log, "stats": strip(lb.get_all_stats()), "unknown": lb.get_worker_stats("nope"),
+                "repr": repr(lb)}
+
+    out = {s: asyncio.run(session(s)) for s in ("round_robin", "least_connections", "random", "least_latency")}
+    dump("load_balancer.json", out)
+
+
 def gen_worker():
     ref_fake.asyncio = types.SimpleNamespace(sleep=_no_sleep)
 
@@ -608,5 +659,6 @@ if __name__ == "__main__":
     gen_kv_policies()
     gen_batcher()
     gen_tick_batcher()
+    gen_load_balancer()
     gen_worker()
     gen_pipeline()
