@@ -26,6 +26,8 @@ struct TcScatter {
 };
 die_status_t linear_tf32_scatter_launch(const float* X, const float* W, const float* b, int B, int K, int N,
                                         const uint32_t* n_rows_dev, const TcScatter& sc, cudaStream_t s);
+die_status_t make_tensor_map_2d(void* tm /*CUtensorMap*/, const void* base, int elem_bytes, uint64_t rows, uint64_t cols,
+                                uint32_t box_rows, uint32_t box_cols);
 die_status_t mlp_bf16_launch(const void* X, const void* W1, const float* b1, const void* W2, const float* b2,
                              void* hidden, void* Y, int B, int D, int H, cudaStream_t s);
 

@@ -22,12 +22,7 @@ namespace die {
 constexpr int G_BM = 128, G_BN = 256, G_BK = 64, G_STAGES = 4, G_THREADS = 192;
 constexpr int G_A_BYTES = G_BM * G_BK * 2, G_B_BYTES = G_BN * G_BK * 2, G_STAGE_BYTES = G_A_BYTES + G_B_BYTES;
 
-__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tm, int c0, int c1, uint64_t* bar) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-        ::"r"(tc::smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(c0), "r"(c1), "r"(tc::smem_u32(bar))
-        : "memory");
-}
+using tc::tma_load_2d;
 
 template <bool RELU>
 __global__ void __launch_bounds__(G_THREADS, 1)
@@ -154,19 +149,24 @@ static die_status_t encode_fn(EncodeTiledFn* out) {
     return DIE_OK;
 }
 
-// [rows, K] row-major bf16 -> boxes of [box_rows, 64] (128 bytes inner = one SWIZZLE_128B atom)
-static die_status_t make_map(CUtensorMap* tm, const void* base, uint64_t rows, uint64_t K, uint32_t box_rows) {
+// [rows, cols] row-major, 2- or 4-byte elements -> boxes of [box_rows, box_cols] whose inner extent is 128 bytes = one
+// SWIZZLE_128B atom.  Host-side encode only (no CUDA call): safe inside stream capture.
+die_status_t make_tensor_map_2d(void* tm, const void* base, int elem_bytes, uint64_t rows, uint64_t cols, uint32_t box_rows,
+                                uint32_t box_cols) {
     EncodeTiledFn fn;
     DIE_TRY(encode_fn(&fn));
-    const cuuint64_t dims[2] = {K, rows};
-    const cuuint64_t strides[1] = {K * 2};
-    const cuuint32_t box[2] = {(cuuint32_t)G_BK, box_rows};
+    const cuuint64_t dims[2] = {cols, rows};
+    const cuuint64_t strides[1] = {cols * (uint64_t)elem_bytes};
+    const cuuint32_t box[2] = {box_cols, box_rows};
     const cuuint32_t estr[2] = {1, 1};
-    const CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    const CUresult r = fn(static_cast<CUtensorMap*>(tm), elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                          2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) DIE_FAIL(DIE_ERR_CUDA, "cuTensorMapEncodeTiled failed with %d", (int)r);
     return DIE_OK;
+}
+static die_status_t make_map(CUtensorMap* tm, const void* base, uint64_t rows, uint64_t K, uint32_t box_rows) {
+    return make_tensor_map_2d(tm, base, 2, rows, K, box_rows, (uint32_t)G_BK);
 }
 
 static die_status_t gemm_bf16_launch(const void* A, const void* Bm, const float* bias, void* C, int M, int N, int K,

@@ -9,6 +9,8 @@
 //   - warps 0-3 read the fp32 accumulators with tcgen05.ld (32 lanes x 32 columns), add the bias
 //     and stage the tile in shared memory; all warps then write whole rows with 512-byte coalesced
 //     stores.  The layer is HBM-bound (32 flop/B), so the tensor pipe only has to stay out of the way.
+#include <cuda.h>
+
 #include "model_internal.cuh"
 #include "tc_common.cuh"
 
@@ -273,6 +275,114 @@ linear_tf32_stream_kernel(const float* __restrict__ X, const float* __restrict__
     }
 }
 
+// The same persistent layer with TMA on both sides: one thread asks for the next A tile as K/32 boxes of
+// [128 rows x 32 tf32] (cp.async.bulk.tensor, SWIZZLE_128B: exactly the K-major layout the MMA reads) and, after the
+// eight warps have drained the accumulator into the consumed A tile in that same layout, hands the tile back to the
+// TMA unit as N/32 boxes of the output.  No thread touches global memory for X or Y; what the 256 threads do per tile
+// is tcgen05.ld + st.shared.  Rows past B are zero-filled on the way in and clipped on the way out by the tensor maps.
+__global__ void __launch_bounds__(TC_THREADS, 1)
+linear_tf32_tma_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmY,
+                       const float* __restrict__ W, const float* __restrict__ bias, int B, int K, int N) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+    __shared__ __align__(8) uint64_t bar, full[2];
+    __shared__ uint32_t tmem_base;
+    __shared__ __align__(16) float s_bias[256];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int KB = K / 32, chunks_per_row = K / 4;
+    uint8_t* b_base = smem;
+    uint8_t* a_base0 = smem + (size_t)N * K * 4;
+    const size_t a_bytes = (size_t)TC_M * K * 4;
+    const uint32_t ncols = pow2_cols((uint32_t)N);
+    const int tiles = (B + TC_M - 1) / TC_M;
+    if (warp == 0) tc::tmem_alloc(&tmem_base, ncols);
+    if (tid == 32) {
+        tc::mbar_init(&bar, 1);
+        tc::mbar_init(&full[0], 1);
+        tc::mbar_init(&full[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < N) s_bias[tid] = bias ? bias[tid] : 0.f;
+    for (int e = tid; e < N * chunks_per_row; e += TC_THREADS) {
+        const int r = e / chunks_per_row, ck = e - r * chunks_per_row;
+        cp_async16(b_base + (size_t)(ck >> 3) * ((size_t)N * 128) + tc::sw128_offset(r, ck & 7), W + (size_t)r * K + ck * 4, 16u);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    tc::fence_proxy_async_smem();
+    tc::fence_before_thread_sync();
+    __syncthreads();
+    tc::fence_after_thread_sync();
+    auto load_tile = [&](int t, int buf) {  // one thread
+        tc::mbar_arrive_expect_tx(&full[buf], (uint32_t)a_bytes);
+        uint8_t* a = a_base0 + (size_t)buf * a_bytes;
+        for (int kb = 0; kb < KB; ++kb) tc::tma_load_2d(a + (size_t)kb * (TC_M * 128), &tmX, kb * 32, t * TC_M, &full[buf]);
+    };
+    int t = (int)blockIdx.x;
+    if (tid == 0 && t < tiles) load_tile(t, 0);
+    const uint32_t taddr = tmem_base;
+    const int col_half = (N / 2) % 32 == 0 ? N / 2 : N;
+    unsigned phase = 0;
+    for (int it = 0; t < tiles; t += (int)gridDim.x, ++it) {
+        const int buf = it & 1;
+        uint8_t* a_cur = a_base0 + (size_t)buf * a_bytes;
+        const int t_next = t + (int)gridDim.x;
+        if (tid == 0) {
+            if (t_next < tiles) {
+                tc::bulk_wait_read_all();   // the other buffer's tile (stored one iteration ago) has left shared memory
+                load_tile(t_next, buf ^ 1);
+            }
+            tc::mbar_wait(&full[buf], (unsigned)(it >> 1) & 1u);
+            tc::fence_after_thread_sync();
+            const uint32_t idesc = tc::instr_desc(tc::FMT_TF32, TC_M, (uint32_t)N);
+            const uint32_t a_s = tc::smem_u32(a_cur), b_s = tc::smem_u32(b_base);
+            for (int kb = 0; kb < KB; ++kb) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    tc::mma_tf32(taddr, tc::smem_desc_k_major_sw128(a_s + kb * (TC_M * 128) + j * 32),
+                                 tc::smem_desc_k_major_sw128(b_s + kb * (N * 128) + j * 32), idesc, (kb | j) != 0);
+            }
+            tc::mma_commit(&bar);
+        }
+        tc::mbar_wait(&bar, phase & 1u);
+        ++phase;
+        tc::fence_after_thread_sync();
+        {   // accumulator (+bias) -> the consumed A tile, as N/32 blocks of [128 rows x 128 B], SWIZZLE_128B
+            const int q = warp & 3, row = q * 32 + lane;
+            const int c_lo = col_half == N ? 0 : (warp >> 2) * col_half;
+            const int c_hi = col_half == N ? (warp < 4 ? N : 0) : c_lo + col_half;
+            for (int c0 = c_lo; c0 < c_hi; c0 += 32) {
+                uint32_t v[32];
+                tc::tmem_ld_32x32(taddr + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+                uint8_t* blk = a_cur + (size_t)(c0 >> 5) * (TC_M * 128);
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    const float4 bv = *reinterpret_cast<const float4*>(s_bias + c0 + j);
+                    float4 o;
+                    o.x = __uint_as_float(v[j + 0]) + bv.x;
+                    o.y = __uint_as_float(v[j + 1]) + bv.y;
+                    o.z = __uint_as_float(v[j + 2]) + bv.z;
+                    o.w = __uint_as_float(v[j + 3]) + bv.w;
+                    *reinterpret_cast<float4*>(blk + tc::sw128_offset((uint32_t)row, (uint32_t)(j >> 2))) = o;
+                }
+            }
+        }
+        tc::fence_proxy_async_smem();      // the staged tile is read by the TMA unit
+        tc::fence_before_thread_sync();    // ... and the accumulator is free for the next tile's MMA
+        __syncthreads();
+        if (tid == 0) {
+            for (int cg = 0; cg < N / 32; ++cg) tc::tma_store_2d(&tmY, a_cur + (size_t)cg * (TC_M * 128), cg * 32, t * TC_M);
+            tc::bulk_commit();
+        }
+    }
+    if (tid == 0) tc::bulk_wait_all();
+    __syncthreads();
+    if (warp == 0) {
+        tc::fence_after_thread_sync();
+        tc::tmem_dealloc(taddr, ncols);
+    }
+}
+
 static die_status_t tf32_launch(const float* X, const float* W, const float* b, float* Y, int B, int K, int N,
                                 const uint32_t* n_rows_dev, const TcScatter* scatter, cudaStream_t s) {
     if (B == 0) return DIE_OK;
@@ -284,6 +394,20 @@ static die_status_t tf32_launch(const float* X, const float* W, const float* b, 
     {   // large batches: the persistent streaming form (N a multiple of 32 chunks it can swizzle, rows fit the A tile)
         const size_t smem_s = (size_t)N * K * 4 + 2 * (size_t)TC_M * K * 4 + 1024;
         if (!scatter && tiles >= 2 * num_sms() && smem_s <= 200 * 1024 && N <= K && N % 32 == 0) {
+            static int use_tma = -1;
+            if (use_tma < 0) use_tma = getenv("DIE_TF32_TMA") ? atoi(getenv("DIE_TF32_TMA")) : 1;
+            if (use_tma && !n_rows_dev) {  // exact row count on the host: the tensor maps clip the last tile
+                CUtensorMap tmX, tmY;
+                DIE_TRY(make_tensor_map_2d(&tmX, X, 4, (uint64_t)B, (uint64_t)K, TC_M, 32));
+                DIE_TRY(make_tensor_map_2d(&tmY, Y, 4, (uint64_t)B, (uint64_t)N, TC_M, 32));
+                static bool configured_t = false;
+                if (!configured_t) {
+                    DIE_CUDA(cudaFuncSetAttribute(linear_tf32_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+                    configured_t = true;
+                }
+                DIE_LAUNCH(ST_MODEL, s, linear_tf32_tma_kernel<<<num_sms(), TC_THREADS, smem_s, s>>>(tmX, tmY, W, b, B, K, N));
+                return DIE_OK;
+            }
             static bool configured_s = false;
             if (!configured_s) {
                 DIE_CUDA(cudaFuncSetAttribute(linear_tf32_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
