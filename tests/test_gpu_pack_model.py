@@ -33,9 +33,14 @@ def pack_ref(vals, off, Lpad, src_index=None):
 
 @pytest.mark.parametrize("elem_bytes,n_req,Lpad,min_len", [(4, 256, 2048, 16), (4, 1000, 64, 0), (4, 4096, 128, 128),
                                                            (1, 300, 48, 0), (2, 300, 40, 0), (8, 200, 10, 0),
-                                                           (4, 77, 13, 0), (1, 50, 7, 0)])
-def test_pack_layout_and_unpack_roundtrip(elem_bytes, n_req, Lpad, min_len):
+                                                           (4, 77, 13, 0), (1, 50, 7, 0),
+                                                           # rows of 1 KB and more: the bulk-copy kernels (csrc/pack.cu)
+                                                           (4, 500, 256, 0), (8, 300, 512, 3), (4, 700, 4096, 1),
+                                                           (1, 300, 2048, 0), (2, 300, 1024, 5), (4, 2000, 1024, 1000)])
+def test_pack_layout_and_unpack_roundtrip(elem_bytes, n_req, Lpad, min_len, monkeypatch):
     from die import ops
+    if n_req % 2 == 0:   # half of the shapes through the opt-in bulk-copy kernels (rows of 1 KB and more take them)
+        monkeypatch.setenv("DIE_PACK_BULK", "1")
     rng = np.random.default_rng(n_req + Lpad)
     vals, off, lens = ragged(rng, n_req, Lpad, elem_bytes, min_len)
     v_d, off_d = torch.from_numpy(vals).cuda(), torch.from_numpy(off).cuda()
