@@ -8,9 +8,10 @@
 //                      into a 4-stage shared-memory ring, completion on mbarriers (complete_tx)
 //   warp 1 (one lane)  MMA issuer: 4 x tcgen05.mma.kind::f16 (M128 N256 K16) per stage, accumulator
 //                      128 lanes x 256 columns of TMEM; tcgen05.commit releases the stage / signals the epilogue
-//   warps 2-5          epilogue: tcgen05.ld -> +bias, relu, bf16 -> swizzled shared staging -> 512-byte
-//                      coalesced row stores
-// One 128x256 output tile per CTA (M=1024, N=4096 -> 128 CTAs on 148 SMs).
+//   warps 2-5          epilogue: tcgen05.ld -> +bias, relu, bf16 -> global (64 contiguous bytes per row and chunk: whole
+//                      sectors; no shared staging, the operand ring belongs to the next tile by then)
+// Persistent CTAs (one per SM) walk the 128x256 output tiles; TMEM holds two accumulators so that the epilogue of one
+// tile overlaps the MMAs of the next.
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -30,11 +31,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  const float* __restrict__ bias, __nv_bfloat16* __restrict__ C, int M, int N, int K) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
-    __shared__ __align__(8) uint64_t full[G_STAGES], empty[G_STAGES], tmem_full;
+    __shared__ __align__(8) uint64_t full[G_STAGES], empty[G_STAGES], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_base;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.y * G_BM, n0 = blockIdx.x * G_BN;
     const int num_k = (K + G_BK - 1) / G_BK;
+    const int tiles_n = (N + G_BN - 1) / G_BN, tiles_m = (M + G_BM - 1) / G_BM;
+    const int tiles = tiles_m * tiles_n;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
@@ -43,92 +45,107 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tc::mbar_init(&full[s], 1);
             tc::mbar_init(&empty[s], 1);
         }
-        tc::mbar_init(&tmem_full, 1);
+        for (int a = 0; a < 2; ++a) {
+            tc::mbar_init(&acc_full[a], 1);
+            tc::mbar_init(&acc_empty[a], 4);   // one arrival per epilogue warp
+        }
     }
-    if (warp == 1) tc::tmem_alloc(&tmem_base, 256);
+    if (warp == 1) tc::tmem_alloc(&tmem_base, 512);   // two 128 x 256 fp32 accumulators: all of TMEM
     tc::fence_before_thread_sync();
     __syncthreads();
     tc::fence_after_thread_sync();
     const uint32_t taddr = tmem_base;
 
+    // Persistent: CTA b works on tiles b, b + grid, ... (n fastest, so the CTAs of a wave share a few A row-blocks and
+    // stream the weights from L2).  The operand ring and the accumulator pair run across tile boundaries: while the
+    // epilogue warps drain accumulator i & 1, the MMA warp is already filling the other one with tile i + 1.
     if (warp == 0) {
         if (lane == 0) {  // ---- TMA producer
-            for (int kb = 0; kb < num_k; ++kb) {
-                const int s = kb % G_STAGES;
-                const uint32_t ph = (uint32_t)(kb / G_STAGES) & 1u;
-                tc::mbar_wait(&empty[s], ph ^ 1u);  // slot free (passes at once on a fresh barrier)
-                tc::mbar_arrive_expect_tx(&full[s], G_STAGE_BYTES);
-                uint8_t* a = smem + (size_t)s * G_STAGE_BYTES;
-                tma_load_2d(a, &tmA, kb * G_BK, m0, &full[s]);
-                tma_load_2d(a + G_A_BYTES, &tmB, kb * G_BK, n0, &full[s]);
+            uint32_t it = 0;
+            for (int t = (int)blockIdx.x; t < tiles; t += (int)gridDim.x) {
+                const int m0 = (t / tiles_n) * G_BM, n0 = (t % tiles_n) * G_BN;
+                for (int kb = 0; kb < num_k; ++kb, ++it) {
+                    const uint32_t s = it % G_STAGES, ph = (it / G_STAGES) & 1u;
+                    tc::mbar_wait(&empty[s], ph ^ 1u);  // slot free (passes at once on a fresh barrier)
+                    tc::mbar_arrive_expect_tx(&full[s], G_STAGE_BYTES);
+                    uint8_t* a = smem + (size_t)s * G_STAGE_BYTES;
+                    tma_load_2d(a, &tmA, kb * G_BK, m0, &full[s]);
+                    tma_load_2d(a + G_A_BYTES, &tmB, kb * G_BK, n0, &full[s]);
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {  // ---- MMA issuer
             const uint32_t idesc = tc::instr_desc(tc::FMT_BF16, G_BM, G_BN);
-            for (int kb = 0; kb < num_k; ++kb) {
-                const int s = kb % G_STAGES;
-                const uint32_t ph = (uint32_t)(kb / G_STAGES) & 1u;
-                tc::mbar_wait(&full[s], ph);  // both tiles of the stage have landed
+            uint32_t it = 0, i = 0;
+            for (int t = (int)blockIdx.x; t < tiles; t += (int)gridDim.x, ++i) {
+                const uint32_t acc = i & 1u;
+                tc::mbar_wait(&acc_empty[acc], ((i >> 1) & 1u) ^ 1u);   // the epilogue has drained this accumulator
                 tc::fence_after_thread_sync();
-                const uint32_t a_s = tc::smem_u32(smem + (size_t)s * G_STAGE_BYTES), b_s = a_s + G_A_BYTES;
+                const uint32_t d = taddr + acc * (uint32_t)G_BN;
+                for (int kb = 0; kb < num_k; ++kb, ++it) {
+                    const uint32_t s = it % G_STAGES, ph = (it / G_STAGES) & 1u;
+                    tc::mbar_wait(&full[s], ph);  // both tiles of the stage have landed
+                    tc::fence_after_thread_sync();
+                    const uint32_t a_s = tc::smem_u32(smem + (size_t)s * G_STAGE_BYTES), b_s = a_s + G_A_BYTES;
 #pragma unroll
-                for (int j = 0; j < G_BK / 16; ++j)  // K = 16 bf16 = 32 bytes per instruction
-                    tc::mma_f16(taddr, tc::smem_desc_k_major_sw128(a_s + j * 32), tc::smem_desc_k_major_sw128(b_s + j * 32),
-                                idesc, (kb | j) != 0);
-                tc::mma_commit(&empty[s]);  // the stage is free once these MMAs have read it
+                    for (int j = 0; j < G_BK / 16; ++j)  // K = 16 bf16 = 32 bytes per instruction
+                        tc::mma_f16(d, tc::smem_desc_k_major_sw128(a_s + j * 32), tc::smem_desc_k_major_sw128(b_s + j * 32),
+                                    idesc, (kb | j) != 0);
+                    tc::mma_commit(&empty[s]);  // the stage is free once these MMAs have read it
+                }
+                tc::mma_commit(&acc_full[acc]);  // accumulator complete
             }
-            tc::mma_commit(&tmem_full);  // accumulator complete
         }
-    } else {  // ---- epilogue warps 2..5
-        tc::mbar_wait(&tmem_full, 0);
-        tc::fence_after_thread_sync();
+    } else {  // ---- epilogue warps 2..5: TMEM -> (+bias, relu, bf16) -> global, 64 contiguous bytes per row and chunk
         const int q = warp & 3;  // TMEM lane quarter this warp may read
         const int row = q * 32 + lane;
-        uint8_t* stage = smem;  // the operand ring is idle now: 128 rows x 512 B, 16-byte chunks XOR-swizzled by row
-        for (int c0 = 0; c0 < G_BN; c0 += 32) {
-            uint32_t v[32];
-            tc::tmem_ld_32x32(taddr + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
-            uint32_t packed[16];
+        uint32_t i = 0;
+        for (int t = (int)blockIdx.x; t < tiles; t += (int)gridDim.x, ++i) {
+            const int m0 = (t / tiles_n) * G_BM, n0 = (t % tiles_n) * G_BN;
+            const uint32_t acc = i & 1u;
+            tc::mbar_wait(&acc_full[acc], (i >> 1) & 1u);
+            tc::fence_after_thread_sync();
+            const int gr = m0 + row;
+            for (int c0 = 0; c0 < G_BN; c0 += 32) {
+                uint32_t v[32];
+                tc::tmem_ld_32x32(taddr + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)G_BN + (uint32_t)c0, v);
+                uint32_t packed[16];
 #pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-                float x0 = __uint_as_float(v[j]), x1 = __uint_as_float(v[j + 1]);
-                const int c = n0 + c0 + j;
-                if (bias) {
-                    x0 += c < N ? bias[c] : 0.f;
-                    x1 += c + 1 < N ? bias[c + 1] : 0.f;
+                for (int j = 0; j < 32; j += 2) {
+                    float x0 = __uint_as_float(v[j]), x1 = __uint_as_float(v[j + 1]);
+                    const int c = n0 + c0 + j;
+                    if (bias) {
+                        x0 += c < N ? __ldg(bias + c) : 0.f;
+                        x1 += c + 1 < N ? __ldg(bias + c + 1) : 0.f;
+                    }
+                    if (RELU) {
+                        x0 = fmaxf(x0, 0.f);
+                        x1 = fmaxf(x1, 0.f);
+                    }
+                    const __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
+                    packed[j >> 1] = *reinterpret_cast<const uint32_t*>(&h);
                 }
-                if (RELU) {
-                    x0 = fmaxf(x0, 0.f);
-                    x1 = fmaxf(x1, 0.f);
-                }
-                const __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
-                packed[j >> 1] = *reinterpret_cast<const uint32_t*>(&h);
-            }
+                if (gr < M) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {  // 4 chunks of 8 bf16
-                const int chunk = (c0 >> 3) + j;
-                *reinterpret_cast<uint4*>(stage + (size_t)row * 512 + ((chunk ^ (row & 31)) << 4)) =
-                    make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+                    for (int j = 0; j < 4; ++j) {  // 4 chunks of 8 bf16 (N is a multiple of 8)
+                        const int col = n0 + c0 + j * 8;
+                        if (col < N)
+                            *reinterpret_cast<uint4*>(C + (size_t)gr * N + col) =
+                                make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+                    }
+                }
             }
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
-        const int ew = warp - 2;
-        for (int r = ew; r < G_BM; r += 4) {
-            const int gr = m0 + r;
-            if (gr >= M) break;
-            const int col = n0 + lane * 8;
-            if (col < N) {
-                const uint4 o = *reinterpret_cast<const uint4*>(stage + (size_t)r * 512 + ((lane ^ (r & 31)) << 4));
-                *reinterpret_cast<uint4*>(C + (size_t)gr * N + col) = o;
-            }
+            tc::fence_before_thread_sync();   // this warp's tcgen05.ld of the accumulator are done
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&acc_empty[acc]);
         }
     }
     tc::fence_before_thread_sync();
     __syncthreads();
     if (warp == 1) {
         tc::fence_after_thread_sync();
-        tc::tmem_dealloc(taddr, 256);
+        tc::tmem_dealloc(taddr, 512);
     }
 }
 
@@ -185,7 +202,8 @@ static die_status_t gemm_bf16_launch(const void* A, const void* Bm, const float*
         DIE_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = true;
     }
-    dim3 grid(ceil_div(N, G_BN), ceil_div(M, G_BM));
+    const int tiles = ceil_div(N, G_BN) * ceil_div(M, G_BM);
+    dim3 grid((unsigned)std::min(tiles, num_sms()));   // persistent CTAs, one per SM
     __nv_bfloat16* c = static_cast<__nv_bfloat16*>(C);
     if (relu)
         DIE_LAUNCH(ST_MODEL, s, gemm_bf16_kernel<true><<<grid, G_THREADS, smem, s>>>(tmA, tmB, bias, c, M, N, K));
