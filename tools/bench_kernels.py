@@ -130,7 +130,7 @@ def run(kv_entries=10_000_000, quick=False):
     xs = [torch.empty((1 << 17, 128), dtype=torch.float32, device="cuda").normal_() for _ in range(3)]
     s = timed(lambda i: ops.linear_fwd(xs[i % 3], wd, bd, _cabi.LINEAR_TF32), 8)
     rows = 1 << 17
-    K.append(entry("linear_tf32_kernel", s, rows * 1024 + 65536, rows, "rows", peak, "131072 x 128 -> 128, tcgen05 kind::tf32"))
+    K.append(entry("linear_tf32_kernel", s, rows * 1024 + 65536, rows, "rows", peak, "131072 x 128 -> 128, tcgen05 kind::tf32, TMA in and out (linear_tf32_tma_kernel)"))
     del xs
 
     # ---- bf16 MLP (C5: hidden 4096, batch 8192): the tensor-bound kernel of the path --------------------------------
@@ -147,7 +147,7 @@ def run(kv_entries=10_000_000, quick=False):
     b2 = torch.zeros(Dm, dtype=torch.float32, device="cuda")
     s = timed(lambda i: ops.mlp_fwd_bf16(xs[i % 2], w1, b1, w2, b2), 5)
     flops = 2 * 2.0 * Bm * Dm * Hm
-    out["mlp_bf16"] = {"kernel": "mlp_gemm_kernel x2 (tcgen05 kind::f16, TMA, TMEM)", "batch": Bm, "dim": Dm, "hidden": Hm,
+    out["mlp_bf16"] = {"kernel": "gemm_bf16_kernel x2 (persistent, tcgen05 kind::f16, TMA, two TMEM accumulators)", "batch": Bm, "dim": Dm, "hidden": Hm,
                        "ms_per_forward": round(s * 1e3, 4), "tflops": round(flops / s / 1e12, 1), "peak_tflops": tf_peak,
                        "peak_source": tf_src, "frac_of_tensor_peak": round(flops / s / 1e12 / tf_peak, 4),
                        "rows_per_s": round(Bm / s, 1)}
