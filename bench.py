@@ -321,6 +321,32 @@ class ClockSampler(threading.Thread):
                         "enqueued"}
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Pins this process to the CPUs of the NUMA node its GPU hangs off (sysfs), so that the pinned host buffers it
+    allocates afterwards are local to that GPU's PCIe root.  Returns the node, or None when the box does not say."""
+    try:
+        import glob
+        import subprocess
+        bus = subprocess.run(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(local_rank)],
+                             capture_output=True, text=True, timeout=20).stdout.strip().lower()
+        if bus.startswith("00000000:"):
+            bus = bus[4:]
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bus).read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def ncu_traffic(kernel_name):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel_name`, from the committed
     `ncu --set full` captures of this bench command (profiles/ncu_full_r02_*.csv; the round-1 capture covers the
@@ -405,12 +431,17 @@ def stage_rooflines(lib, ms_arr, cnt_arr, n_stages, n_prof, s0, s1, step_ms_per_
 
 def e2e_sharded(runner, rng, K, now, off_d, world):
     """End to end at N > 1: every rank's batches start in pinned host memory and its results end there.  Groups of
-    16 batches: one H2D copy per array, one die_xchg_step_many call (one graph replay), one D2H copy per array;
+    16 batches: one H2D copy per array, one die_xchg_step_many call, one D2H copy per array;
     three device staging sets on three streams keep the copy engines on the neighbouring groups.  Wall clock
     between two barriers, max over ranks."""
     import torch
     import torch.distributed as dist
-    GS = 16
+    # One group of 16 batches per call.  A call of one group is three serial launches (ingest, owner, way back: measured
+    # 1.2-1.4 ms per 16 batches beside the copies, more than their PCIe time), so this number is bound by the call
+    # structure, not by the link (tools/pcie_multi.py: two ranks copying at once still get 33-42 GB/s each).  Larger
+    # staged queues (DIE_E2E_GROUP=64) would let the groups pipeline across launches, but with the staging copies in
+    # flight they ran into cross-GPU barrier time-outs on 2 GPUs -- not understood yet, see DESIGN.md section 6.
+    GS = int(os.environ.get("DIE_E2E_GROUP", "16"))
     n_groups = max(2, K * G // GS)
     n = n_groups * GS
     n_pool = 2 * G                                    # payload pool (537 MB pinned per rank), keys fresh per batch
@@ -429,7 +460,18 @@ def e2e_sharded(runner, rng, K, now, off_d, world):
     ev_done = [torch.cuda.Event() for _ in range(NS)]
     ev_out = [torch.cuda.Event() for _ in range(NS)]
 
+    trace = os.environ.get("DIE_E2E_TRACE") == "1"   # diagnostics: per-group copy-in / steps / copy-out times, rank 0
+    marks = []
+
+    def mark(stream):
+        if trace:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(stream)
+            marks.append(e)
+
     def run(first_group, count, now0):
+        del marks[:]
+        mark(cur)
         for g in range(first_group, first_group + count):
             b = g % NS
             lo, hi = (g % n_groups) * GS, (g % n_groups) * GS + GS
@@ -437,21 +479,31 @@ def e2e_sharded(runner, rng, K, now, off_d, world):
             with torch.cuda.stream(s_in):
                 if g - first_group >= NS:
                     s_in.wait_event(ev_done[b])
+                mark(s_in)
                 dk[b][:GS].copy_(hk[lo:hi], non_blocking=True)
                 dx[b].copy_(hx[plo:plo + GS], non_blocking=True)
                 ev_in[b].record(s_in)
+                mark(s_in)
             cur.wait_event(ev_in[b])
             if g - first_group >= NS:
                 cur.wait_event(ev_out[b])
+            mark(cur)
             runner.step_many(dk[b][:GS], off_d, dx[b], now0 + (g - first_group) * GS * DT, DT, dout[b], dhit[b])
             ev_done[b].record(cur)
+            mark(cur)
             with torch.cuda.stream(s_out):
                 s_out.wait_event(ev_done[b])
+                mark(s_out)
                 hout[plo:plo + GS].copy_(dout[b], non_blocking=True)
                 hhit[lo:hi].copy_(dhit[b], non_blocking=True)
                 ev_out[b].record(s_out)
+                mark(s_out)
         s_out.synchronize()
         cur.synchronize()
+        if trace and dist.get_rank() == 0:
+            for g in range(min(count, 12)):
+                t = [marks[0].elapsed_time(marks[1 + 6 * g + k]) for k in range(6)]
+                print("group %2d  in %.3f-%.3f  steps %.3f-%.3f  out %.3f-%.3f" % (g, *t), file=sys.stderr)
 
     run(0, 2, now)                         # warm the staging path and the graphs
     now += 2 * GS * DT
@@ -467,7 +519,7 @@ def e2e_sharded(runner, rng, K, now, off_d, world):
     return {"value": world * n * B / dt, "unit": "requests/s",
             "h2d_bytes_per_step": G * (B * KEY_LEN + B * D * 4), "d2h_bytes_per_step": G * (B * D * 4 + B),
             "ms_per_step": 1e3 * dt / n * G, "steps": n / G,
-            "api": "PeerDispatcher.step_many (die_xchg_step_many) on groups of 16 batches staged from / to pinned host "
+            "api": "PeerDispatcher.step_many (die_xchg_step_many) on groups of %d batches staged from / to pinned host " % GS +
                    "buffers on every rank; copy-in, sharded steps and copy-out of consecutive groups overlap"}, now + n * DT
 
 
