@@ -778,16 +778,20 @@ bool pipe_step_shape(int B, int K, int N, int n_chunks, int* R_out, int* n_req_o
         *n_req_out = n_req;
         return true;
     }
-    // As many request CTAs as the SMs left beside the window CTAs (at most one per 32 requests); R = what each of them
-    // must be able to hold.  A batch smaller than B is spread evenly over them (ps_span), so a grid sized for owner_max
-    // works on the usual half-full batch with ~B / (2 n_req) rows per CTA instead of R.
-    const int n_req = std::min(max_ctas - n_chunks, ceil_div(B, 32));
-    if (n_req < 1) return false;
-    const int R = ceil_div(ceil_div(B, n_req), 32) * 32;
-    if (R > PS_MAX_R || (size_t)R * (N + 4) * 4 > (size_t)PS_M * K * 4) return false;  // epilogue staging lives in the consumed A tile
-    *R_out = R;
-    *n_req_out = n_req;
-    return true;
+    // The fewest rows per request CTA (a multiple of 32) whose grid fits beside the window CTAs.  A grid sized for
+    // owner_max (2 x the usual batch) therefore leaves SMs free: wanted, since the sharded step's copy and barrier
+    // kernels run beside this one and a cooperative grid that needs every SM waits for each of them to go idle.
+    // The batch itself is spread evenly over the request CTAs (ps_span), whatever R allows.
+    for (int R = 32; R <= PS_MAX_R; R += 32) {
+        if ((size_t)R * (N + 4) * 4 > (size_t)PS_M * K * 4) break;  // epilogue staging lives in the consumed A tile
+        const int n_req = ceil_div(B, R);
+        if (n_req + n_chunks <= max_ctas) {
+            *R_out = R;
+            *n_req_out = n_req;
+            return true;
+        }
+    }
+    return false;
 }
 
 die_status_t pipe_step_launch(const StepRef& sr, const QueueDesc* qv, int n_steps, int B, int n_chunks, int K, int N,
