@@ -439,8 +439,8 @@ def e2e_sharded(runner, rng, K, now, off_d, world):
     # One group of 16 batches per call.  A call of one group is three serial launches (ingest, owner, way back: measured
     # 1.2-1.4 ms per 16 batches beside the copies, more than their PCIe time), so this number is bound by the call
     # structure, not by the link (tools/pcie_multi.py: two ranks copying at once still get 33-42 GB/s each).  Larger
-    # staged queues (DIE_E2E_GROUP=64) would let the groups pipeline across launches, but with the staging copies in
-    # flight they ran into cross-GPU barrier time-outs on 2 GPUs -- not understood yet, see DESIGN.md section 6.
+    # staged queues (DIE_E2E_GROUP=64) let the groups pipeline across launches but measured slower beside the staging
+    # copies (4-5 ms per 64 batches), see DESIGN.md section 6.
     GS = int(os.environ.get("DIE_E2E_GROUP", "16"))
     n_groups = max(2, K * G // GS)
     n = n_groups * GS
