@@ -13,10 +13,11 @@
 // Return window of a rank:   back  [world][cap][dim_out + 4]    region d is written only by owner d:
 //                                   result row, then one 16-byte tail whose first word is the hit flag
 // cap = the ingest batch size, so no (source, owner) region can overflow whatever the key distribution.
-// The fused step routes with md5 mod world only: it assumes every rank of the group is up (a rank that is not
-// cannot run its barriers either).  Router's health gate and failover (router.py:165-221) are served by
-// die_route_md5 + die_bucket_by_shard and the stand-alone phase entry points below; an owner is sized for
-// owner_max requests per step and a step that exceeds it raises the error die_xchg_check_sync reports.
+// Every rank of the group must be up (a rank that is not cannot run its barriers either); which owners the ROUTER
+// considers usable is a separate matter: die_xchg_set_health hands the route kernel the health gate and failover list
+// of router.py:165-221 (same arithmetic as die_route_md5), requests without an owner come back as zeros with shard -1.
+// An owner is sized for owner_max requests per step and a step that exceeds it -- failover can do that -- raises the
+// error die_xchg_check_sync reports.
 // Owners see the sources in rank order, request order kept inside each source: the order the CPU oracle's
 // process_exchange applies.
 //
@@ -167,9 +168,20 @@ xchg_scatter_perm_kernel(StepRef sr, const int4* __restrict__ back, const int32_
 //     (requests for that owner in earlier CTAs) + (rank inside its CTA)         -- request order, as the
 // oracle's process_exchange applies -- and the dispatch and scatter kernels work in request order straight from
 // these two small arrays: nothing is sorted, nothing is gathered through a permutation.
+// The router's view of the owners (Router.route_request's health gate and _find_alternative_shard, router.py:165-221),
+// device-resident so that replayed route kernels see an update without being re-captured: shard p = md5 mod world is
+// taken if routable[p]; else, with failover, healthy_idx[md5 mod n_healthy]; else the request has no owner (None).
+struct XchgHealth {
+    int32_t enabled;   // 0: every rank routable (md5 mod world)
+    int32_t failover, n_healthy;
+    int32_t healthy_idx[XCHG_MAX_WORLD];
+    uint8_t routable[XCHG_MAX_WORLD];
+};
+
 __global__ void __launch_bounds__(ROUTE_THREADS)
 xchg_route_kernel(StepRef sr, int B, int world, int32_t* __restrict__ shard_out, uint4* __restrict__ digests,
-                  int32_t* __restrict__ loc, int32_t* __restrict__ cta_cnt /*[gridDim.x][XCHG_MAX_WORLD]*/) {
+                  int32_t* __restrict__ loc, int32_t* __restrict__ cta_cnt /*[gridDim.x][XCHG_MAX_WORLD]*/,
+                  const XchgHealth* __restrict__ health) {
     __shared__ __align__(16) uint8_t stage[ROUTE_STAGE_BYTES + 32];
     __shared__ int wcnt[ROUTE_THREADS / 32][XCHG_MAX_WORLD];
     const StepArgs a = step_resolve(sr);
@@ -184,16 +196,18 @@ xchg_route_kernel(StepRef sr, int B, int world, int32_t* __restrict__ shard_out,
     if (active) {
         digests[i] = make_uint4(st.a, st.b, st.c, st.d);
         d = (int)md5_mod(st, (uint32_t)world);
+        if (health->enabled && !health->routable[d])
+            d = health->failover && health->n_healthy > 0 ? health->healthy_idx[md5_mod(st, (uint32_t)health->n_healthy)] : -1;
         shard_out[i] = d;
     }
     const unsigned peers = __match_any_sync(0xffffffffu, d);  // lanes of this warp with the same owner
     const int rank_w = __popc(peers & ((1u << lane) - 1u));
-    if (active && rank_w == 0) wcnt[warp][d] = __popc(peers);
+    if (active && d >= 0 && rank_w == 0) wcnt[warp][d] = __popc(peers);
     __syncthreads();
     if (active) {
         int r = rank_w;
-        for (int w = 0; w < warp; ++w) r += wcnt[w][d];
-        loc[i] = (d << 16) | r;
+        for (int w = 0; w < warp && d >= 0; ++w) r += wcnt[w][d];
+        loc[i] = d >= 0 ? (d << 16) | r : -1;   // -1: no owner, the request is answered with zeros (Router returns None)
     }
     if (tid < world) {
         int c = 0;
@@ -238,6 +252,7 @@ xchg_dispatch_kernel(StepRef sr, const int4* __restrict__ digests, const int32_t
     const long long warps = (long long)gridDim.x * 8;
     for (long long q = blockIdx.x * 8ll + (threadIdx.x >> 5); q < B; q += warps) {
         const int l = loc[q];
+        if (l < 0) continue;   // no owner
         const int d = l >> 16;
         const long long i = s_off[(q >> 8) * world + d] + (l & 0xffff);
         int4* dst = static_cast<int4*>(rows.p[d]) + ((long long)rank * cap + i) * rv;
@@ -262,6 +277,11 @@ xchg_scatter_kernel(StepRef sr, const int4* __restrict__ back, const int32_t* __
     const long long warps = (long long)gridDim.x * 8;
     for (long long q = blockIdx.x * 8ll + (threadIdx.x >> 5); q < B; q += warps) {
         const int l = loc[q];
+        if (l < 0) {   // no owner: zeros, not a hit
+            for (int c = lane; c < vout; c += 32) stg_stream(out + q * vout + c, make_int4(0, 0, 0, 0));
+            if (lane == 0) hit[q] = 0;
+            continue;
+        }
         const int d = l >> 16;
         const long long i = s_off[(q >> 8) * world + d] + (l & 0xffff);
         const int4* src = back + ((long long)d * cap + i) * rv;  // peer-written: read at L2
@@ -462,6 +482,7 @@ struct die_xchg {
     uint8_t* ring_hit;
     uint32_t* ring_ndev;
     bool owner_group;     // the owner pipeline has the persistent form: groups are replayed software-pipelined
+    XchgHealth* health;   // device: the router's view of the owners (die_xchg_set_health)
 };
 
 static size_t xchg_rows_bytes(int world, int cap, int dim) { return (size_t)world * cap * (dim + 4) * sizeof(float); }
@@ -548,6 +569,8 @@ extern "C" die_status_t die_xchg_create(int32_t world, int32_t rank, int32_t cap
     DIE_CUDA(cudaMalloc(&x->error_flag, sizeof(unsigned int)));
     DIE_CUDA(cudaMemset(x->error_flag, 0, sizeof(unsigned int)));
     DIE_CUDA(cudaMalloc(&x->qdesc, 2 * sizeof(QueueDesc)));
+    DIE_CUDA(cudaMalloc(&x->health, sizeof(XchgHealth)));
+    DIE_CUDA(cudaMemset(x->health, 0, sizeof(XchgHealth)));
     x->owner_group = pipeline_owner_group_supported(pipe, x->bmax);
     DIE_CUDA(cudaStreamCreateWithFlags(&x->cap_stream, cudaStreamNonBlocking));
     x->graph_steps = 16;
@@ -575,6 +598,7 @@ extern "C" die_status_t die_xchg_destroy(die_xchg_t* x) {
     for (int g = 0; g < x->n_graphs; ++g) cudaGraphExecDestroy(x->graphs[g].exec);
     if (x->cap_stream) cudaStreamDestroy(x->cap_stream);
     cudaFree(x->qdesc);
+    cudaFree(x->health);
     cudaFree(x->ring_dig); cudaFree(x->ring_pay); cudaFree(x->ring_out); cudaFree(x->ring_hit); cudaFree(x->ring_ndev);
     if (x->entry) cudaEventDestroy(x->entry);
     cudaFree(x->error_flag);
@@ -610,7 +634,7 @@ static die_status_t xchg_launch_step(die_xchg* x, int lane, const StepRef& user,
         // ---- stage 1, ingest: this set's scratch and windows are free once its previous step has scattered
         if (L.used) DIE_CUDA(cudaStreamWaitEvent(s, L.done, 0));
         DIE_LAUNCH(ST_ROUTE, s, xchg_route_kernel<<<n_cta, ROUTE_THREADS, 0, s>>>(
-            user, B, W, shard, reinterpret_cast<uint4*>(L.digests), L.loc, L.cta_cnt));
+            user, B, W, shard, reinterpret_cast<uint4*>(L.digests), L.loc, L.cta_cnt, x->health));
         DIE_LAUNCH(ST_XCHG, s, xchg_dispatch_kernel<<<grid_for_rows(B), 256, off_bytes, s>>>(
             user, reinterpret_cast<const int4*>(L.digests), L.loc, L.cta_cnt, n_cta, B, vdim, W, x->rank, x->cap, L.rows,
             L.counts));
@@ -926,6 +950,29 @@ extern "C" die_status_t die_xchg_prepare(die_xchg_t* x, int32_t B) {
         for (int set0 = 0; set0 < XCHG_SETS && st == DIE_OK; set0 += K) st = xchg_graph_get(x, B, K, 0, set0 % XCHG_SETS, &exec);
     }
     return st;
+}
+
+// The router's health view for the steps enqueued after this call (every rank of the group must pass the same one).
+// routable == nullptr: back to plain md5 mod world.
+extern "C" die_status_t die_xchg_set_health(die_xchg_t* x, const uint8_t* routable, const int32_t* healthy_idx,
+                                            int32_t n_healthy, int32_t failover, die_stream_t stream) {
+    if (!x || n_healthy < 0 || n_healthy > x->world || (n_healthy > 0 && !healthy_idx))
+        DIE_FAIL(DIE_ERR_INVALID, "die_xchg_set_health: bad arguments");
+    XchgHealth h;
+    memset(&h, 0, sizeof(h));
+    if (routable) {
+        h.enabled = 1;
+        h.failover = failover ? 1 : 0;
+        h.n_healthy = n_healthy;
+        for (int i = 0; i < x->world; ++i) h.routable[i] = routable[i] ? 1 : 0;
+        for (int i = 0; i < n_healthy; ++i) {
+            if (healthy_idx[i] < 0 || healthy_idx[i] >= x->world) DIE_FAIL(DIE_ERR_INVALID, "die_xchg_set_health: healthy_idx out of range");
+            h.healthy_idx[i] = healthy_idx[i];
+        }
+    }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    DIE_CUDA(cudaMemcpyAsync(x->health, &h, sizeof(h), cudaMemcpyHostToDevice, s));  // pageable source: staged before return
+    return DIE_OK;
 }
 
 // Synchronises and reports whether a barrier of this context ever timed out (a peer stopped calling).

@@ -97,6 +97,7 @@ SIGNATURES = {
     "die_xchg_step_many": (c_int32, [P, c_int32, P, c_int64, P, c_int64, c_int32, P, c_double, c_double, P, P, c_int32, P]),
     "die_xchg_check_sync": (c_int32, [P, P]),
     "die_xchg_prepare": (c_int32, [P, c_int32]),
+    "die_xchg_set_health": (c_int32, [P, P, P, c_int32, c_int32, P]),
     "die_frame_decode": (c_int32, [P, P, c_int32, c_int32, P, P, P, P, P, P, P, P]),
     "die_batcher_create": (c_int32, [c_int32, c_int32, c_double, c_int32, c_int32, c_int32, P, P, POINTER(c_void_p)]),
     "die_batcher_destroy": (c_int32, [P]),

@@ -127,6 +127,20 @@ class ShardedDispatcher:
         return out, hit2.reshape(-1), shard
 
 
+def _set_health(lib, cabi, x, world, routable, healthy, failover):
+    import ctypes
+    if routable is None:
+        cabi.check(lib.die_xchg_set_health(x, None, None, 0, 1 if failover else 0, cabi.stream_ptr()))
+        return
+    if len(routable) != world:
+        raise ValueError("routable must have one entry per rank")
+    r = (ctypes.c_uint8 * world)(*[1 if v else 0 for v in routable])
+    healthy = list(healthy or [])
+    h = (ctypes.c_int32 * max(len(healthy), 1))(*healthy)
+    cabi.check(lib.die_xchg_set_health(x, ctypes.addressof(r), ctypes.addressof(h) if healthy else None, len(healthy),
+                                       1 if failover else 0, cabi.stream_ptr()))
+
+
 class PeerDispatcher:
     """The same dispatch over NVLink by direct peer stores (csrc/exchange.cu): no collective, no host sync.
 
@@ -234,6 +248,11 @@ class PeerDispatcher:
                                                      0 if shared else key_off.stride(0), B, ptr(payload), now0, now_step,
                                                      ptr(out), ptr(hit), out.shape[0], self._cabi.stream_ptr()))
 
+    def set_health(self, routable=None, healthy=None, failover: bool = True) -> None:
+        """The router's view of the owners for the following steps: `Router.health_masks(shards, prefer_healthy)` gives
+        both lists.  None: every rank routable.  Every rank must pass the same view."""
+        _set_health(self.lib, self._cabi, self._x, self.world, routable, healthy, failover)
+
     def check(self) -> None:
         self._cabi.check(self.lib.die_xchg_check_sync(self._x, self._cabi.stream_ptr()))
 
@@ -269,11 +288,22 @@ class LoopbackPeerGroup:
         self.windows = [torch.zeros((nbytes + 3) // 4, dtype=torch.float32, device=self.dev) for _ in range(world)]
         self._peers = (ctypes.c_void_p * world)(*[w.data_ptr() for w in self.windows])
         self._x = []
-        for r in range(world):
-            h = ctypes.c_void_p()
-            _cabi.check(self.lib.die_xchg_create(world, r, self.cap, dim, self.bmax, self.pipes[r]._h, self._peers,
-                                                 ctypes.byref(h)))
-            self._x.append(h.value)
+        # All ranks' stage streams live on ONE device here and a barrier kernel spins on its stream's hardware queue until
+        # its peers arrive: the group's streams (2 * ways + 1 per rank) must fit the device's 32 queues with room for the
+        # callers' streams, or a peer's kernel can sit behind the very barrier that waits for it.
+        import os
+        ways_before = os.environ.get("DIE_XCHG_WAYS")
+        if ways_before is None:
+            os.environ["DIE_XCHG_WAYS"] = str(max(1, min(4, (24 // world - 1) // 2)))
+        try:
+            for r in range(world):
+                h = ctypes.c_void_p()
+                _cabi.check(self.lib.die_xchg_create(world, r, self.cap, dim, self.bmax, self.pipes[r]._h, self._peers,
+                                                     ctypes.byref(h)))
+                self._x.append(h.value)
+        finally:
+            if ways_before is None:
+                del os.environ["DIE_XCHG_WAYS"]
         self.streams = [torch.cuda.Stream() for _ in range(world)]
         torch.cuda.synchronize()
         if _warm:
@@ -304,6 +334,11 @@ class LoopbackPeerGroup:
     def maintain(self):
         for p in self.pipes:
             p.kv.maintain(force=False)
+
+    def set_health(self, routable=None, healthy=None, failover: bool = True) -> None:
+        for r, h in enumerate(self._x):
+            with torch.cuda.stream(self.streams[r]):
+                _set_health(self.lib, self._cabi, h, self.world, routable, healthy, failover)
 
     def step(self, keys, payloads, now: float):
         """keys[r] / payloads[r]: the batch rank r ingests.  -> [(out, hit, shard)] per rank."""

@@ -429,6 +429,15 @@ die_status_t die_xchg_check_sync(die_xchg_t* x, die_stream_t stream);
  * die_xchg_step_many(B, ...) of this context would use: keeps graph instantiation (which may allocate and
  * synchronise the device) out of the first serving call. */
 die_status_t die_xchg_prepare(die_xchg_t* x, int32_t B);
+/* The Router's view of the owners for the steps enqueued afterwards (Router.route_request's health gate and
+ * _find_alternative_shard, src/router.py:165-221; same arithmetic as die_route_md5): routable[world] [host] and the
+ * ordered positions of the HEALTHY shards.  A request whose shard is not routable goes to
+ * healthy_idx[md5 mod n_healthy] when failover is on and to nobody otherwise (shard -1, zero row, not a hit).
+ * routable == NULL: every rank routable.  Every rank of the group passes the same view; a rank marked unhealthy still
+ * takes part in the step's barriers (it is the router's opinion, not a dead process).  With failover an owner can
+ * receive more than its share: size owner_max for it, an overflow is reported by die_xchg_check_sync. */
+die_status_t die_xchg_set_health(die_xchg_t* x, const uint8_t* routable /*[host]*/, const int32_t* healthy_idx /*[host]*/,
+                                 int32_t n_healthy, int32_t failover, die_stream_t stream);
 
 /* A queue of n flushed batches in one call (each batch is still one pass of the path, applied strictly in
  * order): batch j reads key_bytes + j*key_bytes_stride, key_off + j*key_off_stride (0 = shared offsets),

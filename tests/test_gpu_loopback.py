@@ -13,6 +13,7 @@ import pytest
 import torch
 
 from oracle import models
+from oracle import ref_port as rp
 from oracle.pipeline import OraclePipeline
 
 pytestmark = pytest.mark.gpu
@@ -139,3 +140,58 @@ def test_loopback_replayed_queue_matches_oracle(monkeypatch, owner_group):
     assert group.lib.die_replay_count() - replays0 == world * groups
     check_owner_state(group, ref)
     assert all(s["evictions"] > 0 for s in ref.state())
+
+
+@pytest.mark.parametrize("failover", [True, False])
+def test_loopback_sharded_steps_follow_the_router_health_gate(failover):
+    """Router.route_request's health gate and _find_alternative_shard (router.py:165-221) on the fused sharded step
+    (die_xchg_set_health): one of four owners is marked unhealthy after a few steps and recovers later.  With failover
+    its keys go to healthy_idx[md5 mod n_healthy]; without, those requests have no owner (shard -1, zero row, no hit).
+    Single steps and a replayed queue; shard ids, hit flags, results, owner tables against the oracle's PortRouter."""
+    from die import ops
+    from die.exchange import LoopbackPeerGroup
+    world, B, D, max_size, ttl, n_ids = 4, 256, 128, 900, 50.0, 3000
+    rng = np.random.default_rng(5 if failover else 6)
+    model = "linear"
+    w, b, fn = make_model(model, D, rng)
+    group = LoopbackPeerGroup(world, max_size, B, D, w, b, ttl, model=model)
+    ref = OraclePipeline(world, max_size, ttl, fn, failover_enabled=failover)
+
+    def healthy_flags():
+        return [ref.router.workers["w%d" % s][0] == rp.HEALTHY for s in range(world)]
+
+    def step(now):
+        per_rank = [(["user-%010d" % i for i in rng.integers(0, n_ids, B)],
+                     rng.standard_normal((B, D)).astype(np.float32)) for _ in range(world)]
+        res = group.step([ops.KeyBatch.from_strings(k) for k, _ in per_rank],
+                         [torch.from_numpy(p).cuda() for _, p in per_rank], now)
+        want = ref.process_exchange([(k, [r for r in p]) for k, p in per_rank], now)
+        for r in range(world):
+            out, hit, shard = res[r]
+            assert shard.tolist() == want[r]["shard"], r
+            assert hit.tolist() == want[r]["hit"], r
+            rows = [np.stack([np.zeros(D), np.zeros(D)]) if o is None else o for o in want[r]["out"]]
+            check_outputs(model, out, rows, r)
+        group.maintain()   # table housekeeping between steps: inside one it would synchronise the device all ranks share
+        return sum(1 for r in range(world) for s in want[r]["shard"] if s < 0)
+
+    now = 1.0
+    for _ in range(3):
+        now += 1.0
+        assert step(now) == 0
+    for _ in range(3):
+        ref.router.mark_worker_failure("w2")
+    flags = healthy_flags()
+    assert flags == [True, True, False, True]
+    group.set_health([1 if f else 0 for f in flags], [i for i, f in enumerate(flags) if f], failover)
+    dropped = 0
+    for _ in range(4):
+        now += 1.0
+        dropped += step(now)
+    assert (dropped == 0) == failover
+    ref.router.mark_worker_success("w2")
+    group.set_health(None)
+    for _ in range(3):
+        now += 1.0
+        assert step(now) == 0
+    check_owner_state(group, ref)
