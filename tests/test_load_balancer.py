@@ -77,3 +77,33 @@ def test_health_check_marks_and_recovers_workers():
 
     picks, pinned, healthy_b, back, probes_a = asyncio.run(run())
     assert picks == {"a"} and pinned is None and healthy_b is False and back is True and probes_a >= 3
+
+
+def test_wire_frames_encode_and_split_on_the_host():
+    """die.wire's host half (no GPU): frames carry the fields of the reference's JSON request (worker.py:96-100), the
+    receive-loop walk finds every frame start from the length prefixes and stops at a prefix that leaves the buffer;
+    the CPU reading of the same bytes (oracle/wire.py, what the GPU decode is checked against) gets the fields back."""
+    import struct
+
+    import numpy as np
+    from die import wire
+    from oracle import wire as owire
+    reqs = [(7, "user-0000000001", 0, [1.0, 2.5]), (2**64 - 1, "", 3, []), (9, "ключ-é", 1, list(range(9)))]
+    frames = [wire.encode_request(*r) for r in reqs]
+    assert all(len(f) % 4 == 0 for f in frames)
+    buf = b"".join(frames)
+    offs = wire.split_frames(buf)
+    assert offs.tolist() == [0, len(frames[0]), len(frames[0]) + len(frames[1]), len(buf)]
+    got = owire.decode(buf, offs, 16)
+    for (rid, key, q, x), (st, grid, gq, gkey, row) in zip(reqs, got):
+        assert (st, grid, gq, gkey) == (0, rid, q, key.encode())
+        assert row[:len(x)].tolist() == [float(v) for v in x] and not row[len(x):].any()
+    # a prefix that points past the buffer ends the walk: one trailing bad frame
+    cut = bytearray(buf)
+    struct.pack_into("<I", cut, len(frames[0]) + 4, 1 << 20)
+    offs = wire.split_frames(bytes(cut))
+    assert offs.tolist() == [0, len(frames[0]), len(buf)]
+    assert [g[0] for g in owire.decode(bytes(cut), offs, 16)] == [0, 1]
+    assert owire.decode(wire.encode_request(1, "k", 0, np.ones(17)), [0, 24 + 4 + 68], 16)[0][0] == 2   # too wide
+    with pytest.raises(ValueError):
+        wire.encode_request(1, "k" * 70000, 0, [])
