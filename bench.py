@@ -431,17 +431,16 @@ def stage_rooflines(lib, ms_arr, cnt_arr, n_stages, n_prof, s0, s1, step_ms_per_
 
 def e2e_sharded(runner, rng, K, now, off_d, world):
     """End to end at N > 1: every rank's batches start in pinned host memory and its results end there.  Groups of
-    16 batches: one H2D copy per array, one die_xchg_step_many call, one D2H copy per array;
+    64 batches: one H2D copy per array, one die_xchg_step_many call, one D2H copy per array;
     three device staging sets on three streams keep the copy engines on the neighbouring groups.  Wall clock
     between two barriers, max over ranks."""
     import torch
     import torch.distributed as dist
-    # One group of 16 batches per call.  A call of one group is three serial launches (ingest, owner, way back: measured
-    # 1.2-1.4 ms per 16 batches beside the copies, more than their PCIe time), so this number is bound by the call
-    # structure, not by the link (tools/pcie_multi.py: two ranks copying at once still get 33-42 GB/s each).  Larger
-    # staged queues (DIE_E2E_GROUP=64) let the groups pipeline across launches but measured slower beside the staging
-    # copies (4-5 ms per 64 batches), see DESIGN.md section 6.
-    GS = int(os.environ.get("DIE_E2E_GROUP", "16"))
+    # 64 batches per call: die_xchg_step_many pipelines its groups of 16 across launches (ingest | owner | way back), so a
+    # call of one group would be three serial launches (measured 1.2-1.4 ms per 16 batches beside the copies, more than
+    # their PCIe time: 59 M requests/s at N = 2) while four groups per call cost six (101 M).  The warm-up is long enough
+    # (24 calls) to take the tables' first housekeeping -- a one-time stall of ~0.5 s -- out of the timed region.
+    GS = int(os.environ.get("DIE_E2E_GROUP", "64"))
     n_groups = max(2, K * G // GS)
     n = n_groups * GS
     n_pool = 2 * G                                    # payload pool (537 MB pinned per rank), keys fresh per batch
@@ -505,8 +504,9 @@ def e2e_sharded(runner, rng, K, now, off_d, world):
                 t = [marks[0].elapsed_time(marks[1 + 6 * g + k]) for k in range(6)]
                 print("group %2d  in %.3f-%.3f  steps %.3f-%.3f  out %.3f-%.3f" % (g, *t), file=sys.stderr)
 
-    run(0, 2, now)                         # warm the staging path and the graphs
-    now += 2 * GS * DT
+    n_warm = int(os.environ.get("DIE_E2E_WARM_GROUPS", "24"))
+    run(0, n_warm, now)                    # warm the staging path and the graphs
+    now += n_warm * GS * DT
     torch.cuda.synchronize()
     dist.barrier()
     t0 = time.perf_counter()
